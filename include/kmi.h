@@ -1,0 +1,160 @@
+/* kmi.h — C ABI of the B200-native k-mer index construction path (libkmi.so).
+ *
+ * Drop-in boundary for ParBLiSS/kmerind's `bliss::index::kmer::Index<MapType, KmerParser>`
+ * (reference src/index/kmer_index.hpp:98-394) on the build / count / find / erase path. The
+ * reference has no FFI: its boundary is a C++ template, so the replacement has two faces — this
+ * C ABI, and the header-only C++ adapter include/kmi_index.hpp that gives it the reference's
+ * member set (CountIndex / PositionIndex). INTEGRATION.md shows the reference-side binding.
+ *
+ * Conventions
+ *  - A k-mer is `nw = (K <= 32 ? 1 : 2)` consecutive uint64_t, word 0 least significant, first
+ *    base in the most significant used bits: exactly `bliss::common::Kmer<K, DNA, uint64_t>::data`
+ *    (reference src/common/kmer.hpp:76-100,177), so `std::vector<Kmer>` can be passed by
+ *    reinterpret_cast. K must leave >= 2 pad bits (K <= 31 or 33 <= K <= 63), as the reference's
+ *    unsplit dense-hash maps require for their sentinels (src/index/kmer_hash.hpp:396-414).
+ *  - Every function returns KMI_OK (0) or a negative kmi_status; nothing throws across the ABI.
+ *    kmi_last_error() returns a thread-local message for the last failure.
+ *  - `*_dev` entry points take DEVICE pointers (inputs already resident in HBM); the others take
+ *    HOST pointers and do their own host<->device copies. Work is issued on the index's stream
+ *    (default: the legacy default stream 0); host-pointer calls are blocking, `*_dev` calls are
+ *    stream-ordered unless they return a count to the host.
+ *  - There is no CPU fallback: without a CUDA device every compute call fails with KMI_ERR_CUDA.
+ */
+#ifndef KMI_H_
+#define KMI_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  KMI_OK = 0,
+  KMI_ERR_ARG = -1,          /* std::invalid_argument in the reference */
+  KMI_ERR_CUDA = -2,         /* device/runtime failure, or no device */
+  KMI_ERR_FORMAT = -3,       /* malformed FASTQ: std::logic_error (fastq_loader.hpp:393,419,435) */
+  KMI_ERR_CAPACITY = -4,     /* caller-provided output buffer too small */
+  KMI_ERR_UNSUPPORTED = -5,  /* K / mode combination not instantiated */
+  KMI_ERR_NOMEM = -6
+} kmi_status;
+
+typedef enum { KMI_MODE_COUNT = 0, KMI_MODE_POSITION = 1 } kmi_mode;
+
+/* Hash families of reference src/index/kmer_hash.hpp:243-311. The store hash (Prefix=false:
+ * murmur h[0] / farm seed 42) places a key in the local table, the dist hash (Prefix=true:
+ * murmur h[1] / farm seed 83) picks the owning rank: owner = dist % nranks
+ * (src/containers/distributed_densehash_map.hpp:148-170). FARM_DEBUG is farmhash as the
+ * reference's default RelWithDebInfo build computes it (DebugTweak, no NDEBUG). */
+typedef enum { KMI_HASH_MURMUR = 0, KMI_HASH_FARM = 1, KMI_HASH_FARM_DEBUG = 2 } kmi_hash_kind;
+
+typedef struct {
+  int32_t k;            /* k-mer length */
+  int32_t mode;         /* kmi_mode */
+  int32_t canonical;    /* 1: lex_less input transform (CanonicalHashMapParams), 0: identity */
+  int32_t hash;         /* kmi_hash_kind, used for both dist and store hash */
+  int32_t nsplit;       /* 0: N -> A (default parser), 1: NSplitSequencesIterator semantics */
+  int32_t device;       /* CUDA device ordinal */
+  int32_t rank;         /* this index' shard (GPU ordinal within the job) */
+  int32_t nranks;       /* number of shards; owner(key) = dist_hash(key) % nranks */
+  uint64_t reserve;     /* expected distinct keys (0 = grow on demand, like the reference) */
+} kmi_config;
+
+typedef struct kmi_index kmi_index;
+
+/* ---- lifetime ------------------------------------------------------------------------------ */
+/* Index::Index(comm)  — kmer_index.hpp:115 */
+int kmi_create(const kmi_config* cfg, kmi_index** out);
+void kmi_destroy(kmi_index* idx);
+const char* kmi_last_error(void);
+/* run subsequent work of this index on `cuda_stream` (a cudaStream_t); NULL = default stream */
+int kmi_set_stream(kmi_index* idx, void* cuda_stream);
+/* map_base::reserve — src/containers/distributed_map_base.hpp:149-302 */
+int kmi_reserve(kmi_index* idx, uint64_t n_distinct);
+/* remove every entry, keep the allocation */
+int kmi_clear(kmi_index* idx);
+
+/* ---- build from file bytes (Index::build_posix<FASTQParser|FASTAParser>, kmer_index.hpp:332-372;
+ *      KmerFileHelper::read_file_posix + Index::insert, kmer_file_helper.hpp:622-633) ------------
+ * `bytes` must start at a record boundary (FASTQ: an '@' header line; FASTA: anywhere in line
+ * start position) and hold whole records; `file_offset` is the offset of bytes[0] in the file
+ * (only used for position ids). Every k-mer of the block is inserted into THIS index regardless
+ * of owner (nranks == 1 semantics); the sharded build is parse_*_dev + partition_dev + exchange +
+ * insert_dev. n_kmers (optional) receives the number of k-mer occurrences generated. */
+int kmi_build_fastq(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers);
+int kmi_build_fasta(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t* n_kmers);
+int kmi_build_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers);
+int kmi_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* n_kmers);
+
+/* ---- stages, device resident ------------------------------------- */
+/* a2-a10: record boundaries + 2-bit encode + sliding window (+ lex_less if cfg.canonical).
+ * Writes up to `cap` keys (nw words each) and, if d_ids != NULL, their position ids
+ * (FASTA: LongSequenceKmerId, sequence.hpp:180-236). Order of the output is unspecified. */
+int kmi_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset,
+                        uint64_t* d_keys, uint64_t* d_ids, size_t cap, uint64_t* n_kmers);
+int kmi_parse_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n,
+                        uint64_t* d_keys, uint64_t* d_ids, size_t cap, uint64_t* n_kmers);
+/* a10: out = canonical(in) (lex_less, kmer_transform.hpp:109-126); in == out allowed */
+int kmi_canonicalize_dev(kmi_index* idx, const uint64_t* d_keys, uint64_t* d_out, size_t n);
+/* a11/a12: which = 0 store hash, 1 dist hash, of the keys AS GIVEN (no transform) */
+int kmi_hash_dev(kmi_index* idx, int which, const uint64_t* d_keys, uint64_t* d_hash, size_t n);
+/* a13/a14: imxx::distribute's local half (incremental_mxx.hpp:273-364,596-640): stable
+ * counting-sort of n keys (+ optional 8-byte values) by owner = dist_hash % nranks.
+ * h_counts[nranks] receives the per-owner counts (the send counts of the all-to-all). */
+int kmi_partition_dev(kmi_index* idx, const uint64_t* d_keys, const uint64_t* d_vals, size_t n,
+                      uint64_t* d_keys_out, uint64_t* d_vals_out, uint64_t* h_counts);
+
+/* ---- insert (Index::insert, kmer_index.hpp:201-225) ---------------------------------------- */
+/* COUNT mode: vals ignored (each key counts 1; counting_densehash_map::insert(vector<Key>&),
+ * distributed_densehash_map.hpp:2714-2899). POSITION mode: vals[i] is the id of keys[i]
+ * (densehash_multimap::insert, :2329-2384; duplicates kept). Keys are canonicalised first when
+ * cfg.canonical (transform_input, distributed_map_base.hpp:286-301); the caller's arrays are not
+ * modified. */
+int kmi_insert(kmi_index* idx, const uint64_t* keys, const uint64_t* vals, size_t n);
+int kmi_insert_dev(kmi_index* idx, const uint64_t* d_keys, const uint64_t* d_vals, size_t n);
+
+/* ---- batched query (kmer_index.hpp:132-194; distributed_densehash_map.hpp:1122-1216,327-448) -
+ * Results are in INPUT order (the reference returns them grouped by answering rank; the adapter
+ * documents the difference). Queries are canonicalised first when cfg.canonical.
+ * count: counts[i] = 0/1 presence for a COUNT index (dense_hash_map::count), multiplicity for a
+ *        POSITION index (LocalCount, :234-266).
+ * find (COUNT): vals[i] = stored frequency, found[i] = 0/1 (LocalFind, :1769-1798).
+ * find (POSITION): CSR answer — offsets[n+1] into vals; cap = capacity of vals (LocalFind :2094-2133). */
+int kmi_count(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* counts);
+int kmi_find(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* vals, uint8_t* found);
+int kmi_find_positions(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* offsets,
+                       uint64_t* vals, size_t cap);
+int kmi_erase(kmi_index* idx, const uint64_t* keys, size_t n);
+int kmi_count_dev(kmi_index* idx, const uint64_t* d_keys, size_t n, uint64_t* d_counts);
+int kmi_find_dev(kmi_index* idx, const uint64_t* d_keys, size_t n, uint64_t* d_vals, uint8_t* d_found);
+
+/* ---- accessors ----------------------------------------------------------------------------- */
+/* local_size(): distinct keys (COUNT) / stored tuples (POSITION) — kmer_index.hpp:386-391 */
+int kmi_local_size(kmi_index* idx, uint64_t* n);
+/* distinct keys in either mode */
+int kmi_num_keys(kmi_index* idx, uint64_t* n);
+/* to_vector(): every (key, value) entry, unordered. COUNT: value = frequency. POSITION: one
+ * entry per stored (key, id) tuple. n_out receives the number written (<= cap). */
+int kmi_dump(kmi_index* idx, uint64_t* keys, uint64_t* vals, size_t cap, size_t* n_out);
+/* order-independent 64-bit checksums of the contents: sum over entries of mix(key)*value and of
+ * value (mod 2^64) — used to compare builds at sizes where a dump diff is impractical */
+int kmi_checksum(kmi_index* idx, uint64_t* key_value_sum, uint64_t* value_sum);
+/* table geometry for reporting: slots, bytes per slot, device bytes held */
+int kmi_table_info(kmi_index* idx, uint64_t* slots, uint64_t* slot_bytes, uint64_t* device_bytes);
+/* number of kernels this index has launched since creation (bench.py's gpu_launches) */
+int kmi_launch_count(kmi_index* idx, uint64_t* n);
+/* device time (ms) of the stages of the last build_* call, in the reference's BL_BENCH stage
+ * names order: [0] scan (record boundaries), [1] parse+insert (fused) or parse, [2] insert */
+int kmi_last_stage_ms(kmi_index* idx, float* ms3);
+
+/* ---- synthetic workload (same bytes as oracle/kmi_oracle.c kmio_synth_fastq) - */
+size_t kmi_synth_record_bytes(uint32_t read_len);
+int kmi_synth_fastq_dev(int device, uint8_t* d_out, uint64_t first_read, uint64_t n_reads,
+                        uint32_t read_len, uint64_t genome_len, uint64_t seed, uint32_t err_ppm,
+                        uint32_t n_ppm);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KMI_H_ */

@@ -1,0 +1,420 @@
+// kmi_kernels.cuh — table, query, partition and utility kernels (sm_100a).
+#pragma once
+#include "kmi_table.cuh"
+
+namespace kmi {
+
+template <int NW> __device__ __forceinline__ Key<NW> load_key(const u64* __restrict__ keys, u64 i) {
+  Key<NW> k;
+  if (NW == 1) {
+    k.w[0] = __ldg(keys + i);
+  } else {
+    const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>(keys) + i);
+    k.w[0] = v.x; k.w[NW - 1] = v.y;
+  }
+  return k;
+}
+template <int NW> __device__ __forceinline__ void store_key(u64* __restrict__ keys, u64 i, const Key<NW>& k) {
+  if (NW == 1) keys[i] = k.w[0];
+  else reinterpret_cast<ulonglong2*>(keys)[i] = make_ulonglong2(k.w[0], k.w[NW - 1]);
+}
+__device__ __forceinline__ u32 warp_sum(u32 v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+  return v;
+}
+
+// ---- table maintenance ---------------------------------------------------------------------
+template <int NW> __global__ void k_table_clear(Slot<NW>* __restrict__ slots, u64 n) {
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+    if (NW == 1) {
+      reinterpret_cast<ulonglong2*>(slots)[i] = make_ulonglong2(KEY_EMPTY_TOP, 0ULL);
+    } else {
+      ulonglong2* p = reinterpret_cast<ulonglong2*>(slots) + 2 * i;
+      p[0] = make_ulonglong2(0ULL, KEY_EMPTY_TOP);
+      p[1] = make_ulonglong2(0ULL, 0ULL);
+    }
+  }
+}
+
+// a15: counting insert, distributed_densehash_map.hpp:2463-2482 / :2714-2899 (val += 1 per key)
+template <int K, int HASH>
+__global__ void __launch_bounds__(256) k_insert_keys(TableView t, const u64* __restrict__ keys, u64 n, const bool CANON) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  u32 n_new = 0;
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+    Key<NW> key = load_key<NW>(keys, i);
+    if (CANON) key = canonical<K>(key);
+    bool was_new;
+    u64 s = table_upsert<NW>(t, key, store_hash<K, HASH>(key), was_new);
+    if (s != ~0ULL) {
+      atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].val, 1u);
+      n_new += was_new ? 1u : 0u;
+    }
+  }
+  n_new = warp_sum(n_new);
+  if ((threadIdx.x & 31) == 0 && n_new) atomicAdd(t.size, (u64)n_new);
+}
+
+// growth: re-insert every live entry of the old table (dense_hash_map's rehash on resize)
+template <int K, int HASH>
+__global__ void __launch_bounds__(256) k_rehash(const Slot<(K <= 32 ? 1 : 2)>* __restrict__ old, u64 n_old, TableView t) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  u32 n_new = 0;
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n_old; i += (u64)gridDim.x * blockDim.x) {
+    Key<NW> key = slot_key<NW>(old + i);
+    if (!is_live<NW>(key)) continue;
+    bool was_new;
+    u64 s = table_upsert<NW>(t, key, store_hash<K, HASH>(key), was_new);
+    if (s != ~0ULL) {
+      atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].val, old[i].val);
+      n_new += was_new ? 1u : 0u;
+    }
+  }
+  n_new = warp_sum(n_new);
+  if ((threadIdx.x & 31) == 0 && n_new) atomicAdd(t.size, (u64)n_new);
+}
+
+// a18: batched probe. vals[i] = stored value (0 when absent), found[i] = 0/1; slot_idx optional.
+template <int K, int HASH>
+__global__ void __launch_bounds__(256)
+k_lookup(TableView t, const u64* __restrict__ keys, u64 n, u64* __restrict__ vals, uint8_t* __restrict__ found,
+         u64* __restrict__ slot_idx, const bool CANON) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+    Key<NW> key = load_key<NW>(keys, i);
+    if (CANON) key = canonical<K>(key);
+    u64 s = table_find<NW>(t, key, store_hash<K, HASH>(key));
+    if (vals) vals[i] = (s == ~0ULL) ? 0ULL : (u64) reinterpret_cast<const Slot<NW>*>(t.slots)[s].val;
+    if (found) found[i] = (s == ~0ULL) ? 0 : 1;
+    if (slot_idx) slot_idx[i] = s;
+  }
+}
+
+// erase: tombstone the key (dense_hash_map deleted key), distributed_densehash_map.hpp:1602-1663
+template <int K, int HASH>
+__global__ void __launch_bounds__(256) k_erase(TableView t, const u64* __restrict__ keys, u64 n, u64* __restrict__ vals_removed, const bool CANON) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+    Key<NW> key = load_key<NW>(keys, i);
+    if (CANON) key = canonical<K>(key);
+    u64 s = table_find<NW>(t, key, store_hash<K, HASH>(key));
+    if (s == ~0ULL) continue;
+    Slot<NW>* sl = reinterpret_cast<Slot<NW>*>(t.slots) + s;
+    bool won;
+    if (NW == 1) {
+      won = atomicCAS(&reinterpret_cast<Slot<1>*>(sl)->key, key.w[0], KEY_DELETED_TOP) == key.w[0];
+    } else {
+      u64 olo, ohi;
+      cas128(sl, key.w[0], key.w[NW - 1], 0ULL, KEY_DELETED_TOP, olo, ohi);
+      won = (olo == key.w[0] && ohi == key.w[NW - 1]);
+    }
+    if (won) {
+      atomicAdd(t.size, ~0ULL);  // -1
+      if (vals_removed) atomicAdd(vals_removed, (u64)sl->val);
+    }
+  }
+}
+
+// to_vector(): compact live entries (unordered)
+template <int NW>
+__global__ void __launch_bounds__(256)
+k_dump(const Slot<NW>* __restrict__ slots, u64 n_slots, u64* __restrict__ keys, u64* __restrict__ vals, u64 cap,
+       u64* __restrict__ cursor) {
+  for (u64 base = (u64)blockIdx.x * blockDim.x; base < n_slots; base += (u64)gridDim.x * blockDim.x) {
+    u64 i = base + threadIdx.x;
+    Key<NW> key; key.w[NW - 1] = KEY_EMPTY_TOP;
+    if (i < n_slots) key = slot_key<NW>(slots + i);
+    bool live = is_live<NW>(key);
+    u32 m = __ballot_sync(0xffffffffu, live);
+    u64 wbase = 0;
+    if ((threadIdx.x & 31) == 0 && m) wbase = atomicAdd(cursor, (u64)__popc(m));
+    wbase = __shfl_sync(0xffffffffu, wbase, 0);
+    if (live) {
+      u64 at = wbase + __popc(m & ((1u << (threadIdx.x & 31)) - 1));
+      if (at < cap) {
+        store_key<NW>(keys, at, key);
+        if (vals) vals[at] = slots[i].val;
+      }
+    }
+  }
+}
+
+// order-independent checksums: sum mix(key)*val, sum val
+template <int NW>
+__global__ void __launch_bounds__(256) k_checksum(const Slot<NW>* __restrict__ slots, u64 n_slots, u64* __restrict__ out2) {
+  u64 a = 0, b = 0;
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (u64)gridDim.x * blockDim.x) {
+    Key<NW> key = slot_key<NW>(slots + i);
+    if (!is_live<NW>(key)) continue;
+    u64 v = slots[i].val;
+    u64 m = mix64(key.w[0]);
+    if (NW == 2) m = mix64(m ^ key.w[NW - 1]);
+    a += m * v; b += v;
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    a += __shfl_xor_sync(0xffffffffu, a, d);
+    b += __shfl_xor_sync(0xffffffffu, b, d);
+  }
+  if ((threadIdx.x & 31) == 0) { atomicAdd(out2, a); atomicAdd(out2 + 1, b); }
+}
+
+// ---- value transforms --------------------------------------------------------------------------
+template <int K> __global__ void __launch_bounds__(256) k_canonicalize(const u64* in, u64* out, u64 n) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x)
+    store_key<NW>(out, i, canonical<K>(load_key<NW>(in, i)));
+}
+template <int K, int HASH> __global__ void __launch_bounds__(256) k_hash(int which, const u64* __restrict__ in, u64* __restrict__ out, u64 n) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+    u64 s, d;
+    kmer_hashes<K, HASH>(load_key<NW>(in, i), s, d);
+    out[i] = which ? d : s;
+  }
+}
+
+// ---- a13/a14: owner = dist_hash % p, stable counting-sort by owner -----------------------------------
+// Replaces imxx::local::assign_to_buckets / bucket_to_permutation / permute
+// (reference src/io/incremental_mxx.hpp:273-364,596-640). Chunk = PART_ITEMS consecutive keys per
+// block; histogram is [owner][chunk] so that one exclusive scan yields every (owner, chunk) base.
+static constexpr int PART_THREADS = 256;
+static constexpr int PART_ROUNDS = 8;
+static constexpr int PART_ITEMS = PART_THREADS * PART_ROUNDS;
+static constexpr int MAX_RANKS = 256;
+
+template <int K, int HASH>
+__device__ __forceinline__ u32 owner_of(const Key<(K <= 32 ? 1 : 2)>& key, u32 p) {
+  u64 s, d;
+  kmer_hashes<K, HASH>(key, s, d);
+  return (u32)(d % (u64)p);
+}
+
+template <int K, int HASH>
+__global__ void __launch_bounds__(PART_THREADS)
+k_part_hist(const u64* __restrict__ keys, u64 n, u32 p, u32* __restrict__ hist, u64 n_chunks) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  __shared__ u32 h[MAX_RANKS];
+  for (u32 r = threadIdx.x; r < p; r += PART_THREADS) h[r] = 0;
+  __syncthreads();
+  const u64 base = (u64)blockIdx.x * PART_ITEMS;
+  for (int rd = 0; rd < PART_ROUNDS; ++rd) {
+    u64 i = base + (u64)rd * PART_THREADS + threadIdx.x;
+    if (i < n) atomicAdd(&h[owner_of<K, HASH>(load_key<NW>(keys, i), p)], 1u);
+  }
+  __syncthreads();
+  for (u32 r = threadIdx.x; r < p; r += PART_THREADS) hist[(u64)r * n_chunks + blockIdx.x] = h[r];
+}
+
+template <int K, int HASH>
+__global__ void __launch_bounds__(PART_THREADS)
+k_part_scatter(const u64* __restrict__ keys, const u64* __restrict__ vals, u64 n, u32 p,
+               const u32* __restrict__ hist_scanned, const u32* __restrict__ hist_block_sums, u64 n_chunks,
+               u64* __restrict__ keys_out, u64* __restrict__ vals_out) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  constexpr int NWARPS = PART_THREADS / 32;
+  __shared__ u32 run[MAX_RANKS];              // next free offset per owner for this chunk
+  __shared__ u32 wcnt[NWARPS][MAX_RANKS];     // per-warp counts of the current round
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (u32 r = threadIdx.x; r < p; r += PART_THREADS) {
+    u64 hi = (u64)r * n_chunks + blockIdx.x;
+    run[r] = hist_scanned[hi] + hist_block_sums[hi >> 10];
+  }
+  const u64 base = (u64)blockIdx.x * PART_ITEMS;
+  for (int rd = 0; rd < PART_ROUNDS; ++rd) {
+    for (u32 r = threadIdx.x; r < p * NWARPS; r += PART_THREADS) wcnt[r / p][r % p] = 0;
+    __syncthreads();
+    u64 i = base + (u64)rd * PART_THREADS + threadIdx.x;
+    bool ok = i < n;
+    Key<NW> key;
+    u32 own = 0xFFFFFFFFu;
+    if (ok) { key = load_key<NW>(keys, i); own = owner_of<K, HASH>(key, p); }
+    u32 peers = __match_any_sync(0xffffffffu, own);
+    u32 rank_in_warp = __popc(peers & ((1u << lane) - 1));
+    if (ok && rank_in_warp == 0) wcnt[warp][own] = __popc(peers);
+    __syncthreads();
+    if (ok) {
+      u32 o = run[own] + rank_in_warp;
+      for (int w = 0; w < warp; ++w) o += wcnt[w][own];
+      store_key<NW>(keys_out, o, key);
+      if (vals) vals_out[o] = vals[i];
+    }
+    __syncthreads();
+    for (u32 r = threadIdx.x; r < p; r += PART_THREADS) {
+      u32 s = 0;
+      for (int w = 0; w < NWARPS; ++w) s += wcnt[w][r];
+      run[r] += s;
+    }
+    __syncthreads();
+  }
+}
+
+// ---- a17: multimap as CSR (key -> [offset, offset+multiplicity) into a value array) --------------
+// Replaces fsc::densehash_multimap's singleton/vector split (reference
+// src/containers/densehash_map.hpp:2022-2044,2190-2249): count -> exclusive scan -> fill.
+// scan level 1 over slot multiplicities (dead slots count 0); 1024 slots per block
+template <int NW>
+__global__ void __launch_bounds__(1024)
+k_csr_scan_l1(const Slot<NW>* __restrict__ slots, u64 n_slots, u64* __restrict__ offsets, u64* __restrict__ block_sums) {
+  __shared__ u64 tmp[33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  u64 i = (u64)blockIdx.x * 1024 + threadIdx.x;
+  u64 x = 0;
+  if (i < n_slots) {
+    Key<NW> key = slot_key<NW>(slots + i);
+    if (is_live<NW>(key)) x = slots[i].val;
+  }
+  u64 inc = x;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    u64 o = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += o;
+  }
+  if (lane == 31) tmp[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    u64 w = tmp[lane], winc = w;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      u64 o = __shfl_up_sync(0xffffffffu, winc, d);
+      if (lane >= d) winc += o;
+    }
+    tmp[lane] = winc - w;
+    if (lane == 31) tmp[32] = winc;
+  }
+  __syncthreads();
+  if (i < n_slots) offsets[i] = tmp[warp] + inc - x;
+  if (threadIdx.x == 0) block_sums[blockIdx.x] = tmp[32];
+}
+#ifdef KMI_SHARED_KERNELS
+__global__ void __launch_bounds__(1024) k_scan64(u64* __restrict__ v, u64 n) {
+  __shared__ u64 tmp[33];
+  __shared__ u64 carry_s;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (u64 base = 0; base < n; base += 1024) {
+    u64 i = base + threadIdx.x;
+    u64 x = (i < n) ? v[i] : 0, inc = x;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      u64 o = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += o;
+    }
+    if (lane == 31) tmp[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      u64 w = tmp[lane], winc = w;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        u64 o = __shfl_up_sync(0xffffffffu, winc, d);
+        if (lane >= d) winc += o;
+      }
+      tmp[lane] = winc - w;
+      if (lane == 31) tmp[32] = winc;
+    }
+    __syncthreads();
+    u64 carry = carry_s;
+    if (i < n) v[i] = carry + tmp[warp] + inc - x;
+    __syncthreads();
+    if (threadIdx.x == 0) carry_s = carry + tmp[32];
+    __syncthreads();
+  }
+}
+__global__ void __launch_bounds__(1024) k_csr_add_block(u64* __restrict__ offsets, u64 n, const u64* __restrict__ block_sums) {
+  u64 i = (u64)blockIdx.x * 1024 + threadIdx.x;
+  if (i < n) offsets[i] += block_sums[blockIdx.x];
+}
+#endif  // KMI_SHARED_KERNELS
+// fill: every logged (key, id) goes to values[offset[slot] + cursor++]; aux is the cursor
+template <int K, int HASH>
+__global__ void __launch_bounds__(256)
+k_csr_fill(TableView t, const u64* __restrict__ keys, const u64* __restrict__ ids, u64 n,
+           const u64* __restrict__ offsets, u64* __restrict__ values) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+    Key<NW> key = load_key<NW>(keys, i);
+    u64 s = table_find<NW>(t, key, store_hash<K, HASH>(key));
+    if (s == ~0ULL) continue;
+    u32 c = atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].aux, 1u);
+    values[offsets[s] + c] = ids[i];
+  }
+}
+#ifdef KMI_SHARED_KERNELS
+// find (multimap): per query multiplicity, then gather
+__global__ void __launch_bounds__(256)
+k_csr_gather(const u64* __restrict__ slot_idx, const u64* __restrict__ out_off, u64 n, const u64* __restrict__ offsets,
+             const u64* __restrict__ values, u64* __restrict__ out_vals, u64 cap) {
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+    u64 s = slot_idx[i];
+    if (s == ~0ULL) continue;
+    u64 b = out_off[i], e = out_off[i + 1], src = offsets[s];
+    for (u64 j = b; j < e && j < cap; ++j) out_vals[j] = values[src + (j - b)];
+  }
+}
+#endif  // KMI_SHARED_KERNELS
+// drop logged tuples whose key is no longer live (after erase); stable not required
+template <int K, int HASH>
+__global__ void __launch_bounds__(256)
+k_log_filter(TableView t, const u64* __restrict__ keys, const u64* __restrict__ ids, u64 n, u64* __restrict__ keys_out,
+             u64* __restrict__ ids_out, u64* __restrict__ cursor) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  for (u64 base = (u64)blockIdx.x * blockDim.x; base < n; base += (u64)gridDim.x * blockDim.x) {
+    u64 i = base + threadIdx.x;
+    bool keep = false;
+    Key<NW> key;
+    if (i < n) { key = load_key<NW>(keys, i); keep = table_find<NW>(t, key, store_hash<K, HASH>(key)) != ~0ULL; }
+    u32 m = __ballot_sync(0xffffffffu, keep);
+    u64 wbase = 0;
+    if ((threadIdx.x & 31) == 0 && m) wbase = atomicAdd(cursor, (u64)__popc(m));
+    wbase = __shfl_sync(0xffffffffu, wbase, 0);
+    if (keep) {
+      u64 at = wbase + __popc(m & ((1u << (threadIdx.x & 31)) - 1));
+      store_key<NW>(keys_out, at, key);
+      ids_out[at] = ids[i];
+    }
+  }
+}
+template <int NW> __global__ void k_zero_aux(Slot<NW>* __restrict__ slots, u64 n) {
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) slots[i].aux = 0;
+}
+
+// ---- synthetic FASTQ (same bytes as oracle/kmi_oracle.c: kmio_synth_fastq) ---------------------
+__device__ __forceinline__ u64 sm64(u64 x) { return mix64(x); }
+__device__ __forceinline__ u32 syn_genome_base(u64 seed, u64 i) {
+  return (u32)((sm64(seed * 0x100000001b3ULL + (i >> 5)) >> (2 * (i & 31))) & 3);
+}
+#ifdef KMI_SHARED_KERNELS
+__global__ void __launch_bounds__(256)
+k_synth_fastq(uint8_t* __restrict__ out, u64 first_read, u64 n_reads, u32 L, u64 G, u64 seed, u32 err_ppm, u32 n_ppm) {
+  const u32 HDR = 13;
+  const u64 rec = HDR + 2ULL * L + 4, total = n_reads * rec;
+  for (u64 idx = (u64)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (u64)gridDim.x * blockDim.x) {
+    u64 r = first_read + idx / rec;
+    u32 o = (u32)(idx % rec);
+    uint8_t ch;
+    if (o < HDR) {
+      if (o == 0) ch = '@';
+      else if (o == 1) ch = 'S';
+      else if (o == HDR - 1) ch = '\n';
+      else { u64 d = r; for (u32 k = HDR - 2; k > o; --k) d /= 10; ch = (uint8_t)('0' + d % 10); }
+    } else if (o - HDR < L) {
+      u32 q = o - HDR;
+      u64 h = sm64((seed + 1) * 0x9e3779b97f4a7c15ULL + r);
+      u64 start = (h >> 1) % (G - L + 1);
+      u32 b = (h & 1) ? 3u - syn_genome_base(seed, start + (L - 1 - q)) : syn_genome_base(seed, start + q);
+      u64 e = sm64((seed + 2) * 0xd1b54a32d192ed03ULL + r * L + q);
+      if ((u32)(e % 1000000u) < err_ppm) b = (b + 1 + (u32)((e >> 40) % 3)) & 3;
+      ch = ((u32)((e >> 20) % 1000000u) < n_ppm) ? (uint8_t)'N' : (uint8_t)"ACGT"[b];
+    } else {
+      u32 q = o - HDR - L;
+      ch = (q == 0) ? '\n' : (q == 1) ? '+' : (q == 2) ? '\n' : (q - 3 < L) ? 'I' : '\n';
+    }
+    out[idx] = ch;
+  }
+}
+
+#endif  // KMI_SHARED_KERNELS
+
+}  // namespace kmi

@@ -1,0 +1,119 @@
+// kmi_ops.cuh — host-side launchers, one table of function pointers per (K, hash).
+// kmi_ops_inst.cu is compiled once per supported K (-DKMI_K=...), so that the API translation
+// unit carries no templates and the per-K objects build in parallel.
+#pragma once
+#include "kmi_parse.cuh"
+#include "kmi_kernels.cuh"
+
+namespace kmi {
+
+struct Ops {
+  int K, NW, hash;
+  // parse (FASTQ). sink_kind 0: key stream, 1: straight into the table
+  void (*fastq_kmers)(cudaStream_t, int sink_kind, const uint8_t* bytes, u64 n, u64 n_tiles, const u32* tile_lines,
+                      const u32* block_sums, KeySink sink, TableView table, u64* n_kmers, u32* perr, bool canon,
+                      bool nsplit, u64 tile_begin);
+  void (*table_clear)(cudaStream_t, void* slots, u64 n);
+  void (*insert_keys)(cudaStream_t, TableView, const u64* keys, u64 n, bool canon);
+  void (*rehash)(cudaStream_t, const void* old_slots, u64 n_old, TableView);
+  void (*lookup)(cudaStream_t, TableView, const u64* keys, u64 n, u64* vals, uint8_t* found, u64* slot_idx, bool canon);
+  void (*erase)(cudaStream_t, TableView, const u64* keys, u64 n, u64* vals_removed, bool canon);
+  void (*dump)(cudaStream_t, const void* slots, u64 n_slots, u64* keys, u64* vals, u64 cap, u64* cursor);
+  void (*checksum)(cudaStream_t, const void* slots, u64 n_slots, u64* out2);
+  void (*canonicalize)(cudaStream_t, const u64* in, u64* out, u64 n);
+  void (*hash_keys)(cudaStream_t, int which, const u64* in, u64* out, u64 n);
+  void (*part_hist)(cudaStream_t, const u64* keys, u64 n, u32 p, u32* hist, u64 n_chunks);
+  void (*part_scatter)(cudaStream_t, const u64* keys, const u64* vals, u64 n, u32 p, const u32* hist_scanned,
+                       const u32* hist_block_sums, u64 n_chunks, u64* keys_out, u64* vals_out);
+  void (*csr_scan_l1)(cudaStream_t, const void* slots, u64 n_slots, u64* offsets, u64* block_sums);
+  void (*csr_fill)(cudaStream_t, TableView, const u64* keys, const u64* ids, u64 n, const u64* offsets, u64* values);
+  void (*log_filter)(cudaStream_t, TableView, const u64* keys, const u64* ids, u64 n, u64* keys_out, u64* ids_out,
+                     u64* cursor);
+  void (*zero_aux)(cudaStream_t, void* slots, u64 n);
+};
+
+static inline unsigned grid_for(u64 n, unsigned block, unsigned max_blocks = 148u * 16u) {
+  u64 g = (n + block - 1) / block;
+  if (g < 1) g = 1;
+  if (g > max_blocks) g = max_blocks;
+  return (unsigned)g;
+}
+
+template <int K, int HASH>
+struct OpsImpl {
+  static constexpr int NW = (K <= 32 ? 1 : 2);
+  typedef Slot<NW> S;
+  static void fastq_kmers(cudaStream_t st, int sink_kind, const uint8_t* bytes, u64 n, u64 n_tiles, const u32* tile_lines,
+                          const u32* block_sums, KeySink sink, TableView table, u64* n_kmers, u32* perr, bool canon,
+                          bool nsplit, u64 tile_begin) {
+    if (n_tiles == 0) return;
+    if (sink_kind == 0)
+      k_fastq_kmers<K, HASH, 0><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table,
+                                                                          n_kmers, perr, canon, nsplit, tile_begin);
+    else
+      k_fastq_kmers<K, HASH, 1><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table,
+                                                                          n_kmers, perr, canon, nsplit, tile_begin);
+  }
+  static void table_clear(cudaStream_t st, void* slots, u64 n) {
+    k_table_clear<NW><<<grid_for(n, 256), 256, 0, st>>>(reinterpret_cast<S*>(slots), n);
+  }
+  static void insert_keys(cudaStream_t st, TableView t, const u64* keys, u64 n, bool canon) {
+    if (n) k_insert_keys<K, HASH><<<grid_for(n, 256, 148u * 32u), 256, 0, st>>>(t, keys, n, canon);
+  }
+  static void rehash(cudaStream_t st, const void* old_slots, u64 n_old, TableView t) {
+    k_rehash<K, HASH><<<grid_for(n_old, 256, 148u * 32u), 256, 0, st>>>(reinterpret_cast<const S*>(old_slots), n_old, t);
+  }
+  static void lookup(cudaStream_t st, TableView t, const u64* keys, u64 n, u64* vals, uint8_t* found, u64* slot_idx,
+                     bool canon) {
+    if (n) k_lookup<K, HASH><<<grid_for(n, 256, 148u * 32u), 256, 0, st>>>(t, keys, n, vals, found, slot_idx, canon);
+  }
+  static void erase(cudaStream_t st, TableView t, const u64* keys, u64 n, u64* vals_removed, bool canon) {
+    if (n) k_erase<K, HASH><<<grid_for(n, 256), 256, 0, st>>>(t, keys, n, vals_removed, canon);
+  }
+  static void dump(cudaStream_t st, const void* slots, u64 n_slots, u64* keys, u64* vals, u64 cap, u64* cursor) {
+    k_dump<NW><<<grid_for(n_slots, 256), 256, 0, st>>>(reinterpret_cast<const S*>(slots), n_slots, keys, vals, cap, cursor);
+  }
+  static void checksum(cudaStream_t st, const void* slots, u64 n_slots, u64* out2) {
+    k_checksum<NW><<<grid_for(n_slots, 256), 256, 0, st>>>(reinterpret_cast<const S*>(slots), n_slots, out2);
+  }
+  static void canonicalize(cudaStream_t st, const u64* in, u64* out, u64 n) {
+    if (n) k_canonicalize<K><<<grid_for(n, 256), 256, 0, st>>>(in, out, n);
+  }
+  static void hash_keys(cudaStream_t st, int which, const u64* in, u64* out, u64 n) {
+    if (n) k_hash<K, HASH><<<grid_for(n, 256), 256, 0, st>>>(which, in, out, n);
+  }
+  static void part_hist(cudaStream_t st, const u64* keys, u64 n, u32 p, u32* hist, u64 n_chunks) {
+    if (n_chunks) k_part_hist<K, HASH><<<(unsigned)n_chunks, PART_THREADS, 0, st>>>(keys, n, p, hist, n_chunks);
+  }
+  static void part_scatter(cudaStream_t st, const u64* keys, const u64* vals, u64 n, u32 p, const u32* hist_scanned,
+                           const u32* hist_block_sums, u64 n_chunks, u64* keys_out, u64* vals_out) {
+    if (n_chunks)
+      k_part_scatter<K, HASH><<<(unsigned)n_chunks, PART_THREADS, 0, st>>>(keys, vals, n, p, hist_scanned, hist_block_sums,
+                                                                          n_chunks, keys_out, vals_out);
+  }
+  static void csr_scan_l1(cudaStream_t st, const void* slots, u64 n_slots, u64* offsets, u64* block_sums) {
+    k_csr_scan_l1<NW><<<(unsigned)((n_slots + 1023) / 1024), 1024, 0, st>>>(reinterpret_cast<const S*>(slots), n_slots,
+                                                                           offsets, block_sums);
+  }
+  static void csr_fill(cudaStream_t st, TableView t, const u64* keys, const u64* ids, u64 n, const u64* offsets, u64* values) {
+    if (n) k_csr_fill<K, HASH><<<grid_for(n, 256, 148u * 32u), 256, 0, st>>>(t, keys, ids, n, offsets, values);
+  }
+  static void log_filter(cudaStream_t st, TableView t, const u64* keys, const u64* ids, u64 n, u64* keys_out, u64* ids_out,
+                         u64* cursor) {
+    if (n) k_log_filter<K, HASH><<<grid_for(n, 256), 256, 0, st>>>(t, keys, ids, n, keys_out, ids_out, cursor);
+  }
+  static void zero_aux(cudaStream_t st, void* slots, u64 n) {
+    k_zero_aux<NW><<<grid_for(n, 256), 256, 0, st>>>(reinterpret_cast<S*>(slots), n);
+  }
+  static Ops make() {
+    Ops o;
+    o.K = K; o.NW = NW; o.hash = HASH;
+    o.fastq_kmers = fastq_kmers; o.table_clear = table_clear; o.insert_keys = insert_keys; o.rehash = rehash;
+    o.lookup = lookup; o.erase = erase; o.dump = dump; o.checksum = checksum; o.canonicalize = canonicalize;
+    o.hash_keys = hash_keys; o.part_hist = part_hist; o.part_scatter = part_scatter; o.csr_scan_l1 = csr_scan_l1;
+    o.csr_fill = csr_fill; o.log_filter = log_filter; o.zero_aux = zero_aux;
+    return o;
+  }
+};
+
+}  // namespace kmi

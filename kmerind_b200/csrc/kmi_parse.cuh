@@ -1,0 +1,413 @@
+// kmi_parse.cuh — record-boundary finding, 2-bit encoding and k-mer generation (sm_100a).
+//
+// Replaces, for whole record blocks resident in HBM, the reference's per-byte iterator stack:
+//   SequentialFASTQParser::get_next_record      src/io/fastq_loader.hpp:389-470       (a3)
+//   NotEOL filter + ASCII2<DNA>                 src/utils/file_utils.hpp:43-54,
+//                                               src/common/alphabets.hpp:139-157      (a7)
+//   KmerSlidingWindow / Kmer::nextFromChar      src/common/kmer_iterators.hpp:82-100,
+//                                               src/common/kmer.hpp:731-741           (a8)
+//   NSplitSequencesIterator                     src/io/filtered_sequence_iterator.hpp:225-236 (a5)
+//   lex_less                                    src/common/kmer_transform.hpp:109-126 (a10)
+//
+// Layout: the text is cut into 4 KiB tiles of 256 16-byte groups; one thread owns one group and
+// loads it with a single coalesced 128-bit load. FASTQ structure is recovered exactly as the
+// reference walks it — a record is four consecutive NON-EMPTY lines (findNonEOL skips every
+// '\n'/'\r', so blank lines vanish) — by numbering line starts globally: pass A counts line
+// starts per tile, a scan turns that into each tile's first line number, pass B classifies
+// every byte (line number mod 4 == 1 -> sequence line). Per tile the 2-bit codes (32 bits per
+// group, first base most significant) and a one-bit-per-byte "is a base of a sequence line"
+// flag live in shared memory; a k-mer starts at byte p iff flags p..p+K-1 are all set, and its
+// value is a funnel-shift of the packed codes. Valid start positions are compacted into a
+// shared work list so that the expensive part (reverse complement, min, hash, sink) runs with
+// all lanes busy and the key stream is written coalesced.
+#pragma once
+#include "kmi_table.cuh"
+
+namespace kmi {
+
+static constexpr int TILE_THREADS = 256;
+static constexpr int GROUP_BYTES = 16;
+static constexpr int TILE_BYTES = TILE_THREADS * GROUP_BYTES;  // 4096
+static constexpr int HALO_GROUPS = 4;                          // 64 bytes >= K-1 for K <= 63
+static constexpr int TILE_GROUPS = TILE_THREADS + HALO_GROUPS;
+
+// error bits reported by the parse kernels
+static constexpr u32 PERR_NO_AT = 1u;    // fastq_loader.hpp:393,419
+static constexpr u32 PERR_NO_PLUS = 2u;  // fastq_loader.hpp:435
+static constexpr u32 PERR_OVERFLOW = 4u; // output capacity exceeded
+static constexpr u32 PERR_HALO = 8u;     // FASTA: K-1 bases do not fit the halo (retry wider)
+
+// ---- byte-parallel classification of one 16-byte group ------------------------------------
+__device__ __forceinline__ u32 nib(u32 bytemask) {  // 0xFF/0x00 per byte -> 4 bits, byte 0 -> bit 0
+  return ((bytemask & 0x08040201u) * 0x01010101u) >> 24;
+}
+__device__ __forceinline__ u32 mask16(u32 a, u32 b, u32 c, u32 d) {
+  return nib(a) | (nib(b) << 4) | (nib(c) << 8) | (nib(d) << 12);
+}
+// 2-bit codes of 4 bytes packed into 8 bits, byte 0 in the two most significant bits.
+// DNA::FROM_ASCII: A/a 0, C/c 1, G/g 2, T/t 3, everything else 0.
+__device__ __forceinline__ u32 codes4(u32 w) {
+  u32 f = w & 0xDFDFDFDFu;  // fold case: only 'c','g','t' fold onto 'C','G','T'
+  u32 c = (__vcmpeq4(f, 0x43434343u) & 0x01010101u) | (__vcmpeq4(f, 0x47474747u) & 0x02020202u) |
+          (__vcmpeq4(f, 0x54545454u) & 0x03030303u);
+  return (c * 0x40100401u) >> 24;
+}
+struct Group {
+  u32 codes;  // 16 bases, first base in bits 31..30
+  u32 eol;    // bit b: byte b is '\n' or '\r'
+  u32 nl;     // bit b: byte b is '\n'
+  u32 nmask;  // bit b: byte b is 'N' or 'n'
+};
+__device__ __forceinline__ Group classify(const uint4& v) {
+  Group g;
+  g.codes = (codes4(v.x) << 24) | (codes4(v.y) << 16) | (codes4(v.z) << 8) | codes4(v.w);
+  u32 a = __vcmpeq4(v.x, 0x0A0A0A0Au), b = __vcmpeq4(v.y, 0x0A0A0A0Au), c = __vcmpeq4(v.z, 0x0A0A0A0Au),
+      d = __vcmpeq4(v.w, 0x0A0A0A0Au);
+  g.nl = mask16(a, b, c, d);
+  g.eol = g.nl | mask16(__vcmpeq4(v.x, 0x0D0D0D0Du), __vcmpeq4(v.y, 0x0D0D0D0Du),
+                        __vcmpeq4(v.z, 0x0D0D0D0Du), __vcmpeq4(v.w, 0x0D0D0D0Du));
+  g.nmask = mask16(__vcmpeq4(v.x & 0xDFDFDFDFu, 0x4E4E4E4Eu), __vcmpeq4(v.y & 0xDFDFDFDFu, 0x4E4E4E4Eu),
+                   __vcmpeq4(v.z & 0xDFDFDFDFu, 0x4E4E4E4Eu), __vcmpeq4(v.w & 0xDFDFDFDFu, 0x4E4E4E4Eu));
+  return g;
+}
+// 16 bytes at offset `off` of a 16-byte aligned buffer of n bytes; bytes past the end read as '\n'
+__device__ __forceinline__ uint4 load_group(const uint8_t* __restrict__ bytes, u64 off, u64 n) {
+  if (off + GROUP_BYTES <= n) {
+    return __ldg(reinterpret_cast<const uint4*>(bytes + off));
+  }
+  u32 w[4] = {0x0A0A0A0Au, 0x0A0A0A0Au, 0x0A0A0A0Au, 0x0A0A0A0Au};
+  for (int b = 0; b < GROUP_BYTES; ++b)
+    if (off + b < n) w[b >> 2] = (w[b >> 2] & ~(0xFFu << (8 * (b & 3)))) | ((u32)bytes[off + b] << (8 * (b & 3)));
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+__device__ __forceinline__ u32 byte_of(const uint4& v, int b) {
+  u32 w = (b < 4) ? v.x : (b < 8) ? v.y : (b < 12) ? v.z : v.w;
+  return (w >> (8 * (b & 3))) & 0xFFu;
+}
+// is the byte before offset `off` an EOL (file start counts as one)
+__device__ __forceinline__ bool prev_is_eol(const uint8_t* __restrict__ bytes, u64 off, u64 n) {
+  if (off == 0 || off > n) return true;
+  uint8_t c = __ldg(bytes + off - 1);
+  return c == '\n' || c == '\r';
+}
+// FASTQ line starts: a non-EOL byte preceded by an EOL byte (blank lines vanish, as findNonEOL
+// skips every EOL char: reference src/io/file_loader.hpp:146-152)
+__device__ __forceinline__ u32 line_starts(u32 eol, bool prev_eol) {
+  return (~eol) & ((eol << 1) | (prev_eol ? 1u : 0u)) & 0xFFFFu;
+}
+
+// block-wide exclusive scan of one u32 per thread (TILE_THREADS threads); returns the exclusive
+// prefix, total in `total`. `tmp` is TILE_THREADS/32 + 1 words of shared memory.
+__device__ __forceinline__ u32 block_excl_scan(u32 v, u32* tmp, u32& total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  u32 inc = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    u32 o = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += o;
+  }
+  if (lane == 31) tmp[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    u32 w = (lane < TILE_THREADS / 32) ? tmp[lane] : 0;
+    u32 winc = w;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      u32 o = __shfl_up_sync(0xffffffffu, winc, d);
+      if (lane >= d) winc += o;
+    }
+    if (lane < TILE_THREADS / 32) tmp[lane] = winc - w;
+    if (lane == TILE_THREADS / 32 - 1) tmp[TILE_THREADS / 32] = winc;
+  }
+  __syncthreads();
+  total = tmp[TILE_THREADS / 32];
+  u32 r = tmp[warp] + inc - v;
+  __syncthreads();
+  return r;
+}
+
+#ifdef KMI_SHARED_KERNELS  // non-template kernels: compiled once, in the API translation unit
+// ---- pass A: line starts per tile ------------------------------------------------------------
+__global__ void __launch_bounds__(TILE_THREADS) k_fastq_count_lines(const uint8_t* __restrict__ bytes, u64 n,
+                                                                     u32* __restrict__ tile_lines) {
+  __shared__ u32 tmp[TILE_THREADS / 32 + 1];
+  u64 off = (u64)blockIdx.x * TILE_BYTES + (u64)threadIdx.x * GROUP_BYTES;
+  u32 cnt = 0;
+  if (off < n) {
+    uint4 v = load_group(bytes, off, n);
+    Group g = classify(v);
+    cnt = __popc(line_starts(g.eol, prev_is_eol(bytes, off, n)));
+  }
+  u32 total;
+  block_excl_scan(cnt, tmp, total);
+  if (threadIdx.x == 0) tile_lines[blockIdx.x] = total;
+}
+
+// exclusive scan of the per-tile counts (modulo 2^32: only the value mod 4 matters downstream)
+__global__ void __launch_bounds__(1024) k_scan_tiles(u32* __restrict__ v, u64 n) {
+  __shared__ u32 tmp[33];
+  __shared__ u32 carry_s;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (u64 base = 0; base < n; base += 1024) {
+    u64 i = base + threadIdx.x;
+    u32 x = (i < n) ? v[i] : 0;
+    u32 inc = x;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      u32 o = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += o;
+    }
+    if (lane == 31) tmp[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      u32 w = tmp[lane], winc = w;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        u32 o = __shfl_up_sync(0xffffffffu, winc, d);
+        if (lane >= d) winc += o;
+      }
+      tmp[lane] = winc - w;
+      if (lane == 31) tmp[32] = winc;
+    }
+    __syncthreads();
+    u32 carry = carry_s;
+    if (i < n) v[i] = carry + tmp[warp] + inc - x;
+    __syncthreads();
+    if (threadIdx.x == 0) carry_s = carry + tmp[32];
+    __syncthreads();
+  }
+}
+
+// level-1 of the tile scan: each block scans 1024 tile counts in place (exclusive) and writes
+// its total; k_scan_tiles then scans the block totals; consumers add the two.
+__global__ void __launch_bounds__(1024) k_scan_l1(u32* __restrict__ v, u64 n, u32* __restrict__ block_sums) {
+  __shared__ u32 tmp[33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  u64 i = (u64)blockIdx.x * 1024 + threadIdx.x;
+  u32 x = (i < n) ? v[i] : 0;
+  u32 inc = x;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    u32 o = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += o;
+  }
+  if (lane == 31) tmp[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    u32 w = tmp[lane], winc = w;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      u32 o = __shfl_up_sync(0xffffffffu, winc, d);
+      if (lane >= d) winc += o;
+    }
+    tmp[lane] = winc - w;
+    if (lane == 31) tmp[32] = winc;
+  }
+  __syncthreads();
+  if (i < n) v[i] = tmp[warp] + inc - x;
+  if (threadIdx.x == 0) block_sums[blockIdx.x] = tmp[32];
+}
+
+#endif  // KMI_SHARED_KERNELS
+
+// ---- k-mer extraction from the packed code stream --------------------------------------------
+// c[0..4]: code words of groups g..g+4 (first base most significant); j: start base in group g.
+template <int K> __device__ __forceinline__ Key<(K <= 32 ? 1 : 2)> extract_kmer(const u32* c, int j) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  const int s = 2 * j;  // 0..30
+  Key<NW> k;
+  if (NW == 1) {
+    u32 w0 = __funnelshift_l(c[1], c[0], s), w1 = __funnelshift_l(c[2], c[1], s);
+    u64 top = ((u64)w0 << 32) | w1;
+    k.w[0] = top >> (64 - 2 * K);
+  } else {
+    u32 w0 = __funnelshift_l(c[1], c[0], s), w1 = __funnelshift_l(c[2], c[1], s);
+    u32 w2 = __funnelshift_l(c[3], c[2], s), w3 = __funnelshift_l(c[4], c[3], s);
+    u64 hi = ((u64)w0 << 32) | w1, lo = ((u64)w2 << 32) | w3;
+    constexpr int S = 128 - 2 * K;  // 2..62
+    k.w[0] = (lo >> S) | (hi << (64 - S));
+    k.w[NW - 1] = hi >> S;
+  }
+  return k;
+}
+
+// bit j of the result: flag bits j..j+K-1 are all set. f[0..4]: 16-bit flag words of groups g..g+4.
+template <int K> __device__ __forceinline__ u32 window_all_set(const u32* f) {
+  if (K <= 33) {  // needs bits 0..K+14 <= 47
+    u64 F = (u64)f[0] | ((u64)f[1] << 16) | ((u64)f[2] << 32) | ((u64)f[3] << 48);
+    u64 A = F, R = ~0ULL;
+    int r = 0;
+#pragma unroll
+    for (int len = 1; len <= K; len <<= 1) {
+      if (K & len) { R &= (A >> r); r += len; }
+      A &= (A >> len);
+    }
+    return (u32)(R & 0xFFFFu);
+  } else {
+    unsigned __int128 F = (unsigned __int128)((u64)f[0] | ((u64)f[1] << 16) | ((u64)f[2] << 32) | ((u64)f[3] << 48)) |
+                          ((unsigned __int128)f[4] << 64);
+    unsigned __int128 A = F, R = ~(unsigned __int128)0;
+    int r = 0;
+#pragma unroll
+    for (int len = 1; len <= K; len <<= 1) {
+      if (K & len) { R &= (A >> r); r += len; }
+      A &= (A >> len);
+    }
+    return (u32)((u64)R & 0xFFFFu);
+  }
+}
+
+// ---- sinks: what happens to a generated k-mer ---------------------------------------------------
+struct KeySink {     // dense key (+id) stream
+  u64* keys; u64* ids; u64 cap; u64* cursor;
+};
+
+// ---- pass B: FASTQ tile -> k-mers ------------------------------------------------------------------
+// SINK 0: write canonical (or forward) keys to sink.keys (block-contiguous, order of blocks free)
+// SINK 1: insert straight into the count table (val += 1), no key stream at all
+template <int K, int HASH, int SINK>
+__global__ void __launch_bounds__(TILE_THREADS)
+k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ tile_lines,
+              const u32* __restrict__ block_sums, KeySink sink, TableView table, u64* __restrict__ n_kmers,
+              u32* __restrict__ perr, const bool CANON, const bool NSPLIT, const u64 tile_begin) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  __shared__ u32 s_codes[TILE_GROUPS + 1];
+  __shared__ u32 s_flags[TILE_GROUPS + 1];
+  __shared__ u32 s_aux[HALO_GROUPS * 2];       // halo: line-start masks / popcounts
+  __shared__ u32 s_tmp[TILE_THREADS / 32 + 1];
+  __shared__ unsigned short s_list[TILE_BYTES];
+  __shared__ u64 s_base;
+
+  const int t = threadIdx.x;
+  const u64 tile = tile_begin + blockIdx.x;
+  const u64 tile_off = tile * TILE_BYTES;
+  const u64 off = tile_off + (u64)t * GROUP_BYTES;
+
+  // -- P1: load + classify own group (and, for the first HALO_GROUPS threads, a halo group)
+  uint4 v = load_group(bytes, off, n);
+  Group g = classify(v);
+  u32 ls = (off < n) ? line_starts(g.eol, prev_is_eol(bytes, off, n)) : 0u;
+  s_codes[t] = g.codes;
+  u32 hls = 0, heol = 0, hn = 0;
+  if (t < HALO_GROUPS) {
+    u64 hoff = tile_off + TILE_BYTES + (u64)t * GROUP_BYTES;
+    uint4 hv = load_group(bytes, hoff, n);
+    Group hg = classify(hv);
+    hls = (hoff < n) ? line_starts(hg.eol, prev_is_eol(bytes, hoff, n)) : 0u;
+    heol = hg.eol; hn = hg.nmask;
+    s_codes[TILE_THREADS + t] = hg.codes;
+    s_aux[t] = __popc(hls);
+  }
+  if (t == 0) s_codes[TILE_GROUPS] = 0;
+
+  // -- P2: line number at the start of every group
+  u32 total_ls;
+  u32 before = block_excl_scan(__popc(ls), s_tmp, total_ls);
+  const u32 tile_first = tile_lines[tile] + block_sums[tile >> 10];
+  // (block_excl_scan ends with a barrier: s_aux is visible)
+
+  // -- P3: per-byte "base of a sequence line" flags; header checks at line starts
+  {
+    u32 idx = tile_first + before;  // number of line starts before this group
+    u32 flags;
+    if (ls == 0) {
+      // every byte of the group is on line (idx-1); sequence lines are 1 mod 4
+      flags = (idx != 0 && ((idx - 1) & 3u) == 1u) ? (~g.eol & 0xFFFFu) : 0u;
+    } else {
+      flags = 0;
+      u32 err = 0;
+#pragma unroll
+      for (int b = 0; b < GROUP_BYTES; ++b) {
+        if ((ls >> b) & 1u) {
+          u32 c = byte_of(v, b);
+          if ((idx & 3u) == 0u && c != '@') err |= PERR_NO_AT;
+          if ((idx & 3u) == 2u && c != '+') err |= PERR_NO_PLUS;
+          ++idx;
+        }
+        if (idx != 0 && ((idx - 1) & 3u) == 1u) flags |= (1u << b);
+      }
+      flags &= ~g.eol;
+      if (err) atomicOr(perr, err);
+    }
+    if (NSPLIT) flags &= ~g.nmask;
+    s_flags[t] = flags & 0xFFFFu;
+    if (t < HALO_GROUPS) {
+      u32 hidx = tile_first + total_ls;
+      for (int q = 0; q < t; ++q) hidx += s_aux[q];
+      u32 hflags = 0;
+#pragma unroll
+      for (int b = 0; b < GROUP_BYTES; ++b) {
+        if ((hls >> b) & 1u) ++hidx;
+        if (hidx != 0 && ((hidx - 1) & 3u) == 1u) hflags |= (1u << b);
+      }
+      hflags &= ~heol;
+      if (NSPLIT) hflags &= ~hn;
+      s_flags[TILE_THREADS + t] = hflags & 0xFFFFu;
+    }
+    if (t == 0) s_flags[TILE_GROUPS] = 0;
+  }
+  __syncthreads();
+
+  // -- P4: valid k-mer starts of this group -> dense work list
+  u32 f5[5];
+#pragma unroll
+  for (int q = 0; q < 5; ++q) f5[q] = s_flags[min(t + q, TILE_GROUPS)];
+  u32 valid = window_all_set<K>(f5);
+  u32 total;
+  u32 rank = block_excl_scan(__popc(valid), s_tmp, total);
+  {
+    u32 m = valid;
+    while (m) {
+      int j = __ffs(m) - 1;
+      m &= m - 1;
+      s_list[rank++] = (unsigned short)(t * GROUP_BYTES + j);
+    }
+  }
+  if (t == 0) {
+    u64 base = 0;
+    if (total) {
+      if (SINK == 0) base = atomicAdd(sink.cursor, (u64)total);
+      atomicAdd(n_kmers, (u64)total);
+    }
+    s_base = base;
+  }
+  __syncthreads();
+
+  // -- P5: dense loop over the tile's k-mers
+  u32 n_new = 0;
+  for (u32 r = t; r < total; r += TILE_THREADS) {
+    const u32 pos = s_list[r];
+    const int gi = pos >> 4, j = pos & 15;
+    u32 c5[5];
+#pragma unroll
+    for (int q = 0; q < 5; ++q) c5[q] = s_codes[min(gi + q, TILE_GROUPS)];
+    Key<NW> key = extract_kmer<K>(c5, j);
+    if (CANON) key = canonical<K>(key);
+    if (SINK == 0) {
+      const u64 at = s_base + r;
+      if (at < sink.cap) {
+#pragma unroll
+        for (int w = 0; w < NW; ++w) sink.keys[at * NW + w] = key.w[w];
+      } else {
+        atomicOr(perr, PERR_OVERFLOW);
+      }
+    } else {
+      bool was_new;
+      u64 slot = table_upsert<NW>(table, key, store_hash<K, HASH>(key), was_new);
+      if (slot != ~0ULL) {
+        atomicAdd(&reinterpret_cast<Slot<NW>*>(table.slots)[slot].val, 1u);
+        n_new += was_new ? 1u : 0u;
+      }
+    }
+  }
+  if (SINK == 1) {
+    // one size update per warp
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) n_new += __shfl_xor_sync(0xffffffffu, n_new, d);
+    if ((t & 31) == 0 && n_new) atomicAdd(table.size, (u64)n_new);
+  }
+}
+
+}  // namespace kmi

@@ -1,0 +1,95 @@
+// kmi_table.cuh — open-addressing k-mer table in HBM and its kernels (sm_100a).
+// Replaces the local half of dsc::counting_densehash_map / densehash_multimap
+// (reference src/containers/densehash_map.hpp:928-1229,2015-2400 over google::dense_hash_map):
+// power-of-two slots, the reference's store hash picks the home slot, linear probing inside HBM
+// sectors (one 16-byte slot per K<=31 key, one 32-byte slot per K<=63 key, so a probe touches a
+// single 32-byte sector), claim by 64/128-bit CAS on the key, count by a fire-and-forget RED.
+#pragma once
+#include "kmi_device.cuh"
+
+namespace kmi {
+
+template <int NW> struct Slot;
+template <> struct alignas(16) Slot<1> { u64 key; u32 val; u32 aux; };
+template <> struct alignas(32) Slot<2> { u64 lo; u64 hi; u32 val; u32 aux; u64 pad; };
+
+struct TableView {
+  void* slots;
+  u64 mask;        // slots - 1
+  u64* size;       // device counter: occupied (live) keys
+  u32* error;      // device flag: 1 = probe limit hit (table full)
+};
+
+// ---- raw slot access -----------------------------------------------------------------------
+__device__ __forceinline__ u64 ld_cg_u64(const u64* p) {
+  u64 v; asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(v) : "l"(p)); return v;
+}
+__device__ __forceinline__ void ld_cg_u64x2(const void* p, u64& a, u64& b) {
+  asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p));
+}
+__device__ __forceinline__ void cas128(void* addr, u64 clo, u64 chi, u64 vlo, u64 vhi, u64& olo, u64& ohi) {
+  asm volatile(
+      "{\n .reg .b128 c, v, o;\n mov.b128 c, {%2, %3};\n mov.b128 v, {%4, %5};\n"
+      " atom.global.relaxed.gpu.cas.b128 o, [%6], c, v;\n mov.b128 {%0, %1}, o;\n}\n"
+      : "=l"(olo), "=l"(ohi) : "l"(clo), "l"(chi), "l"(vlo), "l"(vhi), "l"(addr) : "memory");
+}
+
+template <int NW> __device__ __forceinline__ Key<NW> slot_key(const Slot<NW>* s);
+template <> __device__ __forceinline__ Key<1> slot_key<1>(const Slot<1>* s) {
+  Key<1> k; k.w[0] = ld_cg_u64(&s->key); return k;
+}
+template <> __device__ __forceinline__ Key<2> slot_key<2>(const Slot<2>* s) {
+  Key<2> k; ld_cg_u64x2(s, k.w[0], k.w[1]); return k;
+}
+template <int NW> __device__ __forceinline__ bool is_empty(const Key<NW>& k) { return k.w[NW - 1] == KEY_EMPTY_TOP; }
+template <int NW> __device__ __forceinline__ bool is_deleted(const Key<NW>& k) { return k.w[NW - 1] == KEY_DELETED_TOP; }
+template <int NW> __device__ __forceinline__ bool is_live(const Key<NW>& k) { return (k.w[NW - 1] >> 63) == 0; }
+
+// try to claim an EMPTY slot for `key`: true when this thread's CAS installed it; `seen` is what
+// the slot held before the CAS
+template <int NW> __device__ __forceinline__ bool slot_claim(Slot<NW>* s, const Key<NW>& key, Key<NW>& seen);
+template <> __device__ __forceinline__ bool slot_claim<1>(Slot<1>* s, const Key<1>& key, Key<1>& seen) {
+  seen.w[0] = atomicCAS(&s->key, KEY_EMPTY_TOP, key.w[0]);
+  return seen.w[0] == KEY_EMPTY_TOP;
+}
+template <> __device__ __forceinline__ bool slot_claim<2>(Slot<2>* s, const Key<2>& key, Key<2>& seen) {
+  cas128(s, 0ULL, KEY_EMPTY_TOP, key.w[0], key.w[1], seen.w[0], seen.w[1]);
+  return seen.w[1] == KEY_EMPTY_TOP;
+}
+
+// ---- find-or-insert: returns the slot index of `key`, claiming a slot when absent.
+// was_new tells whether this call created the entry. Returns ~0 when the table is full.
+template <int NW>
+__device__ __forceinline__ u64 table_upsert(const TableView& t, const Key<NW>& key, u64 hash, bool& was_new) {
+  Slot<NW>* slots = reinterpret_cast<Slot<NW>*>(t.slots);
+  u64 i = hash & t.mask;
+  was_new = false;
+  for (u64 probes = 0; probes <= t.mask; ++probes) {
+    Key<NW> cur = slot_key<NW>(slots + i);
+    if (key_eq<NW>(cur, key)) return i;
+    if (is_empty<NW>(cur)) {
+      Key<NW> seen;
+      if (slot_claim<NW>(slots + i, key, seen)) { was_new = true; return i; }
+      if (key_eq<NW>(seen, key)) return i;  // a racing twin installed the same key first
+    }
+    i = (i + 1) & t.mask;
+  }
+  atomicExch(t.error, 1u);
+  return ~0ULL;
+}
+
+// read-only probe: slot index or ~0
+template <int NW>
+__device__ __forceinline__ u64 table_find(const TableView& t, const Key<NW>& key, u64 hash) {
+  const Slot<NW>* slots = reinterpret_cast<const Slot<NW>*>(t.slots);
+  u64 i = hash & t.mask;
+  for (u64 probes = 0; probes <= t.mask; ++probes) {
+    Key<NW> cur = slot_key<NW>(slots + i);
+    if (key_eq<NW>(cur, key)) return i;
+    if (is_empty<NW>(cur)) return ~0ULL;
+    i = (i + 1) & t.mask;
+  }
+  return ~0ULL;
+}
+
+}  // namespace kmi
