@@ -1,0 +1,62 @@
+"""Builds libkmi.so (the C-ABI CUDA library) in-tree with nvcc for sm_100a.
+
+One object per supported k-mer length (kmi_ops_inst.cu with -DKMI_K=...) plus the API object,
+compiled in parallel, linked into kmerind_b200/libkmi.so. No GPU is needed to build.
+"""
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+OUT = os.path.join(HERE, "libkmi.so")
+KS = (15, 21, 31, 35, 47, 63)
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo",
+         "-Xcompiler", "-fPIC", "-diag-suppress", "62,63"]
+
+
+def _newer(target, sources):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources)
+
+
+def _run(cmd):
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("build failed: %s\n%s\n%s" % (" ".join(cmd), r.stdout, r.stderr))
+
+
+def build(force=False, verbose=False):
+    hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh")]
+    hdrs.append(os.path.join(HERE, "..", "include", "kmi.h"))
+    objdir = os.path.join(CSRC, "build")
+    os.makedirs(objdir, exist_ok=True)
+    jobs = []
+    objs = []
+    inst = os.path.join(CSRC, "kmi_ops_inst.cu")
+    for k in KS:
+        o = os.path.join(objdir, "kmi_ops_k%d.o" % k)
+        objs.append(o)
+        if force or _newer(o, hdrs + [inst]):
+            jobs.append([NVCC] + FLAGS + ["-DKMI_K=%d" % k, "-c", inst, "-o", o])
+    api = os.path.join(CSRC, "kmi_api.cu")
+    o = os.path.join(objdir, "kmi_api.o")
+    objs.append(o)
+    if force or _newer(o, hdrs + [api]):
+        jobs.append([NVCC] + FLAGS + ["-c", api, "-o", o])
+    if jobs:
+        with ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
+            list(ex.map(_run, jobs))
+    if jobs or not os.path.exists(OUT):
+        _run([NVCC, "-shared", "-o", OUT] + objs + ["-cudart", "static"])
+    if verbose:
+        print("built", OUT)
+    return OUT
+
+
+if __name__ == "__main__":
+    build(force="--force" in sys.argv, verbose=True)

@@ -1,0 +1,878 @@
+// kmi_api.cu — the C ABI of include/kmi.h: host-side orchestration of the sm_100a kernels.
+// No CPU fallback: every compute entry point needs a CUDA device and fails with KMI_ERR_CUDA
+// otherwise. Reference interfaces replaced are cited in include/kmi.h next to each function.
+#define KMI_SHARED_KERNELS
+#include "../../include/kmi.h"
+#include "kmi_ops.cuh"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+namespace kmi {
+const Ops* kmi_ops_k15(int);
+const Ops* kmi_ops_k21(int);
+const Ops* kmi_ops_k31(int);
+const Ops* kmi_ops_k35(int);
+const Ops* kmi_ops_k47(int);
+const Ops* kmi_ops_k63(int);
+}  // namespace kmi
+
+using namespace kmi;
+
+static thread_local char g_err[512] = "";
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+#define CU(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess) return fail(KMI_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+#define OK(call)            \
+  do {                      \
+    int r_ = (call);        \
+    if (r_ != KMI_OK) return r_; \
+  } while (0)
+
+namespace {
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int ensure(size_t bytes) {
+    if (bytes <= cap) return KMI_OK;
+    if (p) { cudaFree(p); p = nullptr; cap = 0; }
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) { p = nullptr; return fail(KMI_ERR_NOMEM, "cudaMalloc(%zu): %s", want, cudaGetErrorString(e)); }
+    cap = want;
+    return KMI_OK;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+// device counters block
+enum { CTR_SIZE = 0, CTR_NKMERS = 1, CTR_CURSOR = 2, CTR_CK0 = 3, CTR_CK1 = 4, CTR_REMOVED = 5, CTR_ERR = 6, CTR_PERR = 7, CTR_N = 8 };
+
+}  // namespace
+
+struct kmi_index {
+  kmi_config cfg;
+  const Ops* ops = nullptr;
+  cudaStream_t stream = 0;
+  int nw = 1;
+  size_t slot_bytes = 16;
+  // table
+  void* slots = nullptr;
+  u64 cap = 0;             // number of slots (power of two)
+  u64* ctr = nullptr;      // device counters (CTR_N x u64)
+  u64 size_exact = 0;      // last size read back
+  u64 size_upper = 0;      // upper bound on the current size (exact + keys issued since)
+  // scratch
+  DevBuf tile_lines, block_sums, stage_in, stage_keys, stage_vals, stage_out, stage_found, hist, hist_sums;
+  // POSITION mode: tuple log + CSR
+  DevBuf log_keys, log_ids, log_keys2, log_ids2, offsets, csr_sums, values;
+  u64 log_n = 0;
+  bool csr_dirty = false;
+  // accounting
+  u64 launches = 0;
+  float stage_ms[3] = {0, 0, 0};
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+
+  TableView view() const {
+    TableView t;
+    t.slots = slots; t.mask = cap - 1; t.size = ctr + CTR_SIZE; t.error = reinterpret_cast<u32*>(ctr + CTR_ERR);
+    return t;
+  }
+};
+
+static const Ops* find_ops(int k, int hash) {
+  switch (k) {
+    case 15: return kmi_ops_k15(hash);
+    case 21: return kmi_ops_k21(hash);
+    case 31: return kmi_ops_k31(hash);
+    case 35: return kmi_ops_k35(hash);
+    case 47: return kmi_ops_k47(hash);
+    case 63: return kmi_ops_k63(hash);
+    default: return nullptr;
+  }
+}
+
+static u64 pow2_at_least(u64 x) {
+  u64 p = 1024;
+  while (p < x) p <<= 1;
+  return p;
+}
+static const double MAX_LOAD = 0.7;  // dense_hash_map max load, reference densehash_map.hpp:969
+
+static int read_ctr(kmi_index* idx, int which, u64* out) {
+  CU(cudaMemcpyAsync(out, idx->ctr + which, sizeof(u64), cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaStreamSynchronize(idx->stream));
+  return KMI_OK;
+}
+static int zero_ctr(kmi_index* idx, int which, int count = 1) {
+  CU(cudaMemsetAsync(idx->ctr + which, 0, sizeof(u64) * count, idx->stream));
+  return KMI_OK;
+}
+static int check_table_error(kmi_index* idx) {
+  u64 e = 0;
+  OK(read_ctr(idx, CTR_ERR, &e));
+  if (e) return fail(KMI_ERR_CAPACITY, "hash table overflow (probe limit reached)");
+  return KMI_OK;
+}
+
+// allocate a cleared table of `cap` slots
+static int table_alloc(kmi_index* idx, u64 cap, void** out) {
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, cap * idx->slot_bytes);
+  if (e != cudaSuccess) return fail(KMI_ERR_NOMEM, "cudaMalloc table %llu slots: %s", (unsigned long long)cap, cudaGetErrorString(e));
+  idx->ops->table_clear(idx->stream, p, cap);
+  idx->launches++;
+  *out = p;
+  return KMI_OK;
+}
+
+// grow (rehash) to `new_cap` slots
+static int table_grow(kmi_index* idx, u64 new_cap) {
+  void* fresh = nullptr;
+  OK(table_alloc(idx, new_cap, &fresh));
+  void* old = idx->slots;
+  u64 old_cap = idx->cap;
+  idx->slots = fresh;
+  idx->cap = new_cap;
+  OK(zero_ctr(idx, CTR_SIZE));
+  if (old) {
+    idx->ops->rehash(idx->stream, old, old_cap, idx->view());
+    idx->launches++;
+    CU(cudaStreamSynchronize(idx->stream));
+    CU(cudaFree(old));
+  }
+  OK(read_ctr(idx, CTR_SIZE, &idx->size_exact));
+  idx->size_upper = idx->size_exact;
+  return KMI_OK;
+}
+
+// Make room for up to `incoming` more distinct keys. Returns in *grant how many keys the caller
+// may issue before calling again (>= 1 unless incoming == 0). The table never exceeds MAX_LOAD:
+// the bound is tracked on the host and refreshed from the device counter only when it runs out.
+static int table_room(kmi_index* idx, u64 incoming, u64* grant) {
+  if (incoming == 0) { *grant = 0; return KMI_OK; }
+  if (!idx->slots) OK(table_grow(idx, pow2_at_least((u64)(std::min<u64>(incoming, 1u << 20) / MAX_LOAD) + 1)));
+  for (;;) {
+    u64 limit = (u64)(idx->cap * MAX_LOAD);
+    u64 slack = limit > idx->size_upper ? limit - idx->size_upper : 0;
+    if (slack >= incoming) { *grant = incoming; break; }
+    // refresh the bound
+    if (idx->size_upper != idx->size_exact) {
+      OK(read_ctr(idx, CTR_SIZE, &idx->size_exact));
+      idx->size_upper = idx->size_exact;
+      continue;
+    }
+    u64 min_chunk = std::max<u64>(idx->cap / 8, 1u << 12);
+    if (slack >= min_chunk) { *grant = std::min(slack, incoming); break; }
+    OK(table_grow(idx, idx->cap * 2));
+  }
+  idx->size_upper += *grant;
+  return KMI_OK;
+}
+
+extern "C" const char* kmi_last_error(void) { return g_err; }
+
+extern "C" int kmi_create(const kmi_config* cfg, kmi_index** out) {
+  if (!cfg || !out) return fail(KMI_ERR_ARG, "null argument");
+  *out = nullptr;
+  if (cfg->k < 2 || cfg->k > 63 || cfg->k == 32) return fail(KMI_ERR_ARG, "k=%d needs >= 2 pad bits (k <= 31 or 33..63)", cfg->k);
+  if (cfg->mode != KMI_MODE_COUNT && cfg->mode != KMI_MODE_POSITION) return fail(KMI_ERR_ARG, "bad mode %d", cfg->mode);
+  if (cfg->hash < 0 || cfg->hash > 2) return fail(KMI_ERR_ARG, "bad hash kind %d", cfg->hash);
+  if (cfg->nranks < 1 || cfg->nranks > MAX_RANKS || cfg->rank < 0 || cfg->rank >= cfg->nranks)
+    return fail(KMI_ERR_ARG, "bad rank %d / nranks %d (max %d)", cfg->rank, cfg->nranks, MAX_RANKS);
+  const Ops* ops = find_ops(cfg->k, cfg->hash);
+  if (!ops) return fail(KMI_ERR_UNSUPPORTED, "k=%d is not instantiated (built: 15, 21, 31, 35, 47, 63)", cfg->k);
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(KMI_ERR_CUDA, "no CUDA device (%s): this library has no CPU path", cudaGetErrorString(e));
+  if (cfg->device < 0 || cfg->device >= ndev) return fail(KMI_ERR_ARG, "device %d of %d", cfg->device, ndev);
+  CU(cudaSetDevice(cfg->device));
+  kmi_index* idx = new (std::nothrow) kmi_index();
+  if (!idx) return fail(KMI_ERR_NOMEM, "host allocation");
+  idx->cfg = *cfg;
+  idx->ops = ops;
+  idx->nw = ops->NW;
+  idx->slot_bytes = ops->NW == 1 ? sizeof(Slot<1>) : sizeof(Slot<2>);
+  e = cudaMalloc(&idx->ctr, sizeof(u64) * CTR_N);
+  if (e != cudaSuccess) { delete idx; return fail(KMI_ERR_CUDA, "cudaMalloc counters: %s", cudaGetErrorString(e)); }
+  cudaMemset(idx->ctr, 0, sizeof(u64) * CTR_N);
+  for (int i = 0; i < 4; ++i) cudaEventCreate(&idx->ev[i]);
+  *out = idx;
+  if (cfg->reserve) {
+    int r = kmi_reserve(idx, cfg->reserve);
+    if (r != KMI_OK) { kmi_destroy(idx); *out = nullptr; return r; }
+  }
+  return KMI_OK;
+}
+
+extern "C" void kmi_destroy(kmi_index* idx) {
+  if (!idx) return;
+  cudaSetDevice(idx->cfg.device);
+  cudaStreamSynchronize(idx->stream);
+  if (idx->slots) cudaFree(idx->slots);
+  if (idx->ctr) cudaFree(idx->ctr);
+  DevBuf* bufs[] = {&idx->tile_lines, &idx->block_sums, &idx->stage_in, &idx->stage_keys, &idx->stage_vals,
+                    &idx->stage_out, &idx->stage_found, &idx->hist, &idx->hist_sums, &idx->log_keys, &idx->log_ids,
+                    &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values};
+  for (DevBuf* b : bufs) b->release();
+  for (int i = 0; i < 4; ++i) if (idx->ev[i]) cudaEventDestroy(idx->ev[i]);
+  delete idx;
+}
+
+extern "C" int kmi_set_stream(kmi_index* idx, void* cuda_stream) {
+  if (!idx) return fail(KMI_ERR_ARG, "null index");
+  idx->stream = reinterpret_cast<cudaStream_t>(cuda_stream);
+  return KMI_OK;
+}
+
+extern "C" int kmi_reserve(kmi_index* idx, uint64_t n_distinct) {
+  if (!idx) return fail(KMI_ERR_ARG, "null index");
+  CU(cudaSetDevice(idx->cfg.device));
+  u64 want = pow2_at_least((u64)(n_distinct / MAX_LOAD) + 1);
+  if (want > idx->cap) OK(table_grow(idx, want));
+  return KMI_OK;
+}
+
+extern "C" int kmi_clear(kmi_index* idx) {
+  if (!idx) return fail(KMI_ERR_ARG, "null index");
+  CU(cudaSetDevice(idx->cfg.device));
+  if (idx->slots) { idx->ops->table_clear(idx->stream, idx->slots, idx->cap); idx->launches++; }
+  CU(cudaMemsetAsync(idx->ctr, 0, sizeof(u64) * CTR_N, idx->stream));
+  idx->size_exact = idx->size_upper = 0;
+  idx->log_n = 0;
+  idx->csr_dirty = false;
+  return KMI_OK;
+}
+
+// ---- record boundaries (pass A + scan), shared by parse and fused build ------------------------
+static int fastq_scan(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64* n_tiles_out) {
+  if ((reinterpret_cast<uintptr_t>(d_bytes) & 15) != 0) return fail(KMI_ERR_ARG, "device text buffer must be 16-byte aligned");
+  u64 n_tiles = (n + TILE_BYTES - 1) / TILE_BYTES;
+  *n_tiles_out = n_tiles;
+  if (n_tiles == 0) return KMI_OK;
+  if (n_tiles > 0x7fffffffULL) return fail(KMI_ERR_ARG, "block of %zu bytes too large for one call (max 8 TiB)", n);
+  u64 n_blocks = (n_tiles + 1023) / 1024;
+  OK(idx->tile_lines.ensure(sizeof(u32) * n_tiles));
+  OK(idx->block_sums.ensure(sizeof(u32) * n_blocks));
+  k_fastq_count_lines<<<(unsigned)n_tiles, TILE_THREADS, 0, idx->stream>>>(d_bytes, n, idx->tile_lines.as<u32>());
+  k_scan_l1<<<(unsigned)n_blocks, 1024, 0, idx->stream>>>(idx->tile_lines.as<u32>(), n_tiles, idx->block_sums.as<u32>());
+  k_scan_tiles<<<1, 1024, 0, idx->stream>>>(idx->block_sums.as<u32>(), n_blocks);
+  idx->launches += 3;
+  return KMI_OK;
+}
+static int parse_error(u64 perr) {
+  if (perr & PERR_NO_AT) return fail(KMI_ERR_FORMAT, "malformed FASTQ: missing @ on first line of a record");
+  if (perr & PERR_NO_PLUS) return fail(KMI_ERR_FORMAT, "malformed FASTQ: missing + on third line of a record");
+  if (perr & PERR_OVERFLOW) return fail(KMI_ERR_CAPACITY, "k-mer output buffer too small");
+  if (perr & PERR_HALO) return fail(KMI_ERR_FORMAT, "FASTA line structure too sparse for the tile halo");
+  return KMI_OK;
+}
+
+extern "C" int kmi_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset,
+                                   uint64_t* d_keys, uint64_t* d_ids, size_t cap, uint64_t* n_kmers) {
+  (void)file_offset;
+  if (!idx || (!d_bytes && n)) return fail(KMI_ERR_ARG, "null argument");
+  if (d_ids) return fail(KMI_ERR_UNSUPPORTED, "FASTQ position ids (ShortSequenceKmerId) are not built yet");
+  CU(cudaSetDevice(idx->cfg.device));
+  u64 n_tiles = 0;
+  OK(fastq_scan(idx, d_bytes, n, &n_tiles));
+  OK(zero_ctr(idx, CTR_NKMERS, 2));  // NKMERS, CURSOR
+  OK(zero_ctr(idx, CTR_PERR));
+  KeySink sink;
+  sink.keys = reinterpret_cast<u64*>(d_keys); sink.ids = nullptr; sink.cap = cap; sink.cursor = idx->ctr + CTR_CURSOR;
+  TableView none; none.slots = nullptr; none.mask = 0; none.size = nullptr; none.error = nullptr;
+  idx->ops->fastq_kmers(idx->stream, 0, d_bytes, n, n_tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), sink, none,
+                        idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0,
+                        idx->cfg.nsplit != 0, 0);
+  idx->launches++;
+  u64 host[8];
+  CU(cudaMemcpyAsync(host, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaStreamSynchronize(idx->stream));
+  if (n_kmers) *n_kmers = host[CTR_NKMERS];
+  return parse_error(host[CTR_PERR]);
+}
+
+// fused S1-S5: text -> table, no key stream in HBM
+extern "C" int kmi_build_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers) {
+  (void)file_offset;
+  if (!idx || (!d_bytes && n)) return fail(KMI_ERR_ARG, "null argument");
+  if (idx->cfg.mode != KMI_MODE_COUNT)
+    return fail(KMI_ERR_UNSUPPORTED, "FASTQ PositionIndex (ShortSequenceKmerId) is not built yet; use FASTA");
+  CU(cudaSetDevice(idx->cfg.device));
+  u64 n_tiles = 0;
+  CU(cudaEventRecord(idx->ev[0], idx->stream));
+  OK(fastq_scan(idx, d_bytes, n, &n_tiles));
+  CU(cudaEventRecord(idx->ev[1], idx->stream));
+  OK(zero_ctr(idx, CTR_NKMERS));
+  OK(zero_ctr(idx, CTR_PERR));
+  KeySink nosink; nosink.keys = nullptr; nosink.ids = nullptr; nosink.cap = 0; nosink.cursor = nullptr;
+  u64 tile = 0;
+  while (tile < n_tiles) {
+    // a FASTQ record spends at most half of its bytes on bases
+    u64 bytes_left = n - tile * TILE_BYTES;
+    u64 grant = 0;
+    OK(table_room(idx, bytes_left / 2 + 1, &grant));
+    u64 tiles = std::max<u64>(1, (grant * 2) / TILE_BYTES);
+    tiles = std::min(tiles, n_tiles - tile);
+    idx->ops->fastq_kmers(idx->stream, 1, d_bytes, n, tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), nosink,
+                          idx->view(), idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR),
+                          idx->cfg.canonical != 0, idx->cfg.nsplit != 0, tile);
+    idx->launches++;
+    tile += tiles;
+  }
+  CU(cudaEventRecord(idx->ev[2], idx->stream));
+  u64 host[8];
+  CU(cudaMemcpyAsync(host, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaStreamSynchronize(idx->stream));
+  cudaEventElapsedTime(&idx->stage_ms[0], idx->ev[0], idx->ev[1]);
+  cudaEventElapsedTime(&idx->stage_ms[1], idx->ev[1], idx->ev[2]);
+  idx->stage_ms[2] = 0;
+  idx->size_exact = idx->size_upper = host[CTR_SIZE];
+  if (n_kmers) *n_kmers = host[CTR_NKMERS];
+  if (host[CTR_ERR]) return fail(KMI_ERR_CAPACITY, "hash table overflow (probe limit reached)");
+  return parse_error(host[CTR_PERR]);
+}
+
+extern "C" int kmi_build_fastq(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers) {
+  if (!idx || (!bytes && n)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  OK(idx->stage_in.ensure(n + 64));
+  CU(cudaMemcpyAsync(idx->stage_in.p, bytes, n, cudaMemcpyHostToDevice, idx->stream));
+  return kmi_build_fastq_dev(idx, idx->stage_in.as<uint8_t>(), n, file_offset, n_kmers);
+}
+
+// ---- insert --------------------------------------------------------------------------------------------
+static int log_append(kmi_index* idx, const u64* d_keys, const u64* d_vals, size_t n) {
+  size_t kb = sizeof(u64) * idx->nw;
+  if ((idx->log_n + n) * kb > idx->log_keys.cap) {
+    // grow geometrically, preserving contents
+    DevBuf nk, nv;
+    size_t want = std::max<size_t>((idx->log_n + n) * 2, 1024);
+    OK(nk.ensure(want * kb));
+    OK(nv.ensure(want * sizeof(u64)));
+    if (idx->log_n) {
+      CU(cudaMemcpyAsync(nk.p, idx->log_keys.p, idx->log_n * kb, cudaMemcpyDeviceToDevice, idx->stream));
+      CU(cudaMemcpyAsync(nv.p, idx->log_ids.p, idx->log_n * sizeof(u64), cudaMemcpyDeviceToDevice, idx->stream));
+      CU(cudaStreamSynchronize(idx->stream));
+    }
+    idx->log_keys.release(); idx->log_ids.release();
+    idx->log_keys = nk; idx->log_ids = nv;
+  }
+  u64* dst = idx->log_keys.as<u64>() + idx->log_n * idx->nw;
+  if (idx->cfg.canonical) { idx->ops->canonicalize(idx->stream, d_keys, dst, n); idx->launches++; }
+  else CU(cudaMemcpyAsync(dst, d_keys, n * kb, cudaMemcpyDeviceToDevice, idx->stream));
+  CU(cudaMemcpyAsync(idx->log_ids.as<u64>() + idx->log_n, d_vals, n * sizeof(u64), cudaMemcpyDeviceToDevice, idx->stream));
+  idx->log_n += n;
+  return KMI_OK;
+}
+
+static int insert_keys_chunked(kmi_index* idx, const u64* d_keys, size_t n, bool canon) {
+  size_t done = 0;
+  while (done < n) {
+    u64 grant = 0;
+    OK(table_room(idx, n - done, &grant));
+    idx->ops->insert_keys(idx->stream, idx->view(), d_keys + done * idx->nw, grant, canon);
+    idx->launches++;
+    done += grant;
+  }
+  return KMI_OK;
+}
+
+extern "C" int kmi_insert_dev(kmi_index* idx, const uint64_t* d_keys_, const uint64_t* d_vals_, size_t n) {
+  if (!idx || (!d_keys_ && n)) return fail(KMI_ERR_ARG, "null argument");
+  const u64* d_keys = reinterpret_cast<const u64*>(d_keys_);
+  const u64* d_vals = reinterpret_cast<const u64*>(d_vals_);
+  CU(cudaSetDevice(idx->cfg.device));
+  if (n == 0) return KMI_OK;
+  if (idx->nw == 2 && (reinterpret_cast<uintptr_t>(d_keys) & 15)) return fail(KMI_ERR_ARG, "2-word keys must be 16-byte aligned");
+  if (idx->cfg.mode == KMI_MODE_POSITION) {
+    if (!d_vals) return fail(KMI_ERR_ARG, "POSITION insert needs ids");
+    OK(log_append(idx, d_keys, d_vals, n));
+    // multiplicities go into the table now (keys in the log are already canonical)
+    OK(insert_keys_chunked(idx, idx->log_keys.as<u64>() + (idx->log_n - n) * idx->nw, n, false));
+    idx->csr_dirty = true;
+  } else {
+    OK(insert_keys_chunked(idx, d_keys, n, idx->cfg.canonical != 0));
+  }
+  return KMI_OK;
+}
+
+extern "C" int kmi_insert(kmi_index* idx, const uint64_t* keys, const uint64_t* vals, size_t n) {
+  if (!idx || (!keys && n)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  if (n == 0) return KMI_OK;
+  size_t kb = sizeof(u64) * idx->nw;
+  OK(idx->stage_keys.ensure(n * kb));
+  CU(cudaMemcpyAsync(idx->stage_keys.p, keys, n * kb, cudaMemcpyHostToDevice, idx->stream));
+  const uint64_t* dv = nullptr;
+  if (idx->cfg.mode == KMI_MODE_POSITION) {
+    if (!vals) return fail(KMI_ERR_ARG, "POSITION insert needs ids");
+    OK(idx->stage_vals.ensure(n * sizeof(u64)));
+    CU(cudaMemcpyAsync(idx->stage_vals.p, vals, n * sizeof(u64), cudaMemcpyHostToDevice, idx->stream));
+    dv = idx->stage_vals.as<uint64_t>();
+  }
+  OK(kmi_insert_dev(idx, idx->stage_keys.as<uint64_t>(), dv, n));
+  CU(cudaStreamSynchronize(idx->stream));
+  return check_table_error(idx);
+}
+
+// ---- POSITION mode: (re)build the CSR from the tuple log ----------------------------------------------
+static int csr_finalize(kmi_index* idx) {
+  if (!idx->csr_dirty) return KMI_OK;
+  if (!idx->slots) { idx->csr_dirty = false; return KMI_OK; }
+  u64 n_blocks = (idx->cap + 1023) / 1024;
+  OK(idx->offsets.ensure(sizeof(u64) * idx->cap));
+  OK(idx->csr_sums.ensure(sizeof(u64) * n_blocks));
+  OK(idx->values.ensure(sizeof(u64) * std::max<u64>(idx->log_n, 1)));
+  idx->ops->zero_aux(idx->stream, idx->slots, idx->cap);
+  idx->ops->csr_scan_l1(idx->stream, idx->slots, idx->cap, idx->offsets.as<u64>(), idx->csr_sums.as<u64>());
+  k_scan64<<<1, 1024, 0, idx->stream>>>(idx->csr_sums.as<u64>(), n_blocks);
+  k_csr_add_block<<<(unsigned)n_blocks, 1024, 0, idx->stream>>>(idx->offsets.as<u64>(), idx->cap, idx->csr_sums.as<u64>());
+  idx->ops->csr_fill(idx->stream, idx->view(), idx->log_keys.as<u64>(), idx->log_ids.as<u64>(), idx->log_n,
+                     idx->offsets.as<u64>(), idx->values.as<u64>());
+  idx->launches += 5;
+  idx->csr_dirty = false;
+  return KMI_OK;
+}
+
+// ---- batched query -----------------------------------------------------------------------------------
+extern "C" int kmi_find_dev(kmi_index* idx, const uint64_t* d_keys, size_t n, uint64_t* d_vals, uint8_t* d_found) {
+  if (!idx || (!d_keys && n)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  if (n == 0) return KMI_OK;
+  if (!idx->slots) {
+    if (d_vals) CU(cudaMemsetAsync(d_vals, 0, n * sizeof(u64), idx->stream));
+    if (d_found) CU(cudaMemsetAsync(d_found, 0, n, idx->stream));
+    return KMI_OK;
+  }
+  idx->ops->lookup(idx->stream, idx->view(), reinterpret_cast<const u64*>(d_keys), n, reinterpret_cast<u64*>(d_vals), d_found,
+                   nullptr, idx->cfg.canonical != 0);
+  idx->launches++;
+  return KMI_OK;
+}
+// count(): presence (0/1) for a COUNT index, multiplicity for a POSITION index
+extern "C" int kmi_count_dev(kmi_index* idx, const uint64_t* d_keys, size_t n, uint64_t* d_counts) {
+  if (!idx || (!d_keys && n) || (!d_counts && n)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  if (n == 0) return KMI_OK;
+  if (idx->cfg.mode == KMI_MODE_POSITION) return kmi_find_dev(idx, d_keys, n, d_counts, nullptr);
+  OK(idx->stage_found.ensure(n));
+  OK(kmi_find_dev(idx, d_keys, n, nullptr, idx->stage_found.as<uint8_t>()));
+  k_widen_u8<<<grid_for(n, 256), 256, 0, idx->stream>>>(idx->stage_found.as<uint8_t>(), reinterpret_cast<u64*>(d_counts), n);
+  idx->launches++;
+  return KMI_OK;
+}
+
+static int stage_query(kmi_index* idx, const uint64_t* keys, size_t n) {
+  size_t kb = sizeof(u64) * idx->nw;
+  OK(idx->stage_keys.ensure(std::max<size_t>(n * kb, 16)));
+  OK(idx->stage_out.ensure(std::max<size_t>((n + 1) * sizeof(u64), 16)));
+  OK(idx->stage_found.ensure(std::max<size_t>(n, 16)));
+  CU(cudaMemcpyAsync(idx->stage_keys.p, keys, n * kb, cudaMemcpyHostToDevice, idx->stream));
+  return KMI_OK;
+}
+
+extern "C" int kmi_count(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* counts) {
+  if (!idx || (!keys && n) || (!counts && n)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  if (n == 0) return KMI_OK;
+  OK(stage_query(idx, keys, n));
+  DevBuf tmp;  // counts need their own buffer: count_dev uses stage_found internally
+  OK(tmp.ensure(n * sizeof(u64)));
+  int r = kmi_count_dev(idx, idx->stage_keys.as<uint64_t>(), n, tmp.as<uint64_t>());
+  if (r == KMI_OK) {
+    cudaError_t e = cudaMemcpyAsync(counts, tmp.p, n * sizeof(u64), cudaMemcpyDeviceToHost, idx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(idx->stream);
+    if (e != cudaSuccess) r = fail(KMI_ERR_CUDA, "count copy back: %s", cudaGetErrorString(e));
+  }
+  tmp.release();
+  return r;
+}
+
+extern "C" int kmi_find(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* vals, uint8_t* found) {
+  if (!idx || (!keys && n)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  if (n == 0) return KMI_OK;
+  OK(stage_query(idx, keys, n));
+  OK(kmi_find_dev(idx, idx->stage_keys.as<uint64_t>(), n, idx->stage_out.as<uint64_t>(), idx->stage_found.as<uint8_t>()));
+  if (vals) CU(cudaMemcpyAsync(vals, idx->stage_out.p, n * sizeof(u64), cudaMemcpyDeviceToHost, idx->stream));
+  if (found) CU(cudaMemcpyAsync(found, idx->stage_found.p, n, cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaStreamSynchronize(idx->stream));
+  return KMI_OK;
+}
+
+extern "C" int kmi_find_positions(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* offsets, uint64_t* vals, size_t cap) {
+  if (!idx || (!keys && n) || !offsets) return fail(KMI_ERR_ARG, "null argument");
+  if (idx->cfg.mode != KMI_MODE_POSITION) return fail(KMI_ERR_ARG, "find_positions needs a POSITION index");
+  CU(cudaSetDevice(idx->cfg.device));
+  offsets[0] = 0;
+  if (n == 0) return KMI_OK;
+  if (!idx->slots) { for (size_t i = 0; i <= n; ++i) offsets[i] = 0; return KMI_OK; }
+  OK(csr_finalize(idx));
+  OK(stage_query(idx, keys, n));
+  DevBuf slot_idx, out_off, out_vals;
+  int r = slot_idx.ensure(n * sizeof(u64));
+  if (r == KMI_OK) r = out_off.ensure((n + 1) * sizeof(u64));
+  if (r != KMI_OK) { slot_idx.release(); out_off.release(); return r; }
+  // multiplicities -> exclusive scan (n+1 entries) -> gather
+  cudaMemsetAsync(out_off.p, 0, (n + 1) * sizeof(u64), idx->stream);
+  idx->ops->lookup(idx->stream, idx->view(), idx->stage_keys.as<u64>(), n, out_off.as<u64>(), nullptr, slot_idx.as<u64>(),
+                   idx->cfg.canonical != 0);
+  k_scan64<<<1, 1024, 0, idx->stream>>>(out_off.as<u64>(), n + 1);
+  idx->launches += 2;
+  cudaMemcpyAsync(offsets, out_off.p, (n + 1) * sizeof(u64), cudaMemcpyDeviceToHost, idx->stream);
+  cudaStreamSynchronize(idx->stream);
+  u64 total = offsets[n];
+  if (total > cap) { slot_idx.release(); out_off.release(); return fail(KMI_ERR_CAPACITY, "find_positions: %llu values, capacity %zu", (unsigned long long)total, cap); }
+  if (total) {
+    r = out_vals.ensure(total * sizeof(u64));
+    if (r == KMI_OK) {
+      k_csr_gather<<<grid_for(n, 256), 256, 0, idx->stream>>>(slot_idx.as<u64>(), out_off.as<u64>(), n, idx->offsets.as<u64>(),
+                                                            idx->values.as<u64>(), out_vals.as<u64>(), total);
+      idx->launches++;
+      cudaMemcpyAsync(vals, out_vals.p, total * sizeof(u64), cudaMemcpyDeviceToHost, idx->stream);
+      cudaStreamSynchronize(idx->stream);
+    }
+  }
+  slot_idx.release(); out_off.release(); out_vals.release();
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(KMI_ERR_CUDA, "find_positions: %s", cudaGetErrorString(e));
+  return r;
+}
+
+extern "C" int kmi_erase(kmi_index* idx, const uint64_t* keys, size_t n) {
+  if (!idx || (!keys && n)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  if (n == 0 || !idx->slots) return KMI_OK;
+  OK(stage_query(idx, keys, n));
+  OK(zero_ctr(idx, CTR_REMOVED));
+  idx->ops->erase(idx->stream, idx->view(), idx->stage_keys.as<u64>(), n, idx->ctr + CTR_REMOVED, idx->cfg.canonical != 0);
+  idx->launches++;
+  if (idx->cfg.mode == KMI_MODE_POSITION && idx->log_n) {
+    // drop the erased keys' tuples from the log
+    size_t kb = sizeof(u64) * idx->nw;
+    OK(idx->log_keys2.ensure(idx->log_keys.cap));
+    OK(idx->log_ids2.ensure(idx->log_ids.cap));
+    OK(zero_ctr(idx, CTR_CURSOR));
+    idx->ops->log_filter(idx->stream, idx->view(), idx->log_keys.as<u64>(), idx->log_ids.as<u64>(), idx->log_n,
+                         idx->log_keys2.as<u64>(), idx->log_ids2.as<u64>(), idx->ctr + CTR_CURSOR);
+    idx->launches++;
+    u64 kept = 0;
+    OK(read_ctr(idx, CTR_CURSOR, &kept));
+    std::swap(idx->log_keys, idx->log_keys2);
+    std::swap(idx->log_ids, idx->log_ids2);
+    idx->log_n = kept;
+    idx->csr_dirty = true;
+    (void)kb;
+  }
+  OK(read_ctr(idx, CTR_SIZE, &idx->size_exact));
+  idx->size_upper = idx->size_exact;
+  return KMI_OK;
+}
+
+// ---- accessors -----------------------------------------------------------------------------------------
+extern "C" int kmi_num_keys(kmi_index* idx, uint64_t* n) {
+  if (!idx || !n) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  u64 v = 0;
+  OK(read_ctr(idx, CTR_SIZE, &v));
+  idx->size_exact = idx->size_upper = v;
+  *n = v;
+  return check_table_error(idx);
+}
+extern "C" int kmi_local_size(kmi_index* idx, uint64_t* n) {
+  if (!idx || !n) return fail(KMI_ERR_ARG, "null argument");
+  if (idx->cfg.mode == KMI_MODE_POSITION) {
+    CU(cudaSetDevice(idx->cfg.device));
+    CU(cudaStreamSynchronize(idx->stream));
+    *n = idx->log_n;
+    return KMI_OK;
+  }
+  return kmi_num_keys(idx, n);
+}
+
+extern "C" int kmi_dump(kmi_index* idx, uint64_t* keys, uint64_t* vals, size_t cap, size_t* n_out) {
+  if (!idx || !n_out) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  *n_out = 0;
+  size_t kb = sizeof(u64) * idx->nw;
+  if (idx->cfg.mode == KMI_MODE_POSITION) {
+    if (idx->log_n > cap) return fail(KMI_ERR_CAPACITY, "dump: %llu tuples, capacity %zu", (unsigned long long)idx->log_n, cap);
+    if (idx->log_n) {
+      if (keys) CU(cudaMemcpyAsync(keys, idx->log_keys.p, idx->log_n * kb, cudaMemcpyDeviceToHost, idx->stream));
+      if (vals) CU(cudaMemcpyAsync(vals, idx->log_ids.p, idx->log_n * sizeof(u64), cudaMemcpyDeviceToHost, idx->stream));
+    }
+    CU(cudaStreamSynchronize(idx->stream));
+    *n_out = idx->log_n;
+    return KMI_OK;
+  }
+  u64 size = 0;
+  OK(read_ctr(idx, CTR_SIZE, &size));
+  if (size > cap) return fail(KMI_ERR_CAPACITY, "dump: %llu entries, capacity %zu", (unsigned long long)size, cap);
+  if (size == 0 || !idx->slots) return KMI_OK;
+  DevBuf dk, dv;
+  int r = dk.ensure(size * kb);
+  if (r == KMI_OK) r = dv.ensure(size * sizeof(u64));
+  if (r == KMI_OK) {
+    zero_ctr(idx, CTR_CURSOR);
+    idx->ops->dump(idx->stream, idx->slots, idx->cap, dk.as<u64>(), dv.as<u64>(), size, idx->ctr + CTR_CURSOR);
+    idx->launches++;
+    cudaError_t e = cudaSuccess;
+    if (keys) e = cudaMemcpyAsync(keys, dk.p, size * kb, cudaMemcpyDeviceToHost, idx->stream);
+    if (e == cudaSuccess && vals) e = cudaMemcpyAsync(vals, dv.p, size * sizeof(u64), cudaMemcpyDeviceToHost, idx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(idx->stream);
+    if (e != cudaSuccess) r = fail(KMI_ERR_CUDA, "dump: %s", cudaGetErrorString(e));
+    else *n_out = size;
+  }
+  dk.release(); dv.release();
+  return r;
+}
+
+extern "C" int kmi_checksum(kmi_index* idx, uint64_t* key_value_sum, uint64_t* value_sum) {
+  if (!idx) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  OK(zero_ctr(idx, CTR_CK0, 2));
+  if (idx->slots) { idx->ops->checksum(idx->stream, idx->slots, idx->cap, idx->ctr + CTR_CK0); idx->launches++; }
+  u64 host[2];
+  CU(cudaMemcpyAsync(host, idx->ctr + CTR_CK0, sizeof(host), cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaStreamSynchronize(idx->stream));
+  if (key_value_sum) *key_value_sum = host[0];
+  if (value_sum) *value_sum = host[1];
+  return KMI_OK;
+}
+
+extern "C" int kmi_table_info(kmi_index* idx, uint64_t* slots, uint64_t* slot_bytes, uint64_t* device_bytes) {
+  if (!idx) return fail(KMI_ERR_ARG, "null argument");
+  if (slots) *slots = idx->cap;
+  if (slot_bytes) *slot_bytes = idx->slot_bytes;
+  if (device_bytes) {
+    u64 b = idx->cap * idx->slot_bytes;
+    const DevBuf* bufs[] = {&idx->tile_lines, &idx->block_sums, &idx->stage_in, &idx->stage_keys, &idx->stage_vals,
+                            &idx->stage_out, &idx->stage_found, &idx->hist, &idx->hist_sums, &idx->log_keys, &idx->log_ids,
+                            &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values};
+    for (const DevBuf* d : bufs) b += d->cap;
+    *device_bytes = b;
+  }
+  return KMI_OK;
+}
+extern "C" int kmi_launch_count(kmi_index* idx, uint64_t* n) {
+  if (!idx || !n) return fail(KMI_ERR_ARG, "null argument");
+  *n = idx->launches;
+  return KMI_OK;
+}
+extern "C" int kmi_last_stage_ms(kmi_index* idx, float* ms3) {
+  if (!idx || !ms3) return fail(KMI_ERR_ARG, "null argument");
+  for (int i = 0; i < 3; ++i) ms3[i] = idx->stage_ms[i];
+  return KMI_OK;
+}
+
+// ---- stages ----------------------------------------------------------------------------------------------
+extern "C" int kmi_canonicalize_dev(kmi_index* idx, const uint64_t* d_keys, uint64_t* d_out, size_t n) {
+  if (!idx || ((!d_keys || !d_out) && n)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  idx->ops->canonicalize(idx->stream, reinterpret_cast<const u64*>(d_keys), reinterpret_cast<u64*>(d_out), n);
+  idx->launches++;
+  return KMI_OK;
+}
+extern "C" int kmi_hash_dev(kmi_index* idx, int which, const uint64_t* d_keys, uint64_t* d_hash, size_t n) {
+  if (!idx || ((!d_keys || !d_hash) && n)) return fail(KMI_ERR_ARG, "null argument");
+  if (which != 0 && which != 1) return fail(KMI_ERR_ARG, "which must be 0 (store) or 1 (dist)");
+  CU(cudaSetDevice(idx->cfg.device));
+  idx->ops->hash_keys(idx->stream, which, reinterpret_cast<const u64*>(d_keys), reinterpret_cast<u64*>(d_hash), n);
+  idx->launches++;
+  return KMI_OK;
+}
+
+extern "C" int kmi_partition_dev(kmi_index* idx, const uint64_t* d_keys, const uint64_t* d_vals, size_t n,
+                                 uint64_t* d_keys_out, uint64_t* d_vals_out, uint64_t* h_counts) {
+  if (!idx || !h_counts || ((!d_keys || !d_keys_out) && n) || (d_vals && !d_vals_out)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  const u32 p = (u32)idx->cfg.nranks;
+  for (u32 r = 0; r < p; ++r) h_counts[r] = 0;
+  if (n == 0) return KMI_OK;
+  if (n >= 0xffffffffULL) return fail(KMI_ERR_ARG, "partition: at most 2^32-2 keys per call");
+  u64 n_chunks = (n + PART_ITEMS - 1) / PART_ITEMS;
+  u64 n_hist = n_chunks * p;
+  u64 n_blocks = (n_hist + 1023) / 1024;
+  OK(idx->hist.ensure(sizeof(u32) * (n_hist + 1)));
+  OK(idx->hist_sums.ensure(sizeof(u32) * (n_blocks + 1)));
+  idx->ops->part_hist(idx->stream, reinterpret_cast<const u64*>(d_keys), n, p, idx->hist.as<u32>(), n_chunks);
+  k_scan_l1<<<(unsigned)n_blocks, 1024, 0, idx->stream>>>(idx->hist.as<u32>(), n_hist, idx->hist_sums.as<u32>());
+  k_scan_tiles<<<1, 1024, 0, idx->stream>>>(idx->hist_sums.as<u32>(), n_blocks);
+  idx->ops->part_scatter(idx->stream, reinterpret_cast<const u64*>(d_keys), reinterpret_cast<const u64*>(d_vals), n, p,
+                         idx->hist.as<u32>(), idx->hist_sums.as<u32>(), n_chunks, reinterpret_cast<u64*>(d_keys_out),
+                         reinterpret_cast<u64*>(d_vals_out));
+  idx->launches += 4;
+  // owner r starts at scanned[r * n_chunks]: read the p starts back
+  std::vector<u32> starts(p), sums(p);
+  for (u32 r = 0; r < p; ++r) {
+    u64 hi = (u64)r * n_chunks;
+    CU(cudaMemcpyAsync(&starts[r], idx->hist.as<u32>() + hi, sizeof(u32), cudaMemcpyDeviceToHost, idx->stream));
+    CU(cudaMemcpyAsync(&sums[r], idx->hist_sums.as<u32>() + (hi >> 10), sizeof(u32), cudaMemcpyDeviceToHost, idx->stream));
+  }
+  CU(cudaStreamSynchronize(idx->stream));
+  for (u32 r = 0; r < p; ++r) {
+    u64 b = (u64)starts[r] + sums[r];
+    u64 e = (r + 1 < p) ? (u64)starts[r + 1] + sums[r + 1] : (u64)n;
+    h_counts[r] = e - b;
+  }
+  return KMI_OK;
+}
+
+// ---- synthetic workload ------------------------------------------------------------------------------------
+extern "C" size_t kmi_synth_record_bytes(uint32_t read_len) { return 13 + 2 * (size_t)read_len + 4; }
+extern "C" int kmi_synth_fastq_dev(int device, uint8_t* d_out, uint64_t first_read, uint64_t n_reads, uint32_t read_len,
+                                   uint64_t genome_len, uint64_t seed, uint32_t err_ppm, uint32_t n_ppm) {
+  if (!d_out && n_reads) return fail(KMI_ERR_ARG, "null argument");
+  if (genome_len < read_len || read_len == 0) return fail(KMI_ERR_ARG, "genome shorter than a read");
+  CU(cudaSetDevice(device));
+  if (n_reads == 0) return KMI_OK;
+  u64 total = n_reads * kmi_synth_record_bytes(read_len);
+  k_synth_fastq<<<grid_for(total, 256, 148u * 32u), 256>>>(d_out, first_read, n_reads, read_len, genome_len, seed, err_ppm, n_ppm);
+  CU(cudaGetLastError());
+  return KMI_OK;
+}
+
+// ---- FASTA ---------------------------------------------------------------------------------------------------
+// pass A: line kinds entering every tile (max-scan) and header runs before every tile (sum-scan)
+static int fasta_scan(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64* n_tiles_out) {
+  if ((reinterpret_cast<uintptr_t>(d_bytes) & 15) != 0) return fail(KMI_ERR_ARG, "device text buffer must be 16-byte aligned");
+  u64 n_tiles = (n + TILE_BYTES - 1) / TILE_BYTES;
+  *n_tiles_out = n_tiles;
+  if (n_tiles == 0) return KMI_OK;
+  if (n_tiles > 0x3fffffffULL) return fail(KMI_ERR_ARG, "block of %zu bytes too large for one call", n);
+  u64 n_blocks = (n_tiles + 1023) / 1024;
+  // tile_lines: enc (max-scanned in place) | first_t | runs   ; block_sums: enc block maxima | runs block sums
+  OK(idx->tile_lines.ensure(sizeof(u32) * n_tiles * 3));
+  OK(idx->block_sums.ensure(sizeof(u32) * n_blocks * 2));
+  u32* enc = idx->tile_lines.as<u32>();
+  u32* first_t = enc + n_tiles;
+  u32* runs = enc + 2 * n_tiles;
+  u32* enc_max = idx->block_sums.as<u32>();
+  u32* runs_sums = enc_max + n_blocks;
+  k_fasta_tiles<<<(unsigned)n_tiles, TILE_THREADS, 0, idx->stream>>>(d_bytes, n, enc, first_t);
+  k_maxscan_l1<<<(unsigned)n_blocks, 1024, 0, idx->stream>>>(enc, n_tiles, enc_max);
+  k_maxscan_l2<<<1, 32, 0, idx->stream>>>(enc_max, n_blocks);
+  k_fasta_tile_starts<<<grid_for(n_tiles, 256), 256, 0, idx->stream>>>(enc, enc_max, first_t, n_tiles, runs);
+  k_scan_l1<<<(unsigned)n_blocks, 1024, 0, idx->stream>>>(runs, n_tiles, runs_sums);
+  k_scan_tiles<<<1, 1024, 0, idx->stream>>>(runs_sums, n_blocks);
+  idx->launches += 6;
+  return KMI_OK;
+}
+
+// parse tiles [tile_begin, tile_begin + tiles) into the sink; retries with the wide halo when needed
+static int fasta_parse_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64 n_tiles_total, u64 tile_begin, u64 tiles,
+                             KeySink sink, u64* produced) {
+  u64 n_blocks = (n_tiles_total + 1023) / 1024;
+  u32* enc = idx->tile_lines.as<u32>();
+  u32* runs = enc + 2 * n_tiles_total;
+  u32* enc_max = idx->block_sums.as<u32>();
+  u32* runs_sums = enc_max + n_blocks;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    OK(zero_ctr(idx, CTR_NKMERS, 2));
+    OK(zero_ctr(idx, CTR_PERR));
+    idx->ops->fasta_kmers(idx->stream, attempt == 1, d_bytes, n, tiles, enc, enc_max, runs, runs_sums, sink, idx->ctr + CTR_NKMERS,
+                          reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0, idx->cfg.nsplit != 0, tile_begin);
+    idx->launches++;
+    u64 host[8];
+    CU(cudaMemcpyAsync(host, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
+    CU(cudaStreamSynchronize(idx->stream));
+    *produced = host[CTR_NKMERS];
+    if ((host[CTR_PERR] & PERR_HALO) && attempt == 0) continue;
+    return parse_error(host[CTR_PERR]);
+  }
+  return KMI_OK;
+}
+
+extern "C" int kmi_parse_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* d_keys, uint64_t* d_ids,
+                                   size_t cap, uint64_t* n_kmers) {
+  if (!idx || (!d_bytes && n) || (!d_keys && cap)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  if (n_kmers) *n_kmers = 0;
+  u64 n_tiles = 0;
+  OK(fasta_scan(idx, d_bytes, n, &n_tiles));
+  if (n_tiles == 0) return KMI_OK;
+  KeySink sink;
+  sink.keys = reinterpret_cast<u64*>(d_keys); sink.ids = reinterpret_cast<u64*>(d_ids); sink.cap = cap; sink.cursor = idx->ctr + CTR_CURSOR;
+  u64 produced = 0;
+  OK(fasta_parse_range(idx, d_bytes, n, n_tiles, 0, n_tiles, sink, &produced));
+  if (n_kmers) *n_kmers = produced;
+  return KMI_OK;
+}
+
+extern "C" int kmi_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* n_kmers) {
+  if (!idx || (!d_bytes && n)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  if (n_kmers) *n_kmers = 0;
+  u64 n_tiles = 0;
+  CU(cudaEventRecord(idx->ev[0], idx->stream));
+  OK(fasta_scan(idx, d_bytes, n, &n_tiles));
+  CU(cudaEventRecord(idx->ev[1], idx->stream));
+  if (n_tiles == 0) return KMI_OK;
+  // bounded staging: at most CHUNK_TILES tiles of text become keys (+ids) at a time
+  const u64 CHUNK_TILES = 16384;  // 64 MiB of text -> <= 64 Mi k-mers
+  const bool pos = idx->cfg.mode == KMI_MODE_POSITION;
+  size_t kb = sizeof(u64) * idx->nw;
+  u64 cap = std::min<u64>(n_tiles, CHUNK_TILES) * TILE_BYTES;
+  DevBuf keys, ids;
+  int r = keys.ensure(cap * kb);
+  if (r == KMI_OK && pos) r = ids.ensure(cap * sizeof(u64));
+  u64 total = 0;
+  float parse_ms = 0, insert_ms = 0;
+  for (u64 tile = 0; r == KMI_OK && tile < n_tiles; tile += CHUNK_TILES) {
+    u64 tiles = std::min<u64>(CHUNK_TILES, n_tiles - tile);
+    KeySink sink;
+    sink.keys = keys.as<u64>(); sink.ids = pos ? ids.as<u64>() : nullptr; sink.cap = cap; sink.cursor = idx->ctr + CTR_CURSOR;
+    u64 produced = 0;
+    cudaEventRecord(idx->ev[2], idx->stream);
+    r = fasta_parse_range(idx, d_bytes, n, n_tiles, tile, tiles, sink, &produced);
+    cudaEventRecord(idx->ev[3], idx->stream);
+    if (r != KMI_OK) break;
+    // keys are already canonical: insert them as they are
+    if (pos) {
+      int32_t canon = idx->cfg.canonical;
+      idx->cfg.canonical = 0;
+      r = kmi_insert_dev(idx, keys.as<uint64_t>(), ids.as<uint64_t>(), produced);
+      idx->cfg.canonical = canon;
+    } else {
+      r = insert_keys_chunked(idx, keys.as<u64>(), produced, false);
+    }
+    cudaStreamSynchronize(idx->stream);
+    float a = 0;
+    cudaEventElapsedTime(&a, idx->ev[2], idx->ev[3]);
+    parse_ms += a;
+    total += produced;
+  }
+  (void)insert_ms;
+  keys.release(); ids.release();
+  if (r != KMI_OK) return r;
+  cudaEventElapsedTime(&idx->stage_ms[0], idx->ev[0], idx->ev[1]);
+  idx->stage_ms[1] = parse_ms;
+  idx->stage_ms[2] = 0;
+  if (n_kmers) *n_kmers = total;
+  return check_table_error(idx);
+}
+
+extern "C" int kmi_build_fasta(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t* n_kmers) {
+  if (!idx || (!bytes && n)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  OK(idx->stage_in.ensure(n + 64));
+  CU(cudaMemcpyAsync(idx->stage_in.p, bytes, n, cudaMemcpyHostToDevice, idx->stream));
+  return kmi_build_fasta_dev(idx, idx->stage_in.as<uint8_t>(), n, n_kmers);
+}

@@ -342,6 +342,9 @@ k_csr_fill(TableView t, const u64* __restrict__ keys, const u64* __restrict__ id
   }
 }
 #ifdef KMI_SHARED_KERNELS
+__global__ void __launch_bounds__(256) k_widen_u8(const uint8_t* __restrict__ in, u64* __restrict__ out, u64 n) {
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) out[i] = in[i];
+}
 // find (multimap): per query multiplicity, then gather
 __global__ void __launch_bounds__(256)
 k_csr_gather(const u64* __restrict__ slot_idx, const u64* __restrict__ out_off, u64 n, const u64* __restrict__ offsets,

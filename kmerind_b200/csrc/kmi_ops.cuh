@@ -4,6 +4,7 @@
 #pragma once
 #include "kmi_parse.cuh"
 #include "kmi_kernels.cuh"
+#include "kmi_fasta.cuh"
 
 namespace kmi {
 
@@ -13,6 +14,10 @@ struct Ops {
   void (*fastq_kmers)(cudaStream_t, int sink_kind, const uint8_t* bytes, u64 n, u64 n_tiles, const u32* tile_lines,
                       const u32* block_sums, KeySink sink, TableView table, u64* n_kmers, u32* perr, bool canon,
                       bool nsplit, u64 tile_begin);
+  // parse (FASTA) to a key(+id) stream; wide_halo selects the 1 KiB halo variant
+  void (*fasta_kmers)(cudaStream_t, bool wide_halo, const uint8_t* bytes, u64 n, u64 n_tiles, const u32* tile_enc_scanned,
+                      const u32* enc_block_max, const u32* tile_runs, const u32* runs_block_sums, KeySink sink, u64* n_kmers,
+                      u32* perr, bool canon, bool nsplit, u64 tile_begin);
   void (*table_clear)(cudaStream_t, void* slots, u64 n);
   void (*insert_keys)(cudaStream_t, TableView, const u64* keys, u64 n, bool canon);
   void (*rehash)(cudaStream_t, const void* old_slots, u64 n_old, TableView);
@@ -53,6 +58,19 @@ struct OpsImpl {
     else
       k_fastq_kmers<K, HASH, 1><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table,
                                                                           n_kmers, perr, canon, nsplit, tile_begin);
+  }
+  static void fasta_kmers(cudaStream_t st, bool wide_halo, const uint8_t* bytes, u64 n, u64 n_tiles, const u32* tile_enc_scanned,
+                          const u32* enc_block_max, const u32* tile_runs, const u32* runs_block_sums, KeySink sink,
+                          u64* n_kmers, u32* perr, bool canon, bool nsplit, u64 tile_begin) {
+    if (n_tiles == 0) return;
+    if (!wide_halo)
+      k_fasta_kmers<K, HASH, 4><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_enc_scanned, enc_block_max, tile_runs,
+                                                                          runs_block_sums, sink, n_kmers, perr, canon, nsplit,
+                                                                          tile_begin);
+    else
+      k_fasta_kmers<K, HASH, 64><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_enc_scanned, enc_block_max, tile_runs,
+                                                                           runs_block_sums, sink, n_kmers, perr, canon, nsplit,
+                                                                           tile_begin);
   }
   static void table_clear(cudaStream_t st, void* slots, u64 n) {
     k_table_clear<NW><<<grid_for(n, 256), 256, 0, st>>>(reinterpret_cast<S*>(slots), n);
@@ -108,7 +126,7 @@ struct OpsImpl {
   static Ops make() {
     Ops o;
     o.K = K; o.NW = NW; o.hash = HASH;
-    o.fastq_kmers = fastq_kmers; o.table_clear = table_clear; o.insert_keys = insert_keys; o.rehash = rehash;
+    o.fastq_kmers = fastq_kmers; o.fasta_kmers = fasta_kmers; o.table_clear = table_clear; o.insert_keys = insert_keys; o.rehash = rehash;
     o.lookup = lookup; o.erase = erase; o.dump = dump; o.checksum = checksum; o.canonicalize = canonicalize;
     o.hash_keys = hash_keys; o.part_hist = part_hist; o.part_scatter = part_scatter; o.csr_scan_l1 = csr_scan_l1;
     o.csr_fill = csr_fill; o.log_filter = log_filter; o.zero_aux = zero_aux;
