@@ -1,0 +1,322 @@
+"""kmerind_b200 — B200-native k-mer index construction path behind ParBLiSS/kmerind's Index API.
+
+The product is the C-ABI CUDA library ``libkmi.so`` (include/kmi.h; C++ adapter in
+include/kmi_index.hpp). This module is the thin ctypes binding the tests and bench.py use: it
+mirrors ``bliss::index::kmer::Index`` member for member (reference src/index/kmer_index.hpp:98-394)
+and never computes anything itself. There is no CPU fallback: if the library is missing or no CUDA
+device is present, calls raise.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libkmi.so")
+
+MODE_COUNT, MODE_POSITION = 0, 1
+HASH_MURMUR, HASH_FARM, HASH_FARM_DEBUG = 0, 1, 2
+SUPPORTED_K = (15, 21, 31, 35, 47, 63)
+
+KMI_OK = 0
+ERR_ARG, ERR_CUDA, ERR_FORMAT, ERR_CAPACITY, ERR_UNSUPPORTED, ERR_NOMEM = -1, -2, -3, -4, -5, -6
+
+
+class KmiError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("kmi error %d: %s" % (code, msg))
+        self.code = code
+
+
+class KmiFormatError(KmiError, ValueError):
+    """std::logic_error in the reference (malformed FASTQ, fastq_loader.hpp:393,419,435)."""
+
+
+class KmiConfig(ctypes.Structure):
+    _fields_ = [("k", ctypes.c_int32), ("mode", ctypes.c_int32), ("canonical", ctypes.c_int32),
+                ("hash", ctypes.c_int32), ("nsplit", ctypes.c_int32), ("device", ctypes.c_int32),
+                ("rank", ctypes.c_int32), ("nranks", ctypes.c_int32), ("reserve", ctypes.c_uint64)]
+
+
+_lib = None
+_P = ctypes.c_void_p
+_SZ = ctypes.c_size_t
+_U64 = ctypes.c_uint64
+
+
+def load_library(build_if_missing=False):
+    """dlopen libkmi.so (in-tree). Raises if it has not been built — no fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        if build_if_missing:
+            from . import build as _b
+            _b.build()
+        else:
+            raise ImportError("libkmi.so is not built (run python -m kmerind_b200.build); there is no CPU path")
+    lib = ctypes.CDLL(LIB_PATH)
+    lib.kmi_last_error.restype = ctypes.c_char_p
+    lib.kmi_synth_record_bytes.restype = _SZ
+    lib.kmi_synth_record_bytes.argtypes = [ctypes.c_uint32]
+    lib.kmi_create.argtypes = [ctypes.POINTER(KmiConfig), ctypes.POINTER(_P)]
+    lib.kmi_destroy.argtypes = [_P]
+    lib.kmi_destroy.restype = None
+    sig = {
+        "kmi_set_stream": [_P, _P], "kmi_reserve": [_P, _U64], "kmi_clear": [_P],
+        "kmi_build_fastq": [_P, _P, _SZ, _U64, _P], "kmi_build_fasta": [_P, _P, _SZ, _P],
+        "kmi_build_fastq_dev": [_P, _P, _SZ, _U64, _P], "kmi_build_fasta_dev": [_P, _P, _SZ, _P],
+        "kmi_parse_fastq_dev": [_P, _P, _SZ, _U64, _P, _P, _SZ, _P],
+        "kmi_parse_fasta_dev": [_P, _P, _SZ, _P, _P, _SZ, _P],
+        "kmi_canonicalize_dev": [_P, _P, _P, _SZ], "kmi_hash_dev": [_P, ctypes.c_int, _P, _P, _SZ],
+        "kmi_partition_dev": [_P, _P, _P, _SZ, _P, _P, _P],
+        "kmi_insert": [_P, _P, _P, _SZ], "kmi_insert_dev": [_P, _P, _P, _SZ],
+        "kmi_count": [_P, _P, _SZ, _P], "kmi_find": [_P, _P, _SZ, _P, _P],
+        "kmi_find_positions": [_P, _P, _SZ, _P, _P, _SZ], "kmi_erase": [_P, _P, _SZ],
+        "kmi_count_dev": [_P, _P, _SZ, _P], "kmi_find_dev": [_P, _P, _SZ, _P, _P],
+        "kmi_local_size": [_P, _P], "kmi_num_keys": [_P, _P], "kmi_dump": [_P, _P, _P, _SZ, _P],
+        "kmi_checksum": [_P, _P, _P], "kmi_table_info": [_P, _P, _P, _P], "kmi_launch_count": [_P, _P],
+        "kmi_last_stage_ms": [_P, _P],
+        "kmi_synth_fastq_dev": [ctypes.c_int, _P, _U64, _U64, ctypes.c_uint32, _U64, _U64, ctypes.c_uint32,
+                                ctypes.c_uint32],
+    }
+    for name, args in sig.items():
+        fn = getattr(lib, name)
+        fn.argtypes = args
+        fn.restype = ctypes.c_int
+    _lib = lib
+    return lib
+
+
+EXPORTED_SYMBOLS = (
+    "kmi_create", "kmi_destroy", "kmi_last_error", "kmi_set_stream", "kmi_reserve", "kmi_clear",
+    "kmi_build_fastq", "kmi_build_fasta", "kmi_build_fastq_dev", "kmi_build_fasta_dev",
+    "kmi_parse_fastq_dev", "kmi_parse_fasta_dev", "kmi_canonicalize_dev", "kmi_hash_dev",
+    "kmi_partition_dev", "kmi_insert", "kmi_insert_dev", "kmi_count", "kmi_find", "kmi_find_positions",
+    "kmi_erase", "kmi_count_dev", "kmi_find_dev", "kmi_local_size", "kmi_num_keys", "kmi_dump",
+    "kmi_checksum", "kmi_table_info", "kmi_launch_count", "kmi_last_stage_ms",
+    "kmi_synth_record_bytes", "kmi_synth_fastq_dev",
+)
+
+
+def _check(code):
+    if code != KMI_OK:
+        msg = load_library().kmi_last_error().decode("utf-8", "replace")
+        if code == ERR_FORMAT:
+            raise KmiFormatError(code, msg)
+        raise KmiError(code, msg)
+
+
+def _hptr(a):
+    return a.ctypes.data_as(_P) if a is not None else None
+
+
+def nwords(k):
+    return 1 if k <= 32 else 2
+
+
+def _as_keys(keys, nw):
+    a = np.ascontiguousarray(keys, dtype=np.uint64)
+    if nw == 2:
+        a = a.reshape(-1, 2)
+    else:
+        a = a.reshape(-1)
+    return a
+
+
+class Index:
+    """CountIndex / PositionIndex over one GPU (one shard).
+
+    Mirrors ``Index<MapType, KmerParser>``: insert, find, count, erase, build_*, size, local_size
+    (reference src/index/kmer_index.hpp:115-392). Keys are numpy uint64 arrays of shape (n,) for
+    K <= 31 or (n, 2) [low word, high word] for 33 <= K <= 63 — the memory layout of
+    ``std::vector<Kmer<K, DNA, uint64_t>>``.
+    """
+
+    def __init__(self, k=31, mode=MODE_COUNT, canonical=True, hash=HASH_MURMUR, nsplit=False, device=0,
+                 rank=0, nranks=1, reserve=0):
+        self._lib = load_library()
+        self.k, self.mode, self.nw = k, mode, nwords(k)
+        cfg = KmiConfig(k, mode, 1 if canonical else 0, hash, 1 if nsplit else 0, device, rank, nranks, reserve)
+        self._h = _P()
+        _check(self._lib.kmi_create(ctypes.byref(cfg), ctypes.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.kmi_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # -- build ------------------------------------------------------------------------------
+    def build_fastq(self, data, file_offset=0):
+        """build_posix<FASTQParser>: host bytes -> index. Returns k-mer occurrences generated."""
+        buf = np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data
+        n = _U64(0)
+        _check(self._lib.kmi_build_fastq(self._h, _hptr(buf), buf.size, file_offset, ctypes.byref(n)))
+        return n.value
+
+    def build_fasta(self, data):
+        buf = np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data
+        n = _U64(0)
+        _check(self._lib.kmi_build_fasta(self._h, _hptr(buf), buf.size, ctypes.byref(n)))
+        return n.value
+
+    def build_fastq_dev(self, dptr, nbytes, file_offset=0):
+        n = _U64(0)
+        _check(self._lib.kmi_build_fastq_dev(self._h, dptr, nbytes, file_offset, ctypes.byref(n)))
+        return n.value
+
+    def build_fasta_dev(self, dptr, nbytes):
+        n = _U64(0)
+        _check(self._lib.kmi_build_fasta_dev(self._h, dptr, nbytes, ctypes.byref(n)))
+        return n.value
+
+    # -- stages on device pointers ------------------------------------------------------------
+    def parse_fastq_dev(self, dptr, nbytes, d_keys, cap, d_ids=None, file_offset=0):
+        n = _U64(0)
+        _check(self._lib.kmi_parse_fastq_dev(self._h, dptr, nbytes, file_offset, d_keys, d_ids, cap, ctypes.byref(n)))
+        return n.value
+
+    def parse_fasta_dev(self, dptr, nbytes, d_keys, cap, d_ids=None):
+        n = _U64(0)
+        _check(self._lib.kmi_parse_fasta_dev(self._h, dptr, nbytes, d_keys, d_ids, cap, ctypes.byref(n)))
+        return n.value
+
+    def canonicalize_dev(self, d_in, d_out, n):
+        _check(self._lib.kmi_canonicalize_dev(self._h, d_in, d_out, n))
+
+    def hash_dev(self, which, d_keys, d_out, n):
+        _check(self._lib.kmi_hash_dev(self._h, which, d_keys, d_out, n))
+
+    def partition_dev(self, d_keys, d_vals, n, d_keys_out, d_vals_out, nranks):
+        counts = np.zeros(nranks, dtype=np.uint64)
+        _check(self._lib.kmi_partition_dev(self._h, d_keys, d_vals, n, d_keys_out, d_vals_out, _hptr(counts)))
+        return counts
+
+    def insert_dev(self, d_keys, n, d_vals=None):
+        _check(self._lib.kmi_insert_dev(self._h, d_keys, d_vals, n))
+
+    def count_dev(self, d_keys, n, d_counts):
+        _check(self._lib.kmi_count_dev(self._h, d_keys, n, d_counts))
+
+    def find_dev(self, d_keys, n, d_vals, d_found):
+        _check(self._lib.kmi_find_dev(self._h, d_keys, n, d_vals, d_found))
+
+    # -- Index API on host arrays ---------------------------------------------------------------
+    def insert(self, keys, vals=None):
+        a = _as_keys(keys, self.nw)
+        v = None if vals is None else np.ascontiguousarray(vals, dtype=np.uint64)
+        _check(self._lib.kmi_insert(self._h, _hptr(a), _hptr(v), a.shape[0]))
+
+    def count(self, keys):
+        a = _as_keys(keys, self.nw)
+        out = np.zeros(a.shape[0], dtype=np.uint64)
+        _check(self._lib.kmi_count(self._h, _hptr(a), a.shape[0], _hptr(out)))
+        return out
+
+    def find(self, keys):
+        """COUNT index: (values, found) in input order; the reference returns only the hits."""
+        a = _as_keys(keys, self.nw)
+        vals = np.zeros(a.shape[0], dtype=np.uint64)
+        found = np.zeros(a.shape[0], dtype=np.uint8)
+        _check(self._lib.kmi_find(self._h, _hptr(a), a.shape[0], _hptr(vals), _hptr(found)))
+        return vals, found
+
+    def find_positions(self, keys, cap=None):
+        a = _as_keys(keys, self.nw)
+        n = a.shape[0]
+        if cap is None:
+            cap = int(self.count(a).sum())
+        offsets = np.zeros(n + 1, dtype=np.uint64)
+        vals = np.zeros(max(cap, 1), dtype=np.uint64)
+        _check(self._lib.kmi_find_positions(self._h, _hptr(a), n, _hptr(offsets), _hptr(vals), cap))
+        return offsets, vals[:int(offsets[-1])]
+
+    def erase(self, keys):
+        a = _as_keys(keys, self.nw)
+        _check(self._lib.kmi_erase(self._h, _hptr(a), a.shape[0]))
+
+    def reserve(self, n):
+        _check(self._lib.kmi_reserve(self._h, n))
+
+    def clear(self):
+        _check(self._lib.kmi_clear(self._h))
+
+    def local_size(self):
+        n = _U64(0)
+        _check(self._lib.kmi_local_size(self._h, ctypes.byref(n)))
+        return n.value
+
+    size = local_size  # single shard; the sharded size() is a sum over ranks (kmerind_b200.dist)
+
+    def num_keys(self):
+        n = _U64(0)
+        _check(self._lib.kmi_num_keys(self._h, ctypes.byref(n)))
+        return n.value
+
+    def to_vector(self):
+        """(keys, values), unordered — Index::get_map().to_vector()."""
+        n = self.local_size()
+        keys = np.zeros((n, 2) if self.nw == 2 else (n,), dtype=np.uint64)
+        vals = np.zeros(n, dtype=np.uint64)
+        got = _SZ(0)
+        _check(self._lib.kmi_dump(self._h, _hptr(keys), _hptr(vals), n, ctypes.byref(got)))
+        return keys[:got.value], vals[:got.value]
+
+    def sorted_dump(self):
+        """Sorted by (key as multi-word unsigned integer, value): the parity dump."""
+        keys, vals = self.to_vector()
+        if self.nw == 2:
+            order = np.lexsort((vals, keys[:, 0], keys[:, 1]))
+        else:
+            order = np.lexsort((vals, keys))
+        return keys[order], vals[order]
+
+    def checksum(self):
+        a, b = _U64(0), _U64(0)
+        _check(self._lib.kmi_checksum(self._h, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
+
+    def table_info(self):
+        a, b, c = _U64(0), _U64(0), _U64(0)
+        _check(self._lib.kmi_table_info(self._h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c)))
+        return {"slots": a.value, "slot_bytes": b.value, "device_bytes": c.value}
+
+    def launch_count(self):
+        n = _U64(0)
+        _check(self._lib.kmi_launch_count(self._h, ctypes.byref(n)))
+        return n.value
+
+    def last_stage_ms(self):
+        ms = (ctypes.c_float * 3)()
+        _check(self._lib.kmi_last_stage_ms(self._h, ms))
+        return [float(x) for x in ms]
+
+    def set_stream(self, cuda_stream_ptr):
+        _check(self._lib.kmi_set_stream(self._h, cuda_stream_ptr))
+
+
+def CountIndex(k=31, **kw):
+    """CountIndex<MapType> alias, reference src/index/kmer_index.hpp:408-409."""
+    return Index(k=k, mode=MODE_COUNT, **kw)
+
+
+def PositionIndex(k=21, **kw):
+    """PositionIndex<MapType> alias, reference src/index/kmer_index.hpp:402-403."""
+    return Index(k=k, mode=MODE_POSITION, **kw)
+
+
+def synth_record_bytes(read_len=150):
+    return load_library().kmi_synth_record_bytes(read_len)
+
+
+def synth_fastq_dev(device, dptr, first_read, n_reads, read_len, genome_len, seed, err_ppm=5000, n_ppm=0):
+    _check(load_library().kmi_synth_fastq_dev(device, dptr, first_read, n_reads, read_len, genome_len, seed, err_ppm,
+                                              n_ppm))

@@ -150,8 +150,13 @@ struct Ops {
 
 }  // namespace
 
-#define DISPATCH(K, EXPR21, EXPR31, EXPR63, FALLBACK) \
-  switch (K) { case 21: EXPR21; break; case 31: EXPR31; break; case 63: EXPR63; break; default: FALLBACK; }
+// k-mer lengths instantiated (the ones libkmi.so builds)
+#define DISPATCH(K, CALL, FALLBACK)                                                        \
+  switch (K) {                                                                              \
+    case 15: return Ops<15>::CALL; case 21: return Ops<21>::CALL; case 31: return Ops<31>::CALL; \
+    case 35: return Ops<35>::CALL; case 47: return Ops<47>::CALL; case 63: return Ops<63>::CALL; \
+    default: return FALLBACK;                                                               \
+  }
 
 extern "C" {
 
@@ -165,31 +170,14 @@ int kmiref_debug_mode(void) {
 }
 uint8_t kmiref_from_ascii(uint8_t c) { return DNA::FROM_ASCII[c]; }
 
-size_t kmiref_windows(int K, const uint8_t* s, size_t n, uint64_t* out) {
-  DISPATCH(K, return Ops<21>::windows(s, n, out), return Ops<31>::windows(s, n, out),
-           return Ops<63>::windows(s, n, out), return 0)
-  return 0;
-}
-void kmiref_revcomp(int K, const uint64_t* in, uint64_t* out, size_t n) {
-  DISPATCH(K, Ops<21>::revcomp(in, out, n), Ops<31>::revcomp(in, out, n), Ops<63>::revcomp(in, out, n), (void)0)
-}
-void kmiref_canonical(int K, const uint64_t* in, uint64_t* out, size_t n) {
-  DISPATCH(K, Ops<21>::canonical(in, out, n), Ops<31>::canonical(in, out, n), Ops<63>::canonical(in, out, n), (void)0)
-}
-void kmiref_hash(int K, int which, const uint64_t* in, uint64_t* out, size_t n) {
-  DISPATCH(K, Ops<21>::hash(which, in, out, n), Ops<31>::hash(which, in, out, n), Ops<63>::hash(which, in, out, n), (void)0)
-}
-void kmiref_sentinels(int K, uint64_t* out) {
-  DISPATCH(K, Ops<21>::sentinels(out), Ops<31>::sentinels(out), Ops<63>::sentinels(out), (void)0)
-}
-size_t kmiref_count_build(int K, const uint8_t* seqs, const uint64_t* off, size_t nseq, int p,
-                          int hash_kind, uint64_t* out_keys, uint32_t* out_counts, size_t cap,
-                          uint64_t* per_rank_sizes) {
-  DISPATCH(K, return Ops<21>::count_build(seqs, off, nseq, p, hash_kind, out_keys, out_counts, cap, per_rank_sizes),
-           return Ops<31>::count_build(seqs, off, nseq, p, hash_kind, out_keys, out_counts, cap, per_rank_sizes),
-           return Ops<63>::count_build(seqs, off, nseq, p, hash_kind, out_keys, out_counts, cap, per_rank_sizes),
-           return 0)
-  return 0;
+size_t kmiref_windows(int K, const uint8_t* s, size_t n, uint64_t* out) { DISPATCH(K, windows(s, n, out), 0) }
+void kmiref_revcomp(int K, const uint64_t* in, uint64_t* out, size_t n) { DISPATCH(K, revcomp(in, out, n), (void)0) }
+void kmiref_canonical(int K, const uint64_t* in, uint64_t* out, size_t n) { DISPATCH(K, canonical(in, out, n), (void)0) }
+void kmiref_hash(int K, int which, const uint64_t* in, uint64_t* out, size_t n) { DISPATCH(K, hash(which, in, out, n), (void)0) }
+void kmiref_sentinels(int K, uint64_t* out) { DISPATCH(K, sentinels(out), (void)0) }
+size_t kmiref_count_build(int K, const uint8_t* seqs, const uint64_t* off, size_t nseq, int p, int hash_kind,
+                          uint64_t* out_keys, uint32_t* out_counts, size_t cap, uint64_t* per_rank_sizes) {
+  DISPATCH(K, count_build(seqs, off, nseq, p, hash_kind, out_keys, out_counts, cap, per_rank_sizes), 0)
 }
 
 }  // extern "C"

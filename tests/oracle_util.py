@@ -1,0 +1,170 @@
+"""ctypes access to the CPU checkers under oracle/ (TEST INFRASTRUCTURE ONLY)."""
+import ctypes
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+DATA = os.path.join(ROOT, "tests", "golden", "data")
+_P = ctypes.c_void_p
+_SZ = ctypes.c_size_t
+_U64 = ctypes.c_uint64
+
+
+def _ptr(a):
+    return a.ctypes.data_as(_P) if a is not None else None
+
+
+def nwords(k):
+    return 1 if k <= 32 else 2
+
+
+_oracle = None
+
+
+def oracle():
+    global _oracle
+    if _oracle is None:
+        lib = ctypes.CDLL(os.path.join(ROOT, "oracle", "libkmi_oracle.so"))
+        lib.kmio_fastq_kmers.restype = ctypes.c_long
+        lib.kmio_fastq_kmers.argtypes = [_P, _SZ, _U64, ctypes.c_int, ctypes.c_int, ctypes.c_int, _P, _P, _SZ, _P]
+        lib.kmio_fasta_kmers.restype = ctypes.c_long
+        lib.kmio_fasta_kmers.argtypes = [_P, _SZ, ctypes.c_int, ctypes.c_int, ctypes.c_int, _P, _P, _SZ, _P]
+        lib.kmio_revcomp.argtypes = [ctypes.c_int, _P, _P, _SZ]
+        lib.kmio_canonical.argtypes = [ctypes.c_int, _P, _P, _SZ]
+        lib.kmio_hash.argtypes = [ctypes.c_int, ctypes.c_int, _P, _P, _SZ]
+        lib.kmio_owner.argtypes = [_P, _SZ, ctypes.c_uint32, _P]
+        lib.kmio_count_sorted.restype = _SZ
+        lib.kmio_count_sorted.argtypes = [ctypes.c_int, _P, _SZ, _P]
+        lib.kmio_sort_tuples.argtypes = [ctypes.c_int, _P, _P, _SZ]
+        lib.kmio_synth_record_bytes.restype = _SZ
+        lib.kmio_synth_record_bytes.argtypes = [ctypes.c_uint32]
+        lib.kmio_synth_fastq.argtypes = [_P, _U64, _U64, ctypes.c_uint32, _U64, _U64, ctypes.c_uint32, ctypes.c_uint32]
+        lib.kmio_synth_fasta.restype = _SZ
+        lib.kmio_synth_fasta.argtypes = [_P, ctypes.c_uint32, _U64, ctypes.c_uint32, _U64]
+        lib.kmio_count_build_port.restype = _SZ
+        lib.kmio_count_build_port.argtypes = [_P, _SZ, ctypes.c_int, ctypes.c_int, _P, _P, _SZ, _P]
+        _oracle = lib
+    return _oracle
+
+
+def ref_lib(flavour="ndebug"):
+    """The reference's own headers compiled into oracle/_ref (None when not built)."""
+    p = os.path.join(ROOT, "oracle", "_ref", "libkmi_ref_%s.so" % flavour)
+    if not os.path.exists(p):
+        return None
+    lib = ctypes.CDLL(p)
+    lib.kmiref_windows.restype = _SZ
+    lib.kmiref_windows.argtypes = [ctypes.c_int, _P, _SZ, _P]
+    lib.kmiref_revcomp.argtypes = [ctypes.c_int, _P, _P, _SZ]
+    lib.kmiref_canonical.argtypes = [ctypes.c_int, _P, _P, _SZ]
+    lib.kmiref_hash.argtypes = [ctypes.c_int, ctypes.c_int, _P, _P, _SZ]
+    lib.kmiref_sentinels.argtypes = [ctypes.c_int, _P]
+    lib.kmiref_count_build.restype = _SZ
+    lib.kmiref_count_build.argtypes = [ctypes.c_int, _P, _P, _SZ, ctypes.c_int, ctypes.c_int, _P, _P, _SZ, _P]
+    return lib
+
+
+def read_fixture(name):
+    return np.fromfile(os.path.join(DATA, name), dtype=np.uint8)
+
+
+def shape_keys(keys, k):
+    return keys.reshape(-1, 2) if nwords(k) == 2 else keys.reshape(-1)
+
+
+def fastq_kmers(buf, k, canonical=True, nsplit=False, want_ids=False, file_offset=0):
+    """(keys, ids, n_reads) of a whole FASTQ buffer, reference order. Raises ValueError on malformed input."""
+    n = int(buf.size)
+    nw = nwords(k)
+    keys = np.zeros(max(n, 1) * nw, dtype=np.uint64)
+    ids = np.zeros(max(n, 1), dtype=np.uint64) if want_ids else None
+    reads = _U64(0)
+    m = oracle().kmio_fastq_kmers(_ptr(buf), n, file_offset, k, int(canonical), int(nsplit), _ptr(keys), _ptr(ids), max(n, 1),
+                                  ctypes.byref(reads))
+    if m < 0:
+        raise ValueError("oracle: malformed FASTQ (%d)" % m)
+    return shape_keys(keys[:m * nw].copy(), k), (ids[:m].copy() if want_ids else None), reads.value
+
+
+def fasta_kmers(buf, k, canonical=True, nsplit=False):
+    n = int(buf.size)
+    nw = nwords(k)
+    keys = np.zeros(max(n, 1) * nw, dtype=np.uint64)
+    ids = np.zeros(max(n, 1), dtype=np.uint64)
+    seqs = _U64(0)
+    m = oracle().kmio_fasta_kmers(_ptr(buf), n, k, int(canonical), int(nsplit), _ptr(keys), _ptr(ids), max(n, 1),
+                                  ctypes.byref(seqs))
+    if m < 0:
+        raise ValueError("oracle: FASTA failure (%d)" % m)
+    return shape_keys(keys[:m * nw].copy(), k), ids[:m].copy(), seqs.value
+
+
+def revcomp(keys, k):
+    a = np.ascontiguousarray(keys, dtype=np.uint64)
+    out = np.zeros_like(a)
+    oracle().kmio_revcomp(k, _ptr(a), _ptr(out), a.size // nwords(k))
+    return out
+
+
+def canonical(keys, k):
+    a = np.ascontiguousarray(keys, dtype=np.uint64)
+    out = np.zeros_like(a)
+    oracle().kmio_canonical(k, _ptr(a), _ptr(out), a.size // nwords(k))
+    return out
+
+
+def hashes(keys, k, which):
+    """which: 0 murmur store, 1 murmur dist, 2 farm store, 3 farm dist, 4/5 farm with DebugTweak."""
+    a = np.ascontiguousarray(keys, dtype=np.uint64)
+    n = a.size // nwords(k)
+    out = np.zeros(n, dtype=np.uint64)
+    oracle().kmio_hash(k, which, _ptr(a), _ptr(out), n)
+    return out
+
+
+def hash_which(hash_kind, dist):
+    """map (kmi_hash_kind, dist?) to the oracle's `which`."""
+    return {0: 0, 1: 2, 2: 4}[hash_kind] + (1 if dist else 0)
+
+
+def count_sorted(keys, k):
+    """sorted dump of a counting map: (distinct keys ascending, uint32 counts)."""
+    a = np.ascontiguousarray(keys, dtype=np.uint64).reshape(-1).copy()
+    nw = nwords(k)
+    n = a.size // nw
+    counts = np.zeros(max(n, 1), dtype=np.uint32)
+    m = oracle().kmio_count_sorted(k, _ptr(a), n, _ptr(counts))
+    return shape_keys(a[:m * nw].copy(), k), counts[:m].astype(np.uint64)
+
+
+def sort_tuples(keys, ids, k):
+    a = np.ascontiguousarray(keys, dtype=np.uint64).reshape(-1).copy()
+    b = np.ascontiguousarray(ids, dtype=np.uint64).copy()
+    oracle().kmio_sort_tuples(k, _ptr(a), _ptr(b), b.size)
+    return shape_keys(a, k), b
+
+
+def synth_fastq(first_read, n_reads, read_len=150, genome_len=100000, seed=1, err_ppm=5000, n_ppm=0):
+    rec = oracle().kmio_synth_record_bytes(read_len)
+    out = np.zeros(n_reads * rec, dtype=np.uint8)
+    oracle().kmio_synth_fastq(_ptr(out), first_read, n_reads, read_len, genome_len, seed, err_ppm, n_ppm)
+    return out
+
+
+def synth_fasta(n_seq, seq_len, width=80, seed=1):
+    n = oracle().kmio_synth_fasta(None, n_seq, seq_len, width, seed)
+    out = np.zeros(n, dtype=np.uint8)
+    oracle().kmio_synth_fasta(_ptr(out), n_seq, seq_len, width, seed)
+    return out
+
+
+def random_keys(k, n, seed=0):
+    rng = np.random.default_rng(seed)
+    nw = nwords(k)
+    a = rng.integers(0, 2**64, size=(n, nw), dtype=np.uint64)
+    if nw == 1:
+        a[:, 0] &= np.uint64((1 << (2 * k)) - 1)
+        return a.reshape(-1)
+    a[:, 1] &= np.uint64((1 << (2 * (k - 32))) - 1)
+    return a

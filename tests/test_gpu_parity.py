@@ -1,0 +1,341 @@
+"""GPU parity tests: every CUDA stage, through the C ABI, against the CPU oracle and the golden
+vectors produced by the reference's own code. Bit-exact (integer work): no tolerances anywhere."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import kmerind_b200 as kb
+import oracle_util as ou
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+KAT = json.load(open(os.path.join(ou.ROOT, "tests", "golden", "ref_kat.json")))
+KS = (15, 21, 31, 35, 47, 63)
+FASTQ = ["natural.fastq", "natural.withN.fastq", "test.debruijn.small.fastq", "test.debruijn.tiny.fastq",
+         "test.medium.fastq", "test.small.fastq", "test.unitiq1.fastq", "test.unitiq1.short2.fastq",
+         "test.unitiq1.short.fastq", "test.unitiq2.fastq", "test.unitiqs.fastq"]
+FASTA = ["natural.fasta", "natural.withN.fasta", "test2.fasta", "test.fasta", "test.medium.fasta", "test.unitiqs.fasta"]
+
+
+def dev(a):
+    """numpy -> CUDA tensor (torch is only the device-memory plumbing here)."""
+    a = np.ascontiguousarray(a)
+    if a.dtype == np.uint64:
+        return torch.from_numpy(a.view(np.int64)).cuda()
+    return torch.from_numpy(a).cuda()
+
+
+def host_u64(t):
+    return t.cpu().numpy().view(np.uint64)
+
+
+def dev_text(buf):
+    t = torch.empty(buf.size + 64, dtype=torch.uint8, device="cuda")
+    t[:buf.size] = torch.from_numpy(np.ascontiguousarray(buf)).cuda()
+    return t
+
+
+def sort_keys(keys, k):
+    keys = ou.shape_keys(np.ascontiguousarray(keys).reshape(-1), k)
+    if ou.nwords(k) == 2:
+        return keys[np.lexsort((keys[:, 0], keys[:, 1]))]
+    return np.sort(keys)
+
+
+def gpu_parse(buf, k, fasta=False, canonical=True, nsplit=False, want_ids=False, hash=kb.HASH_MURMUR):
+    nw = ou.nwords(k)
+    with kb.Index(k=k, canonical=canonical, nsplit=nsplit, hash=hash) as idx:
+        text = dev_text(buf)
+        cap = max(int(buf.size), 1)
+        keys = torch.zeros(cap * nw, dtype=torch.int64, device="cuda")
+        ids = torch.zeros(cap, dtype=torch.int64, device="cuda") if want_ids else None
+        if fasta:
+            n = idx.parse_fasta_dev(text.data_ptr(), buf.size, keys.data_ptr(), cap, ids.data_ptr() if want_ids else None)
+        else:
+            n = idx.parse_fastq_dev(text.data_ptr(), buf.size, keys.data_ptr(), cap)
+        torch.cuda.synchronize()
+        k_host = ou.shape_keys(host_u64(keys)[:n * nw].copy(), k)
+        return k_host, (host_u64(ids)[:n].copy() if want_ids else None)
+
+
+@pytest.mark.parametrize("k", KS)
+@pytest.mark.parametrize("hash_kind", (kb.HASH_MURMUR, kb.HASH_FARM, kb.HASH_FARM_DEBUG))
+def test_hash_and_canonical_bit_exact(k, hash_kind):
+    nw = ou.nwords(k)
+    e = KAT["k"][str(k)]
+    golden = ou.shape_keys(np.array([int(x, 16) for x in e["keys"]], dtype=np.uint64), k)
+    keys = np.concatenate([golden.reshape(-1), np.ascontiguousarray(ou.random_keys(k, 200000, seed=k)).reshape(-1)])
+    n = keys.size // nw
+    with kb.Index(k=k, hash=hash_kind) as idx:
+        d_in = dev(keys)
+        d_can = torch.zeros_like(d_in)
+        idx.canonicalize_dev(d_in.data_ptr(), d_can.data_ptr(), n)
+        can = host_u64(d_can)
+        assert np.array_equal(can, ou.canonical(keys, k).reshape(-1))
+        ng = golden.size // nw
+        assert np.array_equal(can[:golden.size], np.array([int(x, 16) for x in e["canonical"]], dtype=np.uint64))
+        names = {kb.HASH_MURMUR: "murmur", kb.HASH_FARM: "farm", kb.HASH_FARM_DEBUG: "farm_debug"}[hash_kind]
+        for which, suffix in ((0, "store"), (1, "dist")):
+            d_h = torch.zeros(n, dtype=torch.int64, device="cuda")
+            idx.hash_dev(which, d_can.data_ptr(), d_h.data_ptr(), n)
+            h = host_u64(d_h)
+            assert np.array_equal(h, ou.hashes(can, k, ou.hash_which(hash_kind, which == 1)))
+            want = np.array([int(x, 16) for x in e["hash_of_canonical"]["%s_%s" % (names, suffix)]], dtype=np.uint64)
+            assert np.array_equal(h[:ng], want)  # values computed by the reference's own code
+
+
+@pytest.mark.parametrize("name", FASTQ)
+@pytest.mark.parametrize("k", (15, 31, 35, 63))
+def test_fastq_parse_matches_oracle(name, k):
+    buf = ou.read_fixture(name)
+    for nsplit in (False, True):
+        want, _, _ = ou.fastq_kmers(buf, k, canonical=True, nsplit=nsplit)
+        got, _ = gpu_parse(buf, k, nsplit=nsplit)
+        assert len(got) == len(want), (name, k, nsplit)
+        assert np.array_equal(sort_keys(got, k), sort_keys(want, k))
+    want, _, _ = ou.fastq_kmers(buf, k, canonical=False)
+    got, _ = gpu_parse(buf, k, canonical=False)
+    assert np.array_equal(sort_keys(got, k), sort_keys(want, k))
+
+
+@pytest.mark.parametrize("name", FASTA)
+@pytest.mark.parametrize("k", (21, 35, 63))
+def test_fasta_parse_matches_oracle(name, k):
+    buf = ou.read_fixture(name)
+    for nsplit in (False, True):
+        wk, wi, _ = ou.fasta_kmers(buf, k, canonical=True, nsplit=nsplit)
+        gk, gi = gpu_parse(buf, k, fasta=True, nsplit=nsplit, want_ids=True)
+        assert len(gk) == len(wk), (name, k, nsplit)
+        a, b = ou.sort_tuples(gk, gi, k)
+        c, d = ou.sort_tuples(wk, wi, k)
+        assert np.array_equal(a, c) and np.array_equal(b, d)
+
+
+EDGE_FASTQ = [
+    b"", b"\n\n", b"@a\nACGT\n+\nIIII", b"@a\nACGT\n+\nIIII\n", b"\r\n@a\r\nACGTACGTAC\r\n+\r\nIIIIIIIIII\r\n\r\n\r\n@b\nAC\n+\nII\n",
+    b"@a\nacgtnNACGTacgtRYKM\n+a\n@@@@@@@@@@@@@@@@@@\n@b\nTTTTTTTTTTTTTTTTTTTTTTTTTTTTTTTTTTTTTTTT\n+\n++++++++++++++++++++++++++++++++++++++++\n",
+    b"@q\n" + b"ACGT" * 5000 + b"\n+\n" + b"@" * 20000 + b"\n",
+]
+
+
+@pytest.mark.parametrize("i", range(len(EDGE_FASTQ)))
+def test_fastq_edge_cases(i):
+    buf = np.frombuffer(EDGE_FASTQ[i], dtype=np.uint8)
+    for k in (15, 31, 63):
+        for nsplit in (False, True):
+            want, _, _ = ou.fastq_kmers(buf, k, nsplit=nsplit)
+            got, _ = gpu_parse(buf, k, nsplit=nsplit)
+            assert np.array_equal(sort_keys(got, k), sort_keys(want, k)), (i, k, nsplit)
+
+
+def test_fastq_ragged_random_records():
+    # ragged read lengths straddling tile (4096 B) and group (16 B) boundaries, blank lines, CRLF
+    rng = np.random.default_rng(7)
+    parts = []
+    for r in range(3000):
+        L = int(rng.integers(1, 400))
+        seq = bytes(rng.choice(np.frombuffer(b"ACGTNacgtn", dtype=np.uint8), size=L, p=[.24, .24, .24, .24, .01, .005, .005, .005, .005, .01]))
+        eol = b"\r\n" if r % 7 == 0 else b"\n"
+        parts.append(b"@r%d" % r + eol + seq + eol + b"+" + eol + b"@" * L + eol + (b"\n" if r % 11 == 0 else b""))
+    buf = np.frombuffer(b"".join(parts), dtype=np.uint8)
+    for k in (21, 31, 47, 63):
+        for nsplit in (False, True):
+            want, _, _ = ou.fastq_kmers(buf, k, nsplit=nsplit)
+            got, _ = gpu_parse(buf, k, nsplit=nsplit)
+            assert np.array_equal(sort_keys(got, k), sort_keys(want, k)), (k, nsplit)
+
+
+def test_fastq_malformed_is_reported():
+    for bad in (b"ACGT\nACGT\n+\nIIII\n", b"@a\nACGT\n-\nIIII\n"):
+        buf = np.frombuffer(bad, dtype=np.uint8)
+        with pytest.raises(ValueError):
+            ou.fastq_kmers(buf, 3)
+        with pytest.raises(kb.KmiFormatError):
+            gpu_parse(buf, 15)
+
+
+def test_fasta_edge_cases():
+    cases = [b"", b"ACGT\n", b">h\n", b">h", b"ACGT\n>s1\nACGTAC\nGTACGT\r\nACGTACGTACGTAAC\n;c\n>s2\nTTTTTTTTTTTTTTTTTTTTTTTTT",
+             b">a\n" + b"ACGTTGCA" * 700 + b"\n>b\n\n\n" + b"GATTACA" * 3 + b"\n" + b"C" * 5000,
+             b">x\n" + b"\n".join(b"ACGTA"[:1 + (i % 5)] for i in range(4000)) + b"\n"]
+    for i, c in enumerate(cases):
+        buf = np.frombuffer(c, dtype=np.uint8)
+        for k in (15, 21, 63):
+            wk, wi, _ = ou.fasta_kmers(buf, k)
+            gk, gi = gpu_parse(buf, k, fasta=True, want_ids=True)
+            a, b = ou.sort_tuples(gk, gi, k)
+            c2, d = ou.sort_tuples(wk, wi, k)
+            assert np.array_equal(a, c2) and np.array_equal(b, d), (i, k)
+
+
+@pytest.mark.parametrize("k", (15, 21, 31, 35))
+@pytest.mark.parametrize("fx", ("test.small.fastq", "natural.fastq", "natural.withN.fastq"))
+def test_count_index_equals_reference_dump(k, fx):
+    """Sorted (canonical k-mer, count) dump == what the reference's Kmer + lex_less + dense_hash_map produce."""
+    e = KAT["k"][str(k)]["count"][fx]
+    buf = ou.read_fixture(fx)
+    for hash_kind in (kb.HASH_MURMUR, kb.HASH_FARM, kb.HASH_FARM_DEBUG):
+        with kb.CountIndex(k, hash=hash_kind) as idx:
+            n = idx.build_fastq(buf)
+            keys, counts = idx.sorted_dump()
+            assert idx.size() == e["distinct"]
+            assert np.array_equal(keys, np.array([int(x, 16) for x in e["keys"]], dtype=np.uint64))
+            assert counts.tolist() == e["counts"]
+            assert n == sum(e["counts"])
+
+
+@pytest.mark.parametrize("name", ["test.medium.fastq", "test.unitiqs.fastq", "natural.withN.fastq"])
+@pytest.mark.parametrize("k", (31, 63))
+def test_count_index_fused_build_equals_oracle(name, k):
+    buf = ou.read_fixture(name)
+    for nsplit in (False, True):
+        keys, _, _ = ou.fastq_kmers(buf, k, nsplit=nsplit)
+        wk, wc = ou.count_sorted(keys, k)
+        with kb.CountIndex(k, nsplit=nsplit) as idx:  # no reserve: exercises growth + rehash
+            n = idx.build_fastq(buf)
+            gk, gc = idx.sorted_dump()
+            assert n == len(keys)
+            assert np.array_equal(gk, wk) and np.array_equal(gc, wc)
+            # insert(vector<Kmer>) path gives the same contents, and doubles every count when repeated
+            with kb.CountIndex(k, nsplit=nsplit) as idx2:
+                fwd, _, _ = ou.fastq_kmers(buf, k, canonical=False, nsplit=nsplit)
+                idx2.insert(fwd)
+                assert idx2.checksum() == idx.checksum()
+                idx2.insert(fwd)
+                k2, c2 = idx2.sorted_dump()
+                assert np.array_equal(k2, wk) and np.array_equal(c2, 2 * wc)
+
+
+def test_count_find_erase_semantics():
+    k = 31
+    buf = ou.read_fixture("test.medium.fastq")
+    keys, _, _ = ou.fastq_kmers(buf, k)
+    wk, wc = ou.count_sorted(keys, k)
+    absent = ou.canonical(ou.random_keys(k, 1000, seed=5), k)
+    absent = absent[~np.isin(absent, wk)]
+    with kb.CountIndex(k) as idx:
+        idx.build_fastq(buf)
+        q = np.concatenate([wk, absent, ou.revcomp(wk, k)])  # queries are canonicalised like inserts
+        cnt = idx.count(q)
+        assert cnt[:len(wk)].tolist() == [1] * len(wk)          # dense_hash_map::count is 0/1
+        assert not cnt[len(wk):len(wk) + len(absent)].any()
+        assert cnt[len(wk) + len(absent):].tolist() == [1] * len(wk)
+        vals, found = idx.find(q)
+        assert np.array_equal(vals[:len(wk)], wc) and found[:len(wk)].all()
+        assert not found[len(wk):len(wk) + len(absent)].any()
+        assert np.array_equal(vals[len(wk) + len(absent):], wc)
+        # erase half, duplicates in the erase batch are harmless
+        gone = wk[::2]
+        idx.erase(np.concatenate([gone, gone, absent]))
+        assert idx.size() == len(wk) - len(gone)
+        vals, found = idx.find(wk)
+        assert not found[::2].any() and found[1::2].all()
+        gk, gc = idx.sorted_dump()
+        assert np.array_equal(gk, wk[1::2]) and np.array_equal(gc, wc[1::2])
+        idx.insert(gone[:5])
+        assert idx.size() == len(wk) - len(gone) + 5
+        assert idx.find(gone[:5])[0].tolist() == [1] * 5
+
+
+@pytest.mark.parametrize("name,k", [("test2.fasta", 21), ("test.medium.fasta", 21), ("test.unitiqs.fasta", 63), ("natural.withN.fasta", 15)])
+def test_position_index_equals_oracle(name, k):
+    buf = ou.read_fixture(name)
+    wk, wi, _ = ou.fasta_kmers(buf, k)
+    swk, swi = ou.sort_tuples(wk, wi, k)
+    with kb.PositionIndex(k) as idx:
+        n = idx.build_fasta(buf)
+        assert n == len(wk) and idx.local_size() == len(wk)
+        gk, gi = idx.sorted_dump()
+        assert np.array_equal(gk, swk) and np.array_equal(gi, swi)
+        dk, dc = ou.count_sorted(wk, k)
+        assert idx.num_keys() == len(dk)
+        # count = multiplicity; find = every position of the key
+        sel = dk[:: max(1, len(dk) // 500)]
+        absent = ou.canonical(ou.random_keys(k, 50, seed=3), k)
+        q = np.concatenate([sel.reshape(-1), np.ascontiguousarray(absent).reshape(-1)])
+        q = ou.shape_keys(q, k)
+        cnt = idx.count(q)
+        mult = dict()
+        for kk, c in zip(map(lambda r: tuple(np.atleast_1d(r).tolist()), dk), dc):
+            mult[kk] = int(c)
+        want_cnt = [mult.get(tuple(np.atleast_1d(r).tolist()), 0) for r in q]
+        assert cnt.tolist() == want_cnt
+        off, vals = idx.find_positions(q)
+        assert np.diff(off.astype(np.int64)).tolist() == want_cnt
+        pos_of = {}
+        for kk, i in zip(map(lambda r: tuple(np.atleast_1d(r).tolist()), swk), swi):
+            pos_of.setdefault(kk, []).append(int(i))
+        for j, r in enumerate(q):
+            got = sorted(int(x) for x in vals[int(off[j]):int(off[j + 1])])
+            assert got == pos_of.get(tuple(np.atleast_1d(r).tolist()), [])
+        # erase drops every tuple of the key
+        idx.erase(sel[:3])
+        assert idx.local_size() == len(wk) - sum(want_cnt[:3])
+        assert idx.count(sel[:3]).tolist() == [0, 0, 0]
+
+
+@pytest.mark.parametrize("k", (21, 31, 63))
+@pytest.mark.parametrize("p", (1, 2, 3, 8))
+def test_partition_is_stable_and_by_owner(k, p):
+    nw = ou.nwords(k)
+    keys = np.ascontiguousarray(ou.canonical(ou.random_keys(k, 100003, seed=11 + k), k)).reshape(-1)
+    n = keys.size // nw
+    vals = np.arange(n, dtype=np.uint64)
+    for hash_kind in (kb.HASH_MURMUR, kb.HASH_FARM):
+        with kb.Index(k=k, hash=hash_kind, nranks=p) as idx:
+            dk, dv = dev(keys), dev(vals)
+            ok, ov = torch.zeros_like(dk), torch.zeros_like(dv)
+            counts = idx.partition_dev(dk.data_ptr(), dv.data_ptr(), n, ok.data_ptr(), ov.data_ptr(), p)
+            torch.cuda.synchronize()
+            owner = (ou.hashes(keys, k, ou.hash_which(hash_kind, True)) % np.uint64(p)).astype(np.int64)
+            assert counts.tolist() == np.bincount(owner, minlength=p).tolist()
+            order = np.argsort(owner, kind="stable")  # imxx::distribute keeps the sender's order per bucket
+            assert np.array_equal(host_u64(ov), vals[order])
+            assert np.array_equal(host_u64(ok).reshape(n, nw), keys.reshape(n, nw)[order])
+
+
+def test_synthetic_generator_matches_host_twin():
+    rec = kb.synth_record_bytes(150)
+    assert rec == 317
+    n_reads = 5000
+    for (first, seed, n_ppm) in ((0, 1, 0), (123456789, 9, 1000)):
+        t = torch.zeros(n_reads * rec, dtype=torch.uint8, device="cuda")
+        kb.synth_fastq_dev(0, t.data_ptr(), first, n_reads, 150, 250000, seed, 5000, n_ppm)
+        torch.cuda.synchronize()
+        want = ou.synth_fastq(first, n_reads, 150, 250000, seed, 5000, n_ppm)
+        assert np.array_equal(t.cpu().numpy(), want)
+
+
+def test_synthetic_build_parity_and_properties():
+    """A 30x synthetic slice (the bench workload's shape, smaller): dump equality with the oracle,
+    then size-independent properties: sum of counts == k-mers, chunked build == one-shot build."""
+    n_reads, G = 60000, 300000
+    buf = ou.synth_fastq(0, n_reads, 150, G, 1, 5000, 0)
+    keys, _, reads = ou.fastq_kmers(buf, 31)
+    assert reads == n_reads and len(keys) == n_reads * 120
+    wk, wc = ou.count_sorted(keys, 31)
+    with kb.CountIndex(31, hash=kb.HASH_FARM, reserve=len(wk)) as idx:
+        assert idx.build_fastq(buf) == len(keys)
+        gk, gc = idx.sorted_dump()
+        assert np.array_equal(gk, wk) and np.array_equal(gc, wc)
+        ck = idx.checksum()
+        assert ck[1] == len(keys)
+    with kb.CountIndex(31, hash=kb.HASH_FARM) as idx:  # two record-aligned halves, growth on demand
+        half = (n_reads // 2) * 317
+        idx.build_fastq(buf[:half])
+        idx.build_fastq(buf[half:])
+        assert idx.checksum() == ck
+
+
+def test_k63_count_index_on_synthetic():
+    buf = ou.synth_fastq(1000, 20000, 150, 100000, 3, 5000, 500)
+    for nsplit in (False, True):
+        keys, _, _ = ou.fastq_kmers(buf, 63, nsplit=nsplit)
+        wk, wc = ou.count_sorted(keys, 63)
+        with kb.CountIndex(63, nsplit=nsplit) as idx:
+            assert idx.build_fastq(buf) == len(keys)
+            gk, gc = idx.sorted_dump()
+            assert np.array_equal(gk, wk) and np.array_equal(gc, wc)
