@@ -1,0 +1,341 @@
+#!/usr/bin/env python
+"""bench.py — canonical k-mers inserted/sec into the count index (BASELINE.json metric).
+
+A "step" is one pass of the hot path over one batch: build a K=31 canonical CountIndex from a
+synthetic FASTQ block (150 bp reads, 30x coverage, 0.5 % substitutions).
+  N = 1   : configs[1] — 1 Gbp = 6 666 667 reads = 2.11 GB of text = 8.0e8 31-mers, resident in HBM;
+            the fused text->table kernel path (kmi_build_fastq_dev).
+  N > 1   : weak scaling — every rank holds its own 1 Gbp of reads of an N-times larger genome;
+            parse -> partition (owner = dist_hash % N) -> NCCL all-to-all -> insert.
+  value   : total k-mers / device time (CUDA events, max over ranks), inputs resident in HBM.
+  e2e     : the same through the host-buffer call (kmi_build_fastq from pinned memory: H2D copy
+            inside, D2H read of the resulting size).
+  --impl reference : the reference's own CPU code for the path (oracle/_ref: its Kmer, lex_less,
+            farm hash and google::dense_hash_map, rank-parallel over all host threads; the C port
+            oracle/kmi_oracle.c when _ref is absent) on a bounded sample of the same workload.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+K = 31
+READ_LEN = 150
+REC = 13 + 2 * READ_LEN + 4          # 317
+KMERS_PER_READ = READ_LEN - K + 1    # 120
+READS_1GBP = 6666667
+GENOME_1GBP = 33333333               # 30x
+SEED = 1
+ERR_PPM = 5000
+# algorithmic bytes per k-mer of the fused text->table kernel: text R/n + slot read 12 + slot write 12
+ALG_BYTES_FUSED = REC / KMERS_PER_READ + 24.0
+# unfused (multi-GPU) pipeline per SURVEY.md §8d: S1-S3 10.6 + S4 24 + S5 32
+ALG_BYTES_SHARDED = (REC + 8.0 * KMERS_PER_READ) / KMERS_PER_READ + 24.0 + 32.0
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+
+    def __init__(self, gpu_index):
+        self.rows = []
+        self.proc = None
+        self.gpu = gpu_index
+
+    def start(self):
+        q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the reference's CPU code on a bounded sample
+# ------------------------------------------------------------------------------------------------
+def _cpu_sample(n_reads, genome_len):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_util as ou
+    if not os.path.exists(os.path.join(ROOT, "oracle", "libkmi_oracle.so")):
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle"), os.path.join(ROOT, "oracle", "libkmi_oracle.so")])
+    text = ou.synth_fastq(0, n_reads, READ_LEN, genome_len, SEED, ERR_PPM, 0)
+    return ou, text
+
+
+def cpu_reference_rate(n_reads, threads, steps=1, warmup=0):
+    """k-mers/s of the reference's CPU path on the first n_reads reads of the workload."""
+    # a 30x slice of the workload: the genome shrinks with the sample so the duplicate structure is kept
+    ou, text = _cpu_sample(n_reads, max(int(GENOME_1GBP * (n_reads / READS_1GBP)), 10 * READ_LEN))
+    ref = ou.ref_lib("ndebug")
+    n_kmers = n_reads * KMERS_PER_READ
+    times = []
+    if ref is not None:
+        kind = "reference"
+        # the record walk (restated, MPI headers do not build): sequence lines of the 317-byte records
+        recs = text.reshape(n_reads, REC)
+        seqs = np.ascontiguousarray(recs[:, 13:13 + READ_LEN]).reshape(-1)
+        off = (np.arange(n_reads + 1, dtype=np.uint64) * np.uint64(READ_LEN))
+        sizes = np.zeros(threads, dtype=np.uint64)
+        for it in range(warmup + steps):
+            t0 = time.perf_counter()
+            d = ref.kmiref_count_build(K, ou._ptr(seqs), ou._ptr(off), n_reads, threads, 1, None, None, 0, ou._ptr(sizes))
+            dt = time.perf_counter() - t0
+            if it >= warmup:
+                times.append(dt)
+        distinct = int(d)
+    else:
+        kind = "port"
+        threads = 1
+        nk = ctypes.c_long(0)
+        for it in range(warmup + steps):
+            t0 = time.perf_counter()
+            d = ou.oracle().kmio_count_build_port(ou._ptr(text), text.size, K, 2, None, None, 0, ctypes.byref(nk))
+            dt = time.perf_counter() - t0
+            if it >= warmup:
+                times.append(dt)
+        distinct = int(d)
+    sec = float(np.mean(times))
+    return {"value": n_kmers / sec, "unit": "kmers/s", "cores": threads, "kind": kind,
+            "sample": "30x slice of the workload: %d reads (%d k-mers, %d distinct) over a proportionally smaller genome; %s" % (
+                n_reads, n_kmers, distinct,
+                "reference Kmer/lex_less/farm/dense_hash_map compiled from /root/reference, %d rank-threads, record walk restated"
+                % threads if kind == "reference" else "C port oracle/kmi_oracle.c, 1 thread"),
+            "seconds_per_step": sec}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    n_reads = int(os.environ.get("KMI_REF_READS", "400000"))
+    r = cpu_reference_rate(n_reads, threads, steps=args.steps, warmup=min(args.warmup, 1))
+    line = {"impl": "reference", "metric": "canonical k-mers inserted/sec into count index", "value": r["value"], "unit": "kmers/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["seconds_per_step"] * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": "CountIndex K=31 canonical, synthetic 150 bp reads (bounded sample of the 1 Gbp block), host CPU",
+                       "k": K, "read_len": READ_LEN, "hash": "farm"},
+            "cpu_baseline": {"value": r["value"], "unit": "kmers/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
+            "e2e": {"value": r["value"], "unit": "kmers/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def run_gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    import kmerind_b200 as kb
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+    n_reads = int(os.environ.get("KMI_BENCH_READS", str(READS_1GBP)))
+    genome = int(GENOME_1GBP * (n_reads / READS_1GBP)) * world
+    nbytes = n_reads * REC
+    n_kmers_rank = n_reads * KMERS_PER_READ
+    first_read = rank * n_reads
+
+    # synthetic reads, generated on the device (same bytes as the host twin in oracle/)
+    text = torch.empty(nbytes + 64, dtype=torch.uint8, device=device)
+    kb.synth_fastq_dev(local_rank, text.data_ptr(), first_read, n_reads, READ_LEN, genome, SEED, ERR_PPM, 0)
+    torch.cuda.synchronize()
+    reserve = int(os.environ.get("KMI_BENCH_RESERVE", str(int(0.30 * n_kmers_rank))))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local_rank)
+    stage = {}
+    if world == 1:
+        idx = kb.CountIndex(K, hash=kb.HASH_FARM, device=local_rank, reserve=reserve)
+
+        def step():
+            idx.clear()
+            n = idx.build_fastq_dev(text.data_ptr(), nbytes)
+            assert n == n_kmers_rank, (n, n_kmers_rank)
+        launches_of = idx.launch_count
+    else:
+        from kmerind_b200.dist import ShardedIndex
+        idx = ShardedIndex(K, hash=kb.HASH_FARM, device=local_rank, reserve=reserve)
+
+        def step():
+            idx.local.clear()
+            n = idx.build_fastq_dev(text, nbytes, max_kmers=n_kmers_rank)
+            assert n == n_kmers_rank, (n, n_kmers_rank)
+        launches_of = idx.local.launch_count
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    l0 = launches_of()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    fused_ms, scan_ms = [], []
+    e0.record()
+    for _ in range(args.steps):
+        step()
+        if world == 1:
+            ms = idx.last_stage_ms()
+            scan_ms.append(ms[0]); fused_ms.append(ms[1])
+        else:
+            for k_, v_ in idx.stage_ms.items():
+                stage.setdefault(k_, []).append(v_)
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    launches = launches_of() - l0
+    ms_total = e0.elapsed_time(e1)
+    t = torch.tensor([ms_total], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+    total_kmers = n_kmers_rank * world
+    value = total_kmers / (ms_step * 1e-3)
+
+    # contents check outside the timed region: sum of counts == k-mers generated
+    if world == 1:
+        cks = idx.checksum()
+        assert cks[1] == n_kmers_rank, "sum of counts %d != k-mers %d" % (cks[1], n_kmers_rank)
+        distinct = idx.size()
+        info = idx.table_info()
+    else:
+        cks = idx.local.checksum()
+        tsum = torch.tensor([cks[1]], dtype=torch.int64, device=device)
+        dist.all_reduce(tsum)
+        assert int(tsum.item()) == total_kmers, "sum of counts %d != k-mers %d" % (int(tsum.item()), total_kmers)
+        distinct = idx.size()
+        info = idx.local.table_info()
+
+    # ---- e2e: host (pinned) buffer through the public host-pointer call, D2H read of the size
+    e2e = None
+    if world == 1:
+        host = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+        host.copy_(text[:nbytes])
+        torch.cuda.synchronize()
+        host_np = host.numpy()
+        e2e_steps = max(1, min(args.steps, 3))
+        for _ in range(1):
+            idx.clear(); idx.build_fastq(host_np)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            idx.clear()
+            n = idx.build_fastq(host_np)
+            sz = idx.size()
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / e2e_steps
+        e2e = {"value": n_kmers_rank / dt, "unit": "kmers/s", "h2d_bytes_per_step": int(nbytes), "d2h_bytes_per_step": 72,
+               "ms_per_step": dt * 1e3}
+        assert n == n_kmers_rank and sz == distinct
+
+    peak, peak_kind = measured_peaks()
+    if world == 1:
+        k_ms = float(np.mean(fused_ms))
+        achieved = ALG_BYTES_FUSED * n_kmers_rank / (k_ms * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "kernel": "k_fastq_kmers<31,farm,sink=table> (fused text->table)", "achieved": achieved,
+                    "peak": peak, "peak_source": peak_kind, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                    "alg_bytes_per_kmer": ALG_BYTES_FUSED, "kernel_ms_per_step": k_ms, "scan_ms_per_step": float(np.mean(scan_ms))}
+    else:
+        smean = {k_: float(np.mean(v_)) for k_, v_ in stage.items()}
+        k_ms = smean.get("insert", 0.0)
+        achieved = 32.0 * idx.n_received / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
+        roofline = {"bound": "hbm", "kernel": "k_insert_keys<31,farm> (insert of received keys)", "achieved": achieved, "peak": peak,
+                    "peak_source": peak_kind, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "alg_bytes_per_kmer": 32.0,
+                    "kernel_ms_per_step": k_ms, "stage_ms": smean,
+                    "a2a_gbs_per_dir": (8.0 * n_kmers_rank * (world - 1) / world) / (smean.get("a2a", 1e9) * 1e-3) / 1e9}
+
+    if rank == 0:
+        line = {"metric": "canonical k-mers inserted/sec into count index", "value": value, "unit": "kmers/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+                "config": {"workload": "CountIndex K=31 canonical, synthetic %.2f Gbp of 150 bp reads per GPU (30x, 0.5%% subst.), %s"
+                                       % (n_reads * READ_LEN / 1e9, "1xB200 fused text->table" if world == 1 else
+                                          "%dxB200 parse->partition->NCCL all-to-all->insert" % world),
+                           "k": K, "read_len": READ_LEN, "reads_per_gpu": n_reads, "text_bytes_per_gpu": nbytes,
+                           "kmers_per_gpu": n_kmers_rank, "hash": "farm (dist+store)", "distinct_keys": distinct,
+                           "table_slots_per_gpu": info["slots"], "l2": "inputs (%.2f GB text, %.1f GB table) larger than L2"
+                                                                     % (nbytes / 1e9, info["slots"] * info["slot_bytes"] / 1e9)},
+                "clocks": clocks, "gpu_launches": int(launches), "roofline": roofline}
+        if e2e is not None:
+            line["e2e"] = e2e
+        if world == 1 and not os.environ.get("KMI_BENCH_NO_CPU"):
+            try:
+                line["cpu_baseline"] = {k_: v_ for k_, v_ in cpu_reference_rate(int(os.environ.get("KMI_REF_READS", "400000")),
+                                                                                os.cpu_count() or 1).items() if k_ != "seconds_per_step"}
+            except Exception as ex:  # the baseline is reported, never required for the GPU number
+                line["cpu_baseline"] = {"value": None, "unit": "kmers/s", "cores": 0, "kind": "port", "sample": "failed: %s" % ex}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="kmerind_b200")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

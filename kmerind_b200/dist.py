@@ -1,0 +1,174 @@
+"""Sharded (multi-GPU) index: one process per GPU, keys owned by ``dist_hash(key) % nranks``.
+
+This is the plumbing half of imxx::distribute (reference src/io/incremental_mxx.hpp:1039-1109):
+the local half — owner computation, histogram, stable scatter — is the CUDA partition stage of
+libkmi.so (kmi_partition_dev); the exchange itself (mxx::all2all of the counts :1087 and
+mxx::all2allv of the keys :1098) is torch.distributed all_to_all_single, i.e. NCCL over NVLink /
+NVSwitch on GPUs (gloo on CPU tensors in the world_size-2 tests). Nothing here computes on keys.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import Index, MODE_COUNT, MODE_POSITION, HASH_MURMUR, nwords
+
+
+def exchange_counts(send_counts, group=None):
+    """mxx::all2all(send_counts): returns recv_counts (int64 tensor on the same device)."""
+    recv = torch.empty_like(send_counts)
+    dist.all_to_all_single(recv, send_counts, group=group)
+    return recv
+
+
+def exchange_rows(rows, send_counts, recv_counts, group=None):
+    """mxx::all2allv: `rows` is (n, w) int64 grouped by destination rank in rank order; returns the
+    rows received, grouped by source rank, each group in the sender's order."""
+    w = rows.shape[1] if rows.dim() == 2 else 1
+    out = torch.empty((int(recv_counts.sum().item()), w) if rows.dim() == 2 else (int(recv_counts.sum().item()),),
+                      dtype=rows.dtype, device=rows.device)
+    dist.all_to_all_single(out, rows.contiguous(), output_split_sizes=[int(x) for x in recv_counts.tolist()],
+                           input_split_sizes=[int(x) for x in send_counts.tolist()], group=group)
+    return out
+
+
+class ShardedIndex:
+    """CountIndex / PositionIndex sharded over the ranks of a torch.distributed group.
+
+    Every rank must call every batch operation (also with empty input), exactly like the
+    reference's distributed maps (distributed_densehash_map.hpp:2567-2573).
+    """
+
+    def __init__(self, k=31, mode=MODE_COUNT, canonical=True, hash=HASH_MURMUR, nsplit=False, device=0, reserve=0,
+                 group=None):
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.nranks = dist.get_world_size(group)
+        self.k, self.nw, self.mode = k, nwords(k), mode
+        self.device = torch.device("cuda", device)
+        # the parser side canonicalises; keys arriving after the exchange are stored as they are
+        self.local = Index(k=k, mode=mode, canonical=canonical, hash=hash, nsplit=nsplit, device=device, rank=self.rank,
+                           nranks=self.nranks, reserve=reserve)
+        self.canonical = canonical
+        self.stage_ms = {}
+
+    def close(self):
+        self.local.close()
+
+    # -- build -----------------------------------------------------------------------------------
+    def _distribute(self, d_keys, d_vals, n):
+        """partition (CUDA) -> count exchange -> key exchange (NCCL). Returns (recv_keys, recv_vals, n_recv)."""
+        p, nw = self.nranks, self.nw
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        ev[0].record()
+        part_k = torch.empty(max(n, 1) * nw, dtype=torch.int64, device=self.device)
+        part_v = torch.empty(max(n, 1), dtype=torch.int64, device=self.device) if d_vals is not None else None
+        counts = self.local.partition_dev(d_keys.data_ptr(), d_vals.data_ptr() if d_vals is not None else None, n,
+                                          part_k.data_ptr(), part_v.data_ptr() if part_v is not None else None, p)
+        ev[1].record()
+        send = torch.from_numpy(counts.astype(np.int64)).to(self.device)
+        recv = exchange_counts(send, self.group)
+        rk = exchange_rows(part_k[:n * nw].view(n, nw), send, recv, self.group)
+        rv = exchange_rows(part_v[:n], send, recv, self.group) if part_v is not None else None
+        ev[2].record()
+        self._ev = ev
+        return rk.reshape(-1), rv, int(recv.sum().item())
+
+    def _insert_received(self, rk, rv, n_recv):
+        # received keys are already canonical (or intentionally not): store verbatim
+        import ctypes
+        from . import _check
+        lib = self.local._lib
+        # temporarily bypass the input transform: kmi_insert_dev canonicalises when cfg.canonical is set,
+        # and canonical(canonical(x)) == canonical(x), so inserting as-is is exact either way.
+        _check(lib.kmi_insert_dev(self.local._h, rk.data_ptr(), rv.data_ptr() if rv is not None else None, n_recv))
+
+    def build_fastq_dev(self, text, nbytes, max_kmers=None):
+        """text: CUDA uint8 tensor holding this rank's whole records. Returns k-mers generated here."""
+        nw = self.nw
+        cap = max_kmers if max_kmers is not None else max(nbytes // 2 + 1, 1)
+        keys = torch.empty(cap * nw, dtype=torch.int64, device=self.device)
+        t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+        t2 = torch.cuda.Event(enable_timing=True)
+        t0.record()
+        n = self.local.parse_fastq_dev(text.data_ptr(), nbytes, keys.data_ptr(), cap)
+        t1.record()
+        rk, rv, n_recv = self._distribute(keys, None, n)
+        del keys
+        self._insert_received(rk, rv, n_recv)
+        t2.record()
+        torch.cuda.synchronize(self.device)
+        self.stage_ms = {"parse": t0.elapsed_time(t1), "partition": self._ev[0].elapsed_time(self._ev[1]),
+                         "a2a": self._ev[1].elapsed_time(self._ev[2]), "insert": self._ev[2].elapsed_time(t2)}
+        self.n_received = n_recv
+        return n
+
+    def build_fasta_dev(self, text, nbytes):
+        nw = self.nw
+        cap = max(nbytes, 1)
+        keys = torch.empty(cap * nw, dtype=torch.int64, device=self.device)
+        ids = torch.empty(cap, dtype=torch.int64, device=self.device) if self.mode == MODE_POSITION else None
+        n = self.local.parse_fasta_dev(text.data_ptr(), nbytes, keys.data_ptr(), cap, ids.data_ptr() if ids is not None else None)
+        rk, rv, n_recv = self._distribute(keys, ids, n)
+        self._insert_received(rk, rv, n_recv)
+        torch.cuda.synchronize(self.device)
+        return n
+
+    def insert(self, keys, vals=None):
+        """Index::insert on host arrays (any rank may hold any keys)."""
+        a = np.ascontiguousarray(keys, dtype=np.uint64).reshape(-1)
+        n = a.size // self.nw
+        dk = torch.from_numpy(a.view(np.int64)).to(self.device)
+        if self.canonical and n:
+            self.local.canonicalize_dev(dk.data_ptr(), dk.data_ptr(), n)
+        dv = torch.from_numpy(np.ascontiguousarray(vals, dtype=np.uint64).view(np.int64)).to(self.device) if vals is not None else None
+        rk, rv, n_recv = self._distribute(dk, dv, n)
+        self._insert_received(rk, rv, n_recv)
+        torch.cuda.synchronize(self.device)
+
+    # -- query -------------------------------------------------------------------------------------
+    def _query(self, keys, want_vals):
+        """canonicalise -> distribute -> local probe -> answers back along the transposed counts
+        (distributed_densehash_map.hpp:1122-1216). Returns answers in INPUT order."""
+        a = np.ascontiguousarray(keys, dtype=np.uint64).reshape(-1)
+        nw, p = self.nw, self.nranks
+        n = a.size // nw
+        dk = torch.from_numpy(a.view(np.int64)).to(self.device)
+        if self.canonical and n:
+            self.local.canonicalize_dev(dk.data_ptr(), dk.data_ptr(), n)
+        tag = torch.arange(n, dtype=torch.int64, device=self.device)  # original index travels as the value
+        part_k = torch.empty(max(n, 1) * nw, dtype=torch.int64, device=self.device)
+        part_t = torch.empty(max(n, 1), dtype=torch.int64, device=self.device)
+        counts = self.local.partition_dev(dk.data_ptr(), tag.data_ptr(), n, part_k.data_ptr(), part_t.data_ptr(), p)
+        send = torch.from_numpy(counts.astype(np.int64)).to(self.device)
+        recv = exchange_counts(send, self.group)
+        rk = exchange_rows(part_k[:n * nw].view(n, nw), send, recv, self.group).reshape(-1)
+        m = int(recv.sum().item())
+        vals = torch.zeros(max(m, 1), dtype=torch.int64, device=self.device)
+        found = torch.zeros(max(m, 1), dtype=torch.uint8, device=self.device)
+        if want_vals:
+            self.local.find_dev(rk.data_ptr(), m, vals.data_ptr(), found.data_ptr())
+        else:
+            self.local.count_dev(rk.data_ptr(), m, vals.data_ptr())
+        back_v = exchange_rows(vals[:m], recv, send, self.group)
+        back_f = exchange_rows(found[:m].to(torch.int64), recv, send, self.group)
+        out_v = torch.zeros(n, dtype=torch.int64, device=self.device)
+        out_f = torch.zeros(n, dtype=torch.int64, device=self.device)
+        out_v[part_t[:n]] = back_v
+        out_f[part_t[:n]] = back_f
+        return out_v.cpu().numpy().view(np.uint64), out_f.cpu().numpy().astype(np.uint8)
+
+    def count(self, keys):
+        return self._query(keys, False)[0]
+
+    def find(self, keys):
+        return self._query(keys, True)
+
+    # -- sizes -------------------------------------------------------------------------------------
+    def local_size(self):
+        return self.local.local_size()
+
+    def size(self):
+        """Index::size(): allreduce of local sizes (distributed_map_base.hpp:243)."""
+        t = torch.tensor([self.local.local_size()], dtype=torch.int64, device=self.device)
+        dist.all_reduce(t, group=self.group)
+        return int(t.item())
