@@ -1,0 +1,62 @@
+"""Times the stages of the count-index build separately on one GPU (CUDA events, resident inputs):
+scan, parse->keys (sink 0), insert of the key stream, fused text->table. Usage:
+    python tools/stage_times.py [n_reads] [reserve_frac]
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import kmerind_b200 as kb  # noqa: E402
+
+n_reads = int(sys.argv[1]) if len(sys.argv) > 1 else 6666667
+frac = float(sys.argv[2]) if len(sys.argv) > 2 else 0.3
+REC, KPR = 317, 120
+nbytes = n_reads * REC
+n_kmers = n_reads * KPR
+genome = int(33333333 * n_reads / 6666667)
+text = torch.empty(nbytes + 64, dtype=torch.uint8, device="cuda")
+kb.synth_fastq_dev(0, text.data_ptr(), 0, n_reads, 150, genome, 1, 5000, 0)
+keys = torch.empty(n_kmers, dtype=torch.int64, device="cuda")
+torch.cuda.synchronize()
+
+
+def timed(fn, reps=3):
+    fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+idx = kb.CountIndex(31, hash=kb.HASH_FARM, reserve=int(frac * n_kmers))
+t_parse = timed(lambda: idx.parse_fastq_dev(text.data_ptr(), nbytes, keys.data_ptr(), n_kmers))
+
+
+def ins():
+    idx.clear()
+    idx.insert_dev(keys.data_ptr(), n_kmers)
+
+
+t_clear = timed(lambda: idx.clear())
+t_ins = timed(ins) - t_clear
+
+
+def fused():
+    idx.clear()
+    idx.build_fastq_dev(text.data_ptr(), nbytes)
+
+
+t_fused = timed(fused) - t_clear
+st = idx.last_stage_ms()
+info = idx.table_info()
+print("reads %d kmers %d distinct %d slots %d" % (n_reads, n_kmers, idx.size(), info["slots"]))
+print("parse->keys (incl. scan) %.3f ms | clear %.3f ms | insert(keys) %.3f ms | fused build %.3f ms (scan %.3f, kernel %.3f)"
+      % (t_parse, t_clear, t_ins, t_fused, st[0], st[1]))
+print("rates: parse %.2f G/s, insert %.2f G/s, fused %.2f G/s" % (n_kmers / t_parse / 1e6, n_kmers / t_ins / 1e6, n_kmers / t_fused / 1e6))
