@@ -70,6 +70,13 @@ void kmi_destroy(kmi_index* idx);
 const char* kmi_last_error(void);
 /* run subsequent work of this index on `cuda_stream` (a cudaStream_t); NULL = default stream */
 int kmi_set_stream(kmi_index* idx, void* cuda_stream);
+/* Tuning knobs without a reference counterpart. KMI_PARAM_BUILD_PATH: how k-mers reach the table —
+ * 0 auto (by input size), 1 direct atomics from the parser, 2 through the 256 hash-prefix buckets
+ * (table segments stay L2-resident). KMI_PARAM_SEGMENT_INSERT (bucketed path, K <= 31): 1 (default) =
+ * second-level scatter + table segments updated in shared memory, 0 = L2-resident global atomics.
+ * Results are identical on every path. */
+typedef enum { KMI_PARAM_BUILD_PATH = 1, KMI_PARAM_SEGMENT_INSERT = 2 } kmi_param;
+int kmi_set_param(kmi_index* idx, int param, int64_t value);
 /* map_base::reserve — src/containers/distributed_map_base.hpp:149-302 */
 int kmi_reserve(kmi_index* idx, uint64_t n_distinct);
 /* remove every entry, keep the allocation */

@@ -63,7 +63,7 @@ def load_library(build_if_missing=False):
     lib.kmi_destroy.argtypes = [_P]
     lib.kmi_destroy.restype = None
     sig = {
-        "kmi_set_stream": [_P, _P], "kmi_reserve": [_P, _U64], "kmi_clear": [_P],
+        "kmi_set_stream": [_P, _P], "kmi_set_param": [_P, ctypes.c_int, ctypes.c_int64], "kmi_reserve": [_P, _U64], "kmi_clear": [_P],
         "kmi_build_fastq": [_P, _P, _SZ, _U64, _P], "kmi_build_fasta": [_P, _P, _SZ, _P],
         "kmi_build_fastq_dev": [_P, _P, _SZ, _U64, _P], "kmi_build_fasta_dev": [_P, _P, _SZ, _P],
         "kmi_parse_fastq_dev": [_P, _P, _SZ, _U64, _P, _P, _SZ, _P],
@@ -89,7 +89,7 @@ def load_library(build_if_missing=False):
 
 
 EXPORTED_SYMBOLS = (
-    "kmi_create", "kmi_destroy", "kmi_last_error", "kmi_set_stream", "kmi_reserve", "kmi_clear",
+    "kmi_create", "kmi_destroy", "kmi_last_error", "kmi_set_stream", "kmi_set_param", "kmi_reserve", "kmi_clear",
     "kmi_build_fastq", "kmi_build_fasta", "kmi_build_fastq_dev", "kmi_build_fasta_dev",
     "kmi_parse_fastq_dev", "kmi_parse_fasta_dev", "kmi_canonicalize_dev", "kmi_hash_dev",
     "kmi_partition_dev", "kmi_insert", "kmi_insert_dev", "kmi_count", "kmi_find", "kmi_find_positions",
@@ -298,6 +298,14 @@ class Index:
         ms = (ctypes.c_float * 3)()
         _check(self._lib.kmi_last_stage_ms(self._h, ms))
         return [float(x) for x in ms]
+
+    def set_build_path(self, path):
+        """0 auto, 1 direct atomics, 2 hash-prefix buckets (KMI_PARAM_BUILD_PATH)."""
+        _check(self._lib.kmi_set_param(self._h, 1, path))
+
+    def set_segment_insert(self, on):
+        """bucketed path: shared-memory segment insert (default) or L2 atomics (KMI_PARAM_SEGMENT_INSERT)."""
+        _check(self._lib.kmi_set_param(self._h, 2, 1 if on else 0))
 
     def set_stream(self, cuda_stream_ptr):
         _check(self._lib.kmi_set_stream(self._h, cuda_stream_ptr))

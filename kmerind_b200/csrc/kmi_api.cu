@@ -6,6 +6,7 @@
 #include "kmi_ops.cuh"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -63,6 +64,9 @@ struct DevBuf {
 // device counters block
 enum { CTR_SIZE = 0, CTR_NKMERS = 1, CTR_CURSOR = 2, CTR_CK0 = 3, CTR_CK1 = 4, CTR_REMOVED = 5, CTR_ERR = 6, CTR_PERR = 7, CTR_N = 8 };
 
+// bkt_meta layout (u32 words): cursors [0, N_BUCKETS], HLL registers from META_HLL
+enum { META_HLL = 512, META_WORDS = META_HLL + HLL_M };
+
 }  // namespace
 
 struct kmi_index {
@@ -83,14 +87,22 @@ struct kmi_index {
   DevBuf log_keys, log_ids, log_keys2, log_ids2, offsets, csr_sums, values;
   u64 log_n = 0;
   bool csr_dirty = false;
+  // hash-prefix buckets (kmi_bucket.cuh): key regions, cursors + HyperLogLog registers
+  DevBuf bkt_keys, bkt_meta, fine_keys, fine_cur;
+  u32 h_cursor[N_BUCKETS + 1];   // last read-back of the coarse cursors
+  int seg_path = 1;        // KMI_PARAM_SEGMENT_INSERT: 1 = shared-memory segment insert where possible, 0 = L2 atomics
+  bool hll_ready = false;
+  u64 non_hll_upper = 0;   // keys inserted by paths that do not feed the HLL (upper bound on their distinct keys)
+  int build_path = 0;      // kmi_param KMI_PARAM_BUILD_PATH: 0 auto, 1 direct atomics, 2 bucketed
   // accounting
   u64 launches = 0;
   float stage_ms[3] = {0, 0, 0};
-  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  float scatter_ms = 0;    // parse+scatter share of the last bucketed build
 
   TableView view() const {
     TableView t;
-    t.slots = slots; t.mask = cap - 1; t.size = ctr + CTR_SIZE; t.error = reinterpret_cast<u32*>(ctr + CTR_ERR);
+    t.slots = slots; t.mask = cap - 1; t.shift = 64u - (u32)__builtin_ctzll(cap ? cap : 1); t.size = ctr + CTR_SIZE; t.error = reinterpret_cast<u32*>(ctr + CTR_ERR);
     return t;
   }
 };
@@ -212,7 +224,7 @@ extern "C" int kmi_create(const kmi_config* cfg, kmi_index** out) {
   e = cudaMalloc(&idx->ctr, sizeof(u64) * CTR_N);
   if (e != cudaSuccess) { delete idx; return fail(KMI_ERR_CUDA, "cudaMalloc counters: %s", cudaGetErrorString(e)); }
   cudaMemset(idx->ctr, 0, sizeof(u64) * CTR_N);
-  for (int i = 0; i < 4; ++i) cudaEventCreate(&idx->ev[i]);
+  for (int i = 0; i < 6; ++i) cudaEventCreate(&idx->ev[i]);
   *out = idx;
   if (cfg->reserve) {
     int r = kmi_reserve(idx, cfg->reserve);
@@ -229,9 +241,9 @@ extern "C" void kmi_destroy(kmi_index* idx) {
   if (idx->ctr) cudaFree(idx->ctr);
   DevBuf* bufs[] = {&idx->tile_lines, &idx->block_sums, &idx->stage_in, &idx->stage_keys, &idx->stage_vals,
                     &idx->stage_out, &idx->stage_found, &idx->hist, &idx->hist_sums, &idx->log_keys, &idx->log_ids,
-                    &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values};
+                    &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur};
   for (DevBuf* b : bufs) b->release();
-  for (int i = 0; i < 4; ++i) if (idx->ev[i]) cudaEventDestroy(idx->ev[i]);
+  for (int i = 0; i < 6; ++i) if (idx->ev[i]) cudaEventDestroy(idx->ev[i]);
   delete idx;
 }
 
@@ -239,6 +251,20 @@ extern "C" int kmi_set_stream(kmi_index* idx, void* cuda_stream) {
   if (!idx) return fail(KMI_ERR_ARG, "null index");
   idx->stream = reinterpret_cast<cudaStream_t>(cuda_stream);
   return KMI_OK;
+}
+
+extern "C" int kmi_set_param(kmi_index* idx, int param, int64_t value) {
+  if (!idx) return fail(KMI_ERR_ARG, "null index");
+  if (param == KMI_PARAM_BUILD_PATH) {
+    if (value < 0 || value > 2) return fail(KMI_ERR_ARG, "build path must be 0 (auto), 1 (direct) or 2 (bucketed)");
+    idx->build_path = (int)value;
+    return KMI_OK;
+  }
+  if (param == KMI_PARAM_SEGMENT_INSERT) {
+    idx->seg_path = value != 0;
+    return KMI_OK;
+  }
+  return fail(KMI_ERR_ARG, "unknown parameter %d", param);
 }
 
 extern "C" int kmi_reserve(kmi_index* idx, uint64_t n_distinct) {
@@ -257,6 +283,139 @@ extern "C" int kmi_clear(kmi_index* idx) {
   idx->size_exact = idx->size_upper = 0;
   idx->log_n = 0;
   idx->csr_dirty = false;
+  idx->non_hll_upper = 0;
+  if (idx->hll_ready) CU(cudaMemsetAsync(idx->bkt_meta.as<u32>() + META_HLL, 0, sizeof(u32) * HLL_M, idx->stream));
+  return KMI_OK;
+}
+
+
+// ---- hash-prefix buckets (kmi_bucket.cuh) -------------------------------------------------------------
+static const u64 BUCKET_MAX_KEYS = 1ULL << 31;   // per round trip; keeps every cursor and their sum below 2^32
+
+// (re)size the bucket regions for up to `max_keys` keys and zero the cursors
+static int bucket_prepare(kmi_index* idx, u64 max_keys, BucketSink* bs) {
+  if (max_keys > BUCKET_MAX_KEYS) return fail(KMI_ERR_ARG, "bucket round of %llu keys", (unsigned long long)max_keys);
+  // uniform hash: a bucket receives max_keys/256 +- a few sigma; 6 % + 1024 slack, the rest goes to the overflow region
+  u64 capb = max_keys / N_BUCKETS + max_keys / (N_BUCKETS * 16) + 1024;
+  u64 ovf = max_keys / 8 + 4096;
+  OK(idx->bkt_keys.ensure((capb * N_BUCKETS + ovf) * sizeof(u64) * idx->nw));
+  if (!idx->hll_ready) {
+    OK(idx->bkt_meta.ensure(sizeof(u32) * META_WORDS));
+    CU(cudaMemsetAsync(idx->bkt_meta.p, 0, sizeof(u32) * META_WORDS, idx->stream));
+    idx->hll_ready = true;
+  } else {
+    CU(cudaMemsetAsync(idx->bkt_meta.p, 0, sizeof(u32) * META_HLL, idx->stream));
+  }
+  bs->keys = idx->bkt_keys.as<u64>();
+  bs->cursor = idx->bkt_meta.as<u32>();
+  bs->hll = idx->bkt_meta.as<u32>() + META_HLL;
+  bs->capb = (u32)capb;
+  bs->ovf_cap = (u32)ovf;
+  return KMI_OK;
+}
+
+// HyperLogLog estimate (Flajolet et al. 2007, with the small-range linear-counting correction)
+static double hll_estimate(const u32* reg) {
+  double sum = 0;
+  int zeros = 0;
+  for (int i = 0; i < HLL_M; ++i) { sum += std::ldexp(1.0, -(int)reg[i]); zeros += reg[i] == 0; }
+  const double m = HLL_M, alpha = 0.7213 / (1.0 + 1.079 / m);
+  double e = alpha * m * m / sum;
+  if (e <= 2.5 * m && zeros) e = m * std::log(m / zeros);
+  return e;
+}
+
+// one synchronisation per round: counters + HLL registers
+static int bucket_readback(kmi_index* idx, const BucketSink& bs, u64* host_ctr, std::vector<u32>& reg) {
+  reg.resize(HLL_M);
+  CU(cudaMemcpyAsync(reg.data(), bs.hll, sizeof(u32) * HLL_M, cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaMemcpyAsync(host_ctr, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaMemcpyAsync(idx->h_cursor, bs.cursor, sizeof(u32) * (N_BUCKETS + 1), cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaStreamSynchronize(idx->stream));
+  return KMI_OK;
+}
+
+// Size the table for what the buckets hold, then insert them segment by segment. n_keys = keys
+// scattered this round; size_now = live keys in the table before the insert.
+static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 size_now, const std::vector<u32>& reg) {
+  if (n_keys == 0) return KMI_OK;
+  // distinct keys after this insert: at most size + n_keys, and (6 sigma) at most 1.05 * HLL + keys the HLL never saw
+  const u64 by_hll = (u64)(hll_estimate(reg.data()) * 1.05) + 1024 + idx->non_hll_upper;
+  const u64 need = std::min(size_now + n_keys, std::max(by_hll, size_now));
+  if (!idx->slots || (double)need > idx->cap * MAX_LOAD) {
+    u64 want = pow2_at_least((u64)(need / MAX_LOAD) + 1);
+    if (want > idx->cap) OK(table_grow(idx, want));
+  }
+  idx->size_upper = need;
+  idx->size_exact = ~0ULL;  // stale until read back
+  // second level: table segments of <= 4096 slots (8192 beyond 2^31 slots) updated in shared memory
+  const int log_cap = __builtin_ctzll(idx->cap);
+  int log_segs = std::max(LOG_BUCKETS, log_cap - 12);
+  log_segs = std::min(log_segs, LOG_BUCKETS + MAX_LOG_F);
+  const int log_seg = log_cap - log_segs;
+  if (idx->seg_path && idx->ops->insert_segments && idx->nw == 1 && log_seg <= 13 && log_seg >= 8) {
+    const u32 log_f = (u32)(log_segs - LOG_BUCKETS);
+    const u64 n_regions = (u64)N_BUCKETS << log_f;
+    FineSink fs;
+    fs.log_f = log_f;
+    bool fine_ok = true;
+    if (log_f == 0) {
+      fs.keys = bs.keys; fs.cursor = bs.cursor; fs.capf = bs.capb;
+    } else {
+      const double mean = (double)n_keys / (double)n_regions;
+      const u64 capf = (u64)(mean + 8.0 * std::sqrt(mean) + 32.0);
+      OK(idx->fine_keys.ensure(n_regions * capf * sizeof(u64)));
+      OK(idx->fine_cur.ensure(n_regions * sizeof(u32)));
+      CU(cudaMemsetAsync(idx->fine_cur.p, 0, n_regions * sizeof(u32), idx->stream));
+      fs.keys = idx->fine_keys.as<u64>(); fs.cursor = idx->fine_cur.as<u32>(); fs.capf = (u32)capf;
+      idx->ops->scatter_fine(idx->stream, bs, fs, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), n_keys);
+      idx->launches++;
+      u64 perr = 0;
+      OK(read_ctr(idx, CTR_PERR, &perr));
+      if (perr & PERR_OVERFLOW) {
+        // skewed fine buckets exhausted the overflow region: undo its tail and take the L2 path below
+        OK(zero_ctr(idx, CTR_PERR));
+        CU(cudaMemcpyAsync(bs.cursor + N_BUCKETS, idx->h_cursor + N_BUCKETS, sizeof(u32), cudaMemcpyHostToDevice, idx->stream));
+        fine_ok = false;
+      }
+    }
+    if (fine_ok) {
+      int e = idx->ops->insert_segments(idx->stream, idx->view(), fs, bs, (u32)log_seg, (u32)n_regions,
+                                        reinterpret_cast<u32*>(idx->ctr + CTR_PERR));
+      if (e) return fail(KMI_ERR_CUDA, "segment kernel configuration: %s", cudaGetErrorString((cudaError_t)e));
+      idx->ops->insert_overflow(idx->stream, idx->view(), bs);
+      idx->launches += 2;
+      return KMI_OK;
+    }
+  }
+  idx->ops->insert_buckets(idx->stream, idx->view(), bs, n_keys);
+  idx->launches++;
+  return KMI_OK;
+}
+
+static int insert_keys_chunked(kmi_index* idx, const u64* d_keys, size_t n, bool canon);
+
+// key stream -> buckets -> table, in rounds of at most BUCKET_MAX_KEYS keys
+static int insert_keys_bucketed(kmi_index* idx, const u64* d_keys, size_t n, bool canon) {
+  size_t done = 0;
+  std::vector<u32> reg;
+  while (done < n) {
+    u64 m = std::min<u64>(n - done, BUCKET_MAX_KEYS);
+    BucketSink bs;
+    OK(bucket_prepare(idx, m, &bs));
+    OK(zero_ctr(idx, CTR_PERR));
+    idx->ops->scatter_keys(idx->stream, d_keys + done * idx->nw, m, bs, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), canon);
+    idx->launches++;
+    u64 host[CTR_N];
+    OK(bucket_readback(idx, bs, host, reg));
+    if (host[CTR_PERR] & PERR_OVERFLOW) {
+      // extreme key skew: nothing of this round is in the table yet, redo it with direct atomics
+      OK(insert_keys_chunked(idx, d_keys + done * idx->nw, m, canon));
+    } else {
+      OK(bucket_commit(idx, bs, m, host[CTR_SIZE], reg));
+    }
+    done += m;
+  }
   return KMI_OK;
 }
 
@@ -281,6 +440,7 @@ static int parse_error(u64 perr) {
   if (perr & PERR_NO_PLUS) return fail(KMI_ERR_FORMAT, "malformed FASTQ: missing + on third line of a record");
   if (perr & PERR_OVERFLOW) return fail(KMI_ERR_CAPACITY, "k-mer output buffer too small");
   if (perr & PERR_HALO) return fail(KMI_ERR_FORMAT, "FASTA line structure too sparse for the tile halo");
+  if (perr & PERR_SPILL) return fail(KMI_ERR_CAPACITY, "segment spill list exhausted: index contents are incomplete");
   return KMI_OK;
 }
 
@@ -296,8 +456,8 @@ extern "C" int kmi_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_
   OK(zero_ctr(idx, CTR_PERR));
   KeySink sink;
   sink.keys = reinterpret_cast<u64*>(d_keys); sink.ids = nullptr; sink.cap = cap; sink.cursor = idx->ctr + CTR_CURSOR;
-  TableView none; none.slots = nullptr; none.mask = 0; none.size = nullptr; none.error = nullptr;
-  idx->ops->fastq_kmers(idx->stream, 0, d_bytes, n, n_tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), sink, none,
+  TableView none; none.slots = nullptr; none.mask = 0; none.shift = 63; none.size = nullptr; none.error = nullptr;
+  idx->ops->fastq_kmers(idx->stream, 0, d_bytes, n, n_tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), sink, none, BucketSink(),
                         idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0,
                         idx->cfg.nsplit != 0, 0);
   idx->launches++;
@@ -308,7 +468,66 @@ extern "C" int kmi_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_
   return parse_error(host[CTR_PERR]);
 }
 
-// fused S1-S5: text -> table, no key stream in HBM
+// S1-S5 with direct atomics: text -> table, no key stream in HBM (tiles [tile, tile_end))
+static int build_fastq_direct(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64 tile, u64 tile_end) {
+  KeySink nosink; nosink.keys = nullptr; nosink.ids = nullptr; nosink.cap = 0; nosink.cursor = nullptr;
+  while (tile < tile_end) {
+    // a FASTQ record spends at most half of its bytes on bases
+    u64 bytes_left = std::min<u64>(n, tile_end * TILE_BYTES) - tile * TILE_BYTES;
+    u64 grant = 0;
+    OK(table_room(idx, bytes_left / 2 + 1, &grant));
+    u64 tiles = std::max<u64>(1, (grant * 2) / TILE_BYTES);
+    tiles = std::min(tiles, tile_end - tile);
+    idx->ops->fastq_kmers(idx->stream, 1, d_bytes, n, tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), nosink,
+                          idx->view(), BucketSink(), idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR),
+                          idx->cfg.canonical != 0, idx->cfg.nsplit != 0, tile);
+    idx->launches++;
+    idx->non_hll_upper += grant;
+    tile += tiles;
+  }
+  return KMI_OK;
+}
+
+// S1-S5 through the hash-prefix buckets: text -> buckets -> table, at most 4 GiB of text per round
+static int build_fastq_bucketed(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64 n_tiles) {
+  const u64 MAX_TILES = (2 * BUCKET_MAX_KEYS) / TILE_BYTES;
+  const u64 n_rounds = (n_tiles + MAX_TILES - 1) / MAX_TILES;
+  const u64 per_round = (n_tiles + n_rounds - 1) / n_rounds;
+  KeySink nosink; nosink.keys = nullptr; nosink.ids = nullptr; nosink.cap = 0; nosink.cursor = nullptr;
+  std::vector<u32> reg;
+  u64 kmers_before = 0;
+  for (u64 tile = 0; tile < n_tiles; tile += per_round) {
+    const u64 tiles = std::min(per_round, n_tiles - tile);
+    BucketSink bs;
+    OK(bucket_prepare(idx, tiles * TILE_BYTES / 2 + 1, &bs));
+    CU(cudaEventRecord(idx->ev[4], idx->stream));
+    idx->ops->fastq_kmers(idx->stream, 2, d_bytes, n, tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), nosink,
+                          idx->view(), bs, idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR),
+                          idx->cfg.canonical != 0, idx->cfg.nsplit != 0, tile);
+    idx->launches++;
+    CU(cudaEventRecord(idx->ev[5], idx->stream));
+    u64 host[CTR_N];
+    OK(bucket_readback(idx, bs, host, reg));
+    { float ms = 0; cudaEventElapsedTime(&ms, idx->ev[4], idx->ev[5]); idx->scatter_ms += ms; }
+    if (host[CTR_PERR] & (PERR_NO_AT | PERR_NO_PLUS)) return KMI_OK;  // reported by the caller; nothing of this round inserted
+    if (host[CTR_PERR] & PERR_OVERFLOW) {
+      // extreme key skew: redo this round with direct atomics (nothing of it is in the table yet)
+      OK(zero_ctr(idx, CTR_PERR));
+      CU(cudaMemcpyAsync(idx->ctr + CTR_NKMERS, &kmers_before, sizeof(u64), cudaMemcpyHostToDevice, idx->stream));
+      CU(cudaStreamSynchronize(idx->stream));
+      OK(build_fastq_direct(idx, d_bytes, n, tile, tile + tiles));
+      OK(read_ctr(idx, CTR_NKMERS, &kmers_before));
+      continue;
+    }
+    OK(bucket_commit(idx, bs, host[CTR_NKMERS] - kmers_before, host[CTR_SIZE], reg));
+    kmers_before = host[CTR_NKMERS];
+  }
+  return KMI_OK;
+}
+
+static const size_t AUTO_BUCKET_KEYS = 1u << 21;
+static const size_t AUTO_BUCKET_BYTES = 8u << 20;  // below this the direct path wins (bucket set-up dominates)
+
 extern "C" int kmi_build_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers) {
   (void)file_offset;
   if (!idx || (!d_bytes && n)) return fail(KMI_ERR_ARG, "null argument");
@@ -321,28 +540,21 @@ extern "C" int kmi_build_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_
   CU(cudaEventRecord(idx->ev[1], idx->stream));
   OK(zero_ctr(idx, CTR_NKMERS));
   OK(zero_ctr(idx, CTR_PERR));
-  KeySink nosink; nosink.keys = nullptr; nosink.ids = nullptr; nosink.cap = 0; nosink.cursor = nullptr;
-  u64 tile = 0;
-  while (tile < n_tiles) {
-    // a FASTQ record spends at most half of its bytes on bases
-    u64 bytes_left = n - tile * TILE_BYTES;
-    u64 grant = 0;
-    OK(table_room(idx, bytes_left / 2 + 1, &grant));
-    u64 tiles = std::max<u64>(1, (grant * 2) / TILE_BYTES);
-    tiles = std::min(tiles, n_tiles - tile);
-    idx->ops->fastq_kmers(idx->stream, 1, d_bytes, n, tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), nosink,
-                          idx->view(), idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR),
-                          idx->cfg.canonical != 0, idx->cfg.nsplit != 0, tile);
-    idx->launches++;
-    tile += tiles;
-  }
+  const bool bucketed = idx->build_path == 2 || (idx->build_path == 0 && n >= AUTO_BUCKET_BYTES);
+  idx->scatter_ms = 0;
+  if (bucketed) OK(build_fastq_bucketed(idx, d_bytes, n, n_tiles));
+  else OK(build_fastq_direct(idx, d_bytes, n, 0, n_tiles));
   CU(cudaEventRecord(idx->ev[2], idx->stream));
-  u64 host[8];
+  u64 host[CTR_N];
   CU(cudaMemcpyAsync(host, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
   CU(cudaStreamSynchronize(idx->stream));
   cudaEventElapsedTime(&idx->stage_ms[0], idx->ev[0], idx->ev[1]);
   cudaEventElapsedTime(&idx->stage_ms[1], idx->ev[1], idx->ev[2]);
   idx->stage_ms[2] = 0;
+  if (bucketed) {  // [1] parse + scatter into buckets, [2] table sizing + insert from buckets
+    idx->stage_ms[2] = idx->stage_ms[1] - idx->scatter_ms;
+    idx->stage_ms[1] = idx->scatter_ms;
+  }
   idx->size_exact = idx->size_upper = host[CTR_SIZE];
   if (n_kmers) *n_kmers = host[CTR_NKMERS];
   if (host[CTR_ERR]) return fail(KMI_ERR_CAPACITY, "hash table overflow (probe limit reached)");
@@ -389,6 +601,7 @@ static int insert_keys_chunked(kmi_index* idx, const u64* d_keys, size_t n, bool
     OK(table_room(idx, n - done, &grant));
     idx->ops->insert_keys(idx->stream, idx->view(), d_keys + done * idx->nw, grant, canon);
     idx->launches++;
+    idx->non_hll_upper += grant;
     done += grant;
   }
   return KMI_OK;
@@ -407,6 +620,8 @@ extern "C" int kmi_insert_dev(kmi_index* idx, const uint64_t* d_keys_, const uin
     // multiplicities go into the table now (keys in the log are already canonical)
     OK(insert_keys_chunked(idx, idx->log_keys.as<u64>() + (idx->log_n - n) * idx->nw, n, false));
     idx->csr_dirty = true;
+  } else if (idx->build_path == 2 || (idx->build_path == 0 && n >= AUTO_BUCKET_KEYS)) {
+    OK(insert_keys_bucketed(idx, d_keys, n, idx->cfg.canonical != 0));
   } else {
     OK(insert_keys_chunked(idx, d_keys, n, idx->cfg.canonical != 0));
   }
@@ -665,7 +880,7 @@ extern "C" int kmi_table_info(kmi_index* idx, uint64_t* slots, uint64_t* slot_by
     u64 b = idx->cap * idx->slot_bytes;
     const DevBuf* bufs[] = {&idx->tile_lines, &idx->block_sums, &idx->stage_in, &idx->stage_keys, &idx->stage_vals,
                             &idx->stage_out, &idx->stage_found, &idx->hist, &idx->hist_sums, &idx->log_keys, &idx->log_ids,
-                            &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values};
+                            &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur};
     for (const DevBuf* d : bufs) b += d->cap;
     *device_bytes = b;
   }

@@ -1,0 +1,362 @@
+// kmi_bucket.cuh — hash-prefix bucketing of the key stream in front of the table (sm_100a).
+//
+// Why: a count insert is a random read-modify-write of a 16/32-byte slot in a multi-GB table; done
+// straight from the parser it drags ~165 B of DRAM traffic per k-mer (profiles/r01_fused_direct_
+// atomics.md). Because the home slot is the TOP bits of the store hash (kmi_table.cuh), the top
+// LOG_BUCKETS bits name a contiguous 1/256 segment of the table whatever its capacity. Keys are
+// therefore first scattered into 256 hash-prefix buckets (streaming, coalesced runs assembled in
+// shared memory) and then inserted bucket after bucket, so that the table segment being updated is
+// L2-resident and every slot sector crosses the HBM interface once per sweep instead of once per k-mer.
+//
+// This replaces nothing in the reference one-to-one: it is the GPU counterpart of the cache
+// blocking the reference gets for free from per-rank tables that are 1/p of the data
+// (distributed_densehash_map.hpp:2565-2628), and it reuses the histogram -> scan -> scatter shape of
+// imxx::local::assign_to_buckets / permute (src/io/incremental_mxx.hpp:273-364,596-640), unordered.
+#pragma once
+#include "kmi_block.cuh"
+
+namespace kmi {
+
+static constexpr int LOG_BUCKETS = 8;
+static constexpr int N_BUCKETS = 1 << LOG_BUCKETS;        // == TILE_THREADS (one scan slot per thread)
+static constexpr int HLL_P = 14;
+static constexpr int HLL_M = 1 << HLL_P;                  // HyperLogLog registers (sigma = 0.81 %)
+static constexpr u32 BKT_NONE = 0xFFFFFFFFu;
+
+template <int NW> struct BktRound { static constexpr int R = (NW == 1 ? 8 : 4); };  // keys / thread / round
+
+struct BucketSink {
+  u64* keys;     // N_BUCKETS regions of `capb` keys, then one overflow region of `ovf_cap` keys
+  u32* cursor;   // N_BUCKETS + 1 fill counters; a counter may run past its capacity (clamp when reading)
+  u32 capb;
+  u32 ovf_cap;
+  u32* hll;      // HLL_M registers: distinct-key estimate that sizes the table before the insert
+};
+
+template <int NW> struct BucketSmem;
+template <> struct BucketSmem<0> { u32 unused; };   // kernels instantiated without the bucket sink
+template <int NW> struct BucketSmem {
+  static constexpr int R = BktRound<NW>::R;
+  static constexpr int ROUND_KEYS = TILE_THREADS * R;
+  u64 sorted[ROUND_KEYS * NW];
+  u32 hist[N_BUCKETS];
+  u32 scan[N_BUCKETS];
+  u32 delta[N_BUCKETS];
+  u32 tmp[TILE_THREADS / 32 + 1];
+  uint8_t sbid[ROUND_KEYS];
+};
+
+__device__ __forceinline__ u32 bucket_of(u64 store_hash) { return (u32)(store_hash >> (64 - LOG_BUCKETS)); }
+
+// HyperLogLog update from the store hash: register = low HLL_P bits, rank from the 42 bits above
+// them (the top 8 bits pick the bucket and stay out of it).
+__device__ __forceinline__ void hll_update(u32* __restrict__ hll, u64 h) {
+  const u32 reg = (u32)h & (HLL_M - 1);
+  const u64 w = (h >> HLL_P) << (HLL_P + LOG_BUCKETS);   // 42 significant bits, left aligned
+  const u32 rank = (u32)__clzll(w | (1ULL << (HLL_P + LOG_BUCKETS - 1))) + 1u;
+  if (hll[reg] < rank) atomicMax(hll + reg, rank);       // the plain read may be stale: then the max is redundant, never wrong
+}
+
+// One round: every thread brings up to R keys (bkt[q] == BKT_NONE: no key). The block sorts them
+// by bucket in shared memory, reserves one run per non-empty bucket with a single atomicAdd, and
+// writes the runs coalesced. Keys that do not fit their bucket go to the overflow region; if that is
+// full too, PERR_OVERFLOW is raised and the host redoes the chunk on the direct path.
+template <int NW>
+__device__ __forceinline__ void bucket_round(const BucketSink& bs, BucketSmem<NW>& sm, const Key<NW> (&key)[BktRound<NW>::R],
+                                             const u32 (&bkt)[BktRound<NW>::R], u32* __restrict__ perr) {
+  constexpr int R = BktRound<NW>::R;
+  const int t = threadIdx.x;
+  sm.hist[t] = 0;
+  __syncthreads();
+  u32 rank[R];
+#pragma unroll
+  for (int q = 0; q < R; ++q) rank[q] = (bkt[q] != BKT_NONE) ? atomicAdd(&sm.hist[bkt[q]], 1u) : 0u;
+  __syncthreads();
+  const u32 cnt = sm.hist[t];
+  u32 total;
+  const u32 ex = block_excl_scan(cnt, sm.tmp, total);
+  sm.scan[t] = ex;
+  const u32 gbase = cnt ? atomicAdd(bs.cursor + t, cnt) : 0u;
+  sm.delta[t] = gbase - ex;
+  __syncthreads();
+#pragma unroll
+  for (int q = 0; q < R; ++q) {
+    if (bkt[q] != BKT_NONE) {
+      const u32 pos = sm.scan[bkt[q]] + rank[q];
+      if (NW == 1) sm.sorted[pos] = key[q].w[0];
+      else reinterpret_cast<ulonglong2*>(sm.sorted)[pos] = make_ulonglong2(key[q].w[0], key[q].w[NW - 1]);
+      sm.sbid[pos] = (uint8_t)bkt[q];
+    }
+  }
+  __syncthreads();
+  for (u32 r = t; r < total; r += TILE_THREADS) {
+    const u32 b = sm.sbid[r];
+    u32 at = sm.delta[b] + r;
+    u64 region = (u64)b * bs.capb;
+    if (at >= bs.capb) {
+      at = atomicAdd(bs.cursor + N_BUCKETS, 1u);
+      region = (u64)N_BUCKETS * bs.capb;
+      if (at >= bs.ovf_cap) { atomicOr(perr, PERR_OVERFLOW); continue; }
+    }
+    if (NW == 1) bs.keys[region + at] = sm.sorted[r];
+    else reinterpret_cast<ulonglong2*>(bs.keys)[region + at] = reinterpret_cast<const ulonglong2*>(sm.sorted)[r];
+  }
+  __syncthreads();
+}
+
+// key stream -> buckets (used by kmi_insert_dev and the FASTA / sharded builds)
+template <int K, int HASH>
+__global__ void __launch_bounds__(TILE_THREADS)
+k_scatter_keys(const u64* __restrict__ keys, u64 n, BucketSink bs, u32* __restrict__ perr, const bool CANON) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  constexpr int R = BktRound<NW>::R;
+  __shared__ BucketSmem<NW> sm;
+  const u64 per_round = (u64)TILE_THREADS * R;
+  for (u64 base = (u64)blockIdx.x * per_round; base < n; base += (u64)gridDim.x * per_round) {
+    Key<NW> key[R];
+    u32 bkt[R];
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+      const u64 i = base + (u64)q * TILE_THREADS + threadIdx.x;
+      bkt[q] = BKT_NONE;
+      if (i < n) {
+        key[q] = load_key<NW>(keys, i);
+        if (CANON) key[q] = canonical<K>(key[q]);
+        const u64 h = store_hash<K, HASH>(key[q]);
+        bkt[q] = bucket_of(h);
+        hll_update(bs.hll, h);
+      }
+    }
+    bucket_round<NW>(bs, sm, key, bkt, perr);
+  }
+}
+
+// buckets -> table. The grid walks the concatenation of the buckets front to back (grid-stride), so
+// at any moment all CTAs work on the same one or two table segments: those stay in L2.
+template <int K, int HASH>
+__global__ void __launch_bounds__(256) k_insert_buckets(TableView t, BucketSink bs) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  __shared__ u64 pre[N_BUCKETS + 2];
+  __shared__ u32 tmp[TILE_THREADS / 32 + 1];
+  {
+    const u32 cnt = min(bs.cursor[threadIdx.x], bs.capb);
+    u32 total;
+    const u32 ex = block_excl_scan(cnt, tmp, total);   // chunk sizes keep the total below 2^32
+    pre[threadIdx.x] = ex;
+    if (threadIdx.x == 0) {
+      pre[N_BUCKETS] = total;
+      pre[N_BUCKETS + 1] = (u64)total + min(bs.cursor[N_BUCKETS], bs.ovf_cap);
+    }
+  }
+  __syncthreads();
+  const u64 T = pre[N_BUCKETS + 1];
+  u32 n_new = 0;
+  for (u64 g = (u64)blockIdx.x * blockDim.x + threadIdx.x; g < T; g += (u64)gridDim.x * blockDim.x) {
+    int lo = 0, hi = N_BUCKETS;                         // largest b with pre[b] <= g
+#pragma unroll
+    for (int s = 0; s < LOG_BUCKETS + 1; ++s) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (pre[mid] <= g) lo = mid; else hi = mid - 1;
+    }
+    const u64 at = (u64)lo * bs.capb + (g - pre[lo]);
+    Key<NW> key = load_key<NW>(bs.keys, at);
+    bool was_new;
+    const u64 s = table_upsert<NW>(t, key, store_hash<K, HASH>(key), was_new);
+    if (s != ~0ULL) {
+      atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].val, 1u);
+      n_new += was_new ? 1u : 0u;
+    }
+  }
+  n_new = warp_sum(n_new);
+  if ((threadIdx.x & 31) == 0 && n_new) atomicAdd(t.size, (u64)n_new);
+}
+
+
+// ======================================================================================================
+// Second level: table segments small enough for shared memory.
+//
+// L2-resident atomics top out near 25 G k-mers/s (profiles/r01_bucketed_l2.md): the table update itself
+// has to leave the L2 atomic units. A second 2^log_f-way scatter (same shape as the first, on the next
+// hash bits) cuts every coarse bucket into fine buckets whose table segment (<= 8192 slots) fits in
+// shared memory; one CTA then loads the segment, applies its fine bucket with shared-memory atomics,
+// and writes the segment back with coalesced 128-bit stores: the table crosses HBM once per sweep.
+// ======================================================================================================
+static constexpr int MAX_LOG_F = 11;
+static constexpr int FINE_ROUND = 2048;                   // keys per CTA round of the second scatter
+static constexpr u32 PERR_SPILL = 16u;                    // overflow region exhausted by segment spills (fatal)
+
+struct FineSink {
+  u64* keys;       // (N_BUCKETS << log_f) regions of capf keys
+  u32* cursor;     // one fill counter per region (may run past capf)
+  u32 capf;
+  u32 log_f;
+};
+
+template <int K, int HASH>
+__global__ void __launch_bounds__(TILE_THREADS)
+k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
+  static_assert(K <= 32, "segment path is built for one-word keys");
+  __shared__ u64 sorted[FINE_ROUND];
+  __shared__ u32 hist[1 << MAX_LOG_F], scan[1 << MAX_LOG_F], delta[1 << MAX_LOG_F];
+  __shared__ unsigned short sbid[FINE_ROUND];
+  __shared__ u32 cpre[N_BUCKETS + 1];
+  __shared__ u32 tmp[TILE_THREADS / 32 + 1];
+  constexpr int R = FINE_ROUND / TILE_THREADS;
+  const int t = threadIdx.x;
+  const u32 F = 1u << fs.log_f;
+  const u32 EPT = F >= TILE_THREADS ? F / TILE_THREADS : 1u;   // histogram entries per thread
+  const u32 my_cnt = min(bs.cursor[t], bs.capb);
+  u32 n_chunks;
+  {
+    const u32 ex = block_excl_scan((my_cnt + FINE_ROUND - 1) / FINE_ROUND, tmp, n_chunks);
+    cpre[t] = ex;
+    if (t == 0) cpre[N_BUCKETS] = n_chunks;
+  }
+  __syncthreads();
+  for (u32 c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+    int lo = 0, hi = N_BUCKETS - 1;                       // largest b with cpre[b] <= c and a non-empty bucket
+#pragma unroll
+    for (int s = 0; s < LOG_BUCKETS; ++s) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (cpre[mid] <= c) lo = mid; else hi = mid - 1;
+    }
+    const u32 b = (u32)lo;
+    const u32 first = (c - cpre[b]) * FINE_ROUND;
+    const u32 cnt_b = min(bs.cursor[b], bs.capb);
+    const u32 m = min((u32)FINE_ROUND, cnt_b - first);
+    const u64* src = bs.keys + (u64)b * bs.capb + first;
+    for (u32 f = t; f < F; f += TILE_THREADS) hist[f] = 0;
+    __syncthreads();
+    u64 key[R];
+    u32 fid[R], rank[R];
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+      const u32 i = q * TILE_THREADS + t;
+      fid[q] = BKT_NONE;
+      if (i < m) {
+        key[q] = __ldg(src + i);
+        Key<1> kk; kk.w[0] = key[q];
+        const u64 h = store_hash<K, HASH>(kk);
+        fid[q] = (u32)(h >> (64 - LOG_BUCKETS - fs.log_f)) & (F - 1);
+        rank[q] = atomicAdd(&hist[fid[q]], 1u);
+      }
+    }
+    __syncthreads();
+    {
+      u32 local = 0;
+      for (u32 e = 0; e < EPT; ++e) { const u32 f = t * EPT + e; if (f < F) local += hist[f]; }
+      u32 total;
+      u32 ex = block_excl_scan(local, tmp, total);
+      for (u32 e = 0; e < EPT; ++e) {
+        const u32 f = t * EPT + e;
+        if (f < F) {
+          const u32 cnt = hist[f];
+          scan[f] = ex;
+          if (cnt) delta[f] = atomicAdd(fs.cursor + ((u64)b << fs.log_f) + f, cnt) - ex;
+          ex += cnt;
+        }
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+      if (fid[q] != BKT_NONE) {
+        const u32 pos = scan[fid[q]] + rank[q];
+        sorted[pos] = key[q];
+        sbid[pos] = (unsigned short)fid[q];
+      }
+    }
+    __syncthreads();
+    for (u32 r = t; r < m; r += TILE_THREADS) {
+      const u32 f = sbid[r];
+      const u32 at = delta[f] + r;
+      if (at < fs.capf) {
+        fs.keys[(((u64)b << fs.log_f) + f) * fs.capf + at] = sorted[r];
+      } else {
+        const u32 o = atomicAdd(bs.cursor + N_BUCKETS, 1u);
+        if (o < bs.ovf_cap) bs.keys[(u64)N_BUCKETS * bs.capb + o] = sorted[r];
+        else atomicOr(perr, PERR_OVERFLOW);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// fine buckets -> table, one CTA per table segment resident in shared memory (K <= 31).
+// A probe that runs off the end of the segment "spills": the key is appended to the overflow region
+// and inserted afterwards by k_insert_overflow with global atomics, which continues the linear probe
+// into the next segment exactly as table_upsert would have.
+template <int K, int HASH>
+__global__ void __launch_bounds__(TILE_THREADS)
+k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, const u32 n_segs, u32* __restrict__ perr) {
+  static_assert(K <= 32, "segment path is built for one-word keys");
+  extern __shared__ __align__(16) unsigned char seg_raw[];
+  Slot<1>* seg = reinterpret_cast<Slot<1>*>(seg_raw);
+  const u32 SEG = 1u << log_seg;
+  const int tid = threadIdx.x;
+  u32 n_new = 0;
+  for (u32 s = blockIdx.x; s < n_segs; s += gridDim.x) {
+    const u32 cnt = min(fs.cursor[s], fs.capf);
+    if (cnt == 0) continue;                               // block-uniform
+    uint4* gseg = reinterpret_cast<uint4*>(reinterpret_cast<Slot<1>*>(t.slots) + ((u64)s << log_seg));
+    for (u32 i = tid; i < SEG; i += TILE_THREADS) reinterpret_cast<uint4*>(seg)[i] = gseg[i];
+    __syncthreads();
+    const u64* src = fs.keys + (u64)s * fs.capf;
+    for (u32 i0 = 0; i0 < cnt; i0 += 4 * TILE_THREADS) {
+      u64 kq[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const u32 i = i0 + q * TILE_THREADS + tid;
+        kq[q] = (i < cnt) ? __ldg(src + i) : KEY_EMPTY_TOP;
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const u64 key = kq[q];
+        if (key == KEY_EMPTY_TOP) continue;
+        Key<1> kk; kk.w[0] = key;
+        u32 li = (u32)(store_hash<K, HASH>(kk) >> t.shift) & (SEG - 1);
+        for (;;) {
+          u64 cur = seg[li].key;
+          if (cur == KEY_EMPTY_TOP) {
+            cur = atomicCAS(&seg[li].key, KEY_EMPTY_TOP, key);
+            if (cur == KEY_EMPTY_TOP) { ++n_new; cur = key; }
+          }
+          if (cur == key) { atomicAdd(&seg[li].val, 1u); break; }
+          if (++li == SEG) {
+            const u32 o = atomicAdd(bs.cursor + N_BUCKETS, 1u);
+            if (o < bs.ovf_cap) bs.keys[(u64)N_BUCKETS * bs.capb + o] = key;
+            else atomicOr(perr, PERR_SPILL);
+            break;
+          }
+        }
+      }
+    }
+    __syncthreads();
+    for (u32 i = tid; i < SEG; i += TILE_THREADS) gseg[i] = reinterpret_cast<const uint4*>(seg)[i];
+    __syncthreads();
+  }
+  n_new = warp_sum(n_new);
+  if ((tid & 31) == 0 && n_new) atomicAdd(t.size, (u64)n_new);
+}
+
+// the overflow region (bucket overflow + segment spills) -> table with global atomics
+template <int K, int HASH>
+__global__ void __launch_bounds__(256) k_insert_overflow(TableView t, BucketSink bs) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  const u64 n = min(bs.cursor[N_BUCKETS], bs.ovf_cap);
+  const u64 base = (u64)N_BUCKETS * bs.capb;
+  u32 n_new = 0;
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+    Key<NW> key = load_key<NW>(bs.keys, base + i);
+    bool was_new;
+    const u64 s = table_upsert<NW>(t, key, store_hash<K, HASH>(key), was_new);
+    if (s != ~0ULL) {
+      atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].val, 1u);
+      n_new += was_new ? 1u : 0u;
+    }
+  }
+  n_new = warp_sum(n_new);
+  if ((threadIdx.x & 31) == 0 && n_new) atomicAdd(t.size, (u64)n_new);
+}
+
+}  // namespace kmi

@@ -1,28 +1,8 @@
 // kmi_kernels.cuh — table, query, partition and utility kernels (sm_100a).
 #pragma once
-#include "kmi_table.cuh"
+#include "kmi_block.cuh"
 
 namespace kmi {
-
-template <int NW> __device__ __forceinline__ Key<NW> load_key(const u64* __restrict__ keys, u64 i) {
-  Key<NW> k;
-  if (NW == 1) {
-    k.w[0] = __ldg(keys + i);
-  } else {
-    const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>(keys) + i);
-    k.w[0] = v.x; k.w[NW - 1] = v.y;
-  }
-  return k;
-}
-template <int NW> __device__ __forceinline__ void store_key(u64* __restrict__ keys, u64 i, const Key<NW>& k) {
-  if (NW == 1) keys[i] = k.w[0];
-  else reinterpret_cast<ulonglong2*>(keys)[i] = make_ulonglong2(k.w[0], k.w[NW - 1]);
-}
-__device__ __forceinline__ u32 warp_sum(u32 v) {
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
-  return v;
-}
 
 // ---- table maintenance ---------------------------------------------------------------------
 template <int NW> __global__ void k_table_clear(Slot<NW>* __restrict__ slots, u64 n) {

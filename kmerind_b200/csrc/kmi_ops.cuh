@@ -10,10 +10,16 @@ namespace kmi {
 
 struct Ops {
   int K, NW, hash;
-  // parse (FASTQ). sink_kind 0: key stream, 1: straight into the table
+  // parse (FASTQ). sink_kind 0: key stream, 1: straight into the table, 2: hash-prefix buckets
   void (*fastq_kmers)(cudaStream_t, int sink_kind, const uint8_t* bytes, u64 n, u64 n_tiles, const u32* tile_lines,
-                      const u32* block_sums, KeySink sink, TableView table, u64* n_kmers, u32* perr, bool canon,
-                      bool nsplit, u64 tile_begin);
+                      const u32* block_sums, KeySink sink, TableView table, BucketSink bsink, u64* n_kmers, u32* perr,
+                      bool canon, bool nsplit, u64 tile_begin);
+  void (*scatter_keys)(cudaStream_t, const u64* keys, u64 n, BucketSink bsink, u32* perr, bool canon);
+  void (*insert_buckets)(cudaStream_t, TableView, BucketSink bsink, u64 n_hint);
+  // second level (one-word keys only; null for K > 32): fine scatter, shared-memory segment insert
+  void (*scatter_fine)(cudaStream_t, BucketSink bsink, FineSink fsink, u32* perr, u64 n_hint);
+  int (*insert_segments)(cudaStream_t, TableView, FineSink fsink, BucketSink bsink, u32 log_seg, u32 n_segs, u32* perr);
+  void (*insert_overflow)(cudaStream_t, TableView, BucketSink bsink);
   // parse (FASTA) to a key(+id) stream; wide_halo selects the 1 KiB halo variant
   void (*fasta_kmers)(cudaStream_t, bool wide_halo, const uint8_t* bytes, u64 n, u64 n_tiles, const u32* tile_enc_scanned,
                       const u32* enc_block_max, const u32* tile_runs, const u32* runs_block_sums, KeySink sink, u64* n_kmers,
@@ -49,15 +55,24 @@ struct OpsImpl {
   static constexpr int NW = (K <= 32 ? 1 : 2);
   typedef Slot<NW> S;
   static void fastq_kmers(cudaStream_t st, int sink_kind, const uint8_t* bytes, u64 n, u64 n_tiles, const u32* tile_lines,
-                          const u32* block_sums, KeySink sink, TableView table, u64* n_kmers, u32* perr, bool canon,
-                          bool nsplit, u64 tile_begin) {
+                          const u32* block_sums, KeySink sink, TableView table, BucketSink bsink, u64* n_kmers, u32* perr,
+                          bool canon, bool nsplit, u64 tile_begin) {
     if (n_tiles == 0) return;
     if (sink_kind == 0)
-      k_fastq_kmers<K, HASH, 0><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table,
+      k_fastq_kmers<K, HASH, 0><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table, bsink,
+                                                                          n_kmers, perr, canon, nsplit, tile_begin);
+    else if (sink_kind == 1)
+      k_fastq_kmers<K, HASH, 1><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table, bsink,
                                                                           n_kmers, perr, canon, nsplit, tile_begin);
     else
-      k_fastq_kmers<K, HASH, 1><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table,
+      k_fastq_kmers<K, HASH, 2><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table, bsink,
                                                                           n_kmers, perr, canon, nsplit, tile_begin);
+  }
+  static void scatter_keys(cudaStream_t st, const u64* keys, u64 n, BucketSink bsink, u32* perr, bool canon) {
+    if (n) k_scatter_keys<K, HASH><<<grid_for(n, TILE_THREADS * BktRound<NW>::R, 148u * 8u), TILE_THREADS, 0, st>>>(keys, n, bsink, perr, canon);
+  }
+  static void insert_buckets(cudaStream_t st, TableView t, BucketSink bsink, u64 n_hint) {
+    k_insert_buckets<K, HASH><<<grid_for(n_hint ? n_hint : 1, 256, 148u * 8u), 256, 0, st>>>(t, bsink);
   }
   static void fasta_kmers(cudaStream_t st, bool wide_halo, const uint8_t* bytes, u64 n, u64 n_tiles, const u32* tile_enc_scanned,
                           const u32* enc_block_max, const u32* tile_runs, const u32* runs_block_sums, KeySink sink,
@@ -80,6 +95,25 @@ struct OpsImpl {
   }
   static void rehash(cudaStream_t st, const void* old_slots, u64 n_old, TableView t) {
     k_rehash<K, HASH><<<grid_for(n_old, 256, 148u * 32u), 256, 0, st>>>(reinterpret_cast<const S*>(old_slots), n_old, t);
+  }
+  static void scatter_fine(cudaStream_t st, BucketSink bsink, FineSink fsink, u32* perr, u64 n_hint) {
+    if constexpr (NW == 1)
+      k_scatter_fine<K, HASH><<<grid_for(n_hint ? n_hint : 1, FINE_ROUND, 148u * 4u), TILE_THREADS, 0, st>>>(bsink, fsink, perr);
+  }
+  static int insert_segments(cudaStream_t st, TableView t, FineSink fsink, BucketSink bsink, u32 log_seg, u32 n_segs, u32* perr) {
+    if constexpr (NW == 1) {
+      const size_t smem = sizeof(Slot<1>) << log_seg;
+      if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(k_insert_segments<K, HASH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+      }
+      unsigned grid = n_segs < 148u * 64u ? n_segs : 148u * 64u;
+      k_insert_segments<K, HASH><<<grid, TILE_THREADS, smem, st>>>(t, fsink, bsink, log_seg, n_segs, perr);
+    }
+    return 0;
+  }
+  static void insert_overflow(cudaStream_t st, TableView t, BucketSink bsink) {
+    k_insert_overflow<K, HASH><<<148u * 4u, 256, 0, st>>>(t, bsink);
   }
   static void lookup(cudaStream_t st, TableView t, const u64* keys, u64 n, u64* vals, uint8_t* found, u64* slot_idx,
                      bool canon) {
@@ -126,7 +160,8 @@ struct OpsImpl {
   static Ops make() {
     Ops o;
     o.K = K; o.NW = NW; o.hash = HASH;
-    o.fastq_kmers = fastq_kmers; o.fasta_kmers = fasta_kmers; o.table_clear = table_clear; o.insert_keys = insert_keys; o.rehash = rehash;
+    o.fastq_kmers = fastq_kmers; o.scatter_keys = scatter_keys; o.insert_buckets = insert_buckets;
+    o.scatter_fine = scatter_fine; o.insert_segments = insert_segments; o.insert_overflow = insert_overflow; o.fasta_kmers = fasta_kmers; o.table_clear = table_clear; o.insert_keys = insert_keys; o.rehash = rehash;
     o.lookup = lookup; o.erase = erase; o.dump = dump; o.checksum = checksum; o.canonicalize = canonicalize;
     o.hash_keys = hash_keys; o.part_hist = part_hist; o.part_scatter = part_scatter; o.csr_scan_l1 = csr_scan_l1;
     o.csr_fill = csr_fill; o.log_filter = log_filter; o.zero_aux = zero_aux;

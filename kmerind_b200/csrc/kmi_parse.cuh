@@ -21,21 +21,9 @@
 // shared work list so that the expensive part (reverse complement, min, hash, sink) runs with
 // all lanes busy and the key stream is written coalesced.
 #pragma once
-#include "kmi_table.cuh"
+#include "kmi_bucket.cuh"
 
 namespace kmi {
-
-static constexpr int TILE_THREADS = 256;
-static constexpr int GROUP_BYTES = 16;
-static constexpr int TILE_BYTES = TILE_THREADS * GROUP_BYTES;  // 4096
-static constexpr int HALO_GROUPS = 4;                          // 64 bytes >= K-1 for K <= 63
-static constexpr int TILE_GROUPS = TILE_THREADS + HALO_GROUPS;
-
-// error bits reported by the parse kernels
-static constexpr u32 PERR_NO_AT = 1u;    // fastq_loader.hpp:393,419
-static constexpr u32 PERR_NO_PLUS = 2u;  // fastq_loader.hpp:435
-static constexpr u32 PERR_OVERFLOW = 4u; // output capacity exceeded
-static constexpr u32 PERR_HALO = 8u;     // FASTA: K-1 bases do not fit the halo (retry wider)
 
 // ---- byte-parallel classification of one 16-byte group ------------------------------------
 __device__ __forceinline__ u32 nib(u32 bytemask) {  // 0xFF/0x00 per byte -> 4 bits, byte 0 -> bit 0
@@ -94,36 +82,6 @@ __device__ __forceinline__ bool prev_is_eol(const uint8_t* __restrict__ bytes, u
 // skips every EOL char: reference src/io/file_loader.hpp:146-152)
 __device__ __forceinline__ u32 line_starts(u32 eol, bool prev_eol) {
   return (~eol) & ((eol << 1) | (prev_eol ? 1u : 0u)) & 0xFFFFu;
-}
-
-// block-wide exclusive scan of one u32 per thread (TILE_THREADS threads); returns the exclusive
-// prefix, total in `total`. `tmp` is TILE_THREADS/32 + 1 words of shared memory.
-__device__ __forceinline__ u32 block_excl_scan(u32 v, u32* tmp, u32& total) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  u32 inc = v;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    u32 o = __shfl_up_sync(0xffffffffu, inc, d);
-    if (lane >= d) inc += o;
-  }
-  if (lane == 31) tmp[warp] = inc;
-  __syncthreads();
-  if (warp == 0) {
-    u32 w = (lane < TILE_THREADS / 32) ? tmp[lane] : 0;
-    u32 winc = w;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      u32 o = __shfl_up_sync(0xffffffffu, winc, d);
-      if (lane >= d) winc += o;
-    }
-    if (lane < TILE_THREADS / 32) tmp[lane] = winc - w;
-    if (lane == TILE_THREADS / 32 - 1) tmp[TILE_THREADS / 32] = winc;
-  }
-  __syncthreads();
-  total = tmp[TILE_THREADS / 32];
-  u32 r = tmp[warp] + inc - v;
-  __syncthreads();
-  return r;
 }
 
 #ifdef KMI_SHARED_KERNELS  // non-template kernels: compiled once, in the API translation unit
@@ -267,12 +225,15 @@ struct KeySink {     // dense key (+id) stream
 // ---- pass B: FASTQ tile -> k-mers ------------------------------------------------------------------
 // SINK 0: write canonical (or forward) keys to sink.keys (block-contiguous, order of blocks free)
 // SINK 1: insert straight into the count table (val += 1), no key stream at all
+// SINK 2: scatter into the 256 hash-prefix buckets of kmi_bucket.cuh (the default build path)
 template <int K, int HASH, int SINK>
 __global__ void __launch_bounds__(TILE_THREADS)
 k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ tile_lines,
-              const u32* __restrict__ block_sums, KeySink sink, TableView table, u64* __restrict__ n_kmers,
-              u32* __restrict__ perr, const bool CANON, const bool NSPLIT, const u64 tile_begin) {
+              const u32* __restrict__ block_sums, KeySink sink, TableView table, BucketSink bsink,
+              u64* __restrict__ n_kmers, u32* __restrict__ perr, const bool CANON, const bool NSPLIT,
+              const u64 tile_begin) {
   constexpr int NW = (K <= 32 ? 1 : 2);
+  __shared__ BucketSmem<(SINK == 2 ? NW : 0)> s_bkt;
   __shared__ u32 s_codes[TILE_GROUPS + 1];
   __shared__ u32 s_flags[TILE_GROUPS + 1];
   __shared__ u32 s_aux[HALO_GROUPS * 2];       // halo: line-start masks / popcounts
@@ -376,6 +337,33 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   __syncthreads();
 
   // -- P5: dense loop over the tile's k-mers
+  if (SINK == 2) {
+    constexpr int R = BktRound<NW>::R;
+    BucketSmem<NW>& sm = reinterpret_cast<BucketSmem<NW>&>(s_bkt);
+    for (u32 c0 = 0; c0 < total; c0 += TILE_THREADS * R) {   // block-uniform trip count
+      Key<NW> key[R];
+      u32 bkt[R];
+#pragma unroll
+      for (int q = 0; q < R; ++q) {
+        const u32 r = c0 + q * TILE_THREADS + t;
+        bkt[q] = BKT_NONE;
+        if (r < total) {
+          const u32 pos = s_list[r];
+          const int gi = pos >> 4, j = pos & 15;
+          u32 c5[5];
+#pragma unroll
+          for (int w = 0; w < 5; ++w) c5[w] = s_codes[min(gi + w, TILE_GROUPS)];
+          key[q] = extract_kmer<K>(c5, j);
+          if (CANON) key[q] = canonical<K>(key[q]);
+          const u64 h = store_hash<K, HASH>(key[q]);
+          bkt[q] = bucket_of(h);
+          hll_update(bsink.hll, h);
+        }
+      }
+      bucket_round<NW>(bsink, sm, key, bkt, perr);
+    }
+    return;
+  }
   u32 n_new = 0;
   for (u32 r = t; r < total; r += TILE_THREADS) {
     const u32 pos = s_list[r];

@@ -1,7 +1,7 @@
 // kmi_table.cuh — open-addressing k-mer table in HBM and its kernels (sm_100a).
 // Replaces the local half of dsc::counting_densehash_map / densehash_multimap
 // (reference src/containers/densehash_map.hpp:928-1229,2015-2400 over google::dense_hash_map):
-// power-of-two slots, the reference's store hash picks the home slot, linear probing inside HBM
+// power-of-two slots, the reference's store hash picks the home slot (its top log2(slots) bits), linear probing inside HBM
 // sectors (one 16-byte slot per K<=31 key, one 32-byte slot per K<=63 key, so a probe touches a
 // single 32-byte sector), claim by 64/128-bit CAS on the key, count by a fire-and-forget RED.
 #pragma once
@@ -16,6 +16,8 @@ template <> struct alignas(32) Slot<2> { u64 lo; u64 hi; u32 val; u32 aux; u64 p
 struct TableView {
   void* slots;
   u64 mask;        // slots - 1
+  u32 shift;       // 64 - log2(slots): home slot = store_hash >> shift (TOP bits, so that a hash
+                   // prefix names a contiguous table segment for any capacity: kmi_bucket.cuh)
   u64* size;       // device counter: occupied (live) keys
   u32* error;      // device flag: 1 = probe limit hit (table full)
 };
@@ -62,7 +64,7 @@ template <> __device__ __forceinline__ bool slot_claim<2>(Slot<2>* s, const Key<
 template <int NW>
 __device__ __forceinline__ u64 table_upsert(const TableView& t, const Key<NW>& key, u64 hash, bool& was_new) {
   Slot<NW>* slots = reinterpret_cast<Slot<NW>*>(t.slots);
-  u64 i = hash & t.mask;
+  u64 i = hash >> t.shift;
   was_new = false;
   for (u64 probes = 0; probes <= t.mask; ++probes) {
     Key<NW> cur = slot_key<NW>(slots + i);
@@ -82,7 +84,7 @@ __device__ __forceinline__ u64 table_upsert(const TableView& t, const Key<NW>& k
 template <int NW>
 __device__ __forceinline__ u64 table_find(const TableView& t, const Key<NW>& key, u64 hash) {
   const Slot<NW>* slots = reinterpret_cast<const Slot<NW>*>(t.slots);
-  u64 i = hash & t.mask;
+  u64 i = hash >> t.shift;
   for (u64 probes = 0; probes <= t.mask; ++probes) {
     Key<NW> cur = slot_key<NW>(slots + i);
     if (key_eq<NW>(cur, key)) return i;

@@ -189,18 +189,22 @@ def test_count_index_equals_reference_dump(k, fx):
 
 @pytest.mark.parametrize("name", ["test.medium.fastq", "test.unitiqs.fastq", "natural.withN.fastq"])
 @pytest.mark.parametrize("k", (31, 63))
-def test_count_index_fused_build_equals_oracle(name, k):
+@pytest.mark.parametrize("path", (1, 2))
+def test_count_index_fused_build_equals_oracle(name, k, path):
+    """path 1: direct atomics from the parser; path 2: through the hash-prefix buckets."""
     buf = ou.read_fixture(name)
     for nsplit in (False, True):
         keys, _, _ = ou.fastq_kmers(buf, k, nsplit=nsplit)
         wk, wc = ou.count_sorted(keys, k)
         with kb.CountIndex(k, nsplit=nsplit) as idx:  # no reserve: exercises growth + rehash
+            idx.set_build_path(path)
             n = idx.build_fastq(buf)
             gk, gc = idx.sorted_dump()
             assert n == len(keys)
             assert np.array_equal(gk, wk) and np.array_equal(gc, wc)
             # insert(vector<Kmer>) path gives the same contents, and doubles every count when repeated
             with kb.CountIndex(k, nsplit=nsplit) as idx2:
+                idx2.set_build_path(path)
                 fwd, _, _ = ou.fastq_kmers(buf, k, canonical=False, nsplit=nsplit)
                 idx2.insert(fwd)
                 assert idx2.checksum() == idx.checksum()
@@ -309,7 +313,8 @@ def test_synthetic_generator_matches_host_twin():
         assert np.array_equal(t.cpu().numpy(), want)
 
 
-def test_synthetic_build_parity_and_properties():
+@pytest.mark.parametrize("path", (0, 1, 2, 3))
+def test_synthetic_build_parity_and_properties(path):
     """A 30x synthetic slice (the bench workload's shape, smaller): dump equality with the oracle,
     then size-independent properties: sum of counts == k-mers, chunked build == one-shot build."""
     n_reads, G = 60000, 300000
@@ -317,25 +322,59 @@ def test_synthetic_build_parity_and_properties():
     keys, _, reads = ou.fastq_kmers(buf, 31)
     assert reads == n_reads and len(keys) == n_reads * 120
     wk, wc = ou.count_sorted(keys, 31)
+    seg = path != 3   # path 3: bucketed with L2 atomics instead of shared-memory segments
+    path = min(path, 2)
     with kb.CountIndex(31, hash=kb.HASH_FARM, reserve=len(wk)) as idx:
+        idx.set_build_path(path)
+        idx.set_segment_insert(seg)
         assert idx.build_fastq(buf) == len(keys)
         gk, gc = idx.sorted_dump()
         assert np.array_equal(gk, wk) and np.array_equal(gc, wc)
         ck = idx.checksum()
         assert ck[1] == len(keys)
+        assert idx.table_info()["slots"] * 0.7 >= len(wk)
     with kb.CountIndex(31, hash=kb.HASH_FARM) as idx:  # two record-aligned halves, growth on demand
+        idx.set_build_path(path)
+        idx.set_segment_insert(seg)
         half = (n_reads // 2) * 317
         idx.build_fastq(buf[:half])
         idx.build_fastq(buf[half:])
         assert idx.checksum() == ck
 
 
-def test_k63_count_index_on_synthetic():
+@pytest.mark.parametrize("path", (1, 2))
+def test_k63_count_index_on_synthetic(path):
     buf = ou.synth_fastq(1000, 20000, 150, 100000, 3, 5000, 500)
     for nsplit in (False, True):
         keys, _, _ = ou.fastq_kmers(buf, 63, nsplit=nsplit)
         wk, wc = ou.count_sorted(keys, 63)
         with kb.CountIndex(63, nsplit=nsplit) as idx:
+            idx.set_build_path(path)
             assert idx.build_fastq(buf) == len(keys)
             gk, gc = idx.sorted_dump()
             assert np.array_equal(gk, wk) and np.array_equal(gc, wc)
+
+
+@pytest.mark.parametrize("frac", (0.1, 0.97))
+def test_bucketed_build_survives_key_skew(frac):
+    """A heavy-hitter key (poly-A reads) overflows its hash-prefix bucket: at 10 % the spill goes to the
+    overflow region, at 97 % that is exhausted too and the round is redone with direct atomics. Either
+    way the index equals the oracle's."""
+    n_reads = 40000
+    buf = ou.synth_fastq(0, n_reads, 150, 200000, 7, 5000, 0).copy()
+    recs = buf.reshape(n_reads, 317)
+    rng = np.random.default_rng(5)
+    hot = rng.random(n_reads) < frac
+    recs[hot, 13:163] = ord("A")
+    keys, _, _ = ou.fastq_kmers(buf, 31)
+    wk, wc = ou.count_sorted(keys, 31)
+    with kb.CountIndex(31, hash=kb.HASH_FARM) as idx:
+        idx.set_build_path(2)
+        assert idx.build_fastq(buf) == len(keys)
+        gk, gc = idx.sorted_dump()
+        assert np.array_equal(gk, wk) and np.array_equal(gc, wc)
+    with kb.CountIndex(31, hash=kb.HASH_FARM) as idx:  # the same through insert(vector<Kmer>)
+        idx.set_build_path(2)
+        idx.insert(keys)
+        gk, gc = idx.sorted_dump()
+        assert np.array_equal(gk, wk) and np.array_equal(gc, wc)

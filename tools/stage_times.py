@@ -45,7 +45,6 @@ def ins():
 
 
 t_clear = timed(lambda: idx.clear())
-t_ins = timed(ins) - t_clear
 
 
 def fused():
@@ -53,10 +52,14 @@ def fused():
     idx.build_fastq_dev(text.data_ptr(), nbytes)
 
 
-t_fused = timed(fused) - t_clear
-st = idx.last_stage_ms()
-info = idx.table_info()
-print("reads %d kmers %d distinct %d slots %d" % (n_reads, n_kmers, idx.size(), info["slots"]))
-print("parse->keys (incl. scan) %.3f ms | clear %.3f ms | insert(keys) %.3f ms | fused build %.3f ms (scan %.3f, kernel %.3f)"
-      % (t_parse, t_clear, t_ins, t_fused, st[0], st[1]))
-print("rates: parse %.2f G/s, insert %.2f G/s, fused %.2f G/s" % (n_kmers / t_parse / 1e6, n_kmers / t_ins / 1e6, n_kmers / t_fused / 1e6))
+print("reads %d kmers %d reserve %d" % (n_reads, n_kmers, int(frac * n_kmers)))
+print("parse->keys (incl. scan) %.3f ms | clear %.3f ms" % (t_parse, t_clear))
+for path, name in ((1, "direct"), (3, "bucketed-L2"), (2, "bucketed-smem")):
+    idx.set_build_path(min(path, 2))
+    idx.set_segment_insert(path != 3)
+    t_ins = timed(ins) - t_clear
+    t_fused = timed(fused) - t_clear
+    st = idx.last_stage_ms()
+    info = idx.table_info()
+    print("[%s] distinct %d slots %d | insert(keys) %.3f ms (%.2f G/s) | build %.3f ms (%.2f G/s): scan %.3f, parse(+scatter) %.3f, insert %.3f"
+          % (name, idx.size(), info["slots"], t_ins, n_kmers / t_ins / 1e6, t_fused, n_kmers / t_fused / 1e6, st[0], st[1], st[2]))
