@@ -37,7 +37,10 @@ READS_1GBP = 6666667
 GENOME_1GBP = 33333333               # 30x
 SEED = 1
 ERR_PPM = 5000
-# algorithmic bytes per k-mer of the fused text->table kernel: text R/n + slot read 12 + slot write 12
+# algorithmic bytes per k-mer, kernels of the bucketed single-GPU build
+ALG_BYTES = {"k_fastq_kmers<31,farm,sink=buckets> (text -> 256 hash-prefix buckets)": REC / KMERS_PER_READ + 8.0,
+             "k_scatter_fine<31,farm> (buckets -> table-segment buckets)": 16.0,
+             "k_insert_segments<31,farm> (segment buckets -> table, shared-memory segments)": 32.0}
 ALG_BYTES_FUSED = REC / KMERS_PER_READ + 24.0
 # unfused (multi-GPU) pipeline per SURVEY.md §8d: S1-S3 10.6 + S4 24 + S5 32
 ALG_BYTES_SHARDED = (REC + 8.0 * KMERS_PER_READ) / KMERS_PER_READ + 24.0 + 32.0
@@ -191,7 +194,7 @@ def run_gpu_arm(args):
     text = torch.empty(nbytes + 64, dtype=torch.uint8, device=device)
     kb.synth_fastq_dev(local_rank, text.data_ptr(), first_read, n_reads, READ_LEN, genome, SEED, ERR_PPM, 0)
     torch.cuda.synchronize()
-    reserve = int(os.environ.get("KMI_BENCH_RESERVE", str(int(0.30 * n_kmers_rank))))
+    reserve = int(os.environ.get("KMI_BENCH_RESERVE", str(int(0.20 * n_kmers_rank))))
 
     def barrier():
         torch.cuda.synchronize()
@@ -225,13 +228,12 @@ def run_gpu_arm(args):
     l0 = launches_of()
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    fused_ms, scan_ms = [], []
+    kern_ms = []
     e0.record()
     for _ in range(args.steps):
         step()
         if world == 1:
-            ms = idx.last_stage_ms()
-            scan_ms.append(ms[0]); fused_ms.append(ms[1])
+            kern_ms.append(idx.last_kernel_ms())
         else:
             for k_, v_ in idx.stage_ms.items():
                 stage.setdefault(k_, []).append(v_)
@@ -285,11 +287,26 @@ def run_gpu_arm(args):
 
     peak, peak_kind = measured_peaks()
     if world == 1:
-        k_ms = float(np.mean(fused_ms))
-        achieved = ALG_BYTES_FUSED * n_kmers_rank / (k_ms * 1e-3) / 1e9
-        roofline = {"bound": "hbm", "kernel": "k_fastq_kmers<31,farm,sink=table> (fused text->table)", "achieved": achieved,
-                    "peak": peak, "peak_source": peak_kind, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                    "alg_bytes_per_kmer": ALG_BYTES_FUSED, "kernel_ms_per_step": k_ms, "scan_ms_per_step": float(np.mean(scan_ms))}
+        km = np.mean(np.array(kern_ms), axis=0)   # [whole build, parse+scatter, fine scatter, insert, overflow]
+        kernels = []
+        for (name, alg), ms in zip(ALG_BYTES.items(), km[1:4]):
+            ach = alg * n_kmers_rank / (max(float(ms), 1e-6) * 1e-3) / 1e9
+            kernels.append({"kernel": name, "ms_per_step": float(ms), "alg_bytes_per_kmer": alg, "achieved": ach, "frac": ach / peak})
+        dom = max(kernels, key=lambda k_: k_["ms_per_step"])
+        # traffic: dram bytes read+written per launch of the dominant kernel, from profiles/ (ncu --set full), if recorded
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            try:
+                traffic = json.load(open(tp)).get(dom["kernel"].split("<")[0])
+            except Exception:
+                traffic = None
+        roofline = {"bound": "hbm", "kernel": dom["kernel"], "achieved": dom["achieved"], "peak": peak, "peak_source": peak_kind,
+                    "unit": "GB/s", "frac": dom["frac"], "traffic": traffic, "alg_bytes_per_kmer": dom["alg_bytes_per_kmer"],
+                    "kernel_ms_per_step": dom["ms_per_step"], "build_ms_per_step": float(km[0]), "kernels": kernels,
+                    "whole_build": {"alg_bytes_per_kmer": ALG_BYTES_FUSED,
+                                    "achieved": ALG_BYTES_FUSED * n_kmers_rank / (float(km[0]) * 1e-3) / 1e9,
+                                    "frac": ALG_BYTES_FUSED * n_kmers_rank / (float(km[0]) * 1e-3) / 1e9 / peak}}
     else:
         smean = {k_: float(np.mean(v_)) for k_, v_ in stage.items()}
         k_ms = smean.get("insert", 0.0)
@@ -304,7 +321,7 @@ def run_gpu_arm(args):
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "u64", "data": "synthetic",
                 "config": {"workload": "CountIndex K=31 canonical, synthetic %.2f Gbp of 150 bp reads per GPU (30x, 0.5%% subst.), %s"
-                                       % (n_reads * READ_LEN / 1e9, "1xB200 fused text->table" if world == 1 else
+                                       % (n_reads * READ_LEN / 1e9, "1xB200 text->buckets->segment insert" if world == 1 else
                                           "%dxB200 parse->partition->NCCL all-to-all->insert" % world),
                            "k": K, "read_len": READ_LEN, "reads_per_gpu": n_reads, "text_bytes_per_gpu": nbytes,
                            "kmers_per_gpu": n_kmers_rank, "hash": "farm (dist+store)", "distinct_keys": distinct,

@@ -154,6 +154,10 @@ int kmi_launch_count(kmi_index* idx, uint64_t* n);
 /* device time (ms) of the stages of the last build_* call, in the reference's BL_BENCH stage
  * names order: [0] scan (record boundaries), [1] parse+insert (fused) or parse, [2] insert */
 int kmi_last_stage_ms(kmi_index* idx, float* ms3);
+/* device time (ms, CUDA events on the index's stream) of the kernels of the last build_fastq* call:
+ * [0] whole build, [1] parse (+ bucket scatter), [2] fine scatter, [3] table insert (shared-memory
+ * segments or L2 atomics), [4] overflow / spill insert. [2]-[4] are 0 on the direct path. */
+int kmi_last_kernel_ms(kmi_index* idx, float* ms5);
 
 /* ---- synthetic workload (same bytes as oracle/kmi_oracle.c kmio_synth_fastq) - */
 size_t kmi_synth_record_bytes(uint32_t read_len);

@@ -76,7 +76,7 @@ def load_library(build_if_missing=False):
         "kmi_count_dev": [_P, _P, _SZ, _P], "kmi_find_dev": [_P, _P, _SZ, _P, _P],
         "kmi_local_size": [_P, _P], "kmi_num_keys": [_P, _P], "kmi_dump": [_P, _P, _P, _SZ, _P],
         "kmi_checksum": [_P, _P, _P], "kmi_table_info": [_P, _P, _P, _P], "kmi_launch_count": [_P, _P],
-        "kmi_last_stage_ms": [_P, _P],
+        "kmi_last_stage_ms": [_P, _P], "kmi_last_kernel_ms": [_P, _P],
         "kmi_synth_fastq_dev": [ctypes.c_int, _P, _U64, _U64, ctypes.c_uint32, _U64, _U64, ctypes.c_uint32,
                                 ctypes.c_uint32],
     }
@@ -94,7 +94,7 @@ EXPORTED_SYMBOLS = (
     "kmi_parse_fastq_dev", "kmi_parse_fasta_dev", "kmi_canonicalize_dev", "kmi_hash_dev",
     "kmi_partition_dev", "kmi_insert", "kmi_insert_dev", "kmi_count", "kmi_find", "kmi_find_positions",
     "kmi_erase", "kmi_count_dev", "kmi_find_dev", "kmi_local_size", "kmi_num_keys", "kmi_dump",
-    "kmi_checksum", "kmi_table_info", "kmi_launch_count", "kmi_last_stage_ms",
+    "kmi_checksum", "kmi_table_info", "kmi_launch_count", "kmi_last_stage_ms", "kmi_last_kernel_ms",
     "kmi_synth_record_bytes", "kmi_synth_fastq_dev",
 )
 
@@ -297,6 +297,11 @@ class Index:
     def last_stage_ms(self):
         ms = (ctypes.c_float * 3)()
         _check(self._lib.kmi_last_stage_ms(self._h, ms))
+        return [float(x) for x in ms]
+
+    def last_kernel_ms(self):
+        ms = (ctypes.c_float * 5)()
+        _check(self._lib.kmi_last_kernel_ms(self._h, ms))
         return [float(x) for x in ms]
 
     def set_build_path(self, path):

@@ -62,7 +62,7 @@ struct DevBuf {
 };
 
 // device counters block
-enum { CTR_SIZE = 0, CTR_NKMERS = 1, CTR_CURSOR = 2, CTR_CK0 = 3, CTR_CK1 = 4, CTR_REMOVED = 5, CTR_ERR = 6, CTR_PERR = 7, CTR_N = 8 };
+enum { CTR_SIZE = 0, CTR_NKMERS = 1, CTR_CURSOR = 2, CTR_CK0 = 3, CTR_CK1 = 4, CTR_REMOVED = 5, CTR_ERR = 6, CTR_PERR = 7, CTR_CARRY = 8, CTR_N = 10 };
 
 // bkt_meta layout (u32 words): cursors [0, N_BUCKETS], HLL registers from META_HLL
 enum { META_HLL = 512, META_WORDS = META_HLL + HLL_M };
@@ -98,7 +98,12 @@ struct kmi_index {
   u64 launches = 0;
   float stage_ms[3] = {0, 0, 0};
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-  float scatter_ms = 0;    // parse+scatter share of the last bucketed build
+  float scatter_ms = 0;
+  cudaEvent_t kev[4] = {nullptr, nullptr, nullptr, nullptr};  // around the kernels of bucket_commit
+  bool kev_pending = false;
+  float kernel_ms[5] = {0, 0, 0, 0, 0};  // last build: total, parse+scatter, fine scatter, segment/L2 insert, overflow insert
+  cudaStream_t copy_stream = nullptr;        // H2D copies of the pipelined host-pointer build
+  std::vector<cudaEvent_t> copy_events;    // parse+scatter share of the last bucketed build
 
   TableView view() const {
     TableView t;
@@ -225,6 +230,7 @@ extern "C" int kmi_create(const kmi_config* cfg, kmi_index** out) {
   if (e != cudaSuccess) { delete idx; return fail(KMI_ERR_CUDA, "cudaMalloc counters: %s", cudaGetErrorString(e)); }
   cudaMemset(idx->ctr, 0, sizeof(u64) * CTR_N);
   for (int i = 0; i < 6; ++i) cudaEventCreate(&idx->ev[i]);
+  for (int i = 0; i < 4; ++i) cudaEventCreate(&idx->kev[i]);
   *out = idx;
   if (cfg->reserve) {
     int r = kmi_reserve(idx, cfg->reserve);
@@ -244,6 +250,9 @@ extern "C" void kmi_destroy(kmi_index* idx) {
                     &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 6; ++i) if (idx->ev[i]) cudaEventDestroy(idx->ev[i]);
+  for (int i = 0; i < 4; ++i) if (idx->kev[i]) cudaEventDestroy(idx->kev[i]);
+  for (cudaEvent_t e : idx->copy_events) cudaEventDestroy(e);
+  if (idx->copy_stream) cudaStreamDestroy(idx->copy_stream);
   delete idx;
 }
 
@@ -325,6 +334,17 @@ static double hll_estimate(const u32* reg) {
   return e;
 }
 
+// add the kernel times of the last bucket_commit (its events have completed: call after a sync)
+static void harvest_commit_times(kmi_index* idx) {
+  if (!idx->kev_pending) return;
+  float a = 0, b = 0, c = 0;
+  cudaEventElapsedTime(&a, idx->kev[0], idx->kev[1]);
+  cudaEventElapsedTime(&b, idx->kev[1], idx->kev[2]);
+  cudaEventElapsedTime(&c, idx->kev[2], idx->kev[3]);
+  idx->kernel_ms[2] += a; idx->kernel_ms[3] += b; idx->kernel_ms[4] += c;
+  idx->kev_pending = false;
+}
+
 // one synchronisation per round: counters + HLL registers
 static int bucket_readback(kmi_index* idx, const BucketSink& bs, u64* host_ctr, std::vector<u32>& reg) {
   reg.resize(HLL_M);
@@ -332,6 +352,7 @@ static int bucket_readback(kmi_index* idx, const BucketSink& bs, u64* host_ctr, 
   CU(cudaMemcpyAsync(host_ctr, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
   CU(cudaMemcpyAsync(idx->h_cursor, bs.cursor, sizeof(u32) * (N_BUCKETS + 1), cudaMemcpyDeviceToHost, idx->stream));
   CU(cudaStreamSynchronize(idx->stream));
+  harvest_commit_times(idx);
   return KMI_OK;
 }
 
@@ -359,6 +380,7 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
     FineSink fs;
     fs.log_f = log_f;
     bool fine_ok = true;
+    CU(cudaEventRecord(idx->kev[0], idx->stream));
     if (log_f == 0) {
       fs.keys = bs.keys; fs.cursor = bs.cursor; fs.capf = bs.capb;
     } else {
@@ -380,15 +402,24 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
       }
     }
     if (fine_ok) {
+      CU(cudaEventRecord(idx->kev[1], idx->stream));
       int e = idx->ops->insert_segments(idx->stream, idx->view(), fs, bs, (u32)log_seg, (u32)n_regions,
                                         reinterpret_cast<u32*>(idx->ctr + CTR_PERR));
       if (e) return fail(KMI_ERR_CUDA, "segment kernel configuration: %s", cudaGetErrorString((cudaError_t)e));
+      CU(cudaEventRecord(idx->kev[2], idx->stream));
       idx->ops->insert_overflow(idx->stream, idx->view(), bs);
+      CU(cudaEventRecord(idx->kev[3], idx->stream));
+      idx->kev_pending = true;
       idx->launches += 2;
       return KMI_OK;
     }
   }
+  CU(cudaEventRecord(idx->kev[0], idx->stream));
+  CU(cudaEventRecord(idx->kev[1], idx->stream));
   idx->ops->insert_buckets(idx->stream, idx->view(), bs, n_keys);
+  CU(cudaEventRecord(idx->kev[2], idx->stream));
+  CU(cudaEventRecord(idx->kev[3], idx->stream));
+  idx->kev_pending = true;
   idx->launches++;
   return KMI_OK;
 }
@@ -420,20 +451,31 @@ static int insert_keys_bucketed(kmi_index* idx, const u64* d_keys, size_t n, boo
 }
 
 // ---- record boundaries (pass A + scan), shared by parse and fused build ------------------------
-static int fastq_scan(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64* n_tiles_out) {
+static int fastq_scan_alloc(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64* n_tiles_out) {
   if ((reinterpret_cast<uintptr_t>(d_bytes) & 15) != 0) return fail(KMI_ERR_ARG, "device text buffer must be 16-byte aligned");
   u64 n_tiles = (n + TILE_BYTES - 1) / TILE_BYTES;
   *n_tiles_out = n_tiles;
   if (n_tiles == 0) return KMI_OK;
   if (n_tiles > 0x7fffffffULL) return fail(KMI_ERR_ARG, "block of %zu bytes too large for one call (max 8 TiB)", n);
-  u64 n_blocks = (n_tiles + 1023) / 1024;
   OK(idx->tile_lines.ensure(sizeof(u32) * n_tiles));
-  OK(idx->block_sums.ensure(sizeof(u32) * n_blocks));
-  k_fastq_count_lines<<<(unsigned)n_tiles, TILE_THREADS, 0, idx->stream>>>(d_bytes, n, idx->tile_lines.as<u32>());
-  k_scan_l1<<<(unsigned)n_blocks, 1024, 0, idx->stream>>>(idx->tile_lines.as<u32>(), n_tiles, idx->block_sums.as<u32>());
-  k_scan_tiles<<<1, 1024, 0, idx->stream>>>(idx->block_sums.as<u32>(), n_blocks);
+  OK(idx->block_sums.ensure(sizeof(u32) * ((n_tiles + 1023) / 1024)));
+  OK(zero_ctr(idx, CTR_CARRY));
+  return KMI_OK;
+}
+// line starts of tiles [t0, t1) (t0 a multiple of 1024) -> per-tile prefixes; the running total of
+// earlier ranges is carried in CTR_CARRY so that ranges can be scanned as their bytes arrive
+static int fastq_scan_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64 t0, u64 t1) {
+  if (t1 <= t0) return KMI_OK;
+  const u64 nt = t1 - t0, nb = (nt + 1023) / 1024;
+  k_fastq_count_lines<<<(unsigned)nt, TILE_THREADS, 0, idx->stream>>>(d_bytes, n, idx->tile_lines.as<u32>(), (u32)t0);
+  k_scan_l1<<<(unsigned)nb, 1024, 0, idx->stream>>>(idx->tile_lines.as<u32>() + t0, nt, idx->block_sums.as<u32>() + t0 / 1024);
+  k_scan_tiles<<<1, 1024, 0, idx->stream>>>(idx->block_sums.as<u32>() + t0 / 1024, nb, reinterpret_cast<u32*>(idx->ctr + CTR_CARRY));
   idx->launches += 3;
   return KMI_OK;
+}
+static int fastq_scan(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64* n_tiles_out) {
+  OK(fastq_scan_alloc(idx, d_bytes, n, n_tiles_out));
+  return fastq_scan_range(idx, d_bytes, n, 0, *n_tiles_out);
 }
 static int parse_error(u64 perr) {
   if (perr & PERR_NO_AT) return fail(KMI_ERR_FORMAT, "malformed FASTQ: missing @ on first line of a record");
@@ -461,7 +503,7 @@ extern "C" int kmi_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_
                         idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0,
                         idx->cfg.nsplit != 0, 0);
   idx->launches++;
-  u64 host[8];
+  u64 host[CTR_N];
   CU(cudaMemcpyAsync(host, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
   CU(cudaStreamSynchronize(idx->stream));
   if (n_kmers) *n_kmers = host[CTR_NKMERS];
@@ -488,34 +530,75 @@ static int build_fastq_direct(kmi_index* idx, const uint8_t* d_bytes, size_t n, 
   return KMI_OK;
 }
 
-// S1-S5 through the hash-prefix buckets: text -> buckets -> table, at most 4 GiB of text per round
-static int build_fastq_bucketed(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64 n_tiles) {
+// S1-S5 through the hash-prefix buckets, in rounds: [H2D copy] -> line scan -> parse + scatter ->
+// (HLL read-back, table sizing) -> fine scatter -> segment insert. With `host_src` the round's bytes
+// are copied into d_bytes on the copy stream while the previous round computes, so the PCIe transfer
+// hides the whole build except the last round. A round's last tile needs 64 bytes of the next round
+// (k-mer halo), so it is parsed with the next round.
+struct CopyGuard {  // never return while a copy from the caller's memory is in flight
+  cudaStream_t s;
+  ~CopyGuard() { if (s) cudaStreamSynchronize(s); }
+};
+static int build_fastq_bucketed(kmi_index* idx, uint8_t* d_bytes, size_t n, u64 n_tiles, const uint8_t* host_src) {
+  if (n_tiles == 0) return KMI_OK;
   const u64 MAX_TILES = (2 * BUCKET_MAX_KEYS) / TILE_BYTES;
-  const u64 n_rounds = (n_tiles + MAX_TILES - 1) / MAX_TILES;
-  const u64 per_round = (n_tiles + n_rounds - 1) / n_rounds;
+  u64 per_round;
+  if (host_src) {
+    per_round = std::min<u64>(std::max<u64>(n_tiles / 8, (64u << 20) / TILE_BYTES), MAX_TILES);
+  } else {
+    const u64 n_rounds = (n_tiles + MAX_TILES - 1) / MAX_TILES;
+    per_round = (n_tiles + n_rounds - 1) / std::max<u64>(n_rounds, 1);
+  }
+  per_round = (per_round + 1023) / 1024 * 1024;  // the two-level line scan works in blocks of 1024 tiles
+  const u64 n_rounds = (n_tiles + per_round - 1) / per_round;
+  CopyGuard guard{nullptr};
+  std::vector<cudaEvent_t> copied;
+  if (host_src) {
+    if (!idx->copy_stream) CU(cudaStreamCreateWithFlags(&idx->copy_stream, cudaStreamNonBlocking));
+    guard.s = idx->copy_stream;
+    // the staging buffer may still be in use by earlier work on the compute stream
+    CU(cudaEventRecord(idx->ev[3], idx->stream));
+    CU(cudaStreamWaitEvent(idx->copy_stream, idx->ev[3], 0));
+    while (idx->copy_events.size() < n_rounds) {
+      cudaEvent_t e;
+      CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      idx->copy_events.push_back(e);
+    }
+    for (u64 r = 0; r < n_rounds; ++r) {
+      const u64 b0 = r * per_round * TILE_BYTES, b1 = std::min<u64>(n, (r + 1) * per_round * TILE_BYTES);
+      CU(cudaMemcpyAsync(d_bytes + b0, host_src + b0, b1 - b0, cudaMemcpyHostToDevice, idx->copy_stream));
+      CU(cudaEventRecord(idx->copy_events[r], idx->copy_stream));
+    }
+  }
   KeySink nosink; nosink.keys = nullptr; nosink.ids = nullptr; nosink.cap = 0; nosink.cursor = nullptr;
   std::vector<u32> reg;
   u64 kmers_before = 0;
-  for (u64 tile = 0; tile < n_tiles; tile += per_round) {
-    const u64 tiles = std::min(per_round, n_tiles - tile);
+  for (u64 r = 0; r < n_rounds; ++r) {
+    const u64 t0 = r * per_round, t1 = std::min(n_tiles, t0 + per_round);
+    const bool last = r + 1 == n_rounds;
+    if (host_src) CU(cudaStreamWaitEvent(idx->stream, idx->copy_events[r], 0));
+    OK(fastq_scan_range(idx, d_bytes, n, t0, t1));
+    const u64 p0 = (host_src && r > 0) ? t0 - 1 : t0;
+    const u64 p1 = (host_src && !last) ? t1 - 1 : t1;
+    const u64 tiles = p1 - p0;
     BucketSink bs;
     OK(bucket_prepare(idx, tiles * TILE_BYTES / 2 + 1, &bs));
     CU(cudaEventRecord(idx->ev[4], idx->stream));
     idx->ops->fastq_kmers(idx->stream, 2, d_bytes, n, tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), nosink,
                           idx->view(), bs, idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR),
-                          idx->cfg.canonical != 0, idx->cfg.nsplit != 0, tile);
+                          idx->cfg.canonical != 0, idx->cfg.nsplit != 0, p0);
     idx->launches++;
     CU(cudaEventRecord(idx->ev[5], idx->stream));
     u64 host[CTR_N];
     OK(bucket_readback(idx, bs, host, reg));
     { float ms = 0; cudaEventElapsedTime(&ms, idx->ev[4], idx->ev[5]); idx->scatter_ms += ms; }
-    if (host[CTR_PERR] & (PERR_NO_AT | PERR_NO_PLUS)) return KMI_OK;  // reported by the caller; nothing of this round inserted
+    if (host[CTR_PERR] & (PERR_NO_AT | PERR_NO_PLUS)) return KMI_OK;  // reported by the caller; this round is not inserted
     if (host[CTR_PERR] & PERR_OVERFLOW) {
       // extreme key skew: redo this round with direct atomics (nothing of it is in the table yet)
       OK(zero_ctr(idx, CTR_PERR));
       CU(cudaMemcpyAsync(idx->ctr + CTR_NKMERS, &kmers_before, sizeof(u64), cudaMemcpyHostToDevice, idx->stream));
       CU(cudaStreamSynchronize(idx->stream));
-      OK(build_fastq_direct(idx, d_bytes, n, tile, tile + tiles));
+      OK(build_fastq_direct(idx, d_bytes, n, p0, p1));
       OK(read_ctr(idx, CTR_NKMERS, &kmers_before));
       continue;
     }
@@ -528,21 +611,25 @@ static int build_fastq_bucketed(kmi_index* idx, const uint8_t* d_bytes, size_t n
 static const size_t AUTO_BUCKET_KEYS = 1u << 21;
 static const size_t AUTO_BUCKET_BYTES = 8u << 20;  // below this the direct path wins (bucket set-up dominates)
 
-extern "C" int kmi_build_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers) {
-  (void)file_offset;
-  if (!idx || (!d_bytes && n)) return fail(KMI_ERR_ARG, "null argument");
+static int build_fastq_impl(kmi_index* idx, uint8_t* d_bytes, size_t n, const uint8_t* host_src, uint64_t* n_kmers) {
   if (idx->cfg.mode != KMI_MODE_COUNT)
     return fail(KMI_ERR_UNSUPPORTED, "FASTQ PositionIndex (ShortSequenceKmerId) is not built yet; use FASTA");
-  CU(cudaSetDevice(idx->cfg.device));
   u64 n_tiles = 0;
+  const bool bucketed = idx->build_path == 2 || (idx->build_path == 0 && n >= AUTO_BUCKET_BYTES);
   CU(cudaEventRecord(idx->ev[0], idx->stream));
-  OK(fastq_scan(idx, d_bytes, n, &n_tiles));
+  if (host_src && !bucketed) {
+    CU(cudaMemcpyAsync(d_bytes, host_src, n, cudaMemcpyHostToDevice, idx->stream));
+    host_src = nullptr;
+  }
+  OK(fastq_scan_alloc(idx, d_bytes, n, &n_tiles));
+  if (!bucketed) OK(fastq_scan_range(idx, d_bytes, n, 0, n_tiles));
   CU(cudaEventRecord(idx->ev[1], idx->stream));
   OK(zero_ctr(idx, CTR_NKMERS));
   OK(zero_ctr(idx, CTR_PERR));
-  const bool bucketed = idx->build_path == 2 || (idx->build_path == 0 && n >= AUTO_BUCKET_BYTES);
   idx->scatter_ms = 0;
-  if (bucketed) OK(build_fastq_bucketed(idx, d_bytes, n, n_tiles));
+  for (int i = 0; i < 5; ++i) idx->kernel_ms[i] = 0;
+  idx->kev_pending = false;
+  if (bucketed) OK(build_fastq_bucketed(idx, d_bytes, n, n_tiles, host_src));
   else OK(build_fastq_direct(idx, d_bytes, n, 0, n_tiles));
   CU(cudaEventRecord(idx->ev[2], idx->stream));
   u64 host[CTR_N];
@@ -551,7 +638,10 @@ extern "C" int kmi_build_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_
   cudaEventElapsedTime(&idx->stage_ms[0], idx->ev[0], idx->ev[1]);
   cudaEventElapsedTime(&idx->stage_ms[1], idx->ev[1], idx->ev[2]);
   idx->stage_ms[2] = 0;
-  if (bucketed) {  // [1] parse + scatter into buckets, [2] table sizing + insert from buckets
+  harvest_commit_times(idx);
+  idx->kernel_ms[0] = idx->stage_ms[0] + idx->stage_ms[1];
+  idx->kernel_ms[1] = bucketed ? idx->scatter_ms : idx->stage_ms[1];
+  if (bucketed) {  // [0] nothing (the scan is per round), [1] parse + scatter, [2] scan + table sizing + insert
     idx->stage_ms[2] = idx->stage_ms[1] - idx->scatter_ms;
     idx->stage_ms[1] = idx->scatter_ms;
   }
@@ -561,12 +651,20 @@ extern "C" int kmi_build_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_
   return parse_error(host[CTR_PERR]);
 }
 
+extern "C" int kmi_build_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers) {
+  (void)file_offset;
+  if (!idx || (!d_bytes && n)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  return build_fastq_impl(idx, const_cast<uint8_t*>(d_bytes), n, nullptr, n_kmers);
+}
+
+// host bytes: the H2D copy is pipelined with the build (bucketed path), see build_fastq_bucketed
 extern "C" int kmi_build_fastq(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers) {
+  (void)file_offset;
   if (!idx || (!bytes && n)) return fail(KMI_ERR_ARG, "null argument");
   CU(cudaSetDevice(idx->cfg.device));
   OK(idx->stage_in.ensure(n + 64));
-  CU(cudaMemcpyAsync(idx->stage_in.p, bytes, n, cudaMemcpyHostToDevice, idx->stream));
-  return kmi_build_fastq_dev(idx, idx->stage_in.as<uint8_t>(), n, file_offset, n_kmers);
+  return build_fastq_impl(idx, idx->stage_in.as<uint8_t>(), n, bytes, n_kmers);
 }
 
 // ---- insert --------------------------------------------------------------------------------------------
@@ -891,6 +989,11 @@ extern "C" int kmi_launch_count(kmi_index* idx, uint64_t* n) {
   *n = idx->launches;
   return KMI_OK;
 }
+extern "C" int kmi_last_kernel_ms(kmi_index* idx, float* ms5) {
+  if (!idx || !ms5) return fail(KMI_ERR_ARG, "null argument");
+  for (int i = 0; i < 5; ++i) ms5[i] = idx->kernel_ms[i];
+  return KMI_OK;
+}
 extern "C" int kmi_last_stage_ms(kmi_index* idx, float* ms3) {
   if (!idx || !ms3) return fail(KMI_ERR_ARG, "null argument");
   for (int i = 0; i < 3; ++i) ms3[i] = idx->stage_ms[i];
@@ -1005,7 +1108,7 @@ static int fasta_parse_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, u
     idx->ops->fasta_kmers(idx->stream, attempt == 1, d_bytes, n, tiles, enc, enc_max, runs, runs_sums, sink, idx->ctr + CTR_NKMERS,
                           reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0, idx->cfg.nsplit != 0, tile_begin);
     idx->launches++;
-    u64 host[8];
+    u64 host[CTR_N];
     CU(cudaMemcpyAsync(host, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
     CU(cudaStreamSynchronize(idx->stream));
     *produced = host[CTR_NKMERS];

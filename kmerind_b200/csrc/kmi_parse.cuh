@@ -87,9 +87,10 @@ __device__ __forceinline__ u32 line_starts(u32 eol, bool prev_eol) {
 #ifdef KMI_SHARED_KERNELS  // non-template kernels: compiled once, in the API translation unit
 // ---- pass A: line starts per tile ------------------------------------------------------------
 __global__ void __launch_bounds__(TILE_THREADS) k_fastq_count_lines(const uint8_t* __restrict__ bytes, u64 n,
-                                                                     u32* __restrict__ tile_lines) {
+                                                                     u32* __restrict__ tile_lines, const u32 tile_begin = 0) {
   __shared__ u32 tmp[TILE_THREADS / 32 + 1];
-  u64 off = (u64)blockIdx.x * TILE_BYTES + (u64)threadIdx.x * GROUP_BYTES;
+  const u64 tile = (u64)tile_begin + blockIdx.x;
+  u64 off = tile * TILE_BYTES + (u64)threadIdx.x * GROUP_BYTES;
   u32 cnt = 0;
   if (off < n) {
     uint4 v = load_group(bytes, off, n);
@@ -98,14 +99,14 @@ __global__ void __launch_bounds__(TILE_THREADS) k_fastq_count_lines(const uint8_
   }
   u32 total;
   block_excl_scan(cnt, tmp, total);
-  if (threadIdx.x == 0) tile_lines[blockIdx.x] = total;
+  if (threadIdx.x == 0) tile_lines[tile] = total;
 }
 
 // exclusive scan of the per-tile counts (modulo 2^32: only the value mod 4 matters downstream)
-__global__ void __launch_bounds__(1024) k_scan_tiles(u32* __restrict__ v, u64 n) {
+__global__ void __launch_bounds__(1024) k_scan_tiles(u32* __restrict__ v, u64 n, u32* __restrict__ carry_io = nullptr) {
   __shared__ u32 tmp[33];
   __shared__ u32 carry_s;
-  if (threadIdx.x == 0) carry_s = 0;
+  if (threadIdx.x == 0) carry_s = carry_io ? *carry_io : 0;  // running total of earlier rounds (pipelined builds)
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (u64 base = 0; base < n; base += 1024) {
@@ -136,6 +137,7 @@ __global__ void __launch_bounds__(1024) k_scan_tiles(u32* __restrict__ v, u64 n)
     if (threadIdx.x == 0) carry_s = carry + tmp[32];
     __syncthreads();
   }
+  if (threadIdx.x == 0 && carry_io) *carry_io = carry_s;
 }
 
 // level-1 of the tile scan: each block scans 1024 tile counts in place (exclusive) and writes
