@@ -1,0 +1,135 @@
+"""Exchange plumbing of the sharded index (kmerind_b200/dist.py).
+
+CPU (gloo, world_size 2): the count exchange and the all-to-all of key rows deliver what
+mxx::all2all / mxx::all2allv deliver in imxx::distribute (reference src/io/incremental_mxx.hpp:1087,1098):
+received rows grouped by source rank, each group in the sender's order. The owner rule is checked
+against the oracle's dist hash. GPU (nccl, 2 GPUs when present): a sharded CountIndex equals the
+single-shard one.
+"""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import oracle_util as ou
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _gloo_worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from kmerind_b200.dist import exchange_counts, exchange_rows
+        rng = np.random.default_rng(100 + rank)
+        n = 1000 + 37 * rank
+        keys = rng.integers(0, 1 << 62, size=n, dtype=np.int64)  # any 62-bit value is a 31-mer
+        # owner by the oracle's dist hash (farm seed 83) % world — KeyToRank
+        owner = (ou.hashes(keys.view(np.uint64), 31, 3) % np.uint64(world)).astype(np.int64)
+        order = np.argsort(owner, kind="stable")           # stable: sender order kept inside a group
+        send_rows = torch.from_numpy(keys[order]).view(-1, 1)
+        send_counts = torch.from_numpy(np.bincount(owner, minlength=world).astype(np.int64))
+        recv_counts = exchange_counts(send_counts)
+        got = exchange_rows(send_rows, send_counts, recv_counts).view(-1).numpy()
+        np.save(os.path.join(out_dir, "keys%d.npy" % rank), keys)
+        np.save(os.path.join(out_dir, "owner%d.npy" % rank), owner)
+        np.save(os.path.join(out_dir, "got%d.npy" % rank), got)
+        np.save(os.path.join(out_dir, "rc%d.npy" % rank), recv_counts.numpy())
+        # empty contribution from one rank must still work (every rank calls every collective)
+        empty = torch.zeros((0, 1), dtype=torch.int64)
+        zc = torch.zeros(world, dtype=torch.int64)
+        if rank == 0:
+            r2 = exchange_counts(zc)
+            g2 = exchange_rows(empty, zc, r2)
+        else:
+            r2 = exchange_counts(send_counts)
+            g2 = exchange_rows(send_rows, send_counts, r2)
+        np.save(os.path.join(out_dir, "got2_%d.npy" % rank), g2.view(-1).numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_exchange_gloo_world2(tmp_path):
+    world = 2
+    mp.spawn(_gloo_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    keys = [np.load(tmp_path / ("keys%d.npy" % r)) for r in range(world)]
+    owner = [np.load(tmp_path / ("owner%d.npy" % r)) for r in range(world)]
+    for dst in range(world):
+        got = np.load(tmp_path / ("got%d.npy" % dst))
+        rc = np.load(tmp_path / ("rc%d.npy" % dst))
+        want = np.concatenate([keys[src][owner[src] == dst] for src in range(world)])  # by source, sender order
+        assert rc.tolist() == [int((owner[src] == dst).sum()) for src in range(world)]
+        assert np.array_equal(got, want)
+    # second exchange: rank 0 sent nothing
+    for dst in range(world):
+        got2 = np.load(tmp_path / ("got2_%d.npy" % dst))
+        assert np.array_equal(got2, keys[1][owner[1] == dst])
+
+
+def _nccl_worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        import kmerind_b200 as kb
+        from kmerind_b200.dist import ShardedIndex
+        n_reads = 30000
+        buf = ou.synth_fastq(rank * n_reads, n_reads, 150, 400000, 11, 5000, 0)
+        text = torch.from_numpy(np.concatenate([buf, np.zeros(64, np.uint8)])).cuda()
+        idx = ShardedIndex(31, hash=kb.HASH_FARM, device=rank)
+        n = idx.build_fastq_dev(text, buf.size)
+        assert n == n_reads * 120
+        k, c = idx.local.sorted_dump()
+        np.save(os.path.join(out_dir, "k%d.npy" % rank), k)
+        np.save(os.path.join(out_dir, "c%d.npy" % rank), c)
+        total = idx.size()
+        # batched query through the exchange: every rank asks for its own first 1000 k-mers + 1000 absent keys
+        keys, _, _ = ou.fastq_kmers(buf, 31)
+        q = np.concatenate([keys[:1000], np.arange(1000, dtype=np.uint64) * np.uint64(7919) + np.uint64(1 << 40)])
+        vals, found = idx.find(q)
+        np.save(os.path.join(out_dir, "q%d.npy" % rank), q)
+        np.save(os.path.join(out_dir, "v%d.npy" % rank), vals)
+        np.save(os.path.join(out_dir, "f%d.npy" % rank), found)
+        np.save(os.path.join(out_dir, "size%d.npy" % rank), np.array([total]))
+        idx.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_sharded_count_index_nccl_world2(tmp_path):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    world = 2
+    mp.spawn(_nccl_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    n_reads = 30000
+    bufs = [ou.synth_fastq(r * n_reads, n_reads, 150, 400000, 11, 5000, 0) for r in range(world)]
+    keys = np.concatenate([ou.fastq_kmers(b, 31)[0] for b in bufs])
+    wk, wc = ou.count_sorted(keys, 31)
+    owner = (ou.hashes(wk, 31, 3) % np.uint64(world)).astype(np.int64)
+    for r in range(world):
+        k = np.load(tmp_path / ("k%d.npy" % r))
+        c = np.load(tmp_path / ("c%d.npy" % r))
+        assert np.array_equal(k, wk[owner == r]) and np.array_equal(c, wc[owner == r])   # per-rank local contents
+        assert int(np.load(tmp_path / ("size%d.npy" % r))[0]) == len(wk)
+        q = np.load(tmp_path / ("q%d.npy" % r))
+        v = np.load(tmp_path / ("v%d.npy" % r))
+        f = np.load(tmp_path / ("f%d.npy" % r))
+        cq = ou.canonical(q, 31)
+        pos = np.searchsorted(wk, cq)
+        pos[pos >= len(wk)] = 0
+        hit = wk[pos] == cq
+        assert np.array_equal(f.astype(bool), hit)
+        assert np.array_equal(v[hit], wc[pos[hit]])
