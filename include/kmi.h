@@ -102,6 +102,26 @@ int kmi_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64
                         uint64_t* d_keys, uint64_t* d_ids, size_t cap, uint64_t* n_kmers);
 int kmi_parse_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n,
                         uint64_t* d_keys, uint64_t* d_ids, size_t cap, uint64_t* n_kmers);
+/* a2-a14 fused for the sharded build: parse + owner = dist_hash % nranks + scatter, straight into one
+ * region of `region_cap` keys per owning rank (d_regions + r * region_cap * nw): the send buffers of the
+ * all-to-all, with h_counts[nranks] the send counts (imxx::distribute up to mxx::all2allv,
+ * incremental_mxx.hpp:1039-1098). Order inside a region is unspecified. KMI_ERR_CAPACITY when a region
+ * overflows (skewed owners): fall back to kmi_parse_fastq_dev + kmi_partition_dev. */
+int kmi_parse_fastq_by_owner_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* d_regions,
+                                 size_t region_cap, uint64_t* h_counts, uint64_t* n_kmers);
+/* ---- fused exchange over NVLink peer memory (replaces mxx::all2allv, incremental_mxx.hpp:1098, in the
+ * build): each rank owns a receive buffer of nranks regions of `region_cap` keys (region s = keys from
+ * rank s). kmi_exchange_setup allocates it and returns its CUDA IPC handle; the caller all-gathers the
+ * nranks handles (any transport) and passes them to kmi_exchange_connect. kmi_exchange_parse_fastq_dev
+ * then runs parse + owner + scatter as ONE kernel whose stores land directly in the owners' buffers;
+ * the caller exchanges the send counts (this is also the completion handshake) and calls
+ * kmi_exchange_insert with the counts it received. All ranks must be on one node (CUDA IPC). */
+#define KMI_IPC_HANDLE_BYTES 64
+int kmi_exchange_setup(kmi_index* idx, size_t region_cap, uint8_t* handle_out /* KMI_IPC_HANDLE_BYTES */);
+int kmi_exchange_connect(kmi_index* idx, const uint8_t* handles /* nranks * KMI_IPC_HANDLE_BYTES */);
+int kmi_exchange_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* h_send_counts,
+                                 uint64_t* n_kmers);
+int kmi_exchange_insert(kmi_index* idx, const uint64_t* h_recv_counts);
 /* a10: out = canonical(in) (lex_less, kmer_transform.hpp:109-126); in == out allowed */
 int kmi_canonicalize_dev(kmi_index* idx, const uint64_t* d_keys, uint64_t* d_out, size_t n);
 /* a11/a12: which = 0 store hash, 1 dist hash, of the keys AS GIVEN (no transform) */

@@ -68,6 +68,9 @@ def load_library(build_if_missing=False):
         "kmi_build_fastq_dev": [_P, _P, _SZ, _U64, _P], "kmi_build_fasta_dev": [_P, _P, _SZ, _P],
         "kmi_parse_fastq_dev": [_P, _P, _SZ, _U64, _P, _P, _SZ, _P],
         "kmi_parse_fasta_dev": [_P, _P, _SZ, _P, _P, _SZ, _P],
+        "kmi_parse_fastq_by_owner_dev": [_P, _P, _SZ, _P, _SZ, _P, _P],
+        "kmi_exchange_setup": [_P, _SZ, _P], "kmi_exchange_connect": [_P, _P],
+        "kmi_exchange_parse_fastq_dev": [_P, _P, _SZ, _P, _P], "kmi_exchange_insert": [_P, _P],
         "kmi_canonicalize_dev": [_P, _P, _P, _SZ], "kmi_hash_dev": [_P, ctypes.c_int, _P, _P, _SZ],
         "kmi_partition_dev": [_P, _P, _P, _SZ, _P, _P, _P],
         "kmi_insert": [_P, _P, _P, _SZ], "kmi_insert_dev": [_P, _P, _P, _SZ],
@@ -91,7 +94,8 @@ def load_library(build_if_missing=False):
 EXPORTED_SYMBOLS = (
     "kmi_create", "kmi_destroy", "kmi_last_error", "kmi_set_stream", "kmi_set_param", "kmi_reserve", "kmi_clear",
     "kmi_build_fastq", "kmi_build_fasta", "kmi_build_fastq_dev", "kmi_build_fasta_dev",
-    "kmi_parse_fastq_dev", "kmi_parse_fasta_dev", "kmi_canonicalize_dev", "kmi_hash_dev",
+    "kmi_parse_fastq_dev", "kmi_parse_fasta_dev", "kmi_parse_fastq_by_owner_dev", "kmi_exchange_setup", "kmi_exchange_connect",
+    "kmi_exchange_parse_fastq_dev", "kmi_exchange_insert", "kmi_canonicalize_dev", "kmi_hash_dev",
     "kmi_partition_dev", "kmi_insert", "kmi_insert_dev", "kmi_count", "kmi_find", "kmi_find_positions",
     "kmi_erase", "kmi_count_dev", "kmi_find_dev", "kmi_local_size", "kmi_num_keys", "kmi_dump",
     "kmi_checksum", "kmi_table_info", "kmi_launch_count", "kmi_last_stage_ms", "kmi_last_kernel_ms",
@@ -183,6 +187,34 @@ class Index:
         n = _U64(0)
         _check(self._lib.kmi_parse_fastq_dev(self._h, dptr, nbytes, file_offset, d_keys, d_ids, cap, ctypes.byref(n)))
         return n.value
+
+    def parse_fastq_by_owner_dev(self, dptr, nbytes, d_regions, region_cap, nranks):
+        """(send counts per owner, k-mers generated); owner r's keys at d_regions + r * region_cap * nw."""
+        counts = np.zeros(nranks, dtype=np.uint64)
+        n = _U64(0)
+        _check(self._lib.kmi_parse_fastq_by_owner_dev(self._h, dptr, nbytes, d_regions, region_cap, _hptr(counts),
+                                                      ctypes.byref(n)))
+        return counts, n.value
+
+    # -- fused exchange over NVLink peer memory (kmi_exchange_*) -------------------------------------
+    def exchange_setup(self, region_cap):
+        h = np.zeros(64, dtype=np.uint8)
+        _check(self._lib.kmi_exchange_setup(self._h, region_cap, _hptr(h)))
+        return h.tobytes()
+
+    def exchange_connect(self, handles):
+        buf = np.frombuffer(b"".join(handles), dtype=np.uint8).copy()
+        _check(self._lib.kmi_exchange_connect(self._h, _hptr(buf)))
+
+    def exchange_parse_fastq_dev(self, dptr, nbytes, nranks):
+        counts = np.zeros(nranks, dtype=np.uint64)
+        n = _U64(0)
+        _check(self._lib.kmi_exchange_parse_fastq_dev(self._h, dptr, nbytes, _hptr(counts), ctypes.byref(n)))
+        return counts, n.value
+
+    def exchange_insert(self, recv_counts):
+        c = np.ascontiguousarray(recv_counts, dtype=np.uint64)
+        _check(self._lib.kmi_exchange_insert(self._h, _hptr(c)))
 
     def parse_fasta_dev(self, dptr, nbytes, d_keys, cap, d_ids=None):
         n = _U64(0)

@@ -102,6 +102,11 @@ struct kmi_index {
   cudaEvent_t kev[4] = {nullptr, nullptr, nullptr, nullptr};  // around the kernels of bucket_commit
   bool kev_pending = false;
   float kernel_ms[5] = {0, 0, 0, 0, 0};  // last build: total, parse+scatter, fine scatter, segment/L2 insert, overflow insert
+  // fused exchange (kmi_exchange_*): receive regions of this rank, peers' regions mapped over CUDA IPC
+  void* xchg_recv = nullptr;
+  u64 xchg_region_cap = 0;
+  std::vector<void*> xchg_peer;     // base of rank r's receive buffer in this process (own buffer for r == rank)
+  DevBuf xchg_bases;                // device array: where THIS rank writes keys owned by rank r
   cudaStream_t copy_stream = nullptr;        // H2D copies of the pipelined host-pointer build
   std::vector<cudaEvent_t> copy_events;    // parse+scatter share of the last bucketed build
 
@@ -202,6 +207,10 @@ static int table_room(kmi_index* idx, u64 incoming, u64* grant) {
   return KMI_OK;
 }
 
+static void exchange_close(kmi_index* idx);
+static const size_t AUTO_BUCKET_KEYS = 1u << 21;   // below this the direct path wins (bucket set-up dominates)
+static const size_t AUTO_BUCKET_BYTES = 8u << 20;
+
 extern "C" const char* kmi_last_error(void) { return g_err; }
 
 extern "C" int kmi_create(const kmi_config* cfg, kmi_index** out) {
@@ -253,6 +262,7 @@ extern "C" void kmi_destroy(kmi_index* idx) {
   for (int i = 0; i < 4; ++i) if (idx->kev[i]) cudaEventDestroy(idx->kev[i]);
   for (cudaEvent_t e : idx->copy_events) cudaEventDestroy(e);
   if (idx->copy_stream) cudaStreamDestroy(idx->copy_stream);
+  exchange_close(idx);
   delete idx;
 }
 
@@ -320,6 +330,7 @@ static int bucket_prepare(kmi_index* idx, u64 max_keys, BucketSink* bs) {
   bs->hll = idx->bkt_meta.as<u32>() + META_HLL;
   bs->capb = (u32)capb;
   bs->ovf_cap = (u32)ovf;
+  bs->bases = nullptr;
   return KMI_OK;
 }
 
@@ -426,25 +437,38 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
 
 static int insert_keys_chunked(kmi_index* idx, const u64* d_keys, size_t n, bool canon);
 
+// several key streams -> the same buckets -> table (one table sweep for all of them); total <= BUCKET_MAX_KEYS
+static int insert_streams_bucketed(kmi_index* idx, const u64* const* d_keys, const u64* counts, int n_streams, bool canon) {
+  u64 total = 0;
+  for (int i = 0; i < n_streams; ++i) total += counts[i];
+  if (total == 0) return KMI_OK;
+  std::vector<u32> reg;
+  BucketSink bs;
+  OK(bucket_prepare(idx, total, &bs));
+  OK(zero_ctr(idx, CTR_PERR));
+  for (int i = 0; i < n_streams; ++i) {
+    if (!counts[i]) continue;
+    idx->ops->scatter_keys(idx->stream, d_keys[i], counts[i], bs, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), canon);
+    idx->launches++;
+  }
+  u64 host[CTR_N];
+  OK(bucket_readback(idx, bs, host, reg));
+  if (host[CTR_PERR] & PERR_OVERFLOW) {
+    // extreme key skew: nothing of this round is in the table yet, redo it with direct atomics
+    OK(zero_ctr(idx, CTR_PERR));
+    for (int i = 0; i < n_streams; ++i) OK(insert_keys_chunked(idx, d_keys[i], counts[i], canon));
+    return KMI_OK;
+  }
+  return bucket_commit(idx, bs, total, host[CTR_SIZE], reg);
+}
+
 // key stream -> buckets -> table, in rounds of at most BUCKET_MAX_KEYS keys
 static int insert_keys_bucketed(kmi_index* idx, const u64* d_keys, size_t n, bool canon) {
   size_t done = 0;
-  std::vector<u32> reg;
   while (done < n) {
-    u64 m = std::min<u64>(n - done, BUCKET_MAX_KEYS);
-    BucketSink bs;
-    OK(bucket_prepare(idx, m, &bs));
-    OK(zero_ctr(idx, CTR_PERR));
-    idx->ops->scatter_keys(idx->stream, d_keys + done * idx->nw, m, bs, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), canon);
-    idx->launches++;
-    u64 host[CTR_N];
-    OK(bucket_readback(idx, bs, host, reg));
-    if (host[CTR_PERR] & PERR_OVERFLOW) {
-      // extreme key skew: nothing of this round is in the table yet, redo it with direct atomics
-      OK(insert_keys_chunked(idx, d_keys + done * idx->nw, m, canon));
-    } else {
-      OK(bucket_commit(idx, bs, m, host[CTR_SIZE], reg));
-    }
+    const u64 m = std::min<u64>(n - done, BUCKET_MAX_KEYS);
+    const u64* p = d_keys + done * idx->nw;
+    OK(insert_streams_bucketed(idx, &p, &m, 1, canon));
     done += m;
   }
   return KMI_OK;
@@ -501,13 +525,174 @@ extern "C" int kmi_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_
   TableView none; none.slots = nullptr; none.mask = 0; none.shift = 63; none.size = nullptr; none.error = nullptr;
   idx->ops->fastq_kmers(idx->stream, 0, d_bytes, n, n_tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), sink, none, BucketSink(),
                         idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0,
-                        idx->cfg.nsplit != 0, 0);
+                        idx->cfg.nsplit != 0, 0, 1);
   idx->launches++;
   u64 host[CTR_N];
   CU(cudaMemcpyAsync(host, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
   CU(cudaStreamSynchronize(idx->stream));
   if (n_kmers) *n_kmers = host[CTR_NKMERS];
   return parse_error(host[CTR_PERR]);
+}
+
+// S1-S4 fused for the sharded build: text -> one key region per owning rank (the all-to-all send buffers)
+extern "C" int kmi_parse_fastq_by_owner_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* d_regions,
+                                            size_t region_cap, uint64_t* h_counts, uint64_t* n_kmers) {
+  if (!idx || (!d_bytes && n) || !d_regions || !h_counts) return fail(KMI_ERR_ARG, "null argument");
+  if (region_cap == 0 || region_cap > 0xffffffffULL) return fail(KMI_ERR_ARG, "region capacity out of range");
+  CU(cudaSetDevice(idx->cfg.device));
+  const u32 p = (u32)idx->cfg.nranks;
+  for (u32 r = 0; r < p; ++r) h_counts[r] = 0;
+  if (n_kmers) *n_kmers = 0;
+  u64 n_tiles = 0;
+  OK(fastq_scan(idx, d_bytes, n, &n_tiles));
+  if (n_tiles == 0) return KMI_OK;
+  if (!idx->hll_ready) {
+    OK(idx->bkt_meta.ensure(sizeof(u32) * META_WORDS));
+    CU(cudaMemsetAsync(idx->bkt_meta.p, 0, sizeof(u32) * META_WORDS, idx->stream));
+    idx->hll_ready = true;
+  } else {
+    CU(cudaMemsetAsync(idx->bkt_meta.p, 0, sizeof(u32) * META_HLL, idx->stream));
+  }
+  OK(zero_ctr(idx, CTR_NKMERS));
+  OK(zero_ctr(idx, CTR_PERR));
+  BucketSink bs;
+  bs.keys = reinterpret_cast<u64*>(d_regions); bs.cursor = idx->bkt_meta.as<u32>(); bs.capb = (u32)region_cap; bs.ovf_cap = 0;
+  bs.hll = nullptr; bs.bases = nullptr;
+  KeySink nosink; nosink.keys = nullptr; nosink.ids = nullptr; nosink.cap = 0; nosink.cursor = nullptr;
+  TableView none; none.slots = nullptr; none.mask = 0; none.shift = 63; none.size = nullptr; none.error = nullptr;
+  idx->ops->fastq_kmers(idx->stream, 3, d_bytes, n, n_tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), nosink, none, bs,
+                        idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0,
+                        idx->cfg.nsplit != 0, 0, p);
+  idx->launches++;
+  u64 host[CTR_N];
+  CU(cudaMemcpyAsync(host, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaMemcpyAsync(idx->h_cursor, bs.cursor, sizeof(u32) * (N_BUCKETS + 1), cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaStreamSynchronize(idx->stream));
+  if (n_kmers) *n_kmers = host[CTR_NKMERS];
+  if (host[CTR_PERR] & PERR_OVERFLOW) return fail(KMI_ERR_CAPACITY, "an owner region overflowed (skewed owners): use parse + partition");
+  for (u32 r = 0; r < p; ++r) h_counts[r] = idx->h_cursor[r];
+  return parse_error(host[CTR_PERR]);
+}
+
+// ---- fused exchange over NVLink peer memory ---------------------------------------------------------------
+// Replaces mxx::all2allv in imxx::distribute (incremental_mxx.hpp:1098) for the build: every rank owns a
+// receive buffer of nranks regions (one per SOURCE rank); the parse kernel of rank s writes the keys owned
+// by rank r straight into region s of rank r's buffer with plain stores over NVLink (CUDA IPC mapping), so
+// the transfer overlaps the parsing and no separate collective moves keys. Only the nranks x nranks count
+// matrix still travels through the process group (it doubles as the "writes are complete" handshake).
+static void exchange_close(kmi_index* idx) {
+  for (size_t r = 0; r < idx->xchg_peer.size(); ++r)
+    if (idx->xchg_peer[r] && (int)r != idx->cfg.rank) cudaIpcCloseMemHandle(idx->xchg_peer[r]);
+  idx->xchg_peer.clear();
+  if (idx->xchg_recv) cudaFree(idx->xchg_recv);
+  idx->xchg_recv = nullptr;
+  idx->xchg_region_cap = 0;
+}
+
+extern "C" int kmi_exchange_setup(kmi_index* idx, size_t region_cap, uint8_t* handle_out) {
+  if (!idx || !handle_out || region_cap == 0 || region_cap > 0xffffffffULL) return fail(KMI_ERR_ARG, "bad argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  static_assert(sizeof(cudaIpcMemHandle_t) == KMI_IPC_HANDLE_BYTES, "IPC handle size");
+  CU(cudaStreamSynchronize(idx->stream));
+  exchange_close(idx);
+  const size_t bytes = (size_t)idx->cfg.nranks * region_cap * idx->nw * sizeof(u64);
+  cudaError_t e = cudaMalloc(&idx->xchg_recv, bytes);
+  if (e != cudaSuccess) { idx->xchg_recv = nullptr; return fail(KMI_ERR_NOMEM, "cudaMalloc exchange buffer %zu: %s", bytes, cudaGetErrorString(e)); }
+  idx->xchg_region_cap = region_cap;
+  cudaIpcMemHandle_t h;
+  CU(cudaIpcGetMemHandle(&h, idx->xchg_recv));
+  memcpy(handle_out, &h, sizeof(h));
+  return KMI_OK;
+}
+
+extern "C" int kmi_exchange_connect(kmi_index* idx, const uint8_t* handles) {
+  if (!idx || !handles) return fail(KMI_ERR_ARG, "null argument");
+  if (!idx->xchg_recv) return fail(KMI_ERR_ARG, "kmi_exchange_setup first");
+  CU(cudaSetDevice(idx->cfg.device));
+  const int p = idx->cfg.nranks, me = idx->cfg.rank;
+  idx->xchg_peer.assign(p, nullptr);
+  std::vector<u64*> bases(p);
+  for (int r = 0; r < p; ++r) {
+    void* base = idx->xchg_recv;
+    if (r != me) {
+      cudaIpcMemHandle_t h;
+      memcpy(&h, handles + (size_t)r * KMI_IPC_HANDLE_BYTES, sizeof(h));
+      cudaError_t e = cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess) { exchange_close(idx); return fail(KMI_ERR_CUDA, "cudaIpcOpenMemHandle(rank %d): %s", r, cudaGetErrorString(e)); }
+    }
+    idx->xchg_peer[r] = base;
+    bases[r] = reinterpret_cast<u64*>(base) + (size_t)me * idx->xchg_region_cap * idx->nw;   // my region in r's buffer
+  }
+  OK(idx->xchg_bases.ensure(sizeof(u64*) * p));
+  CU(cudaMemcpy(idx->xchg_bases.p, bases.data(), sizeof(u64*) * p, cudaMemcpyHostToDevice));
+  return KMI_OK;
+}
+
+// parse + owner + scatter into the owners' receive buffers. h_send_counts[r] = keys written to rank r.
+// The caller must make sure (barrier) that no peer is still reading its receive buffer from the last round.
+extern "C" int kmi_exchange_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* h_send_counts,
+                                            uint64_t* n_kmers) {
+  if (!idx || (!d_bytes && n) || !h_send_counts) return fail(KMI_ERR_ARG, "null argument");
+  if (idx->xchg_peer.empty()) return fail(KMI_ERR_ARG, "kmi_exchange_connect first");
+  CU(cudaSetDevice(idx->cfg.device));
+  const u32 p = (u32)idx->cfg.nranks;
+  for (u32 r = 0; r < p; ++r) h_send_counts[r] = 0;
+  if (n_kmers) *n_kmers = 0;
+  u64 n_tiles = 0;
+  OK(fastq_scan(idx, d_bytes, n, &n_tiles));
+  if (n_tiles == 0) return KMI_OK;
+  if (!idx->hll_ready) {
+    OK(idx->bkt_meta.ensure(sizeof(u32) * META_WORDS));
+    CU(cudaMemsetAsync(idx->bkt_meta.p, 0, sizeof(u32) * META_WORDS, idx->stream));
+    idx->hll_ready = true;
+  } else {
+    CU(cudaMemsetAsync(idx->bkt_meta.p, 0, sizeof(u32) * META_HLL, idx->stream));
+  }
+  OK(zero_ctr(idx, CTR_NKMERS));
+  OK(zero_ctr(idx, CTR_PERR));
+  BucketSink bs;
+  bs.keys = nullptr; bs.cursor = idx->bkt_meta.as<u32>(); bs.capb = (u32)idx->xchg_region_cap; bs.ovf_cap = 0; bs.hll = nullptr;
+  bs.bases = idx->xchg_bases.as<u64*>();
+  KeySink nosink; nosink.keys = nullptr; nosink.ids = nullptr; nosink.cap = 0; nosink.cursor = nullptr;
+  TableView none; none.slots = nullptr; none.mask = 0; none.shift = 63; none.size = nullptr; none.error = nullptr;
+  idx->ops->fastq_kmers(idx->stream, 3, d_bytes, n, n_tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), nosink, none, bs,
+                        idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0,
+                        idx->cfg.nsplit != 0, 0, p);
+  idx->launches++;
+  u64 host[CTR_N];
+  CU(cudaMemcpyAsync(host, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaMemcpyAsync(idx->h_cursor, bs.cursor, sizeof(u32) * (N_BUCKETS + 1), cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaStreamSynchronize(idx->stream));   // kernel complete => its peer stores are visible system-wide
+  if (n_kmers) *n_kmers = host[CTR_NKMERS];
+  if (host[CTR_PERR] & PERR_OVERFLOW) return fail(KMI_ERR_CAPACITY, "an owner region overflowed (skewed owners)");
+  for (u32 r = 0; r < p; ++r) h_send_counts[r] = idx->h_cursor[r];
+  return parse_error(host[CTR_PERR]);
+}
+
+// insert what the peers wrote: h_recv_counts[s] = keys rank s put into region s of this rank's buffer
+extern "C" int kmi_exchange_insert(kmi_index* idx, const uint64_t* h_recv_counts) {
+  if (!idx || !h_recv_counts) return fail(KMI_ERR_ARG, "null argument");
+  if (!idx->xchg_recv) return fail(KMI_ERR_ARG, "kmi_exchange_setup first");
+  if (idx->cfg.mode != KMI_MODE_COUNT) return fail(KMI_ERR_UNSUPPORTED, "exchange insert is built for the count index");
+  CU(cudaSetDevice(idx->cfg.device));
+  const int p = idx->cfg.nranks;
+  std::vector<const u64*> ptrs(p);
+  std::vector<u64> cnt(p);
+  u64 total = 0;
+  for (int s = 0; s < p; ++s) {
+    if (h_recv_counts[s] > idx->xchg_region_cap) return fail(KMI_ERR_ARG, "receive count exceeds the region capacity");
+    ptrs[s] = reinterpret_cast<const u64*>(idx->xchg_recv) + (size_t)s * idx->xchg_region_cap * idx->nw;
+    cnt[s] = h_recv_counts[s];
+    total += cnt[s];
+  }
+  // keys arrive canonical already (the sender's parser applied the transform)
+  if (total <= BUCKET_MAX_KEYS && (idx->build_path == 2 || (idx->build_path == 0 && total >= AUTO_BUCKET_KEYS)))
+    return insert_streams_bucketed(idx, ptrs.data(), cnt.data(), p, false);
+  for (int s = 0; s < p; ++s) {
+    if (idx->build_path != 1 && cnt[s] >= AUTO_BUCKET_KEYS) OK(insert_keys_bucketed(idx, ptrs[s], cnt[s], false));
+    else OK(insert_keys_chunked(idx, ptrs[s], cnt[s], false));
+  }
+  return KMI_OK;
 }
 
 // S1-S5 with direct atomics: text -> table, no key stream in HBM (tiles [tile, tile_end))
@@ -522,7 +707,7 @@ static int build_fastq_direct(kmi_index* idx, const uint8_t* d_bytes, size_t n, 
     tiles = std::min(tiles, tile_end - tile);
     idx->ops->fastq_kmers(idx->stream, 1, d_bytes, n, tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), nosink,
                           idx->view(), BucketSink(), idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR),
-                          idx->cfg.canonical != 0, idx->cfg.nsplit != 0, tile);
+                          idx->cfg.canonical != 0, idx->cfg.nsplit != 0, tile, 1);
     idx->launches++;
     idx->non_hll_upper += grant;
     tile += tiles;
@@ -586,7 +771,7 @@ static int build_fastq_bucketed(kmi_index* idx, uint8_t* d_bytes, size_t n, u64 
     CU(cudaEventRecord(idx->ev[4], idx->stream));
     idx->ops->fastq_kmers(idx->stream, 2, d_bytes, n, tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), nosink,
                           idx->view(), bs, idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR),
-                          idx->cfg.canonical != 0, idx->cfg.nsplit != 0, p0);
+                          idx->cfg.canonical != 0, idx->cfg.nsplit != 0, p0, 1);
     idx->launches++;
     CU(cudaEventRecord(idx->ev[5], idx->stream));
     u64 host[CTR_N];
@@ -608,8 +793,6 @@ static int build_fastq_bucketed(kmi_index* idx, uint8_t* d_bytes, size_t n, u64 
   return KMI_OK;
 }
 
-static const size_t AUTO_BUCKET_KEYS = 1u << 21;
-static const size_t AUTO_BUCKET_BYTES = 8u << 20;  // below this the direct path wins (bucket set-up dominates)
 
 static int build_fastq_impl(kmi_index* idx, uint8_t* d_bytes, size_t n, const uint8_t* host_src, uint64_t* n_kmers) {
   if (idx->cfg.mode != KMI_MODE_COUNT)

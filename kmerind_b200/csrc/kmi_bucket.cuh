@@ -31,6 +31,8 @@ struct BucketSink {
   u32 capb;
   u32 ovf_cap;
   u32* hll;      // HLL_M registers: distinct-key estimate that sizes the table before the insert
+  u64* const* bases;  // optional: explicit base pointer per region (peer-GPU receive regions of the
+                      // fused exchange, kmi_exchange_*); null = regions are keys + b * capb
 };
 
 template <int NW> struct BucketSmem;
@@ -92,14 +94,14 @@ __device__ __forceinline__ void bucket_round(const BucketSink& bs, BucketSmem<NW
   for (u32 r = t; r < total; r += TILE_THREADS) {
     const u32 b = sm.sbid[r];
     u32 at = sm.delta[b] + r;
-    u64 region = (u64)b * bs.capb;
+    u64* base = bs.bases ? bs.bases[b] : bs.keys + (u64)b * bs.capb * NW;
     if (at >= bs.capb) {
       at = atomicAdd(bs.cursor + N_BUCKETS, 1u);
-      region = (u64)N_BUCKETS * bs.capb;
+      base = bs.keys + (u64)N_BUCKETS * bs.capb * NW;
       if (at >= bs.ovf_cap) { atomicOr(perr, PERR_OVERFLOW); continue; }
     }
-    if (NW == 1) bs.keys[region + at] = sm.sorted[r];
-    else reinterpret_cast<ulonglong2*>(bs.keys)[region + at] = reinterpret_cast<const ulonglong2*>(sm.sorted)[r];
+    if (NW == 1) base[at] = sm.sorted[r];
+    else reinterpret_cast<ulonglong2*>(base)[at] = reinterpret_cast<const ulonglong2*>(sm.sorted)[r];
   }
   __syncthreads();
 }

@@ -13,7 +13,7 @@ struct Ops {
   // parse (FASTQ). sink_kind 0: key stream, 1: straight into the table, 2: hash-prefix buckets
   void (*fastq_kmers)(cudaStream_t, int sink_kind, const uint8_t* bytes, u64 n, u64 n_tiles, const u32* tile_lines,
                       const u32* block_sums, KeySink sink, TableView table, BucketSink bsink, u64* n_kmers, u32* perr,
-                      bool canon, bool nsplit, u64 tile_begin);
+                      bool canon, bool nsplit, u64 tile_begin, u32 nranks);
   void (*scatter_keys)(cudaStream_t, const u64* keys, u64 n, BucketSink bsink, u32* perr, bool canon);
   void (*insert_buckets)(cudaStream_t, TableView, BucketSink bsink, u64 n_hint);
   // second level (one-word keys only; null for K > 32): fine scatter, shared-memory segment insert
@@ -56,17 +56,20 @@ struct OpsImpl {
   typedef Slot<NW> S;
   static void fastq_kmers(cudaStream_t st, int sink_kind, const uint8_t* bytes, u64 n, u64 n_tiles, const u32* tile_lines,
                           const u32* block_sums, KeySink sink, TableView table, BucketSink bsink, u64* n_kmers, u32* perr,
-                          bool canon, bool nsplit, u64 tile_begin) {
+                          bool canon, bool nsplit, u64 tile_begin, u32 nranks) {
     if (n_tiles == 0) return;
     if (sink_kind == 0)
       k_fastq_kmers<K, HASH, 0><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table, bsink,
-                                                                          n_kmers, perr, canon, nsplit, tile_begin);
+                                                                          n_kmers, perr, canon, nsplit, tile_begin, nranks);
     else if (sink_kind == 1)
       k_fastq_kmers<K, HASH, 1><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table, bsink,
-                                                                          n_kmers, perr, canon, nsplit, tile_begin);
-    else
+                                                                          n_kmers, perr, canon, nsplit, tile_begin, nranks);
+    else if (sink_kind == 2)
       k_fastq_kmers<K, HASH, 2><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table, bsink,
-                                                                          n_kmers, perr, canon, nsplit, tile_begin);
+                                                                          n_kmers, perr, canon, nsplit, tile_begin, nranks);
+    else
+      k_fastq_kmers<K, HASH, 3><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table, bsink,
+                                                                          n_kmers, perr, canon, nsplit, tile_begin, nranks);
   }
   static void scatter_keys(cudaStream_t st, const u64* keys, u64 n, BucketSink bsink, u32* perr, bool canon) {
     if (n) k_scatter_keys<K, HASH><<<grid_for(n, TILE_THREADS * BktRound<NW>::R, 148u * 8u), TILE_THREADS, 0, st>>>(keys, n, bsink, perr, canon);

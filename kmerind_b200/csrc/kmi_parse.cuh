@@ -228,14 +228,16 @@ struct KeySink {     // dense key (+id) stream
 // SINK 0: write canonical (or forward) keys to sink.keys (block-contiguous, order of blocks free)
 // SINK 1: insert straight into the count table (val += 1), no key stream at all
 // SINK 2: scatter into the 256 hash-prefix buckets of kmi_bucket.cuh (the default build path)
+// SINK 3: scatter into one region per owning rank, owner = dist_hash % nranks (KeyToRank,
+//         distributed_densehash_map.hpp:148-170): the send buffers of the all-to-all, no key stream pass
 template <int K, int HASH, int SINK>
 __global__ void __launch_bounds__(TILE_THREADS)
 k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ tile_lines,
               const u32* __restrict__ block_sums, KeySink sink, TableView table, BucketSink bsink,
               u64* __restrict__ n_kmers, u32* __restrict__ perr, const bool CANON, const bool NSPLIT,
-              const u64 tile_begin) {
+              const u64 tile_begin, const u32 nranks) {
   constexpr int NW = (K <= 32 ? 1 : 2);
-  __shared__ BucketSmem<(SINK == 2 ? NW : 0)> s_bkt;
+  __shared__ BucketSmem<(SINK >= 2 ? NW : 0)> s_bkt;
   __shared__ u32 s_codes[TILE_GROUPS + 1];
   __shared__ u32 s_flags[TILE_GROUPS + 1];
   __shared__ u32 s_aux[HALO_GROUPS * 2];       // halo: line-start masks / popcounts
@@ -339,7 +341,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   __syncthreads();
 
   // -- P5: dense loop over the tile's k-mers
-  if (SINK == 2) {
+  if (SINK >= 2) {
     constexpr int R = BktRound<NW>::R;
     BucketSmem<NW>& sm = reinterpret_cast<BucketSmem<NW>&>(s_bkt);
     for (u32 c0 = 0; c0 < total; c0 += TILE_THREADS * R) {   // block-uniform trip count
@@ -357,9 +359,15 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
           for (int w = 0; w < 5; ++w) c5[w] = s_codes[min(gi + w, TILE_GROUPS)];
           key[q] = extract_kmer<K>(c5, j);
           if (CANON) key[q] = canonical<K>(key[q]);
-          const u64 h = store_hash<K, HASH>(key[q]);
-          bkt[q] = bucket_of(h);
-          hll_update(bsink.hll, h);
+          if (SINK == 2) {
+            const u64 h = store_hash<K, HASH>(key[q]);
+            bkt[q] = bucket_of(h);
+            hll_update(bsink.hll, h);
+          } else {
+            u64 hs, hd;
+            kmer_hashes<K, HASH>(key[q], hs, hd);
+            bkt[q] = (u32)(hd % (u64)nranks);
+          }
         }
       }
       bucket_round<NW>(bsink, sm, key, bkt, perr);

@@ -82,8 +82,114 @@ class ShardedIndex:
         # and canonical(canonical(x)) == canonical(x), so inserting as-is is exact either way.
         _check(lib.kmi_insert_dev(self.local._h, rk.data_ptr(), rv.data_ptr() if rv is not None else None, n_recv))
 
+    def _buffer(self, name, n_words):
+        """persistent device scratch (int64 words), grown geometrically"""
+        t = getattr(self, name, None)
+        if t is None or t.numel() < n_words:
+            t = None
+            setattr(self, name, None)
+            t = torch.empty(int(n_words * 1.1) + 1024, dtype=torch.int64, device=self.device)
+            setattr(self, name, t)
+        return t
+
+    def enable_peer_exchange(self, region_cap):
+        """Map every rank's receive buffer into this process (CUDA IPC over NVLink) so that the parse
+        kernel writes keys straight into their owners' memory. Collective. Returns False (and keeps the
+        NCCL all-to-all path) when IPC mapping is not possible."""
+        from . import KmiError
+        ok = 1
+        try:
+            handle = self.local.exchange_setup(int(region_cap))
+        except KmiError:
+            handle, ok = b"\0" * 64, 0
+        handles = [None] * self.nranks
+        dist.all_gather_object(handles, (ok, handle), group=self.group)
+        if all(h[0] for h in handles):
+            try:
+                self.local.exchange_connect([h[1] for h in handles])
+            except KmiError:
+                ok = 0
+        else:
+            ok = 0
+        flag = torch.tensor([ok], dtype=torch.int64, device=self.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        self._peer_cap = int(region_cap) if int(flag.item()) == 1 else 0
+        return self._peer_cap > 0
+
+    def _build_fastq_dev_peer(self, text, nbytes):
+        """parse + owner + scatter + exchange as one kernel (stores land in the owners' HBM over NVLink)."""
+        p = self.nranks
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        dist.barrier(group=self.group)          # nobody is still reading its receive buffer of the last round
+        from . import KmiError, ERR_CAPACITY
+        ev[0].record()
+        try:
+            counts, n = self.local.exchange_parse_fastq_dev(text.data_ptr(), nbytes, p)
+            send_counts = torch.from_numpy(counts.astype(np.int64)).to(self.device)
+        except KmiError as e:
+            if e.code != ERR_CAPACITY:
+                raise
+            n, send_counts = None, torch.full((p,), -1, dtype=torch.int64, device=self.device)  # skewed owners here
+        ev[1].record()
+        recv_counts = exchange_counts(send_counts, self.group).cpu().numpy()   # also: "the writes are complete"
+        bad = torch.tensor([1 if (n is None or (recv_counts < 0).any()) else 0], dtype=torch.int64, device=self.device)
+        dist.all_reduce(bad, op=dist.ReduceOp.MAX, group=self.group)
+        if int(bad.item()):
+            return None                        # every rank leaves the peer path together
+        ev[2].record()
+        self.local.exchange_insert(recv_counts.astype(np.uint64))
+        ev[3].record()
+        torch.cuda.synchronize(self.device)
+        self.stage_ms = {"parse+scatter+exchange": ev[0].elapsed_time(ev[1]), "counts": ev[1].elapsed_time(ev[2]),
+                         "insert": ev[2].elapsed_time(ev[3])}
+        self.n_received = int(recv_counts.sum())
+        return n
+
     def build_fastq_dev(self, text, nbytes, max_kmers=None):
-        """text: CUDA uint8 tensor holding this rank's whole records. Returns k-mers generated here."""
+        """text: CUDA uint8 tensor holding this rank's whole records. Returns k-mers generated here.
+
+        parse + owner + scatter run as ONE kernel straight into the per-owner send regions
+        (kmi_parse_fastq_by_owner_dev); the regions are exchanged with one grouped NCCL all-to-all and the
+        received keys go through the bucketed insert. Falls back to parse -> partition when an owner
+        region overflows (skewed owners)."""
+        from . import KmiError, ERR_CAPACITY
+        nw, p = self.nw, self.nranks
+        if getattr(self, "_peer_cap", 0):
+            n = self._build_fastq_dev_peer(text, nbytes)
+            if n is not None:
+                return n
+        upper = max_kmers if max_kmers is not None else max(nbytes // 2 + 1, 1)
+        region_cap = upper // p + upper // (8 * p) + 4096
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        ev[0].record()
+        send = self._buffer("_send", p * region_cap * nw)
+        try:
+            counts, n = self.local.parse_fastq_by_owner_dev(text.data_ptr(), nbytes, send.data_ptr(), region_cap, p)
+        except KmiError as e:
+            if e.code != ERR_CAPACITY:
+                raise
+            return self._build_fastq_dev_unfused(text, nbytes, max_kmers)
+        ev[1].record()
+        send_counts = torch.from_numpy(counts.astype(np.int64)).to(self.device)
+        recv_counts = exchange_counts(send_counts, self.group).tolist()
+        n_recv = int(sum(recv_counts))
+        recv = self._buffer("_recv", max(n_recv, 1) * nw)
+        ins, outs, off = [], [], 0
+        for r in range(p):
+            ins.append(send[r * region_cap * nw:(r * region_cap + int(counts[r])) * nw])
+            outs.append(recv[off * nw:(off + int(recv_counts[r])) * nw])
+            off += int(recv_counts[r])
+        dist.all_to_all(outs, ins, group=self.group)
+        ev[2].record()
+        self._insert_received(recv, None, n_recv)
+        ev[3].record()
+        torch.cuda.synchronize(self.device)
+        self.stage_ms = {"parse+scatter": ev[0].elapsed_time(ev[1]), "a2a": ev[1].elapsed_time(ev[2]),
+                         "insert": ev[2].elapsed_time(ev[3])}
+        self.n_received = n_recv
+        return n
+
+    def _build_fastq_dev_unfused(self, text, nbytes, max_kmers=None):
         nw = self.nw
         cap = max_kmers if max_kmers is not None else max(nbytes // 2 + 1, 1)
         keys = torch.empty(cap * nw, dtype=torch.int64, device=self.device)

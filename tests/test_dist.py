@@ -77,7 +77,7 @@ def test_exchange_gloo_world2(tmp_path):
         assert np.array_equal(got2, keys[1][owner[1] == dst])
 
 
-def _nccl_worker(rank, world, port, out_dir):
+def _nccl_worker(rank, world, port, out_dir, peer=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
@@ -89,8 +89,15 @@ def _nccl_worker(rank, world, port, out_dir):
         buf = ou.synth_fastq(rank * n_reads, n_reads, 150, 400000, 11, 5000, 0)
         text = torch.from_numpy(np.concatenate([buf, np.zeros(64, np.uint8)])).cuda()
         idx = ShardedIndex(31, hash=kb.HASH_FARM, device=rank)
+        if peer:
+            idx.local.set_build_path(2)   # received keys take the bucketed insert even at this size
+            assert idx.enable_peer_exchange(n_reads * 120), "CUDA IPC peer mapping failed"
         n = idx.build_fastq_dev(text, buf.size)
         assert n == n_reads * 120
+        if peer:
+            assert "parse+scatter+exchange" in idx.stage_ms
+            assert idx.build_fastq_dev(text, buf.size) == n   # a second round through the same buffers
+
         k, c = idx.local.sorted_dump()
         np.save(os.path.join(out_dir, "k%d.npy" % rank), k)
         np.save(os.path.join(out_dir, "c%d.npy" % rank), c)
@@ -109,15 +116,20 @@ def _nccl_worker(rank, world, port, out_dir):
 
 
 @pytest.mark.gpu
-def test_sharded_count_index_nccl_world2(tmp_path):
+@pytest.mark.parametrize("peer", (False, True))
+def test_sharded_count_index_nccl_world2(tmp_path, peer):
+    """peer=False: keys travel by NCCL all-to-all; peer=True: the parse kernel stores them straight into
+    the owners' HBM over NVLink (kmi_exchange_*), and the build is run twice (counts double)."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     world = 2
-    mp.spawn(_nccl_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_nccl_worker, args=(world, _free_port(), str(tmp_path), peer), nprocs=world, join=True)
     n_reads = 30000
     bufs = [ou.synth_fastq(r * n_reads, n_reads, 150, 400000, 11, 5000, 0) for r in range(world)]
     keys = np.concatenate([ou.fastq_kmers(b, 31)[0] for b in bufs])
     wk, wc = ou.count_sorted(keys, 31)
+    if peer:
+        wc = 2 * wc
     owner = (ou.hashes(wk, 31, 3) % np.uint64(world)).astype(np.int64)
     for r in range(world):
         k = np.load(tmp_path / ("k%d.npy" % r))
