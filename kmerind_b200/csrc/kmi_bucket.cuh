@@ -53,6 +53,7 @@ __device__ __forceinline__ u32 bucket_of(u64 store_hash) { return (u32)(store_ha
 // HyperLogLog update from the store hash: register = low HLL_P bits, rank from the 42 bits above
 // them (the top 8 bits pick the bucket and stay out of it).
 __device__ __forceinline__ void hll_update(u32* __restrict__ hll, u64 h) {
+  h ^= h >> 29;                                          // slot_hash mixes upwards: fold the high half into the low bits
   const u32 reg = (u32)h & (HLL_M - 1);
   const u64 w = (h >> HLL_P) << (HLL_P + LOG_BUCKETS);   // 42 significant bits, left aligned
   const u32 rank = (u32)__clzll(w | (1ULL << (HLL_P + LOG_BUCKETS - 1))) + 1u;
@@ -124,7 +125,7 @@ k_scatter_keys(const u64* __restrict__ keys, u64 n, BucketSink bs, u32* __restri
       if (i < n) {
         key[q] = load_key<NW>(keys, i);
         if (CANON) key[q] = canonical<K>(key[q]);
-        const u64 h = store_hash<K, HASH>(key[q]);
+        const u64 h = slot_hash<K>(key[q]);
         bkt[q] = bucket_of(h);
         hll_update(bs.hll, h);
       }
@@ -163,7 +164,7 @@ __global__ void __launch_bounds__(256) k_insert_buckets(TableView t, BucketSink 
     const u64 at = (u64)lo * bs.capb + (g - pre[lo]);
     Key<NW> key = load_key<NW>(bs.keys, at);
     bool was_new;
-    const u64 s = table_upsert<NW>(t, key, store_hash<K, HASH>(key), was_new);
+    const u64 s = table_upsert<NW>(t, key, slot_hash<K>(key), was_new);
     if (s != ~0ULL) {
       atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].val, 1u);
       n_new += was_new ? 1u : 0u;
@@ -238,7 +239,7 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
       if (i < m) {
         key[q] = __ldg(src + i);
         Key<1> kk; kk.w[0] = key[q];
-        const u64 h = store_hash<K, HASH>(kk);
+        const u64 h = slot_hash<K>(kk);
         fid[q] = (u32)(h >> (64 - LOG_BUCKETS - fs.log_f)) & (F - 1);
         rank[q] = atomicAdd(&hist[fid[q]], 1u);
       }
@@ -316,7 +317,7 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
         const u64 key = kq[q];
         if (key == KEY_EMPTY_TOP) continue;
         Key<1> kk; kk.w[0] = key;
-        u32 li = (u32)(store_hash<K, HASH>(kk) >> t.shift) & (SEG - 1);
+        u32 li = (u32)(slot_hash<K>(kk) >> t.shift) & (SEG - 1);
         for (;;) {
           u64 cur = seg[li].key;
           if (cur == KEY_EMPTY_TOP) {
@@ -351,7 +352,7 @@ __global__ void __launch_bounds__(256) k_insert_overflow(TableView t, BucketSink
   for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
     Key<NW> key = load_key<NW>(bs.keys, base + i);
     bool was_new;
-    const u64 s = table_upsert<NW>(t, key, store_hash<K, HASH>(key), was_new);
+    const u64 s = table_upsert<NW>(t, key, slot_hash<K>(key), was_new);
     if (s != ~0ULL) {
       atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].val, 1u);
       n_new += was_new ? 1u : 0u;

@@ -158,6 +158,21 @@ template <int K, int HASH> __device__ __forceinline__ u64 store_hash(const Key<(
   return farm_finish(farm_len0to16<NB>(lo, hi), 42, HASH == 2);
 }
 
+// Placement hash of the local table: picks the home slot (top bits), the hash-prefix bucket and the
+// HyperLogLog register. Where an entry sits inside one GPU's table is unobservable — the reference's
+// StoreHash is a free template parameter for the same reason (kmer_index.hpp:437-466) — so this is a
+// 2-multiply mixer (~15 instructions) instead of the ~90-instruction farm/murmur evaluation, which
+// stays bit-exact where it IS observable: the dist hash that picks the owning rank, and kmi_hash_dev.
+// Measured on 31-mers of the bench workload: bucket balance, probe lengths and HLL error equal farm's.
+template <int K> __device__ __forceinline__ u64 slot_hash(const Key<(K <= 32 ? 1 : 2)>& x) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  u64 h = x.w[0] * 0x9E3779B97F4A7C15ULL;
+  if (NW == 2) h += x.w[NW - 1] * 0xC2B2AE3D27D4EB4FULL;
+  h ^= h >> 32;
+  h *= 0xD6E8FEB86659FD93ULL;
+  return h;
+}
+
 // order-independent content checksum mixer (splitmix64 finaliser)
 __host__ __device__ __forceinline__ u64 mix64(u64 x) {
   u64 z = x + 0x9e3779b97f4a7c15ULL;

@@ -26,7 +26,7 @@ __global__ void __launch_bounds__(256) k_insert_keys(TableView t, const u64* __r
     Key<NW> key = load_key<NW>(keys, i);
     if (CANON) key = canonical<K>(key);
     bool was_new;
-    u64 s = table_upsert<NW>(t, key, store_hash<K, HASH>(key), was_new);
+    u64 s = table_upsert<NW>(t, key, slot_hash<K>(key), was_new);
     if (s != ~0ULL) {
       atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].val, 1u);
       n_new += was_new ? 1u : 0u;
@@ -45,7 +45,7 @@ __global__ void __launch_bounds__(256) k_rehash(const Slot<(K <= 32 ? 1 : 2)>* _
     Key<NW> key = slot_key<NW>(old + i);
     if (!is_live<NW>(key)) continue;
     bool was_new;
-    u64 s = table_upsert<NW>(t, key, store_hash<K, HASH>(key), was_new);
+    u64 s = table_upsert<NW>(t, key, slot_hash<K>(key), was_new);
     if (s != ~0ULL) {
       atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].val, old[i].val);
       n_new += was_new ? 1u : 0u;
@@ -64,7 +64,7 @@ k_lookup(TableView t, const u64* __restrict__ keys, u64 n, u64* __restrict__ val
   for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
     Key<NW> key = load_key<NW>(keys, i);
     if (CANON) key = canonical<K>(key);
-    u64 s = table_find<NW>(t, key, store_hash<K, HASH>(key));
+    u64 s = table_find<NW>(t, key, slot_hash<K>(key));
     if (vals) vals[i] = (s == ~0ULL) ? 0ULL : (u64) reinterpret_cast<const Slot<NW>*>(t.slots)[s].val;
     if (found) found[i] = (s == ~0ULL) ? 0 : 1;
     if (slot_idx) slot_idx[i] = s;
@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(256) k_erase(TableView t, const u64* __restric
   for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
     Key<NW> key = load_key<NW>(keys, i);
     if (CANON) key = canonical<K>(key);
-    u64 s = table_find<NW>(t, key, store_hash<K, HASH>(key));
+    u64 s = table_find<NW>(t, key, slot_hash<K>(key));
     if (s == ~0ULL) continue;
     Slot<NW>* sl = reinterpret_cast<Slot<NW>*>(t.slots) + s;
     bool won;
@@ -315,7 +315,7 @@ k_csr_fill(TableView t, const u64* __restrict__ keys, const u64* __restrict__ id
   constexpr int NW = (K <= 32 ? 1 : 2);
   for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
     Key<NW> key = load_key<NW>(keys, i);
-    u64 s = table_find<NW>(t, key, store_hash<K, HASH>(key));
+    u64 s = table_find<NW>(t, key, slot_hash<K>(key));
     if (s == ~0ULL) continue;
     u32 c = atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].aux, 1u);
     values[offsets[s] + c] = ids[i];
@@ -347,7 +347,7 @@ k_log_filter(TableView t, const u64* __restrict__ keys, const u64* __restrict__ 
     u64 i = base + threadIdx.x;
     bool keep = false;
     Key<NW> key;
-    if (i < n) { key = load_key<NW>(keys, i); keep = table_find<NW>(t, key, store_hash<K, HASH>(key)) != ~0ULL; }
+    if (i < n) { key = load_key<NW>(keys, i); keep = table_find<NW>(t, key, slot_hash<K>(key)) != ~0ULL; }
     u32 m = __ballot_sync(0xffffffffu, keep);
     u64 wbase = 0;
     if ((threadIdx.x & 31) == 0 && m) wbase = atomicAdd(cursor, (u64)__popc(m));

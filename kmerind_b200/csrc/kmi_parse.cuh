@@ -360,7 +360,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
           key[q] = extract_kmer<K>(c5, j);
           if (CANON) key[q] = canonical<K>(key[q]);
           if (SINK == 2) {
-            const u64 h = store_hash<K, HASH>(key[q]);
+            const u64 h = slot_hash<K>(key[q]);
             bkt[q] = bucket_of(h);
             hll_update(bsink.hll, h);
           } else {
@@ -393,7 +393,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
       }
     } else {
       bool was_new;
-      u64 slot = table_upsert<NW>(table, key, store_hash<K, HASH>(key), was_new);
+      u64 slot = table_upsert<NW>(table, key, slot_hash<K>(key), was_new);
       if (slot != ~0ULL) {
         atomicAdd(&reinterpret_cast<Slot<NW>*>(table.slots)[slot].val, 1u);
         n_new += was_new ? 1u : 0u;
