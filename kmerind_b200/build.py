@@ -14,7 +14,7 @@ OUT = os.path.join(HERE, "libkmi.so")
 KS = (15, 21, 31, 35, 47, 63)
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo",
-         "-Xcompiler", "-fPIC", "-diag-suppress", "62,63"]
+         "-Xcompiler", "-fPIC", "-diag-suppress", "62,63"] + os.environ.get("KMI_NVCC_FLAGS", "").split()
 
 
 def _newer(target, sources):

@@ -115,15 +115,33 @@ k_scatter_keys(const u64* __restrict__ keys, u64 n, BucketSink bs, u32* __restri
   constexpr int R = BktRound<NW>::R;
   __shared__ BucketSmem<NW> sm;
   const u64 per_round = (u64)TILE_THREADS * R;
+  Key<NW> nkey[R];                                       // next round's keys, requested one round ahead
+  {
+    const u64 base = (u64)blockIdx.x * per_round;
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+      const u64 i = base + (u64)q * TILE_THREADS + threadIdx.x;
+      if (i < n) nkey[q] = load_key<NW>(keys, i);
+    }
+  }
   for (u64 base = (u64)blockIdx.x * per_round; base < n; base += (u64)gridDim.x * per_round) {
     Key<NW> key[R];
     u32 bkt[R];
+#pragma unroll
+    for (int q = 0; q < R; ++q) key[q] = nkey[q];
+    {
+      const u64 nbase = base + (u64)gridDim.x * per_round;
+#pragma unroll
+      for (int q = 0; q < R; ++q) {
+        const u64 i = nbase + (u64)q * TILE_THREADS + threadIdx.x;
+        if (i < n) nkey[q] = load_key<NW>(keys, i);
+      }
+    }
 #pragma unroll
     for (int q = 0; q < R; ++q) {
       const u64 i = base + (u64)q * TILE_THREADS + threadIdx.x;
       bkt[q] = BKT_NONE;
       if (i < n) {
-        key[q] = load_key<NW>(keys, i);
         if (CANON) key[q] = canonical<K>(key[q]);
         const u64 h = slot_hash<K>(key[q]);
         bkt[q] = bucket_of(h);
@@ -216,28 +234,48 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
     if (t == 0) cpre[N_BUCKETS] = n_chunks;
   }
   __syncthreads();
-  for (u32 c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+  // software pipeline: the keys of the NEXT chunk are requested before this chunk is ranked, so the
+  // global-load latency (the kernel's main stall before: profiles/r01_*) hides behind a whole round
+  auto locate = [&](u32 c, u32& b, u32& m, const u64*& src) {
     int lo = 0, hi = N_BUCKETS - 1;                       // largest b with cpre[b] <= c and a non-empty bucket
 #pragma unroll
     for (int s = 0; s < LOG_BUCKETS; ++s) {
       const int mid = (lo + hi + 1) >> 1;
       if (cpre[mid] <= c) lo = mid; else hi = mid - 1;
     }
-    const u32 b = (u32)lo;
+    b = (u32)lo;
     const u32 first = (c - cpre[b]) * FINE_ROUND;
     const u32 cnt_b = min(bs.cursor[b], bs.capb);
-    const u32 m = min((u32)FINE_ROUND, cnt_b - first);
-    const u64* src = bs.keys + (u64)b * bs.capb + first;
+    m = min((u32)FINE_ROUND, cnt_b - first);
+    src = bs.keys + (u64)b * bs.capb + first;
+  };
+  u64 nkey[R];
+  u32 nb = 0, nm = 0;
+  if (blockIdx.x < n_chunks) {
+    const u64* src;
+    locate(blockIdx.x, nb, nm, src);
+#pragma unroll
+    for (int q = 0; q < R; ++q) { const u32 i = q * TILE_THREADS + t; nkey[q] = (i < nm) ? __ldg(src + i) : 0ULL; }
+  }
+  for (u32 c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+    const u32 b = nb, m = nm;
+    u64 key[R];
+#pragma unroll
+    for (int q = 0; q < R; ++q) key[q] = nkey[q];
+    if (c + gridDim.x < n_chunks) {
+      const u64* src;
+      locate(c + gridDim.x, nb, nm, src);
+#pragma unroll
+      for (int q = 0; q < R; ++q) { const u32 i = q * TILE_THREADS + t; nkey[q] = (i < nm) ? __ldg(src + i) : 0ULL; }
+    }
     for (u32 f = t; f < F; f += TILE_THREADS) hist[f] = 0;
     __syncthreads();
-    u64 key[R];
     u32 fid[R], rank[R];
 #pragma unroll
     for (int q = 0; q < R; ++q) {
       const u32 i = q * TILE_THREADS + t;
       fid[q] = BKT_NONE;
       if (i < m) {
-        key[q] = __ldg(src + i);
         Key<1> kk; kk.w[0] = key[q];
         const u64 h = slot_hash<K>(kk);
         fid[q] = (u32)(h >> (64 - LOG_BUCKETS - fs.log_f)) & (F - 1);
@@ -289,31 +327,38 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
 // A probe that runs off the end of the segment "spills": the key is appended to the overflow region
 // and inserted afterwards by k_insert_overflow with global atomics, which continues the linear probe
 // into the next segment exactly as table_upsert would have.
+static constexpr int SEG_THREADS = 512;
 template <int K, int HASH>
-__global__ void __launch_bounds__(TILE_THREADS)
+__global__ void __launch_bounds__(SEG_THREADS)
 k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, const u32 n_segs, u32* __restrict__ perr) {
   static_assert(K <= 32, "segment path is built for one-word keys");
   extern __shared__ __align__(16) unsigned char seg_raw[];
   Slot<1>* seg = reinterpret_cast<Slot<1>*>(seg_raw);
+  constexpr int U = 4;                                    // keys per thread in flight
   const u32 SEG = 1u << log_seg;
   const int tid = threadIdx.x;
   u32 n_new = 0;
   for (u32 s = blockIdx.x; s < n_segs; s += gridDim.x) {
     const u32 cnt = min(fs.cursor[s], fs.capf);
     if (cnt == 0) continue;                               // block-uniform
-    uint4* gseg = reinterpret_cast<uint4*>(reinterpret_cast<Slot<1>*>(t.slots) + ((u64)s << log_seg));
-    for (u32 i = tid; i < SEG; i += TILE_THREADS) reinterpret_cast<uint4*>(seg)[i] = gseg[i];
-    __syncthreads();
     const u64* src = fs.keys + (u64)s * fs.capf;
-    for (u32 i0 = 0; i0 < cnt; i0 += 4 * TILE_THREADS) {
-      u64 kq[4];
+    u64 nk[U];                                            // first keys are requested before the segment is loaded
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const u32 i = i0 + q * TILE_THREADS + tid;
-        kq[q] = (i < cnt) ? __ldg(src + i) : KEY_EMPTY_TOP;
+    for (int q = 0; q < U; ++q) { const u32 i = q * SEG_THREADS + tid; nk[q] = (i < cnt) ? __ldg(src + i) : KEY_EMPTY_TOP; }
+    uint4* gseg = reinterpret_cast<uint4*>(reinterpret_cast<Slot<1>*>(t.slots) + ((u64)s << log_seg));
+    for (u32 i = tid; i < SEG; i += SEG_THREADS) reinterpret_cast<uint4*>(seg)[i] = gseg[i];
+    __syncthreads();
+    for (u32 i0 = 0; i0 < cnt; i0 += U * SEG_THREADS) {
+      u64 kq[U];
+#pragma unroll
+      for (int q = 0; q < U; ++q) kq[q] = nk[q];
+#pragma unroll
+      for (int q = 0; q < U; ++q) {                       // next batch in flight while this one probes
+        const u32 i = i0 + (U + q) * SEG_THREADS + tid;
+        nk[q] = (i < cnt) ? __ldg(src + i) : KEY_EMPTY_TOP;
       }
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
+      for (int q = 0; q < U; ++q) {
         const u64 key = kq[q];
         if (key == KEY_EMPTY_TOP) continue;
         Key<1> kk; kk.w[0] = key;
@@ -335,7 +380,7 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
       }
     }
     __syncthreads();
-    for (u32 i = tid; i < SEG; i += TILE_THREADS) gseg[i] = reinterpret_cast<const uint4*>(seg)[i];
+    for (u32 i = tid; i < SEG; i += SEG_THREADS) gseg[i] = reinterpret_cast<const uint4*>(seg)[i];
     __syncthreads();
   }
   n_new = warp_sum(n_new);

@@ -111,7 +111,7 @@ struct OpsImpl {
         if (e != cudaSuccess) return (int)e;
       }
       unsigned grid = n_segs < 148u * 64u ? n_segs : 148u * 64u;
-      k_insert_segments<K, HASH><<<grid, TILE_THREADS, smem, st>>>(t, fsink, bsink, log_seg, n_segs, perr);
+      k_insert_segments<K, HASH><<<grid, SEG_THREADS, smem, st>>>(t, fsink, bsink, log_seg, n_segs, perr);
     }
     return 0;
   }
