@@ -372,7 +372,9 @@ static int bucket_readback(kmi_index* idx, const BucketSink& bs, u64* host_ctr, 
 static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 size_now, const std::vector<u32>& reg) {
   if (n_keys == 0) return KMI_OK;
   // distinct keys after this insert: at most size + n_keys, and (6 sigma) at most 1.05 * HLL + keys the HLL never saw
-  const u64 by_hll = (u64)(hll_estimate(reg.data()) * 1.05) + 1024 + idx->non_hll_upper;
+  // (the registers see a 1/HLL_SAMPLE hash-sampled subset: scale back, add 6 sigma of the sampling error)
+  const double est = hll_estimate(reg.data()) * (double)HLL_SAMPLE;
+  const u64 by_hll = (u64)(est * 1.05 + 6.0 * std::sqrt(est * (double)HLL_SAMPLE)) + 4096 + idx->non_hll_upper;
   const u64 need = std::min(size_now + n_keys, std::max(by_hll, size_now));
   if (!idx->slots || (double)need > idx->cap * MAX_LOAD) {
     u64 want = pow2_at_least((u64)(need / MAX_LOAD) + 1);

@@ -41,8 +41,7 @@ template <int NW> struct BucketSmem {
   static constexpr int R = BktRound<NW>::R;
   static constexpr int ROUND_KEYS = TILE_THREADS * R;
   u64 sorted[ROUND_KEYS * NW];
-  u32 hist[N_BUCKETS];
-  u32 scan[N_BUCKETS];
+  u32 hist[N_BUCKETS];    // counts while ranking, exclusive prefix afterwards
   u32 delta[N_BUCKETS];
   u32 tmp[TILE_THREADS / 32 + 1];
   uint8_t sbid[ROUND_KEYS];
@@ -50,48 +49,86 @@ template <int NW> struct BucketSmem {
 
 __device__ __forceinline__ u32 bucket_of(u64 store_hash) { return (u32)(store_hash >> (64 - LOG_BUCKETS)); }
 
-// HyperLogLog update from the store hash: register = low HLL_P bits, rank from the 42 bits above
-// them (the top 8 bits pick the bucket and stay out of it).
+// HyperLogLog over a 1/HLL_SAMPLE hash-sampled subset of the keys (distinct sampling: a key is in the
+// subset iff HLL_SAMPLE_BITS bits of its hash are zero, so the subset's distinct count is 1/HLL_SAMPLE of the
+// total and the estimate is scaled back on the host). Register = low HLL_P bits, rank from the bits
+// above the sample bits (the top 8 bits pick the bucket and stay out of it). Sampling keeps the global
+// read + atomicMax off the per-k-mer path: a warp skips the update unless one of its lanes is sampled.
+static constexpr int HLL_SAMPLE_BITS = 6;
+static constexpr int HLL_SAMPLE = 1 << HLL_SAMPLE_BITS;
 __device__ __forceinline__ void hll_update(u32* __restrict__ hll, u64 h) {
   h ^= h >> 29;                                          // slot_hash mixes upwards: fold the high half into the low bits
+  if ((u32)(h >> HLL_P) & (HLL_SAMPLE - 1)) return;
   const u32 reg = (u32)h & (HLL_M - 1);
-  const u64 w = (h >> HLL_P) << (HLL_P + LOG_BUCKETS);   // 42 significant bits, left aligned
-  const u32 rank = (u32)__clzll(w | (1ULL << (HLL_P + LOG_BUCKETS - 1))) + 1u;
+  constexpr int USED = HLL_P + HLL_SAMPLE_BITS;
+  const u64 w = (h >> USED) << (USED + LOG_BUCKETS);     // 64 - USED - LOG_BUCKETS significant bits, left aligned
+  const u32 rank = (u32)__clzll(w | (1ULL << (USED + LOG_BUCKETS - 1))) + 1u;
   if (hll[reg] < rank) atomicMax(hll + reg, rank);       // the plain read may be stale: then the max is redundant, never wrong
 }
 
-// One round: every thread brings up to R keys (bkt[q] == BKT_NONE: no key). The block sorts them
-// by bucket in shared memory, reserves one run per non-empty bucket with a single atomicAdd, and
-// writes the runs coalesced. Keys that do not fit their bucket go to the overflow region; if that is
-// full too, PERR_OVERFLOW is raised and the host redoes the chunk on the direct path.
+// block scan without the trailing barrier of block_excl_scan: the caller guarantees a barrier between
+// this call's reads of tmp and the next write to it
+__device__ __forceinline__ u32 block_excl_scan_nb(u32 v, u32* tmp, u32& total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  u32 inc = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    u32 o = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += o;
+  }
+  if (lane == 31) tmp[warp] = inc;
+  __syncthreads();
+  u32 w = (lane < TILE_THREADS / 32) ? tmp[lane] : 0;    // every warp scans the 8 warp totals itself
+  u32 winc = w;
+#pragma unroll
+  for (int d = 1; d < TILE_THREADS / 32; d <<= 1) {
+    u32 o = __shfl_up_sync(0xffffffffu, winc, d);
+    if (lane >= d) winc += o;
+  }
+  total = __shfl_sync(0xffffffffu, winc, TILE_THREADS / 32 - 1);
+  const u32 wex = __shfl_sync(0xffffffffu, winc - w, warp);
+  return wex + inc - v;
+}
+
+// zero the histogram; call once per kernel before the first bucket_round
+template <int NW> __device__ __forceinline__ void bucket_init(BucketSmem<NW>& sm) {
+  sm.hist[threadIdx.x] = 0;
+  __syncthreads();
+}
+
+// One round: every thread brings up to R keys (bkt[q] == BKT_NONE: no key). The block ranks them by
+// bucket in shared memory, reserves one run per non-empty bucket with a single global atomicAdd (in
+// flight while the keys are sorted), and writes the runs coalesced. Keys that do not fit their bucket
+// go to the overflow region; if that is full too, PERR_OVERFLOW is raised and the host redoes the chunk
+// on the direct path. (Ranking by ballots over the digit bits with warp-private counters instead of
+// shared-memory atomics was measured slower: parse+scatter 11.8 vs 9.4 ms, fine scatter 7.5 vs 5.6 ms.)
 template <int NW>
 __device__ __forceinline__ void bucket_round(const BucketSink& bs, BucketSmem<NW>& sm, const Key<NW> (&key)[BktRound<NW>::R],
                                              const u32 (&bkt)[BktRound<NW>::R], u32* __restrict__ perr) {
   constexpr int R = BktRound<NW>::R;
   const int t = threadIdx.x;
-  sm.hist[t] = 0;
-  __syncthreads();
   u32 rank[R];
 #pragma unroll
   for (int q = 0; q < R; ++q) rank[q] = (bkt[q] != BKT_NONE) ? atomicAdd(&sm.hist[bkt[q]], 1u) : 0u;
   __syncthreads();
   const u32 cnt = sm.hist[t];
+  const u32 gbase = cnt ? atomicAdd(bs.cursor + t, cnt) : 0u;    // in flight during the scan and the sort
   u32 total;
-  const u32 ex = block_excl_scan(cnt, sm.tmp, total);
-  sm.scan[t] = ex;
-  const u32 gbase = cnt ? atomicAdd(bs.cursor + t, cnt) : 0u;
-  sm.delta[t] = gbase - ex;
+  const u32 ex = block_excl_scan_nb(cnt, sm.tmp, total);
+  sm.hist[t] = ex;
   __syncthreads();
 #pragma unroll
   for (int q = 0; q < R; ++q) {
     if (bkt[q] != BKT_NONE) {
-      const u32 pos = sm.scan[bkt[q]] + rank[q];
+      const u32 pos = sm.hist[bkt[q]] + rank[q];
       if (NW == 1) sm.sorted[pos] = key[q].w[0];
       else reinterpret_cast<ulonglong2*>(sm.sorted)[pos] = make_ulonglong2(key[q].w[0], key[q].w[NW - 1]);
       sm.sbid[pos] = (uint8_t)bkt[q];
     }
   }
+  sm.delta[t] = gbase - ex;
   __syncthreads();
+  sm.hist[t] = 0;                                         // dead now: cleared for the next round
   for (u32 r = t; r < total; r += TILE_THREADS) {
     const u32 b = sm.sbid[r];
     u32 at = sm.delta[b] + r;
@@ -115,6 +152,7 @@ k_scatter_keys(const u64* __restrict__ keys, u64 n, BucketSink bs, u32* __restri
   constexpr int R = BktRound<NW>::R;
   __shared__ BucketSmem<NW> sm;
   const u64 per_round = (u64)TILE_THREADS * R;
+  bucket_init<NW>(sm);
   Key<NW> nkey[R];                                       // next round's keys, requested one round ahead
   {
     const u64 base = (u64)blockIdx.x * per_round;
@@ -213,18 +251,26 @@ struct FineSink {
   u32 log_f;
 };
 
+// dynamic shared memory of k_scatter_fine for 2^log_f fine buckets
+__host__ __device__ inline size_t scatter_fine_smem(u32 log_f) {
+  const size_t F = (size_t)1 << log_f;
+  return FINE_ROUND * sizeof(u64) + 2 * F * sizeof(u32) + FINE_ROUND * sizeof(unsigned short);
+}
+
 template <int K, int HASH>
-__global__ void __launch_bounds__(TILE_THREADS)
+__global__ void __launch_bounds__(TILE_THREADS, 4)
 k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
   static_assert(K <= 32, "segment path is built for one-word keys");
-  __shared__ u64 sorted[FINE_ROUND];
-  __shared__ u32 hist[1 << MAX_LOG_F], scan[1 << MAX_LOG_F], delta[1 << MAX_LOG_F];
-  __shared__ unsigned short sbid[FINE_ROUND];
+  extern __shared__ __align__(16) unsigned char fine_raw[];
   __shared__ u32 cpre[N_BUCKETS + 1];
   __shared__ u32 tmp[TILE_THREADS / 32 + 1];
   constexpr int R = FINE_ROUND / TILE_THREADS;
   const int t = threadIdx.x;
   const u32 F = 1u << fs.log_f;
+  u64* sorted = reinterpret_cast<u64*>(fine_raw);                       // FINE_ROUND keys
+  u32* hist = reinterpret_cast<u32*>(sorted + FINE_ROUND);             // F: counts while ranking, exclusive prefix afterwards
+  u32* delta = hist + F;                                                // F
+  unsigned short* sbid = reinterpret_cast<unsigned short*>(delta + F);  // FINE_ROUND
   const u32 EPT = F >= TILE_THREADS ? F / TILE_THREADS : 1u;   // histogram entries per thread
   const u32 my_cnt = min(bs.cursor[t], bs.capb);
   u32 n_chunks;
@@ -233,9 +279,10 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
     cpre[t] = ex;
     if (t == 0) cpre[N_BUCKETS] = n_chunks;
   }
+  for (u32 f = t; f < F; f += TILE_THREADS) hist[f] = 0;
   __syncthreads();
   // software pipeline: the keys of the NEXT chunk are requested before this chunk is ranked, so the
-  // global-load latency (the kernel's main stall before: profiles/r01_*) hides behind a whole round
+  // global-load latency hides behind a whole round
   auto locate = [&](u32 c, u32& b, u32& m, const u64*& src) {
     int lo = 0, hi = N_BUCKETS - 1;                       // largest b with cpre[b] <= c and a non-empty bucket
 #pragma unroll
@@ -268,8 +315,6 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
 #pragma unroll
       for (int q = 0; q < R; ++q) { const u32 i = q * TILE_THREADS + t; nkey[q] = (i < nm) ? __ldg(src + i) : 0ULL; }
     }
-    for (u32 f = t; f < F; f += TILE_THREADS) hist[f] = 0;
-    __syncthreads();
     u32 fid[R], rank[R];
 #pragma unroll
     for (int q = 0; q < R; ++q) {
@@ -287,12 +332,12 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
       u32 local = 0;
       for (u32 e = 0; e < EPT; ++e) { const u32 f = t * EPT + e; if (f < F) local += hist[f]; }
       u32 total;
-      u32 ex = block_excl_scan(local, tmp, total);
+      u32 ex = block_excl_scan_nb(local, tmp, total);
       for (u32 e = 0; e < EPT; ++e) {
         const u32 f = t * EPT + e;
         if (f < F) {
           const u32 cnt = hist[f];
-          scan[f] = ex;
+          hist[f] = ex;
           if (cnt) delta[f] = atomicAdd(fs.cursor + ((u64)b << fs.log_f) + f, cnt) - ex;
           ex += cnt;
         }
@@ -302,17 +347,19 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
 #pragma unroll
     for (int q = 0; q < R; ++q) {
       if (fid[q] != BKT_NONE) {
-        const u32 pos = scan[fid[q]] + rank[q];
+        const u32 pos = hist[fid[q]] + rank[q];
         sorted[pos] = key[q];
         sbid[pos] = (unsigned short)fid[q];
       }
     }
     __syncthreads();
+    for (u32 f = t; f < F; f += TILE_THREADS) hist[f] = 0;
+    const u64 region0 = (u64)b << fs.log_f;
     for (u32 r = t; r < m; r += TILE_THREADS) {
       const u32 f = sbid[r];
       const u32 at = delta[f] + r;
       if (at < fs.capf) {
-        fs.keys[(((u64)b << fs.log_f) + f) * fs.capf + at] = sorted[r];
+        fs.keys[(region0 + f) * fs.capf + at] = sorted[r];
       } else {
         const u32 o = atomicAdd(bs.cursor + N_BUCKETS, 1u);
         if (o < bs.ovf_cap) bs.keys[(u64)N_BUCKETS * bs.capb + o] = sorted[r];

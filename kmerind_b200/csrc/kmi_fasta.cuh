@@ -65,8 +65,8 @@ struct FaGroup {
 __device__ __forceinline__ FaGroup fasta_lines(const uint4& v, u32 nl, bool prev_nl) {
   FaGroup f;
   f.ls = ((nl << 1) | (prev_nl ? 1u : 0u)) & 0xFFFFu;
-  u32 h = mask16(__vcmpeq4(v.x, 0x3E3E3E3Eu) | __vcmpeq4(v.x, 0x3B3B3B3Bu), __vcmpeq4(v.y, 0x3E3E3E3Eu) | __vcmpeq4(v.y, 0x3B3B3B3Bu),
-                 __vcmpeq4(v.z, 0x3E3E3E3Eu) | __vcmpeq4(v.z, 0x3B3B3B3Bu), __vcmpeq4(v.w, 0x3E3E3E3Eu) | __vcmpeq4(v.w, 0x3B3B3B3Bu));
+  u32 h = mask16(eq4(v.x, 0x3E3E3E3Eu) | eq4(v.x, 0x3B3B3B3Bu), eq4(v.y, 0x3E3E3E3Eu) | eq4(v.y, 0x3B3B3B3Bu),
+                 eq4(v.z, 0x3E3E3E3Eu) | eq4(v.z, 0x3B3B3B3Bu), eq4(v.w, 0x3E3E3E3Eu) | eq4(v.w, 0x3B3B3B3Bu));
   f.hdr = f.ls & h;
   return f;
 }

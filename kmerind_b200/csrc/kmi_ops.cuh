@@ -100,8 +100,11 @@ struct OpsImpl {
     k_rehash<K, HASH><<<grid_for(n_old, 256, 148u * 32u), 256, 0, st>>>(reinterpret_cast<const S*>(old_slots), n_old, t);
   }
   static void scatter_fine(cudaStream_t st, BucketSink bsink, FineSink fsink, u32* perr, u64 n_hint) {
-    if constexpr (NW == 1)
-      k_scatter_fine<K, HASH><<<grid_for(n_hint ? n_hint : 1, FINE_ROUND, 148u * 4u), TILE_THREADS, 0, st>>>(bsink, fsink, perr);
+    if constexpr (NW == 1) {
+      const size_t smem = scatter_fine_smem(fsink.log_f);
+      if (smem > 48 * 1024) cudaFuncSetAttribute(k_scatter_fine<K, HASH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      k_scatter_fine<K, HASH><<<grid_for(n_hint ? n_hint : 1, FINE_ROUND, 148u * 4u), TILE_THREADS, smem, st>>>(bsink, fsink, perr);
+    }
   }
   static int insert_segments(cudaStream_t st, TableView t, FineSink fsink, BucketSink bsink, u32 log_seg, u32 n_segs, u32* perr) {
     if constexpr (NW == 1) {

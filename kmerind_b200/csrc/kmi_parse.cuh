@@ -26,18 +26,20 @@
 namespace kmi {
 
 // ---- byte-parallel classification of one 16-byte group ------------------------------------
-__device__ __forceinline__ u32 nib(u32 bytemask) {  // 0xFF/0x00 per byte -> 4 bits, byte 0 -> bit 0
-  return ((bytemask & 0x08040201u) * 0x01010101u) >> 24;
-}
+// zb: 0x80 in every byte of x that is zero (exact, no carries between bytes); nib80 gathers those four
+// flag bits into a nibble, byte 0 -> bit 0.
+__device__ __forceinline__ u32 zb(u32 x) { return ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x | 0x7F7F7F7Fu); }
+__device__ __forceinline__ u32 nib80(u32 z) { return ((z >> 7) * 0x01020408u) >> 24; }
 __device__ __forceinline__ u32 mask16(u32 a, u32 b, u32 c, u32 d) {
-  return nib(a) | (nib(b) << 4) | (nib(c) << 8) | (nib(d) << 12);
+  return nib80(a) | (nib80(b) << 4) | (nib80(c) << 8) | (nib80(d) << 12);
 }
+__device__ __forceinline__ u32 eq4(u32 w, u32 c4) { return zb(w ^ c4); }
 // 2-bit codes of 4 bytes packed into 8 bits, byte 0 in the two most significant bits.
 // DNA::FROM_ASCII: A/a 0, C/c 1, G/g 2, T/t 3, everything else 0.
 __device__ __forceinline__ u32 codes4(u32 w) {
-  u32 f = w & 0xDFDFDFDFu;  // fold case: only 'c','g','t' fold onto 'C','G','T'
-  u32 c = (__vcmpeq4(f, 0x43434343u) & 0x01010101u) | (__vcmpeq4(f, 0x47474747u) & 0x02020202u) |
-          (__vcmpeq4(f, 0x54545454u) & 0x03030303u);
+  const u32 f = w & 0xDFDFDFDFu;  // fold case: only 'c','g','t' fold onto 'C','G','T'
+  const u32 zc = eq4(f, 0x43434343u), zg = eq4(f, 0x47474747u), zt = eq4(f, 0x54545454u);
+  const u32 c = ((zc | zt) >> 7) | ((zg | zt) >> 6);
   return (c * 0x40100401u) >> 24;
 }
 struct Group {
@@ -46,16 +48,23 @@ struct Group {
   u32 nl;     // bit b: byte b is '\n'
   u32 nmask;  // bit b: byte b is 'N' or 'n'
 };
+__device__ __forceinline__ u32 eol16(const uint4& v) {
+  return mask16(eq4(v.x, 0x0A0A0A0Au) | eq4(v.x, 0x0D0D0D0Du), eq4(v.y, 0x0A0A0A0Au) | eq4(v.y, 0x0D0D0D0Du),
+                eq4(v.z, 0x0A0A0A0Au) | eq4(v.z, 0x0D0D0D0Du), eq4(v.w, 0x0A0A0A0Au) | eq4(v.w, 0x0D0D0D0Du));
+}
+__device__ __forceinline__ u32 codes16(const uint4& v) {
+  return (codes4(v.x) << 24) | (codes4(v.y) << 16) | (codes4(v.z) << 8) | codes4(v.w);
+}
+__device__ __forceinline__ u32 nmask16(const uint4& v) {
+  return mask16(eq4(v.x & 0xDFDFDFDFu, 0x4E4E4E4Eu), eq4(v.y & 0xDFDFDFDFu, 0x4E4E4E4Eu),
+                eq4(v.z & 0xDFDFDFDFu, 0x4E4E4E4Eu), eq4(v.w & 0xDFDFDFDFu, 0x4E4E4E4Eu));
+}
 __device__ __forceinline__ Group classify(const uint4& v) {
   Group g;
-  g.codes = (codes4(v.x) << 24) | (codes4(v.y) << 16) | (codes4(v.z) << 8) | codes4(v.w);
-  u32 a = __vcmpeq4(v.x, 0x0A0A0A0Au), b = __vcmpeq4(v.y, 0x0A0A0A0Au), c = __vcmpeq4(v.z, 0x0A0A0A0Au),
-      d = __vcmpeq4(v.w, 0x0A0A0A0Au);
-  g.nl = mask16(a, b, c, d);
-  g.eol = g.nl | mask16(__vcmpeq4(v.x, 0x0D0D0D0Du), __vcmpeq4(v.y, 0x0D0D0D0Du),
-                        __vcmpeq4(v.z, 0x0D0D0D0Du), __vcmpeq4(v.w, 0x0D0D0D0Du));
-  g.nmask = mask16(__vcmpeq4(v.x & 0xDFDFDFDFu, 0x4E4E4E4Eu), __vcmpeq4(v.y & 0xDFDFDFDFu, 0x4E4E4E4Eu),
-                   __vcmpeq4(v.z & 0xDFDFDFDFu, 0x4E4E4E4Eu), __vcmpeq4(v.w & 0xDFDFDFDFu, 0x4E4E4E4Eu));
+  g.codes = codes16(v);
+  g.nl = mask16(eq4(v.x, 0x0A0A0A0Au), eq4(v.y, 0x0A0A0A0Au), eq4(v.z, 0x0A0A0A0Au), eq4(v.w, 0x0A0A0A0Au));
+  g.eol = g.nl | mask16(eq4(v.x, 0x0D0D0D0Du), eq4(v.y, 0x0D0D0D0Du), eq4(v.z, 0x0D0D0D0Du), eq4(v.w, 0x0D0D0D0Du));
+  g.nmask = nmask16(v);
   return g;
 }
 // 16 bytes at offset `off` of a 16-byte aligned buffer of n bytes; bytes past the end read as '\n'
@@ -94,8 +103,7 @@ __global__ void __launch_bounds__(TILE_THREADS) k_fastq_count_lines(const uint8_
   u32 cnt = 0;
   if (off < n) {
     uint4 v = load_group(bytes, off, n);
-    Group g = classify(v);
-    cnt = __popc(line_starts(g.eol, prev_is_eol(bytes, off, n)));
+    cnt = __popc(line_starts(eol16(v), prev_is_eol(bytes, off, n)));
   }
   u32 total;
   block_excl_scan(cnt, tmp, total);
@@ -281,17 +289,17 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
       // every byte of the group is on line (idx-1); sequence lines are 1 mod 4
       flags = (idx != 0 && ((idx - 1) & 3u) == 1u) ? (~g.eol & 0xFFFFu) : 0u;
     } else {
+      // walk the line starts of the group: bytes [lo, hi) lie on line (idx-1); a start at hi opens line idx
       flags = 0;
-      u32 err = 0;
-#pragma unroll
-      for (int b = 0; b < GROUP_BYTES; ++b) {
-        if ((ls >> b) & 1u) {
-          u32 c = byte_of(v, b);
-          if ((idx & 3u) == 0u && c != '@') err |= PERR_NO_AT;
-          if ((idx & 3u) == 2u && c != '+') err |= PERR_NO_PLUS;
-          ++idx;
-        }
-        if (idx != 0 && ((idx - 1) & 3u) == 1u) flags |= (1u << b);
+      u32 err = 0, m = ls, lo = 0;
+      for (;;) {
+        const u32 hi = m ? (u32)__ffs(m) - 1u : (u32)GROUP_BYTES;
+        if ((idx & 3u) == 2u) flags |= (1u << hi) - (1u << lo);
+        if (!m) break;
+        const u32 c = byte_of(v, (int)hi);
+        if ((idx & 3u) == 0u && c != '@') err |= PERR_NO_AT;
+        if ((idx & 3u) == 2u && c != '+') err |= PERR_NO_PLUS;
+        ++idx; lo = hi; m &= m - 1;
       }
       flags &= ~g.eol;
       if (err) atomicOr(perr, err);
@@ -302,10 +310,14 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
       u32 hidx = tile_first + total_ls;
       for (int q = 0; q < t; ++q) hidx += s_aux[q];
       u32 hflags = 0;
-#pragma unroll
-      for (int b = 0; b < GROUP_BYTES; ++b) {
-        if ((hls >> b) & 1u) ++hidx;
-        if (hidx != 0 && ((hidx - 1) & 3u) == 1u) hflags |= (1u << b);
+      {
+        u32 m = hls, lo = 0;
+        for (;;) {
+          const u32 hi = m ? (u32)__ffs(m) - 1u : (u32)GROUP_BYTES;
+          if ((hidx & 3u) == 2u) hflags |= (1u << hi) - (1u << lo);
+          if (!m) break;
+          ++hidx; lo = hi; m &= m - 1;
+        }
       }
       hflags &= ~heol;
       if (NSPLIT) hflags &= ~hn;
@@ -344,6 +356,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   if (SINK >= 2) {
     constexpr int R = BktRound<NW>::R;
     BucketSmem<NW>& sm = reinterpret_cast<BucketSmem<NW>&>(s_bkt);
+    bucket_init<NW>(sm);
     for (u32 c0 = 0; c0 < total; c0 += TILE_THREADS * R) {   // block-uniform trip count
       Key<NW> key[R];
       u32 bkt[R];
