@@ -49,13 +49,14 @@ def load_library(build_if_missing=False):
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
+    path = os.environ.get("KMI_LIB", LIB_PATH)   # tuning experiments: another build of the same library
+    if not os.path.exists(path):
         if build_if_missing:
             from . import build as _b
             _b.build()
         else:
             raise ImportError("libkmi.so is not built (run python -m kmerind_b200.build); there is no CPU path")
-    lib = ctypes.CDLL(LIB_PATH)
+    lib = ctypes.CDLL(path)
     lib.kmi_last_error.restype = ctypes.c_char_p
     lib.kmi_synth_record_bytes.restype = _SZ
     lib.kmi_synth_record_bytes.argtypes = [ctypes.c_uint32]

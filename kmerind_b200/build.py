@@ -10,7 +10,9 @@ from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OUT = os.path.join(HERE, "libkmi.so")
+# KMI_VARIANT=name (tuning experiments only): separate object directory and libkmi_name.so, picked up by KMI_LIB
+VARIANT = os.environ.get("KMI_VARIANT", "")
+OUT = os.path.join(HERE, "libkmi_%s.so" % VARIANT if VARIANT else "libkmi.so")
 KS = (15, 21, 31, 35, 47, 63)
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo",
@@ -33,7 +35,7 @@ def _run(cmd):
 def build(force=False, verbose=False):
     hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh")]
     hdrs.append(os.path.join(HERE, "..", "include", "kmi.h"))
-    objdir = os.path.join(CSRC, "build")
+    objdir = os.path.join(CSRC, "build", VARIANT) if VARIANT else os.path.join(CSRC, "build")
     os.makedirs(objdir, exist_ok=True)
     jobs = []
     objs = []

@@ -359,6 +359,8 @@ static void harvest_commit_times(kmi_index* idx) {
 // one synchronisation per round: counters + HLL registers
 static int bucket_readback(kmi_index* idx, const BucketSink& bs, u64* host_ctr, std::vector<u32>& reg) {
   reg.resize(HLL_M);
+  idx->ops->hll_buckets(idx->stream, bs);
+  idx->launches++;
   CU(cudaMemcpyAsync(reg.data(), bs.hll, sizeof(u32) * HLL_M, cudaMemcpyDeviceToHost, idx->stream));
   CU(cudaMemcpyAsync(host_ctr, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
   CU(cudaMemcpyAsync(idx->h_cursor, bs.cursor, sizeof(u32) * (N_BUCKETS + 1), cudaMemcpyDeviceToHost, idx->stream));

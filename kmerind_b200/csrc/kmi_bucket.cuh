@@ -49,20 +49,21 @@ template <int NW> struct BucketSmem {
 
 __device__ __forceinline__ u32 bucket_of(u64 store_hash) { return (u32)(store_hash >> (64 - LOG_BUCKETS)); }
 
-// HyperLogLog over a 1/HLL_SAMPLE hash-sampled subset of the keys (distinct sampling: a key is in the
-// subset iff HLL_SAMPLE_BITS bits of its hash are zero, so the subset's distinct count is 1/HLL_SAMPLE of the
-// total and the estimate is scaled back on the host). Register = low HLL_P bits, rank from the bits
-// above the sample bits (the top 8 bits pick the bucket and stay out of it). Sampling keeps the global
-// read + atomicMax off the per-k-mer path: a warp skips the update unless one of its lanes is sampled.
-static constexpr int HLL_SAMPLE_BITS = 6;
-static constexpr int HLL_SAMPLE = 1 << HLL_SAMPLE_BITS;
+// HyperLogLog over a 1/HLL_SAMPLE hash-sampled subset of the keys (distinct sampling: the keys whose
+// hash prefix names one of HLL_SAMPLE_BUCKETS evenly spaced coarse buckets hold 1/HLL_SAMPLE of the distinct
+// keys; the estimate is scaled back on the host). Because the sample IS a set of buckets, the registers are
+// filled by a small kernel over those buckets after the scatter (k_hll_buckets, ~0.1 GB read) and the
+// per-k-mer path carries no HLL work at all (it used to cost 13 % of the parser: profiles/r01_*).
+// Register = low HLL_P bits of the folded hash, rank from the 42 bits above them (the top 8 bits pick the
+// bucket and stay out of it).
+static constexpr int HLL_SAMPLE_BUCKETS = 4;
+static constexpr int HLL_SAMPLE = N_BUCKETS / HLL_SAMPLE_BUCKETS;
+__device__ __forceinline__ bool hll_sampled(u32 bucket) { return (bucket & (HLL_SAMPLE - 1)) == 0; }
 __device__ __forceinline__ void hll_update(u32* __restrict__ hll, u64 h) {
   h ^= h >> 29;                                          // slot_hash mixes upwards: fold the high half into the low bits
-  if ((u32)(h >> HLL_P) & (HLL_SAMPLE - 1)) return;
   const u32 reg = (u32)h & (HLL_M - 1);
-  constexpr int USED = HLL_P + HLL_SAMPLE_BITS;
-  const u64 w = (h >> USED) << (USED + LOG_BUCKETS);     // 64 - USED - LOG_BUCKETS significant bits, left aligned
-  const u32 rank = (u32)__clzll(w | (1ULL << (USED + LOG_BUCKETS - 1))) + 1u;
+  const u64 w = (h >> HLL_P) << (HLL_P + LOG_BUCKETS);   // 42 significant bits, left aligned
+  const u32 rank = (u32)__clzll(w | (1ULL << (HLL_P + LOG_BUCKETS - 1))) + 1u;
   if (hll[reg] < rank) atomicMax(hll + reg, rank);       // the plain read may be stale: then the max is redundant, never wrong
 }
 
@@ -104,12 +105,16 @@ template <int NW> __device__ __forceinline__ void bucket_init(BucketSmem<NW>& sm
 // shared-memory atomics was measured slower: parse+scatter 11.8 vs 9.4 ms, fine scatter 7.5 vs 5.6 ms.)
 template <int NW>
 __device__ __forceinline__ void bucket_round(const BucketSink& bs, BucketSmem<NW>& sm, const Key<NW> (&key)[BktRound<NW>::R],
-                                             const u32 (&bkt)[BktRound<NW>::R], u32* __restrict__ perr) {
+                                             const u32 (&bkt)[BktRound<NW>::R], const u32 n_round, u32* __restrict__ perr) {
+  // n_round (block-uniform): keys of this round; slot row q (keys q*TILE_THREADS ..) is skipped whole when empty
   constexpr int R = BktRound<NW>::R;
   const int t = threadIdx.x;
   u32 rank[R];
 #pragma unroll
-  for (int q = 0; q < R; ++q) rank[q] = (bkt[q] != BKT_NONE) ? atomicAdd(&sm.hist[bkt[q]], 1u) : 0u;
+  for (int q = 0; q < R; ++q) {
+    rank[q] = 0u;
+    if ((u32)(q * TILE_THREADS) < n_round && bkt[q] != BKT_NONE) rank[q] = atomicAdd(&sm.hist[bkt[q]], 1u);
+  }
   __syncthreads();
   const u32 cnt = sm.hist[t];
   const u32 gbase = cnt ? atomicAdd(bs.cursor + t, cnt) : 0u;    // in flight during the scan and the sort
@@ -119,7 +124,7 @@ __device__ __forceinline__ void bucket_round(const BucketSink& bs, BucketSmem<NW
   __syncthreads();
 #pragma unroll
   for (int q = 0; q < R; ++q) {
-    if (bkt[q] != BKT_NONE) {
+    if ((u32)(q * TILE_THREADS) < n_round && bkt[q] != BKT_NONE) {
       const u32 pos = sm.hist[bkt[q]] + rank[q];
       if (NW == 1) sm.sorted[pos] = key[q].w[0];
       else reinterpret_cast<ulonglong2*>(sm.sorted)[pos] = make_ulonglong2(key[q].w[0], key[q].w[NW - 1]);
@@ -183,10 +188,24 @@ k_scatter_keys(const u64* __restrict__ keys, u64 n, BucketSink bs, u32* __restri
         if (CANON) key[q] = canonical<K>(key[q]);
         const u64 h = slot_hash<K>(key[q]);
         bkt[q] = bucket_of(h);
-        hll_update(bs.hll, h);
       }
     }
-    bucket_round<NW>(bs, sm, key, bkt, perr);
+    bucket_round<NW>(bs, sm, key, bkt, (u32)min((u64)per_round, n - base), perr);
+  }
+}
+
+// HLL registers from the sampled buckets (and the sampled keys of the overflow region); grid.y = sampled
+// bucket index, the last y-slice walks the overflow region
+template <int K>
+__global__ void __launch_bounds__(256) k_hll_buckets(BucketSink bs) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  const bool ovf = blockIdx.y == HLL_SAMPLE_BUCKETS;
+  const u32 b = ovf ? (u32)N_BUCKETS : blockIdx.y * HLL_SAMPLE;
+  const u32 n = ovf ? min(bs.cursor[N_BUCKETS], bs.ovf_cap) : min(bs.cursor[b], bs.capb);
+  const u64 base = (u64)b * bs.capb;
+  for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const u64 h = slot_hash<K>(load_key<NW>(bs.keys, base + i));
+    if (!ovf || hll_sampled(bucket_of(h))) hll_update(bs.hll, h);
   }
 }
 
@@ -257,8 +276,11 @@ __host__ __device__ inline size_t scatter_fine_smem(u32 log_f) {
   return FINE_ROUND * sizeof(u64) + 2 * F * sizeof(u32) + FINE_ROUND * sizeof(unsigned short);
 }
 
+#ifndef KMI_FINE_MINB
+#define KMI_FINE_MINB 4       // CTAs per SM of the (persistent) fine scatter
+#endif
 template <int K, int HASH>
-__global__ void __launch_bounds__(TILE_THREADS, 4)
+__global__ void __launch_bounds__(TILE_THREADS, KMI_FINE_MINB)
 k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
   static_assert(K <= 32, "segment path is built for one-word keys");
   extern __shared__ __align__(16) unsigned char fine_raw[];
@@ -375,54 +397,70 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
 // and inserted afterwards by k_insert_overflow with global atomics, which continues the linear probe
 // into the next segment exactly as table_upsert would have.
 static constexpr int SEG_THREADS = 512;
+// Probing is organised so that no lane waits for its neighbours' longer probe sequences: every warp owns a
+// contiguous slice of the fine bucket, keeps the next 64 keys of it in two registers per lane (coalesced
+// loads, one ahead), and a lane that has finished its key takes the next unclaimed one from that window
+// (ballot + shuffle) in the same loop iteration in which the other lanes advance their probes. A loop
+// iteration is therefore one probe for every lane, instead of max-over-lanes probes per key.
 template <int K, int HASH>
 __global__ void __launch_bounds__(SEG_THREADS)
 k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, const u32 n_segs, u32* __restrict__ perr) {
   static_assert(K <= 32, "segment path is built for one-word keys");
   extern __shared__ __align__(16) unsigned char seg_raw[];
   Slot<1>* seg = reinterpret_cast<Slot<1>*>(seg_raw);
-  constexpr int U = 4;                                    // keys per thread in flight
+  constexpr int NWARP = SEG_THREADS / 32;
   const u32 SEG = 1u << log_seg;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const u32 lt = (1u << lane) - 1u;
   u32 n_new = 0;
   for (u32 s = blockIdx.x; s < n_segs; s += gridDim.x) {
     const u32 cnt = min(fs.cursor[s], fs.capf);
     if (cnt == 0) continue;                               // block-uniform
     const u64* src = fs.keys + (u64)s * fs.capf;
-    u64 nk[U];                                            // first keys are requested before the segment is loaded
-#pragma unroll
-    for (int q = 0; q < U; ++q) { const u32 i = q * SEG_THREADS + tid; nk[q] = (i < cnt) ? __ldg(src + i) : KEY_EMPTY_TOP; }
+    const u32 per = ((cnt + NWARP * 32 - 1) / (NWARP * 32)) * 32;   // keys per warp, whole 32-key chunks
+    const u32 wb = min(cnt, (u32)warp * per), we = min(cnt, wb + per);
+    u32 nxt = wb + lane;
+    u64 buf0 = (nxt < we) ? __ldg(src + nxt) : KEY_EMPTY_TOP; nxt += 32;   // requested before the segment is loaded
+    u64 buf1 = (nxt < we) ? __ldg(src + nxt) : KEY_EMPTY_TOP; nxt += 32;
     uint4* gseg = reinterpret_cast<uint4*>(reinterpret_cast<Slot<1>*>(t.slots) + ((u64)s << log_seg));
     for (u32 i = tid; i < SEG; i += SEG_THREADS) reinterpret_cast<uint4*>(seg)[i] = gseg[i];
     __syncthreads();
-    for (u32 i0 = 0; i0 < cnt; i0 += U * SEG_THREADS) {
-      u64 kq[U];
-#pragma unroll
-      for (int q = 0; q < U; ++q) kq[q] = nk[q];
-#pragma unroll
-      for (int q = 0; q < U; ++q) {                       // next batch in flight while this one probes
-        const u32 i = i0 + (U + q) * SEG_THREADS + tid;
-        nk[q] = (i < cnt) ? __ldg(src + i) : KEY_EMPTY_TOP;
+    int remaining = (int)(we - wb);                       // keys of the slice not yet handed to a lane (warp-uniform)
+    u32 pos = 0;                                          // consumed keys of buf0
+    u64 key = KEY_EMPTY_TOP;
+    u32 li = 0;
+    for (;;) {
+      const u32 need = __ballot_sync(0xffffffffu, key == KEY_EMPTY_TOP);
+      if (need && remaining > 0) {                        // warp-uniform
+        const u32 idx = pos + __popc(need & lt);
+        const u64 k0 = __shfl_sync(0xffffffffu, buf0, idx & 31), k1 = __shfl_sync(0xffffffffu, buf1, idx & 31);
+        if (key == KEY_EMPTY_TOP) {
+          key = (idx < 32) ? k0 : k1;
+          Key<1> kk; kk.w[0] = key;
+          li = (u32)(slot_hash<K>(kk) >> t.shift) & (SEG - 1);
+        }
+        const u32 n = __popc(need);
+        pos += n; remaining -= (int)n;
+        if (pos >= 32) {
+          pos -= 32; buf0 = buf1;
+          buf1 = (nxt < we) ? __ldg(src + nxt) : KEY_EMPTY_TOP; nxt += 32;
+        }
       }
-#pragma unroll
-      for (int q = 0; q < U; ++q) {
-        const u64 key = kq[q];
-        if (key == KEY_EMPTY_TOP) continue;
-        Key<1> kk; kk.w[0] = key;
-        u32 li = (u32)(slot_hash<K>(kk) >> t.shift) & (SEG - 1);
-        for (;;) {
-          u64 cur = seg[li].key;
-          if (cur == KEY_EMPTY_TOP) {
-            cur = atomicCAS(&seg[li].key, KEY_EMPTY_TOP, key);
-            if (cur == KEY_EMPTY_TOP) { ++n_new; cur = key; }
-          }
-          if (cur == key) { atomicAdd(&seg[li].val, 1u); break; }
-          if (++li == SEG) {
-            const u32 o = atomicAdd(bs.cursor + N_BUCKETS, 1u);
-            if (o < bs.ovf_cap) bs.keys[(u64)N_BUCKETS * bs.capb + o] = key;
-            else atomicOr(perr, PERR_SPILL);
-            break;
-          }
+      if (__ballot_sync(0xffffffffu, key != KEY_EMPTY_TOP) == 0) break;
+      if (key != KEY_EMPTY_TOP) {
+        u64 cur = seg[li].key;
+        if (cur == KEY_EMPTY_TOP) {
+          cur = atomicCAS(&seg[li].key, KEY_EMPTY_TOP, key);
+          if (cur == KEY_EMPTY_TOP) { ++n_new; cur = key; }
+        }
+        if (cur == key) {
+          atomicAdd(&seg[li].val, 1u);
+          key = KEY_EMPTY_TOP;
+        } else if (++li == SEG) {
+          const u32 o = atomicAdd(bs.cursor + N_BUCKETS, 1u);
+          if (o < bs.ovf_cap) bs.keys[(u64)N_BUCKETS * bs.capb + o] = key;
+          else atomicOr(perr, PERR_SPILL);
+          key = KEY_EMPTY_TOP;
         }
       }
     }

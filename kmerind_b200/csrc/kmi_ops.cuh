@@ -15,6 +15,7 @@ struct Ops {
                       const u32* block_sums, KeySink sink, TableView table, BucketSink bsink, u64* n_kmers, u32* perr,
                       bool canon, bool nsplit, u64 tile_begin, u32 nranks);
   void (*scatter_keys)(cudaStream_t, const u64* keys, u64 n, BucketSink bsink, u32* perr, bool canon);
+  void (*hll_buckets)(cudaStream_t, BucketSink bsink);   // HLL registers from the sampled buckets (table sizing)
   void (*insert_buckets)(cudaStream_t, TableView, BucketSink bsink, u64 n_hint);
   // second level (one-word keys only; null for K > 32): fine scatter, shared-memory segment insert
   void (*scatter_fine)(cudaStream_t, BucketSink bsink, FineSink fsink, u32* perr, u64 n_hint);
@@ -74,6 +75,9 @@ struct OpsImpl {
   static void scatter_keys(cudaStream_t st, const u64* keys, u64 n, BucketSink bsink, u32* perr, bool canon) {
     if (n) k_scatter_keys<K, HASH><<<grid_for(n, TILE_THREADS * BktRound<NW>::R, 148u * 8u), TILE_THREADS, 0, st>>>(keys, n, bsink, perr, canon);
   }
+  static void hll_buckets(cudaStream_t st, BucketSink bsink) {
+    k_hll_buckets<K><<<dim3(148u * 2u, HLL_SAMPLE_BUCKETS + 1), 256, 0, st>>>(bsink);
+  }
   static void insert_buckets(cudaStream_t st, TableView t, BucketSink bsink, u64 n_hint) {
     k_insert_buckets<K, HASH><<<grid_for(n_hint ? n_hint : 1, 256, 148u * 8u), 256, 0, st>>>(t, bsink);
   }
@@ -103,7 +107,7 @@ struct OpsImpl {
     if constexpr (NW == 1) {
       const size_t smem = scatter_fine_smem(fsink.log_f);
       if (smem > 48 * 1024) cudaFuncSetAttribute(k_scatter_fine<K, HASH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      k_scatter_fine<K, HASH><<<grid_for(n_hint ? n_hint : 1, FINE_ROUND, 148u * 4u), TILE_THREADS, smem, st>>>(bsink, fsink, perr);
+      k_scatter_fine<K, HASH><<<grid_for(n_hint ? n_hint : 1, FINE_ROUND, 148u * KMI_FINE_MINB), TILE_THREADS, smem, st>>>(bsink, fsink, perr);
     }
   }
   static int insert_segments(cudaStream_t st, TableView t, FineSink fsink, BucketSink bsink, u32 log_seg, u32 n_segs, u32* perr) {
@@ -166,7 +170,7 @@ struct OpsImpl {
   static Ops make() {
     Ops o;
     o.K = K; o.NW = NW; o.hash = HASH;
-    o.fastq_kmers = fastq_kmers; o.scatter_keys = scatter_keys; o.insert_buckets = insert_buckets;
+    o.fastq_kmers = fastq_kmers; o.scatter_keys = scatter_keys; o.insert_buckets = insert_buckets; o.hll_buckets = hll_buckets;
     o.scatter_fine = scatter_fine; o.insert_segments = insert_segments; o.insert_overflow = insert_overflow; o.fasta_kmers = fasta_kmers; o.table_clear = table_clear; o.insert_keys = insert_keys; o.rehash = rehash;
     o.lookup = lookup; o.erase = erase; o.dump = dump; o.checksum = checksum; o.canonicalize = canonicalize;
     o.hash_keys = hash_keys; o.part_hist = part_hist; o.part_scatter = part_scatter; o.csr_scan_l1 = csr_scan_l1;

@@ -238,8 +238,11 @@ struct KeySink {     // dense key (+id) stream
 // SINK 2: scatter into the 256 hash-prefix buckets of kmi_bucket.cuh (the default build path)
 // SINK 3: scatter into one region per owning rank, owner = dist_hash % nranks (KeyToRank,
 //         distributed_densehash_map.hpp:148-170): the send buffers of the all-to-all, no key stream pass
+#ifndef KMI_PARSE_MINB
+#define KMI_PARSE_MINB 7      // CTAs per SM the parser is compiled for (register cap 36; measured 8.1 ms at 4, 7.2 at 6, 7.0 at 7 and 8)
+#endif
 template <int K, int HASH, int SINK>
-__global__ void __launch_bounds__(TILE_THREADS)
+__global__ void __launch_bounds__(TILE_THREADS, KMI_PARSE_MINB)
 k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ tile_lines,
               const u32* __restrict__ block_sums, KeySink sink, TableView table, BucketSink bsink,
               u64* __restrict__ n_kmers, u32* __restrict__ perr, const bool CANON, const bool NSPLIT,
@@ -249,7 +252,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   __shared__ u32 s_codes[TILE_GROUPS + 1];
   __shared__ u32 s_flags[TILE_GROUPS + 1];
   __shared__ u32 s_aux[HALO_GROUPS * 2];       // halo: line-start masks / popcounts
-  __shared__ u32 s_tmp[TILE_THREADS / 32 + 1];
+  __shared__ u32 s_tmp[TILE_THREADS / 32 + 1], s_tmp2[TILE_THREADS / 32 + 1];
   __shared__ unsigned short s_list[TILE_BYTES];
   __shared__ u64 s_base;
 
@@ -277,9 +280,9 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
 
   // -- P2: line number at the start of every group
   u32 total_ls;
-  u32 before = block_excl_scan(__popc(ls), s_tmp, total_ls);
+  u32 before = block_excl_scan_nb(__popc(ls), s_tmp, total_ls);
   const u32 tile_first = tile_lines[tile] + block_sums[tile >> 10];
-  // (block_excl_scan ends with a barrier: s_aux is visible)
+  // (the scan contains a barrier after the writes above: s_aux is visible)
 
   // -- P3: per-byte "base of a sequence line" flags; header checks at line starts
   {
@@ -333,7 +336,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   for (int q = 0; q < 5; ++q) f5[q] = s_flags[min(t + q, TILE_GROUPS)];
   u32 valid = window_all_set<K>(f5);
   u32 total;
-  u32 rank = block_excl_scan(__popc(valid), s_tmp, total);
+  u32 rank = block_excl_scan_nb(__popc(valid), s_tmp2, total);
   {
     u32 m = valid;
     while (m) {
@@ -364,6 +367,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
       for (int q = 0; q < R; ++q) {
         const u32 r = c0 + q * TILE_THREADS + t;
         bkt[q] = BKT_NONE;
+        if (c0 + q * TILE_THREADS >= total) continue;      // block-uniform: nobody has a key in this slot row
         if (r < total) {
           const u32 pos = s_list[r];
           const int gi = pos >> 4, j = pos & 15;
@@ -375,7 +379,6 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
           if (SINK == 2) {
             const u64 h = slot_hash<K>(key[q]);
             bkt[q] = bucket_of(h);
-            hll_update(bsink.hll, h);
           } else {
             u64 hs, hd;
             kmer_hashes<K, HASH>(key[q], hs, hd);
@@ -383,7 +386,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
           }
         }
       }
-      bucket_round<NW>(bsink, sm, key, bkt, perr);
+      bucket_round<NW>(bsink, sm, key, bkt, min(total - c0, (u32)(TILE_THREADS * R)), perr);
     }
     return;
   }
