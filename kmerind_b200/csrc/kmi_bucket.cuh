@@ -350,18 +350,26 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
       }
     }
     __syncthreads();
+    u32 gb1 = 0, ex1 = 0;                                 // EPT == 1: the cursor atomic stays in flight during the sort
     {
       u32 local = 0;
       for (u32 e = 0; e < EPT; ++e) { const u32 f = t * EPT + e; if (f < F) local += hist[f]; }
       u32 total;
       u32 ex = block_excl_scan_nb(local, tmp, total);
-      for (u32 e = 0; e < EPT; ++e) {
-        const u32 f = t * EPT + e;
-        if (f < F) {
-          const u32 cnt = hist[f];
-          hist[f] = ex;
-          if (cnt) delta[f] = atomicAdd(fs.cursor + ((u64)b << fs.log_f) + f, cnt) - ex;
-          ex += cnt;
+      if (EPT == 1) {
+        if ((u32)t < F) {
+          if (local) gb1 = atomicAdd(fs.cursor + ((u64)b << fs.log_f) + t, local);
+          hist[t] = ex; ex1 = ex;
+        }
+      } else {
+        for (u32 e = 0; e < EPT; ++e) {
+          const u32 f = t * EPT + e;
+          if (f < F) {
+            const u32 cnt = hist[f];
+            hist[f] = ex;
+            if (cnt) delta[f] = atomicAdd(fs.cursor + ((u64)b << fs.log_f) + f, cnt) - ex;
+            ex += cnt;
+          }
         }
       }
     }
@@ -374,6 +382,7 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
         sbid[pos] = (unsigned short)fid[q];
       }
     }
+    if (EPT == 1 && (u32)t < F) delta[t] = gb1 - ex1;
     __syncthreads();
     for (u32 f = t; f < F; f += TILE_THREADS) hist[f] = 0;
     const u64 region0 = (u64)b << fs.log_f;
@@ -397,6 +406,10 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
 // and inserted afterwards by k_insert_overflow with global atomics, which continues the linear probe
 // into the next segment exactly as table_upsert would have.
 static constexpr int SEG_THREADS = 512;
+#ifndef KMI_SEG_PF
+#define KMI_SEG_PF -1         // <0: the whole fine bucket is prefetched into L2 at segment start (-2: and the next table segment); >0: in-loop distance in chunks; 0 off
+#endif
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
 // Probing is organised so that no lane waits for its neighbours' longer probe sequences: every warp owns a
 // contiguous slice of the fine bucket, keeps the next 64 keys of it in two registers per lane (coalesced
 // loads, one ahead), and a lane that has finished its key takes the next unclaimed one from that window
@@ -422,6 +435,20 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
     u32 nxt = wb + lane;
     u64 buf0 = (nxt < we) ? __ldg(src + nxt) : KEY_EMPTY_TOP; nxt += 32;   // requested before the segment is loaded
     u64 buf1 = (nxt < we) ? __ldg(src + nxt) : KEY_EMPTY_TOP; nxt += 32;
+#if KMI_SEG_PF < 0
+    for (u32 i = tid * 16u; i < cnt; i += SEG_THREADS * 16u) prefetch_l2(src + i);   // the whole fine bucket -> L2
+#if KMI_SEG_PF < -1
+    if (s + gridDim.x < n_segs) {                         // the CTA's next table segment -> L2
+      const char* nslots = reinterpret_cast<const char*>(reinterpret_cast<const Slot<1>*>(t.slots) + ((u64)(s + gridDim.x) << log_seg));
+      for (u32 i = tid * 128u; i < SEG * (u32)sizeof(Slot<1>); i += SEG_THREADS * 128u) prefetch_l2(nslots + i);
+    }
+#endif
+#else
+    if (KMI_SEG_PF) {                                     // chunks 2 .. PF+1 of the slice -> L2, one 128-byte line per lane
+      const u32 i = wb + 64 + lane * 16;
+      if (lane < 2 * KMI_SEG_PF && i < we) prefetch_l2(src + i);
+    }
+#endif
     uint4* gseg = reinterpret_cast<uint4*>(reinterpret_cast<Slot<1>*>(t.slots) + ((u64)s << log_seg));
     for (u32 i = tid; i < SEG; i += SEG_THREADS) reinterpret_cast<uint4*>(seg)[i] = gseg[i];
     __syncthreads();
@@ -443,7 +470,9 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
         pos += n; remaining -= (int)n;
         if (pos >= 32) {
           pos -= 32; buf0 = buf1;
-          buf1 = (nxt < we) ? __ldg(src + nxt) : KEY_EMPTY_TOP; nxt += 32;
+          buf1 = (nxt < we) ? __ldg(src + nxt) : KEY_EMPTY_TOP;
+          if (KMI_SEG_PF > 0 && (lane & 15) == 0 && nxt + KMI_SEG_PF * 32 < we) prefetch_l2(src + nxt + KMI_SEG_PF * 32);
+          nxt += 32;
         }
       }
       if (__ballot_sync(0xffffffffu, key != KEY_EMPTY_TOP) == 0) break;
