@@ -386,7 +386,7 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
   idx->size_exact = ~0ULL;  // stale until read back
   // second level: table segments of <= 4096 slots (8192 beyond 2^31 slots) updated in shared memory
   const int log_cap = __builtin_ctzll(idx->cap);
-  int log_segs = std::max(LOG_BUCKETS, log_cap - 12);
+  int log_segs = std::max(LOG_BUCKETS, log_cap - KMI_LOG_SEG_SLOTS);
   log_segs = std::min(log_segs, LOG_BUCKETS + MAX_LOG_F);
   const int log_seg = log_cap - log_segs;
   if (idx->seg_path && idx->ops->insert_segments && idx->nw == 1 && log_seg <= 13 && log_seg >= 8) {
@@ -495,7 +495,7 @@ static int fastq_scan_alloc(kmi_index* idx, const uint8_t* d_bytes, size_t n, u6
 static int fastq_scan_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64 t0, u64 t1) {
   if (t1 <= t0) return KMI_OK;
   const u64 nt = t1 - t0, nb = (nt + 1023) / 1024;
-  k_fastq_count_lines<<<(unsigned)nt, TILE_THREADS, 0, idx->stream>>>(d_bytes, n, idx->tile_lines.as<u32>(), (u32)t0);
+  k_fastq_count_lines<<<(unsigned)std::min<u64>((nt + 7) / 8, 148 * 16), COUNT_THREADS, 0, idx->stream>>>(d_bytes, n, idx->tile_lines.as<u32>(), (u32)t0, (u32)nt);
   k_scan_l1<<<(unsigned)nb, 1024, 0, idx->stream>>>(idx->tile_lines.as<u32>() + t0, nt, idx->block_sums.as<u32>() + t0 / 1024);
   k_scan_tiles<<<1, 1024, 0, idx->stream>>>(idx->block_sums.as<u32>() + t0 / 1024, nb, reinterpret_cast<u32*>(idx->ctr + CTR_CARRY));
   idx->launches += 3;

@@ -405,7 +405,17 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
 // A probe that runs off the end of the segment "spills": the key is appended to the overflow region
 // and inserted afterwards by k_insert_overflow with global atomics, which continues the linear probe
 // into the next segment exactly as table_upsert would have.
-static constexpr int SEG_THREADS = 512;
+#ifndef KMI_SEG_THREADS
+#define KMI_SEG_THREADS 384   // 4 CTAs/SM with the 48 KB keys[]+vals[] segment (measured: 5.01 ms vs 5.13 at 512 x 3)
+#endif
+#ifndef KMI_LOG_SEG_SLOTS
+#define KMI_LOG_SEG_SLOTS 12  // log2 of the slots of one shared-memory table segment
+#endif
+#ifndef KMI_SEG_SOA
+#define KMI_SEG_SOA 1         // shared-memory segment as keys[] + vals[] (12 B/slot, fewer bank conflicts) instead of 16-byte slots
+#endif
+static constexpr int SEG_THREADS = KMI_SEG_THREADS;
+__host__ __device__ inline size_t segment_smem(u32 log_seg) { return (size_t)(KMI_SEG_SOA ? 12 : 16) << log_seg; }
 #ifndef KMI_SEG_PF
 #define KMI_SEG_PF -1         // <0: the whole fine bucket is prefetched into L2 at segment start (-2: and the next table segment); >0: in-loop distance in chunks; 0 off
 #endif
@@ -420,9 +430,14 @@ __global__ void __launch_bounds__(SEG_THREADS)
 k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, const u32 n_segs, u32* __restrict__ perr) {
   static_assert(K <= 32, "segment path is built for one-word keys");
   extern __shared__ __align__(16) unsigned char seg_raw[];
-  Slot<1>* seg = reinterpret_cast<Slot<1>*>(seg_raw);
-  constexpr int NWARP = SEG_THREADS / 32;
   const u32 SEG = 1u << log_seg;
+#if KMI_SEG_SOA
+  u64* skey = reinterpret_cast<u64*>(seg_raw);
+  u32* sval = reinterpret_cast<u32*>(skey + SEG);
+#else
+  Slot<1>* seg = reinterpret_cast<Slot<1>*>(seg_raw);
+#endif
+  constexpr int NWARP = SEG_THREADS / 32;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const u32 lt = (1u << lane) - 1u;
   u32 n_new = 0;
@@ -450,7 +465,14 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
     }
 #endif
     uint4* gseg = reinterpret_cast<uint4*>(reinterpret_cast<Slot<1>*>(t.slots) + ((u64)s << log_seg));
+#if KMI_SEG_SOA
+    for (u32 i = tid; i < SEG; i += SEG_THREADS) {
+      const uint4 v = gseg[i];
+      skey[i] = (u64)v.x | ((u64)v.y << 32); sval[i] = v.z;
+    }
+#else
     for (u32 i = tid; i < SEG; i += SEG_THREADS) reinterpret_cast<uint4*>(seg)[i] = gseg[i];
+#endif
     __syncthreads();
     int remaining = (int)(we - wb);                       // keys of the slice not yet handed to a lane (warp-uniform)
     u32 pos = 0;                                          // consumed keys of buf0
@@ -477,13 +499,18 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
       }
       if (__ballot_sync(0xffffffffu, key != KEY_EMPTY_TOP) == 0) break;
       if (key != KEY_EMPTY_TOP) {
-        u64 cur = seg[li].key;
+#if KMI_SEG_SOA
+        u64* const kp = skey + li; u32* const vp = sval + li;
+#else
+        u64* const kp = &seg[li].key; u32* const vp = &seg[li].val;
+#endif
+        u64 cur = *kp;
         if (cur == KEY_EMPTY_TOP) {
-          cur = atomicCAS(&seg[li].key, KEY_EMPTY_TOP, key);
+          cur = atomicCAS(kp, KEY_EMPTY_TOP, key);
           if (cur == KEY_EMPTY_TOP) { ++n_new; cur = key; }
         }
         if (cur == key) {
-          atomicAdd(&seg[li].val, 1u);
+          atomicAdd(vp, 1u);
           key = KEY_EMPTY_TOP;
         } else if (++li == SEG) {
           const u32 o = atomicAdd(bs.cursor + N_BUCKETS, 1u);
@@ -494,7 +521,12 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
       }
     }
     __syncthreads();
+#if KMI_SEG_SOA
+    // aux (the CSR fill cursor of the position index) is scratch that csr_finalize zeroes before use: written as 0
+    for (u32 i = tid; i < SEG; i += SEG_THREADS) { const u64 k = skey[i]; gseg[i] = make_uint4((u32)k, (u32)(k >> 32), sval[i], 0u); }
+#else
     for (u32 i = tid; i < SEG; i += SEG_THREADS) gseg[i] = reinterpret_cast<const uint4*>(seg)[i];
+#endif
     __syncthreads();
   }
   n_new = warp_sum(n_new);

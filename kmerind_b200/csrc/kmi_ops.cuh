@@ -112,7 +112,7 @@ struct OpsImpl {
   }
   static int insert_segments(cudaStream_t st, TableView t, FineSink fsink, BucketSink bsink, u32 log_seg, u32 n_segs, u32* perr) {
     if constexpr (NW == 1) {
-      const size_t smem = sizeof(Slot<1>) << log_seg;
+      const size_t smem = segment_smem(log_seg);
       if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(k_insert_segments<K, HASH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return (int)e;

@@ -95,19 +95,35 @@ __device__ __forceinline__ u32 line_starts(u32 eol, bool prev_eol) {
 
 #ifdef KMI_SHARED_KERNELS  // non-template kernels: compiled once, in the API translation unit
 // ---- pass A: line starts per tile ------------------------------------------------------------
-__global__ void __launch_bounds__(TILE_THREADS) k_fastq_count_lines(const uint8_t* __restrict__ bytes, u64 n,
-                                                                     u32* __restrict__ tile_lines, const u32 tile_begin = 0) {
-  __shared__ u32 tmp[TILE_THREADS / 32 + 1];
-  const u64 tile = (u64)tile_begin + blockIdx.x;
-  u64 off = tile * TILE_BYTES + (u64)threadIdx.x * GROUP_BYTES;
-  u32 cnt = 0;
-  if (off < n) {
-    uint4 v = load_group(bytes, off, n);
-    cnt = __popc(line_starts(eol16(v), prev_is_eol(bytes, off, n)));
+// One WARP per 4 KiB tile, no block barrier: the eight 512-byte rows of the tile are requested together
+// (eight 128-bit loads in flight per lane), the "previous byte is an EOL" bit of a group comes from its
+// left neighbour's mask by shuffle, and the warp total goes out with one store. Warps stride over tiles.
+static constexpr int COUNT_THREADS = 256;
+__global__ void __launch_bounds__(COUNT_THREADS) k_fastq_count_lines(const uint8_t* __restrict__ bytes, u64 n,
+                                                                      u32* __restrict__ tile_lines, const u32 tile_begin,
+                                                                      const u32 n_tiles) {
+  constexpr int ROWS = TILE_BYTES / (32 * GROUP_BYTES);   // 8
+  const int lane = threadIdx.x & 31;
+  const u32 warps = gridDim.x * (COUNT_THREADS / 32);
+  for (u32 w = blockIdx.x * (COUNT_THREADS / 32) + (threadIdx.x >> 5); w < n_tiles; w += warps) {
+    const u64 tile = (u64)tile_begin + w;
+    const u64 base = tile * TILE_BYTES + (u64)lane * GROUP_BYTES;
+    u32 e[ROWS];
+#pragma unroll
+    for (int j = 0; j < ROWS; ++j) e[j] = eol16(load_group(bytes, base + (u64)j * 32 * GROUP_BYTES, n));   // past the end: all EOL
+    u32 prev_last = prev_is_eol(bytes, tile * TILE_BYTES, n) ? 0x8000u : 0u;   // mask whose bit 15 = byte before the row
+    u32 cnt = 0;
+#pragma unroll
+    for (int j = 0; j < ROWS; ++j) {
+      u32 left = __shfl_up_sync(0xffffffffu, e[j], 1);
+      if (lane == 0) left = prev_last;
+      cnt += __popc(line_starts(e[j], (left >> 15) & 1u));
+      prev_last = __shfl_sync(0xffffffffu, e[j], 31);
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
+    if (lane == 0) tile_lines[tile] = cnt;
   }
-  u32 total;
-  block_excl_scan(cnt, tmp, total);
-  if (threadIdx.x == 0) tile_lines[tile] = total;
 }
 
 // exclusive scan of the per-tile counts (modulo 2^32: only the value mod 4 matters downstream)
