@@ -43,6 +43,7 @@ template <int NW> struct BucketSmem {
   u64 sorted[ROUND_KEYS * NW];
   u32 hist[N_BUCKETS];    // counts while ranking, exclusive prefix afterwards
   u32 delta[N_BUCKETS];
+  u64 dst[N_BUCKETS];     // where sorted[0] would land if the bucket's run started there (bytes); bit 63: run does not fit
   u32 tmp[TILE_THREADS / 32 + 1];
   uint8_t sbid[ROUND_KEYS];
 };
@@ -105,15 +106,15 @@ template <int NW> __device__ __forceinline__ void bucket_init(BucketSmem<NW>& sm
 // shared-memory atomics was measured slower: parse+scatter 11.8 vs 9.4 ms, fine scatter 7.5 vs 5.6 ms.)
 template <int NW>
 __device__ __forceinline__ void bucket_round(const BucketSink& bs, BucketSmem<NW>& sm, const Key<NW> (&key)[BktRound<NW>::R],
-                                             const u32 (&bkt)[BktRound<NW>::R], const u32 n_round, u32* __restrict__ perr) {
-  // n_round (block-uniform): keys of this round; slot row q (keys q*TILE_THREADS ..) is skipped whole when empty
+                                             const u32 (&bkt)[BktRound<NW>::R], u32* __restrict__ perr) {
   constexpr int R = BktRound<NW>::R;
+  constexpr u64 DST_SLOW = 1ULL << 63;
   const int t = threadIdx.x;
   u32 rank[R];
 #pragma unroll
   for (int q = 0; q < R; ++q) {
     rank[q] = 0u;
-    if ((u32)(q * TILE_THREADS) < n_round && bkt[q] != BKT_NONE) rank[q] = atomicAdd(&sm.hist[bkt[q]], 1u);
+    if (bkt[q] != BKT_NONE) rank[q] = atomicAdd(&sm.hist[bkt[q]], 1u);
   }
   __syncthreads();
   const u32 cnt = sm.hist[t];
@@ -124,18 +125,33 @@ __device__ __forceinline__ void bucket_round(const BucketSink& bs, BucketSmem<NW
   __syncthreads();
 #pragma unroll
   for (int q = 0; q < R; ++q) {
-    if ((u32)(q * TILE_THREADS) < n_round && bkt[q] != BKT_NONE) {
+    if (bkt[q] != BKT_NONE) {
       const u32 pos = sm.hist[bkt[q]] + rank[q];
       if (NW == 1) sm.sorted[pos] = key[q].w[0];
       else reinterpret_cast<ulonglong2*>(sm.sorted)[pos] = make_ulonglong2(key[q].w[0], key[q].w[NW - 1]);
       sm.sbid[pos] = (uint8_t)bkt[q];
     }
   }
-  sm.delta[t] = gbase - ex;
+  {
+    // run of bucket t: sorted[ex .. ex+cnt) -> region[gbase .. gbase+cnt). One 64-bit destination per bucket, so
+    // that the copy-out below is load / add / store per key; runs that cross the region's capacity take the
+    // slow branch (overflow region).
+    u64* const region = bs.bases ? bs.bases[t] : bs.keys + (u64)t * bs.capb * NW;
+    u64 d = reinterpret_cast<u64>(region) + ((u64)gbase - (u64)ex) * (8u * NW);
+    if ((u64)gbase + cnt > (u64)bs.capb) d = DST_SLOW;
+    sm.dst[t] = d;
+    sm.delta[t] = gbase - ex;
+  }
   __syncthreads();
   sm.hist[t] = 0;                                         // dead now: cleared for the next round
   for (u32 r = t; r < total; r += TILE_THREADS) {
     const u32 b = sm.sbid[r];
+    const u64 d = sm.dst[b];
+    if (!(d & DST_SLOW)) {
+      if (NW == 1) *reinterpret_cast<u64*>(d + (u64)r * 8u) = sm.sorted[r];
+      else *reinterpret_cast<ulonglong2*>(d + (u64)r * 16u) = reinterpret_cast<const ulonglong2*>(sm.sorted)[r];
+      continue;
+    }
     u32 at = sm.delta[b] + r;
     u64* base = bs.bases ? bs.bases[b] : bs.keys + (u64)b * bs.capb * NW;
     if (at >= bs.capb) {
@@ -190,7 +206,7 @@ k_scatter_keys(const u64* __restrict__ keys, u64 n, BucketSink bs, u32* __restri
         bkt[q] = bucket_of(h);
       }
     }
-    bucket_round<NW>(bs, sm, key, bkt, (u32)min((u64)per_round, n - base), perr);
+    bucket_round<NW>(bs, sm, key, bkt, perr);
   }
 }
 

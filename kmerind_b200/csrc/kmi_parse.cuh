@@ -243,6 +243,68 @@ template <int K> __device__ __forceinline__ u32 window_all_set(const u32* f) {
   }
 }
 
+// ---- rolling extraction: R consecutive start positions from one aligned block of code words -------------
+// W[0..N): code words, first base in the top bits of W[0]. window_at returns the K bases that start at bit
+// offset `bitoff` (a compile-time constant after unrolling: the word picks and shifts fold to immediates).
+template <int N> __device__ __forceinline__ u32 word_at(const u32 (&W)[N], int i) { return (i >= 0 && i < N) ? W[i] : 0u; }
+template <int K, int N> __device__ __forceinline__ Key<(K <= 32 ? 1 : 2)> window_at(const u32 (&W)[N], const int bitoff) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  const int ws = bitoff >> 5, sh = bitoff & 31;
+  Key<NW> k;
+  const u32 w0 = __funnelshift_l(word_at<N>(W, ws + 1), word_at<N>(W, ws), sh);
+  const u32 w1 = __funnelshift_l(word_at<N>(W, ws + 2), word_at<N>(W, ws + 1), sh);
+  if (NW == 1) {
+    k.w[0] = (((u64)w0 << 32) | w1) >> (64 - 2 * K);
+  } else {
+    const u32 w2 = __funnelshift_l(word_at<N>(W, ws + 3), word_at<N>(W, ws + 2), sh);
+    const u32 w3 = __funnelshift_l(word_at<N>(W, ws + 4), word_at<N>(W, ws + 3), sh);
+    const u64 hi = ((u64)w0 << 32) | w1, lo = ((u64)w2 << 32) | w3;
+    constexpr int S = 128 - 2 * K;  // 2..62
+    k.w[0] = (lo >> S) | (hi << (64 - S));
+    k.w[NW - 1] = hi >> S;
+  }
+  return k;
+}
+// reverse complement of 16 bases held in one code word (first base in the top bits)
+__device__ __forceinline__ u32 revcomp16(u32 x) {
+  const u32 r = __brev(x);
+  return ~(((r >> 1) & 0x55555555u) | ((r & 0x55555555u) << 1));
+}
+// Entry = R consecutive candidate start positions (R = keys per thread per bucket round): the thread that owns
+// an entry loads the code words once and rolls the window over them, forward and reverse-complement strand
+// (the reverse complement of the whole block is built once, then each k-mer's is a window of it: lex_less,
+// kmer_transform.hpp:109-126, without a per-k-mer bit reversal).
+template <int K> struct Roll {
+  static constexpr int NW = (K <= 32 ? 1 : 2);
+  static constexpr int R = BktRound<NW>::R;            // 8 (one word) / 4 (two words)
+  static constexpr int EPG = GROUP_BYTES / R;           // entries per 16-byte group
+  static constexpr int NA = (R - 1 + K + 15) / 16;      // aligned code words an entry needs
+  static constexpr int LOG_EPG = (EPG == 2 ? 1 : 2);
+  u32 A[NA], RB[NA];
+  // s_codes: the tile's code words; entry id = group * EPG + sub
+  __device__ __forceinline__ void load(const u32* s_codes, u32 id, bool canon) {
+    const u32 g = id >> LOG_EPG, sh = (id & (EPG - 1)) * (2 * R);
+    u32 c[NA + 1];
+#pragma unroll
+    for (int w = 0; w <= NA; ++w) c[w] = s_codes[min(g + w, (u32)TILE_GROUPS)];
+#pragma unroll
+    for (int w = 0; w < NA; ++w) A[w] = __funnelshift_l(c[w + 1], c[w], sh);
+    if (canon) {
+#pragma unroll
+      for (int w = 0; w < NA; ++w) RB[w] = revcomp16(A[NA - 1 - w]);
+    }
+  }
+  // k-mer that starts at position i (0 <= i < R, compile-time) of the entry
+  __device__ __forceinline__ Key<NW> get(const int i, bool canon) const {
+    Key<NW> f = window_at<K, NA>(A, 2 * i);
+    if (canon) {
+      const Key<NW> rc = window_at<K, NA>(RB, 2 * (16 * NA - K - i));
+      if (!key_less<NW>(f, rc)) f = rc;
+    }
+    return f;
+  }
+};
+
 // ---- sinks: what happens to a generated k-mer ---------------------------------------------------
 struct KeySink {     // dense key (+id) stream
   u64* keys; u64* ids; u64 cap; u64* cursor;
@@ -269,7 +331,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   __shared__ u32 s_flags[TILE_GROUPS + 1];
   __shared__ u32 s_aux[HALO_GROUPS * 2];       // halo: line-start masks / popcounts
   __shared__ u32 s_tmp[TILE_THREADS / 32 + 1], s_tmp2[TILE_THREADS / 32 + 1];
-  __shared__ unsigned short s_list[TILE_BYTES];
+  __shared__ u32 s_ent[TILE_THREADS * (GROUP_BYTES / BktRound<(K <= 32 ? 1 : 2)>::R)];   // entry list (P4)
   __shared__ u64 s_base;
 
   const int t = threadIdx.x;
@@ -346,19 +408,25 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   }
   __syncthreads();
 
-  // -- P4: valid k-mer starts of this group -> dense work list
+  // -- P4: valid k-mer starts -> dense list of ENTRIES (R consecutive start positions with at least one valid)
+  using RollT = Roll<K>;
+  constexpr int R = RollT::R, EPG = RollT::EPG;
   u32 f5[5];
 #pragma unroll
   for (int q = 0; q < 5; ++q) f5[q] = s_flags[min(t + q, TILE_GROUPS)];
-  u32 valid = window_all_set<K>(f5);
-  u32 total;
-  u32 rank = block_excl_scan_nb(__popc(valid), s_tmp2, total);
+  const u32 valid = window_all_set<K>(f5);
+  u32 ne = 0;
+#pragma unroll
+  for (int e = 0; e < EPG; ++e) ne += ((valid >> (e * R)) & ((1u << R) - 1u)) ? 1u : 0u;
+  u32 tot;
+  const u32 pre = block_excl_scan_nb((ne << 16) | (u32)__popc(valid), s_tmp2, tot);   // entries : k-mers (<= 4096)
+  const u32 total_e = tot >> 16, total = tot & 0xFFFFu;
   {
-    u32 m = valid;
-    while (m) {
-      int j = __ffs(m) - 1;
-      m &= m - 1;
-      s_list[rank++] = (unsigned short)(t * GROUP_BYTES + j);
+    u32 er = pre >> 16, kp = pre & 0xFFFFu;
+#pragma unroll
+    for (int e = 0; e < EPG; ++e) {
+      const u32 v = (valid >> (e * R)) & ((1u << R) - 1u);
+      if (v) { s_ent[er++] = (u32)(t * EPG + e) | (v << 10) | (kp << 18); kp += __popc(v); }   // id : mask : k-mers before it
     }
   }
   if (t == 0) {
@@ -371,64 +439,64 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   }
   __syncthreads();
 
-  // -- P5: dense loop over the tile's k-mers
+  // -- P5: one entry per thread: load its code words once, roll the window over the R positions
   if (SINK >= 2) {
-    constexpr int R = BktRound<NW>::R;
     BucketSmem<NW>& sm = reinterpret_cast<BucketSmem<NW>&>(s_bkt);
     bucket_init<NW>(sm);
-    for (u32 c0 = 0; c0 < total; c0 += TILE_THREADS * R) {   // block-uniform trip count
+    for (u32 e0 = 0; e0 < total_e; e0 += TILE_THREADS) {     // block-uniform trip count
       Key<NW> key[R];
       u32 bkt[R];
 #pragma unroll
-      for (int q = 0; q < R; ++q) {
-        const u32 r = c0 + q * TILE_THREADS + t;
-        bkt[q] = BKT_NONE;
-        if (c0 + q * TILE_THREADS >= total) continue;      // block-uniform: nobody has a key in this slot row
-        if (r < total) {
-          const u32 pos = s_list[r];
-          const int gi = pos >> 4, j = pos & 15;
-          u32 c5[5];
+      for (int q = 0; q < R; ++q) bkt[q] = BKT_NONE;
+      if (e0 + t < total_e) {
+        const u32 ent = s_ent[e0 + t];
+        const u32 v = (ent >> 10) & 0xFFu;
+        RollT roll;
+        roll.load(s_codes, ent & 1023u, CANON);
 #pragma unroll
-          for (int w = 0; w < 5; ++w) c5[w] = s_codes[min(gi + w, TILE_GROUPS)];
-          key[q] = extract_kmer<K>(c5, j);
-          if (CANON) key[q] = canonical<K>(key[q]);
+        for (int q = 0; q < R; ++q) {
+          key[q] = roll.get(q, CANON);
+          u32 b;
           if (SINK == 2) {
-            const u64 h = slot_hash<K>(key[q]);
-            bkt[q] = bucket_of(h);
+            b = bucket_of(slot_hash<K>(key[q]));
           } else {
             u64 hs, hd;
             kmer_hashes<K, HASH>(key[q], hs, hd);
-            bkt[q] = (u32)(hd % (u64)nranks);
+            b = (u32)(hd % (u64)nranks);
           }
+          bkt[q] = ((v >> q) & 1u) ? b : BKT_NONE;
         }
       }
-      bucket_round<NW>(bsink, sm, key, bkt, min(total - c0, (u32)(TILE_THREADS * R)), perr);
+      bucket_round<NW>(bsink, sm, key, bkt, perr);
     }
     return;
   }
   u32 n_new = 0;
-  for (u32 r = t; r < total; r += TILE_THREADS) {
-    const u32 pos = s_list[r];
-    const int gi = pos >> 4, j = pos & 15;
-    u32 c5[5];
+  for (u32 e = t; e < total_e; e += TILE_THREADS) {
+    const u32 ent = s_ent[e];
+    const u32 v = (ent >> 10) & 0xFFu;
+    u64 at = s_base + (ent >> 18);
+    RollT roll;
+    roll.load(s_codes, ent & 1023u, CANON);
 #pragma unroll
-    for (int q = 0; q < 5; ++q) c5[q] = s_codes[min(gi + q, TILE_GROUPS)];
-    Key<NW> key = extract_kmer<K>(c5, j);
-    if (CANON) key = canonical<K>(key);
-    if (SINK == 0) {
-      const u64 at = s_base + r;
-      if (at < sink.cap) {
+    for (int q = 0; q < R; ++q) {
+      if (!((v >> q) & 1u)) continue;
+      const Key<NW> key = roll.get(q, CANON);
+      if (SINK == 0) {
+        if (at < sink.cap) {
 #pragma unroll
-        for (int w = 0; w < NW; ++w) sink.keys[at * NW + w] = key.w[w];
+          for (int w = 0; w < NW; ++w) sink.keys[at * NW + w] = key.w[w];
+        } else {
+          atomicOr(perr, PERR_OVERFLOW);
+        }
+        ++at;
       } else {
-        atomicOr(perr, PERR_OVERFLOW);
-      }
-    } else {
-      bool was_new;
-      u64 slot = table_upsert<NW>(table, key, slot_hash<K>(key), was_new);
-      if (slot != ~0ULL) {
-        atomicAdd(&reinterpret_cast<Slot<NW>*>(table.slots)[slot].val, 1u);
-        n_new += was_new ? 1u : 0u;
+        bool was_new;
+        u64 slot = table_upsert<NW>(table, key, slot_hash<K>(key), was_new);
+        if (slot != ~0ULL) {
+          atomicAdd(&reinterpret_cast<Slot<NW>*>(table.slots)[slot].val, 1u);
+          n_new += was_new ? 1u : 0u;
+        }
       }
     }
   }
