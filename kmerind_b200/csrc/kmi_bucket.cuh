@@ -427,6 +427,9 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
 #ifndef KMI_LOG_SEG_SLOTS
 #define KMI_LOG_SEG_SLOTS 12  // log2 of the slots of one shared-memory table segment
 #endif
+#ifndef KMI_SEG_MINB
+#define KMI_SEG_MINB 4
+#endif
 #ifndef KMI_SEG_SOA
 #define KMI_SEG_SOA 1         // shared-memory segment as keys[] + vals[] (12 B/slot, fewer bank conflicts) instead of 16-byte slots
 #endif
@@ -442,7 +445,7 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 // (ballot + shuffle) in the same loop iteration in which the other lanes advance their probes. A loop
 // iteration is therefore one probe for every lane, instead of max-over-lanes probes per key.
 template <int K, int HASH>
-__global__ void __launch_bounds__(SEG_THREADS)
+__global__ void __launch_bounds__(SEG_THREADS, KMI_SEG_MINB)
 k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, const u32 n_segs, u32* __restrict__ perr) {
   static_assert(K <= 32, "segment path is built for one-word keys");
   extern __shared__ __align__(16) unsigned char seg_raw[];
@@ -466,6 +469,8 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
     u32 nxt = wb + lane;
     u64 buf0 = (nxt < we) ? __ldg(src + nxt) : KEY_EMPTY_TOP; nxt += 32;   // requested before the segment is loaded
     u64 buf1 = (nxt < we) ? __ldg(src + nxt) : KEY_EMPTY_TOP; nxt += 32;
+    u64 buf2 = (nxt < we) ? __ldg(src + nxt) : KEY_EMPTY_TOP; nxt += 32;
+    u32 ph = 0;
 #if KMI_SEG_PF < 0
     for (u32 i = tid * 16u; i < cnt; i += SEG_THREADS * 16u) prefetch_l2(src + i);   // the whole fine bucket -> L2
 #if KMI_SEG_PF < -1
@@ -498,20 +503,33 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
       const u32 need = __ballot_sync(0xffffffffu, key == KEY_EMPTY_TOP);
       if (need && remaining > 0) {                        // warp-uniform
         const u32 idx = pos + __popc(need & lt);
-        const u64 k0 = __shfl_sync(0xffffffffu, buf0, idx & 31), k1 = __shfl_sync(0xffffffffu, buf1, idx & 31);
-        if (key == KEY_EMPTY_TOP) {
-          key = (idx < 32) ? k0 : k1;
-          Key<1> kk; kk.w[0] = key;
-          li = (u32)(slot_hash<K>(kk) >> t.shift) & (SEG - 1);
-        }
         const u32 n = __popc(need);
-        pos += n; remaining -= (int)n;
-        if (pos >= 32) {
-          pos -= 32; buf0 = buf1;
-          buf1 = (nxt < we) ? __ldg(src + nxt) : KEY_EMPTY_TOP;
-          if (KMI_SEG_PF > 0 && (lane & 15) == 0 && nxt + KMI_SEG_PF * 32 < we) prefetch_l2(src + nxt + KMI_SEG_PF * 32);
-          nxt += 32;
+        // C = chunk being handed out, N = the one after it; the exhausted chunk's register takes the new load, and
+        // the roles rotate by phase instead of by register moves (a move would wait for the load in flight)
+#define KMI_REFILL(C, N)                                                                            \
+        {                                                                                          \
+          u64 kx = __shfl_sync(0xffffffffu, C, idx & 31);                                          \
+          if (pos + n > 32) {                                                                      \
+            const u64 k1 = __shfl_sync(0xffffffffu, N, idx & 31);                                  \
+            if (idx >= 32) kx = k1;                                                                \
+          }                                                                                        \
+          if (key == KEY_EMPTY_TOP) {                                                              \
+            key = kx;                                                                              \
+            Key<1> kk; kk.w[0] = key;                                                              \
+            li = (u32)(slot_hash<K>(kk) >> t.shift) & (SEG - 1);                                   \
+          }                                                                                        \
+          pos += n; remaining -= (int)n;                                                           \
+          if (pos >= 32) {                                                                         \
+            pos -= 32;                                                                             \
+            C = (nxt < we) ? __ldg(src + nxt) : KEY_EMPTY_TOP;                                     \
+            nxt += 32;                                                                             \
+            ph = (ph == 2) ? 0 : ph + 1;                                                           \
+          }                                                                                        \
         }
+        if (ph == 0) KMI_REFILL(buf0, buf1)
+        else if (ph == 1) KMI_REFILL(buf1, buf2)
+        else KMI_REFILL(buf2, buf0)
+#undef KMI_REFILL
       }
       if (__ballot_sync(0xffffffffu, key != KEY_EMPTY_TOP) == 0) break;
       if (key != KEY_EMPTY_TOP) {

@@ -317,7 +317,7 @@ struct KeySink {     // dense key (+id) stream
 // SINK 3: scatter into one region per owning rank, owner = dist_hash % nranks (KeyToRank,
 //         distributed_densehash_map.hpp:148-170): the send buffers of the all-to-all, no key stream pass
 #ifndef KMI_PARSE_MINB
-#define KMI_PARSE_MINB 7      // CTAs per SM the parser is compiled for (register cap 36; measured 8.1 ms at 4, 7.2 at 6, 7.0 at 7 and 8)
+#define KMI_PARSE_MINB 5      // CTAs per SM the parser is compiled for (48 registers; measured 5.59 ms at 5, 5.61 at 6, 5.71 at 7 and 8)
 #endif
 template <int K, int HASH, int SINK>
 __global__ void __launch_bounds__(TILE_THREADS, KMI_PARSE_MINB)
