@@ -289,7 +289,7 @@ struct FineSink {
 // dynamic shared memory of k_scatter_fine for 2^log_f fine buckets
 __host__ __device__ inline size_t scatter_fine_smem(u32 log_f) {
   const size_t F = (size_t)1 << log_f;
-  return FINE_ROUND * sizeof(u64) + 2 * F * sizeof(u32) + FINE_ROUND * sizeof(unsigned short);
+  return FINE_ROUND * sizeof(u64) + F * sizeof(u64) + 2 * F * sizeof(u32) + FINE_ROUND * sizeof(unsigned short);
 }
 
 #ifndef KMI_FINE_MINB
@@ -306,7 +306,8 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
   const int t = threadIdx.x;
   const u32 F = 1u << fs.log_f;
   u64* sorted = reinterpret_cast<u64*>(fine_raw);                       // FINE_ROUND keys
-  u32* hist = reinterpret_cast<u32*>(sorted + FINE_ROUND);             // F: counts while ranking, exclusive prefix afterwards
+  u64* dst = sorted + FINE_ROUND;                                       // F: byte address sorted[0] would land at (bit 63: run does not fit)
+  u32* hist = reinterpret_cast<u32*>(dst + F);                          // F: counts while ranking, exclusive prefix afterwards
   u32* delta = hist + F;                                                // F
   unsigned short* sbid = reinterpret_cast<unsigned short*>(delta + F);  // FINE_ROUND
   const u32 EPT = F >= TILE_THREADS ? F / TILE_THREADS : 1u;   // histogram entries per thread
@@ -366,7 +367,7 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
       }
     }
     __syncthreads();
-    u32 gb1 = 0, ex1 = 0;                                 // EPT == 1: the cursor atomic stays in flight during the sort
+    u32 gb1 = 0, ex1 = 0, cnt1 = 0;                       // EPT == 1: the cursor atomic stays in flight during the sort
     {
       u32 local = 0;
       for (u32 e = 0; e < EPT; ++e) { const u32 f = t * EPT + e; if (f < F) local += hist[f]; }
@@ -375,7 +376,7 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
       if (EPT == 1) {
         if ((u32)t < F) {
           if (local) gb1 = atomicAdd(fs.cursor + ((u64)b << fs.log_f) + t, local);
-          hist[t] = ex; ex1 = ex;
+          hist[t] = ex; ex1 = ex; cnt1 = local;
         }
       } else {
         for (u32 e = 0; e < EPT; ++e) {
@@ -398,12 +399,20 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
         sbid[pos] = (unsigned short)fid[q];
       }
     }
-    if (EPT == 1 && (u32)t < F) delta[t] = gb1 - ex1;
+    const u64 region0 = (u64)b << fs.log_f;
+    if (EPT == 1 && (u32)t < F) {
+      delta[t] = gb1 - ex1;
+      const bool fits = (u64)gb1 + cnt1 <= (u64)fs.capf;
+      dst[t] = fits ? reinterpret_cast<u64>(fs.keys + (region0 + t) * fs.capf) + ((u64)gb1 - (u64)ex1) * 8u : (1ULL << 63);
+    }
     __syncthreads();
     for (u32 f = t; f < F; f += TILE_THREADS) hist[f] = 0;
-    const u64 region0 = (u64)b << fs.log_f;
     for (u32 r = t; r < m; r += TILE_THREADS) {
       const u32 f = sbid[r];
+      if (EPT == 1) {
+        const u64 d = dst[f];
+        if (!(d >> 63)) { *reinterpret_cast<u64*>(d + (u64)r * 8u) = sorted[r]; continue; }
+      }
       const u32 at = delta[f] + r;
       if (at < fs.capf) {
         fs.keys[(region0 + f) * fs.capf + at] = sorted[r];

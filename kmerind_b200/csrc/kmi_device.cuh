@@ -158,6 +158,20 @@ template <int K, int HASH> __device__ __forceinline__ u64 store_hash(const Key<(
   return farm_finish(farm_len0to16<NB>(lo, hi), 42, HASH == 2);
 }
 
+// 16-byte asynchronous global -> shared copy (LDGSTS), bypassing L1
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// dist_hash % p (KeyToRank, distributed_densehash_map.hpp:148-170): p is uniform over the grid, and 2/4/8 ranks are
+// the common case, so the ~40-instruction 64-bit division is kept for the other values of p only
+__device__ __forceinline__ u32 mod_ranks(u64 d, u32 p) {
+  return ((p & (p - 1u)) == 0u) ? ((u32)d & (p - 1u)) : (u32)(d % (u64)p);
+}
+
 // Placement hash of the local table: picks the home slot (top bits), the hash-prefix bucket and the
 // HyperLogLog register. Where an entry sits inside one GPU's table is unobservable — the reference's
 // StoreHash is a free template parameter for the same reason (kmer_index.hpp:437-466) — so this is a

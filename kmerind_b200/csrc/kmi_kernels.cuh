@@ -168,7 +168,7 @@ template <int K, int HASH>
 __device__ __forceinline__ u32 owner_of(const Key<(K <= 32 ? 1 : 2)>& key, u32 p) {
   u64 s, d;
   kmer_hashes<K, HASH>(key, s, d);
-  return (u32)(d % (u64)p);
+  return mod_ranks(d, p);
 }
 
 template <int K, int HASH>

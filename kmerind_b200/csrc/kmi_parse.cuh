@@ -341,20 +341,30 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
 
   // -- P1: load + classify own group (and, for the first HALO_GROUPS threads, a halo group)
   uint4 v = load_group(bytes, off, n);
-  Group g = classify(v);
-  u32 ls = (off < n) ? line_starts(g.eol, prev_is_eol(bytes, off, n)) : 0u;
+  Group g;                                            // FASTQ needs no separate '\n' mask, and the N mask only when splitting
+  g.codes = codes16(v); g.eol = eol16(v); g.nl = 0; g.nmask = NSPLIT ? nmask16(v) : 0u;
+  bool prev_eol;                                      // byte before the group: the left neighbour's last byte
+  {
+    const u32 left = __shfl_up_sync(0xffffffffu, v.w >> 24, 1);
+    prev_eol = (left == '\n' || left == '\r');
+    if ((t & 31) == 0) prev_eol = prev_is_eol(bytes, off, n);
+    if (off > n) prev_eol = true;
+  }
+  u32 ls = (off < n) ? line_starts(g.eol, prev_eol) : 0u;
   s_codes[t] = g.codes;
   u32 hls = 0, heol = 0, hn = 0;
   if (t < HALO_GROUPS) {
     u64 hoff = tile_off + TILE_BYTES + (u64)t * GROUP_BYTES;
     uint4 hv = load_group(bytes, hoff, n);
-    Group hg = classify(hv);
+    Group hg;
+    hg.codes = codes16(hv); hg.eol = eol16(hv); hg.nl = 0; hg.nmask = NSPLIT ? nmask16(hv) : 0u;
     hls = (hoff < n) ? line_starts(hg.eol, prev_is_eol(bytes, hoff, n)) : 0u;
     heol = hg.eol; hn = hg.nmask;
     s_codes[TILE_THREADS + t] = hg.codes;
     s_aux[t] = __popc(hls);
   }
   if (t == 0) s_codes[TILE_GROUPS] = 0;
+  if (SINK >= 2) reinterpret_cast<BucketSmem<NW>&>(s_bkt).hist[t] = 0;   // bucket_init, under the barriers of P2-P4
 
   // -- P2: line number at the start of every group
   u32 total_ls;
@@ -441,8 +451,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
 
   // -- P5: one entry per thread: load its code words once, roll the window over the R positions
   if (SINK >= 2) {
-    BucketSmem<NW>& sm = reinterpret_cast<BucketSmem<NW>&>(s_bkt);
-    bucket_init<NW>(sm);
+    BucketSmem<NW>& sm = reinterpret_cast<BucketSmem<NW>&>(s_bkt);     // histogram zeroed in P1
     for (u32 e0 = 0; e0 < total_e; e0 += TILE_THREADS) {     // block-uniform trip count
       Key<NW> key[R];
       u32 bkt[R];
@@ -462,7 +471,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
           } else {
             u64 hs, hd;
             kmer_hashes<K, HASH>(key[q], hs, hd);
-            b = (u32)(hd % (u64)nranks);
+            b = mod_ranks(hd, nranks);
           }
           bkt[q] = ((v >> q) & 1u) ? b : BKT_NONE;
         }
