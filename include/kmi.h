@@ -115,13 +115,20 @@ int kmi_parse_fastq_by_owner_dev(kmi_index* idx, const uint8_t* d_bytes, size_t 
  * nranks handles (any transport) and passes them to kmi_exchange_connect. kmi_exchange_parse_fastq_dev
  * then runs parse + owner + scatter as ONE kernel whose stores land directly in the owners' buffers;
  * the caller exchanges the send counts (this is also the completion handshake) and calls
- * kmi_exchange_insert with the counts it received. All ranks must be on one node (CUDA IPC). */
+ * kmi_exchange_insert with the counts it received. All ranks must be on one node (CUDA IPC).
+ *
+ * Sub-bins (opt-in, environment KMI_EXCHANGE_PREFIX=1): for one-word keys on 2/4/8 ranks every (source, owner) region is cut into B = 256 / nranks sub-bins by the top
+ * bits of the table-placement hash, inside the same shared-memory sort of the sender, so that the receiver's table build
+ * starts at its fine scatter (no coarse pass over the received keys). kmi_exchange_bins returns B (1 otherwise); the
+ * count arrays then hold nranks * B entries, entry r * B + c = keys for / from rank r in sub-bin c, and are exchanged
+ * block-wise (all-to-all of B counts per peer). */
 #define KMI_IPC_HANDLE_BYTES 64
 int kmi_exchange_setup(kmi_index* idx, size_t region_cap, uint8_t* handle_out /* KMI_IPC_HANDLE_BYTES */);
 int kmi_exchange_connect(kmi_index* idx, const uint8_t* handles /* nranks * KMI_IPC_HANDLE_BYTES */);
-int kmi_exchange_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* h_send_counts,
+int kmi_exchange_bins(kmi_index* idx, uint32_t* bins_per_rank);
+int kmi_exchange_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* h_send_counts /* nranks * B */,
                                  uint64_t* n_kmers);
-int kmi_exchange_insert(kmi_index* idx, const uint64_t* h_recv_counts);
+int kmi_exchange_insert(kmi_index* idx, const uint64_t* h_recv_counts /* nranks * B */);
 /* a10: out = canonical(in) (lex_less, kmer_transform.hpp:109-126); in == out allowed */
 int kmi_canonicalize_dev(kmi_index* idx, const uint64_t* d_keys, uint64_t* d_out, size_t n);
 /* a11/a12: which = 0 store hash, 1 dist hash, of the keys AS GIVEN (no transform) */

@@ -72,6 +72,7 @@ def load_library(build_if_missing=False):
         "kmi_parse_fastq_by_owner_dev": [_P, _P, _SZ, _P, _SZ, _P, _P],
         "kmi_exchange_setup": [_P, _SZ, _P], "kmi_exchange_connect": [_P, _P],
         "kmi_exchange_parse_fastq_dev": [_P, _P, _SZ, _P, _P], "kmi_exchange_insert": [_P, _P],
+        "kmi_exchange_bins": [_P, _P],
         "kmi_canonicalize_dev": [_P, _P, _P, _SZ], "kmi_hash_dev": [_P, ctypes.c_int, _P, _P, _SZ],
         "kmi_partition_dev": [_P, _P, _P, _SZ, _P, _P, _P],
         "kmi_insert": [_P, _P, _P, _SZ], "kmi_insert_dev": [_P, _P, _P, _SZ],
@@ -96,7 +97,7 @@ EXPORTED_SYMBOLS = (
     "kmi_create", "kmi_destroy", "kmi_last_error", "kmi_set_stream", "kmi_set_param", "kmi_reserve", "kmi_clear",
     "kmi_build_fastq", "kmi_build_fasta", "kmi_build_fastq_dev", "kmi_build_fasta_dev",
     "kmi_parse_fastq_dev", "kmi_parse_fasta_dev", "kmi_parse_fastq_by_owner_dev", "kmi_exchange_setup", "kmi_exchange_connect",
-    "kmi_exchange_parse_fastq_dev", "kmi_exchange_insert", "kmi_canonicalize_dev", "kmi_hash_dev",
+    "kmi_exchange_parse_fastq_dev", "kmi_exchange_insert", "kmi_exchange_bins", "kmi_canonicalize_dev", "kmi_hash_dev",
     "kmi_partition_dev", "kmi_insert", "kmi_insert_dev", "kmi_count", "kmi_find", "kmi_find_positions",
     "kmi_erase", "kmi_count_dev", "kmi_find_dev", "kmi_local_size", "kmi_num_keys", "kmi_dump",
     "kmi_checksum", "kmi_table_info", "kmi_launch_count", "kmi_last_stage_ms", "kmi_last_kernel_ms",
@@ -207,8 +208,14 @@ class Index:
         buf = np.frombuffer(b"".join(handles), dtype=np.uint8).copy()
         _check(self._lib.kmi_exchange_connect(self._h, _hptr(buf)))
 
+    def exchange_bins(self):
+        """sub-bins per peer of the count arrays (kmi_exchange_bins): 1, or 256 / nranks with the prefix layout"""
+        b = ctypes.c_uint32(0)
+        _check(self._lib.kmi_exchange_bins(self._h, ctypes.byref(b)))
+        return b.value
+
     def exchange_parse_fastq_dev(self, dptr, nbytes, nranks):
-        counts = np.zeros(nranks, dtype=np.uint64)
+        counts = np.zeros(nranks * self.exchange_bins(), dtype=np.uint64)
         n = _U64(0)
         _check(self._lib.kmi_exchange_parse_fastq_dev(self._h, dptr, nbytes, _hptr(counts), ctypes.byref(n)))
         return counts, n.value

@@ -9,6 +9,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -105,6 +106,9 @@ struct kmi_index {
   // fused exchange (kmi_exchange_*): receive regions of this rank, peers' regions mapped over CUDA IPC
   void* xchg_recv = nullptr;
   u64 xchg_region_cap = 0;
+  u32 xchg_log_cb = 0;              // > 0: every (source, owner) region is cut into 2^log_cb sub-bins by slot-hash prefix
+  u64 xchg_cap_bin = 0;             // keys per sub-bin
+  u64 xchg_ovf_cap = 0;             // overflow region behind the sub-bins (fine-scatter excess, segment spills)
   std::vector<void*> xchg_peer;     // base of rank r's receive buffer in this process (own buffer for r == rank)
   DevBuf xchg_bases;                // device array: where THIS rank writes keys owned by rank r
   cudaStream_t copy_stream = nullptr;        // H2D copies of the pipelined host-pointer build
@@ -386,12 +390,14 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
   idx->size_exact = ~0ULL;  // stale until read back
   // second level: table segments of <= 4096 slots (8192 beyond 2^31 slots) updated in shared memory
   const int log_cap = __builtin_ctzll(idx->cap);
-  int log_segs = std::max(LOG_BUCKETS, log_cap - KMI_LOG_SEG_SLOTS);
-  log_segs = std::min(log_segs, LOG_BUCKETS + MAX_LOG_F);
+  // (regions of the exchange buffer share only log_pre < 8 prefix bits: their fine scatter is wider, never skipped)
+  const int log_pre = (int)bs.log_pre;
+  int log_segs = std::max(std::max(LOG_BUCKETS, log_pre + (log_pre < LOG_BUCKETS ? 1 : 0)), log_cap - KMI_LOG_SEG_SLOTS);
+  log_segs = std::min(log_segs, log_pre + MAX_LOG_F);
   const int log_seg = log_cap - log_segs;
   if (idx->seg_path && idx->ops->insert_segments && idx->nw == 1 && log_seg <= 13 && log_seg >= 8) {
-    const u32 log_f = (u32)(log_segs - LOG_BUCKETS);
-    const u64 n_regions = (u64)N_BUCKETS << log_f;
+    const u32 log_f = (u32)(log_segs - log_pre);
+    const u64 n_regions = (u64)1 << log_segs;
     FineSink fs;
     fs.log_f = log_f;
     bool fine_ok = true;
@@ -566,7 +572,7 @@ extern "C" int kmi_parse_fastq_by_owner_dev(kmi_index* idx, const uint8_t* d_byt
   TableView none; none.slots = nullptr; none.mask = 0; none.shift = 63; none.size = nullptr; none.error = nullptr;
   idx->ops->fastq_kmers(idx->stream, 3, d_bytes, n, n_tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), nosink, none, bs,
                         idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0,
-                        idx->cfg.nsplit != 0, 0, p);
+                        idx->cfg.nsplit != 0, 0, p | (idx->xchg_log_cb << 16));
   idx->launches++;
   u64 host[CTR_N];
   CU(cudaMemcpyAsync(host, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
@@ -599,7 +605,26 @@ extern "C" int kmi_exchange_setup(kmi_index* idx, size_t region_cap, uint8_t* ha
   static_assert(sizeof(cudaIpcMemHandle_t) == KMI_IPC_HANDLE_BYTES, "IPC handle size");
   CU(cudaStreamSynchronize(idx->stream));
   exchange_close(idx);
-  const size_t bytes = (size_t)idx->cfg.nranks * region_cap * idx->nw * sizeof(u64);
+  // Sub-bin layout (one-word keys, 2/4/8 ranks; opt-in with KMI_EXCHANGE_PREFIX=1): the sender's 256-way shared-memory
+  // sort bins by (owner, top bits of the slot hash), so what arrives is already cut by hash prefix and the receiver needs
+  // no coarse scatter pass. Measured at 2 GPUs it LOSES: the receiver saves 2.1 ms (11.9 -> 9.8) but the peer stores
+  // shrink from 8 KB to 64-byte runs and the parse+exchange kernel goes from 7.4 to 12.8 ms (250 GB/s over NVLink), so
+  // the default keeps one large run per owner.
+  const int p0 = idx->cfg.nranks;
+  const char* env = getenv("KMI_EXCHANGE_PREFIX");
+  idx->xchg_log_cb = 0;
+  if (idx->nw == 1 && p0 >= 2 && p0 <= 8 && (p0 & (p0 - 1)) == 0 && env && env[0] == '1') {
+    int lp = 0;
+    while ((1 << lp) < p0) ++lp;
+    idx->xchg_log_cb = (u32)(LOG_BUCKETS - lp);
+  }
+  size_t bytes = (size_t)p0 * region_cap * idx->nw * sizeof(u64);
+  if (idx->xchg_log_cb) {
+    const u64 cb = 1ULL << idx->xchg_log_cb;
+    idx->xchg_cap_bin = region_cap / cb + region_cap / (cb * 16) + 1024;
+    idx->xchg_ovf_cap = (u64)p0 * region_cap / 8 + 4096;
+    bytes = ((size_t)N_BUCKETS * idx->xchg_cap_bin + idx->xchg_ovf_cap) * sizeof(u64);
+  }
   cudaError_t e = cudaMalloc(&idx->xchg_recv, bytes);
   if (e != cudaSuccess) { idx->xchg_recv = nullptr; return fail(KMI_ERR_NOMEM, "cudaMalloc exchange buffer %zu: %s", bytes, cudaGetErrorString(e)); }
   idx->xchg_region_cap = region_cap;
@@ -615,7 +640,8 @@ extern "C" int kmi_exchange_connect(kmi_index* idx, const uint8_t* handles) {
   CU(cudaSetDevice(idx->cfg.device));
   const int p = idx->cfg.nranks, me = idx->cfg.rank;
   idx->xchg_peer.assign(p, nullptr);
-  std::vector<u64*> bases(p);
+  const u32 cb = 1u << idx->xchg_log_cb;                 // 1 without sub-bins
+  std::vector<u64*> bases((size_t)p * cb);
   for (int r = 0; r < p; ++r) {
     void* base = idx->xchg_recv;
     if (r != me) {
@@ -625,10 +651,21 @@ extern "C" int kmi_exchange_connect(kmi_index* idx, const uint8_t* handles) {
       if (e != cudaSuccess) { exchange_close(idx); return fail(KMI_ERR_CUDA, "cudaIpcOpenMemHandle(rank %d): %s", r, cudaGetErrorString(e)); }
     }
     idx->xchg_peer[r] = base;
-    bases[r] = reinterpret_cast<u64*>(base) + (size_t)me * idx->xchg_region_cap * idx->nw;   // my region in r's buffer
+    if (!idx->xchg_log_cb) {
+      bases[r] = reinterpret_cast<u64*>(base) + (size_t)me * idx->xchg_region_cap * idx->nw;   // my region in r's buffer
+    } else {
+      for (u32 c = 0; c < cb; ++c)                       // my sub-bin c in r's buffer: region me * CB + c
+        bases[(size_t)r * cb + c] = reinterpret_cast<u64*>(base) + ((size_t)me * cb + c) * idx->xchg_cap_bin;
+    }
   }
-  OK(idx->xchg_bases.ensure(sizeof(u64*) * p));
-  CU(cudaMemcpy(idx->xchg_bases.p, bases.data(), sizeof(u64*) * p, cudaMemcpyHostToDevice));
+  OK(idx->xchg_bases.ensure(sizeof(u64*) * bases.size()));
+  CU(cudaMemcpy(idx->xchg_bases.p, bases.data(), sizeof(u64*) * bases.size(), cudaMemcpyHostToDevice));
+  return KMI_OK;
+}
+
+extern "C" int kmi_exchange_bins(kmi_index* idx, uint32_t* bins_per_rank) {
+  if (!idx || !bins_per_rank) return fail(KMI_ERR_ARG, "null argument");
+  *bins_per_rank = 1u << idx->xchg_log_cb;
   return KMI_OK;
 }
 
@@ -640,7 +677,8 @@ extern "C" int kmi_exchange_parse_fastq_dev(kmi_index* idx, const uint8_t* d_byt
   if (idx->xchg_peer.empty()) return fail(KMI_ERR_ARG, "kmi_exchange_connect first");
   CU(cudaSetDevice(idx->cfg.device));
   const u32 p = (u32)idx->cfg.nranks;
-  for (u32 r = 0; r < p; ++r) h_send_counts[r] = 0;
+  const u32 n_bins = p << idx->xchg_log_cb;
+  for (u32 r = 0; r < n_bins; ++r) h_send_counts[r] = 0;
   if (n_kmers) *n_kmers = 0;
   u64 n_tiles = 0;
   OK(fastq_scan(idx, d_bytes, n, &n_tiles));
@@ -655,13 +693,14 @@ extern "C" int kmi_exchange_parse_fastq_dev(kmi_index* idx, const uint8_t* d_byt
   OK(zero_ctr(idx, CTR_NKMERS));
   OK(zero_ctr(idx, CTR_PERR));
   BucketSink bs;
-  bs.keys = nullptr; bs.cursor = idx->bkt_meta.as<u32>(); bs.capb = (u32)idx->xchg_region_cap; bs.ovf_cap = 0; bs.hll = nullptr;
+  bs.keys = nullptr; bs.cursor = idx->bkt_meta.as<u32>(); bs.ovf_cap = 0; bs.hll = nullptr;
+  bs.capb = (u32)(idx->xchg_log_cb ? idx->xchg_cap_bin : idx->xchg_region_cap);
   bs.bases = idx->xchg_bases.as<u64*>();
   KeySink nosink; nosink.keys = nullptr; nosink.ids = nullptr; nosink.cap = 0; nosink.cursor = nullptr;
   TableView none; none.slots = nullptr; none.mask = 0; none.shift = 63; none.size = nullptr; none.error = nullptr;
   idx->ops->fastq_kmers(idx->stream, 3, d_bytes, n, n_tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), nosink, none, bs,
                         idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0,
-                        idx->cfg.nsplit != 0, 0, p);
+                        idx->cfg.nsplit != 0, 0, p | (idx->xchg_log_cb << 16));
   idx->launches++;
   u64 host[CTR_N];
   CU(cudaMemcpyAsync(host, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
@@ -669,7 +708,7 @@ extern "C" int kmi_exchange_parse_fastq_dev(kmi_index* idx, const uint8_t* d_byt
   CU(cudaStreamSynchronize(idx->stream));   // kernel complete => its peer stores are visible system-wide
   if (n_kmers) *n_kmers = host[CTR_NKMERS];
   if (host[CTR_PERR] & PERR_OVERFLOW) return fail(KMI_ERR_CAPACITY, "an owner region overflowed (skewed owners)");
-  for (u32 r = 0; r < p; ++r) h_send_counts[r] = idx->h_cursor[r];
+  for (u32 r = 0; r < n_bins; ++r) h_send_counts[r] = idx->h_cursor[r];
   return parse_error(host[CTR_PERR]);
 }
 
@@ -680,6 +719,35 @@ extern "C" int kmi_exchange_insert(kmi_index* idx, const uint64_t* h_recv_counts
   if (idx->cfg.mode != KMI_MODE_COUNT) return fail(KMI_ERR_UNSUPPORTED, "exchange insert is built for the count index");
   CU(cudaSetDevice(idx->cfg.device));
   const int p = idx->cfg.nranks;
+  if (idx->xchg_log_cb) {
+    // region s * CB + c holds the keys of source s whose slot hash starts with c: the 256 regions go to the fine scatter
+    // as they are (k_scatter_fine with log_pre = log2 CB), no coarse pass
+    u32 cur[N_BUCKETS + 1];
+    u64 total = 0;
+    for (int r = 0; r < N_BUCKETS; ++r) {
+      if (h_recv_counts[r] > idx->xchg_cap_bin) return fail(KMI_ERR_ARG, "receive count exceeds the sub-bin capacity");
+      cur[r] = (u32)h_recv_counts[r];
+      total += h_recv_counts[r];
+    }
+    cur[N_BUCKETS] = 0;
+    if (total == 0) return KMI_OK;
+    if (total > BUCKET_MAX_KEYS) return fail(KMI_ERR_ARG, "exchange round of %llu keys", (unsigned long long)total);
+    BucketSink bs;
+    bs.keys = reinterpret_cast<u64*>(idx->xchg_recv);
+    bs.cursor = idx->bkt_meta.as<u32>();
+    bs.hll = idx->bkt_meta.as<u32>() + META_HLL;
+    bs.capb = (u32)idx->xchg_cap_bin;
+    bs.ovf_cap = (u32)std::min<u64>(idx->xchg_ovf_cap, 0xffffffffULL);
+    bs.bases = nullptr;
+    bs.log_pre = idx->xchg_log_cb;
+    bs.pre_mask = (1u << idx->xchg_log_cb) - 1u;
+    CU(cudaMemcpyAsync(bs.cursor, cur, sizeof(cur), cudaMemcpyHostToDevice, idx->stream));
+    OK(zero_ctr(idx, CTR_PERR));
+    std::vector<u32> reg;
+    u64 host[CTR_N];
+    OK(bucket_readback(idx, bs, host, reg));
+    return bucket_commit(idx, bs, total, host[CTR_SIZE], reg);
+  }
   std::vector<const u64*> ptrs(p);
   std::vector<u64> cnt(p);
   u64 total = 0;

@@ -33,6 +33,11 @@ struct BucketSink {
   u32* hll;      // HLL_M registers: distinct-key estimate that sizes the table before the insert
   u64* const* bases;  // optional: explicit base pointer per region (peer-GPU receive regions of the
                       // fused exchange, kmi_exchange_*); null = regions are keys + b * capb
+  // What the keys of region r have in common: the top `log_pre` bits of their slot hash equal r & pre_mask.
+  // Local build: log_pre = LOG_BUCKETS, pre_mask = 255 (region = hash prefix). Receive buffer of the fused exchange:
+  // region = source rank * CB + prefix with CB = N_BUCKETS / nranks sub-bins, log_pre = log2(CB), pre_mask = CB - 1.
+  u32 log_pre = LOG_BUCKETS;
+  u32 pre_mask = N_BUCKETS - 1;
 };
 
 template <int NW> struct BucketSmem;
@@ -215,13 +220,17 @@ k_scatter_keys(const u64* __restrict__ keys, u64 n, BucketSink bs, u32* __restri
 template <int K>
 __global__ void __launch_bounds__(256) k_hll_buckets(BucketSink bs) {
   constexpr int NW = (K <= 32 ? 1 : 2);
-  const bool ovf = blockIdx.y == HLL_SAMPLE_BUCKETS;
-  const u32 b = ovf ? (u32)N_BUCKETS : blockIdx.y * HLL_SAMPLE;
+  // y-slice = (group, j): the region of group `y / 4` whose prefix covers sampled bucket j * HLL_SAMPLE; a local build
+  // has one group (region = bucket), the exchange buffer one per source rank; the last slice is the overflow region
+  const u32 n_groups = N_BUCKETS >> bs.log_pre;          // regions per prefix value
+  const bool ovf = blockIdx.y == HLL_SAMPLE_BUCKETS * n_groups;
+  const u32 grp = blockIdx.y / HLL_SAMPLE_BUCKETS, j = blockIdx.y % HLL_SAMPLE_BUCKETS;
+  const u32 b = ovf ? (u32)N_BUCKETS : (grp << bs.log_pre) + ((j * HLL_SAMPLE) >> (LOG_BUCKETS - bs.log_pre));
   const u32 n = ovf ? min(bs.cursor[N_BUCKETS], bs.ovf_cap) : min(bs.cursor[b], bs.capb);
   const u64 base = (u64)b * bs.capb;
   for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const u64 h = slot_hash<K>(load_key<NW>(bs.keys, base + i));
-    if (!ovf || hll_sampled(bucket_of(h))) hll_update(bs.hll, h);
+    if (hll_sampled(bucket_of(h))) hll_update(bs.hll, h);
   }
 }
 
@@ -362,11 +371,12 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
       if (i < m) {
         Key<1> kk; kk.w[0] = key[q];
         const u64 h = slot_hash<K>(kk);
-        fid[q] = (u32)(h >> (64 - LOG_BUCKETS - fs.log_f)) & (F - 1);
+        fid[q] = (u32)(h >> (64 - bs.log_pre - fs.log_f)) & (F - 1);
         rank[q] = atomicAdd(&hist[fid[q]], 1u);
       }
     }
     __syncthreads();
+    const u64 region0 = (u64)(b & bs.pre_mask) << fs.log_f;   // first fine region (= table segment) of this hash prefix
     u32 gb1 = 0, ex1 = 0, cnt1 = 0;                       // EPT == 1: the cursor atomic stays in flight during the sort
     {
       u32 local = 0;
@@ -375,7 +385,7 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
       u32 ex = block_excl_scan_nb(local, tmp, total);
       if (EPT == 1) {
         if ((u32)t < F) {
-          if (local) gb1 = atomicAdd(fs.cursor + ((u64)b << fs.log_f) + t, local);
+          if (local) gb1 = atomicAdd(fs.cursor + region0 + t, local);
           hist[t] = ex; ex1 = ex; cnt1 = local;
         }
       } else {
@@ -384,7 +394,7 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
           if (f < F) {
             const u32 cnt = hist[f];
             hist[f] = ex;
-            if (cnt) delta[f] = atomicAdd(fs.cursor + ((u64)b << fs.log_f) + f, cnt) - ex;
+            if (cnt) delta[f] = atomicAdd(fs.cursor + region0 + f, cnt) - ex;
             ex += cnt;
           }
         }
@@ -399,7 +409,6 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
         sbid[pos] = (unsigned short)fid[q];
       }
     }
-    const u64 region0 = (u64)b << fs.log_f;
     if (EPT == 1 && (u32)t < F) {
       delta[t] = gb1 - ex1;
       const bool fits = (u64)gb1 + cnt1 <= (u64)fs.capf;

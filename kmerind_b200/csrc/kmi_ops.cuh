@@ -76,7 +76,7 @@ struct OpsImpl {
     if (n) k_scatter_keys<K, HASH><<<grid_for(n, TILE_THREADS * BktRound<NW>::R, 148u * 8u * 16u), TILE_THREADS, 0, st>>>(keys, n, bsink, perr, canon);
   }
   static void hll_buckets(cudaStream_t st, BucketSink bsink) {
-    k_hll_buckets<K><<<dim3(148u * 2u, HLL_SAMPLE_BUCKETS + 1), 256, 0, st>>>(bsink);
+    k_hll_buckets<K><<<dim3(148u * 2u, HLL_SAMPLE_BUCKETS * (N_BUCKETS >> bsink.log_pre) + 1), 256, 0, st>>>(bsink);
   }
   static void insert_buckets(cudaStream_t st, TableView t, BucketSink bsink, u64 n_hint) {
     k_insert_buckets<K, HASH><<<grid_for(n_hint ? n_hint : 1, 256, 148u * 8u), 256, 0, st>>>(t, bsink);

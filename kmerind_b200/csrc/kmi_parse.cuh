@@ -471,7 +471,9 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
           } else {
             u64 hs, hd;
             kmer_hashes<K, HASH>(key[q], hs, hd);
-            b = mod_ranks(hd, nranks);
+            b = mod_ranks(hd, nranks & 0xFFFFu);
+            const u32 lcb = nranks >> 16;                  // sub-bins per owner by slot-hash prefix (fused exchange)
+            if (lcb) b = (b << lcb) | (u32)(slot_hash<K>(key[q]) >> (64 - lcb));
           }
           bkt[q] = ((v >> q) & 1u) ? b : BKT_NONE;
         }

@@ -129,7 +129,7 @@ class ShardedIndex:
         except KmiError as e:
             if e.code != ERR_CAPACITY:
                 raise
-            n, send_counts = None, torch.full((p,), -1, dtype=torch.int64, device=self.device)  # skewed owners here
+            n, send_counts = None, torch.full((p * self.local.exchange_bins(),), -1, dtype=torch.int64, device=self.device)  # skewed owners here
         ev[1].record()
         recv_counts = exchange_counts(send_counts, self.group).cpu().numpy()   # also: "the writes are complete"
         bad = torch.tensor([1 if (n is None or (recv_counts < 0).any()) else 0], dtype=torch.int64, device=self.device)

@@ -78,6 +78,8 @@ def test_exchange_gloo_world2(tmp_path):
 
 
 def _nccl_worker(rank, world, port, out_dir, peer=False):
+    if peer == "prefix":          # sub-bin layout of the receive buffer (kmi_exchange_bins > 1)
+        os.environ["KMI_EXCHANGE_PREFIX"] = "1"
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
@@ -92,6 +94,7 @@ def _nccl_worker(rank, world, port, out_dir, peer=False):
         if peer:
             idx.local.set_build_path(2)   # received keys take the bucketed insert even at this size
             assert idx.enable_peer_exchange(n_reads * 120), "CUDA IPC peer mapping failed"
+            assert idx.local.exchange_bins() == (128 if peer == "prefix" else 1)
         n = idx.build_fastq_dev(text, buf.size)
         assert n == n_reads * 120
         if peer:
@@ -116,7 +119,7 @@ def _nccl_worker(rank, world, port, out_dir, peer=False):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("peer", (False, True))
+@pytest.mark.parametrize("peer", (False, True, "prefix"))
 def test_sharded_count_index_nccl_world2(tmp_path, peer):
     """peer=False: keys travel by NCCL all-to-all; peer=True: the parse kernel stores them straight into
     the owners' HBM over NVLink (kmi_exchange_*), and the build is run twice (counts double)."""
