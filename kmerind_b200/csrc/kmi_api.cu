@@ -114,7 +114,16 @@ struct kmi_index {
   cudaStream_t copy_stream = nullptr;        // H2D copies of the pipelined host-pointer build
   std::vector<cudaEvent_t> copy_events;    // parse+scatter share of the last bucketed build
 
-  TableView view() const {
+  // Lazy clear: `virgin` = the table is logically empty but its memory has not been written. The segment insert of a
+  // bucketed build initialises every segment in shared memory and writes all of them, so a build into an empty table
+  // never pays the 16 B/slot clear nor the read of empty segments; everything else goes through view(), which clears first.
+  bool virgin = false;
+  void touch() {
+    if (virgin && slots) { ops->table_clear(stream, slots, cap); launches++; }
+    virgin = false;
+  }
+  TableView view() { touch(); return raw_view(); }
+  TableView raw_view() const {
     TableView t;
     t.slots = slots; t.mask = cap - 1; t.shift = 64u - (u32)__builtin_ctzll(cap ? cap : 1); t.size = ctr + CTR_SIZE; t.error = reinterpret_cast<u32*>(ctr + CTR_ERR);
     return t;
@@ -156,13 +165,11 @@ static int check_table_error(kmi_index* idx) {
   return KMI_OK;
 }
 
-// allocate a cleared table of `cap` slots
+// allocate a table of `cap` slots (contents undefined: the caller clears it or marks the index virgin)
 static int table_alloc(kmi_index* idx, u64 cap, void** out) {
   void* p = nullptr;
   cudaError_t e = cudaMalloc(&p, cap * idx->slot_bytes);
   if (e != cudaSuccess) return fail(KMI_ERR_NOMEM, "cudaMalloc table %llu slots: %s", (unsigned long long)cap, cudaGetErrorString(e));
-  idx->ops->table_clear(idx->stream, p, cap);
-  idx->launches++;
   *out = p;
   return KMI_OK;
 }
@@ -173,12 +180,16 @@ static int table_grow(kmi_index* idx, u64 new_cap) {
   OK(table_alloc(idx, new_cap, &fresh));
   void* old = idx->slots;
   u64 old_cap = idx->cap;
+  const bool old_has_content = old && !idx->virgin;
   idx->slots = fresh;
   idx->cap = new_cap;
+  idx->virgin = true;                                   // nothing written yet
   OK(zero_ctr(idx, CTR_SIZE));
-  if (old) {
-    idx->ops->rehash(idx->stream, old, old_cap, idx->view());
+  if (old_has_content) {
+    idx->ops->rehash(idx->stream, old, old_cap, idx->view());   // view() clears the new table first
     idx->launches++;
+  }
+  if (old) {
     CU(cudaStreamSynchronize(idx->stream));
     CU(cudaFree(old));
   }
@@ -301,7 +312,7 @@ extern "C" int kmi_reserve(kmi_index* idx, uint64_t n_distinct) {
 extern "C" int kmi_clear(kmi_index* idx) {
   if (!idx) return fail(KMI_ERR_ARG, "null index");
   CU(cudaSetDevice(idx->cfg.device));
-  if (idx->slots) { idx->ops->table_clear(idx->stream, idx->slots, idx->cap); idx->launches++; }
+  idx->virgin = idx->slots != nullptr;                  // cleared lazily (kmi_index::touch) or never (segment insert)
   CU(cudaMemsetAsync(idx->ctr, 0, sizeof(u64) * CTR_N, idx->stream));
   idx->size_exact = idx->size_upper = 0;
   idx->log_n = 0;
@@ -424,8 +435,10 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
     }
     if (fine_ok) {
       CU(cudaEventRecord(idx->kev[1], idx->stream));
-      int e = idx->ops->insert_segments(idx->stream, idx->view(), fs, bs, (u32)log_seg, (u32)n_regions,
-                                        reinterpret_cast<u32*>(idx->ctr + CTR_PERR));
+      const bool fresh_table = idx->virgin;             // every segment is initialised in shared memory and written
+      int e = idx->ops->insert_segments(idx->stream, idx->raw_view(), fs, bs, (u32)log_seg, (u32)n_regions,
+                                        reinterpret_cast<u32*>(idx->ctr + CTR_PERR), fresh_table);
+      idx->virgin = false;
       if (e) return fail(KMI_ERR_CUDA, "segment kernel configuration: %s", cudaGetErrorString((cudaError_t)e));
       CU(cudaEventRecord(idx->kev[2], idx->stream));
       idx->ops->insert_overflow(idx->stream, idx->view(), bs);
@@ -842,7 +855,7 @@ static int build_fastq_bucketed(kmi_index* idx, uint8_t* d_bytes, size_t n, u64 
     OK(bucket_prepare(idx, tiles * TILE_BYTES / 2 + 1, &bs));
     CU(cudaEventRecord(idx->ev[4], idx->stream));
     idx->ops->fastq_kmers(idx->stream, 2, d_bytes, n, tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), nosink,
-                          idx->view(), bs, idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR),
+                          idx->raw_view() /* unused by sink 2: no lazy clear */, bs, idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR),
                           idx->cfg.canonical != 0, idx->cfg.nsplit != 0, p0, 1);
     idx->launches++;
     CU(cudaEventRecord(idx->ev[5], idx->stream));
@@ -1008,6 +1021,7 @@ static int csr_finalize(kmi_index* idx) {
   OK(idx->offsets.ensure(sizeof(u64) * idx->cap));
   OK(idx->csr_sums.ensure(sizeof(u64) * n_blocks));
   OK(idx->values.ensure(sizeof(u64) * std::max<u64>(idx->log_n, 1)));
+  idx->touch();
   idx->ops->zero_aux(idx->stream, idx->slots, idx->cap);
   idx->ops->csr_scan_l1(idx->stream, idx->slots, idx->cap, idx->offsets.as<u64>(), idx->csr_sums.as<u64>());
   k_scan64<<<1, 1024, 0, idx->stream>>>(idx->csr_sums.as<u64>(), n_blocks);
@@ -1199,6 +1213,7 @@ extern "C" int kmi_dump(kmi_index* idx, uint64_t* keys, uint64_t* vals, size_t c
   if (r == KMI_OK) r = dv.ensure(size * sizeof(u64));
   if (r == KMI_OK) {
     zero_ctr(idx, CTR_CURSOR);
+    idx->touch();
     idx->ops->dump(idx->stream, idx->slots, idx->cap, dk.as<u64>(), dv.as<u64>(), size, idx->ctr + CTR_CURSOR);
     idx->launches++;
     cudaError_t e = cudaSuccess;
@@ -1216,6 +1231,7 @@ extern "C" int kmi_checksum(kmi_index* idx, uint64_t* key_value_sum, uint64_t* v
   if (!idx) return fail(KMI_ERR_ARG, "null argument");
   CU(cudaSetDevice(idx->cfg.device));
   OK(zero_ctr(idx, CTR_CK0, 2));
+  idx->touch();
   if (idx->slots) { idx->ops->checksum(idx->stream, idx->slots, idx->cap, idx->ctr + CTR_CK0); idx->launches++; }
   u64 host[2];
   CU(cudaMemcpyAsync(host, idx->ctr + CTR_CK0, sizeof(host), cudaMemcpyDeviceToHost, idx->stream));

@@ -464,7 +464,8 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 // iteration is therefore one probe for every lane, instead of max-over-lanes probes per key.
 template <int K, int HASH>
 __global__ void __launch_bounds__(SEG_THREADS, KMI_SEG_MINB)
-k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, const u32 n_segs, u32* __restrict__ perr) {
+k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, const u32 n_segs, u32* __restrict__ perr,
+                  const u32 fresh) {
   static_assert(K <= 32, "segment path is built for one-word keys");
   extern __shared__ __align__(16) unsigned char seg_raw[];
   const u32 SEG = 1u << log_seg;
@@ -480,7 +481,7 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
   u32 n_new = 0;
   for (u32 s = blockIdx.x; s < n_segs; s += gridDim.x) {
     const u32 cnt = min(fs.cursor[s], fs.capf);
-    if (cnt == 0) continue;                               // block-uniform
+    if (cnt == 0 && !fresh) continue;                     // block-uniform (a fresh table still needs its EMPTY pattern written)
     const u64* src = fs.keys + (u64)s * fs.capf;
     const u32 per = ((cnt + NWARP * 32 - 1) / (NWARP * 32)) * 32;   // keys per warp, whole 32-key chunks
     const u32 wb = min(cnt, (u32)warp * per), we = min(cnt, wb + per);
@@ -504,13 +505,22 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
     }
 #endif
     uint4* gseg = reinterpret_cast<uint4*>(reinterpret_cast<Slot<1>*>(t.slots) + ((u64)s << log_seg));
+    // fresh: the table is logically empty and its memory was never written (lazy clear, kmi_clear): nothing to load
 #if KMI_SEG_SOA
-    for (u32 i = tid; i < SEG; i += SEG_THREADS) {
-      const uint4 v = gseg[i];
-      skey[i] = (u64)v.x | ((u64)v.y << 32); sval[i] = v.z;
+    if (fresh) {
+      for (u32 i = tid; i < SEG; i += SEG_THREADS) { skey[i] = KEY_EMPTY_TOP; sval[i] = 0u; }
+    } else {
+      for (u32 i = tid; i < SEG; i += SEG_THREADS) {
+        const uint4 v = gseg[i];
+        skey[i] = (u64)v.x | ((u64)v.y << 32); sval[i] = v.z;
+      }
     }
 #else
-    for (u32 i = tid; i < SEG; i += SEG_THREADS) reinterpret_cast<uint4*>(seg)[i] = gseg[i];
+    if (fresh) {
+      for (u32 i = tid; i < SEG; i += SEG_THREADS) reinterpret_cast<uint4*>(seg)[i] = make_uint4(0u, 0x80000000u, 0u, 0u);
+    } else {
+      for (u32 i = tid; i < SEG; i += SEG_THREADS) reinterpret_cast<uint4*>(seg)[i] = gseg[i];
+    }
 #endif
     __syncthreads();
     int remaining = (int)(we - wb);                       // keys of the slice not yet handed to a lane (warp-uniform)

@@ -19,7 +19,7 @@ struct Ops {
   void (*insert_buckets)(cudaStream_t, TableView, BucketSink bsink, u64 n_hint);
   // second level (one-word keys only; null for K > 32): fine scatter, shared-memory segment insert
   void (*scatter_fine)(cudaStream_t, BucketSink bsink, FineSink fsink, u32* perr, u64 n_hint);
-  int (*insert_segments)(cudaStream_t, TableView, FineSink fsink, BucketSink bsink, u32 log_seg, u32 n_segs, u32* perr);
+  int (*insert_segments)(cudaStream_t, TableView, FineSink fsink, BucketSink bsink, u32 log_seg, u32 n_segs, u32* perr, bool fresh);
   void (*insert_overflow)(cudaStream_t, TableView, BucketSink bsink);
   // parse (FASTA) to a key(+id) stream; wide_halo selects the 1 KiB halo variant
   void (*fasta_kmers)(cudaStream_t, bool wide_halo, const uint8_t* bytes, u64 n, u64 n_tiles, const u32* tile_enc_scanned,
@@ -112,7 +112,7 @@ struct OpsImpl {
       k_scatter_fine<K, HASH><<<grid_for(n_hint ? n_hint : 1, FINE_ROUND, 148u * KMI_FINE_MINB * 32u), TILE_THREADS, smem, st>>>(bsink, fsink, perr);
     }
   }
-  static int insert_segments(cudaStream_t st, TableView t, FineSink fsink, BucketSink bsink, u32 log_seg, u32 n_segs, u32* perr) {
+  static int insert_segments(cudaStream_t st, TableView t, FineSink fsink, BucketSink bsink, u32 log_seg, u32 n_segs, u32* perr, bool fresh) {
     if constexpr (NW == 1) {
       const size_t smem = segment_smem(log_seg);
       if (smem > 48 * 1024) {
@@ -120,7 +120,7 @@ struct OpsImpl {
         if (e != cudaSuccess) return (int)e;
       }
       const unsigned grid = n_segs;   // one CTA per segment: the block scheduler balances the SMs (4.60 ms vs 4.85 at 64 CTAs per SM)
-      k_insert_segments<K, HASH><<<grid, SEG_THREADS, smem, st>>>(t, fsink, bsink, log_seg, n_segs, perr);
+      k_insert_segments<K, HASH><<<grid, SEG_THREADS, smem, st>>>(t, fsink, bsink, log_seg, n_segs, perr, fresh ? 1u : 0u);
     }
     return 0;
   }
