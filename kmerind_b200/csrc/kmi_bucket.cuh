@@ -462,6 +462,8 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 // loads, one ahead), and a lane that has finished its key takes the next unclaimed one from that window
 // (ballot + shuffle) in the same loop iteration in which the other lanes advance their probes. A loop
 // iteration is therefore one probe for every lane, instead of max-over-lanes probes per key.
+// EMPTY sentinel test on the top word alone: one-word keys are < 2^62, so no real key shares it
+__device__ __forceinline__ bool idle(u64 k) { return (u32)(k >> 32) == (u32)(KEY_EMPTY_TOP >> 32); }
 template <int K, int HASH>
 __global__ void __launch_bounds__(SEG_THREADS, KMI_SEG_MINB)
 k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, const u32 n_segs, u32* __restrict__ perr,
@@ -528,7 +530,7 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
     u64 key = KEY_EMPTY_TOP;
     u32 li = 0;
     for (;;) {
-      const u32 need = __ballot_sync(0xffffffffu, key == KEY_EMPTY_TOP);
+      const u32 need = __ballot_sync(0xffffffffu, idle(key));
       if (need && remaining > 0) {                        // warp-uniform
         const u32 idx = pos + __popc(need & lt);
         const u32 n = __popc(need);
@@ -541,7 +543,7 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
             const u64 k1 = __shfl_sync(0xffffffffu, N, idx & 31);                                  \
             if (idx >= 32) kx = k1;                                                                \
           }                                                                                        \
-          if (key == KEY_EMPTY_TOP) {                                                              \
+          if (idle(key)) {                                                                         \
             key = kx;                                                                              \
             Key<1> kk; kk.w[0] = key;                                                              \
             li = (u32)(slot_hash<K>(kk) >> t.shift) & (SEG - 1);                                   \
@@ -559,17 +561,18 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
         else KMI_REFILL(buf2, buf0)
 #undef KMI_REFILL
       }
-      if (__ballot_sync(0xffffffffu, key != KEY_EMPTY_TOP) == 0) break;
-      if (key != KEY_EMPTY_TOP) {
+      // every lane holds a key while the slice still has some; only at its end does the warp have to vote
+      if (remaining <= 0 && __ballot_sync(0xffffffffu, !idle(key)) == 0) break;
+      if (!idle(key)) {
 #if KMI_SEG_SOA
         u64* const kp = skey + li; u32* const vp = sval + li;
 #else
         u64* const kp = &seg[li].key; u32* const vp = &seg[li].val;
 #endif
         u64 cur = *kp;
-        if (cur == KEY_EMPTY_TOP) {
+        if (idle(cur)) {
           cur = atomicCAS(kp, KEY_EMPTY_TOP, key);
-          if (cur == KEY_EMPTY_TOP) { ++n_new; cur = key; }
+          if (idle(cur)) { ++n_new; cur = key; }
         }
         if (cur == key) {
           atomicAdd(vp, 1u);
