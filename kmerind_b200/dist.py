@@ -189,6 +189,36 @@ class ShardedIndex:
         self.n_received = n_recv
         return n
 
+    def build_fastq_host(self, host, cuts, max_kmers_per_chunk=None):
+        """Host-buffer build of this rank's share (the sharded counterpart of kmi_build_fastq).
+
+        host: pinned CPU uint8 tensor with whole FASTQ records; cuts: record-aligned offsets [0, c1, ..., nbytes] (every
+        rank must pass the same NUMBER of chunks: each chunk is one collective exchange round). Chunk i+1 crosses PCIe on
+        a copy stream while chunk i is parsed, exchanged and inserted, so the transfer hides all but the last round."""
+        n_chunks = len(cuts) - 1
+        big = max(int(cuts[i + 1] - cuts[i]) for i in range(n_chunks)) if n_chunks else 0
+        if not hasattr(self, "_copy_stream"):
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        bufs = [self._buffer("_text%d" % j, (big + 64 + 7) // 8).view(torch.uint8) for j in range(2)]
+        done = [torch.cuda.Event() for _ in range(n_chunks)]
+
+        def copy(i):
+            a, b = int(cuts[i]), int(cuts[i + 1])
+            with torch.cuda.stream(self._copy_stream):
+                bufs[i % 2][:b - a].copy_(host[a:b], non_blocking=True)
+                done[i].record(self._copy_stream)
+
+        self._copy_stream.wait_stream(torch.cuda.current_stream(self.device))   # the staging buffers may still be in use
+        total = 0
+        if n_chunks:
+            copy(0)
+        for i in range(n_chunks):
+            if i + 1 < n_chunks:
+                copy(i + 1)       # its buffer held chunk i-1, whose parse has completed (the call below is synchronous)
+            torch.cuda.current_stream(self.device).wait_event(done[i])
+            total += self.build_fastq_dev(bufs[i % 2], int(cuts[i + 1] - cuts[i]), max_kmers=max_kmers_per_chunk)
+        return total
+
     def _build_fastq_dev_unfused(self, text, nbytes, max_kmers=None):
         nw = self.nw
         cap = max_kmers if max_kmers is not None else max(nbytes // 2 + 1, 1)

@@ -100,6 +100,10 @@ def _nccl_worker(rank, world, port, out_dir, peer=False):
         if peer:
             assert "parse+scatter+exchange" in idx.stage_ms
             assert idx.build_fastq_dev(text, buf.size) == n   # a second round through the same buffers
+            # third time from a pinned host buffer in 3 record-aligned chunks (H2D copies pipelined with the rounds)
+            host = torch.from_numpy(buf.copy()).pin_memory()
+            rec = buf.size // n_reads
+            assert idx.build_fastq_host(host, [0, 10000 * rec, 20000 * rec, buf.size]) == n
 
         k, c = idx.local.sorted_dump()
         np.save(os.path.join(out_dir, "k%d.npy" % rank), k)
@@ -122,7 +126,7 @@ def _nccl_worker(rank, world, port, out_dir, peer=False):
 @pytest.mark.parametrize("peer", (False, True, "prefix"))
 def test_sharded_count_index_nccl_world2(tmp_path, peer):
     """peer=False: keys travel by NCCL all-to-all; peer=True: the parse kernel stores them straight into
-    the owners' HBM over NVLink (kmi_exchange_*), and the build is run twice (counts double)."""
+    the owners' HBM over NVLink (kmi_exchange_*), and the build is run three times, the last one from pinned host memory in chunks (counts triple)."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     world = 2
@@ -132,7 +136,7 @@ def test_sharded_count_index_nccl_world2(tmp_path, peer):
     keys = np.concatenate([ou.fastq_kmers(b, 31)[0] for b in bufs])
     wk, wc = ou.count_sorted(keys, 31)
     if peer:
-        wc = 2 * wc
+        wc = 3 * wc
     owner = (ou.hashes(wk, 31, 3) % np.uint64(world)).astype(np.int64)
     for r in range(world):
         k = np.load(tmp_path / ("k%d.npy" % r))
