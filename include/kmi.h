@@ -86,7 +86,8 @@ int kmi_clear(kmi_index* idx);
  *      KmerFileHelper::read_file_posix + Index::insert, kmer_file_helper.hpp:622-633) ------------
  * `bytes` must start at a record boundary (FASTQ: an '@' header line; FASTA: anywhere in line
  * start position) and hold whole records; `file_offset` is the offset of bytes[0] in the file
- * (only used for position ids). Every k-mer of the block is inserted into THIS index regardless
+ * (only used for position ids: a POSITION-mode index built from FASTQ stores ShortSequenceKmerId values, from FASTA
+ * LongSequenceKmerId values). Every k-mer of the block is inserted into THIS index regardless
  * of owner (nranks == 1 semantics); the sharded build is parse_*_dev + partition_dev + exchange +
  * insert_dev. n_kmers (optional) receives the number of k-mer occurrences generated. */
 int kmi_build_fastq(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers);
@@ -97,7 +98,10 @@ int kmi_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64
 /* ---- stages, device resident ------------------------------------- */
 /* a2-a10: record boundaries + 2-bit encode + sliding window (+ lex_less if cfg.canonical).
  * Writes up to `cap` keys (nw words each) and, if d_ids != NULL, their position ids
- * (FASTA: LongSequenceKmerId, sequence.hpp:180-236). Order of the output is unspecified. */
+ * (FASTA: LongSequenceKmerId = seq_id << 40 | file byte of the first base, sequence.hpp:180-236;
+ *  FASTQ: ShortSequenceKmerId = (file offset of the record's '@' & (2^40 - 1)) << 16, plus the offset of the first base
+ *  inside the record, sequence.hpp:103-160, kmer_parser.hpp:378-399, with file offset = file_offset + offset in d_bytes).
+ * Order of the output is unspecified. */
 int kmi_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset,
                         uint64_t* d_keys, uint64_t* d_ids, size_t cap, uint64_t* n_kmers);
 int kmi_parse_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n,

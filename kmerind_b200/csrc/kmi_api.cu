@@ -83,6 +83,7 @@ struct kmi_index {
   u64 size_exact = 0;      // last size read back
   u64 size_upper = 0;      // upper bound on the current size (exact + keys issued since)
   // scratch
+  DevBuf tile_rec;   // FASTQ position ids: record start open at every tile (k_fastq_rec_carry)
   DevBuf tile_lines, block_sums, stage_in, stage_keys, stage_vals, stage_out, stage_found, hist, hist_sums;
   // POSITION mode: tuple log + CSR
   DevBuf log_keys, log_ids, log_keys2, log_ids2, offsets, csr_sums, values;
@@ -524,6 +525,15 @@ static int fastq_scan(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64* n_t
   OK(fastq_scan_alloc(idx, d_bytes, n, n_tiles_out));
   return fastq_scan_range(idx, d_bytes, n, 0, *n_tiles_out);
 }
+// record start that is open at the first byte of every tile (FASTQ position ids); after fastq_scan
+static int fastq_rec_carry(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64 n_tiles) {
+  if (n_tiles == 0) return KMI_OK;
+  OK(idx->tile_rec.ensure(sizeof(u64) * n_tiles));
+  k_fastq_rec_carry<<<(unsigned)std::min<u64>((n_tiles + 7) / 8, 148 * 16), COUNT_THREADS, 0, idx->stream>>>(
+      d_bytes, n, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), idx->tile_rec.as<u64>(), (u32)n_tiles);
+  idx->launches++;
+  return KMI_OK;
+}
 static int parse_error(u64 perr) {
   if (perr & PERR_NO_AT) return fail(KMI_ERR_FORMAT, "malformed FASTQ: missing @ on first line of a record");
   if (perr & PERR_NO_PLUS) return fail(KMI_ERR_FORMAT, "malformed FASTQ: missing + on third line of a record");
@@ -535,16 +545,16 @@ static int parse_error(u64 perr) {
 
 extern "C" int kmi_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset,
                                    uint64_t* d_keys, uint64_t* d_ids, size_t cap, uint64_t* n_kmers) {
-  (void)file_offset;
   if (!idx || (!d_bytes && n)) return fail(KMI_ERR_ARG, "null argument");
-  if (d_ids) return fail(KMI_ERR_UNSUPPORTED, "FASTQ position ids (ShortSequenceKmerId) are not built yet");
   CU(cudaSetDevice(idx->cfg.device));
   u64 n_tiles = 0;
   OK(fastq_scan(idx, d_bytes, n, &n_tiles));
+  if (d_ids) OK(fastq_rec_carry(idx, d_bytes, n, n_tiles));
   OK(zero_ctr(idx, CTR_NKMERS, 2));  // NKMERS, CURSOR
   OK(zero_ctr(idx, CTR_PERR));
   KeySink sink;
-  sink.keys = reinterpret_cast<u64*>(d_keys); sink.ids = nullptr; sink.cap = cap; sink.cursor = idx->ctr + CTR_CURSOR;
+  sink.keys = reinterpret_cast<u64*>(d_keys); sink.ids = reinterpret_cast<u64*>(d_ids); sink.cap = cap; sink.cursor = idx->ctr + CTR_CURSOR;
+  sink.file_offset = file_offset; sink.tile_rec = d_ids ? idx->tile_rec.as<u64>() : nullptr;
   TableView none; none.slots = nullptr; none.mask = 0; none.shift = 63; none.size = nullptr; none.error = nullptr;
   idx->ops->fastq_kmers(idx->stream, 0, d_bytes, n, n_tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), sink, none, BucketSink(),
                         idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0,
@@ -881,9 +891,58 @@ static int build_fastq_bucketed(kmi_index* idx, uint8_t* d_bytes, size_t n, u64 
 }
 
 
-static int build_fastq_impl(kmi_index* idx, uint8_t* d_bytes, size_t n, const uint8_t* host_src, uint64_t* n_kmers) {
-  if (idx->cfg.mode != KMI_MODE_COUNT)
-    return fail(KMI_ERR_UNSUPPORTED, "FASTQ PositionIndex (ShortSequenceKmerId) is not built yet; use FASTA");
+// PositionIndex from FASTQ: (k-mer, ShortSequenceKmerId) tuples, chunk by chunk through the tuple log + table
+// (KmerPositionTupleParser, kmer_parser.hpp:465-567; densehash_multimap::insert)
+static int build_fastq_positions(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64 file_offset, uint64_t* n_kmers) {
+  if (n_kmers) *n_kmers = 0;
+  u64 n_tiles = 0;
+  OK(fastq_scan(idx, d_bytes, n, &n_tiles));
+  if (n_tiles == 0) return KMI_OK;
+  OK(fastq_rec_carry(idx, d_bytes, n, n_tiles));
+  OK(zero_ctr(idx, CTR_NKMERS));
+  OK(zero_ctr(idx, CTR_PERR));
+  const u64 CHUNK_TILES = 16384;  // 64 MiB of text -> <= 32 Mi k-mers
+  const u64 cap = std::min<u64>(n_tiles, CHUNK_TILES) * TILE_BYTES / 2 + 1;
+  DevBuf keys, ids;
+  int r = keys.ensure(cap * sizeof(u64) * idx->nw);
+  if (r == KMI_OK) r = ids.ensure(cap * sizeof(u64));
+  TableView none; none.slots = nullptr; none.mask = 0; none.shift = 63; none.size = nullptr; none.error = nullptr;
+  u64 total = 0, perr = 0;
+  for (u64 tile = 0; r == KMI_OK && tile < n_tiles; tile += CHUNK_TILES) {
+    const u64 tiles = std::min<u64>(CHUNK_TILES, n_tiles - tile);
+    KeySink sink;
+    sink.keys = keys.as<u64>(); sink.ids = ids.as<u64>(); sink.cap = cap; sink.cursor = idx->ctr + CTR_CURSOR;
+    sink.file_offset = file_offset; sink.tile_rec = idx->tile_rec.as<u64>();
+    r = zero_ctr(idx, CTR_CURSOR);
+    if (r != KMI_OK) break;
+    idx->ops->fastq_kmers(idx->stream, 0, d_bytes, n, tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), sink, none,
+                          BucketSink(), idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR),
+                          idx->cfg.canonical != 0, idx->cfg.nsplit != 0, tile, 1);
+    idx->launches++;
+    u64 produced = 0;
+    r = read_ctr(idx, CTR_CURSOR, &produced);
+    if (r == KMI_OK) r = read_ctr(idx, CTR_PERR, &perr);
+    if (r != KMI_OK || perr) break;
+    const int32_t canon = idx->cfg.canonical;   // keys are canonical already
+    idx->cfg.canonical = 0;
+    r = kmi_insert_dev(idx, keys.as<uint64_t>(), ids.as<uint64_t>(), produced);
+    idx->cfg.canonical = canon;
+    cudaStreamSynchronize(idx->stream);
+    total += produced;
+  }
+  keys.release(); ids.release();
+  if (r != KMI_OK) return r;
+  if (perr) return parse_error(perr);
+  if (n_kmers) *n_kmers = total;
+  return check_table_error(idx);
+}
+
+static int build_fastq_impl(kmi_index* idx, uint8_t* d_bytes, size_t n, const uint8_t* host_src, uint64_t* n_kmers,
+                            u64 file_offset = 0) {
+  if (idx->cfg.mode != KMI_MODE_COUNT) {
+    if (host_src) CU(cudaMemcpyAsync(d_bytes, host_src, n, cudaMemcpyHostToDevice, idx->stream));
+    return build_fastq_positions(idx, d_bytes, n, file_offset, n_kmers);
+  }
   u64 n_tiles = 0;
   const bool bucketed = idx->build_path == 2 || (idx->build_path == 0 && n >= AUTO_BUCKET_BYTES);
   CU(cudaEventRecord(idx->ev[0], idx->stream));
@@ -922,19 +981,17 @@ static int build_fastq_impl(kmi_index* idx, uint8_t* d_bytes, size_t n, const ui
 }
 
 extern "C" int kmi_build_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers) {
-  (void)file_offset;
   if (!idx || (!d_bytes && n)) return fail(KMI_ERR_ARG, "null argument");
   CU(cudaSetDevice(idx->cfg.device));
-  return build_fastq_impl(idx, const_cast<uint8_t*>(d_bytes), n, nullptr, n_kmers);
+  return build_fastq_impl(idx, const_cast<uint8_t*>(d_bytes), n, nullptr, n_kmers, file_offset);
 }
 
 // host bytes: the H2D copy is pipelined with the build (bucketed path), see build_fastq_bucketed
 extern "C" int kmi_build_fastq(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers) {
-  (void)file_offset;
   if (!idx || (!bytes && n)) return fail(KMI_ERR_ARG, "null argument");
   CU(cudaSetDevice(idx->cfg.device));
   OK(idx->stage_in.ensure(n + 64));
-  return build_fastq_impl(idx, idx->stage_in.as<uint8_t>(), n, bytes, n_kmers);
+  return build_fastq_impl(idx, idx->stage_in.as<uint8_t>(), n, bytes, n_kmers, file_offset);
 }
 
 // ---- insert --------------------------------------------------------------------------------------------

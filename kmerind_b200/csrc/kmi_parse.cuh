@@ -126,6 +126,58 @@ __global__ void __launch_bounds__(COUNT_THREADS) k_fastq_count_lines(const uint8
   }
 }
 
+// ---- record starts for FASTQ position ids (ShortSequenceKmerId, src/common/sequence.hpp:103-160) ----------
+// tile_rec[tile] = 1 + offset of the '@' line (line index 0 mod 4) that is open at the tile's first byte, i.e. the
+// most recent header-line start strictly before the tile; 0 when there is none. With F line starts before the tile,
+// that is the j-th line start walking backwards, j = F mod 4 (4 when F mod 4 == 0). One warp per tile walks back in
+// 512-byte windows (a record header is normally found in the first one; long reads take more).
+__global__ void __launch_bounds__(COUNT_THREADS) k_fastq_rec_carry(const uint8_t* __restrict__ bytes, u64 n,
+                                                                    const u32* __restrict__ tile_lines,
+                                                                    const u32* __restrict__ block_sums,
+                                                                    u64* __restrict__ tile_rec, const u32 n_tiles) {
+  const int lane = threadIdx.x & 31;
+  const u32 warps = gridDim.x * (COUNT_THREADS / 32);
+  for (u32 tile = blockIdx.x * (COUNT_THREADS / 32) + (threadIdx.x >> 5); tile < n_tiles; tile += warps) {
+    const u32 first = tile_lines[tile] + block_sums[tile >> 10];
+    u32 j = first & 3u;
+    if (j == 0) j = 4;
+    u64 end = (u64)tile * TILE_BYTES, found = 0;
+    while (end > 0) {                                       // warp-uniform
+      const u64 start = end >= 512 ? end - 512 : 0;         // 16-byte aligned: end is
+      const u64 off = start + (u64)lane * GROUP_BYTES;
+      u32 e = 0xFFFFu;
+      if (off < end) e = eol16(load_group(bytes, off, n));
+      u32 left = __shfl_up_sync(0xffffffffu, e, 1);
+      bool prev = ((left >> 15) & 1u) != 0;
+      if (lane == 0) prev = prev_is_eol(bytes, off, n);
+      const u32 ls = (off < end) ? line_starts(e, prev) : 0u;
+      u32 suf = __popc(ls);                                 // line starts in lanes >= this one (closest to the tile last)
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const u32 o = __shfl_down_sync(0xffffffffu, suf, d);
+        if (lane + d < 32) suf += o;
+      }
+      const u32 total = __shfl_sync(0xffffffffu, suf, 0);
+      if (total >= j) {
+        const u32 have = __ballot_sync(0xffffffffu, suf >= j);   // lanes 0..L
+        const int L = 31 - __clz((int)have);
+        const u32 suf_next = __shfl_sync(0xffffffffu, suf, min(L + 1, 31));
+        if (lane == L) {
+          u32 k = j - ((L == 31) ? 0u : suf_next);          // the k-th last set bit of this lane's mask
+          u32 m = ls;
+          while (k > 1) { m &= ~(1u << (31 - __clz((int)m))); --k; }
+          found = off + (u64)(31 - __clz((int)m)) + 1;
+        }
+        found = __shfl_sync(0xffffffffu, found, L);
+        break;
+      }
+      j -= total;
+      end = start;
+    }
+    if (lane == 0) tile_rec[tile] = found;
+  }
+}
+
 // exclusive scan of the per-tile counts (modulo 2^32: only the value mod 4 matters downstream)
 __global__ void __launch_bounds__(1024) k_scan_tiles(u32* __restrict__ v, u64 n, u32* __restrict__ carry_io = nullptr) {
   __shared__ u32 tmp[33];
@@ -308,7 +360,13 @@ template <int K> struct Roll {
 // ---- sinks: what happens to a generated k-mer ---------------------------------------------------
 struct KeySink {     // dense key (+id) stream
   u64* keys; u64* ids; u64 cap; u64* cursor;
+  u64 file_offset = 0;            // offset of bytes[0] in the file (FASTQ position ids)
+  const u64* tile_rec = nullptr;  // k_fastq_rec_carry output, needed when ids != nullptr
 };
+// per-group record starts inside the tile (position-id variant of the FASTQ parser only)
+template <bool ON> struct RecSmem { u32 unused; };
+template <> struct RecSmem<true> { u32 hdr[TILE_THREADS]; u32 before[TILE_THREADS]; u32 tmp[TILE_THREADS / 32]; };
+
 
 // ---- pass B: FASTQ tile -> k-mers ------------------------------------------------------------------
 // SINK 0: write canonical (or forward) keys to sink.keys (block-contiguous, order of blocks free)
@@ -333,6 +391,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   __shared__ u32 s_tmp[TILE_THREADS / 32 + 1], s_tmp2[TILE_THREADS / 32 + 1];
   __shared__ u32 s_ent[TILE_THREADS * (GROUP_BYTES / BktRound<(K <= 32 ? 1 : 2)>::R)];   // entry list (P4)
   __shared__ u64 s_base;
+  __shared__ RecSmem<(SINK == 0)> s_rec;
 
   const int t = threadIdx.x;
   const u64 tile = tile_begin + blockIdx.x;
@@ -376,6 +435,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   {
     u32 idx = tile_first + before;  // number of line starts before this group
     u32 flags;
+    u32 hdr = 0;                    // 1 + byte of the last header-line ('@', line 0 mod 4) start in this group
     if (ls == 0) {
       // every byte of the group is on line (idx-1); sequence lines are 1 mod 4
       flags = (idx != 0 && ((idx - 1) & 3u) == 1u) ? (~g.eol & 0xFFFFu) : 0u;
@@ -390,6 +450,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
         const u32 c = byte_of(v, (int)hi);
         if ((idx & 3u) == 0u && c != '@') err |= PERR_NO_AT;
         if ((idx & 3u) == 2u && c != '+') err |= PERR_NO_PLUS;
+        if ((idx & 3u) == 0u) hdr = hi + 1u;
         ++idx; lo = hi; m &= m - 1;
       }
       flags &= ~g.eol;
@@ -415,6 +476,26 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
       s_flags[TILE_THREADS + t] = hflags & 0xFFFFu;
     }
     if (t == 0) s_flags[TILE_GROUPS] = 0;
+    if (SINK == 0) {
+      if (sink.ids) {               // position ids: latest header start before every group (block max-scan, 1-based)
+        RecSmem<true>& rs = reinterpret_cast<RecSmem<true>&>(s_rec);
+        const int lane = t & 31, warp = t >> 5;
+        const u32 x = hdr ? (u32)t * GROUP_BYTES + hdr : 0u;
+        u32 inc = x;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const u32 o = __shfl_up_sync(0xffffffffu, inc, d);
+          if (lane >= d) inc = max(inc, o);
+        }
+        if (lane == 31) rs.tmp[warp] = inc;
+        rs.hdr[t] = x;
+        __syncthreads();
+        u32 ex = __shfl_up_sync(0xffffffffu, inc, 1);
+        if (lane == 0) ex = 0;
+        for (int w = 0; w < warp; ++w) ex = max(ex, rs.tmp[w]);
+        rs.before[t] = ex;
+      }
+    }
   }
   __syncthreads();
 
@@ -489,6 +570,19 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
     u64 at = s_base + (ent >> 18);
     RollT roll;
     roll.load(s_codes, ent & 1023u, CANON);
+    u64 id0 = 0;                    // ShortSequenceKmerId of start position 0 of the entry
+    if (SINK == 0) {
+      if (sink.ids) {
+        const RecSmem<true>& rs = reinterpret_cast<const RecSmem<true>&>(s_rec);
+        const u32 g = (ent & 1023u) >> RollT::LOG_EPG, pos0 = g * GROUP_BYTES + (ent & (EPG - 1)) * R;
+        const u32 first = pos0 + (u32)__ffs((int)v) - 1u, own = rs.hdr[g];
+        u64 rec;                    // file-buffer offset of the record's '@'
+        if (own && own - 1u <= first) rec = tile_off + own - 1u;
+        else if (rs.before[g]) rec = tile_off + rs.before[g] - 1u;
+        else rec = sink.tile_rec[tile] - 1u;                 // record opened in an earlier tile (0 - 1 if none: malformed, flagged by PERR_NO_AT)
+        id0 = (((sink.file_offset + rec) & 0xFFFFFFFFFFULL) << 16) + (tile_off + pos0 - rec);
+      }
+    }
 #pragma unroll
     for (int q = 0; q < R; ++q) {
       if (!((v >> q) & 1u)) continue;
@@ -497,6 +591,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
         if (at < sink.cap) {
 #pragma unroll
           for (int w = 0; w < NW; ++w) sink.keys[at * NW + w] = key.w[w];
+          if (sink.ids) sink.ids[at] = id0 + (u64)q;
         } else {
           atomicOr(perr, PERR_OVERFLOW);
         }

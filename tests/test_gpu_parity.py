@@ -45,7 +45,7 @@ def sort_keys(keys, k):
     return np.sort(keys)
 
 
-def gpu_parse(buf, k, fasta=False, canonical=True, nsplit=False, want_ids=False, hash=kb.HASH_MURMUR):
+def gpu_parse(buf, k, fasta=False, canonical=True, nsplit=False, want_ids=False, hash=kb.HASH_MURMUR, file_offset=0):
     nw = ou.nwords(k)
     with kb.Index(k=k, canonical=canonical, nsplit=nsplit, hash=hash) as idx:
         text = dev_text(buf)
@@ -55,7 +55,8 @@ def gpu_parse(buf, k, fasta=False, canonical=True, nsplit=False, want_ids=False,
         if fasta:
             n = idx.parse_fasta_dev(text.data_ptr(), buf.size, keys.data_ptr(), cap, ids.data_ptr() if want_ids else None)
         else:
-            n = idx.parse_fastq_dev(text.data_ptr(), buf.size, keys.data_ptr(), cap)
+            n = idx.parse_fastq_dev(text.data_ptr(), buf.size, keys.data_ptr(), cap, ids.data_ptr() if want_ids else None,
+                                    file_offset)
         torch.cuda.synchronize()
         k_host = ou.shape_keys(host_u64(keys)[:n * nw].copy(), k)
         return k_host, (host_u64(ids)[:n].copy() if want_ids else None)
@@ -146,6 +147,60 @@ def test_fastq_ragged_random_records():
             want, _, _ = ou.fastq_kmers(buf, k, nsplit=nsplit)
             got, _ = gpu_parse(buf, k, nsplit=nsplit)
             assert np.array_equal(sort_keys(got, k), sort_keys(want, k)), (k, nsplit)
+
+
+def _ragged_fastq(seed, n_rec, max_len):
+    rng = np.random.default_rng(seed)
+    parts = []
+    for r in range(n_rec):
+        L = int(rng.integers(1, max_len))
+        seq = bytes(rng.choice(np.frombuffer(b"ACGTN", dtype=np.uint8), size=L, p=[.245, .245, .245, .245, .02]))
+        eol = b"\r\n" if r % 7 == 0 else b"\n"
+        name = b"@" if r % 13 == 0 else b"@read%d some description" % r      # 1-byte headers: '@' and bases in one 16-byte group
+        parts.append(name + eol + seq + eol + b"+" + eol + b"@" * L + eol + (b"\n" if r % 11 == 0 else b""))
+    return np.frombuffer(b"".join(parts), dtype=np.uint8)
+
+
+@pytest.mark.parametrize("case", ("fixtures", "edge", "ragged", "long_reads"))
+def test_fastq_position_ids_match_oracle(case):
+    """ShortSequenceKmerId = (file offset of the record's '@' << 16) + offset in the record (sequence.hpp:103-160,
+    kmer_parser.hpp:378-399): the (k-mer, id) multiset equals the oracle's, also when the '@' lies in an earlier tile."""
+    if case == "fixtures":
+        bufs = [ou.read_fixture(n) for n in FASTQ]
+    elif case == "edge":
+        bufs = [np.frombuffer(b, dtype=np.uint8) for b in EDGE_FASTQ]
+    elif case == "ragged":
+        bufs = [_ragged_fastq(5, 3000, 400)]
+    else:
+        bufs = [_ragged_fastq(6, 40, 30000)]      # reads of up to 30 kbp: records span several 4 KiB tiles
+    for buf in bufs:
+        for k, nsplit, off in ((15, False, 0), (31, True, 12345678901), (63, False, 77)):
+            wk, wi, _ = ou.fastq_kmers(buf, k, nsplit=nsplit, want_ids=True, file_offset=off)
+            gk, gi = gpu_parse(buf, k, nsplit=nsplit, want_ids=True, file_offset=off)
+            assert len(gk) == len(wk)
+            a, b = ou.sort_tuples(wk, wi, k), ou.sort_tuples(gk, gi, k)
+            assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]), (case, k, nsplit)
+
+
+def test_fastq_position_index_equals_oracle():
+    buf = _ragged_fastq(8, 2000, 300)
+    k = 21
+    wk, wi, _ = ou.fastq_kmers(buf, k, want_ids=True, file_offset=4096)
+    swk, swi = ou.sort_tuples(wk, wi, k)
+    for host in (True, False):
+        with kb.PositionIndex(k) as idx:
+            if host:
+                n = idx.build_fastq(buf, file_offset=4096)
+            else:
+                text = dev_text(buf)
+                n = idx.build_fastq_dev(text.data_ptr(), buf.size, file_offset=4096)
+            assert n == len(wk) and idx.local_size() == len(wk)
+            gk, gi = idx.sorted_dump()
+            assert np.array_equal(gk, swk) and np.array_equal(gi, swi)
+            dk, dc = ou.count_sorted(wk, k)
+            sel = dk[:: max(1, len(dk) // 200)]
+            off, vals = idx.find_positions(sel)
+            assert np.diff(off.astype(np.int64)).tolist() == dc[:: max(1, len(dk) // 200)].tolist()
 
 
 def test_fastq_malformed_is_reported():
