@@ -404,10 +404,11 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
   const int log_cap = __builtin_ctzll(idx->cap);
   // (regions of the exchange buffer share only log_pre < 8 prefix bits: their fine scatter is wider, never skipped)
   const int log_pre = (int)bs.log_pre;
-  int log_segs = std::max(std::max(LOG_BUCKETS, log_pre + (log_pre < LOG_BUCKETS ? 1 : 0)), log_cap - KMI_LOG_SEG_SLOTS);
+  const int log_seg_slots = idx->nw == 1 ? KMI_LOG_SEG_SLOTS : LOG_SEG_SLOTS2;
+  int log_segs = std::max(std::max(LOG_BUCKETS, log_pre + (log_pre < LOG_BUCKETS ? 1 : 0)), log_cap - log_seg_slots);
   log_segs = std::min(log_segs, log_pre + MAX_LOG_F);
   const int log_seg = log_cap - log_segs;
-  if (idx->seg_path && idx->ops->insert_segments && idx->nw == 1 && log_seg <= 13 && log_seg >= 8) {
+  if (idx->seg_path && idx->ops->insert_segments && log_seg <= (idx->nw == 1 ? 13 : 12) && log_seg >= 8) {
     const u32 log_f = (u32)(log_segs - log_pre);
     const u64 n_regions = (u64)1 << log_segs;
     FineSink fs;
@@ -419,7 +420,7 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
     } else {
       const double mean = (double)n_keys / (double)n_regions;
       const u64 capf = (u64)(mean + 8.0 * std::sqrt(mean) + 32.0);
-      OK(idx->fine_keys.ensure(n_regions * capf * sizeof(u64)));
+      OK(idx->fine_keys.ensure(n_regions * capf * sizeof(u64) * idx->nw));
       OK(idx->fine_cur.ensure(n_regions * sizeof(u32)));
       CU(cudaMemsetAsync(idx->fine_cur.p, 0, n_regions * sizeof(u32), idx->stream));
       fs.keys = idx->fine_keys.as<u64>(); fs.cursor = idx->fine_cur.as<u32>(); fs.capf = (u32)capf;

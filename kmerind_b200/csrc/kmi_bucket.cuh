@@ -598,6 +598,193 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
   if ((tid & 31) == 0 && n_new) atomicAdd(t.size, (u64)n_new);
 }
 
+// ======================================================================================================
+// Two-word keys (33 <= K <= 63): the same second level with 16-byte keys and 32-byte slots.
+// Shared memory has no 128-bit CAS, so a slot is claimed in two steps: CAS of its top word from EMPTY to LOCK,
+// low word stored, top word published; a prober that sees LOCK looks at the same slot again (the claiming lane
+// never waits in between, so this cannot dead-lock inside a warp).
+// ======================================================================================================
+static constexpr int FINE_ROUND2 = 1024;
+static constexpr int LOG_SEG_SLOTS2 = 11;                 // 2048 slots x 20 B (hi[] + lo[] + val[]) = 40 KB per CTA
+static constexpr u64 KEY_LOCK_TOP = 0xA000000000000000ULL; // top word of a slot whose low word is being written
+__host__ __device__ inline size_t scatter_fine2_smem(u32 log_f) {
+  const size_t F = (size_t)1 << log_f;
+  return FINE_ROUND2 * sizeof(ulonglong2) + F * sizeof(u64) + 2 * F * sizeof(u32) + FINE_ROUND2 * sizeof(unsigned short);
+}
+__host__ __device__ inline size_t segment2_smem(u32 log_seg) { return (size_t)20 << log_seg; }
+
+template <int K, int HASH>
+__global__ void __launch_bounds__(TILE_THREADS, 4)
+k_scatter_fine2(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
+  static_assert(K > 32, "two-word keys");
+  extern __shared__ __align__(16) unsigned char fine_raw[];
+  __shared__ u32 cpre[N_BUCKETS + 1];
+  __shared__ u32 tmp[TILE_THREADS / 32 + 1];
+  constexpr int R = FINE_ROUND2 / TILE_THREADS;
+  const int t = threadIdx.x;
+  const u32 F = 1u << fs.log_f;
+  ulonglong2* sorted = reinterpret_cast<ulonglong2*>(fine_raw);
+  u64* dst = reinterpret_cast<u64*>(sorted + FINE_ROUND2);
+  u32* hist = reinterpret_cast<u32*>(dst + F);
+  u32* delta = hist + F;
+  unsigned short* sbid = reinterpret_cast<unsigned short*>(delta + F);
+  const u32 my_cnt = min(bs.cursor[t], bs.capb);
+  u32 n_chunks;
+  {
+    const u32 ex = block_excl_scan((my_cnt + FINE_ROUND2 - 1) / FINE_ROUND2, tmp, n_chunks);
+    cpre[t] = ex;
+    if (t == 0) cpre[N_BUCKETS] = n_chunks;
+  }
+  for (u32 f = t; f < F; f += TILE_THREADS) hist[f] = 0;
+  __syncthreads();
+  for (u32 c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+    int lo = 0, hi = N_BUCKETS - 1;                       // largest b with cpre[b] <= c
+#pragma unroll
+    for (int s = 0; s < LOG_BUCKETS; ++s) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (cpre[mid] <= c) lo = mid; else hi = mid - 1;
+    }
+    const u32 b = (u32)lo, first = (c - cpre[b]) * FINE_ROUND2;
+    const u32 m = min((u32)FINE_ROUND2, min(bs.cursor[b], bs.capb) - first);
+    const ulonglong2* src = reinterpret_cast<const ulonglong2*>(bs.keys) + (u64)b * bs.capb + first;
+    const u64 region0 = (u64)(b & bs.pre_mask) << fs.log_f;
+    ulonglong2 key[R];
+    u32 fid[R], rank[R];
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+      const u32 i = q * TILE_THREADS + t;
+      fid[q] = BKT_NONE;
+      if (i < m) {
+        key[q] = __ldg(src + i);
+        Key<2> kk; kk.w[0] = key[q].x; kk.w[1] = key[q].y;
+        const u64 h = slot_hash<K>(kk);
+        fid[q] = (u32)(h >> (64 - bs.log_pre - fs.log_f)) & (F - 1);
+        rank[q] = atomicAdd(&hist[fid[q]], 1u);
+      }
+    }
+    __syncthreads();
+    for (u32 f = t; f < F; f += TILE_THREADS) delta[f] = hist[f];          // counts
+    __syncthreads();
+    {                                                     // exclusive prefix of the counts into hist (F <= 2048: 8 per thread)
+      const u32 EPT = (F + TILE_THREADS - 1) / TILE_THREADS;
+      u32 local = 0;
+      for (u32 e = 0; e < EPT; ++e) { const u32 f = t * EPT + e; if (f < F) local += delta[f]; }
+      u32 total;
+      u32 ex = block_excl_scan_nb(local, tmp, total);
+      for (u32 e = 0; e < EPT; ++e) {
+        const u32 f = t * EPT + e;
+        if (f < F) {
+          const u32 cnt = delta[f];
+          hist[f] = ex;
+          u64 d = 1ULL << 63;
+          u32 gb = 0;
+          if (cnt) {
+            gb = atomicAdd(fs.cursor + region0 + f, cnt);
+            if ((u64)gb + cnt <= (u64)fs.capf)
+              d = reinterpret_cast<u64>(reinterpret_cast<ulonglong2*>(fs.keys) + (region0 + f) * fs.capf) + ((u64)gb - (u64)ex) * 16u;
+          }
+          dst[f] = d;
+          delta[f] = gb - ex;                              // slow path: position in the region = delta + r
+          ex += cnt;
+        }
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+      if (fid[q] != BKT_NONE) {
+        const u32 pos = hist[fid[q]] + rank[q];
+        sorted[pos] = key[q];
+        sbid[pos] = (unsigned short)fid[q];
+      }
+    }
+    __syncthreads();
+    for (u32 f = t; f < F; f += TILE_THREADS) hist[f] = 0;
+    for (u32 r = t; r < m; r += TILE_THREADS) {
+      const u32 f = sbid[r];
+      const u64 d = dst[f];
+      if (!(d >> 63)) { *reinterpret_cast<ulonglong2*>(d + (u64)r * 16u) = sorted[r]; continue; }
+      const u32 at = delta[f] + r;                          // the run crosses the region's capacity: key by key
+      if (at < fs.capf) { reinterpret_cast<ulonglong2*>(fs.keys)[(region0 + f) * fs.capf + at] = sorted[r]; continue; }
+      const u32 o = atomicAdd(bs.cursor + N_BUCKETS, 1u);   // the fine region is full: overflow region
+      if (o < bs.ovf_cap) reinterpret_cast<ulonglong2*>(bs.keys)[(u64)N_BUCKETS * bs.capb + o] = sorted[r];
+      else atomicOr(perr, PERR_OVERFLOW);
+    }
+    __syncthreads();
+  }
+}
+
+__device__ __forceinline__ u64 lds_volatile(const u64* p) { return *reinterpret_cast<const volatile u64*>(p); }
+
+template <int K, int HASH>
+__global__ void __launch_bounds__(384, 4)
+k_insert_segments2(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, const u32 n_segs, u32* __restrict__ perr,
+                   const u32 fresh) {
+  static_assert(K > 32, "two-word keys");
+  extern __shared__ __align__(16) unsigned char seg_raw[];
+  const u32 SEG = 1u << log_seg;
+  u64* shi = reinterpret_cast<u64*>(seg_raw);
+  u64* slo = shi + SEG;
+  u32* sval = reinterpret_cast<u32*>(slo + SEG);
+  const int tid = threadIdx.x;
+  u32 n_new = 0;
+  for (u32 s = blockIdx.x; s < n_segs; s += gridDim.x) {
+    const u32 cnt = min(fs.cursor[s], fs.capf);
+    if (cnt == 0 && !fresh) continue;
+    const ulonglong2* src = reinterpret_cast<const ulonglong2*>(fs.keys) + (u64)s * fs.capf;
+    for (u32 i = tid * 8u; i < cnt; i += 384u * 8u) prefetch_l2(src + i);       // the whole fine bucket -> L2
+    Slot<2>* gseg = reinterpret_cast<Slot<2>*>(t.slots) + ((u64)s << log_seg);
+    if (fresh) {
+      for (u32 i = tid; i < SEG; i += 384) { shi[i] = KEY_EMPTY_TOP; slo[i] = 0; sval[i] = 0; }
+    } else {
+      for (u32 i = tid; i < SEG; i += 384) {
+        const ulonglong2 k = *reinterpret_cast<const ulonglong2*>(&gseg[i]);
+        slo[i] = k.x; shi[i] = k.y; sval[i] = gseg[i].val;
+      }
+    }
+    __syncthreads();
+    ulonglong2 nk = (tid < (int)cnt) ? __ldg(src + tid) : make_ulonglong2(0, 0);
+    for (u32 i = tid; i < cnt; i += 384) {
+      const ulonglong2 key = nk;
+      if (i + 384 < cnt) nk = __ldg(src + i + 384);
+      Key<2> kk; kk.w[0] = key.x; kk.w[1] = key.y;
+      u32 li = (u32)(slot_hash<K>(kk) >> t.shift) & (SEG - 1);
+      for (;;) {
+        u64 h = lds_volatile(shi + li);
+        if (h == KEY_EMPTY_TOP) {
+          h = atomicCAS(shi + li, KEY_EMPTY_TOP, KEY_LOCK_TOP);
+          if (h == KEY_EMPTY_TOP) {                        // claimed: low word, then publish the top word
+            *reinterpret_cast<volatile u64*>(slo + li) = key.x;
+            __threadfence_block();
+            *reinterpret_cast<volatile u64*>(shi + li) = key.y;
+            atomicAdd(sval + li, 1u);
+            ++n_new;
+            break;
+          }
+        }
+        if (h == KEY_LOCK_TOP) continue;                   // being claimed: look again
+        if (h == key.y && lds_volatile(slo + li) == key.x) { atomicAdd(sval + li, 1u); break; }
+        if (++li == SEG) {                                 // ran off the segment: global linear probe continues there
+          const u32 o = atomicAdd(bs.cursor + N_BUCKETS, 1u);
+          if (o < bs.ovf_cap) reinterpret_cast<ulonglong2*>(bs.keys)[(u64)N_BUCKETS * bs.capb + o] = key;
+          else atomicOr(perr, PERR_SPILL);
+          break;
+        }
+      }
+    }
+    __syncthreads();
+    for (u32 i = tid; i < SEG; i += 384) {                 // aux is scratch (zeroed before the CSR fill), pad unused
+      uint4* g = reinterpret_cast<uint4*>(&gseg[i]);
+      const u64 l = slo[i], h = shi[i];
+      g[0] = make_uint4((u32)l, (u32)(l >> 32), (u32)h, (u32)(h >> 32));
+      g[1] = make_uint4(sval[i], 0u, 0u, 0u);
+    }
+    __syncthreads();
+  }
+  n_new = warp_sum(n_new);
+  if ((tid & 31) == 0 && n_new) atomicAdd(t.size, (u64)n_new);
+}
+
 // the overflow region (bucket overflow + segment spills) -> table with global atomics
 template <int K, int HASH>
 __global__ void __launch_bounds__(256) k_insert_overflow(TableView t, BucketSink bs) {

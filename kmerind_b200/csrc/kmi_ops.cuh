@@ -110,6 +110,10 @@ struct OpsImpl {
       // ~20 chunks per CTA: enough for the register prefetch to pay, short enough for the block scheduler to even out
       // the SMs (measured: 4.13 ms with one resident wave of CTAs, 3.50 with 32 waves, 4.09 with one chunk per CTA)
       k_scatter_fine<K, HASH><<<grid_for(n_hint ? n_hint : 1, FINE_ROUND, 148u * KMI_FINE_MINB * 32u), TILE_THREADS, smem, st>>>(bsink, fsink, perr);
+    } else {
+      const size_t smem = scatter_fine2_smem(fsink.log_f);
+      if (smem > 48 * 1024) cudaFuncSetAttribute(k_scatter_fine2<K, HASH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      k_scatter_fine2<K, HASH><<<grid_for(n_hint ? n_hint : 1, FINE_ROUND2, 148u * 4u * 32u), TILE_THREADS, smem, st>>>(bsink, fsink, perr);
     }
   }
   static int insert_segments(cudaStream_t st, TableView t, FineSink fsink, BucketSink bsink, u32 log_seg, u32 n_segs, u32* perr, bool fresh) {
@@ -121,6 +125,13 @@ struct OpsImpl {
       }
       const unsigned grid = n_segs;   // one CTA per segment: the block scheduler balances the SMs (4.60 ms vs 4.85 at 64 CTAs per SM)
       k_insert_segments<K, HASH><<<grid, SEG_THREADS, smem, st>>>(t, fsink, bsink, log_seg, n_segs, perr, fresh ? 1u : 0u);
+    } else {
+      const size_t smem = segment2_smem(log_seg);
+      if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(k_insert_segments2<K, HASH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+      }
+      k_insert_segments2<K, HASH><<<n_segs, 384, smem, st>>>(t, fsink, bsink, log_seg, n_segs, perr, fresh ? 1u : 0u);
     }
     return 0;
   }
