@@ -72,7 +72,7 @@ const char* kmi_last_error(void);
 int kmi_set_stream(kmi_index* idx, void* cuda_stream);
 /* Tuning knobs without a reference counterpart. KMI_PARAM_BUILD_PATH: how k-mers reach the table —
  * 0 auto (by input size), 1 direct atomics from the parser, 2 through the 256 hash-prefix buckets
- * (table segments stay L2-resident). KMI_PARAM_SEGMENT_INSERT (bucketed path, K <= 31): 1 (default) =
+ * (table segments stay L2-resident). KMI_PARAM_SEGMENT_INSERT (bucketed path): 1 (default) =
  * second-level scatter + table segments updated in shared memory, 0 = L2-resident global atomics.
  * Results are identical on every path. */
 typedef enum { KMI_PARAM_BUILD_PATH = 1, KMI_PARAM_SEGMENT_INSERT = 2 } kmi_param;

@@ -604,7 +604,7 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
 // low word stored, top word published; a prober that sees LOCK looks at the same slot again (the claiming lane
 // never waits in between, so this cannot dead-lock inside a warp).
 // ======================================================================================================
-static constexpr int FINE_ROUND2 = 1024;
+static constexpr int FINE_ROUND2 = 2048;
 static constexpr int LOG_SEG_SLOTS2 = 11;                 // 2048 slots x 20 B (hi[] + lo[] + val[]) = 40 KB per CTA
 static constexpr u64 KEY_LOCK_TOP = 0xA000000000000000ULL; // top word of a slot whose low word is being written
 __host__ __device__ inline size_t scatter_fine2_smem(u32 log_f) {
