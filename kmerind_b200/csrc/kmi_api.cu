@@ -83,6 +83,7 @@ struct kmi_index {
   u64 size_exact = 0;      // last size read back
   u64 size_upper = 0;      // upper bound on the current size (exact + keys issued since)
   // scratch
+  DevBuf parse_keys, parse_ids;   // staging of the parse -> insert builds (FASTA, FASTQ positions): kept between calls
   DevBuf tile_rec;   // FASTQ position ids: record start open at every tile (k_fastq_rec_carry)
   DevBuf tile_lines, block_sums, stage_in, stage_keys, stage_vals, stage_out, stage_found, hist, hist_sums;
   // POSITION mode: tuple log + CSR
@@ -272,7 +273,7 @@ extern "C" void kmi_destroy(kmi_index* idx) {
   if (idx->ctr) cudaFree(idx->ctr);
   DevBuf* bufs[] = {&idx->tile_lines, &idx->block_sums, &idx->stage_in, &idx->stage_keys, &idx->stage_vals,
                     &idx->stage_out, &idx->stage_found, &idx->hist, &idx->hist_sums, &idx->log_keys, &idx->log_ids,
-                    &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur};
+                    &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->xchg_bases};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 6; ++i) if (idx->ev[i]) cudaEventDestroy(idx->ev[i]);
   for (int i = 0; i < 4; ++i) if (idx->kev[i]) cudaEventDestroy(idx->kev[i]);
@@ -902,9 +903,9 @@ static int build_fastq_positions(kmi_index* idx, const uint8_t* d_bytes, size_t 
   OK(fastq_rec_carry(idx, d_bytes, n, n_tiles));
   OK(zero_ctr(idx, CTR_NKMERS));
   OK(zero_ctr(idx, CTR_PERR));
-  const u64 CHUNK_TILES = 16384;  // 64 MiB of text -> <= 32 Mi k-mers
+  const u64 CHUNK_TILES = 65536;  // 256 MiB of text -> <= 128 Mi k-mers per chunk (every chunk costs one sweep of the table)
   const u64 cap = std::min<u64>(n_tiles, CHUNK_TILES) * TILE_BYTES / 2 + 1;
-  DevBuf keys, ids;
+  DevBuf& keys = idx->parse_keys; DevBuf& ids = idx->parse_ids;
   int r = keys.ensure(cap * sizeof(u64) * idx->nw);
   if (r == KMI_OK) r = ids.ensure(cap * sizeof(u64));
   TableView none; none.slots = nullptr; none.mask = 0; none.shift = 63; none.size = nullptr; none.error = nullptr;
@@ -931,7 +932,6 @@ static int build_fastq_positions(kmi_index* idx, const uint8_t* d_bytes, size_t 
     cudaStreamSynchronize(idx->stream);
     total += produced;
   }
-  keys.release(); ids.release();
   if (r != KMI_OK) return r;
   if (perr) return parse_error(perr);
   if (n_kmers) *n_kmers = total;
@@ -1043,8 +1043,10 @@ extern "C" int kmi_insert_dev(kmi_index* idx, const uint64_t* d_keys_, const uin
   if (idx->cfg.mode == KMI_MODE_POSITION) {
     if (!d_vals) return fail(KMI_ERR_ARG, "POSITION insert needs ids");
     OK(log_append(idx, d_keys, d_vals, n));
-    // multiplicities go into the table now (keys in the log are already canonical)
-    OK(insert_keys_chunked(idx, idx->log_keys.as<u64>() + (idx->log_n - n) * idx->nw, n, false));
+    // multiplicities go into the table now (keys in the log are already canonical), large batches through the buckets
+    const u64* logged = idx->log_keys.as<u64>() + (idx->log_n - n) * idx->nw;
+    if (idx->build_path == 2 || (idx->build_path == 0 && n >= AUTO_BUCKET_KEYS)) OK(insert_keys_bucketed(idx, logged, n, false));
+    else OK(insert_keys_chunked(idx, logged, n, false));
     idx->csr_dirty = true;
   } else if (idx->build_path == 2 || (idx->build_path == 0 && n >= AUTO_BUCKET_KEYS)) {
     OK(insert_keys_bucketed(idx, d_keys, n, idx->cfg.canonical != 0));
@@ -1309,7 +1311,7 @@ extern "C" int kmi_table_info(kmi_index* idx, uint64_t* slots, uint64_t* slot_by
     u64 b = idx->cap * idx->slot_bytes;
     const DevBuf* bufs[] = {&idx->tile_lines, &idx->block_sums, &idx->stage_in, &idx->stage_keys, &idx->stage_vals,
                             &idx->stage_out, &idx->stage_found, &idx->hist, &idx->hist_sums, &idx->log_keys, &idx->log_ids,
-                            &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur};
+                            &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->xchg_bases};
     for (const DevBuf* d : bufs) b += d->cap;
     *device_bytes = b;
   }
@@ -1475,11 +1477,11 @@ extern "C" int kmi_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_
   CU(cudaEventRecord(idx->ev[1], idx->stream));
   if (n_tiles == 0) return KMI_OK;
   // bounded staging: at most CHUNK_TILES tiles of text become keys (+ids) at a time
-  const u64 CHUNK_TILES = 16384;  // 64 MiB of text -> <= 64 Mi k-mers
+  const u64 CHUNK_TILES = 65536;  // 256 MiB of text -> <= 256 Mi k-mers (4 GiB of key + id staging): every chunk costs one sweep of the table
   const bool pos = idx->cfg.mode == KMI_MODE_POSITION;
   size_t kb = sizeof(u64) * idx->nw;
   u64 cap = std::min<u64>(n_tiles, CHUNK_TILES) * TILE_BYTES;
-  DevBuf keys, ids;
+  DevBuf& keys = idx->parse_keys; DevBuf& ids = idx->parse_ids;
   int r = keys.ensure(cap * kb);
   if (r == KMI_OK && pos) r = ids.ensure(cap * sizeof(u64));
   u64 total = 0;
@@ -1509,7 +1511,6 @@ extern "C" int kmi_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_
     total += produced;
   }
   (void)insert_ms;
-  keys.release(); ids.release();
   if (r != KMI_OK) return r;
   cudaEventElapsedTime(&idx->stage_ms[0], idx->ev[0], idx->ev[1]);
   idx->stage_ms[1] = parse_ms;
