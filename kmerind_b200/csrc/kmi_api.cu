@@ -83,6 +83,7 @@ struct kmi_index {
   u64 size_exact = 0;      // last size read back
   u64 size_upper = 0;      // upper bound on the current size (exact + keys issued since)
   // scratch
+  DevBuf mid_keys, mid_cur;        // first of two fine passes (very large tables)
   DevBuf parse_keys, parse_ids;   // staging of the parse -> insert builds (FASTA, FASTQ positions): kept between calls
   DevBuf tile_rec;   // FASTQ position ids: record start open at every tile (k_fastq_rec_carry)
   DevBuf tile_lines, block_sums, stage_in, stage_keys, stage_vals, stage_out, stage_found, hist, hist_sums;
@@ -273,7 +274,7 @@ extern "C" void kmi_destroy(kmi_index* idx) {
   if (idx->ctr) cudaFree(idx->ctr);
   DevBuf* bufs[] = {&idx->tile_lines, &idx->block_sums, &idx->stage_in, &idx->stage_keys, &idx->stage_vals,
                     &idx->stage_out, &idx->stage_found, &idx->hist, &idx->hist_sums, &idx->log_keys, &idx->log_ids,
-                    &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->xchg_bases};
+                    &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->xchg_bases, &idx->mid_keys, &idx->mid_cur};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 6; ++i) if (idx->ev[i]) cudaEventDestroy(idx->ev[i]);
   for (int i = 0; i < 4; ++i) if (idx->kev[i]) cudaEventDestroy(idx->kev[i]);
@@ -407,7 +408,10 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
   const int log_pre = (int)bs.log_pre;
   const int log_seg_slots = idx->nw == 1 ? KMI_LOG_SEG_SLOTS : LOG_SEG_SLOTS2;
   int log_segs = std::max(std::max(LOG_BUCKETS, log_pre + (log_pre < LOG_BUCKETS ? 1 : 0)), log_cap - log_seg_slots);
-  log_segs = std::min(log_segs, log_pre + MAX_LOG_F);
+  // beyond 2^9 fine buckets per coarse bucket the scatter runs shrink to one or two keys: very large tables take TWO
+  // fine passes instead (2^(log_f - 8) mid buckets, then 256 fine buckets inside every group of 256 mid regions)
+  const bool two_pass = log_pre == LOG_BUCKETS && log_segs - log_pre >= 10 && log_segs - log_pre <= 16;
+  if (!two_pass) log_segs = std::min(log_segs, log_pre + MAX_LOG_F);
   const int log_seg = log_cap - log_segs;
   if (idx->seg_path && idx->ops->insert_segments && log_seg <= (idx->nw == 1 ? 13 : 12) && log_seg >= 8) {
     const u32 log_f = (u32)(log_segs - log_pre);
@@ -425,8 +429,34 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
       OK(idx->fine_cur.ensure(n_regions * sizeof(u32)));
       CU(cudaMemsetAsync(idx->fine_cur.p, 0, n_regions * sizeof(u32), idx->stream));
       fs.keys = idx->fine_keys.as<u64>(); fs.cursor = idx->fine_cur.as<u32>(); fs.capf = (u32)capf;
-      idx->ops->scatter_fine(idx->stream, bs, fs, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), n_keys);
-      idx->launches++;
+      if (!two_pass) {
+        idx->ops->scatter_fine(idx->stream, bs, fs, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), n_keys);
+        idx->launches++;
+      } else {
+        FineSink mid;
+        mid.log_f = log_f - LOG_BUCKETS;
+        const u64 n_mid = (u64)N_BUCKETS << mid.log_f;
+        const double mean1 = (double)n_keys / (double)n_mid;
+        const u64 capm = (u64)(mean1 + 8.0 * std::sqrt(mean1) + 32.0);
+        OK(idx->mid_keys.ensure(n_mid * capm * sizeof(u64) * idx->nw));
+        OK(idx->mid_cur.ensure(n_mid * sizeof(u32)));
+        CU(cudaMemsetAsync(idx->mid_cur.p, 0, n_mid * sizeof(u32), idx->stream));
+        mid.keys = idx->mid_keys.as<u64>(); mid.cursor = idx->mid_cur.as<u32>(); mid.capf = (u32)capm;
+        idx->ops->scatter_fine(idx->stream, bs, mid, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), n_keys);
+        idx->launches++;
+        fs.log_f = LOG_BUCKETS;                            // per group of 256 mid regions
+        for (u64 g = 0; g < n_mid / N_BUCKETS; ++g) {
+          BucketSink bg;
+          bg.keys = mid.keys + g * N_BUCKETS * capm * idx->nw;
+          bg.cursor = mid.cursor + g * N_BUCKETS;
+          bg.capb = (u32)capm; bg.ovf_cap = bs.ovf_cap; bg.hll = nullptr; bg.bases = nullptr;
+          bg.log_pre = (u32)LOG_BUCKETS + mid.log_f; bg.pre_mask = N_BUCKETS - 1; bg.pre_base = (u32)(g * N_BUCKETS);
+          bg.ovf_keys = bs.keys + (u64)N_BUCKETS * bs.capb * idx->nw; bg.ovf_cursor = bs.cursor + N_BUCKETS;
+          idx->ops->scatter_fine(idx->stream, bg, fs, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), n_keys / (n_mid / N_BUCKETS) + 1);
+          idx->launches++;
+        }
+        fs.log_f = log_f;                                  // the insert sees 2^log_segs regions, as after a single pass
+      }
       u64 perr = 0;
       OK(read_ctr(idx, CTR_PERR, &perr));
       if (perr & PERR_OVERFLOW) {
@@ -1311,7 +1341,7 @@ extern "C" int kmi_table_info(kmi_index* idx, uint64_t* slots, uint64_t* slot_by
     u64 b = idx->cap * idx->slot_bytes;
     const DevBuf* bufs[] = {&idx->tile_lines, &idx->block_sums, &idx->stage_in, &idx->stage_keys, &idx->stage_vals,
                             &idx->stage_out, &idx->stage_found, &idx->hist, &idx->hist_sums, &idx->log_keys, &idx->log_ids,
-                            &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->xchg_bases};
+                            &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->xchg_bases, &idx->mid_keys, &idx->mid_cur};
     for (const DevBuf* d : bufs) b += d->cap;
     *device_bytes = b;
   }

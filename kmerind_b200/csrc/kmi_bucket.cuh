@@ -38,7 +38,17 @@ struct BucketSink {
   // region = source rank * CB + prefix with CB = N_BUCKETS / nranks sub-bins, log_pre = log2(CB), pre_mask = CB - 1.
   u32 log_pre = LOG_BUCKETS;
   u32 pre_mask = N_BUCKETS - 1;
+  // A sink that views 256 consecutive regions of a LARGER set (third scatter level of very large tables: the output
+  // regions of a first fine pass, taken 256 at a time): prefix of region r = pre_base + (r & pre_mask); the overflow
+  // region then is not "behind region 255" but wherever the owner of the whole set keeps it.
+  u32 pre_base = 0;
+  u64* ovf_keys = nullptr;        // null: keys + N_BUCKETS * capb (* words per key)
+  u32* ovf_cursor = nullptr;      // null: cursor + N_BUCKETS
 };
+template <int NW> __device__ __forceinline__ u64* ovf_base(const BucketSink& bs) {
+  return bs.ovf_keys ? bs.ovf_keys : bs.keys + (u64)N_BUCKETS * bs.capb * NW;
+}
+__device__ __forceinline__ u32* ovf_cur(const BucketSink& bs) { return bs.ovf_cursor ? bs.ovf_cursor : bs.cursor + N_BUCKETS; }
 
 template <int NW> struct BucketSmem;
 template <> struct BucketSmem<0> { u32 unused; };   // kernels instantiated without the bucket sink
@@ -284,7 +294,10 @@ __global__ void __launch_bounds__(256) k_insert_buckets(TableView t, BucketSink 
 // shared memory; one CTA then loads the segment, applies its fine bucket with shared-memory atomics,
 // and writes the segment back with coalesced 128-bit stores: the table crosses HBM once per sweep.
 // ======================================================================================================
-static constexpr int MAX_LOG_F = 11;
+#ifndef KMI_MAX_LOG_F
+#define KMI_MAX_LOG_F 11
+#endif
+static constexpr int MAX_LOG_F = KMI_MAX_LOG_F;
 static constexpr int FINE_ROUND = 2048;                   // keys per CTA round of the second scatter
 static constexpr u32 PERR_SPILL = 16u;                    // overflow region exhausted by segment spills (fatal)
 
@@ -376,7 +389,7 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
       }
     }
     __syncthreads();
-    const u64 region0 = (u64)(b & bs.pre_mask) << fs.log_f;   // first fine region (= table segment) of this hash prefix
+    const u64 region0 = (u64)(bs.pre_base + (b & bs.pre_mask)) << fs.log_f;   // first fine region (= table segment) of this hash prefix
     u32 gb1 = 0, ex1 = 0, cnt1 = 0;                       // EPT == 1: the cursor atomic stays in flight during the sort
     {
       u32 local = 0;
@@ -426,8 +439,8 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
       if (at < fs.capf) {
         fs.keys[(region0 + f) * fs.capf + at] = sorted[r];
       } else {
-        const u32 o = atomicAdd(bs.cursor + N_BUCKETS, 1u);
-        if (o < bs.ovf_cap) bs.keys[(u64)N_BUCKETS * bs.capb + o] = sorted[r];
+        const u32 o = atomicAdd(ovf_cur(bs), 1u);
+        if (o < bs.ovf_cap) ovf_base<1>(bs)[o] = sorted[r];
         else atomicOr(perr, PERR_OVERFLOW);
       }
     }
@@ -647,7 +660,7 @@ k_scatter_fine2(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
     const u32 b = (u32)lo, first = (c - cpre[b]) * FINE_ROUND2;
     const u32 m = min((u32)FINE_ROUND2, min(bs.cursor[b], bs.capb) - first);
     const ulonglong2* src = reinterpret_cast<const ulonglong2*>(bs.keys) + (u64)b * bs.capb + first;
-    const u64 region0 = (u64)(b & bs.pre_mask) << fs.log_f;
+    const u64 region0 = (u64)(bs.pre_base + (b & bs.pre_mask)) << fs.log_f;
     ulonglong2 key[R];
     u32 fid[R], rank[R];
 #pragma unroll
@@ -706,8 +719,8 @@ k_scatter_fine2(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
       if (!(d >> 63)) { *reinterpret_cast<ulonglong2*>(d + (u64)r * 16u) = sorted[r]; continue; }
       const u32 at = delta[f] + r;                          // the run crosses the region's capacity: key by key
       if (at < fs.capf) { reinterpret_cast<ulonglong2*>(fs.keys)[(region0 + f) * fs.capf + at] = sorted[r]; continue; }
-      const u32 o = atomicAdd(bs.cursor + N_BUCKETS, 1u);   // the fine region is full: overflow region
-      if (o < bs.ovf_cap) reinterpret_cast<ulonglong2*>(bs.keys)[(u64)N_BUCKETS * bs.capb + o] = sorted[r];
+      const u32 o = atomicAdd(ovf_cur(bs), 1u);             // the fine region is full: overflow region
+      if (o < bs.ovf_cap) reinterpret_cast<ulonglong2*>(ovf_base<2>(bs))[o] = sorted[r];
       else atomicOr(perr, PERR_OVERFLOW);
     }
     __syncthreads();

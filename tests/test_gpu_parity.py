@@ -410,6 +410,27 @@ def test_k63_count_index_on_synthetic(path):
             assert np.array_equal(gk, wk) and np.array_equal(gc, wc)
 
 
+def test_two_fine_passes_on_a_very_large_table():
+    """A table of 2^30 slots has 2^18 shared-memory segments = 1024 fine buckets per coarse bucket: the fine scatter
+    then runs as two passes (4 mid buckets, then 256 fine buckets per group of 256 mid regions). Same contents."""
+    free, _ = torch.cuda.mem_get_info()
+    if free < 24 << 30:
+        pytest.skip("needs 24 GB of free device memory")
+    buf = ou.synth_fastq(0, 30000, 150, 200000, 5, 5000, 0)
+    keys, _, _ = ou.fastq_kmers(buf, 31)
+    wk, wc = ou.count_sorted(keys, 31)
+    with kb.CountIndex(31, hash=kb.HASH_FARM, reserve=700_000_000) as idx:
+        idx.set_build_path(2)
+        assert idx.table_info()["slots"] == 1 << 30
+        assert idx.build_fastq(buf) == len(keys)
+        assert idx.build_fastq(buf) == len(keys)           # second build: segments are loaded, not initialised
+        assert idx.local_size() == len(wk)
+        assert idx.checksum()[1] == 2 * len(keys)
+        q = wk[:: max(1, len(wk) // 5000)]
+        vals, found = idx.find(q)
+        assert found.all() and np.array_equal(vals, 2 * wc[:: max(1, len(wk) // 5000)].astype(np.uint64))
+
+
 @pytest.mark.parametrize("frac", (0.1, 0.97))
 def test_bucketed_build_survives_key_skew(frac):
     """A heavy-hitter key (poly-A reads) overflows its hash-prefix bucket: at 10 % the spill goes to the
