@@ -410,6 +410,36 @@ def test_k63_count_index_on_synthetic(path):
             assert np.array_equal(gk, wk) and np.array_equal(gc, wc)
 
 
+def test_lazy_clear_is_invisible():
+    """kmi_clear does not write the table (the next bucketed build initialises it in shared memory); every other access
+    must still see an empty table."""
+    buf = ou.synth_fastq(0, 20000, 150, 100000, 9, 5000, 0)
+    keys, _, _ = ou.fastq_kmers(buf, 31)
+    wk, wc = ou.count_sorted(keys, 31)
+    q = wk[:2000]
+    with kb.CountIndex(31) as idx:
+        idx.set_build_path(2)
+        assert idx.build_fastq(buf) == len(keys)
+        idx.clear()
+        assert idx.local_size() == 0
+        vals, found = idx.find(q)                       # lookup on the lazily cleared table
+        assert not found.any() and not vals.any()
+        assert idx.count(q).tolist() == [0] * len(q)
+        k0, c0 = idx.sorted_dump()
+        assert len(k0) == 0 and idx.checksum() == (0, 0)
+        idx.insert(q[:100])                             # direct insert after the reads above
+        assert idx.local_size() == 100 and idx.find(q[:100])[1].all()
+        idx.clear()
+        idx.erase(q[:10])                               # erase on an empty (virgin) table
+        idx.insert(q[:50])                              # small insert straight after a clear
+        assert idx.local_size() == 50
+        idx.clear()
+        idx.reserve(4 * len(wk))                        # growth of a virgin table: nothing to rehash
+        assert idx.build_fastq(buf) == len(keys)
+        gk, gc = idx.sorted_dump()
+        assert np.array_equal(gk, wk) and np.array_equal(gc, wc)
+
+
 def test_two_fine_passes_on_a_very_large_table():
     """A table of 2^30 slots has 2^18 shared-memory segments = 1024 fine buckets per coarse bucket: the fine scatter
     then runs as two passes (4 mid buckets, then 256 fine buckets per group of 256 mid regions). Same contents."""
