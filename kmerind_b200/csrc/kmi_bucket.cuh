@@ -298,7 +298,10 @@ __global__ void __launch_bounds__(256) k_insert_buckets(TableView t, BucketSink 
 #define KMI_MAX_LOG_F 11
 #endif
 static constexpr int MAX_LOG_F = KMI_MAX_LOG_F;
-static constexpr int FINE_ROUND = 2048;                   // keys per CTA round of the second scatter
+#ifndef KMI_FINE_ROUND
+#define KMI_FINE_ROUND 2048
+#endif
+static constexpr int FINE_ROUND = KMI_FINE_ROUND;         // keys per CTA round of the second scatter
 static constexpr u32 PERR_SPILL = 16u;                    // overflow region exhausted by segment spills (fatal)
 
 struct FineSink {
