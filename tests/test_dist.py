@@ -77,7 +77,7 @@ def test_exchange_gloo_world2(tmp_path):
         assert np.array_equal(got2, keys[1][owner[1] == dst])
 
 
-def _nccl_worker(rank, world, port, out_dir, peer=False):
+def _nccl_worker(rank, world, port, out_dir, peer=False, k=31):
     if peer == "prefix":          # sub-bin layout of the receive buffer (kmi_exchange_bins > 1)
         os.environ["KMI_EXCHANGE_PREFIX"] = "1"
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -90,13 +90,16 @@ def _nccl_worker(rank, world, port, out_dir, peer=False):
         n_reads = 30000
         buf = ou.synth_fastq(rank * n_reads, n_reads, 150, 400000, 11, 5000, 0)
         text = torch.from_numpy(np.concatenate([buf, np.zeros(64, np.uint8)])).cuda()
-        idx = ShardedIndex(31, hash=kb.HASH_FARM, device=rank)
+        idx = ShardedIndex(k, hash=kb.HASH_FARM, device=rank)
         if peer:
             idx.local.set_build_path(2)   # received keys take the bucketed insert even at this size
             assert idx.enable_peer_exchange(n_reads * 120), "CUDA IPC peer mapping failed"
-            assert idx.local.exchange_bins() == (128 if peer == "prefix" else 1)
+            if k > 32:
+                assert idx.local.exchange_bins() == 1
+            if k <= 32:
+                assert idx.local.exchange_bins() == (128 if peer == "prefix" else 1)
         n = idx.build_fastq_dev(text, buf.size)
-        assert n == n_reads * 120
+        assert n == n_reads * (150 - k + 1)
         if peer:
             assert "parse+scatter+exchange" in idx.stage_ms
             assert idx.build_fastq_dev(text, buf.size) == n   # a second round through the same buffers
@@ -105,13 +108,16 @@ def _nccl_worker(rank, world, port, out_dir, peer=False):
             rec = buf.size // n_reads
             assert idx.build_fastq_host(host, [0, 10000 * rec, 20000 * rec, buf.size]) == n
 
-        k, c = idx.local.sorted_dump()
-        np.save(os.path.join(out_dir, "k%d.npy" % rank), k)
-        np.save(os.path.join(out_dir, "c%d.npy" % rank), c)
+        dk, dc = idx.local.sorted_dump()
+        np.save(os.path.join(out_dir, "k%d.npy" % rank), dk)
+        np.save(os.path.join(out_dir, "c%d.npy" % rank), dc)
         total = idx.size()
         # batched query through the exchange: every rank asks for its own first 1000 k-mers + 1000 absent keys
-        keys, _, _ = ou.fastq_kmers(buf, 31)
-        q = np.concatenate([keys[:1000], np.arange(1000, dtype=np.uint64) * np.uint64(7919) + np.uint64(1 << 40)])
+        keys, _, _ = ou.fastq_kmers(buf, k)
+        absent = np.arange(1000, dtype=np.uint64) * np.uint64(7919) + np.uint64(1 << 40)
+        if k > 32:
+            absent = np.stack([absent, absent >> np.uint64(3)], axis=1)
+        q = np.concatenate([keys[:1000], absent])
         vals, found = idx.find(q)
         np.save(os.path.join(out_dir, "q%d.npy" % rank), q)
         np.save(os.path.join(out_dir, "v%d.npy" % rank), vals)
@@ -123,21 +129,24 @@ def _nccl_worker(rank, world, port, out_dir, peer=False):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("peer", (False, True, "prefix"))
-def test_sharded_count_index_nccl_world2(tmp_path, peer):
+@pytest.mark.parametrize("peer,K", ((False, 31), (True, 31), ("prefix", 31), (True, 63)))
+def test_sharded_count_index_nccl_world2(tmp_path, peer, K):
     """peer=False: keys travel by NCCL all-to-all; peer=True: the parse kernel stores them straight into
-    the owners' HBM over NVLink (kmi_exchange_*), and the build is run three times, the last one from pinned host memory in chunks (counts triple)."""
+    the owners' HBM over NVLink (kmi_exchange_*), and the build is run three times, the last one from pinned host memory in
+    chunks (counts triple); K=63: two-word keys through the same exchange and the two-word segment insert."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     world = 2
-    mp.spawn(_nccl_worker, args=(world, _free_port(), str(tmp_path), peer), nprocs=world, join=True)
+    mp.spawn(_nccl_worker, args=(world, _free_port(), str(tmp_path), peer, K), nprocs=world, join=True)
     n_reads = 30000
+    nw = ou.nwords(K)
     bufs = [ou.synth_fastq(r * n_reads, n_reads, 150, 400000, 11, 5000, 0) for r in range(world)]
-    keys = np.concatenate([ou.fastq_kmers(b, 31)[0] for b in bufs])
-    wk, wc = ou.count_sorted(keys, 31)
+    keys = np.concatenate([ou.fastq_kmers(b, K)[0] for b in bufs])
+    wk, wc = ou.count_sorted(keys, K)
     if peer:
         wc = 3 * wc
-    owner = (ou.hashes(wk, 31, 3) % np.uint64(world)).astype(np.int64)
+    owner = (ou.hashes(wk, K, 3) % np.uint64(world)).astype(np.int64)
+    rows = (lambda a: [tuple(np.atleast_1d(r).tolist()) for r in a])
     for r in range(world):
         k = np.load(tmp_path / ("k%d.npy" % r))
         c = np.load(tmp_path / ("c%d.npy" % r))
@@ -146,9 +155,8 @@ def test_sharded_count_index_nccl_world2(tmp_path, peer):
         q = np.load(tmp_path / ("q%d.npy" % r))
         v = np.load(tmp_path / ("v%d.npy" % r))
         f = np.load(tmp_path / ("f%d.npy" % r))
-        cq = ou.canonical(q, 31)
-        pos = np.searchsorted(wk, cq)
-        pos[pos >= len(wk)] = 0
-        hit = wk[pos] == cq
-        assert np.array_equal(f.astype(bool), hit)
-        assert np.array_equal(v[hit], wc[pos[hit]])
+        cq = ou.shape_keys(np.ascontiguousarray(ou.canonical(q, K)).reshape(-1), K)
+        want = dict(zip(rows(wk), wc.tolist()))
+        got_hit = [kk in want for kk in rows(cq)]
+        assert f.astype(bool).tolist() == got_hit
+        assert [int(x) for x, h in zip(v, got_hit) if h] == [want[kk] for kk in rows(cq) if kk in want]
