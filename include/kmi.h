@@ -95,6 +95,16 @@ int kmi_build_fasta(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t* n_
 int kmi_build_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers);
 int kmi_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* n_kmers);
 
+/* ---- a2: record-aligned blocks (FASTQParser::find_first_record, fastq_loader.hpp:269-357,696-873) ---------------
+ * Host side, as in the reference (it looks at four lines). `bytes` holds file bytes [mem_offset, mem_offset + n); the
+ * search starts at search_begin (dropping a partial first line unless search_begin == parent_begin) and matches the first
+ * characters of four consecutive non-empty lines against @?+? / ?@?+ / +?@? / ?+?@. *offset = file offset of the '@' of
+ * the first whole record, or the end of the search range when it holds no complete record. KMI_ERR_FORMAT when no marker
+ * pattern is found in a range that is not the parent's tail (the reference throws IOException). Use it to cut a file
+ * into the blocks kmi_build_fastq / kmi_parse_fastq_dev take: block r = [first_record(cut r), first_record(cut r+1)). */
+int kmi_fastq_find_first_record(const uint8_t* bytes, uint64_t mem_offset, size_t n, uint64_t search_begin,
+                                uint64_t search_end, uint64_t parent_begin, uint64_t parent_end, uint64_t* offset);
+
 /* ---- stages, device resident ------------------------------------- */
 /* a2-a10: record boundaries + 2-bit encode + sliding window (+ lex_less if cfg.canonical).
  * Writes up to `cap` keys (nw words each) and, if d_ids != NULL, their position ids

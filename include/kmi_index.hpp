@@ -22,6 +22,7 @@
 #ifndef KMI_INDEX_HPP_
 #define KMI_INDEX_HPP_
 
+#include <algorithm>
 #include <cstdint>
 #include <cstring>
 #include <fstream>
@@ -33,6 +34,21 @@
 #include "kmi.h"
 
 namespace kmi {
+
+/// Record-aligned block boundaries {0, c1, ..., n} of a FASTQ file held in memory, for `parts` ranks / GPUs: equal byte
+/// ranges, each moved forward to its first whole record — what partitioned_file<...,FASTQParser>::read_file does with
+/// BlockPartitioner + FASTQParser::find_first_record (reference src/io/file.hpp:1342-1431, fastq_loader.hpp:269-357).
+inline std::vector<size_t> fastq_cuts(const uint8_t* bytes, size_t n, int parts) {
+  std::vector<size_t> cuts(1, 0);
+  for (int r = 1; r < parts; ++r) {
+    uint64_t at = 0;
+    if (kmi_fastq_find_first_record(bytes, 0, n, (uint64_t)n * r / parts, n, 0, n, &at) != KMI_OK)
+      throw std::logic_error(kmi_last_error());
+    cuts.push_back(std::max<size_t>(cuts.back(), (size_t)at));
+  }
+  cuts.push_back(n);
+  return cuts;
+}
 
 /// bliss::common::Kmer<K, DNA, uint64_t> look-alike: same size, same word order.
 template <unsigned K_>

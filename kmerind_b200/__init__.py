@@ -73,6 +73,7 @@ def load_library(build_if_missing=False):
         "kmi_exchange_setup": [_P, _SZ, _P], "kmi_exchange_connect": [_P, _P],
         "kmi_exchange_parse_fastq_dev": [_P, _P, _SZ, _P, _P], "kmi_exchange_insert": [_P, _P],
         "kmi_exchange_bins": [_P, _P],
+        "kmi_fastq_find_first_record": [_P, _U64, _SZ, _U64, _U64, _U64, _U64, _P],
         "kmi_canonicalize_dev": [_P, _P, _P, _SZ], "kmi_hash_dev": [_P, ctypes.c_int, _P, _P, _SZ],
         "kmi_partition_dev": [_P, _P, _P, _SZ, _P, _P, _P],
         "kmi_insert": [_P, _P, _P, _SZ], "kmi_insert_dev": [_P, _P, _P, _SZ],
@@ -97,7 +98,7 @@ EXPORTED_SYMBOLS = (
     "kmi_create", "kmi_destroy", "kmi_last_error", "kmi_set_stream", "kmi_set_param", "kmi_reserve", "kmi_clear",
     "kmi_build_fastq", "kmi_build_fasta", "kmi_build_fastq_dev", "kmi_build_fasta_dev",
     "kmi_parse_fastq_dev", "kmi_parse_fasta_dev", "kmi_parse_fastq_by_owner_dev", "kmi_exchange_setup", "kmi_exchange_connect",
-    "kmi_exchange_parse_fastq_dev", "kmi_exchange_insert", "kmi_exchange_bins", "kmi_canonicalize_dev", "kmi_hash_dev",
+    "kmi_exchange_parse_fastq_dev", "kmi_exchange_insert", "kmi_exchange_bins", "kmi_fastq_find_first_record", "kmi_canonicalize_dev", "kmi_hash_dev",
     "kmi_partition_dev", "kmi_insert", "kmi_insert_dev", "kmi_count", "kmi_find", "kmi_find_positions",
     "kmi_erase", "kmi_count_dev", "kmi_find_dev", "kmi_local_size", "kmi_num_keys", "kmi_dump",
     "kmi_checksum", "kmi_table_info", "kmi_launch_count", "kmi_last_stage_ms", "kmi_last_kernel_ms",
@@ -128,6 +129,29 @@ def _as_keys(keys, nw):
     else:
         a = a.reshape(-1)
     return a
+
+
+def fastq_find_first_record(buf, search_begin, search_end=None, mem_offset=0, parent=None):
+    """FASTQParser::find_first_record on host bytes (kmi_fastq_find_first_record): file offset of the first whole record
+    at or after search_begin; buf holds file bytes [mem_offset, mem_offset + len(buf))."""
+    buf = np.ascontiguousarray(buf, dtype=np.uint8)
+    end = mem_offset + buf.size
+    search_end = end if search_end is None else search_end
+    pb, pe = parent if parent is not None else (mem_offset, end)
+    out = _U64(0)
+    _check(load_library().kmi_fastq_find_first_record(_hptr(buf), mem_offset, buf.size, search_begin, search_end, pb, pe, ctypes.byref(out)))
+    return out.value
+
+
+def fastq_cuts(buf, parts):
+    """Record-aligned block boundaries [0, c1, ..., len(buf)] for `parts` ranks, as partitioned_file::read_file cuts a file
+    (equal byte ranges, each moved forward to its first whole record: file.hpp:1342-1431)."""
+    n = int(np.asarray(buf).size)
+    cuts = [0]
+    for r in range(1, parts):
+        cuts.append(max(cuts[-1], fastq_find_first_record(buf, n * r // parts)))
+    cuts.append(n)
+    return cuts
 
 
 class Index:

@@ -530,6 +530,43 @@ static int insert_keys_bucketed(kmi_index* idx, const u64* d_keys, size_t n, boo
   return KMI_OK;
 }
 
+// ---- a2: where the first whole record of a byte range starts (host side, as in the reference: four lines) -------
+// FASTQParser::find_first_record, src/io/fastq_loader.hpp:269-357 / :696-873. `bytes` holds file bytes
+// [mem_offset, mem_offset + n); the first characters of four consecutive non-empty lines at or after search_begin
+// are matched against @?+? / ?@?+ / +?@? / ?+?@. This is what cuts a file into the record-aligned blocks that
+// kmi_build_fastq / kmi_parse_fastq_dev take (one block per GPU, or per pipelined chunk).
+static inline bool host_is_eol(uint8_t c) { return c == '\n' || c == '\r'; }
+extern "C" int kmi_fastq_find_first_record(const uint8_t* bytes, uint64_t mem_offset, size_t n, uint64_t search_begin,
+                                           uint64_t search_end, uint64_t parent_begin, uint64_t parent_end, uint64_t* offset) {
+  if ((!bytes && n) || !offset) return fail(KMI_ERR_ARG, "null argument");
+  if (parent_begin > mem_offset || parent_end < mem_offset + n) return fail(KMI_ERR_ARG, "parent range does not contain the bytes in memory");
+  const uint64_t ts = std::max(search_begin, mem_offset);
+  const uint64_t te = std::max(ts, std::min<uint64_t>(search_end, mem_offset + n));
+  auto at = [&](uint64_t i) { return bytes[i - mem_offset]; };
+  uint64_t i = ts;
+  *offset = te;
+  if (i == te) return KMI_OK;
+  if (ts > parent_begin && !host_is_eol(at(i))) while (i < te && !host_is_eol(at(i))) ++i;   // not a line start: drop the partial line
+  while (i < te && host_is_eol(at(i))) ++i;
+  if (i == te) return KMI_OK;
+  uint8_t first[4] = {at(i), 0, 0, 0};
+  uint64_t off[4] = {i, te, te, te};
+  for (int j = 1; j < 4; ++j) {
+    while (i < te && !host_is_eol(at(i))) ++i;
+    while (i < te && host_is_eol(at(i))) ++i;
+    off[j] = i;
+    if (i != te) first[j] = at(i);
+  }
+  if (i == te) return KMI_OK;                             // fewer than four lines: no complete record in range
+  if (first[0] == '@' && first[2] == '+') { *offset = off[0]; return KMI_OK; }
+  if (first[1] == '@' && first[3] == '+') { *offset = off[1]; return KMI_OK; }
+  if (first[0] == '+' && first[2] == '@') { *offset = off[2]; return KMI_OK; }
+  if (first[1] == '+' && first[3] == '@') { *offset = off[3]; return KMI_OK; }
+  if (te == parent_end) return KMI_OK;
+  return fail(KMI_ERR_FORMAT, "bytes [%llu, %llu) do not contain valid FASTQ markers (first chars %c %c %c %c)",
+              (unsigned long long)ts, (unsigned long long)te, first[0], first[1], first[2], first[3]);
+}
+
 // ---- record boundaries (pass A + scan), shared by parse and fused build ------------------------
 static int fastq_scan_alloc(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64* n_tiles_out) {
   if ((reinterpret_cast<uintptr_t>(d_bytes) & 15) != 0) return fail(KMI_ERR_ARG, "device text buffer must be 16-byte aligned");

@@ -399,6 +399,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   const u64 off = tile_off + (u64)t * GROUP_BYTES;
 
   // -- P1: load + classify own group (and, for the first HALO_GROUPS threads, a halo group)
+  const u32 tile_first_a = __ldg(tile_lines + tile), tile_first_b = __ldg(block_sums + (tile >> 10));   // needed in P3: in flight with the text
   uint4 v = load_group(bytes, off, n);
   Group g;                                            // FASTQ needs no separate '\n' mask, and the N mask only when splitting
   g.codes = codes16(v); g.eol = eol16(v); g.nl = 0; g.nmask = NSPLIT ? nmask16(v) : 0u;
@@ -428,7 +429,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   // -- P2: line number at the start of every group
   u32 total_ls;
   u32 before = block_excl_scan_nb(__popc(ls), s_tmp, total_ls);
-  const u32 tile_first = tile_lines[tile] + block_sums[tile >> 10];
+  const u32 tile_first = tile_first_a + tile_first_b;
   // (the scan contains a barrier after the writes above: s_aux is visible)
 
   // -- P3: per-byte "base of a sequence line" flags; header checks at line starts

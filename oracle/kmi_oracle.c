@@ -262,6 +262,41 @@ long kmio_fastq_kmers(const uint8_t* buf, size_t n, uint64_t file_offset, int K,
   return (long)total;
 }
 
+/* ---- a2: FASTQParser::find_first_record (serial), src/io/fastq_loader.hpp:269-357: first record start inside the
+ * search range [s, e) of a file whose bytes [mem, mem + n) are in buf; parent = [ps, pe) is the enclosing
+ * record-aligned range. Walks to the first line start, takes the first characters of four consecutive non-empty
+ * lines and votes @?+? / ?@?+ / +?@? / ?+?@ (:337-340). Returns 0 and the offset (e when the range holds no complete
+ * record and ends with the parent), -1 when no marker pattern is found inside a range that is not the parent's tail
+ * (the reference throws IOException there, :342-357). */
+int kmio_fastq_find_first_record(const uint8_t* buf, uint64_t mem, size_t n, uint64_t s, uint64_t e, uint64_t ps,
+                                 uint64_t pe, uint64_t* out) {
+  uint64_t ts = s > mem ? s : mem, te = e < mem + n ? e : mem + n;
+  uint64_t i = ts;
+  uint8_t first[4] = {0, 0, 0, 0};
+  uint64_t off[4];
+  if (te < ts) te = ts;
+  off[0] = off[1] = off[2] = off[3] = te;
+  if (i == te) { *out = te; return 0; }
+  if (ts > ps && !is_eol(buf[i - mem])) { while (i < te && !is_eol(buf[i - mem])) ++i; }   /* findEOL */
+  if (i == te) { *out = te; return 0; }
+  while (i < te && is_eol(buf[i - mem])) ++i;                                              /* findNonEOL */
+  if (i == te) { *out = te; return 0; }
+  first[0] = buf[i - mem]; off[0] = i;
+  for (int j = 1; j < 4; ++j) {
+    while (i < te && !is_eol(buf[i - mem])) ++i;
+    while (i < te && is_eol(buf[i - mem])) ++i;
+    off[j] = i;
+    if (i != te) first[j] = buf[i - mem];
+  }
+  if (i == te) { *out = te; return 0; }
+  if (first[0] == '@' && first[2] == '+') { *out = off[0]; return 0; }
+  if (first[1] == '@' && first[3] == '+') { *out = off[1]; return 0; }
+  if (first[0] == '+' && first[2] == '@') { *out = off[2]; return 0; }
+  if (first[1] == '+' && first[3] == '@') { *out = off[3]; return 0; }
+  if (te == pe) { *out = te; return 0; }
+  return -1;
+}
+
 /* ---- a4: FASTAParser::init_parser (serial), src/io/fasta_loader.hpp:485-616, and
  * get_next_record :618-723 at p = 1. Line starts follow '\n' only; a line is a header iff it
  * starts with '>' or ';'; runs of same-kind lines are merged; a sequence is everything from the

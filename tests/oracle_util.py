@@ -34,6 +34,7 @@ def oracle():
         lib.kmio_canonical.argtypes = [ctypes.c_int, _P, _P, _SZ]
         lib.kmio_hash.argtypes = [ctypes.c_int, ctypes.c_int, _P, _P, _SZ]
         lib.kmio_owner.argtypes = [_P, _SZ, ctypes.c_uint32, _P]
+        lib.kmio_fastq_find_first_record.argtypes = [_P, _U64, _SZ, _U64, _U64, _U64, _U64, _P]
         lib.kmio_count_sorted.restype = _SZ
         lib.kmio_count_sorted.argtypes = [ctypes.c_int, _P, _SZ, _P]
         lib.kmio_sort_tuples.argtypes = [ctypes.c_int, _P, _P, _SZ]
@@ -85,6 +86,17 @@ def fastq_kmers(buf, k, canonical=True, nsplit=False, want_ids=False, file_offse
     if m < 0:
         raise ValueError("oracle: malformed FASTQ (%d)" % m)
     return shape_keys(keys[:m * nw].copy(), k), (ids[:m].copy() if want_ids else None), reads.value
+
+
+def fastq_find_first_record(buf, s, e=None, mem=0, parent=None):
+    n = int(buf.size)
+    e = mem + n if e is None else e
+    pb, pe = parent if parent is not None else (mem, mem + n)
+    out = _U64(0)
+    rc = oracle().kmio_fastq_find_first_record(_ptr(buf), mem, n, s, e, pb, pe, ctypes.byref(out))
+    if rc != 0:
+        raise ValueError("oracle: no FASTQ markers in range")
+    return out.value
 
 
 def fasta_kmers(buf, k, canonical=True, nsplit=False):

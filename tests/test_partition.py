@@ -1,0 +1,78 @@
+"""Record-aligned cutting of a FASTQ file: kmi_fastq_find_first_record is host code, like the
+reference's FASTQParser::find_first_record (fastq_loader.hpp:269-357), so these tests need no GPU. The C ABI function is
+compared with the oracle's restatement at every cut point, and both with the true record starts of the fixtures (what the
+reference's own partition tests assert: every block starts at an '@' header line, mpi_test_fastq_seq_parse.cpp)."""
+import numpy as np
+import pytest
+
+import kmerind_b200 as kb
+import oracle_util as ou
+
+FASTQ = ["test.small.fastq", "test.medium.fastq", "natural.fastq", "natural.withN.fastq"]
+
+
+def record_starts(buf):
+    """offsets of line 0 (mod 4) starts, counting non-empty lines as the reference's record walk does"""
+    b = buf.tobytes()
+    starts, i, line, n = [], 0, 0, len(b)
+    while i < n:
+        while i < n and b[i] in (10, 13):
+            i += 1
+        if i >= n:
+            break
+        if line % 4 == 0:
+            starts.append(i)
+        while i < n and b[i] not in (10, 13):
+            i += 1
+        line += 1
+    return np.array(starts, dtype=np.int64)
+
+
+@pytest.mark.parametrize("name", FASTQ)
+def test_find_first_record_matches_oracle_and_true_starts(name):
+    buf = ou.read_fixture(name)
+    n = buf.size
+    starts = record_starts(buf)
+    step = max(1, n // 400)
+    for c in list(range(0, n, step)) + [n - 1, n]:
+        want = ou.fastq_find_first_record(buf, c)
+        got = kb.fastq_find_first_record(buf, c)
+        assert got == want, (name, c)
+        if got < n:
+            assert got in starts and got >= c or c == 0, (name, c, got)
+            # it is the FIRST record start whose header line begins at or after the first line start >= c
+            nxt = starts[starts >= c]
+            assert len(nxt) and got <= nxt[min(1, len(nxt) - 1)], (name, c, got)
+
+
+def test_find_first_record_windows_and_errors():
+    buf = ou.read_fixture("test.small.fastq")
+    n = buf.size
+    starts = record_starts(buf)
+    # bytes in memory are a window of the file: offsets stay file offsets
+    lo, hi = int(starts[2]) - 5, int(starts[5]) + 40
+    win = buf[lo:hi]
+    assert kb.fastq_find_first_record(win, lo, hi, mem_offset=lo, parent=(0, n)) == ou.fastq_find_first_record(win, lo, hi, lo, (0, n)) == int(starts[2])
+    # a range too short to hold four lines and not at the parent's end -> end of the range; garbage -> format error
+    assert kb.fastq_find_first_record(buf, 3, 20, parent=(0, n)) == 20
+    junk = np.frombuffer(b"xxxx\nyyyy\nzzzz\nwwww\nvvvv\nuuuu\n", dtype=np.uint8)
+    with pytest.raises(ValueError):
+        ou.fastq_find_first_record(junk, 2, 25, 0, (0, 1000))
+    with pytest.raises(kb.KmiError):
+        kb.fastq_find_first_record(junk, 2, 25, parent=(0, 1000))
+
+
+@pytest.mark.parametrize("parts", (2, 3, 8))
+def test_cuts_partition_the_kmers(parts):
+    """blocks cut at kmi_fastq_find_first_record boundaries are whole records: their k-mer multisets add up"""
+    buf = ou.read_fixture("natural.fastq")
+    cuts = kb.fastq_cuts(buf, parts)
+    assert cuts[0] == 0 and cuts[-1] == buf.size and all(a <= b for a, b in zip(cuts, cuts[1:]))
+    whole, _, reads = ou.fastq_kmers(buf, 21)
+    got, n_reads = [], 0
+    for a, b in zip(cuts, cuts[1:]):
+        k, _, r = ou.fastq_kmers(buf[a:b], 21)
+        got.append(k)
+        n_reads += r
+    assert n_reads == reads
+    assert np.array_equal(np.sort(np.concatenate(got)), np.sort(whole))
