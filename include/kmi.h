@@ -95,6 +95,35 @@ int kmi_build_fasta(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t* n_
 int kmi_build_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers);
 int kmi_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* n_kmers);
 
+/* ---- a6: one block of a partitioned FASTA file (KmerParser::get_valid_iterator_range, kmer_parser.hpp:114-157; the
+ * FASTA tail rule of KmerFileHelper::read_block, kmer_file_helper.hpp:153-173; the cross-rank part of
+ * FASTAParser::init_parser, fasta_loader.hpp:202-483). A block may begin and end at ANY byte. The `n` bytes passed are
+ * the block's own bytes [0, n_valid) followed by halo bytes: a k-mer is emitted iff its first base lies in the block,
+ * and it may run K-1 bases into the halo, so the halo must hold K-1 non-EOL bytes or reach the end of the file
+ * (kmi_fasta_halo_end). What precedes the block enters as three facts: how many header runs began before it
+ * (sequence id = that count, minus one when the file opens with a header line), whether the last line start before it
+ * began a header line, and whether its first byte starts a line. kmi_fasta_block_summary_dev computes a block's own
+ * contribution so that ranks can combine them with one exclusive scan (kmi::fasta_chain in kmi_index.hpp):
+ *   out[0] the block holds a line start, out[1] its first line start begins a header, out[2] its last one does,
+ *   out[3] header runs starting inside it, counted as if the line before the block were no header (subtract one when
+ *   out[1] is set and the previous block hands over a header line).
+ * block == NULL means the whole file (kmi_build_fasta / kmi_parse_fasta_dev are exactly that). */
+typedef struct {
+  uint64_t file_offset;         /* file byte of bytes[0] (position ids carry file offsets) */
+  uint64_t n_valid;             /* bytes owned by the block; the rest of the buffer is halo */
+  uint32_t header_runs_before;  /* header runs that start before the block */
+  uint32_t flags;               /* KMI_FASTA_* */
+} kmi_fasta_block;
+#define KMI_FASTA_BOL 1u                       /* bytes[0] starts a line (file start, or the previous byte is '\n') */
+#define KMI_FASTA_PREV_HEADER 2u               /* the last line start before the block begins a header line */
+#define KMI_FASTA_FILE_STARTS_WITH_HEADER 4u   /* byte 0 of the FILE is '>' or ';' */
+int kmi_fasta_block_summary_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n_valid, int bol, uint32_t* out /* 4 */);
+int kmi_build_fasta_block(kmi_index* idx, const uint8_t* bytes, size_t n, const kmi_fasta_block* block, uint64_t* n_kmers);
+int kmi_build_fasta_block_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, const kmi_fasta_block* block, uint64_t* n_kmers);
+/* host: end of the halo of a block ending at file byte valid_end: the first offset by which K-1 non-EOL bytes follow
+ * valid_end, or n_file. `bytes` holds the file bytes [mem_offset, mem_offset + n). */
+int kmi_fasta_halo_end(const uint8_t* bytes, uint64_t mem_offset, size_t n, uint64_t valid_end, int k, uint64_t* halo_end);
+
 /* ---- a2: record-aligned blocks (FASTQParser::find_first_record, fastq_loader.hpp:269-357,696-873) ---------------
  * Host side, as in the reference (it looks at four lines). `bytes` holds file bytes [mem_offset, mem_offset + n); the
  * search starts at search_begin (dropping a partial first line unless search_begin == parent_begin) and matches the first
@@ -116,6 +145,8 @@ int kmi_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64
                         uint64_t* d_keys, uint64_t* d_ids, size_t cap, uint64_t* n_kmers);
 int kmi_parse_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n,
                         uint64_t* d_keys, uint64_t* d_ids, size_t cap, uint64_t* n_kmers);
+int kmi_parse_fasta_block_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, const kmi_fasta_block* block,
+                              uint64_t* d_keys, uint64_t* d_ids, size_t cap, uint64_t* n_kmers);
 /* a2-a14 fused for the sharded build: parse + owner = dist_hash % nranks + scatter, straight into one
  * region of `region_cap` keys per owning rank (d_regions + r * region_cap * nw): the send buffers of the
  * all-to-all, with h_counts[nranks] the send counts (imxx::distribute up to mxx::all2allv,

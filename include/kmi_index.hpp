@@ -50,6 +50,25 @@ inline std::vector<size_t> fastq_cuts(const uint8_t* bytes, size_t n, int parts)
   return cuts;
 }
 
+/// What every block of a partitioned FASTA file inherits from the bytes before it, from the per-block summaries of
+/// kmi_fasta_block_summary_dev (blocks in file order; summaries[r] = 4 words, bol[r] = block r starts a line): an exclusive
+/// scan carrying (header runs so far, kind of the last line start) — the cross-rank part of FASTAParser::init_parser
+/// (reference src/io/fasta_loader.hpp:202-483). Fills header_runs_before and flags of blocks[r]; file_offset and n_valid are
+/// the caller's.
+inline void fasta_chain(const uint32_t (*summaries)[4], const bool* bol, int parts, bool file_starts_with_header,
+                        kmi_fasta_block* blocks) {
+  uint32_t runs = 0, kind = 0;
+  for (int r = 0; r < parts; ++r) {
+    blocks[r].header_runs_before = runs;
+    blocks[r].flags = (bol[r] ? KMI_FASTA_BOL : 0u) | (kind ? KMI_FASTA_PREV_HEADER : 0u) |
+                      (file_starts_with_header ? KMI_FASTA_FILE_STARTS_WITH_HEADER : 0u);
+    if (summaries[r][0]) {
+      runs += summaries[r][3] - ((summaries[r][1] && kind) ? 1u : 0u);
+      kind = summaries[r][2];
+    }
+  }
+}
+
 /// bliss::common::Kmer<K, DNA, uint64_t> look-alike: same size, same word order.
 template <unsigned K_>
 struct Kmer {

@@ -69,6 +69,10 @@ def load_library(build_if_missing=False):
         "kmi_build_fastq_dev": [_P, _P, _SZ, _U64, _P], "kmi_build_fasta_dev": [_P, _P, _SZ, _P],
         "kmi_parse_fastq_dev": [_P, _P, _SZ, _U64, _P, _P, _SZ, _P],
         "kmi_parse_fasta_dev": [_P, _P, _SZ, _P, _P, _SZ, _P],
+        "kmi_parse_fasta_block_dev": [_P, _P, _SZ, _P, _P, _P, _SZ, _P],
+        "kmi_build_fasta_block": [_P, _P, _SZ, _P, _P], "kmi_build_fasta_block_dev": [_P, _P, _SZ, _P, _P],
+        "kmi_fasta_block_summary_dev": [_P, _P, _SZ, ctypes.c_int, _P],
+        "kmi_fasta_halo_end": [_P, _U64, _SZ, _U64, ctypes.c_int, _P],
         "kmi_parse_fastq_by_owner_dev": [_P, _P, _SZ, _P, _SZ, _P, _P],
         "kmi_exchange_setup": [_P, _SZ, _P], "kmi_exchange_connect": [_P, _P],
         "kmi_exchange_parse_fastq_dev": [_P, _P, _SZ, _P, _P], "kmi_exchange_insert": [_P, _P],
@@ -97,7 +101,8 @@ def load_library(build_if_missing=False):
 EXPORTED_SYMBOLS = (
     "kmi_create", "kmi_destroy", "kmi_last_error", "kmi_set_stream", "kmi_set_param", "kmi_reserve", "kmi_clear",
     "kmi_build_fastq", "kmi_build_fasta", "kmi_build_fastq_dev", "kmi_build_fasta_dev",
-    "kmi_parse_fastq_dev", "kmi_parse_fasta_dev", "kmi_parse_fastq_by_owner_dev", "kmi_exchange_setup", "kmi_exchange_connect",
+    "kmi_parse_fastq_dev", "kmi_parse_fasta_dev", "kmi_parse_fasta_block_dev", "kmi_build_fasta_block", "kmi_build_fasta_block_dev",
+    "kmi_fasta_block_summary_dev", "kmi_fasta_halo_end", "kmi_parse_fastq_by_owner_dev", "kmi_exchange_setup", "kmi_exchange_connect",
     "kmi_exchange_parse_fastq_dev", "kmi_exchange_insert", "kmi_exchange_bins", "kmi_fastq_find_first_record", "kmi_canonicalize_dev", "kmi_hash_dev",
     "kmi_partition_dev", "kmi_insert", "kmi_insert_dev", "kmi_count", "kmi_find", "kmi_find_positions",
     "kmi_erase", "kmi_count_dev", "kmi_find_dev", "kmi_local_size", "kmi_num_keys", "kmi_dump",
@@ -141,6 +146,39 @@ def fastq_find_first_record(buf, search_begin, search_end=None, mem_offset=0, pa
     out = _U64(0)
     _check(load_library().kmi_fastq_find_first_record(_hptr(buf), mem_offset, buf.size, search_begin, search_end, pb, pe, ctypes.byref(out)))
     return out.value
+
+
+class KmiFastaBlock(ctypes.Structure):
+    """mirror of kmi_fasta_block (include/kmi.h)"""
+    _fields_ = [("file_offset", ctypes.c_uint64), ("n_valid", ctypes.c_uint64), ("header_runs_before", ctypes.c_uint32),
+                ("flags", ctypes.c_uint32)]
+
+
+FASTA_BOL, FASTA_PREV_HEADER, FASTA_FILE_STARTS_WITH_HEADER = 1, 2, 4
+
+
+def fasta_halo_end(buf, valid_end, k, mem_offset=0):
+    """kmi_fasta_halo_end: file offset up to which a block ending at valid_end needs bytes (K-1 non-EOL bytes)."""
+    a = np.frombuffer(buf, dtype=np.uint8) if not isinstance(buf, np.ndarray) else buf
+    out = _U64(0)
+    _check(load_library().kmi_fasta_halo_end(_hptr(a), mem_offset, a.size, valid_end, k, ctypes.byref(out)))
+    return out.value
+
+
+def fasta_chain(summaries, bol, file_starts_with_header):
+    """Combine the per-block summaries of kmi_fasta_block_summary_dev (blocks in file order) into what each block needs
+    from the bytes before it: an exclusive scan carrying (header runs so far, kind of the last line start) — the
+    cross-rank part of FASTAParser::init_parser (fasta_loader.hpp:202-483). summaries[r] = (has_line_start,
+    first_is_header, last_is_header, runs); bol[r] = block r's first byte starts a line. Returns [(header_runs_before,
+    flags)] for kmi_fasta_block."""
+    out, runs, kind = [], 0, 0
+    for (has, first_h, last_h, r), b in zip(summaries, bol):
+        flags = (FASTA_BOL if b else 0) | (FASTA_PREV_HEADER if kind else 0) | (FASTA_FILE_STARTS_WITH_HEADER if file_starts_with_header else 0)
+        out.append((runs, flags))
+        if has:
+            runs += int(r) - (1 if (first_h and kind) else 0)
+            kind = int(last_h)
+    return out
 
 
 def fastq_cuts(buf, parts):
@@ -192,10 +230,11 @@ class Index:
         _check(self._lib.kmi_build_fastq(self._h, _hptr(buf), buf.size, file_offset, ctypes.byref(n)))
         return n.value
 
-    def build_fasta(self, data):
+    def build_fasta(self, data, block=None):
         buf = np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data
         n = _U64(0)
-        _check(self._lib.kmi_build_fasta(self._h, _hptr(buf), buf.size, ctypes.byref(n)))
+        blk = ctypes.byref(KmiFastaBlock(*block)) if block is not None else None
+        _check(self._lib.kmi_build_fasta_block(self._h, _hptr(buf), buf.size, blk, ctypes.byref(n)))
         return n.value
 
     def build_fastq_dev(self, dptr, nbytes, file_offset=0):
@@ -203,9 +242,10 @@ class Index:
         _check(self._lib.kmi_build_fastq_dev(self._h, dptr, nbytes, file_offset, ctypes.byref(n)))
         return n.value
 
-    def build_fasta_dev(self, dptr, nbytes):
+    def build_fasta_dev(self, dptr, nbytes, block=None):
         n = _U64(0)
-        _check(self._lib.kmi_build_fasta_dev(self._h, dptr, nbytes, ctypes.byref(n)))
+        blk = ctypes.byref(KmiFastaBlock(*block)) if block is not None else None
+        _check(self._lib.kmi_build_fasta_block_dev(self._h, dptr, nbytes, blk, ctypes.byref(n)))
         return n.value
 
     # -- stages on device pointers ------------------------------------------------------------
@@ -248,10 +288,17 @@ class Index:
         c = np.ascontiguousarray(recv_counts, dtype=np.uint64)
         _check(self._lib.kmi_exchange_insert(self._h, _hptr(c)))
 
-    def parse_fasta_dev(self, dptr, nbytes, d_keys, cap, d_ids=None):
+    def parse_fasta_dev(self, dptr, nbytes, d_keys, cap, d_ids=None, block=None):
+        """block = None (whole file) or (file_offset, n_valid, header_runs_before, flags): kmi_fasta_block"""
         n = _U64(0)
-        _check(self._lib.kmi_parse_fasta_dev(self._h, dptr, nbytes, d_keys, d_ids, cap, ctypes.byref(n)))
+        blk = ctypes.byref(KmiFastaBlock(*block)) if block is not None else None
+        _check(self._lib.kmi_parse_fasta_block_dev(self._h, dptr, nbytes, blk, d_keys, d_ids, cap, ctypes.byref(n)))
         return n.value
+
+    def fasta_block_summary_dev(self, dptr, n_valid, bol):
+        out = (ctypes.c_uint32 * 4)()
+        _check(self._lib.kmi_fasta_block_summary_dev(self._h, dptr, n_valid, 1 if bol else 0, out))
+        return tuple(int(x) for x in out)
 
     def canonicalize_dev(self, d_in, d_out, n):
         _check(self._lib.kmi_canonicalize_dev(self._h, d_in, d_out, n))

@@ -63,7 +63,7 @@ struct DevBuf {
 };
 
 // device counters block
-enum { CTR_SIZE = 0, CTR_NKMERS = 1, CTR_CURSOR = 2, CTR_CK0 = 3, CTR_CK1 = 4, CTR_REMOVED = 5, CTR_ERR = 6, CTR_PERR = 7, CTR_CARRY = 8, CTR_N = 10 };
+enum { CTR_SIZE = 0, CTR_NKMERS = 1, CTR_CURSOR = 2, CTR_CK0 = 3, CTR_CK1 = 4, CTR_REMOVED = 5, CTR_ERR = 6, CTR_PERR = 7, CTR_CARRY = 8, CTR_FIRST_LS = 9, CTR_N = 10 };
 
 // bkt_meta layout (u32 words): cursors [0, N_BUCKETS], HLL registers from META_HLL
 enum { META_HLL = 512, META_WORDS = META_HLL + HLL_M };
@@ -536,6 +536,21 @@ static int insert_keys_bucketed(kmi_index* idx, const u64* d_keys, size_t n, boo
 // are matched against @?+? / ?@?+ / +?@? / ?+?@. This is what cuts a file into the record-aligned blocks that
 // kmi_build_fastq / kmi_parse_fastq_dev take (one block per GPU, or per pipelined chunk).
 static inline bool host_is_eol(uint8_t c) { return c == '\n' || c == '\r'; }
+// a6 (host): how far past a block's end its k-mers can reach — K-1 bytes that are not EOL, counted as
+// KmerFileHelper::read_block does for a FASTA sequence that runs into the overlap (kmer_file_helper.hpp:153-173)
+extern "C" int kmi_fasta_halo_end(const uint8_t* bytes, uint64_t mem_offset, size_t n, uint64_t valid_end, int k, uint64_t* halo_end) {
+  if ((!bytes && n) || !halo_end) return fail(KMI_ERR_ARG, "null argument");
+  if (k < 1 || valid_end < mem_offset || valid_end > mem_offset + n) return fail(KMI_ERR_ARG, "valid_end outside the bytes given");
+  uint64_t p = valid_end - mem_offset;
+  int need = k - 1;
+  while (p < n && need > 0) {
+    const uint8_t c = bytes[p++];
+    if (c != '\n' && c != '\r') --need;
+  }
+  *halo_end = mem_offset + p;
+  return KMI_OK;
+}
+
 extern "C" int kmi_fastq_find_first_record(const uint8_t* bytes, uint64_t mem_offset, size_t n, uint64_t search_begin,
                                            uint64_t search_end, uint64_t parent_begin, uint64_t parent_end, uint64_t* offset) {
   if ((!bytes && n) || !offset) return fail(KMI_ERR_ARG, "null argument");
@@ -1468,45 +1483,72 @@ extern "C" int kmi_synth_fastq_dev(int device, uint8_t* d_out, uint64_t first_re
 }
 
 // ---- FASTA ---------------------------------------------------------------------------------------------------
-// pass A: line kinds entering every tile (max-scan) and header runs before every tile (sum-scan)
-static int fasta_scan(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64* n_tiles_out) {
+// per-tile side arrays of one block: enc[n_tiles + 1] (max-scanned in place) | first_t[n_tiles] | runs[n_tiles + 1]
+// (sum-scanned in place); the extra entry is a zero whose exclusive scan value is the whole block's total.
+struct FastaArrays {
+  u64 n_tiles, n_blocks;
+  u32 *enc, *first_t, *runs, *enc_max, *runs_sums;
+};
+static FastaArrays fasta_arrays(kmi_index* idx, u64 n_tiles) {
+  FastaArrays a;
+  a.n_tiles = n_tiles; a.n_blocks = (n_tiles + 1 + 1023) / 1024;
+  a.enc = idx->tile_lines.as<u32>(); a.first_t = a.enc + n_tiles + 1; a.runs = a.first_t + n_tiles;
+  a.enc_max = idx->block_sums.as<u32>(); a.runs_sums = a.enc_max + a.n_blocks;
+  return a;
+}
+static FaBlock whole_file_block(size_t n) {
+  FaBlock b;
+  b.file_offset = 0; b.n_valid = n; b.runs0 = 0; b.kind0 = 0; b.bol = 1; b.first_is_header = 2;  // 2: look at bytes[0]
+  return b;
+}
+static int fasta_block_from_abi(const kmi_fasta_block* in, size_t n, FaBlock* out) {
+  if (!in) { *out = whole_file_block(n); return KMI_OK; }
+  if (in->n_valid > n) return fail(KMI_ERR_ARG, "kmi_fasta_block: n_valid %llu exceeds the %zu bytes given", (unsigned long long)in->n_valid, n);
+  out->file_offset = in->file_offset; out->n_valid = in->n_valid; out->runs0 = in->header_runs_before;
+  out->kind0 = (in->flags & KMI_FASTA_PREV_HEADER) ? 1u : 0u;
+  out->bol = (in->flags & KMI_FASTA_BOL) ? 1u : 0u;
+  out->first_is_header = (in->flags & KMI_FASTA_FILE_STARTS_WITH_HEADER) ? 1u : 0u;
+  return KMI_OK;
+}
+// pass A: line kinds entering every tile (max-scan) and header runs before every tile (sum-scan), over the block's own
+// bytes [0, n_valid); the halo needs no scan (the parse kernel reads its line structure itself)
+static int fasta_scan(kmi_index* idx, const uint8_t* d_bytes, size_t n, FaBlock* blk, u64* n_tiles_out) {
   if ((reinterpret_cast<uintptr_t>(d_bytes) & 15) != 0) return fail(KMI_ERR_ARG, "device text buffer must be 16-byte aligned");
-  u64 n_tiles = (n + TILE_BYTES - 1) / TILE_BYTES;
+  u64 n_tiles = (blk->n_valid + TILE_BYTES - 1) / TILE_BYTES;
   *n_tiles_out = n_tiles;
   if (n_tiles == 0) return KMI_OK;
   if (n_tiles > 0x3fffffffULL) return fail(KMI_ERR_ARG, "block of %zu bytes too large for one call", n);
-  u64 n_blocks = (n_tiles + 1023) / 1024;
-  // tile_lines: enc (max-scanned in place) | first_t | runs   ; block_sums: enc block maxima | runs block sums
-  OK(idx->tile_lines.ensure(sizeof(u32) * n_tiles * 3));
+  if (blk->first_is_header == 2) {   // whole file: its first byte says whether it opens with a header
+    uint8_t c = 0;
+    CU(cudaMemcpyAsync(&c, d_bytes, 1, cudaMemcpyDeviceToHost, idx->stream));
+    CU(cudaStreamSynchronize(idx->stream));
+    blk->first_is_header = (c == '>' || c == ';') ? 1u : 0u;
+  }
+  u64 n_blocks = (n_tiles + 1 + 1023) / 1024;
+  OK(idx->tile_lines.ensure(sizeof(u32) * (n_tiles * 3 + 2)));
   OK(idx->block_sums.ensure(sizeof(u32) * n_blocks * 2));
-  u32* enc = idx->tile_lines.as<u32>();
-  u32* first_t = enc + n_tiles;
-  u32* runs = enc + 2 * n_tiles;
-  u32* enc_max = idx->block_sums.as<u32>();
-  u32* runs_sums = enc_max + n_blocks;
-  k_fasta_tiles<<<(unsigned)n_tiles, TILE_THREADS, 0, idx->stream>>>(d_bytes, n, enc, first_t);
-  k_maxscan_l1<<<(unsigned)n_blocks, 1024, 0, idx->stream>>>(enc, n_tiles, enc_max);
-  k_maxscan_l2<<<1, 32, 0, idx->stream>>>(enc_max, n_blocks);
-  k_fasta_tile_starts<<<grid_for(n_tiles, 256), 256, 0, idx->stream>>>(enc, enc_max, first_t, n_tiles, runs);
-  k_scan_l1<<<(unsigned)n_blocks, 1024, 0, idx->stream>>>(runs, n_tiles, runs_sums);
-  k_scan_tiles<<<1, 1024, 0, idx->stream>>>(runs_sums, n_blocks);
+  FastaArrays a = fasta_arrays(idx, n_tiles);
+  CU(cudaMemsetAsync(idx->ctr + CTR_FIRST_LS, 0xFF, sizeof(u64), idx->stream));
+  k_fasta_tiles<<<(unsigned)n_tiles, TILE_THREADS, 0, idx->stream>>>(d_bytes, n, blk->n_valid, blk->bol, a.enc, a.first_t, idx->ctr + CTR_FIRST_LS);
+  k_maxscan_l1<<<(unsigned)n_blocks, 1024, 0, idx->stream>>>(a.enc, n_tiles + 1, a.enc_max);
+  k_maxscan_l2<<<1, 32, 0, idx->stream>>>(a.enc_max, n_blocks);
+  k_fasta_tile_starts<<<grid_for(n_tiles + 1, 256), 256, 0, idx->stream>>>(a.enc, a.enc_max, a.first_t, n_tiles, blk->kind0, a.runs);
+  k_scan_l1<<<(unsigned)n_blocks, 1024, 0, idx->stream>>>(a.runs, n_tiles + 1, a.runs_sums);
+  k_scan_tiles<<<1, 1024, 0, idx->stream>>>(a.runs_sums, n_blocks);
   idx->launches += 6;
+  CU(cudaGetLastError());
   return KMI_OK;
 }
 
 // parse tiles [tile_begin, tile_begin + tiles) into the sink; retries with the wide halo when needed
-static int fasta_parse_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64 n_tiles_total, u64 tile_begin, u64 tiles,
-                             KeySink sink, u64* produced) {
-  u64 n_blocks = (n_tiles_total + 1023) / 1024;
-  u32* enc = idx->tile_lines.as<u32>();
-  u32* runs = enc + 2 * n_tiles_total;
-  u32* enc_max = idx->block_sums.as<u32>();
-  u32* runs_sums = enc_max + n_blocks;
+static int fasta_parse_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, const FaBlock& blk, u64 n_tiles_total, u64 tile_begin,
+                             u64 tiles, KeySink sink, u64* produced) {
+  FastaArrays a = fasta_arrays(idx, n_tiles_total);
   for (int attempt = 0; attempt < 2; ++attempt) {
     OK(zero_ctr(idx, CTR_NKMERS, 2));
     OK(zero_ctr(idx, CTR_PERR));
-    idx->ops->fasta_kmers(idx->stream, attempt == 1, d_bytes, n, tiles, enc, enc_max, runs, runs_sums, sink, idx->ctr + CTR_NKMERS,
-                          reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0, idx->cfg.nsplit != 0, tile_begin);
+    idx->ops->fasta_kmers(idx->stream, attempt == 1, d_bytes, n, tiles, a.enc, a.enc_max, a.runs, a.runs_sums, sink, idx->ctr + CTR_NKMERS,
+                          reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0, idx->cfg.nsplit != 0, tile_begin, blk);
     idx->launches++;
     u64 host[CTR_N];
     CU(cudaMemcpyAsync(host, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
@@ -1518,29 +1560,64 @@ static int fasta_parse_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, u
   return KMI_OK;
 }
 
-extern "C" int kmi_parse_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* d_keys, uint64_t* d_ids,
-                                   size_t cap, uint64_t* n_kmers) {
+extern "C" int kmi_fasta_block_summary_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n_valid, int bol, uint32_t* out) {
+  if (!idx || (!d_bytes && n_valid) || !out) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  out[0] = out[1] = out[2] = out[3] = 0;
+  FaBlock blk = whole_file_block(n_valid);
+  blk.bol = bol ? 1u : 0u; blk.first_is_header = 0;
+  u64 n_tiles = 0;
+  OK(fasta_scan(idx, d_bytes, n_valid, &blk, &n_tiles));
+  if (n_tiles == 0) return KMI_OK;
+  FastaArrays a = fasta_arrays(idx, n_tiles);
+  u32 enc = 0, enc_b = 0, runs = 0, runs_b = 0;
+  u64 first = 0;
+  CU(cudaMemcpyAsync(&enc, a.enc + n_tiles, 4, cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaMemcpyAsync(&enc_b, a.enc_max + (n_tiles >> 10), 4, cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaMemcpyAsync(&runs, a.runs + n_tiles, 4, cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaMemcpyAsync(&runs_b, a.runs_sums + (n_tiles >> 10), 4, cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaMemcpyAsync(&first, idx->ctr + CTR_FIRST_LS, 8, cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaStreamSynchronize(idx->stream));
+  const u32 last = std::max(enc, enc_b);
+  out[0] = last ? 1u : 0u;                                   // the block holds a line start
+  out[1] = (last && first != ~0ULL) ? (u32)(first & 1u) : 0u;  // its first line start begins a header line
+  out[2] = last & 1u;                                        // its last one does
+  out[3] = runs + runs_b;                                    // header runs starting in the block if the line before it is no header
+  return KMI_OK;
+}
+
+extern "C" int kmi_parse_fasta_block_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, const kmi_fasta_block* block,
+                                         uint64_t* d_keys, uint64_t* d_ids, size_t cap, uint64_t* n_kmers) {
   if (!idx || (!d_bytes && n) || (!d_keys && cap)) return fail(KMI_ERR_ARG, "null argument");
   CU(cudaSetDevice(idx->cfg.device));
   if (n_kmers) *n_kmers = 0;
+  FaBlock blk;
+  OK(fasta_block_from_abi(block, n, &blk));
   u64 n_tiles = 0;
-  OK(fasta_scan(idx, d_bytes, n, &n_tiles));
+  OK(fasta_scan(idx, d_bytes, n, &blk, &n_tiles));
   if (n_tiles == 0) return KMI_OK;
   KeySink sink;
   sink.keys = reinterpret_cast<u64*>(d_keys); sink.ids = reinterpret_cast<u64*>(d_ids); sink.cap = cap; sink.cursor = idx->ctr + CTR_CURSOR;
   u64 produced = 0;
-  OK(fasta_parse_range(idx, d_bytes, n, n_tiles, 0, n_tiles, sink, &produced));
+  OK(fasta_parse_range(idx, d_bytes, n, blk, n_tiles, 0, n_tiles, sink, &produced));
   if (n_kmers) *n_kmers = produced;
   return KMI_OK;
 }
+extern "C" int kmi_parse_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* d_keys, uint64_t* d_ids,
+                                   size_t cap, uint64_t* n_kmers) {
+  return kmi_parse_fasta_block_dev(idx, d_bytes, n, nullptr, d_keys, d_ids, cap, n_kmers);
+}
 
-extern "C" int kmi_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* n_kmers) {
+extern "C" int kmi_build_fasta_block_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, const kmi_fasta_block* block,
+                                         uint64_t* n_kmers) {
   if (!idx || (!d_bytes && n)) return fail(KMI_ERR_ARG, "null argument");
   CU(cudaSetDevice(idx->cfg.device));
   if (n_kmers) *n_kmers = 0;
+  FaBlock blk;
+  OK(fasta_block_from_abi(block, n, &blk));
   u64 n_tiles = 0;
   CU(cudaEventRecord(idx->ev[0], idx->stream));
-  OK(fasta_scan(idx, d_bytes, n, &n_tiles));
+  OK(fasta_scan(idx, d_bytes, n, &blk, &n_tiles));
   CU(cudaEventRecord(idx->ev[1], idx->stream));
   if (n_tiles == 0) return KMI_OK;
   // bounded staging: at most CHUNK_TILES tiles of text become keys (+ids) at a time
@@ -1552,14 +1629,14 @@ extern "C" int kmi_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_
   int r = keys.ensure(cap * kb);
   if (r == KMI_OK && pos) r = ids.ensure(cap * sizeof(u64));
   u64 total = 0;
-  float parse_ms = 0, insert_ms = 0;
+  float parse_ms = 0;
   for (u64 tile = 0; r == KMI_OK && tile < n_tiles; tile += CHUNK_TILES) {
     u64 tiles = std::min<u64>(CHUNK_TILES, n_tiles - tile);
     KeySink sink;
     sink.keys = keys.as<u64>(); sink.ids = pos ? ids.as<u64>() : nullptr; sink.cap = cap; sink.cursor = idx->ctr + CTR_CURSOR;
     u64 produced = 0;
     cudaEventRecord(idx->ev[2], idx->stream);
-    r = fasta_parse_range(idx, d_bytes, n, n_tiles, tile, tiles, sink, &produced);
+    r = fasta_parse_range(idx, d_bytes, n, blk, n_tiles, tile, tiles, sink, &produced);
     cudaEventRecord(idx->ev[3], idx->stream);
     if (r != KMI_OK) break;
     // keys are already canonical: insert them as they are
@@ -1577,7 +1654,6 @@ extern "C" int kmi_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_
     parse_ms += a;
     total += produced;
   }
-  (void)insert_ms;
   if (r != KMI_OK) return r;
   cudaEventElapsedTime(&idx->stage_ms[0], idx->ev[0], idx->ev[1]);
   idx->stage_ms[1] = parse_ms;
@@ -1585,11 +1661,18 @@ extern "C" int kmi_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_
   if (n_kmers) *n_kmers = total;
   return check_table_error(idx);
 }
+extern "C" int kmi_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* n_kmers) {
+  return kmi_build_fasta_block_dev(idx, d_bytes, n, nullptr, n_kmers);
+}
 
-extern "C" int kmi_build_fasta(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t* n_kmers) {
+extern "C" int kmi_build_fasta_block(kmi_index* idx, const uint8_t* bytes, size_t n, const kmi_fasta_block* block,
+                                    uint64_t* n_kmers) {
   if (!idx || (!bytes && n)) return fail(KMI_ERR_ARG, "null argument");
   CU(cudaSetDevice(idx->cfg.device));
   OK(idx->stage_in.ensure(n + 64));
   CU(cudaMemcpyAsync(idx->stage_in.p, bytes, n, cudaMemcpyHostToDevice, idx->stream));
-  return kmi_build_fasta_dev(idx, idx->stage_in.as<uint8_t>(), n, n_kmers);
+  return kmi_build_fasta_block_dev(idx, idx->stage_in.as<uint8_t>(), n, block, n_kmers);
+}
+extern "C" int kmi_build_fasta(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t* n_kmers) {
+  return kmi_build_fasta_block(idx, bytes, n, nullptr, n_kmers);
 }

@@ -70,9 +70,21 @@ __device__ __forceinline__ FaGroup fasta_lines(const uint4& v, u32 nl, bool prev
   f.hdr = f.ls & h;
   return f;
 }
-__device__ __forceinline__ bool prev_is_nl(const uint8_t* __restrict__ bytes, u64 off) {
-  return off == 0 || __ldg(bytes + off - 1) == '\n';
+__device__ __forceinline__ bool prev_is_nl(const uint8_t* __restrict__ bytes, u64 off, bool bol) {
+  return off == 0 ? bol : __ldg(bytes + off - 1) == '\n';
 }
+// One block of a FASTA file (rank r's byte range of a partitioned file, or one chunk of a streamed one). The text
+// passed holds the block's own bytes [0, n_valid) followed by halo bytes up to n: k-mers are emitted for first bases
+// inside [0, n_valid) and may run K-1 bases into the halo (KmerParser::get_valid_iterator_range, kmer_parser.hpp:114-157;
+// FASTA tail rule kmer_file_helper.hpp:153-173). What the bytes before the block contribute is three numbers.
+struct FaBlock {
+  u64 file_offset;      // file byte of bytes[0]
+  u64 n_valid;          // bytes owned by the block
+  u32 runs0;            // header runs that start before the block
+  u32 kind0;            // 1: the last line start before the block begins a header line
+  u32 bol;              // 1: bytes[0] starts a line (file start or previous byte '\n')
+  u32 first_is_header;  // 1: the FILE starts with a header line (sequence id = header runs so far - this)
+};
 // header-run starts inside a group: header line starts whose previous line start (inside the
 // group, else `prev_kind`) is a non-header
 __device__ __forceinline__ u32 header_run_starts(u32 ls, u32 hdr, u32 prev_kind) {
@@ -96,19 +108,20 @@ __device__ __forceinline__ u32 enc_last(u32 ls, u32 hdr, u32 pos) {
 #ifdef KMI_SHARED_KERNELS
 // pass A1: per tile: enc (for the max scan); (internal header-run starts << 2) | has << 1 | kind of first line start
 __global__ void __launch_bounds__(TILE_THREADS)
-k_fasta_tiles(const uint8_t* __restrict__ bytes, u64 n, u32* __restrict__ tile_enc, u32* __restrict__ tile_first_t) {
+k_fasta_tiles(const uint8_t* __restrict__ bytes, u64 n, const u64 n_valid, const u32 bol, u32* __restrict__ tile_enc,
+              u32* __restrict__ tile_first_t, u64* __restrict__ first_ls) {
   __shared__ u32 tmp[TILE_THREADS / 32 + 1];
   __shared__ u32 s_first;
   const int t = threadIdx.x;
   if (t == 0) s_first = 0xFFFFFFFFu;
   u64 off = (u64)blockIdx.x * TILE_BYTES + (u64)t * GROUP_BYTES;
   FaGroup f; f.ls = 0; f.hdr = 0;
-  if (off < n) {
+  if (off < n_valid) {
     uint4 v = load_group(bytes, off, n);
     Group g = classify(v);
-    f = fasta_lines(v, g.nl, prev_is_nl(bytes, off));
-    // line starts at or past the end of the text do not exist
-    if (off + GROUP_BYTES > n) { u32 keep = (1u << (n - off)) - 1; f.ls &= keep; f.hdr &= keep; }
+    f = fasta_lines(v, g.nl, prev_is_nl(bytes, off, bol != 0));
+    // line starts at or past the end of the block are not this block's
+    if (off + GROUP_BYTES > n_valid) { u32 keep = (1u << (n_valid - off)) - 1; f.ls &= keep; f.hdr &= keep; }
   }
   u32 total_enc;
   u32 prev = block_excl_scan_max(enc_last(f.ls, f.hdr, (u32)t), tmp, total_enc);
@@ -122,6 +135,10 @@ k_fasta_tiles(const uint8_t* __restrict__ bytes, u64 n, u32* __restrict__ tile_e
     tile_enc[blockIdx.x] = total_enc ? ((((u32)blockIdx.x + 1) << 1) | (total_enc & 1u)) : 0u;
     u32 first_kind = (s_first == 0xFFFFFFFFu) ? 0u : (s_first & 1u);
     tile_first_t[blockIdx.x] = (total_t << 2) | (total_enc ? 2u : 0u) | first_kind;
+    if (blockIdx.x == 0) tile_enc[gridDim.x] = 0;   // sentinel: its exclusive scan value is the whole block's
+    // first line start of the block (tile << 1 | kind), for the block summary
+    const u64 mine = ((u64)blockIdx.x << 1) | first_kind;
+    if (total_enc && mine < *first_ls) atomicMin(reinterpret_cast<unsigned long long*>(first_ls), (unsigned long long)mine);
   }
 }
 // two-level exclusive max scan (same shape as k_scan_l1 / k_scan_tiles)
@@ -175,11 +192,13 @@ __global__ void __launch_bounds__(32) k_maxscan_l2(u32* __restrict__ v, u64 n) {
 // header-run starts per tile, now that the kind of the line entering each tile is known
 __global__ void __launch_bounds__(256)
 k_fasta_tile_starts(const u32* __restrict__ tile_enc_scanned, const u32* __restrict__ block_max, const u32* __restrict__ tile_first_t,
-                    u64 n_tiles, u32* __restrict__ starts) {
-  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n_tiles; i += (u64)gridDim.x * blockDim.x) {
+                    u64 n_tiles, const u32 kind0, u32* __restrict__ starts) {
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i <= n_tiles; i += (u64)gridDim.x * blockDim.x) {
+    if (i == n_tiles) { starts[i] = 0; continue; }   // sentinel
     u32 prev = max(tile_enc_scanned[i], block_max[i >> 10]);
+    u32 pk = prev ? (prev & 1u) : kind0;
     u32 ft = tile_first_t[i];
-    u32 add = ((ft & 2u) && (ft & 1u) && !(prev & 1u)) ? 1u : 0u;  // has a line start, first is a header, entering line is not
+    u32 add = ((ft & 2u) && (ft & 1u) && !pk) ? 1u : 0u;  // has a line start, first is a header, entering line is not
     starts[i] = (ft >> 2) + add;
   }
 }
@@ -191,7 +210,7 @@ template <int K, int HASH, int FH>
 __global__ void __launch_bounds__(TILE_THREADS)
 k_fasta_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ tile_enc_scanned, const u32* __restrict__ enc_block_max,
               const u32* __restrict__ tile_runs, const u32* __restrict__ runs_block_sums, KeySink sink, u64* __restrict__ n_kmers,
-              u32* __restrict__ perr, const bool CANON, const bool NSPLIT, const u64 tile_begin) {
+              u32* __restrict__ perr, const bool CANON, const bool NSPLIT, const u64 tile_begin, const FaBlock blk) {
   constexpr int NW = (K <= 32 ? 1 : 2);
   constexpr int TG = TILE_THREADS + FH;          // raw groups incl. halo
   constexpr int MAXC = TG * GROUP_BYTES;         // compacted bases upper bound
@@ -210,7 +229,7 @@ k_fasta_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   const int t = threadIdx.x;
   const u64 tile = tile_begin + blockIdx.x;
   const u64 tile_off = tile * TILE_BYTES;
-  const u32 first_is_header = (__ldg(bytes) == '>' || __ldg(bytes) == ';') ? 1u : 0u;
+  const u32 first_is_header = blk.first_is_header;
 
   // -- P1: classify all raw groups
   for (int g = t; g < TG; g += TILE_THREADS) {
@@ -219,7 +238,7 @@ k_fasta_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
     Group gr = classify(v);
     FaGroup f; f.ls = 0; f.hdr = 0;
     if (off < n) {
-      f = fasta_lines(v, gr.nl, prev_is_nl(bytes, off));
+      f = fasta_lines(v, gr.nl, prev_is_nl(bytes, off, blk.bol != 0));
       if (off + GROUP_BYTES > n) { u32 keep = (1u << (n - off)) - 1; f.ls &= keep; f.hdr &= keep; }
     }
     s_codes[g] = gr.codes; s_ls[g] = f.ls; s_hdr[g] = f.hdr; s_eol[g] = gr.eol; s_nm[g] = gr.nmask;
@@ -229,8 +248,8 @@ k_fasta_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
 
   // -- P2: kind of the line in progress and header-run count at the start of every group
   const u32 tprev = max(tile_enc_scanned[tile], enc_block_max[tile >> 10]);
-  const u32 tile_kind = tprev & 1u;   // no line start before the tile -> 0 (non-header)
-  const u32 tile_run0 = tile_runs[tile] + runs_block_sums[tile >> 10];
+  const u32 tile_kind = tprev ? (tprev & 1u) : blk.kind0;   // no line start before the tile: what the block inherits
+  const u32 tile_run0 = blk.runs0 + tile_runs[tile] + runs_block_sums[tile >> 10];
   u32 main_enc_total, main_runs_total;
   {
     u32 ls = s_ls[t], hdr = s_hdr[t];
@@ -312,6 +331,7 @@ k_fasta_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
       cand &= cand - 1;
       u32 c = c0 + j;
       if (c >= m_owned || c + K > M) continue;
+      if (tile_off + s_raw[c] >= blk.n_valid) continue;   // first base in the halo: the next block's k-mer
       if (runs_at(s_raw[c]) == runs_at(s_raw[c + K - 1])) valid |= 1u << j;
     }
   }
@@ -348,7 +368,7 @@ k_fasta_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
       if (sink.ids) {
         const u32 raw = s_raw[c];
         const u64 sid = (u64)((runs_at(raw) - first_is_header) & 0xFFFFu);
-        sink.ids[at] = (sid << 40) | (tile_off + raw);
+        sink.ids[at] = (sid << 40) | (blk.file_offset + tile_off + raw);
       }
     } else {
       atomicOr(perr, PERR_OVERFLOW);

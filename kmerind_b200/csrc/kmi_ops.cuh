@@ -24,7 +24,7 @@ struct Ops {
   // parse (FASTA) to a key(+id) stream; wide_halo selects the 1 KiB halo variant
   void (*fasta_kmers)(cudaStream_t, bool wide_halo, const uint8_t* bytes, u64 n, u64 n_tiles, const u32* tile_enc_scanned,
                       const u32* enc_block_max, const u32* tile_runs, const u32* runs_block_sums, KeySink sink, u64* n_kmers,
-                      u32* perr, bool canon, bool nsplit, u64 tile_begin);
+                      u32* perr, bool canon, bool nsplit, u64 tile_begin, FaBlock blk);
   void (*table_clear)(cudaStream_t, void* slots, u64 n);
   void (*insert_keys)(cudaStream_t, TableView, const u64* keys, u64 n, bool canon);
   void (*rehash)(cudaStream_t, const void* old_slots, u64 n_old, TableView);
@@ -83,16 +83,16 @@ struct OpsImpl {
   }
   static void fasta_kmers(cudaStream_t st, bool wide_halo, const uint8_t* bytes, u64 n, u64 n_tiles, const u32* tile_enc_scanned,
                           const u32* enc_block_max, const u32* tile_runs, const u32* runs_block_sums, KeySink sink,
-                          u64* n_kmers, u32* perr, bool canon, bool nsplit, u64 tile_begin) {
+                          u64* n_kmers, u32* perr, bool canon, bool nsplit, u64 tile_begin, FaBlock blk) {
     if (n_tiles == 0) return;
     if (!wide_halo)
       k_fasta_kmers<K, HASH, 4><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_enc_scanned, enc_block_max, tile_runs,
                                                                           runs_block_sums, sink, n_kmers, perr, canon, nsplit,
-                                                                          tile_begin);
+                                                                          tile_begin, blk);
     else
       k_fasta_kmers<K, HASH, 64><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_enc_scanned, enc_block_max, tile_runs,
                                                                            runs_block_sums, sink, n_kmers, perr, canon, nsplit,
-                                                                           tile_begin);
+                                                                           tile_begin, blk);
   }
   static void table_clear(cudaStream_t st, void* slots, u64 n) {
     k_table_clear<NW><<<grid_for(n, 256), 256, 0, st>>>(reinterpret_cast<S*>(slots), n);

@@ -238,12 +238,29 @@ class ShardedIndex:
         self.n_received = n_recv
         return n
 
-    def build_fasta_dev(self, text, nbytes):
+    def build_fasta_dev(self, text, nbytes, n_valid=None, file_offset=0, bol=True, file_starts_with_header=None):
+        """Sharded FASTA build. With the defaults every rank holds a whole file of its own. With n_valid given, rank r
+        holds block r of ONE file (blocks in rank order, cut at any byte): text = the block's n_valid bytes + halo
+        (kmerind_b200.fasta_halo_end), file_offset = file byte of text[0], bol = text[0] starts a line. The ranks combine
+        their block summaries (header runs, kind of the last line) with one all-gather — the cross-rank part of
+        FASTAParser::init_parser, fasta_loader.hpp:202-483 — and each parses its block with global sequence ids and the
+        K-1 tail rule (kmer_parser.hpp:114-157)."""
+        from . import fasta_chain
         nw = self.nw
-        cap = max(nbytes, 1)
+        block = None
+        if n_valid is not None:
+            mine = self.local.fasta_block_summary_dev(text.data_ptr(), n_valid, bol) + (1 if bol else 0, int(file_offset))
+            every = [None] * self.nranks
+            dist.all_gather_object(every, mine, group=self.group)
+            if file_starts_with_header is None:   # rank 0's block opens the file
+                file_starts_with_header = bool(every[0][0] and every[0][1] and every[0][4] and every[0][5] == 0)
+            runs0, flags = fasta_chain([e[:4] for e in every], [e[4] for e in every], file_starts_with_header)[self.rank]
+            block = (int(file_offset), int(n_valid), runs0, flags)
+        cap = max(nbytes if n_valid is None else n_valid, 1)
         keys = torch.empty(cap * nw, dtype=torch.int64, device=self.device)
         ids = torch.empty(cap, dtype=torch.int64, device=self.device) if self.mode == MODE_POSITION else None
-        n = self.local.parse_fasta_dev(text.data_ptr(), nbytes, keys.data_ptr(), cap, ids.data_ptr() if ids is not None else None)
+        n = self.local.parse_fasta_dev(text.data_ptr(), nbytes, keys.data_ptr(), cap, ids.data_ptr() if ids is not None else None,
+                                       block=block)
         rk, rv, n_recv = self._distribute(keys, ids, n)
         self._insert_received(rk, rv, n_recv)
         torch.cuda.synchronize(self.device)

@@ -112,6 +112,35 @@ def fasta_kmers(buf, k, canonical=True, nsplit=False):
     return shape_keys(keys[:m * nw].copy(), k), ids[:m].copy(), seqs.value
 
 
+def fasta_block_kmers(buf, k, valid_begin, valid_end, canonical=True, nsplit=False):
+    """What rank r of a partitioned FASTA file emits: the file's (k-mer, id) tuples whose first base lies in the rank's valid
+    byte range — KmerParser::get_valid_iterator_range clips a sequence to [valid.start, valid.end) and lets the last windows
+    run K-1 non-EOL characters past the end (kmer_parser.hpp:114-157, kmer_file_helper.hpp:153-173); sequence ids are
+    global (FASTAParser::init_parser, fasta_loader.hpp:202-483)."""
+    keys, ids, _ = fasta_kmers(buf, k, canonical=canonical, nsplit=nsplit)
+    pos = ids & np.uint64((1 << 40) - 1)
+    sel = (pos >= np.uint64(valid_begin)) & (pos < np.uint64(valid_end))
+    return keys[sel], ids[sel]
+
+
+def fasta_prefix_state(buf, off):
+    """(header runs that start before byte off, kind of the last line start before off, off starts a line): the three
+    facts a block beginning at off inherits. Plain restatement for the tests of kmerind_b200.fasta_chain."""
+    b = bytes(np.asarray(buf[:off]).tobytes())
+    runs, kind, have, pos = 0, 0, False, 0
+    while pos < len(b):
+        is_h = b[pos] in (0x3E, 0x3B)
+        if is_h and not (have and kind):
+            runs += 1
+        kind, have = (1 if is_h else 0), True
+        nl = b.find(b"\n", pos)
+        if nl < 0:
+            break
+        pos = nl + 1
+    bol = off == 0 or buf[off - 1] == 0x0A
+    return runs, (kind if have else 0), bool(bol)
+
+
 def revcomp(keys, k):
     a = np.ascontiguousarray(keys, dtype=np.uint64)
     out = np.zeros_like(a)

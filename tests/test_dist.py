@@ -160,3 +160,48 @@ def test_sharded_count_index_nccl_world2(tmp_path, peer, K):
         got_hit = [kk in want for kk in rows(cq)]
         assert f.astype(bool).tolist() == got_hit
         assert [int(x) for x, h in zip(v, got_hit) if h] == [want[kk] for kk in rows(cq) if kk in want]
+
+
+def _nccl_fasta_worker(rank, world, port, out_dir, cut):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        import kmerind_b200 as kb
+        from kmerind_b200.dist import ShardedIndex
+        k = 21
+        buf = ou.read_fixture("test.medium.fasta")
+        cuts = [0, cut, int(buf.size)]
+        b, e = cuts[rank], cuts[rank + 1]
+        he = kb.fasta_halo_end(buf, e, k)
+        text = torch.from_numpy(np.concatenate([buf[b:he], np.zeros(64, np.uint8)])).cuda()
+        idx = ShardedIndex(k, mode=kb.MODE_POSITION, hash=kb.HASH_FARM, device=rank)
+        n = idx.build_fasta_dev(text, he - b, n_valid=e - b, file_offset=b, bol=(b == 0 or buf[b - 1] == 0x0A))
+        dk, dv = idx.local.sorted_dump()
+        np.save(os.path.join(out_dir, "fk%d.npy" % rank), dk)
+        np.save(os.path.join(out_dir, "fv%d.npy" % rank), dv)
+        np.save(os.path.join(out_dir, "fn%d.npy" % rank), np.array([n]))
+        idx.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_sharded_position_index_from_fasta_blocks_nccl_world2(tmp_path):
+    """One FASTA file, two ranks, cut in the middle of a line: every rank parses its byte range (+ K-1 halo) with global
+    sequence ids, the tuples travel to their owners, and each rank ends up with exactly the reference's tuples it owns."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    world, k = 2, 21
+    buf = ou.read_fixture("test.medium.fasta")
+    cut = int(buf.size) // 2 + 17
+    mp.spawn(_nccl_fasta_worker, args=(world, _free_port(), str(tmp_path), cut), nprocs=world, join=True)
+    wk, wi, _ = ou.fasta_kmers(buf, k)
+    owner = (ou.hashes(wk, k, 3) % np.uint64(world)).astype(np.int64)
+    cuts = [0, cut, int(buf.size)]
+    for r in range(world):
+        assert int(np.load(tmp_path / ("fn%d.npy" % r))[0]) == len(ou.fasta_block_kmers(buf, k, cuts[r], cuts[r + 1])[0])
+        sk, si = ou.sort_tuples(wk[owner == r], wi[owner == r], k)
+        assert np.array_equal(np.load(tmp_path / ("fk%d.npy" % r)), sk)
+        assert np.array_equal(np.load(tmp_path / ("fv%d.npy" % r)), si)

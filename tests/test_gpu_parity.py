@@ -212,6 +212,78 @@ def test_fastq_malformed_is_reported():
             gpu_parse(buf, 15)
 
 
+def _fasta_blocks_gpu(buf, k, cuts, nsplit=False):
+    """Parse a FASTA file as len(cuts)-1 blocks cut at arbitrary bytes, the way ranks of a partitioned file do: block
+    summaries on the GPU, chained on the host, each block parsed from its own bytes + halo."""
+    nw = ou.nwords(k)
+    parts = len(cuts) - 1
+    out = []
+    with kb.Index(k=k, nsplit=nsplit) as idx:
+        texts, summ, bol = [], [], []
+        for r in range(parts):
+            b, e = cuts[r], cuts[r + 1]
+            he = kb.fasta_halo_end(buf, e, k)
+            texts.append((dev_text(buf[b:he]), he - b))
+            bol.append(b == 0 or buf[b - 1] == 0x0A)
+            summ.append(idx.fasta_block_summary_dev(texts[r][0].data_ptr(), e - b, bol[r]))
+        fsh = buf.size > 0 and buf[0] in (0x3E, 0x3B)
+        chain = kb.fasta_chain(summ, bol, fsh)
+        for r in range(parts):
+            b, e = cuts[r], cuts[r + 1]
+            assert (chain[r][0], (chain[r][1] >> 1) & 1, bool(chain[r][1] & 1)) == ou.fasta_prefix_state(buf, b), (r, cuts)
+            cap = max(e - b, 1)
+            keys = torch.zeros(cap * nw, dtype=torch.int64, device="cuda")
+            ids = torch.zeros(cap, dtype=torch.int64, device="cuda")
+            n = idx.parse_fasta_dev(texts[r][0].data_ptr(), texts[r][1], keys.data_ptr(), cap, ids.data_ptr(),
+                                    block=(b, e - b, chain[r][0], chain[r][1]))
+            torch.cuda.synchronize()
+            out.append((ou.shape_keys(host_u64(keys)[:n * nw].copy(), k), host_u64(ids)[:n].copy()))
+    return out
+
+
+@pytest.mark.parametrize("name,k", [("test2.fasta", 21), ("test.fasta", 35), ("natural.withN.fasta", 21), ("test.medium.fasta", 21),
+                                    ("test.unitiqs.fasta", 63)])
+def test_fasta_blocks_match_oracle(name, k):
+    """Row a6: every block of a file cut at arbitrary bytes (inside headers, inside lines, empty blocks) emits exactly the
+    reference's tuples for that valid range — global sequence ids, file-offset positions, windows running K-1 bases on."""
+    buf = ou.read_fixture(name)
+    rng = np.random.default_rng(len(name) + k)
+    for parts in (2, 3, 7):
+        cuts = [0] + sorted(int(x) for x in rng.integers(0, buf.size + 1, size=parts - 1)) + [int(buf.size)]
+        if parts == 3:
+            cuts[2] = cuts[1]   # an empty block in the middle
+        for nsplit in ((False, True) if parts == 3 else (False,)):
+            got = _fasta_blocks_gpu(buf, k, cuts, nsplit)
+            total = 0
+            for r in range(parts):
+                wk, wi = ou.fasta_block_kmers(buf, k, cuts[r], cuts[r + 1], nsplit=nsplit)
+                a, b = ou.sort_tuples(got[r][0], got[r][1], k)
+                c, d = ou.sort_tuples(wk, wi, k)
+                assert len(got[r][0]) == len(wk), (name, parts, r, cuts)
+                assert np.array_equal(a, c) and np.array_equal(b, d), (name, parts, r, cuts)
+                total += len(wk)
+            assert total == len(ou.fasta_kmers(buf, k, nsplit=nsplit)[0])
+
+
+def test_fasta_blocks_edge_cuts():
+    """cuts right after '>' / inside a header run / before an EOL, on a file with comment lines, CRLF and blank lines"""
+    c = (b"ACGT\n>s1 desc\n;more\nACGTACGTTG\nGTACGTAAGT\r\nACGTACGTACGTAAC\n\n;c\n>s2\nTTTTTGTTTTTTTCTTTTTTTTATTTTT\n>s3\n"
+         + b"ACGTTGCA" * 1200 + b"\n")
+    buf = np.frombuffer(c, dtype=np.uint8)
+    k = 15
+    whole = len(ou.fasta_kmers(buf, k)[0])
+    for cuts in ([0, 6, 7, 16, 22, int(buf.size)], [0, 5, 5, 5, int(buf.size)], [0, 23, 34, 35, 46, 64, 70, 75, 5000, 5001, int(buf.size)]):
+        got = _fasta_blocks_gpu(buf, k, cuts)
+        n = 0
+        for r in range(len(cuts) - 1):
+            wk, wi = ou.fasta_block_kmers(buf, k, cuts[r], cuts[r + 1])
+            a, b = ou.sort_tuples(got[r][0], got[r][1], k)
+            c2, d = ou.sort_tuples(wk, wi, k)
+            assert np.array_equal(a, c2) and np.array_equal(b, d), (cuts, r)
+            n += len(wk)
+        assert n == whole
+
+
 def test_fasta_edge_cases():
     cases = [b"", b"ACGT\n", b">h\n", b">h", b"ACGT\n>s1\nACGTAC\nGTACGT\r\nACGTACGTACGTAAC\n;c\n>s2\nTTTTTTTTTTTTTTTTTTTTTTTTT",
              b">a\n" + b"ACGTTGCA" * 700 + b"\n>b\n\n\n" + b"GATTACA" * 3 + b"\n" + b"C" * 5000,

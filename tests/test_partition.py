@@ -76,3 +76,60 @@ def test_cuts_partition_the_kmers(parts):
         n_reads += r
     assert n_reads == reads
     assert np.array_equal(np.sort(np.concatenate(got)), np.sort(whole))
+
+
+# ---- FASTA blocks (row a6): host side of the cross-block scan and of the K-1 tail ------------------------------------
+def block_summary(block, bol):
+    """numpy restatement of what kmi_fasta_block_summary_dev reports for a block's own bytes"""
+    b = block.tobytes()
+    starts = ([0] if bol and len(b) else []) + [i + 1 for i in range(len(b) - 1) if b[i] == 0x0A]
+    kinds = [1 if b[s] in (0x3E, 0x3B) else 0 for s in starts]
+    runs, prev = 0, 0
+    for kd in kinds:
+        if kd and not prev:
+            runs += 1
+        prev = kd
+    return (1 if starts else 0, kinds[0] if starts else 0, kinds[-1] if starts else 0, runs)
+
+
+@pytest.mark.parametrize("name", ("test2.fasta", "test.fasta", "natural.withN.fasta"))
+def test_fasta_chain_reproduces_the_prefix_state(name):
+    buf = ou.read_fixture(name)
+    rng = np.random.default_rng(5)
+    fsh = buf[0] in (0x3E, 0x3B)
+    for parts in (1, 2, 5, 16):
+        cuts = [0] + sorted(int(x) for x in rng.integers(0, buf.size + 1, size=parts - 1)) + [int(buf.size)]
+        bol = [c == 0 or buf[c - 1] == 0x0A for c in cuts[:-1]]
+        summ = [block_summary(buf[a:b], bl) for a, b, bl in zip(cuts, cuts[1:], bol)]
+        chain = kb.fasta_chain(summ, bol, fsh)
+        for r, c in enumerate(cuts[:-1]):
+            runs0, flags = chain[r]
+            assert (runs0, (flags >> 1) & 1, bool(flags & 1)) == ou.fasta_prefix_state(buf, c), (name, cuts, r)
+            assert bool(flags & kb.FASTA_FILE_STARTS_WITH_HEADER) == bool(fsh)
+
+
+def test_fasta_halo_end_counts_non_eol_bytes():
+    buf = np.frombuffer(b">h\nACGT\r\nAC\n\nGTTT\n>g\nAAAA", dtype=np.uint8)
+    n = buf.size
+    for k in (1, 2, 5, 8, 40):
+        for e in range(n + 1):
+            p, need = e, k - 1
+            while p < n and need > 0:
+                if buf[p] not in (0x0A, 0x0D):
+                    need -= 1
+                p += 1
+            assert kb.fasta_halo_end(buf, e, k) == p, (k, e)
+    # a window of the file in memory: offsets stay file offsets
+    assert kb.fasta_halo_end(buf[3:], 100 + 4, 3, mem_offset=100) == 100 + 8   # \\r \\n skipped, then A C
+    with pytest.raises(kb.KmiError):
+        kb.fasta_halo_end(buf, n + 1, 3)
+
+
+def test_fasta_blocks_oracle_partition():
+    """the oracle's per-block tuples (first base in the valid range) partition the whole file's"""
+    buf = ou.read_fixture("test.fasta")
+    wk, wi, _ = ou.fasta_kmers(buf, 21)
+    cuts = [0, 100, 101, 5000, int(buf.size)]
+    parts = [ou.fasta_block_kmers(buf, 21, a, b) for a, b in zip(cuts, cuts[1:])]
+    assert sum(len(p[0]) for p in parts) == len(wk)
+    assert np.array_equal(np.sort(np.concatenate([p[1] for p in parts])), np.sort(wi))
