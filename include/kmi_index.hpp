@@ -87,6 +87,19 @@ struct Kmer {
       data[0] = (data[0] << 2) | (code & 3);
     }
   }
+  /// 2-bit code of base i (0 = first base = most significant used bits)
+  uint8_t base(unsigned i) const {
+    const unsigned bit = 2 * (K_ - 1 - i);
+    return (uint8_t)((data[bit >> 6] >> (bit & 63)) & 3);
+  }
+  /// Kmer::reverse_complement (kmer.hpp:1118-1123): DNA complement = 3 - code
+  Kmer reverse_complement() const {
+    Kmer r;
+    for (unsigned i = 0; i < K_; ++i) r.nextFromChar((uint8_t)(3 - base(K_ - 1 - i)));
+    return r;
+  }
+  /// lex_less (kmer_transform.hpp:109-126): the smaller of the k-mer and its reverse complement
+  Kmer canonical() const { Kmer r = reverse_complement(); return r < *this ? r : *this; }
   bool operator==(const Kmer& o) const { return std::memcmp(data, o.data, sizeof(data)) == 0; }
   bool operator<(const Kmer& o) const {
     for (int i = (int)nWords - 1; i >= 0; --i) if (data[i] != o.data[i]) return data[i] < o.data[i];
@@ -129,7 +142,7 @@ class b200_map {
   using const_iterator = typename std::vector<value_type>::const_iterator;
   static constexpr unsigned K = Key::size;
 
-  explicit b200_map(const comm& c = comm(), const map_options& o = map_options()) : comm_(c) {
+  explicit b200_map(const comm& c = comm(), const map_options& o = map_options()) : comm_(c), canonical_(o.canonical) {
     kmi_config cfg;
     cfg.k = (int32_t)K; cfg.mode = Mode; cfg.canonical = o.canonical ? 1 : 0; cfg.hash = o.hash; cfg.nsplit = o.nsplit ? 1 : 0;
     cfg.device = o.device; cfg.rank = c.rank(); cfg.nranks = c.size(); cfg.reserve = o.reserve;
@@ -157,29 +170,34 @@ class b200_map {
     check(kmi_insert(h_, k.data(), Mode == KMI_MODE_POSITION ? v.data() : nullptr, tuples.size()));
     return tuples.size();
   }
-  /// find: COUNT -> (key, frequency) for hits; POSITION -> every (key, id) of every hit — :327-448
+  /// find: COUNT -> (key, frequency) for hits; POSITION -> every (key, id) of every hit — :327-448. As in the reference the
+  /// query vector is transformed in place (canonical keys, distributed_map_base.hpp:286-289) and results carry those keys.
   std::vector<value_type> find(std::vector<Key>& keys) const {
+    std::vector<uint64_t> off, vals;
+    lookup(keys, off, vals);
     std::vector<value_type> out;
-    const uint64_t* kp = reinterpret_cast<const uint64_t*>(keys.data());
-    if (Mode == KMI_MODE_COUNT) {
-      std::vector<uint64_t> vals(keys.size());
-      std::vector<uint8_t> found(keys.size());
-      check(kmi_find(h_, kp, keys.size(), vals.data(), found.data()));
-      for (size_t i = 0; i < keys.size(); ++i) if (found[i]) out.emplace_back(keys[i], from_u64(vals[i]));
-    } else {
-      std::vector<uint64_t> cnt(keys.size()), off(keys.size() + 1);
-      check(kmi_count(h_, kp, keys.size(), cnt.data()));
-      uint64_t total = 0;
-      for (uint64_t c : cnt) total += c;
-      std::vector<uint64_t> vals(total ? total : 1);
-      check(kmi_find_positions(h_, kp, keys.size(), off.data(), vals.data(), total));
-      for (size_t i = 0; i < keys.size(); ++i)
-        for (uint64_t j = off[i]; j < off[i + 1]; ++j) out.emplace_back(keys[i], from_u64(vals[j]));
-    }
+    out.reserve(vals.size());
+    for (size_t i = 0; i < keys.size(); ++i)
+      for (uint64_t j = off[i]; j < off[i + 1]; ++j) out.emplace_back(keys[i], from_u64(vals[j]));
+    return out;
+  }
+  /// find(keys, sorted_input, pred) — kmer_index.hpp:159: hits whose (key, value) satisfies the predicate
+  template <typename Pred>
+  std::vector<value_type> find(std::vector<Key>& keys, bool /*sorted_input*/, const Pred& pred) const {
+    std::vector<value_type> out = find(keys);
+    out.erase(std::remove_if(out.begin(), out.end(), [&](const value_type& v) { return !pred(v); }), out.end());
+    return out;
+  }
+  /// find(pred) — kmer_index.hpp:171: every local entry that satisfies the predicate
+  template <typename Pred>
+  std::vector<value_type> find(const Pred& pred) const {
+    std::vector<value_type> out = to_vector();
+    out.erase(std::remove_if(out.begin(), out.end(), [&](const value_type& v) { return !pred(v); }), out.end());
     return out;
   }
   /// count: one (key, size_t) per query, zeros included — LocalCount, :234-266
   std::vector<std::pair<Key, size_t>> count(std::vector<Key>& keys) const {
+    transform_input(keys);
     std::vector<uint64_t> cnt(keys.size());
     check(kmi_count(h_, reinterpret_cast<const uint64_t*>(keys.data()), keys.size(), cnt.data()));
     std::vector<std::pair<Key, size_t>> out;
@@ -187,10 +205,75 @@ class b200_map {
     for (size_t i = 0; i < keys.size(); ++i) out.emplace_back(keys[i], (size_t)cnt[i]);
     return out;
   }
+  /// count(keys, sorted_input, pred) — kmer_index.hpp:177: per query, how many of its entries satisfy the predicate
+  template <typename Pred>
+  std::vector<std::pair<Key, size_t>> count(std::vector<Key>& keys, bool /*sorted_input*/, const Pred& pred) const {
+    std::vector<uint64_t> off, vals;
+    lookup(keys, off, vals);
+    std::vector<std::pair<Key, size_t>> out;
+    out.reserve(keys.size());
+    for (size_t i = 0; i < keys.size(); ++i) {
+      size_t c = 0;
+      for (uint64_t j = off[i]; j < off[i + 1]; ++j) c += pred(value_type(keys[i], from_u64(vals[j]))) ? 1 : 0;
+      out.emplace_back(keys[i], c);
+    }
+    return out;
+  }
+  /// count(pred) — kmer_index.hpp:182: for every local key, how many of its entries satisfy the predicate
+  template <typename Pred>
+  std::vector<std::pair<Key, size_t>> count(const Pred& pred) const {
+    std::vector<value_type> all = to_vector();
+    std::sort(all.begin(), all.end(), [](const value_type& a, const value_type& b) { return a.first < b.first; });
+    std::vector<std::pair<Key, size_t>> out;
+    for (size_t i = 0; i < all.size(); ++i) {
+      if (i == 0 || !(all[i].first == all[i - 1].first)) out.emplace_back(all[i].first, 0);
+      out.back().second += pred(all[i]) ? 1 : 0;
+    }
+    return out;
+  }
+  /// erase(keys): every entry of the keys — :1602-1663
   size_t erase(std::vector<Key>& keys) {
+    transform_input(keys);
     uint64_t before = local_size();
     check(kmi_erase(h_, reinterpret_cast<const uint64_t*>(keys.data()), keys.size()));
     return (size_t)(before - local_size());
+  }
+  /// erase(keys, sorted_input, pred) — kmer_index.hpp:188: the entries of the keys that satisfy the predicate (for the
+  /// multimap, single values leave a key: densehash_map.hpp:2267-2328). The key's entries are read, the key is erased,
+  /// and the survivors go back in.
+  template <typename Pred>
+  size_t erase(std::vector<Key>& keys, bool /*sorted_input*/, const Pred& pred) {
+    transform_input(keys);
+    std::sort(keys.begin(), keys.end());
+    keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
+    std::vector<uint64_t> off, vals;
+    lookup(keys, off, vals);
+    std::vector<Key> gone;
+    std::vector<value_type> back;
+    size_t removed = 0;
+    for (size_t i = 0; i < keys.size(); ++i) {
+      size_t hit = 0;
+      for (uint64_t j = off[i]; j < off[i + 1]; ++j) hit += pred(value_type(keys[i], from_u64(vals[j]))) ? 1 : 0;
+      if (!hit) continue;
+      removed += hit;
+      gone.push_back(keys[i]);
+      for (uint64_t j = off[i]; j < off[i + 1]; ++j) {
+        value_type v(keys[i], from_u64(vals[j]));
+        if (!pred(v)) back.push_back(v);
+      }
+    }
+    if (!gone.empty()) check(kmi_erase(h_, reinterpret_cast<const uint64_t*>(gone.data()), gone.size()));
+    if (!back.empty()) insert(back);
+    return removed;
+  }
+  /// erase(pred) — kmer_index.hpp:193: every local entry that satisfies the predicate
+  template <typename Pred>
+  size_t erase(const Pred& pred) {
+    std::vector<value_type> all = to_vector();
+    std::vector<Key> keys;
+    keys.reserve(all.size());
+    for (const value_type& v : all) keys.push_back(v.first);
+    return erase(keys, false, pred);
   }
   void reserve(size_t n) { check(kmi_reserve(h_, n)); }
   void clear() { check(kmi_clear(h_)); }
@@ -213,7 +296,7 @@ class b200_map {
     out.reserve(got);
     for (size_t i = 0; i < got; ++i) {
       Key key;
-      std::memcpy(&key, &k[i * nw()], sizeof(Key));
+      std::memcpy(key.data, &k[i * nw()], sizeof(Key));
       out.emplace_back(key, from_u64(v[i]));
     }
   }
@@ -249,11 +332,40 @@ class b200_map {
 
  private:
   static constexpr size_t nw() { return sizeof(Key) / 8; }
+  /// distributed_map_base::transform_input (distributed_map_base.hpp:286-289): queries become canonical in place
+  void transform_input(std::vector<Key>& keys) const {
+    if (canonical_) for (Key& k : keys) k = k.canonical();
+  }
+  /// per query key i its values vals[off[i] .. off[i+1]): COUNT 0 or 1 value (the frequency), POSITION every id
+  void lookup(std::vector<Key>& keys, std::vector<uint64_t>& off, std::vector<uint64_t>& vals) const {
+    transform_input(keys);
+    const uint64_t* kp = reinterpret_cast<const uint64_t*>(keys.data());
+    off.assign(keys.size() + 1, 0);
+    if (Mode == KMI_MODE_COUNT) {
+      std::vector<uint64_t> v(keys.size());
+      std::vector<uint8_t> found(keys.size());
+      check(kmi_find(h_, kp, keys.size(), v.data(), found.data()));
+      vals.clear();
+      for (size_t i = 0; i < keys.size(); ++i) {
+        if (found[i]) vals.push_back(v[i]);
+        off[i + 1] = vals.size();
+      }
+    } else {
+      std::vector<uint64_t> cnt(keys.size());
+      check(kmi_count(h_, kp, keys.size(), cnt.data()));
+      uint64_t total = 0;
+      for (uint64_t c : cnt) total += c;
+      vals.assign(total ? total : 1, 0);
+      check(kmi_find_positions(h_, kp, keys.size(), off.data(), vals.data(), total));
+      vals.resize(total);
+    }
+  }
   static T from_u64(uint64_t v) { T t; std::memset(&t, 0, sizeof(T)); std::memcpy(&t, &v, sizeof(T) < 8 ? sizeof(T) : 8); return t; }
   static bool ends_with(const std::string& s, const std::string& e) {
     return s.size() >= e.size() && s.compare(s.size() - e.size(), e.size(), e) == 0;
   }
   comm comm_;
+  bool canonical_ = true;
   kmi_index* h_ = nullptr;
   mutable std::vector<value_type> snapshot_;
 };

@@ -1,0 +1,225 @@
+// Drives the C++ adapter (include/kmi_index.hpp) the way the reference's container tests drive its maps
+// (src/containers/test/test_densehash_map.cpp:100-762: every operation checked against a std:: container), for the member
+// set Index<MapType,KmerParser> forwards to (kmer_index.hpp:134-194): insert / find / count / erase, each also with a
+// predicate, and to_vector / size. Needs a GPU; exits 0 when every check holds.
+#include <cstdio>
+#include <map>
+#include <random>
+#include <vector>
+
+#include "kmi_index.hpp"
+
+#define CHECK(c)                                                     \
+  do {                                                               \
+    if (!(c)) {                                                      \
+      std::printf("FAIL %s:%d: %s\n", __FILE__, __LINE__, #c);       \
+      return 1;                                                      \
+    }                                                                \
+  } while (0)
+
+template <unsigned K>
+static kmi::Kmer<K> random_kmer(std::mt19937_64& rng) {
+  kmi::Kmer<K> k;
+  for (unsigned i = 0; i < K; ++i) k.nextFromChar((uint8_t)(rng() & 3));
+  return k;
+}
+
+template <typename Pair>
+static void sort_pairs(std::vector<Pair>& v) {
+  std::sort(v.begin(), v.end(), [](const Pair& a, const Pair& b) { return a.first < b.first || (a.first == b.first && a.second < b.second); });
+}
+
+template <unsigned K>
+static int count_checks() {
+  using Key = kmi::Kmer<K>;
+  using Map = kmi::CountIndex<K>;
+  using V = typename Map::value_type;
+  std::mt19937_64 rng(K);
+  std::vector<Key> pool;
+  for (int i = 0; i < 3000; ++i) pool.push_back(random_kmer<K>(rng));
+  std::vector<Key> input;
+  for (int i = 0; i < 20000; ++i) {
+    Key k = pool[(rng() % 3000) * (rng() % 3000) / 3000];   // skewed multiplicities
+    input.push_back((rng() & 1) ? k : k.reverse_complement());
+  }
+  std::map<Key, uint32_t> want;
+  for (const Key& k : input) want[k.canonical()]++;
+  kmi::map_options o;
+  o.hash = KMI_HASH_FARM;
+  Map idx(kmi::comm(), o);
+  idx.insert(input);
+  CHECK(idx.local_size() == want.size() && idx.size() == want.size());
+  CHECK(idx.get_multiplicity() == 1.0f);
+  std::vector<V> all = idx.to_vector();
+  sort_pairs(all);
+  CHECK(all.size() == want.size());
+  {
+    size_t i = 0;
+    for (const auto& kv : want) { CHECK(all[i].first == kv.first && all[i].second == kv.second); ++i; }
+  }
+  // queries: every pool key in a random orientation + keys that are (almost surely) absent
+  std::vector<Key> q;
+  for (const Key& k : pool) q.push_back((rng() & 1) ? k : k.reverse_complement());
+  for (int i = 0; i < 500; ++i) q.push_back(random_kmer<K>(rng));
+  {
+    std::vector<Key> qq = q;
+    std::vector<V> got = idx.find(qq);
+    size_t hits = 0;
+    for (const Key& k : q) hits += want.count(k.canonical());
+    CHECK(got.size() == hits);
+    for (const V& v : got) CHECK(want.count(v.first) && want[v.first] == v.second);   // canonical keys come back
+    qq = q;
+    auto cnt = idx.count(qq);
+    CHECK(cnt.size() == q.size());
+    for (size_t i = 0; i < q.size(); ++i) CHECK(cnt[i].first == q[i].canonical() && cnt[i].second == want.count(q[i].canonical()));
+  }
+  auto often = [](const V& v) { return v.second >= 3; };
+  {
+    std::vector<Key> qq = q;
+    std::vector<V> got = idx.find(qq, false, often);
+    size_t hits = 0;
+    for (const Key& k : q) { auto it = want.find(k.canonical()); hits += (it != want.end() && it->second >= 3) ? 1 : 0; }
+    CHECK(got.size() == hits);
+    for (const V& v : got) CHECK(v.second >= 3 && want[v.first] == v.second);
+    std::vector<V> every = idx.find(often);
+    size_t n3 = 0;
+    for (const auto& kv : want) n3 += kv.second >= 3 ? 1 : 0;
+    CHECK(every.size() == n3);
+    qq = q;
+    auto cnt = idx.count(qq, false, often);
+    for (size_t i = 0; i < q.size(); ++i) {
+      auto it = want.find(q[i].canonical());
+      CHECK(cnt[i].second == ((it != want.end() && it->second >= 3) ? 1u : 0u));
+    }
+    auto per_key = idx.count(often);
+    CHECK(per_key.size() == want.size());
+    size_t s = 0;
+    for (const auto& kc : per_key) s += kc.second;
+    CHECK(s == n3);
+  }
+  // erase with a predicate on half of the queries, then by predicate over the whole map, then plain
+  {
+    std::vector<Key> half(q.begin(), q.begin() + q.size() / 2);
+    size_t expect = 0;
+    for (const Key& k : half) {
+      auto it = want.find(k.canonical());
+      if (it != want.end() && it->second >= 3) { want.erase(it); ++expect; }
+    }
+    CHECK(idx.erase(half, false, often) == expect);
+    CHECK(idx.local_size() == want.size());
+    auto single = [](const V& v) { return v.second == 1; };
+    expect = 0;
+    for (auto it = want.begin(); it != want.end();) {
+      if (it->second == 1) { it = want.erase(it); ++expect; } else ++it;
+    }
+    CHECK(idx.erase(single) == expect);
+    CHECK(idx.local_size() == want.size());
+    std::vector<Key> some(q.begin() + q.size() / 2, q.begin() + q.size() / 2 + 300);
+    expect = 0;
+    for (const Key& k : some) expect += want.erase(k.canonical());
+    CHECK(idx.erase(some) == expect);
+    all = idx.to_vector();
+    sort_pairs(all);
+    CHECK(all.size() == want.size());
+    size_t i = 0;
+    for (const auto& kv : want) { CHECK(all[i].first == kv.first && all[i].second == kv.second); ++i; }
+  }
+  return 0;
+}
+
+template <unsigned K>
+static int position_checks() {
+  using Key = kmi::Kmer<K>;
+  using Map = kmi::PositionIndex<K>;
+  using V = typename Map::value_type;
+  std::mt19937_64 rng(100 + K);
+  std::vector<Key> pool;
+  for (int i = 0; i < 2000; ++i) pool.push_back(random_kmer<K>(rng));
+  std::vector<V> tuples;
+  for (int i = 0; i < 12000; ++i) {
+    Key k = pool[(rng() % 2000) * (rng() % 2000) / 2000];
+    tuples.emplace_back((rng() & 1) ? k : k.reverse_complement(), (uint64_t)(rng() % 64));   // few ids: (key, id) repeats happen
+  }
+  std::vector<V> want;
+  for (const V& t : tuples) want.emplace_back(t.first.canonical(), t.second);
+  sort_pairs(want);
+  Map idx;
+  idx.insert(tuples);
+  CHECK(idx.local_size() == want.size());       // duplicates are all kept (densehash_map.hpp:2190-2249)
+  std::vector<V> all = idx.to_vector();
+  sort_pairs(all);
+  CHECK(all == want);
+  std::map<Key, std::vector<uint64_t>> by_key;
+  for (const V& t : want) by_key[t.first].push_back(t.second);
+  CHECK(idx.get_multiplicity() == (float)want.size() / (float)by_key.size());
+  std::vector<Key> q;
+  for (int i = 0; i < 500; ++i) q.push_back(pool[rng() % 2000].reverse_complement());
+  for (int i = 0; i < 100; ++i) q.push_back(random_kmer<K>(rng));
+  {
+    std::vector<Key> qq = q;
+    std::vector<V> got = idx.find(qq), expect;
+    for (const Key& k : q) {
+      auto it = by_key.find(k.canonical());
+      if (it != by_key.end()) for (uint64_t v : it->second) expect.emplace_back(it->first, v);
+    }
+    sort_pairs(got); sort_pairs(expect);
+    CHECK(got == expect);
+    qq = q;
+    auto cnt = idx.count(qq);
+    for (size_t i = 0; i < q.size(); ++i) {
+      auto it = by_key.find(q[i].canonical());
+      CHECK(cnt[i].second == (it == by_key.end() ? 0 : it->second.size()));
+    }
+    auto odd = [](const V& v) { return (v.second & 1) != 0; };
+    qq = q;
+    auto codd = idx.count(qq, false, odd);
+    for (size_t i = 0; i < q.size(); ++i) {
+      auto it = by_key.find(q[i].canonical());
+      size_t c = 0;
+      if (it != by_key.end()) for (uint64_t v : it->second) c += v & 1;
+      CHECK(codd[i].second == c);
+    }
+    // erase the odd ids of the queried keys: single values leave their key
+    size_t removed = 0;
+    std::vector<Key> uq;
+    for (const Key& k : q) uq.push_back(k.canonical());
+    std::sort(uq.begin(), uq.end());
+    uq.erase(std::unique(uq.begin(), uq.end()), uq.end());
+    for (const Key& k : uq) {
+      auto it = by_key.find(k);
+      if (it == by_key.end()) continue;
+      std::vector<uint64_t> keep;
+      for (uint64_t v : it->second) { if (v & 1) ++removed; else keep.push_back(v); }
+      if (keep.empty()) by_key.erase(it); else it->second.swap(keep);
+    }
+    qq = q;
+    CHECK(idx.erase(qq, false, odd) == removed);
+    want.clear();
+    for (const auto& kv : by_key) for (uint64_t v : kv.second) want.emplace_back(kv.first, v);
+    sort_pairs(want);
+    all = idx.to_vector();
+    sort_pairs(all);
+    CHECK(all == want);
+    // then every id below 8 anywhere in the map
+    auto low = [](const V& v) { return v.second < 8; };
+    removed = 0;
+    for (const V& t : want) removed += t.second < 8 ? 1 : 0;
+    CHECK(idx.erase(low) == removed);
+    want.erase(std::remove_if(want.begin(), want.end(), low), want.end());
+    all = idx.to_vector();
+    sort_pairs(all);
+    CHECK(all == want);
+    CHECK(idx.find(low).empty());
+  }
+  return 0;
+}
+
+int main() {
+  if (count_checks<21>()) return 1;
+  if (count_checks<31>()) return 1;
+  if (count_checks<63>()) return 1;
+  if (position_checks<21>()) return 1;
+  if (position_checks<35>()) return 1;
+  std::printf("adapter ok\n");
+  return 0;
+}

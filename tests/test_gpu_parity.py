@@ -556,3 +556,17 @@ def test_bucketed_build_survives_key_skew(frac):
         idx.insert(keys)
         gk, gc = idx.sorted_dump()
         assert np.array_equal(gk, wk) and np.array_equal(gc, wc)
+
+
+def test_cpp_adapter_against_std_containers(tmp_path):
+    """The header-only MapType (include/kmi_index.hpp) — insert / find / count / erase, each with and without a predicate,
+    to_vector, size — against std::map brute force, in C++, the way the reference tests its maps
+    (src/containers/test/test_densehash_map.cpp)."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "adapter_check")
+    subprocess.check_call(["g++", "-std=c++11", "-O1", "-Wall", "-I", os.path.join(root, "include"),
+                           os.path.join(root, "tests", "cpp", "adapter_check.cpp"), kb.LIB_PATH, "-o", exe,
+                           "-Wl,-rpath," + os.path.dirname(kb.LIB_PATH)])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "adapter ok" in r.stdout, r.stdout + r.stderr
