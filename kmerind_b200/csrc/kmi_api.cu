@@ -1542,10 +1542,12 @@ static int fasta_scan(kmi_index* idx, const uint8_t* d_bytes, size_t n, FaBlock*
 
 // parse tiles [tile_begin, tile_begin + tiles) into the sink; retries with the wide halo when needed
 static int fasta_parse_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, const FaBlock& blk, u64 n_tiles_total, u64 tile_begin,
-                             u64 tiles, KeySink sink, u64* produced) {
+                             u64 tiles, KeySink sink, u64* produced, u64 cursor_start = 0) {
   FastaArrays a = fasta_arrays(idx, n_tiles_total);
+  static_assert(CTR_CURSOR == CTR_NKMERS + 1, "the two counters are set together");
   for (int attempt = 0; attempt < 2; ++attempt) {
-    OK(zero_ctr(idx, CTR_NKMERS, 2));
+    const u64 init[2] = {0, cursor_start};   // output is appended at cursor_start
+    CU(cudaMemcpyAsync(idx->ctr + CTR_NKMERS, init, sizeof(init), cudaMemcpyHostToDevice, idx->stream));
     OK(zero_ctr(idx, CTR_PERR));
     idx->ops->fasta_kmers(idx->stream, attempt == 1, d_bytes, n, tiles, a.enc, a.enc_max, a.runs, a.runs_sums, sink, idx->ctr + CTR_NKMERS,
                           reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0, idx->cfg.nsplit != 0, tile_begin, blk);
@@ -1560,15 +1562,8 @@ static int fasta_parse_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, c
   return KMI_OK;
 }
 
-extern "C" int kmi_fasta_block_summary_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n_valid, int bol, uint32_t* out) {
-  if (!idx || (!d_bytes && n_valid) || !out) return fail(KMI_ERR_ARG, "null argument");
-  CU(cudaSetDevice(idx->cfg.device));
-  out[0] = out[1] = out[2] = out[3] = 0;
-  FaBlock blk = whole_file_block(n_valid);
-  blk.bol = bol ? 1u : 0u; blk.first_is_header = 0;
-  u64 n_tiles = 0;
-  OK(fasta_scan(idx, d_bytes, n_valid, &blk, &n_tiles));
-  if (n_tiles == 0) return KMI_OK;
+// read a scanned block's totals off the sentinel entries (valid after fasta_scan on the same stream)
+static int fasta_read_summary(kmi_index* idx, u64 n_tiles, u32* out) {
   FastaArrays a = fasta_arrays(idx, n_tiles);
   u32 enc = 0, enc_b = 0, runs = 0, runs_b = 0;
   u64 first = 0;
@@ -1579,10 +1574,23 @@ extern "C" int kmi_fasta_block_summary_dev(kmi_index* idx, const uint8_t* d_byte
   CU(cudaMemcpyAsync(&first, idx->ctr + CTR_FIRST_LS, 8, cudaMemcpyDeviceToHost, idx->stream));
   CU(cudaStreamSynchronize(idx->stream));
   const u32 last = std::max(enc, enc_b);
-  out[0] = last ? 1u : 0u;                                   // the block holds a line start
+  out[0] = last ? 1u : 0u;                                     // the block holds a line start
   out[1] = (last && first != ~0ULL) ? (u32)(first & 1u) : 0u;  // its first line start begins a header line
-  out[2] = last & 1u;                                        // its last one does
-  out[3] = runs + runs_b;                                    // header runs starting in the block if the line before it is no header
+  out[2] = last & 1u;                                          // its last one does
+  out[3] = runs + runs_b;                                      // header runs starting in the block, given the kind0 it was scanned with
+  return KMI_OK;
+}
+
+extern "C" int kmi_fasta_block_summary_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n_valid, int bol, uint32_t* out) {
+  if (!idx || (!d_bytes && n_valid) || !out) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  out[0] = out[1] = out[2] = out[3] = 0;
+  FaBlock blk = whole_file_block(n_valid);
+  blk.bol = bol ? 1u : 0u; blk.first_is_header = 0;
+  u64 n_tiles = 0;
+  OK(fasta_scan(idx, d_bytes, n_valid, &blk, &n_tiles));
+  if (n_tiles == 0) return KMI_OK;
+  OK(fasta_read_summary(idx, n_tiles, out));
   return KMI_OK;
 }
 
@@ -1608,18 +1616,16 @@ extern "C" int kmi_parse_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_
   return kmi_parse_fasta_block_dev(idx, d_bytes, n, nullptr, d_keys, d_ids, cap, n_kmers);
 }
 
-extern "C" int kmi_build_fasta_block_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, const kmi_fasta_block* block,
-                                         uint64_t* n_kmers) {
-  if (!idx || (!d_bytes && n)) return fail(KMI_ERR_ARG, "null argument");
-  CU(cudaSetDevice(idx->cfg.device));
-  if (n_kmers) *n_kmers = 0;
-  FaBlock blk;
-  OK(fasta_block_from_abi(block, n, &blk));
+// scan + parse + insert of one block whose bytes are resident; summary (optional) = the block's totals for chaining
+static int fasta_build_block(kmi_index* idx, const uint8_t* d_bytes, size_t n, FaBlock blk, u64* n_kmers, u32* summary,
+                             float* scan_ms, float* parse_ms_out) {
   u64 n_tiles = 0;
   CU(cudaEventRecord(idx->ev[0], idx->stream));
   OK(fasta_scan(idx, d_bytes, n, &blk, &n_tiles));
   CU(cudaEventRecord(idx->ev[1], idx->stream));
+  if (summary) { summary[0] = summary[1] = summary[2] = summary[3] = 0; }
   if (n_tiles == 0) return KMI_OK;
+  if (summary) OK(fasta_read_summary(idx, n_tiles, summary));
   // bounded staging: at most CHUNK_TILES tiles of text become keys (+ids) at a time
   const u64 CHUNK_TILES = 65536;  // 256 MiB of text -> <= 256 Mi k-mers (4 GiB of key + id staging): every chunk costs one sweep of the table
   const bool pos = idx->cfg.mode == KMI_MODE_POSITION;
@@ -1655,9 +1661,25 @@ extern "C" int kmi_build_fasta_block_dev(kmi_index* idx, const uint8_t* d_bytes,
     total += produced;
   }
   if (r != KMI_OK) return r;
-  cudaEventElapsedTime(&idx->stage_ms[0], idx->ev[0], idx->ev[1]);
-  idx->stage_ms[1] = parse_ms;
-  idx->stage_ms[2] = 0;
+  float sm = 0;
+  cudaEventElapsedTime(&sm, idx->ev[0], idx->ev[1]);
+  *scan_ms += sm;
+  *parse_ms_out += parse_ms;
+  *n_kmers += total;
+  return KMI_OK;
+}
+
+extern "C" int kmi_build_fasta_block_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, const kmi_fasta_block* block,
+                                         uint64_t* n_kmers) {
+  if (!idx || (!d_bytes && n)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  if (n_kmers) *n_kmers = 0;
+  FaBlock blk;
+  OK(fasta_block_from_abi(block, n, &blk));
+  u64 total = 0;
+  float scan_ms = 0, parse_ms = 0;
+  OK(fasta_build_block(idx, d_bytes, n, blk, &total, nullptr, &scan_ms, &parse_ms));
+  idx->stage_ms[0] = scan_ms; idx->stage_ms[1] = parse_ms; idx->stage_ms[2] = 0;
   if (n_kmers) *n_kmers = total;
   return check_table_error(idx);
 }
@@ -1665,13 +1687,90 @@ extern "C" int kmi_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_
   return kmi_build_fasta_block_dev(idx, d_bytes, n, nullptr, n_kmers);
 }
 
+// Host-pointer FASTA build: the text goes to the device in chunks on a copy stream, and chunk c is built as a BLOCK of the
+// file (its halo is chunk c+1, its inherited state the chained totals of the chunks before it) while chunks c+2.. are still
+// in flight, so the PCIe transfer hides behind the build (or the other way round).
 extern "C" int kmi_build_fasta_block(kmi_index* idx, const uint8_t* bytes, size_t n, const kmi_fasta_block* block,
                                     uint64_t* n_kmers) {
   if (!idx || (!bytes && n)) return fail(KMI_ERR_ARG, "null argument");
   CU(cudaSetDevice(idx->cfg.device));
+  if (n_kmers) *n_kmers = 0;
+  FaBlock base;
+  OK(fasta_block_from_abi(block, n, &base));
+  if (base.first_is_header == 2) base.first_is_header = (n && (bytes[0] == '>' || bytes[0] == ';')) ? 1u : 0u;
   OK(idx->stage_in.ensure(n + 64));
-  CU(cudaMemcpyAsync(idx->stage_in.p, bytes, n, cudaMemcpyHostToDevice, idx->stream));
-  return kmi_build_fasta_block_dev(idx, idx->stage_in.as<uint8_t>(), n, block, n_kmers);
+  uint8_t* d = idx->stage_in.as<uint8_t>();
+  // Text is staged into keys (+ids) one 256 MiB ROUND at a time (every round costs one sweep of the table when it is
+  // inserted); inside a round the copy and the parse go in CHUNKs of a quarter round, so only the first chunk's copy and the
+  // inserts are exposed. KMI_FASTA_CHUNK_BYTES overrides the chunk size, a round is then 4 chunks (tests).
+  const u64 ROUND_MAX = 256ull << 20;
+  u64 CHUNK = std::min<u64>(std::max<u64>(base.n_valid / 4, 8ull << 20), ROUND_MAX / 4);
+  if (const char* e = getenv("KMI_FASTA_CHUNK_BYTES")) CHUNK = std::max<u64>(strtoull(e, nullptr, 10), TILE_BYTES);
+  CHUNK = (CHUNK + TILE_BYTES - 1) / TILE_BYTES * TILE_BYTES;
+  const u64 ROUND = std::min<u64>(ROUND_MAX, 4 * CHUNK);
+  const u64 n_chunks = std::max<u64>((base.n_valid + CHUNK - 1) / CHUNK, 1);
+  if (!idx->copy_stream) CU(cudaStreamCreateWithFlags(&idx->copy_stream, cudaStreamNonBlocking));
+  CopyGuard guard{idx->copy_stream};
+  CU(cudaEventRecord(idx->ev[3], idx->stream));           // the staging buffer may still be in use by earlier work
+  CU(cudaStreamWaitEvent(idx->copy_stream, idx->ev[3], 0));
+  while (idx->copy_events.size() < n_chunks) {
+    cudaEvent_t e;
+    CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    idx->copy_events.push_back(e);
+  }
+  for (u64 c = 0; c < n_chunks; ++c) {   // the last copy takes the caller's halo along
+    const u64 b0 = c * CHUNK, b1 = (c + 1 == n_chunks) ? n : std::min<u64>(n, (c + 1) * CHUNK);
+    if (b1 > b0) CU(cudaMemcpyAsync(d + b0, bytes + b0, b1 - b0, cudaMemcpyHostToDevice, idx->copy_stream));
+    CU(cudaEventRecord(idx->copy_events[c], idx->copy_stream));
+  }
+  const bool pos = idx->cfg.mode == KMI_MODE_POSITION;
+  const u64 cap = std::min<u64>(ROUND, (base.n_valid + TILE_BYTES - 1) / TILE_BYTES * TILE_BYTES) + 1;
+  OK(idx->parse_keys.ensure(cap * sizeof(u64) * idx->nw));
+  if (pos) OK(idx->parse_ids.ensure(cap * sizeof(u64)));
+  auto flush = [&](u64 count) -> int {   // keys are already canonical: insert them as they are
+    if (count == 0) return KMI_OK;
+    int r;
+    if (pos) {
+      int32_t canon = idx->cfg.canonical;
+      idx->cfg.canonical = 0;
+      r = kmi_insert_dev(idx, idx->parse_keys.as<uint64_t>(), idx->parse_ids.as<uint64_t>(), count);
+      idx->cfg.canonical = canon;
+    } else {
+      r = insert_keys_chunked(idx, idx->parse_keys.as<u64>(), count, false);
+    }
+    return r;
+  };
+  u64 total = 0, staged = 0;
+  u32 runs = base.runs0, kind = base.kind0;
+  for (u64 c = 0; c < n_chunks; ++c) {
+    const u64 b0 = c * CHUNK;
+    const bool last = c + 1 == n_chunks;
+    FaBlock blk = base;
+    blk.file_offset = base.file_offset + b0;
+    blk.n_valid = std::min<u64>(CHUNK, base.n_valid - std::min<u64>(base.n_valid, b0));
+    blk.runs0 = runs; blk.kind0 = kind;
+    blk.bol = (c == 0) ? base.bol : (bytes[b0 - 1] == '\n' ? 1u : 0u);
+    const u64 avail = (last ? n : std::min<u64>(n, (c + 2) * CHUNK)) - b0;
+    if (staged + blk.n_valid > cap) { OK(flush(staged)); staged = 0; }
+    CU(cudaStreamWaitEvent(idx->stream, idx->copy_events[last ? c : c + 1], 0));   // own bytes + halo = the next chunk
+    u64 n_tiles = 0;
+    OK(fasta_scan(idx, d + b0, avail, &blk, &n_tiles));
+    if (n_tiles == 0) continue;
+    u32 sm[4];
+    OK(fasta_read_summary(idx, n_tiles, sm));
+    if (sm[0]) { runs += sm[3]; kind = sm[2]; }
+    KeySink sink;
+    sink.keys = idx->parse_keys.as<u64>(); sink.ids = pos ? idx->parse_ids.as<u64>() : nullptr; sink.cap = cap; sink.cursor = idx->ctr + CTR_CURSOR;
+    u64 produced = 0;
+    OK(fasta_parse_range(idx, d + b0, avail, blk, n_tiles, 0, n_tiles, sink, &produced, staged));
+    staged += produced;
+    total += produced;
+  }
+  OK(flush(staged));
+  CU(cudaStreamSynchronize(idx->stream));
+  idx->stage_ms[0] = 0; idx->stage_ms[1] = 0; idx->stage_ms[2] = 0;
+  if (n_kmers) *n_kmers = total;
+  return check_table_error(idx);
 }
 extern "C" int kmi_build_fasta(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t* n_kmers) {
   return kmi_build_fasta_block(idx, bytes, n, nullptr, n_kmers);

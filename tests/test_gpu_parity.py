@@ -284,6 +284,33 @@ def test_fasta_blocks_edge_cuts():
         assert n == whole
 
 
+@pytest.mark.parametrize("name,k,chunk", [("test.medium.fasta", 21, 4096), ("test.medium.fasta", 21, 40000), ("test.unitiqs.fasta", 63, 4096),
+                                          ("natural.withN.fasta", 21, 4096)])
+def test_fasta_host_build_in_chunks(name, k, chunk, monkeypatch):
+    """kmi_build_fasta from a host pointer streams the text in chunks and builds each chunk as a block of the file (halo = the
+    next chunk, inherited header runs / line kind chained): the position index equals the oracle's whole-file tuples."""
+    buf = ou.read_fixture(name)
+    wk, wi, _ = ou.fasta_kmers(buf, k)
+    swk, swi = ou.sort_tuples(wk, wi, k)
+    monkeypatch.setenv("KMI_FASTA_CHUNK_BYTES", str(chunk))
+    assert buf.size > 2 * chunk
+    with kb.PositionIndex(k) as idx:
+        assert idx.build_fasta(buf) == len(wk)
+        gk, gi = idx.sorted_dump()
+        assert np.array_equal(gk, swk) and np.array_equal(gi, swi)
+    # the same file as two host blocks (a rank's share each), every one streamed in chunks
+    cut = int(buf.size) // 3 + 5
+    he = kb.fasta_halo_end(buf, cut, k)
+    pre = ou.fasta_prefix_state(buf, cut)
+    fsh = kb.FASTA_FILE_STARTS_WITH_HEADER if buf[0] in (0x3E, 0x3B) else 0
+    with kb.PositionIndex(k) as idx:
+        n0 = idx.build_fasta(buf[:he], block=(0, cut, 0, kb.FASTA_BOL | fsh))
+        n1 = idx.build_fasta(buf[cut:], block=(cut, buf.size - cut, pre[0], (kb.FASTA_BOL if pre[2] else 0) | (kb.FASTA_PREV_HEADER if pre[1] else 0) | fsh))
+        assert n0 + n1 == len(wk)
+        gk, gi = idx.sorted_dump()
+        assert np.array_equal(gk, swk) and np.array_equal(gi, swi)
+
+
 def test_fasta_edge_cases():
     cases = [b"", b"ACGT\n", b">h\n", b">h", b"ACGT\n>s1\nACGTAC\nGTACGT\r\nACGTACGTACGTAAC\n;c\n>s2\nTTTTTTTTTTTTTTTTTTTTTTTTT",
              b">a\n" + b"ACGTTGCA" * 700 + b"\n>b\n\n\n" + b"GATTACA" * 3 + b"\n" + b"C" * 5000,

@@ -75,6 +75,17 @@ def fasta_positions(genome_bp, n_q):
     assert n[0] == n_kmers, (n[0], n_kmers)
     print("cfg5 shape: PositionIndex K=21, FASTA genome %.0f Mbp in %d sequences (%d k-mers, %d distinct keys): build %.2f ms = %.2f G k-mers/s"
           % (genome_bp / 1e6, n_seq, n[0], idx.num_keys(), ms, n[0] / ms / 1e6))
+    host = torch.from_numpy(buf).pin_memory()
+    hbuf = host.numpy()
+
+    def build_host():
+        idx.clear()
+        n[0] = idx.build_fasta(hbuf)
+    ms_h = timed(build_host, reps=2)
+    assert n[0] == n_kmers
+    print("            from pinned host memory (chunks streamed under the build): %.2f ms = %.2f G k-mers/s" % (ms_h, n[0] / ms_h / 1e6))
+    idx.clear()
+    idx.build_fasta_dev(text.data_ptr(), buf.size)
     # queries: half = k-mers that exist (parsed from the text itself), half random
     cap = n_kmers + 1024
     keys = torch.empty(cap, dtype=torch.int64, device="cuda")
