@@ -124,6 +124,14 @@ int kmi_build_fasta_block_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, 
  * valid_end, or n_file. `bytes` holds the file bytes [mem_offset, mem_offset + n). */
 int kmi_fasta_halo_end(const uint8_t* bytes, uint64_t mem_offset, size_t n, uint64_t valid_end, int k, uint64_t* halo_end);
 
+/* ---- f1: build from a file (Index::build_posix<FASTQParser|FASTAParser>, kmer_index.hpp:231-260,332-372, with the
+ * posix_file reader of src/io/file.hpp:552-900). format 0 = by extension (.fastq/.fq, .fasta/.fa; anything else is
+ * KMI_ERR_ARG "input filename extension is not supported." as kmer_index.hpp:245-254 throws), 1 = FASTQ, 2 = FASTA. The
+ * file is read with pread into two pinned buffers by a reader thread while the GPU builds from the other buffer: FASTQ
+ * chunks end at a record boundary (kmi_fastq_find_first_record), FASTA chunks are blocks with a K-1 halo (kmi_fasta_block);
+ * position ids carry file offsets. Chunk size 256 MiB (environment KMI_FILE_CHUNK_BYTES overrides it). */
+int kmi_build_file(kmi_index* idx, const char* path, int format, uint64_t* n_kmers);
+
 /* ---- a2: record-aligned blocks (FASTQParser::find_first_record, fastq_loader.hpp:269-357,696-873) ---------------
  * Host side, as in the reference (it looks at four lines). `bytes` holds file bytes [mem_offset, mem_offset + n); the
  * search starts at search_begin (dropping a partial first line unless search_begin == parent_begin) and matches the first

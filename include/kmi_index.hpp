@@ -25,7 +25,6 @@
 #include <algorithm>
 #include <cstdint>
 #include <cstring>
-#include <fstream>
 #include <stdexcept>
 #include <string>
 #include <utility>
@@ -306,16 +305,10 @@ class b200_map {
   const_iterator cend() const { return snapshot_.cend(); }
 
   /// Index::build_posix<FASTQParser|FASTAParser>(filename) — kmer_index.hpp:332-372
-  void build_file(const std::string& filename) {
-    bool fq = ends_with(filename, ".fastq") || ends_with(filename, ".fq");
-    bool fa = ends_with(filename, ".fasta") || ends_with(filename, ".fa");
-    if (!fq && !fa) throw std::invalid_argument("input filename extension is not supported.");
-    std::ifstream f(filename.c_str(), std::ios::binary | std::ios::ate);
-    if (!f) throw std::invalid_argument("cannot open " + filename);
-    std::vector<uint8_t> buf((size_t)f.tellg());
-    f.seekg(0);
-    f.read(reinterpret_cast<char*>(buf.data()), (std::streamsize)buf.size());
-    if (fq) build_fastq(buf.data(), buf.size()); else build_fasta(buf.data(), buf.size());
+  uint64_t build_file(const std::string& filename) {
+    uint64_t kmers = 0;
+    check(kmi_build_file(h_, filename.c_str(), 0, &kmers));   // wrong extension -> std::invalid_argument, as the reference
+    return kmers;
   }
   uint64_t build_fastq(const uint8_t* bytes, size_t n, uint64_t file_offset = 0) {
     uint64_t kmers = 0;
@@ -361,9 +354,6 @@ class b200_map {
     }
   }
   static T from_u64(uint64_t v) { T t; std::memset(&t, 0, sizeof(T)); std::memcpy(&t, &v, sizeof(T) < 8 ? sizeof(T) : 8); return t; }
-  static bool ends_with(const std::string& s, const std::string& e) {
-    return s.size() >= e.size() && s.compare(s.size() - e.size(), e.size(), e) == 0;
-  }
   comm comm_;
   bool canonical_ = true;
   kmi_index* h_ = nullptr;

@@ -1690,13 +1690,8 @@ extern "C" int kmi_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_
 // Host-pointer FASTA build: the text goes to the device in chunks on a copy stream, and chunk c is built as a BLOCK of the
 // file (its halo is chunk c+1, its inherited state the chained totals of the chunks before it) while chunks c+2.. are still
 // in flight, so the PCIe transfer hides behind the build (or the other way round).
-extern "C" int kmi_build_fasta_block(kmi_index* idx, const uint8_t* bytes, size_t n, const kmi_fasta_block* block,
-                                    uint64_t* n_kmers) {
-  if (!idx || (!bytes && n)) return fail(KMI_ERR_ARG, "null argument");
-  CU(cudaSetDevice(idx->cfg.device));
-  if (n_kmers) *n_kmers = 0;
-  FaBlock base;
-  OK(fasta_block_from_abi(block, n, &base));
+static int build_fasta_host(kmi_index* idx, const uint8_t* bytes, size_t n, FaBlock base, uint64_t* n_kmers, u32* runs_out,
+                            u32* kind_out) {
   if (base.first_is_header == 2) base.first_is_header = (n && (bytes[0] == '>' || bytes[0] == ';')) ? 1u : 0u;
   OK(idx->stage_in.ensure(n + 64));
   uint8_t* d = idx->stage_in.as<uint8_t>();
@@ -1770,8 +1765,156 @@ extern "C" int kmi_build_fasta_block(kmi_index* idx, const uint8_t* bytes, size_
   CU(cudaStreamSynchronize(idx->stream));
   idx->stage_ms[0] = 0; idx->stage_ms[1] = 0; idx->stage_ms[2] = 0;
   if (n_kmers) *n_kmers = total;
+  if (runs_out) *runs_out = runs;
+  if (kind_out) *kind_out = kind;
   return check_table_error(idx);
+}
+extern "C" int kmi_build_fasta_block(kmi_index* idx, const uint8_t* bytes, size_t n, const kmi_fasta_block* block,
+                                    uint64_t* n_kmers) {
+  if (!idx || (!bytes && n)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  if (n_kmers) *n_kmers = 0;
+  FaBlock base;
+  OK(fasta_block_from_abi(block, n, &base));
+  return build_fasta_host(idx, bytes, n, base, n_kmers, nullptr, nullptr);
 }
 extern "C" int kmi_build_fasta(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t* n_kmers) {
   return kmi_build_fasta_block(idx, bytes, n, nullptr, n_kmers);
+}
+
+// ---- f1: build straight from a file (Index::build_posix<FASTQParser|FASTAParser>, kmer_index.hpp:231-260,332-372; the
+// posix_file reader of src/io/file.hpp:552-900 replaced by pread into two pinned buffers) -------------------------------
+// A reader thread fills buffer c+1 from the file while the GPU builds from buffer c (whose copy to the device is itself
+// pipelined with the parse). FASTQ chunks end at a record boundary (kmi_fastq_find_first_record near the chunk's end, the
+// remainder is carried to the front of the next buffer); FASTA chunks are blocks of the file (the last K-1 bases stay in the
+// buffer as halo and are carried too, header runs / line kind chained from chunk to chunk).
+#include <fcntl.h>
+#include <future>
+#include <sys/stat.h>
+#include <unistd.h>
+namespace {
+struct PinnedBuf {
+  uint8_t* p = nullptr;
+  size_t cap = 0;
+  ~PinnedBuf() { if (p) cudaFreeHost(p); }
+  int ensure(size_t n) {
+    if (n <= cap) return KMI_OK;
+    if (p) cudaFreeHost(p);
+    p = nullptr; cap = 0;
+    if (cudaHostAlloc(reinterpret_cast<void**>(&p), n, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return KMI_ERR_NOMEM; }
+    cap = n;
+    return KMI_OK;
+  }
+};
+struct FdGuard { int fd; ~FdGuard() { if (fd >= 0) close(fd); } };
+// bytes read (short only at the end of the file), or -1
+long long read_at(int fd, uint8_t* dst, size_t want, unsigned long long at) {
+  size_t got = 0;
+  while (got < want) {
+    ssize_t r = pread(fd, dst + got, want - got, (off_t)(at + got));
+    if (r < 0) return -1;
+    if (r == 0) break;
+    got += (size_t)r;
+  }
+  return (long long)got;
+}
+bool has_suffix(const char* s, const char* e) {
+  size_t a = strlen(s), b = strlen(e);
+  return a >= b && strcmp(s + a - b, e) == 0;
+}
+}  // namespace
+
+extern "C" int kmi_build_file(kmi_index* idx, const char* path, int format, uint64_t* n_kmers) {
+  if (!idx || !path) return fail(KMI_ERR_ARG, "null argument");
+  if (n_kmers) *n_kmers = 0;
+  if (format == 0) {
+    if (has_suffix(path, ".fastq") || has_suffix(path, ".fq")) format = 1;
+    else if (has_suffix(path, ".fasta") || has_suffix(path, ".fa")) format = 2;
+    else return fail(KMI_ERR_ARG, "input filename extension is not supported.");   // kmer_index.hpp:245-254
+  }
+  if (format != 1 && format != 2) return fail(KMI_ERR_ARG, "format must be 0 (by extension), 1 (FASTQ) or 2 (FASTA)");
+  CU(cudaSetDevice(idx->cfg.device));
+  FdGuard f{open(path, O_RDONLY)};
+  if (f.fd < 0) return fail(KMI_ERR_ARG, "cannot open %s", path);
+  struct stat st;
+  if (fstat(f.fd, &st) != 0) return fail(KMI_ERR_ARG, "cannot stat %s", path);
+  const u64 size = (u64)st.st_size;
+  u64 CH = 256ull << 20;
+  if (const char* e = getenv("KMI_FILE_CHUNK_BYTES")) CH = std::max<u64>(strtoull(e, nullptr, 10), 256);
+  CH = std::min<u64>(CH, std::max<u64>(size, 1));
+  PinnedBuf buf[2];
+  OK(buf[0].ensure(2 * CH + 64));
+  if (size > CH) OK(buf[1].ensure(2 * CH + 64));
+  const int K = idx->cfg.k;
+  u64 file_pos = 0;      // next file byte to read
+  u64 base_off = 0;      // file offset of buf[cur][0]
+  u64 carry = 0;         // bytes at the front of buf[cur] carried over from the previous chunk
+  u64 total = 0;
+  u32 runs = 0, kind = 0, first_is_header = 0;
+  uint8_t prev_byte = '\n';
+  int cur = 0;
+  long long got = read_at(f.fd, buf[0].p, (size_t)std::min<u64>(CH, size), 0);
+  if (got < 0) return fail(KMI_ERR_ARG, "read error on %s", path);
+  file_pos = (u64)got;
+  if (size) first_is_header = (buf[0].p[0] == '>' || buf[0].p[0] == ';') ? 1u : 0u;
+  for (;;) {
+    uint8_t* b = buf[cur].p;
+    const u64 len = carry + (file_pos - (base_off + carry));   // bytes in the buffer: [base_off, file_pos)
+    const bool eof = file_pos >= size;
+    // -- where this chunk ends
+    u64 cut = len;
+    if (!eof) {
+      if (format == 1) {
+        cut = 0;
+        for (u64 tail = std::min<u64>(len, std::max<u64>(len / 8, 2048));; tail = std::min<u64>(len, tail * 4)) {
+          uint64_t off = 0;
+          int r = kmi_fastq_find_first_record(b, base_off, len, base_off + len - tail, base_off + len, 0, size, &off);
+          if (r == KMI_OK && off < base_off + len) { cut = off - base_off; break; }
+          if (tail == len) break;
+        }
+        if (cut == 0) return fail(KMI_ERR_FORMAT, "no FASTQ record boundary inside a chunk of %llu bytes at offset %llu", (unsigned long long)len, (unsigned long long)base_off);
+      } else {
+        int need = K - 1;
+        while (cut > 0 && need > 0) { --cut; if (b[cut] != '\n' && b[cut] != '\r') --need; }
+        if (need > 0) return fail(KMI_ERR_FORMAT, "chunk of %llu bytes holds fewer than K-1 bases", (unsigned long long)len);
+      }
+    }
+    // -- start reading the next chunk behind the carried bytes of the other buffer
+    std::future<long long> next;
+    const u64 next_carry = len - cut;
+    if (!eof) {
+      if (next_carry > CH) return fail(KMI_ERR_FORMAT, "a record longer than the chunk size (%llu bytes)", (unsigned long long)CH);
+      uint8_t* nb = buf[cur ^ 1].p;
+      memcpy(nb, b + cut, next_carry);
+      const u64 want = std::min<u64>(CH, size - file_pos), at = file_pos;
+      const int fd = f.fd;
+      next = std::async(std::launch::async, [fd, nb, next_carry, want, at]() { return read_at(fd, nb + next_carry, (size_t)want, at); });
+    }
+    // -- build from this buffer
+    uint64_t produced = 0;
+    int r;
+    if (format == 1) {
+      r = kmi_build_fastq(idx, b, cut, base_off, &produced);
+    } else {
+      FaBlock blk;
+      blk.file_offset = base_off; blk.n_valid = cut; blk.runs0 = runs; blk.kind0 = kind;
+      blk.bol = (base_off == 0 || prev_byte == '\n') ? 1u : 0u;
+      blk.first_is_header = first_is_header;
+      r = build_fasta_host(idx, b, len, blk, &produced, &runs, &kind);
+    }
+    total += produced;
+    if (cut > 0) prev_byte = b[cut - 1];
+    long long g = 0;
+    if (!eof) g = next.get();   // always collect the reader before leaving
+    if (r != KMI_OK) return r;
+    if (eof) break;
+    if (g < 0) return fail(KMI_ERR_ARG, "read error on %s", path);
+    base_off += cut;
+    carry = next_carry;
+    file_pos += (u64)g;
+    if (g == 0 && file_pos < size) return fail(KMI_ERR_ARG, "%s is shorter than its size says", path);
+    cur ^= 1;
+  }
+  if (n_kmers) *n_kmers = total;
+  return KMI_OK;
 }

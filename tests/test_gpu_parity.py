@@ -597,3 +597,53 @@ def test_cpp_adapter_against_std_containers(tmp_path):
                            "-Wl,-rpath," + os.path.dirname(kb.LIB_PATH)])
     r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "adapter ok" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.parametrize("name,k,chunk", [("natural.fastq", 21, 3000), ("test.medium.fastq", 31, 5000), ("natural.withN.fastq", 15, 1 << 28)])
+def test_build_file_fastq_streams_record_aligned_chunks(name, k, chunk, tmp_path, monkeypatch):
+    """kmi_build_file: the file is read in chunks that end at record boundaries (the rest is carried into the next buffer);
+    count index == oracle; position index ids are file offsets of the whole file."""
+    buf = ou.read_fixture(name)
+    path = tmp_path / name
+    path.write_bytes(buf.tobytes())
+    monkeypatch.setenv("KMI_FILE_CHUNK_BYTES", str(chunk))
+    wk, wi, _ = ou.fastq_kmers(buf, k, want_ids=True)
+    dk, dc = ou.count_sorted(wk, k)
+    with kb.CountIndex(k) as idx:
+        assert idx.build_file(str(path)) == len(wk)
+        gk, gc = idx.sorted_dump()
+        assert np.array_equal(gk, dk) and np.array_equal(gc, dc)
+    with kb.PositionIndex(k) as idx:
+        assert idx.build_file(str(path), format=1) == len(wk)
+        gk, gi = idx.sorted_dump()
+        swk, swi = ou.sort_tuples(wk, wi, k)
+        assert np.array_equal(gk, swk) and np.array_equal(gi, swi)
+
+
+@pytest.mark.parametrize("name,k,chunk", [("test.medium.fasta", 21, 50000), ("natural.withN.fasta", 21, 2000), ("test.unitiqs.fasta", 63, 1500),
+                                          ("test2.fasta", 21, 1 << 28)])
+def test_build_file_fasta_streams_blocks(name, k, chunk, tmp_path, monkeypatch):
+    buf = ou.read_fixture(name)
+    path = tmp_path / name
+    path.write_bytes(buf.tobytes())
+    monkeypatch.setenv("KMI_FILE_CHUNK_BYTES", str(chunk))
+    wk, wi, _ = ou.fasta_kmers(buf, k)
+    swk, swi = ou.sort_tuples(wk, wi, k)
+    with kb.PositionIndex(k) as idx:
+        assert idx.build_file(str(path)) == len(wk)
+        gk, gi = idx.sorted_dump()
+        assert np.array_equal(gk, swk) and np.array_equal(gi, swi)
+
+
+def test_build_file_errors(tmp_path):
+    p = tmp_path / "reads.txt"
+    p.write_bytes(b"@a\nACGTACGTTGCATGCA\n+\nIIIIIIIIIIIIIIII\n")
+    with kb.CountIndex(15) as idx:
+        with pytest.raises(kb.KmiError, match="extension is not supported"):
+            idx.build_file(str(p))
+        with pytest.raises(kb.KmiError, match="cannot open"):
+            idx.build_file(str(tmp_path / "missing.fastq"))
+        assert idx.build_file(str(p), format=1) == 2
+        e = tmp_path / "empty.fastq"
+        e.write_bytes(b"")
+        assert idx.build_file(str(e)) == 0
