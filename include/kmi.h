@@ -129,7 +129,7 @@ int kmi_fasta_halo_end(const uint8_t* bytes, uint64_t mem_offset, size_t n, uint
  * KMI_ERR_ARG "input filename extension is not supported." as kmer_index.hpp:245-254 throws), 1 = FASTQ, 2 = FASTA. The
  * file is read with pread into two pinned buffers by a reader thread while the GPU builds from the other buffer: FASTQ
  * chunks end at a record boundary (kmi_fastq_find_first_record), FASTA chunks are blocks with a K-1 halo (kmi_fasta_block);
- * position ids carry file offsets. Chunk size 256 MiB (environment KMI_FILE_CHUNK_BYTES overrides it). */
+ * position ids carry file offsets. Chunk size 1 GiB (environment KMI_FILE_CHUNK_BYTES overrides it). */
 int kmi_build_file(kmi_index* idx, const char* path, int format, uint64_t* n_kmers);
 
 /* ---- a2: record-aligned blocks (FASTQParser::find_first_record, fastq_loader.hpp:269-357,696-873) ---------------
