@@ -193,8 +193,9 @@ int kmi_partition_dev(kmi_index* idx, const uint64_t* d_keys, const uint64_t* d_
                       uint64_t* d_keys_out, uint64_t* d_vals_out, uint64_t* h_counts);
 
 /* ---- insert (Index::insert, kmer_index.hpp:201-225) ---------------------------------------- */
-/* COUNT mode: vals ignored (each key counts 1; counting_densehash_map::insert(vector<Key>&),
- * distributed_densehash_map.hpp:2714-2899). POSITION mode: vals[i] is the id of keys[i]
+/* COUNT mode: vals == NULL: each key counts 1 (counting_densehash_map::insert(vector<Key>&),
+ * distributed_densehash_map.hpp:2714-2899); vals != NULL: (key, count) tuples, vals[i] is ADDED to the entry of keys[i]
+ * (reduction_densehash_map::insert with std::plus<uint32_t>, :2463-2482,2565-2628: the sum wraps at 2^32). POSITION mode: vals[i] is the id of keys[i]
  * (densehash_multimap::insert, :2329-2384; duplicates kept). Keys are canonicalised first when
  * cfg.canonical (transform_input, distributed_map_base.hpp:286-301); the caller's arrays are not
  * modified. */

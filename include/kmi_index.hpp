@@ -156,8 +156,9 @@ class b200_map {
     check(kmi_insert(h_, reinterpret_cast<const uint64_t*>(keys.data()), nullptr, keys.size()));
     return keys.size();
   }
-  /// insert(std::vector<std::pair<Key,T>>&): COUNT adds 1 per tuple (KmerCountTupleParser emits count 1,
-  /// kmer_parser.hpp:941,966); POSITION stores every (key, id) — :2329-2384
+  /// insert(std::vector<std::pair<Key,T>>&): COUNT adds the tuple's count to the key's entry (reduction insert with
+  /// std::plus, distributed_densehash_map.hpp:2463-2482; KmerCountTupleParser emits count 1, kmer_parser.hpp:941,966);
+  /// POSITION stores every (key, id) — :2329-2384
   size_t insert(std::vector<value_type>& tuples) {
     std::vector<uint64_t> k(tuples.size() * nw()), v(tuples.size());
     for (size_t i = 0; i < tuples.size(); ++i) {
@@ -166,7 +167,7 @@ class b200_map {
       std::memcpy(&id, &tuples[i].second, sizeof(T) < 8 ? sizeof(T) : 8);
       v[i] = id;
     }
-    check(kmi_insert(h_, k.data(), Mode == KMI_MODE_POSITION ? v.data() : nullptr, tuples.size()));
+    check(kmi_insert(h_, k.data(), v.data(), tuples.size()));
     return tuples.size();
   }
   /// find: COUNT -> (key, frequency) for hits; POSITION -> every (key, id) of every hit — :327-448. As in the reference the

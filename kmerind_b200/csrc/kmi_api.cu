@@ -494,7 +494,7 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
   return KMI_OK;
 }
 
-static int insert_keys_chunked(kmi_index* idx, const u64* d_keys, size_t n, bool canon);
+static int insert_keys_chunked(kmi_index* idx, const u64* d_keys, size_t n, bool canon, const u64* d_counts = nullptr);
 
 // several key streams -> the same buckets -> table (one table sweep for all of them); total <= BUCKET_MAX_KEYS
 static int insert_streams_bucketed(kmi_index* idx, const u64* const* d_keys, const u64* counts, int n_streams, bool canon) {
@@ -1105,12 +1105,12 @@ static int log_append(kmi_index* idx, const u64* d_keys, const u64* d_vals, size
   return KMI_OK;
 }
 
-static int insert_keys_chunked(kmi_index* idx, const u64* d_keys, size_t n, bool canon) {
+static int insert_keys_chunked(kmi_index* idx, const u64* d_keys, size_t n, bool canon, const u64* d_counts) {
   size_t done = 0;
   while (done < n) {
     u64 grant = 0;
     OK(table_room(idx, n - done, &grant));
-    idx->ops->insert_keys(idx->stream, idx->view(), d_keys + done * idx->nw, grant, canon);
+    idx->ops->insert_keys(idx->stream, idx->view(), d_keys + done * idx->nw, grant, canon, d_counts ? d_counts + done : nullptr);
     idx->launches++;
     idx->non_hll_upper += grant;
     done += grant;
@@ -1133,6 +1133,9 @@ extern "C" int kmi_insert_dev(kmi_index* idx, const uint64_t* d_keys_, const uin
     if (idx->build_path == 2 || (idx->build_path == 0 && n >= AUTO_BUCKET_KEYS)) OK(insert_keys_bucketed(idx, logged, n, false));
     else OK(insert_keys_chunked(idx, logged, n, false));
     idx->csr_dirty = true;
+  } else if (d_vals) {
+    // (key, count) tuples: reduction insert, count added to the entry (direct atomics; the bucketed paths count keys)
+    OK(insert_keys_chunked(idx, d_keys, n, idx->cfg.canonical != 0, d_vals));
   } else if (idx->build_path == 2 || (idx->build_path == 0 && n >= AUTO_BUCKET_KEYS)) {
     OK(insert_keys_bucketed(idx, d_keys, n, idx->cfg.canonical != 0));
   } else {
@@ -1149,7 +1152,7 @@ extern "C" int kmi_insert(kmi_index* idx, const uint64_t* keys, const uint64_t* 
   OK(idx->stage_keys.ensure(n * kb));
   CU(cudaMemcpyAsync(idx->stage_keys.p, keys, n * kb, cudaMemcpyHostToDevice, idx->stream));
   const uint64_t* dv = nullptr;
-  if (idx->cfg.mode == KMI_MODE_POSITION) {
+  if (idx->cfg.mode == KMI_MODE_POSITION || vals) {
     if (!vals) return fail(KMI_ERR_ARG, "POSITION insert needs ids");
     OK(idx->stage_vals.ensure(n * sizeof(u64)));
     CU(cudaMemcpyAsync(idx->stage_vals.p, vals, n * sizeof(u64), cudaMemcpyHostToDevice, idx->stream));

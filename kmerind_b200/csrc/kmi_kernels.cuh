@@ -17,9 +17,11 @@ template <int NW> __global__ void k_table_clear(Slot<NW>* __restrict__ slots, u6
   }
 }
 
-// a15: counting insert, distributed_densehash_map.hpp:2463-2482 / :2714-2899 (val += 1 per key)
+// a15: counting insert, distributed_densehash_map.hpp:2463-2482 / :2714-2899 (val += 1 per key); with `vals` the
+// reduction insert of (key, count) tuples: val += count, std::plus<uint32_t> (wraps at 2^32), :2565-2628
 template <int K, int HASH>
-__global__ void __launch_bounds__(256) k_insert_keys(TableView t, const u64* __restrict__ keys, u64 n, const bool CANON) {
+__global__ void __launch_bounds__(256) k_insert_keys(TableView t, const u64* __restrict__ keys, u64 n, const bool CANON,
+                                                     const u64* __restrict__ vals) {
   constexpr int NW = (K <= 32 ? 1 : 2);
   u32 n_new = 0;
   for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
@@ -28,7 +30,7 @@ __global__ void __launch_bounds__(256) k_insert_keys(TableView t, const u64* __r
     bool was_new;
     u64 s = table_upsert<NW>(t, key, slot_hash<K>(key), was_new);
     if (s != ~0ULL) {
-      atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].val, 1u);
+      atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].val, vals ? (u32)vals[i] : 1u);
       n_new += was_new ? 1u : 0u;
     }
   }

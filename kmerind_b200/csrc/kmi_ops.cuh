@@ -26,7 +26,7 @@ struct Ops {
                       const u32* enc_block_max, const u32* tile_runs, const u32* runs_block_sums, KeySink sink, u64* n_kmers,
                       u32* perr, bool canon, bool nsplit, u64 tile_begin, FaBlock blk);
   void (*table_clear)(cudaStream_t, void* slots, u64 n);
-  void (*insert_keys)(cudaStream_t, TableView, const u64* keys, u64 n, bool canon);
+  void (*insert_keys)(cudaStream_t, TableView, const u64* keys, u64 n, bool canon, const u64* vals);
   void (*rehash)(cudaStream_t, const void* old_slots, u64 n_old, TableView);
   void (*lookup)(cudaStream_t, TableView, const u64* keys, u64 n, u64* vals, uint8_t* found, u64* slot_idx, bool canon);
   void (*erase)(cudaStream_t, TableView, const u64* keys, u64 n, u64* vals_removed, bool canon);
@@ -97,8 +97,8 @@ struct OpsImpl {
   static void table_clear(cudaStream_t st, void* slots, u64 n) {
     k_table_clear<NW><<<grid_for(n, 256), 256, 0, st>>>(reinterpret_cast<S*>(slots), n);
   }
-  static void insert_keys(cudaStream_t st, TableView t, const u64* keys, u64 n, bool canon) {
-    if (n) k_insert_keys<K, HASH><<<grid_for(n, 256, 148u * 32u), 256, 0, st>>>(t, keys, n, canon);
+  static void insert_keys(cudaStream_t st, TableView t, const u64* keys, u64 n, bool canon, const u64* vals) {
+    if (n) k_insert_keys<K, HASH><<<grid_for(n, 256, 148u * 32u), 256, 0, st>>>(t, keys, n, canon, vals);
   }
   static void rehash(cudaStream_t st, const void* old_slots, u64 n_old, TableView t) {
     k_rehash<K, HASH><<<grid_for(n_old, 256, 148u * 32u), 256, 0, st>>>(reinterpret_cast<const S*>(old_slots), n_old, t);

@@ -57,6 +57,24 @@ static int count_checks() {
     size_t i = 0;
     for (const auto& kv : want) { CHECK(all[i].first == kv.first && all[i].second == kv.second); ++i; }
   }
+  // (key, count) tuples add their count (reduction insert), also onto existing entries and for new keys
+  {
+    std::vector<V> tuples;
+    for (int i = 0; i < 1500; ++i) {
+      Key k = (i % 3) ? pool[rng() % 3000] : random_kmer<K>(rng);
+      uint32_t c = (uint32_t)(rng() % 1000);
+      tuples.emplace_back(k.reverse_complement(), c);
+      want[k.canonical()] += c;
+    }
+    tuples.emplace_back(pool[0], 0xFFFFFFF0u);       // std::plus<uint32_t> wraps
+    want[pool[0].canonical()] += 0xFFFFFFF0u;
+    idx.insert(tuples);
+    CHECK(idx.local_size() == want.size());
+    all = idx.to_vector();
+    sort_pairs(all);
+    size_t i = 0;
+    for (const auto& kv : want) { CHECK(all[i].first == kv.first && all[i].second == kv.second); ++i; }
+  }
   // queries: every pool key in a random orientation + keys that are (almost surely) absent
   std::vector<Key> q;
   for (const Key& k : pool) q.push_back((rng() & 1) ? k : k.reverse_complement());

@@ -647,3 +647,25 @@ def test_build_file_errors(tmp_path):
         e = tmp_path / "empty.fastq"
         e.write_bytes(b"")
         assert idx.build_file(str(e)) == 0
+
+
+@pytest.mark.parametrize("k", (21, 63))
+def test_count_tuples_are_added(k):
+    """kmi_insert with values in COUNT mode is the reduction insert: the tuple's count is added to the key's entry."""
+    keys = ou.random_keys(k, 5000, seed=3)
+    keys = np.concatenate([keys, keys[:2000]])
+    cnt = np.arange(1, len(keys) + 1, dtype=np.uint64) % np.uint64(977)
+    can = ou.shape_keys(np.ascontiguousarray(ou.canonical(keys, k)).reshape(-1), k)
+    with kb.CountIndex(k) as idx:
+        idx.insert(keys)                       # +1 each
+        idx.insert(keys, cnt)                  # + count
+        got = idx.count(keys)                  # map semantics: 0/1
+        assert got.min() == 1
+        vals, found = idx.find(keys)
+        assert found.all()
+        want = {}
+        rows = [tuple(np.atleast_1d(r).tolist()) for r in can]
+        for r, c in zip(rows, cnt.tolist()):
+            want[r] = want.get(r, 0) + 1 + c
+        assert [want[r] & 0xFFFFFFFF for r in rows] == vals.tolist()
+        assert idx.local_size() == len(want)
