@@ -132,6 +132,15 @@ int kmi_fasta_halo_end(const uint8_t* bytes, uint64_t mem_offset, size_t n, uint
  * position ids carry file offsets. Chunk size 1 GiB (environment KMI_FILE_CHUNK_BYTES overrides it). */
 int kmi_build_file(kmi_index* idx, const char* path, int format, uint64_t* n_kmers);
 
+/* ---- f2: persistence. The reference keeps no index on disk; this is the wire format of one shard: a 64-byte header
+ * ("KMIDX001", k, mode, words per key, canonical, entry count) followed by the entries of to_vector()
+ * (distributed_densehash_map.hpp:1103-1113) sorted by (key, value): all keys (nw little-endian uint64_t each), then all
+ * values as uint64_t (COUNT: frequency; POSITION: one entry per (key, id)). kmi_load ADDS a file's entries to the index
+ * (counts are summed, ids appended), so shards saved by several ranks can be merged into one index; K and mode must
+ * match (KMI_ERR_ARG). */
+int kmi_save(kmi_index* idx, const char* path);
+int kmi_load(kmi_index* idx, const char* path, uint64_t* n_entries);
+
 /* ---- a2: record-aligned blocks (FASTQParser::find_first_record, fastq_loader.hpp:269-357,696-873) ---------------
  * Host side, as in the reference (it looks at four lines). `bytes` holds file bytes [mem_offset, mem_offset + n); the
  * search starts at search_begin (dropping a partial first line unless search_begin == parent_begin) and matches the first

@@ -321,6 +321,9 @@ class b200_map {
     check(kmi_build_fasta(h_, bytes, n, &kmers));
     return kmers;
   }
+  /// this shard's entries to / from a file (kmi_save / kmi_load; load adds to what the map holds)
+  void save(const std::string& filename) const { check(kmi_save(h_, filename.c_str())); }
+  size_t load(const std::string& filename) { uint64_t n = 0; check(kmi_load(h_, filename.c_str(), &n)); return (size_t)n; }
   kmi_index* handle() const { return h_; }
   const comm& get_comm() const { return comm_; }
 

@@ -74,6 +74,7 @@ def load_library(build_if_missing=False):
         "kmi_fasta_block_summary_dev": [_P, _P, _SZ, ctypes.c_int, _P],
         "kmi_fasta_halo_end": [_P, _U64, _SZ, _U64, ctypes.c_int, _P],
         "kmi_build_file": [_P, ctypes.c_char_p, ctypes.c_int, _P],
+        "kmi_save": [_P, ctypes.c_char_p], "kmi_load": [_P, ctypes.c_char_p, _P],
         "kmi_parse_fastq_by_owner_dev": [_P, _P, _SZ, _P, _SZ, _P, _P],
         "kmi_exchange_setup": [_P, _SZ, _P], "kmi_exchange_connect": [_P, _P],
         "kmi_exchange_parse_fastq_dev": [_P, _P, _SZ, _P, _P], "kmi_exchange_insert": [_P, _P],
@@ -103,7 +104,7 @@ EXPORTED_SYMBOLS = (
     "kmi_create", "kmi_destroy", "kmi_last_error", "kmi_set_stream", "kmi_set_param", "kmi_reserve", "kmi_clear",
     "kmi_build_fastq", "kmi_build_fasta", "kmi_build_fastq_dev", "kmi_build_fasta_dev",
     "kmi_parse_fastq_dev", "kmi_parse_fasta_dev", "kmi_parse_fasta_block_dev", "kmi_build_fasta_block", "kmi_build_fasta_block_dev",
-    "kmi_fasta_block_summary_dev", "kmi_fasta_halo_end", "kmi_build_file", "kmi_parse_fastq_by_owner_dev", "kmi_exchange_setup", "kmi_exchange_connect",
+    "kmi_fasta_block_summary_dev", "kmi_fasta_halo_end", "kmi_build_file", "kmi_save", "kmi_load", "kmi_parse_fastq_by_owner_dev", "kmi_exchange_setup", "kmi_exchange_connect",
     "kmi_exchange_parse_fastq_dev", "kmi_exchange_insert", "kmi_exchange_bins", "kmi_fastq_find_first_record", "kmi_canonicalize_dev", "kmi_hash_dev",
     "kmi_partition_dev", "kmi_insert", "kmi_insert_dev", "kmi_count", "kmi_find", "kmi_find_positions",
     "kmi_erase", "kmi_count_dev", "kmi_find_dev", "kmi_local_size", "kmi_num_keys", "kmi_dump",
@@ -235,6 +236,16 @@ class Index:
         """Index::build_posix: FASTQ / FASTA file by extension (format 1 / 2 to force), streamed from disk."""
         n = _U64(0)
         _check(self._lib.kmi_build_file(self._h, os.fsencode(path), format, ctypes.byref(n)))
+        return n.value
+
+    def save(self, path):
+        """write this shard's entries, sorted by (key, value), to `path` (format: include/kmi.h, kmi_save)"""
+        _check(self._lib.kmi_save(self._h, os.fsencode(path)))
+
+    def load(self, path):
+        """add the entries of a saved shard to this index; returns how many entries the file held"""
+        n = _U64(0)
+        _check(self._lib.kmi_load(self._h, os.fsencode(path), ctypes.byref(n)))
         return n.value
 
     def build_fasta(self, data, block=None):

@@ -1950,3 +1950,76 @@ extern "C" int kmi_build_file(kmi_index* idx, const char* path, int format, uint
   if (n_kmers) *n_kmers = total;
   return KMI_OK;
 }
+
+// ---- f2: persistence (the reference has no on-disk index format; this defines one: what to_vector() returns,
+// distributed_densehash_map.hpp:1103-1113, sorted by (key, value), one file per shard) -------------------------------------
+namespace {
+struct KmiFileHeader {
+  char magic[8];        // "KMIDX001"
+  uint32_t k, mode, nw, canonical;
+  uint64_t n_entries;
+  uint64_t reserved[4];
+};
+static_assert(sizeof(KmiFileHeader) == 64, "header is 64 bytes");
+struct FileGuard { FILE* f; ~FileGuard() { if (f) fclose(f); } };
+}  // namespace
+
+extern "C" int kmi_save(kmi_index* idx, const char* path) {
+  if (!idx || !path) return fail(KMI_ERR_ARG, "null argument");
+  uint64_t n = 0, got = 0;
+  OK(kmi_local_size(idx, &n));
+  const size_t nw = (size_t)idx->nw;
+  std::vector<uint64_t> keys(n * nw + 1), vals(n + 1);
+  OK(kmi_dump(idx, keys.data(), vals.data(), n, &got));
+  std::vector<uint64_t> order(got);
+  for (uint64_t i = 0; i < got; ++i) order[i] = i;
+  std::sort(order.begin(), order.end(), [&](uint64_t a, uint64_t b) {
+    for (size_t w = nw; w-- > 0;) if (keys[a * nw + w] != keys[b * nw + w]) return keys[a * nw + w] < keys[b * nw + w];
+    return vals[a] < vals[b];
+  });
+  FileGuard g{fopen(path, "wb")};
+  if (!g.f) return fail(KMI_ERR_ARG, "cannot create %s", path);
+  KmiFileHeader h;
+  memset(&h, 0, sizeof(h));
+  memcpy(h.magic, "KMIDX001", 8);
+  h.k = (uint32_t)idx->cfg.k; h.mode = (uint32_t)idx->cfg.mode; h.nw = (uint32_t)nw; h.canonical = idx->cfg.canonical ? 1u : 0u;
+  h.n_entries = got;
+  bool ok = fwrite(&h, sizeof(h), 1, g.f) == 1;
+  std::vector<uint64_t> out(1u << 16);
+  for (uint64_t i = 0; ok && i < got;) {            // keys, then values, in sorted order
+    size_t m = 0;
+    for (; i < got && m + nw <= out.size(); ++i) for (size_t w = 0; w < nw; ++w) out[m++] = keys[order[i] * nw + w];
+    ok = fwrite(out.data(), 8, m, g.f) == m;
+  }
+  for (uint64_t i = 0; ok && i < got;) {
+    size_t m = 0;
+    for (; i < got && m < out.size(); ++i) out[m++] = vals[order[i]];
+    ok = fwrite(out.data(), 8, m, g.f) == m;
+  }
+  if (!ok) return fail(KMI_ERR_ARG, "write error on %s", path);
+  return KMI_OK;
+}
+
+extern "C" int kmi_load(kmi_index* idx, const char* path, uint64_t* n_entries) {
+  if (!idx || !path) return fail(KMI_ERR_ARG, "null argument");
+  if (n_entries) *n_entries = 0;
+  FileGuard g{fopen(path, "rb")};
+  if (!g.f) return fail(KMI_ERR_ARG, "cannot open %s", path);
+  KmiFileHeader h;
+  if (fread(&h, sizeof(h), 1, g.f) != 1 || memcmp(h.magic, "KMIDX001", 8) != 0) return fail(KMI_ERR_FORMAT, "%s is not a kmi index file", path);
+  if ((int)h.k != idx->cfg.k || (int)h.mode != idx->cfg.mode || (int)h.nw != idx->nw)
+    return fail(KMI_ERR_ARG, "%s holds a K=%u mode-%u index, this one is K=%d mode-%d", path, h.k, h.mode, idx->cfg.k, idx->cfg.mode);
+  const size_t nw = (size_t)idx->nw;
+  const uint64_t CH = 1u << 24;                      // entries per insert
+  std::vector<uint64_t> keys, vals;
+  for (uint64_t done = 0; done < h.n_entries; done += CH) {
+    const uint64_t m = std::min<uint64_t>(CH, h.n_entries - done);
+    keys.resize(m * nw); vals.resize(m);
+    if (fseeko(g.f, (off_t)(sizeof(h) + done * nw * 8), SEEK_SET) != 0 || fread(keys.data(), 8, m * nw, g.f) != m * nw ||
+        fseeko(g.f, (off_t)(sizeof(h) + h.n_entries * nw * 8 + done * 8), SEEK_SET) != 0 || fread(vals.data(), 8, m, g.f) != m)
+      return fail(KMI_ERR_FORMAT, "%s is truncated", path);
+    OK(kmi_insert(idx, keys.data(), vals.data(), m));   // COUNT: counts are added; POSITION: ids appended
+  }
+  if (n_entries) *n_entries = h.n_entries;
+  return KMI_OK;
+}

@@ -669,3 +669,48 @@ def test_count_tuples_are_added(k):
             want[r] = want.get(r, 0) + 1 + c
         assert [want[r] & 0xFFFFFFFF for r in rows] == vals.tolist()
         assert idx.local_size() == len(want)
+
+
+def test_save_and_load_round_trip(tmp_path):
+    """kmi_save writes to_vector() sorted by (key, value); kmi_load adds a file's entries: a reloaded index equals the
+    original, loading twice doubles the counts, shards merge, a K mismatch is refused."""
+    buf = ou.read_fixture("natural.fastq")
+    for k in (21, 63):
+        p = str(tmp_path / ("count%d.kmi" % k))
+        with kb.CountIndex(k) as idx:
+            idx.build_fastq(buf)
+            dk, dc = idx.sorted_dump()
+            idx.save(p)
+        raw = np.fromfile(p, dtype=np.uint64)
+        nw = ou.nwords(k)
+        assert raw[:1].tobytes() == b"KMIDX001" and int(raw[3]) == len(dk)      # header: magic, (k, mode), (nw, canonical), n
+        assert np.array_equal(raw[8:8 + len(dk) * nw], np.ascontiguousarray(dk).reshape(-1))   # keys sorted, then values
+        assert np.array_equal(raw[8 + len(dk) * nw:], dc.astype(np.uint64))
+        with kb.CountIndex(k) as idx:
+            assert idx.load(p) == len(dk)
+            gk, gc = idx.sorted_dump()
+            assert np.array_equal(gk, dk) and np.array_equal(gc, dc)
+            idx.load(p)
+            gk, gc = idx.sorted_dump()
+            assert np.array_equal(gk, dk) and np.array_equal(gc, 2 * dc)
+        with kb.CountIndex(31) as idx:
+            with pytest.raises(kb.KmiError, match="holds a K="):
+                idx.load(p)
+    fa = ou.read_fixture("test2.fasta")
+    p = str(tmp_path / "pos.kmi")
+    with kb.PositionIndex(21) as idx:
+        idx.build_fasta(fa)
+        dk, di = idx.sorted_dump()
+        idx.save(p)
+    with kb.PositionIndex(21) as idx:
+        assert idx.load(p) == len(dk)
+        gk, gi = idx.sorted_dump()
+        assert np.array_equal(gk, dk) and np.array_equal(gi, di)
+        sel = dk[::7]
+        off, vals = idx.find_positions(sel)
+        assert int(off[-1]) == sum(int((dk == s).sum()) for s in sel)
+    with kb.CountIndex(21) as idx:
+        with pytest.raises(kb.KmiError):
+            idx.load(p)      # a position file into a count index
+        with pytest.raises(kb.KmiError):
+            idx.load(str(tmp_path / "missing.kmi"))
