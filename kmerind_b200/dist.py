@@ -31,6 +31,25 @@ def exchange_rows(rows, send_counts, recv_counts, group=None):
     return out
 
 
+def chain_fasta_blocks(summary, bol, file_offset, group=None, file_starts_with_header=None):
+    """What THIS rank's block of a partitioned FASTA file inherits from the ranks before it: one all-gather of the block
+    summaries (kmi_fasta_block_summary_dev: has a line start, first / last line start is a header, header runs) and the
+    exclusive scan of kmerind_b200.fasta_chain over them — the cross-rank part of FASTAParser::init_parser
+    (fasta_loader.hpp:202-483). Blocks are in rank order. Returns (header_runs_before, flags) for kmi_fasta_block."""
+    from . import fasta_chain
+    world = dist.get_world_size(group)
+    mine = tuple(int(x) for x in summary) + (1 if bol else 0, int(file_offset))
+    every = [None] * world
+    dist.all_gather_object(every, mine, group=group)
+    if file_starts_with_header is None:   # the first non-empty block at file offset 0 opens the file
+        file_starts_with_header = False
+        for e in every:
+            if e[0] and e[4] and e[5] == 0:
+                file_starts_with_header = bool(e[1])
+                break
+    return fasta_chain([e[:4] for e in every], [e[4] for e in every], file_starts_with_header)[dist.get_rank(group)]
+
+
 class ShardedIndex:
     """CountIndex / PositionIndex sharded over the ranks of a torch.distributed group.
 
@@ -245,16 +264,11 @@ class ShardedIndex:
         their block summaries (header runs, kind of the last line) with one all-gather — the cross-rank part of
         FASTAParser::init_parser, fasta_loader.hpp:202-483 — and each parses its block with global sequence ids and the
         K-1 tail rule (kmer_parser.hpp:114-157)."""
-        from . import fasta_chain
         nw = self.nw
         block = None
         if n_valid is not None:
-            mine = self.local.fasta_block_summary_dev(text.data_ptr(), n_valid, bol) + (1 if bol else 0, int(file_offset))
-            every = [None] * self.nranks
-            dist.all_gather_object(every, mine, group=self.group)
-            if file_starts_with_header is None:   # rank 0's block opens the file
-                file_starts_with_header = bool(every[0][0] and every[0][1] and every[0][4] and every[0][5] == 0)
-            runs0, flags = fasta_chain([e[:4] for e in every], [e[4] for e in every], file_starts_with_header)[self.rank]
+            summary = self.local.fasta_block_summary_dev(text.data_ptr(), n_valid, bol)
+            runs0, flags = chain_fasta_blocks(summary, bol, file_offset, self.group, file_starts_with_header)
             block = (int(file_offset), int(n_valid), runs0, flags)
         cap = max(nbytes if n_valid is None else n_valid, 1)
         keys = torch.empty(cap * nw, dtype=torch.int64, device=self.device)

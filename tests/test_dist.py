@@ -60,6 +60,38 @@ def _gloo_worker(rank, world, port, out_dir):
         dist.destroy_process_group()
 
 
+def _gloo_fasta_chain_worker(rank, world, port, out_dir, cuts):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from kmerind_b200.dist import chain_fasta_blocks
+        from test_partition import block_summary
+        buf = ou.read_fixture("test.fasta")
+        b, e = cuts[rank], cuts[rank + 1]
+        bol = b == 0 or buf[b - 1] == 0x0A
+        runs0, flags = chain_fasta_blocks(block_summary(buf[b:e], bol), bol, b)
+        np.save(os.path.join(out_dir, "chain%d.npy" % rank), np.array([runs0, flags]))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("cuts", ([0, 200, 512], [0, 1, 512], [0, 0, 512], [0, 333, 512]))
+def test_fasta_block_chain_gloo_world2(tmp_path, cuts):
+    """the host side of the sharded FASTA build: every rank learns, from one all-gather of block summaries, how many header
+    runs began before its block and what kind of line it starts in"""
+    import kmerind_b200 as kb
+    world = 2
+    mp.spawn(_gloo_fasta_chain_worker, args=(world, _free_port(), str(tmp_path), cuts), nprocs=world, join=True)
+    buf = ou.read_fixture("test.fasta")
+    fsh = buf[0] in (0x3E, 0x3B)
+    for r in range(world):
+        runs0, flags = np.load(tmp_path / ("chain%d.npy" % r)).tolist()
+        want = ou.fasta_prefix_state(buf, cuts[r])
+        assert (runs0, (flags >> 1) & 1, bool(flags & 1)) == want, (r, cuts)
+        assert bool(flags & kb.FASTA_FILE_STARTS_WITH_HEADER) == bool(fsh)
+
+
 def test_exchange_gloo_world2(tmp_path):
     world = 2
     mp.spawn(_gloo_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
