@@ -97,72 +97,91 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
-# reference arm / cpu baseline: the reference's CPU code on a bounded sample
+# the workload, named identically by both arms
 # ------------------------------------------------------------------------------------------------
-def _cpu_sample(n_reads, genome_len):
+def workload_config(world, n_reads):
+    nbytes = n_reads * REC
+    return {"workload": "CountIndex K=31 canonical (lex_less), farm dist+store hash, synthetic %.2f Gbp of 150 bp reads per GPU "
+                        "(30x coverage of a uniform genome, 0.5%% substitutions, 317-byte FASTQ records), %d GPU%s, "
+                        "keys owned by dist_hash %% n_gpus" % (n_reads * READ_LEN / 1e9, world, "" if world == 1 else "s"),
+            "k": K, "read_len": READ_LEN, "reads_per_gpu": n_reads, "text_bytes_per_gpu": nbytes,
+            "kmers_per_gpu": n_reads * KMERS_PER_READ, "hash": "farm (dist+store)", "seed": SEED, "err_ppm": ERR_PPM,
+            "l2": "inputs (%.2f GB text per GPU, multi-GB table) larger than the 126 MB L2; no flush needed" % (nbytes / 1e9)}
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm / cpu baseline / parity checker: the reference's own CPU code (oracle/_ref), else the C port
+# ------------------------------------------------------------------------------------------------
+def _oracle_util():
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_util as ou
     if not os.path.exists(os.path.join(ROOT, "oracle", "libkmi_oracle.so")):
         subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle"), os.path.join(ROOT, "oracle", "libkmi_oracle.so")])
-    text = ou.synth_fastq(0, n_reads, READ_LEN, genome_len, SEED, ERR_PPM, 0)
-    return ou, text
+    return ou
 
 
-def cpu_reference_rate(n_reads, threads, steps=1, warmup=0):
-    """k-mers/s of the reference's CPU path on the first n_reads reads of the workload."""
-    # a 30x slice of the workload: the genome shrinks with the sample so the duplicate structure is kept
-    ou, text = _cpu_sample(n_reads, max(int(GENOME_1GBP * (n_reads / READS_1GBP)), 10 * READ_LEN))
-    ref = ou.ref_lib("ndebug")
-    n_kmers = n_reads * KMERS_PER_READ
-    times = []
-    if ref is not None:
+def reference_build(text, threads, steps=1, warmup=0):
+    """The reference's CountIndex build of FASTQ `text` on `threads` host threads, the whole path inside the timed region:
+    per rank-thread the record walk of its record-aligned byte range (fastq_loader.hpp:389-470, restated: the parser headers
+    need mpi.h), then the reference's own Kmer::nextFromChar window, lex_less, farm KeyToRank, bucket hand-over (all2allv)
+    and google::dense_hash_map insert with count += 1 (oracle/ref_shim.cpp, compiled from /root/reference). Returns the
+    timing and the content summary (distinct keys, sum of counts, sum of mix(key) * count) the GPU index is compared with."""
+    ou = _oracle_util()
+    n_reads = text.size // REC
+    times, res = [], None
+    if ou.ref_lib("ndebug") is not None:
         kind = "reference"
-        # the record walk (restated, MPI headers do not build): sequence lines of the 317-byte records
-        recs = text.reshape(n_reads, REC)
-        seqs = np.ascontiguousarray(recs[:, 13:13 + READ_LEN]).reshape(-1)
-        off = (np.arange(n_reads + 1, dtype=np.uint64) * np.uint64(READ_LEN))
-        sizes = np.zeros(threads, dtype=np.uint64)
         for it in range(warmup + steps):
             t0 = time.perf_counter()
-            d = ref.kmiref_count_build(K, ou._ptr(seqs), ou._ptr(off), n_reads, threads, 1, None, None, 0, ou._ptr(sizes))
+            res = ou.ref_count_build_fastq(text, K, threads, 1)
             dt = time.perf_counter() - t0
             if it >= warmup:
                 times.append(dt)
-        distinct = int(d)
+        distinct = res["distinct"]
+        with np.errstate(over="ignore"):
+            ck = (int(res["ck"][:, 0].sum(dtype=np.uint64)), int(res["ck"][:, 1].sum(dtype=np.uint64)))
+        how = ("reference Kmer / lex_less / farm / google::dense_hash_map compiled from /root/reference (oracle/_ref), %d "
+               "rank-threads, FASTQ record walk restated and inside the timed region" % threads)
     else:
-        kind = "port"
-        threads = 1
+        kind, threads = "port", 1
         nk = ctypes.c_long(0)
         for it in range(warmup + steps):
             t0 = time.perf_counter()
-            d = ou.oracle().kmio_count_build_port(ou._ptr(text), text.size, K, 2, None, None, 0, ctypes.byref(nk))
+            distinct = int(ou.oracle().kmio_count_build_port(ou._ptr(text), text.size, K, 2, None, None, 0, ctypes.byref(nk)))
             dt = time.perf_counter() - t0
             if it >= warmup:
                 times.append(dt)
-        distinct = int(d)
+        ck = None
+        how = "C port oracle/kmi_oracle.c, 1 thread (oracle/_ref not built)"
     sec = float(np.mean(times))
-    return {"value": n_kmers / sec, "unit": "kmers/s", "cores": threads, "kind": kind,
-            "sample": "30x slice of the workload: %d reads (%d k-mers, %d distinct) over a proportionally smaller genome; %s" % (
-                n_reads, n_kmers, distinct,
-                "reference Kmer/lex_less/farm/dense_hash_map compiled from /root/reference, %d rank-threads, record walk restated"
-                % threads if kind == "reference" else "C port oracle/kmi_oracle.c, 1 thread"),
-            "seconds_per_step": sec}
+    n_kmers = n_reads * KMERS_PER_READ
+    return {"value": n_kmers / sec, "unit": "kmers/s", "cores": threads, "kind": kind, "seconds_per_step": sec,
+            "distinct": int(distinct), "checksum": ck, "n_kmers": n_kmers,
+            "sample": "%d reads = %.2f Gbp = %d k-mers (%d distinct): %s" % (n_reads, n_reads * READ_LEN / 1e9, n_kmers, distinct, how)}
 
 
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
     threads = os.cpu_count() or 1
-    n_reads = int(os.environ.get("KMI_REF_READS", "400000"))
-    r = cpu_reference_rate(n_reads, threads, steps=args.steps, warmup=min(args.warmup, 1))
+    n_reads = int(os.environ.get("KMI_BENCH_READS", str(READS_1GBP)))
+    ou = _oracle_util()
+    # One GPU's share of the workload (at N = 1 that IS the workload: same reads, same seed, same bytes as the GPU arm).
+    # At N > 1 the N Gbp job does not fit a host run of a few minutes: the step stays one 1 Gbp / 30x block (k-mers/s is
+    # what is compared; the CPU rate does not grow with the job).
+    text = ou.synth_fastq(0, n_reads, READ_LEN, int(GENOME_1GBP * (n_reads / READS_1GBP)), SEED, ERR_PPM, 0)
+    r = reference_build(text, threads, steps=args.steps, warmup=args.warmup)
+    sample = ("the full single-GPU workload, every step: " if world == 1 else
+              "bounded sample = one GPU's 1/%d share (a 30x block of %.2f Gbp), every step: " % (world, n_reads * READ_LEN / 1e9)) + r["sample"]
     line = {"impl": "reference", "metric": "canonical k-mers inserted/sec into count index", "value": r["value"], "unit": "kmers/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["seconds_per_step"] * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": {"workload": "CountIndex K=31 canonical, synthetic 150 bp reads (bounded sample of the 1 Gbp block), host CPU",
-                       "k": K, "read_len": READ_LEN, "hash": "farm"},
-            "cpu_baseline": {"value": r["value"], "unit": "kmers/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
-            "e2e": {"value": r["value"], "unit": "kmers/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+            "config": workload_config(world, n_reads),
+            "cpu_baseline": {"value": r["value"], "unit": "kmers/s", "cores": r["cores"], "kind": r["kind"], "sample": sample},
+            "e2e": {"value": r["value"], "unit": "kmers/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "index": {"distinct_keys": r["distinct"], "checksum": r["checksum"]}}
     print(json.dumps(line))
 
 
@@ -252,12 +271,28 @@ def run_gpu_arm(args):
     total_kmers = n_kmers_rank * world
     value = total_kmers / (ms_step * 1e-3)
 
-    # contents check outside the timed region: sum of counts == k-mers generated
+    # ---- parity of what was just measured, outside the timed region (full content, not a sum):
+    # N = 1: the reference's own CPU build of the SAME 1 Gbp of text (oracle/_ref) -> distinct keys, sum of counts and
+    # sum of mix(key) * count must equal kmi_local_size / kmi_checksum of the index the timed steps built. The same run
+    # is the cpu_baseline (it is the reference path on this box's host cores, timed).
+    parity, cpu_base = None, None
     if world == 1:
         cks = idx.checksum()
         assert cks[1] == n_kmers_rank, "sum of counts %d != k-mers %d" % (cks[1], n_kmers_rank)
         distinct = idx.size()
         info = idx.table_info()
+        if not os.environ.get("KMI_BENCH_NO_CPU"):
+            host_text = text[:nbytes].cpu().numpy()
+            ref = reference_build(host_text, os.cpu_count() or 1)
+            del host_text
+            cpu_base = {"value": ref["value"], "unit": "kmers/s", "cores": ref["cores"], "kind": ref["kind"],
+                        "sample": "the full workload, one step (also the parity checker): " + ref["sample"]}
+            parity = {"checked_against": "oracle/_ref (reference code) on the same text" if ref["kind"] == "reference" else "oracle C port",
+                      "distinct_keys": [int(distinct), ref["distinct"]], "sum_counts": [int(cks[1]), ref["n_kmers"]],
+                      "sum_mix_key_times_count": [int(cks[0]), ref["checksum"][0] if ref["checksum"] else None]}
+            ok = distinct == ref["distinct"] and (ref["checksum"] is None or (int(cks[0]), int(cks[1])) == ref["checksum"])
+            parity["ok"] = bool(ok)
+            assert ok, "index contents differ from the reference build: %r" % (parity,)
     else:
         cks = idx.local.checksum()
         tsum = torch.tensor([cks[1]], dtype=torch.int64, device=device)
@@ -352,23 +387,18 @@ def run_gpu_arm(args):
         line = {"metric": "canonical k-mers inserted/sec into count index", "value": value, "unit": "kmers/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-                "config": {"workload": "CountIndex K=31 canonical, synthetic %.2f Gbp of 150 bp reads per GPU (30x, 0.5%% subst.), %s"
-                                       % (n_reads * READ_LEN / 1e9, "1xB200 text->buckets->segment insert" if world == 1 else
-                                          "%dxB200 %s" % (world, "parse+owner scatter into peer HBM over NVLink (one kernel)->bucketed insert" if peer
-                                                         else "parse+owner scatter->NCCL all-to-all->bucketed insert")),
-                           "k": K, "read_len": READ_LEN, "reads_per_gpu": n_reads, "text_bytes_per_gpu": nbytes,
-                           "kmers_per_gpu": n_kmers_rank, "hash": "farm (dist+store)", "distinct_keys": distinct,
-                           "table_slots_per_gpu": info["slots"], "l2": "inputs (%.2f GB text, %.1f GB table) larger than L2"
-                                                                     % (nbytes / 1e9, info["slots"] * info["slot_bytes"] / 1e9)},
+                "config": workload_config(world, n_reads),
+                "index": {"distinct_keys": int(distinct), "table_slots_per_gpu": info["slots"], "table_bytes_per_gpu": info["slots"] * info["slot_bytes"],
+                          "path": "1xB200 text->buckets->segment insert" if world == 1 else
+                                  "%dxB200 %s" % (world, "parse+owner scatter into peer HBM over NVLink (one kernel)->bucketed insert" if peer
+                                                 else "parse+owner scatter->NCCL all-to-all->bucketed insert")},
                 "clocks": clocks, "gpu_launches": int(launches), "roofline": roofline}
         if e2e is not None:
             line["e2e"] = e2e
-        if world == 1 and not os.environ.get("KMI_BENCH_NO_CPU"):
-            try:
-                line["cpu_baseline"] = {k_: v_ for k_, v_ in cpu_reference_rate(int(os.environ.get("KMI_REF_READS", "400000")),
-                                                                                os.cpu_count() or 1).items() if k_ != "seconds_per_step"}
-            except Exception as ex:  # the baseline is reported, never required for the GPU number
-                line["cpu_baseline"] = {"value": None, "unit": "kmers/s", "cores": 0, "kind": "port", "sample": "failed: %s" % ex}
+        if cpu_base is not None:
+            line["cpu_baseline"] = cpu_base
+        if parity is not None:
+            line["parity"] = parity
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -16,7 +16,8 @@
 //    src/containers/distributed_map_base.hpp:286-301);
 //  - find()/count() results are in input order (the reference returns them grouped by answering
 //    rank, src/containers/distributed_densehash_map.hpp:1179-1194);
-//  - predicates (find_if / count_if / erase_if) are not offered on the device path.
+//  - predicates (find / count / erase with a functor) run on the host over the entries the device returns; the
+//    common count-threshold predicates have device-side forms (find_if_count / count_if_count / erase_if_count).
 // Errors: KMI_ERR_ARG -> std::invalid_argument, KMI_ERR_FORMAT -> std::logic_error (as
 // fastq_loader.hpp:393,419,435 throws), anything else -> std::runtime_error.
 #ifndef KMI_INDEX_HPP_
@@ -77,6 +78,7 @@ struct Kmer {
   uint64_t data[nWords];
   Kmer() { for (unsigned i = 0; i < nWords; ++i) data[i] = 0; }
   const uint64_t* getData() const { return data; }
+  uint64_t (&getDataRef())[nWords] { return data; }
   /// Kmer::nextFromChar (kmer.hpp:731-741) for a 2-bit code
   void nextFromChar(uint8_t code) {
     if (nWords == 1) {
@@ -105,6 +107,33 @@ struct Kmer {
     return false;
   }
 };
+
+/// lex_less on the word array of a 2-bit DNA k-mer (kmer_transform.hpp:109-126; reverse_complement kmer.hpp:1118-1123),
+/// for ANY key type with the reference's layout — this is what lets b200_map take bliss::common::Kmer<K, DNA, uint64_t>
+/// (whose `data` is private) as well as kmi::Kmer<K>. w: nw words, word 0 least significant.
+inline void canonical_words(uint64_t* w, unsigned k) {
+  const unsigned nw = k <= 32 ? 1 : 2;
+  auto rev2 = [](uint64_t x) {   // reverse the 32 two-bit groups of a word
+    x = ((x >> 2) & 0x3333333333333333ULL) | ((x & 0x3333333333333333ULL) << 2);
+    x = ((x >> 4) & 0x0F0F0F0F0F0F0F0FULL) | ((x & 0x0F0F0F0F0F0F0F0FULL) << 4);
+    x = ((x >> 8) & 0x00FF00FF00FF00FFULL) | ((x & 0x00FF00FF00FF00FFULL) << 8);
+    x = ((x >> 16) & 0x0000FFFF0000FFFFULL) | ((x & 0x0000FFFF0000FFFFULL) << 16);
+    return (x >> 32) | (x << 32);
+  };
+  uint64_t rc[2] = {0, 0};
+  if (nw == 1) {
+    rc[0] = (~rev2(w[0])) >> (64 - 2 * k);
+  } else {
+    const unsigned s = 128 - 2 * k;   // pad bits, 2..62
+    const uint64_t hi = ~rev2(w[0]), lo = ~rev2(w[1]);
+    rc[0] = (lo >> s) | (hi << (64 - s));
+    rc[1] = hi >> s;
+  }
+  bool rc_less = false;
+  for (int i = (int)nw - 1; i >= 0; --i)
+    if (rc[i] != w[i]) { rc_less = rc[i] < w[i]; break; }
+  if (rc_less) for (unsigned i = 0; i < nw; ++i) w[i] = rc[i];
+}
 
 /// what the adapter needs from mxx::comm (rank / size); one process drives one GPU shard
 struct comm {
@@ -141,12 +170,10 @@ class b200_map {
   using const_iterator = typename std::vector<value_type>::const_iterator;
   static constexpr unsigned K = Key::size;
 
-  explicit b200_map(const comm& c = comm(), const map_options& o = map_options()) : comm_(c), canonical_(o.canonical) {
-    kmi_config cfg;
-    cfg.k = (int32_t)K; cfg.mode = Mode; cfg.canonical = o.canonical ? 1 : 0; cfg.hash = o.hash; cfg.nsplit = o.nsplit ? 1 : 0;
-    cfg.device = o.device; cfg.rank = c.rank(); cfg.nranks = c.size(); cfg.reserve = o.reserve;
-    check(kmi_create(&cfg, &h_));
-  }
+  /// Comm: anything with rank() and size() — mxx::comm (Index::Index(const mxx::comm&), kmer_index.hpp:115) or kmi::comm
+  template <typename Comm>
+  explicit b200_map(const Comm& c, const map_options& o = map_options()) : comm_(c.rank(), c.size()), canonical_(o.canonical) { create(o); }
+  explicit b200_map(const map_options& o = map_options()) : comm_(), canonical_(o.canonical) { create(o); }
   ~b200_map() { kmi_destroy(h_); }
   b200_map(const b200_map&) = delete;
   b200_map& operator=(const b200_map&) = delete;
@@ -162,7 +189,7 @@ class b200_map {
   size_t insert(std::vector<value_type>& tuples) {
     std::vector<uint64_t> k(tuples.size() * nw()), v(tuples.size());
     for (size_t i = 0; i < tuples.size(); ++i) {
-      std::memcpy(&k[i * nw()], &tuples[i].first, sizeof(Key));
+      std::memcpy(&k[i * nw()], tuples[i].first.getData(), sizeof(Key));
       uint64_t id = 0;
       std::memcpy(&id, &tuples[i].second, sizeof(T) < 8 ? sizeof(T) : 8);
       v[i] = id;
@@ -296,7 +323,7 @@ class b200_map {
     out.reserve(got);
     for (size_t i = 0; i < got; ++i) {
       Key key;
-      std::memcpy(key.data, &k[i * nw()], sizeof(Key));
+      std::memcpy(key.getDataRef(), &k[i * nw()], sizeof(Key));
       out.emplace_back(key, from_u64(v[i]));
     }
   }
@@ -331,7 +358,13 @@ class b200_map {
   static constexpr size_t nw() { return sizeof(Key) / 8; }
   /// distributed_map_base::transform_input (distributed_map_base.hpp:286-289): queries become canonical in place
   void transform_input(std::vector<Key>& keys) const {
-    if (canonical_) for (Key& k : keys) k = k.canonical();
+    if (canonical_) for (Key& k : keys) canonical_words(k.getDataRef(), K);
+  }
+  void create(const map_options& o) {
+    kmi_config cfg;
+    cfg.k = (int32_t)K; cfg.mode = Mode; cfg.canonical = o.canonical ? 1 : 0; cfg.hash = o.hash; cfg.nsplit = o.nsplit ? 1 : 0;
+    cfg.device = o.device; cfg.rank = comm_.rank(); cfg.nranks = comm_.size(); cfg.reserve = o.reserve;
+    check(kmi_create(&cfg, &h_));
   }
   /// per query key i its values vals[off[i] .. off[i+1]): COUNT 0 or 1 value (the frequency), POSITION every id
   void lookup(std::vector<Key>& keys, std::vector<uint64_t>& off, std::vector<uint64_t>& vals) const {

@@ -82,6 +82,8 @@ struct kmi_index {
   u64* ctr = nullptr;      // device counters (CTR_N x u64)
   u64 size_exact = 0;      // last size read back
   u64 size_upper = 0;      // upper bound on the current size (exact + keys issued since)
+  u64 tombstones = 0;      // DELETED slots in the table: they occupy probe sequences like live keys (dense_hash_map counts
+                           // them in its resize decision too); dropped by the next rehash
   // scratch
   DevBuf mid_keys, mid_cur;        // first of two fine passes (very large tables)
   DevBuf parse_keys, parse_ids;   // staging of the parse -> insert builds (FASTA, FASTQ positions): kept between calls
@@ -163,11 +165,16 @@ static int zero_ctr(kmi_index* idx, int which, int count = 1) {
   CU(cudaMemsetAsync(idx->ctr + which, 0, sizeof(u64) * count, idx->stream));
   return KMI_OK;
 }
+// CTR_ERR holds the sticky TERR_* bits (cleared by kmi_clear only)
+static int table_error(u64 e) {
+  if (e & TERR_SPILL) return fail(KMI_ERR_CAPACITY, "segment spill list exhausted (keys homed past their table segment's end): index contents are incomplete");
+  if (e) return fail(KMI_ERR_CAPACITY, "hash table overflow (probe limit reached)");
+  return KMI_OK;
+}
 static int check_table_error(kmi_index* idx) {
   u64 e = 0;
   OK(read_ctr(idx, CTR_ERR, &e));
-  if (e) return fail(KMI_ERR_CAPACITY, "hash table overflow (probe limit reached)");
-  return KMI_OK;
+  return table_error(e);
 }
 
 // allocate a table of `cap` slots (contents undefined: the caller clears it or marks the index virgin)
@@ -200,6 +207,7 @@ static int table_grow(kmi_index* idx, u64 new_cap) {
   }
   OK(read_ctr(idx, CTR_SIZE, &idx->size_exact));
   idx->size_upper = idx->size_exact;
+  idx->tombstones = 0;                                  // the rehash copies live keys only
   return KMI_OK;
 }
 
@@ -211,7 +219,8 @@ static int table_room(kmi_index* idx, u64 incoming, u64* grant) {
   if (!idx->slots) OK(table_grow(idx, pow2_at_least((u64)(std::min<u64>(incoming, 1u << 20) / MAX_LOAD) + 1)));
   for (;;) {
     u64 limit = (u64)(idx->cap * MAX_LOAD);
-    u64 slack = limit > idx->size_upper ? limit - idx->size_upper : 0;
+    const u64 occupied = idx->size_upper + idx->tombstones;
+    u64 slack = limit > occupied ? limit - occupied : 0;
     if (slack >= incoming) { *grant = incoming; break; }
     // refresh the bound
     if (idx->size_upper != idx->size_exact) {
@@ -221,7 +230,9 @@ static int table_room(kmi_index* idx, u64 incoming, u64* grant) {
     }
     u64 min_chunk = std::max<u64>(idx->cap / 8, 1u << 12);
     if (slack >= min_chunk) { *grant = std::min(slack, incoming); break; }
-    OK(table_grow(idx, idx->cap * 2));
+    // tombstones alone may be what fills the table: then a rehash at the same capacity purges them
+    const bool purge = idx->tombstones && idx->size_upper + std::min(incoming, idx->cap / 4) <= limit;
+    OK(table_grow(idx, purge ? idx->cap : idx->cap * 2));
   }
   idx->size_upper += *grant;
   return KMI_OK;
@@ -321,6 +332,7 @@ extern "C" int kmi_clear(kmi_index* idx) {
   idx->virgin = idx->slots != nullptr;                  // cleared lazily (kmi_index::touch) or never (segment insert)
   CU(cudaMemsetAsync(idx->ctr, 0, sizeof(u64) * CTR_N, idx->stream));
   idx->size_exact = idx->size_upper = 0;
+  idx->tombstones = 0;
   idx->log_n = 0;
   idx->csr_dirty = false;
   idx->non_hll_upper = 0;
@@ -399,9 +411,9 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
   const double est = hll_estimate(reg.data()) * (double)HLL_SAMPLE;
   const u64 by_hll = (u64)(est * 1.05 + 6.0 * std::sqrt(est * (double)HLL_SAMPLE)) + 4096 + idx->non_hll_upper;
   const u64 need = std::min(size_now + n_keys, std::max(by_hll, size_now));
-  if (!idx->slots || (double)need > idx->cap * MAX_LOAD) {
+  if (!idx->slots || (double)(need + idx->tombstones) > idx->cap * MAX_LOAD) {
     u64 want = pow2_at_least((u64)(need / MAX_LOAD) + 1);
-    if (want > idx->cap) OK(table_grow(idx, want));
+    if (want > idx->cap || idx->tombstones) OK(table_grow(idx, std::max(want, idx->cap)));   // same capacity: purge tombstones
   }
   idx->size_upper = need;
   idx->size_exact = ~0ULL;  // stale until read back
@@ -624,9 +636,9 @@ static int fastq_rec_carry(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64
 static int parse_error(u64 perr) {
   if (perr & PERR_NO_AT) return fail(KMI_ERR_FORMAT, "malformed FASTQ: missing @ on first line of a record");
   if (perr & PERR_NO_PLUS) return fail(KMI_ERR_FORMAT, "malformed FASTQ: missing + on third line of a record");
+  if (perr & PERR_ID_RANGE) return fail(KMI_ERR_ARG, "FASTQ record longer than 64 KiB: ShortSequenceKmerId cannot hold the k-mer's offset in its record");
   if (perr & PERR_OVERFLOW) return fail(KMI_ERR_CAPACITY, "k-mer output buffer too small");
   if (perr & PERR_HALO) return fail(KMI_ERR_FORMAT, "FASTA line structure too sparse for the tile halo");
-  if (perr & PERR_SPILL) return fail(KMI_ERR_CAPACITY, "segment spill list exhausted: index contents are incomplete");
   return KMI_OK;
 }
 
@@ -1062,7 +1074,7 @@ static int build_fastq_impl(kmi_index* idx, uint8_t* d_bytes, size_t n, const ui
   }
   idx->size_exact = idx->size_upper = host[CTR_SIZE];
   if (n_kmers) *n_kmers = host[CTR_NKMERS];
-  if (host[CTR_ERR]) return fail(KMI_ERR_CAPACITY, "hash table overflow (probe limit reached)");
+  OK(table_error(host[CTR_ERR]));
   return parse_error(host[CTR_PERR]);
 }
 
@@ -1294,6 +1306,8 @@ extern "C" int kmi_erase(kmi_index* idx, const uint64_t* keys, size_t n) {
   if (n == 0 || !idx->slots) return KMI_OK;
   OK(stage_query(idx, keys, n));
   OK(zero_ctr(idx, CTR_REMOVED));
+  u64 live_before = 0;
+  OK(read_ctr(idx, CTR_SIZE, &live_before));
   idx->ops->erase(idx->stream, idx->view(), idx->stage_keys.as<u64>(), n, idx->ctr + CTR_REMOVED, idx->cfg.canonical != 0);
   idx->launches++;
   if (idx->cfg.mode == KMI_MODE_POSITION && idx->log_n) {
@@ -1315,6 +1329,7 @@ extern "C" int kmi_erase(kmi_index* idx, const uint64_t* keys, size_t n) {
   }
   OK(read_ctr(idx, CTR_SIZE, &idx->size_exact));
   idx->size_upper = idx->size_exact;
+  idx->tombstones += live_before - idx->size_exact;
   return KMI_OK;
 }
 
@@ -1958,7 +1973,8 @@ struct KmiFileHeader {
   char magic[8];        // "KMIDX001"
   uint32_t k, mode, nw, canonical;
   uint64_t n_entries;
-  uint64_t reserved[4];
+  uint32_t hash, rank, nranks, flags;   // hash kind and shard of the index that wrote the file (flags bit 0: fields valid)
+  uint64_t reserved[2];
 };
 static_assert(sizeof(KmiFileHeader) == 64, "header is 64 bytes");
 struct FileGuard { FILE* f; ~FileGuard() { if (f) fclose(f); } };
@@ -1984,6 +2000,7 @@ extern "C" int kmi_save(kmi_index* idx, const char* path) {
   memcpy(h.magic, "KMIDX001", 8);
   h.k = (uint32_t)idx->cfg.k; h.mode = (uint32_t)idx->cfg.mode; h.nw = (uint32_t)nw; h.canonical = idx->cfg.canonical ? 1u : 0u;
   h.n_entries = got;
+  h.hash = (uint32_t)idx->cfg.hash; h.rank = (uint32_t)idx->cfg.rank; h.nranks = (uint32_t)idx->cfg.nranks; h.flags = 1u;
   bool ok = fwrite(&h, sizeof(h), 1, g.f) == 1;
   std::vector<uint64_t> out(1u << 16);
   for (uint64_t i = 0; ok && i < got;) {            // keys, then values, in sorted order
@@ -2009,6 +2026,15 @@ extern "C" int kmi_load(kmi_index* idx, const char* path, uint64_t* n_entries) {
   if (fread(&h, sizeof(h), 1, g.f) != 1 || memcmp(h.magic, "KMIDX001", 8) != 0) return fail(KMI_ERR_FORMAT, "%s is not a kmi index file", path);
   if ((int)h.k != idx->cfg.k || (int)h.mode != idx->cfg.mode || (int)h.nw != idx->nw)
     return fail(KMI_ERR_ARG, "%s holds a K=%u mode-%u index, this one is K=%d mode-%d", path, h.k, h.mode, idx->cfg.k, idx->cfg.mode);
+  // A canonical index stores lex_less keys: loading non-canonical entries into it would merge strands silently, and
+  // entries of a canonical file are not what a non-canonical index would hold. A shard file belongs to owner `rank` of
+  // `nranks` under `hash`: it may be loaded into a single-shard index (merge) or into the same shard of the same layout.
+  if ((h.canonical != 0) != (idx->cfg.canonical != 0))
+    return fail(KMI_ERR_ARG, "%s holds %s keys, this index is %s", path, h.canonical ? "canonical" : "non-canonical", idx->cfg.canonical ? "canonical" : "non-canonical");
+  if ((h.flags & 1u) && idx->cfg.nranks > 1 &&
+      ((int)h.nranks != idx->cfg.nranks || (int)h.rank != idx->cfg.rank || (int)h.hash != idx->cfg.hash))
+    return fail(KMI_ERR_ARG, "%s is shard %u of %u (hash %u); this index is shard %d of %d (hash %d)", path, h.rank, h.nranks, h.hash,
+                idx->cfg.rank, idx->cfg.nranks, idx->cfg.hash);
   const size_t nw = (size_t)idx->nw;
   const uint64_t CH = 1u << 24;                      // entries per insert
   std::vector<uint64_t> keys, vals;

@@ -15,6 +15,7 @@ static constexpr u32 PERR_NO_AT = 1u;    // fastq_loader.hpp:393,419
 static constexpr u32 PERR_NO_PLUS = 2u;  // fastq_loader.hpp:435
 static constexpr u32 PERR_OVERFLOW = 4u; // output capacity exceeded
 static constexpr u32 PERR_HALO = 8u;     // FASTA: K-1 bases do not fit the halo (retry wider)
+static constexpr u32 PERR_ID_RANGE = 32u; // FASTQ position id: offset inside the record >= 2^16 (sequence.hpp:177-183)
 
 template <int NW> __device__ __forceinline__ Key<NW> load_key(const u64* __restrict__ keys, u64 i) {
   Key<NW> k;

@@ -302,7 +302,6 @@ static constexpr int MAX_LOG_F = KMI_MAX_LOG_F;
 #define KMI_FINE_ROUND 2048
 #endif
 static constexpr int FINE_ROUND = KMI_FINE_ROUND;         // keys per CTA round of the second scatter
-static constexpr u32 PERR_SPILL = 16u;                    // overflow region exhausted by segment spills (fatal)
 
 struct FineSink {
   u64* keys;       // (N_BUCKETS << log_f) regions of capf keys
@@ -596,7 +595,7 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
         } else if (++li == SEG) {
           const u32 o = atomicAdd(bs.cursor + N_BUCKETS, 1u);
           if (o < bs.ovf_cap) bs.keys[(u64)N_BUCKETS * bs.capb + o] = key;
-          else atomicOr(perr, PERR_SPILL);
+          else atomicOr(t.error, TERR_SPILL);   // dropped: sticky table error, every caller's check_table_error sees it
           key = KEY_EMPTY_TOP;
         }
       }
@@ -783,7 +782,7 @@ k_insert_segments2(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, c
         if (++li == SEG) {                                 // ran off the segment: global linear probe continues there
           const u32 o = atomicAdd(bs.cursor + N_BUCKETS, 1u);
           if (o < bs.ovf_cap) reinterpret_cast<ulonglong2*>(bs.keys)[(u64)N_BUCKETS * bs.capb + o] = key;
-          else atomicOr(perr, PERR_SPILL);
+          else atomicOr(t.error, TERR_SPILL);   // dropped: sticky table error, every caller's check_table_error sees it
           break;
         }
       }

@@ -581,6 +581,9 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
         if (own && own - 1u <= first) rec = tile_off + own - 1u;
         else if (rs.before[g]) rec = tile_off + rs.before[g] - 1u;
         else rec = sink.tile_rec[tile] - 1u;                 // record opened in an earlier tile (0 - 1 if none: malformed, flagged by PERR_NO_AT)
+        // offset of the k-mer inside its record must fit 16 bits (ShortSequenceKmerId::operator+= throws otherwise,
+        // src/common/sequence.hpp:177-183)
+        if (tile_off + pos0 + (u32)(31 - __clz((int)v)) - rec > 0xFFFFull) atomicOr(perr, PERR_ID_RANGE);
         id0 = (((sink.file_offset + rec) & 0xFFFFFFFFFFULL) << 16) + (tile_off + pos0 - rec);
       }
     }

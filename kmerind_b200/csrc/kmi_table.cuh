@@ -13,13 +13,16 @@ template <int NW> struct Slot;
 template <> struct alignas(16) Slot<1> { u64 key; u32 val; u32 aux; };
 template <> struct alignas(32) Slot<2> { u64 lo; u64 hi; u32 val; u32 aux; u64 pad; };
 
+static constexpr u32 TERR_FULL = 1u, TERR_SPILL = 2u;
+
 struct TableView {
   void* slots;
   u64 mask;        // slots - 1
   u32 shift;       // 64 - log2(slots): home slot = store_hash >> shift (TOP bits, so that a hash
                    // prefix names a contiguous table segment for any capacity: kmi_bucket.cuh)
   u64* size;       // device counter: occupied (live) keys
-  u32* error;      // device flag: 1 = probe limit hit (table full)
+  u32* error;      // device flags, sticky until kmi_clear: TERR_FULL probe limit hit (table full), TERR_SPILL a segment insert
+                   // dropped a key because the spill list was exhausted (kmi_bucket.cuh)
 };
 
 // ---- raw slot access -----------------------------------------------------------------------
@@ -76,7 +79,7 @@ __device__ __forceinline__ u64 table_upsert(const TableView& t, const Key<NW>& k
     }
     i = (i + 1) & t.mask;
   }
-  atomicExch(t.error, 1u);
+  atomicOr(t.error, TERR_FULL);
   return ~0ULL;
 }
 

@@ -9,6 +9,24 @@
 
 #include "kmi_index.hpp"
 
+// -DKMI_CHECK_BLISS: the key type is the REFERENCE's bliss::common::Kmer<K, DNA, uint64_t> (compiled against
+// /root/reference/src where it lies; oracle/Makefile builds that flavour into oracle/_ref/adapter_check_bliss), otherwise the
+// self-contained kmi::Kmer<K>. Everything below is written against the members both have.
+#ifdef KMI_CHECK_BLISS
+#include "common/alphabets.hpp"
+#include "common/kmer.hpp"
+#include "common/kmer_transform.hpp"
+template <unsigned K> using KeyT = bliss::common::Kmer<K, bliss::common::DNA, uint64_t>;
+template <typename Key> static Key canon(const Key& k) { return bliss::kmer::transform::lex_less<Key>()(k); }
+struct ref_like_comm { int rank() const { return 0; } int size() const { return 1; } };   // stands in for mxx::comm (rank()/size())
+#define KEY_FLAVOUR "bliss::common::Kmer"
+#else
+template <unsigned K> using KeyT = kmi::Kmer<K>;
+template <typename Key> static Key canon(const Key& k) { return k.canonical(); }
+typedef kmi::comm ref_like_comm;
+#define KEY_FLAVOUR "kmi::Kmer"
+#endif
+
 #define CHECK(c)                                                     \
   do {                                                               \
     if (!(c)) {                                                      \
@@ -18,8 +36,8 @@
   } while (0)
 
 template <unsigned K>
-static kmi::Kmer<K> random_kmer(std::mt19937_64& rng) {
-  kmi::Kmer<K> k;
+static KeyT<K> random_kmer(std::mt19937_64& rng) {
+  KeyT<K> k;
   for (unsigned i = 0; i < K; ++i) k.nextFromChar((uint8_t)(rng() & 3));
   return k;
 }
@@ -31,8 +49,8 @@ static void sort_pairs(std::vector<Pair>& v) {
 
 template <unsigned K>
 static int count_checks() {
-  using Key = kmi::Kmer<K>;
-  using Map = kmi::CountIndex<K>;
+  using Key = KeyT<K>;
+  using Map = kmi::b200_map<Key, uint32_t, KMI_MODE_COUNT>;
   using V = typename Map::value_type;
   std::mt19937_64 rng(K);
   std::vector<Key> pool;
@@ -43,10 +61,10 @@ static int count_checks() {
     input.push_back((rng() & 1) ? k : k.reverse_complement());
   }
   std::map<Key, uint32_t> want;
-  for (const Key& k : input) want[k.canonical()]++;
+  for (const Key& k : input) want[canon(k)]++;
   kmi::map_options o;
   o.hash = KMI_HASH_FARM;
-  Map idx(kmi::comm(), o);
+  Map idx(ref_like_comm(), o);
   idx.insert(input);
   CHECK(idx.local_size() == want.size() && idx.size() == want.size());
   CHECK(idx.get_multiplicity() == 1.0f);
@@ -64,10 +82,10 @@ static int count_checks() {
       Key k = (i % 3) ? pool[rng() % 3000] : random_kmer<K>(rng);
       uint32_t c = (uint32_t)(rng() % 1000);
       tuples.emplace_back(k.reverse_complement(), c);
-      want[k.canonical()] += c;
+      want[canon(k)] += c;
     }
     tuples.emplace_back(pool[0], 0xFFFFFFF0u);       // std::plus<uint32_t> wraps
-    want[pool[0].canonical()] += 0xFFFFFFF0u;
+    want[canon(pool[0])] += 0xFFFFFFF0u;
     idx.insert(tuples);
     CHECK(idx.local_size() == want.size());
     all = idx.to_vector();
@@ -83,20 +101,20 @@ static int count_checks() {
     std::vector<Key> qq = q;
     std::vector<V> got = idx.find(qq);
     size_t hits = 0;
-    for (const Key& k : q) hits += want.count(k.canonical());
+    for (const Key& k : q) hits += want.count(canon(k));
     CHECK(got.size() == hits);
     for (const V& v : got) CHECK(want.count(v.first) && want[v.first] == v.second);   // canonical keys come back
     qq = q;
     auto cnt = idx.count(qq);
     CHECK(cnt.size() == q.size());
-    for (size_t i = 0; i < q.size(); ++i) CHECK(cnt[i].first == q[i].canonical() && cnt[i].second == want.count(q[i].canonical()));
+    for (size_t i = 0; i < q.size(); ++i) CHECK(cnt[i].first == canon(q[i]) && cnt[i].second == want.count(canon(q[i])));
   }
   auto often = [](const V& v) { return v.second >= 3; };
   {
     std::vector<Key> qq = q;
     std::vector<V> got = idx.find(qq, false, often);
     size_t hits = 0;
-    for (const Key& k : q) { auto it = want.find(k.canonical()); hits += (it != want.end() && it->second >= 3) ? 1 : 0; }
+    for (const Key& k : q) { auto it = want.find(canon(k)); hits += (it != want.end() && it->second >= 3) ? 1 : 0; }
     CHECK(got.size() == hits);
     for (const V& v : got) CHECK(v.second >= 3 && want[v.first] == v.second);
     std::vector<V> every = idx.find(often);
@@ -106,7 +124,7 @@ static int count_checks() {
     qq = q;
     auto cnt = idx.count(qq, false, often);
     for (size_t i = 0; i < q.size(); ++i) {
-      auto it = want.find(q[i].canonical());
+      auto it = want.find(canon(q[i]));
       CHECK(cnt[i].second == ((it != want.end() && it->second >= 3) ? 1u : 0u));
     }
     auto per_key = idx.count(often);
@@ -120,7 +138,7 @@ static int count_checks() {
     std::vector<Key> half(q.begin(), q.begin() + q.size() / 2);
     size_t expect = 0;
     for (const Key& k : half) {
-      auto it = want.find(k.canonical());
+      auto it = want.find(canon(k));
       if (it != want.end() && it->second >= 3) { want.erase(it); ++expect; }
     }
     CHECK(idx.erase(half, false, often) == expect);
@@ -134,7 +152,7 @@ static int count_checks() {
     CHECK(idx.local_size() == want.size());
     std::vector<Key> some(q.begin() + q.size() / 2, q.begin() + q.size() / 2 + 300);
     expect = 0;
-    for (const Key& k : some) expect += want.erase(k.canonical());
+    for (const Key& k : some) expect += want.erase(canon(k));
     CHECK(idx.erase(some) == expect);
     all = idx.to_vector();
     sort_pairs(all);
@@ -147,8 +165,8 @@ static int count_checks() {
 
 template <unsigned K>
 static int position_checks() {
-  using Key = kmi::Kmer<K>;
-  using Map = kmi::PositionIndex<K>;
+  using Key = KeyT<K>;
+  using Map = kmi::b200_map<Key, uint64_t, KMI_MODE_POSITION>;
   using V = typename Map::value_type;
   std::mt19937_64 rng(100 + K);
   std::vector<Key> pool;
@@ -159,7 +177,7 @@ static int position_checks() {
     tuples.emplace_back((rng() & 1) ? k : k.reverse_complement(), (uint64_t)(rng() % 64));   // few ids: (key, id) repeats happen
   }
   std::vector<V> want;
-  for (const V& t : tuples) want.emplace_back(t.first.canonical(), t.second);
+  for (const V& t : tuples) want.emplace_back(canon(t.first), t.second);
   sort_pairs(want);
   Map idx;
   idx.insert(tuples);
@@ -177,7 +195,7 @@ static int position_checks() {
     std::vector<Key> qq = q;
     std::vector<V> got = idx.find(qq), expect;
     for (const Key& k : q) {
-      auto it = by_key.find(k.canonical());
+      auto it = by_key.find(canon(k));
       if (it != by_key.end()) for (uint64_t v : it->second) expect.emplace_back(it->first, v);
     }
     sort_pairs(got); sort_pairs(expect);
@@ -185,14 +203,14 @@ static int position_checks() {
     qq = q;
     auto cnt = idx.count(qq);
     for (size_t i = 0; i < q.size(); ++i) {
-      auto it = by_key.find(q[i].canonical());
+      auto it = by_key.find(canon(q[i]));
       CHECK(cnt[i].second == (it == by_key.end() ? 0 : it->second.size()));
     }
     auto odd = [](const V& v) { return (v.second & 1) != 0; };
     qq = q;
     auto codd = idx.count(qq, false, odd);
     for (size_t i = 0; i < q.size(); ++i) {
-      auto it = by_key.find(q[i].canonical());
+      auto it = by_key.find(canon(q[i]));
       size_t c = 0;
       if (it != by_key.end()) for (uint64_t v : it->second) c += v & 1;
       CHECK(codd[i].second == c);
@@ -200,7 +218,7 @@ static int position_checks() {
     // erase the odd ids of the queried keys: single values leave their key
     size_t removed = 0;
     std::vector<Key> uq;
-    for (const Key& k : q) uq.push_back(k.canonical());
+    for (const Key& k : q) uq.push_back(canon(k));
     std::sort(uq.begin(), uq.end());
     uq.erase(std::unique(uq.begin(), uq.end()), uq.end());
     for (const Key& k : uq) {
@@ -238,6 +256,6 @@ int main() {
   if (count_checks<63>()) return 1;
   if (position_checks<21>()) return 1;
   if (position_checks<35>()) return 1;
-  std::printf("adapter ok\n");
+  std::printf("adapter ok (%s)\n", KEY_FLAVOUR);
   return 0;
 }

@@ -63,7 +63,50 @@ def ref_lib(flavour="ndebug"):
     lib.kmiref_sentinels.argtypes = [ctypes.c_int, _P]
     lib.kmiref_count_build.restype = _SZ
     lib.kmiref_count_build.argtypes = [ctypes.c_int, _P, _P, _SZ, ctypes.c_int, ctypes.c_int, _P, _P, _SZ, _P]
+    lib.kmiref_count_build_fastq.restype = _SZ
+    lib.kmiref_count_build_fastq.argtypes = [ctypes.c_int, _P, _SZ, ctypes.c_int, ctypes.c_int, _P, _P, _P, _SZ, _P, _P]
+    lib.kmiref_owner_checksums_fastq.restype = ctypes.c_int
+    lib.kmiref_owner_checksums_fastq.argtypes = [ctypes.c_int, _P, _SZ, ctypes.c_int, ctypes.c_int, ctypes.c_int, _P]
     return lib
+
+
+def ref_count_build_fastq(text, k, p, hash_kind=1, cuts=None, want_dump=False, flavour="ndebug"):
+    """The reference's p-rank CountIndex build over FASTQ text (oracle/_ref: reference Kmer / lex_less / hashes /
+    dense_hash_map, record walk restated). Returns dict(distinct, sizes[p], ck[p][2]) (+ keys, counts unsorted)."""
+    lib = ref_lib(flavour)
+    if lib is None:
+        return None
+    nw = nwords(k)
+    sizes = np.zeros(p, dtype=np.uint64)
+    ck = np.zeros(2 * p, dtype=np.uint64)
+    c = np.ascontiguousarray(cuts, dtype=np.uint64) if cuts is not None else None
+    keys = counts = None
+    cap = 0
+    if want_dump:
+        cap = int(text.size) // 2 + 1
+        keys = np.zeros(cap * nw, dtype=np.uint64)
+        counts = np.zeros(cap, dtype=np.uint32)
+    d = lib.kmiref_count_build_fastq(k, _ptr(text), int(text.size), p, hash_kind, _ptr(c), _ptr(keys), _ptr(counts), cap,
+                                     _ptr(sizes), _ptr(ck))
+    if d == (1 << 64) - 1:
+        raise ValueError("reference walk: malformed FASTQ")
+    out = {"distinct": int(d), "sizes": sizes, "ck": ck.reshape(p, 2)}
+    if want_dump:
+        out["keys"] = shape_keys(keys[:int(d) * nw], k)
+        out["counts"] = counts[:int(d)]
+    return out
+
+
+def ref_owner_checksums_fastq(text, k, p_owners, hash_kind=1, threads=1, flavour="ndebug"):
+    """per owner rank [sum of mix(key) over k-mer occurrences, number of occurrences] of this text (additive over texts)"""
+    lib = ref_lib(flavour)
+    if lib is None:
+        return None
+    out = np.zeros(2 * p_owners, dtype=np.uint64)
+    rc = lib.kmiref_owner_checksums_fastq(k, _ptr(text), int(text.size), threads, p_owners, hash_kind, _ptr(out))
+    if rc != 0:
+        raise ValueError("reference walk: malformed FASTQ (%d)" % rc)
+    return out.reshape(p_owners, 2)
 
 
 def read_fixture(name):

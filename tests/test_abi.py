@@ -58,6 +58,26 @@ def test_cpp_adapter_compiles(tmp_path):
                            str(tmp_path / "t"), "-Wl,-rpath," + os.path.dirname(kb.LIB_PATH)])
 
 
+REFERENCE = "/root/reference"
+
+
+@pytest.mark.parametrize("flavour", ["kmi", "bliss"])
+def test_adapter_check_compiles_with_both_key_types(flavour, tmp_path):
+    """tests/cpp/adapter_check.cpp (every member Index<MapType,KmerParser> forwards to, kmer_index.hpp:115-194) instantiates
+    kmi::b200_map with kmi::Kmer<K> and — where the reference tree is present — with the reference's own
+    bliss::common::Kmer<K, DNA, uint64_t> (private data, no canonical() member) and a comm type that only has rank()/size(),
+    as mxx::comm does. Compile + link only: running it needs a GPU (tests/test_gpu_parity.py)."""
+    cmd = ["g++", "-std=c++11", "-O0", "-w", "-I", os.path.join(ROOT, "include")]
+    if flavour == "bliss":
+        if not os.path.isdir(os.path.join(REFERENCE, "src")):
+            pytest.skip("reference tree not present (GPU box): the prebuilt oracle/_ref/adapter_check_bliss is run instead")
+        cmd += ["-DKMI_CHECK_BLISS", "-DNDEBUG", "-I", os.path.join(ROOT, "oracle", "refcfg"), "-I", os.path.join(REFERENCE, "src"),
+                "-I", os.path.join(REFERENCE, "ext")]
+    cmd += [os.path.join(ROOT, "tests", "cpp", "adapter_check.cpp"), kb.LIB_PATH, "-o", str(tmp_path / "t"),
+            "-Wl,-rpath," + os.path.dirname(kb.LIB_PATH)]
+    subprocess.check_call(cmd)
+
+
 def test_argument_validation_and_no_cpu_fallback(lib):
     import torch
     h = ctypes.c_void_p()

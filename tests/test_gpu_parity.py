@@ -599,6 +599,18 @@ def test_cpp_adapter_against_std_containers(tmp_path):
     assert r.returncode == 0 and "adapter ok" in r.stdout, r.stdout + r.stderr
 
 
+def test_cpp_adapter_with_the_reference_key_type():
+    """The same checks with Key = bliss::common::Kmer<K, DNA, uint64_t>: the binary was compiled against the reference's
+    headers where they lie (oracle/Makefile -> oracle/_ref/adapter_check_bliss; the headers do not travel to the GPU box)."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "oracle", "_ref", "adapter_check_bliss")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/adapter_check_bliss not built (needs /root/reference at build time)")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "adapter ok (bliss::common::Kmer)" in r.stdout, r.stdout + r.stderr
+
+
 @pytest.mark.parametrize("name,k,chunk", [("natural.fastq", 21, 3000), ("test.medium.fastq", 31, 5000), ("natural.withN.fastq", 15, 1 << 28)])
 def test_build_file_fastq_streams_record_aligned_chunks(name, k, chunk, tmp_path, monkeypatch):
     """kmi_build_file: the file is read in chunks that end at record boundaries (the rest is carried into the next buffer);
@@ -714,3 +726,86 @@ def test_save_and_load_round_trip(tmp_path):
             idx.load(p)      # a position file into a count index
         with pytest.raises(kb.KmiError):
             idx.load(str(tmp_path / "missing.kmi"))
+
+
+def _slot_hash_u64(keys):
+    """kmi_device.cuh slot_hash for one-word keys, in numpy (mod 2^64)."""
+    with np.errstate(over="ignore"):
+        h = keys.astype(np.uint64) * np.uint64(0x9E3779B97F4A7C15)
+        h ^= h >> np.uint64(32)
+        h *= np.uint64(0xD6E8FEB86659FD93)
+    return h
+
+
+@pytest.mark.parametrize("n_keys,expect_error", [(3000, False), (40000, True)])
+def test_segment_spills_are_exact_or_reported(n_keys, expect_error):
+    """Keys whose home slot is one of the last slots of their shared-memory table segment run off the segment end and
+    'spill' to the overflow list, which is inserted with global atomics afterwards. A few thousand of them must come out
+    exact; so many that the list (n/8 + 4096 entries) is exhausted must be REPORTED (KMI_ERR_CAPACITY from the insert and
+    from every later size query: the error is sticky), never silently dropped (round-1 advisor finding)."""
+    k = 31
+    rng = np.random.default_rng(11)
+    cand = rng.integers(0, 1 << 62, size=12_000_000, dtype=np.uint64)
+    cand = np.unique(ou.canonical(cand, k))
+    h = _slot_hash_u64(cand)
+    # home slot of a 2^17-slot table is h >> 47: the last 4 slots of every 1024-slot block are the last slots of every
+    # 256-, 512- and 1024-slot segment (and the last 2 of them for a 2^16-slot table)
+    sel = cand[((h >> np.uint64(47)) & np.uint64(1023)) >= np.uint64(1020)][:n_keys]
+    assert len(sel) == n_keys
+    keys = np.repeat(sel, 3)                      # every key three times
+    rng.shuffle(keys)
+    with kb.CountIndex(k, hash=kb.HASH_FARM) as idx:
+        idx.set_build_path(2)
+        if expect_error:
+            with pytest.raises(kb.KmiError) as e:
+                idx.insert(keys)
+                idx.local_size()
+            assert e.value.code == kb.ERR_CAPACITY
+            with pytest.raises(kb.KmiError):
+                idx.local_size()                  # sticky until clear()
+            idx.clear()
+            idx.insert(sel[:100])
+            assert idx.local_size() == 100
+        else:
+            idx.insert(keys)
+            gk, gc = idx.sorted_dump()
+            assert np.array_equal(gk, np.sort(sel)) and np.all(gc == 3)
+
+
+def test_erase_insert_churn_reclaims_tombstones():
+    """Erased slots stay DELETED until a rehash; the table's load test must count them (dense_hash_map does), otherwise
+    erase/insert churn fills the table with tombstones while the host sees a low load (round-1 advisor finding)."""
+    k = 31
+    with kb.CountIndex(k, hash=kb.HASH_MURMUR) as idx:
+        slots0 = None
+        for r in range(12):
+            keys = ou.canonical(ou.random_keys(k, 60000, seed=100 + r), k)
+            idx.insert(keys)
+            if slots0 is None:
+                slots0 = idx.table_info()["slots"]
+            assert idx.local_size() == len(np.unique(keys))
+            c = idx.count(keys)
+            assert np.all(c == 1)
+            idx.erase(keys)
+            assert idx.local_size() == 0
+        # 12 x 60000 tombstones would not fit the first table (2^17 slots): it was purged, not grown without bound
+        assert idx.table_info()["slots"] <= 2 * slots0
+        keys = ou.canonical(ou.random_keys(k, 1000, seed=999), k)
+        assert np.all(idx.count(keys) == 0)
+
+
+def test_fastq_position_ids_reject_records_over_64k():
+    """ShortSequenceKmerId keeps the k-mer's offset inside its record in 16 bits; the reference throws std::invalid_argument
+    beyond that (src/common/sequence.hpp:177-183). A 70 000-base read must be rejected for a position index (KMI_ERR_ARG)
+    and still build a count index."""
+    rng = np.random.default_rng(3)
+    seq = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, 70000)]
+    rec = np.concatenate([np.frombuffer(b"@long\n", np.uint8), seq, np.frombuffer(b"\n+\n", np.uint8), np.full(70000, ord("I"), np.uint8),
+                          np.frombuffer(b"\n", np.uint8)])
+    wk, _, _ = ou.fastq_kmers(rec, 21)
+    with kb.CountIndex(21) as idx:
+        assert idx.build_fastq(rec) == len(wk)
+    with kb.PositionIndex(21) as idx:
+        with pytest.raises(kb.KmiError) as e:
+            idx.build_fastq(rec)
+        assert e.value.code == kb.ERR_ARG
