@@ -41,7 +41,8 @@ ERR_PPM = 5000
 ALG_BYTES = {"k_fastq_kmers<31,farm,sink=buckets> (text -> 256 hash-prefix buckets)": REC / KMERS_PER_READ + 8.0,
              "k_scatter_fine<31,farm> (buckets -> table-segment buckets)": 16.0,
              "k_insert_segments<31,farm> (segment buckets -> table, shared-memory segments)": 32.0}
-ALG_BYTES_FUSED = REC / KMERS_PER_READ + 24.0
+# whole single-GPU build by SURVEY.md 8d: S1 boundary+encode 3.06 + S2/S3 window+canonical+hash 8.42 + S5 insert 32 = 43.5 B/k-mer
+ALG_BYTES_BUILD = (REC + 38 + 12) / KMERS_PER_READ + (38 + 12 + 8.0 * KMERS_PER_READ) / KMERS_PER_READ + 32.0
 # unfused (multi-GPU) pipeline per SURVEY.md §8d: S1-S3 10.6 + S4 24 + S5 32
 ALG_BYTES_SHARDED = (REC + 8.0 * KMERS_PER_READ) / KMERS_PER_READ + 24.0 + 32.0
 
@@ -188,6 +189,84 @@ def run_reference_arm(args):
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
+def _traffic():
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        return json.load(open(tp))
+    except Exception:
+        return {}
+
+
+def parity_sharded(idx, kb, ou, text, n_reads, world, rank, device):
+    """Content parity of a sharded build, outside the timed region. All ranks call it.
+    full_size: every rank walks ITS 1 Gbp with the reference code (Kmer window, lex_less, farm KeyToRank) and accumulates, per
+      owner rank, [sum of mix(key) over occurrences, occurrences]; both are additive, so the all-reduced row r is exactly
+      what owner r's index must report as kmi_checksum — it catches keys on the wrong rank, merged / split / lost keys and
+      wrong counts at the measured size (distinct counts are not additive: they are pinned by the sample below).
+    sample: a second, smaller build through the SAME sharded path (NVLink push) whose texts rank 0 gathers and hands to the
+      reference's p-rank build (oracle/_ref): per-rank local_size and checksum must equal the reference's per-rank values at
+      p = N, and one sharded find() batch must return the reference's frequencies."""
+    import torch
+    import torch.distributed as dist
+    from kmerind_b200.dist import ShardedIndex
+    out = {}
+    threads = max(1, (os.cpu_count() or 1) // world)
+    nbytes = n_reads * REC
+    host_text = text[:nbytes].cpu().numpy()
+    oc = ou.ref_owner_checksums_fastq(host_text, K, world, 1, threads=threads)
+    if oc is None:
+        return {"ok": None, "note": "oracle/_ref not built: no reference code to compare with"}
+    want = idx.comm.allreduce(oc.reshape(-1), "sum").reshape(world, 2)
+    got = idx.local.checksum()
+    ok_full = int(want[rank, 0]) == int(got[0]) and int(want[rank, 1]) == int(got[1])
+    flags = idx.comm.allreduce(np.array([1 if ok_full else 0], dtype=np.uint64), "min")
+    out["full_size"] = {"what": "per owner rank: sum of counts and sum of mix(key)*count == reference walk of all %d texts, all-reduced" % world,
+                        "rank0_sum_counts": [int(got[1]), int(want[rank, 1])], "rank0_sum_mix": [int(got[0]), int(want[rank, 0])],
+                        "all_ranks_ok": bool(flags[0])}
+    # ---- sample build, exact per-rank comparison with the reference's p-rank build
+    s_reads = max(100000, 1600000 // world)
+    s_bytes = s_reads * REC
+    with ShardedIndex(K, hash=kb.HASH_FARM, device=device.index, comm=idx.comm) as sidx:
+        n = sidx.build_fastq_dev(text.data_ptr(), s_bytes)
+        assert n == s_reads * KMERS_PER_READ
+        mine = np.array([sidx.local_size()] + list(sidx.local.checksum()), dtype=np.uint64)
+        parts = [torch.empty(s_bytes, dtype=torch.uint8, device=device) for _ in range(world)]
+        dist.all_gather(parts, text[:s_bytes].contiguous())
+        ref_vals = np.zeros(3 * world, dtype=np.uint64)
+        q = rv = None
+        if rank == 0:
+            whole = torch.cat(parts).cpu().numpy()
+            ref = ou.ref_count_build_fastq(whole, K, world, 1, cuts=[r * s_bytes for r in range(world + 1)], want_dump=True)
+            for r in range(world):
+                ref_vals[3 * r:3 * r + 3] = [ref["sizes"][r], ref["ck"][r, 0], ref["ck"][r, 1]]
+            order = np.argsort(ref["keys"])
+            sk, sc = ref["keys"][order], ref["counts"][order].astype(np.uint64)
+        del parts
+        ref_vals = idx.comm.allreduce(ref_vals, "sum")               # only rank 0 contributed: a broadcast
+        ok_s = bool((ref_vals[3 * rank:3 * rank + 3] == mine).all())
+        # one query batch, the same on every rank: k-mers of rank 0's first reads in read orientation + absent keys
+        qtext = text[:2000 * REC].clone()
+        dist.broadcast(qtext, src=0)
+        q, _, _ = ou.fastq_kmers(qtext.cpu().numpy(), K, canonical=False)
+        q = np.concatenate([q, (np.arange(5000, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15)) >> np.uint64(3)])
+        vals, found = sidx.find(q)
+        lo = idx.comm.allreduce(vals, "min")
+        hi = idx.comm.allreduce(vals, "max")
+        ok_q = bool((lo == hi).all())
+        if rank == 0:
+            cq = ou.canonical(q, K)
+            pos = np.minimum(np.searchsorted(sk, cq), len(sk) - 1)
+            hit = sk[pos] == cq
+            ok_q = ok_q and bool(np.array_equal(found.astype(bool), hit)) and bool(np.array_equal(vals, np.where(hit, sc[pos], 0)))
+        flags = idx.comm.allreduce(np.array([1 if ok_s else 0, 1 if ok_q else 0], dtype=np.uint64), "min")
+        out["sample"] = {"what": "%d reads per rank through the same sharded path (path %d): per-rank local_size, sum of counts, "
+                                 "sum of mix(key)*count == the reference's %d-rank build (oracle/_ref); one sharded find() of %d keys "
+                                 "== the reference's frequencies on every rank" % (s_reads, sidx.path, world, len(q)),
+                         "rank0_local_size": [int(mine[0]), int(ref_vals[3 * rank])], "per_rank_ok": bool(flags[0]), "find_ok": bool(flags[1])}
+    out["ok"] = bool(out["full_size"]["all_ranks_ok"] and out["sample"]["per_rank_ok"] and out["sample"]["find_ok"])
+    return out
+
+
 def run_gpu_arm(args):
     import torch
     import torch.distributed as dist
@@ -208,6 +287,7 @@ def run_gpu_arm(args):
     nbytes = n_reads * REC
     n_kmers_rank = n_reads * KMERS_PER_READ
     first_read = rank * n_reads
+    no_cpu = bool(os.environ.get("KMI_BENCH_NO_CPU"))
 
     # synthetic reads, generated on the device (same bytes as the host twin in oracle/)
     text = torch.empty(nbytes + 64, dtype=torch.uint8, device=device)
@@ -225,24 +305,22 @@ def run_gpu_arm(args):
     stage = {}
     if world == 1:
         idx = kb.CountIndex(K, hash=kb.HASH_FARM, device=local_rank, reserve=reserve)
+        local = idx
 
         def step():
             idx.clear()
             n = idx.build_fastq_dev(text.data_ptr(), nbytes)
             assert n == n_kmers_rank, (n, n_kmers_rank)
-        launches_of = idx.launch_count
     else:
         from kmerind_b200.dist import ShardedIndex
-        idx = ShardedIndex(K, hash=kb.HASH_FARM, device=local_rank, reserve=reserve)
-        peer = False
-        if not os.environ.get("KMI_BENCH_NCCL_A2A"):
-            peer = idx.enable_peer_exchange(n_kmers_rank // world + n_kmers_rank // (4 * world) + 4096)
+        idx = ShardedIndex(K, hash=kb.HASH_FARM, device=local_rank, reserve=reserve)   # NCCL + CUDA IPC inside libkmi.so
+        local = idx.local
 
         def step():
             idx.local.clear()
-            n = idx.build_fastq_dev(text, nbytes, max_kmers=n_kmers_rank)
+            n = idx.build_fastq_dev(text.data_ptr(), nbytes)
             assert n == n_kmers_rank, (n, n_kmers_rank)
-        launches_of = idx.local.launch_count
+    launches_of = local.launch_count
 
     for _ in range(args.warmup):
         step()
@@ -254,9 +332,8 @@ def run_gpu_arm(args):
     e0.record()
     for _ in range(args.steps):
         step()
-        if world == 1:
-            kern_ms.append(idx.last_kernel_ms())
-        else:
+        kern_ms.append(local.last_kernel_ms())
+        if world > 1:
             for k_, v_ in idx.stage_ms.items():
                 stage.setdefault(k_, []).append(v_)
     e1.record()
@@ -274,14 +351,14 @@ def run_gpu_arm(args):
     # ---- parity of what was just measured, outside the timed region (full content, not a sum):
     # N = 1: the reference's own CPU build of the SAME 1 Gbp of text (oracle/_ref) -> distinct keys, sum of counts and
     # sum of mix(key) * count must equal kmi_local_size / kmi_checksum of the index the timed steps built. The same run
-    # is the cpu_baseline (it is the reference path on this box's host cores, timed).
+    # is the cpu_baseline (it is the reference path on this box's host cores, timed). N > 1: parity_sharded().
     parity, cpu_base = None, None
+    cks = local.checksum()
+    info = local.table_info()
     if world == 1:
-        cks = idx.checksum()
         assert cks[1] == n_kmers_rank, "sum of counts %d != k-mers %d" % (cks[1], n_kmers_rank)
         distinct = idx.size()
-        info = idx.table_info()
-        if not os.environ.get("KMI_BENCH_NO_CPU"):
+        if not no_cpu:
             host_text = text[:nbytes].cpu().numpy()
             ref = reference_build(host_text, os.cpu_count() or 1)
             del host_text
@@ -294,94 +371,102 @@ def run_gpu_arm(args):
             parity["ok"] = bool(ok)
             assert ok, "index contents differ from the reference build: %r" % (parity,)
     else:
-        cks = idx.local.checksum()
-        tsum = torch.tensor([cks[1]], dtype=torch.int64, device=device)
-        dist.all_reduce(tsum)
-        assert int(tsum.item()) == total_kmers, "sum of counts %d != k-mers %d" % (int(tsum.item()), total_kmers)
+        tsum = idx.comm.allreduce(np.array([cks[1]], dtype=np.uint64), "sum")
+        assert int(tsum[0]) == total_kmers, "sum of counts %d != k-mers %d" % (int(tsum[0]), total_kmers)
         distinct = idx.size()
-        info = idx.local.table_info()
+        if not no_cpu:
+            parity = parity_sharded(idx, kb, _oracle_util(), text, n_reads, world, rank, device)
+            assert parity["ok"] is not False, "sharded index differs from the reference: %r" % (parity,)
 
     # ---- e2e: host (pinned) buffer through the public host-pointer call, D2H read of the size
-    e2e = None
-    if world == 1:
-        host = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
-        host.copy_(text[:nbytes])
-        torch.cuda.synchronize()
-        host_np = host.numpy()
-        e2e_steps = max(1, min(args.steps, 3))
-        for _ in range(1):
-            idx.clear(); idx.build_fastq(host_np)
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            idx.clear()
-            n = idx.build_fastq(host_np)
-            sz = idx.size()
-        torch.cuda.synchronize()
-        dt = (time.perf_counter() - t0) / e2e_steps
-        e2e = {"value": n_kmers_rank / dt, "unit": "kmers/s", "h2d_bytes_per_step": int(nbytes), "d2h_bytes_per_step": 72,
-               "ms_per_step": dt * 1e3}
-        assert n == n_kmers_rank and sz == distinct
-    else:
-        # every rank's text starts in ITS pinned host buffer; 4 record-aligned chunks, copy of chunk i+1 under the
-        # parse / exchange / insert of chunk i (ShardedIndex.build_fastq_host); D2H: the all-reduced index size
-        host = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
-        host.copy_(text[:nbytes])
-        torch.cuda.synchronize()
-        n_chunks = 4
-        per = (n_reads + n_chunks - 1) // n_chunks
-        cuts = [min(i * per, n_reads) * REC for i in range(n_chunks + 1)]
-        cap_chunk = per * KMERS_PER_READ
-        e2e_steps = max(1, min(args.steps, 3))
-        idx.local.clear(); idx.build_fastq_host(host, cuts, cap_chunk)
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            idx.local.clear()
-            n = idx.build_fastq_host(host, cuts, cap_chunk)
-            sz = idx.size()
-        barrier()
-        dt = torch.tensor([(time.perf_counter() - t0) / e2e_steps], dtype=torch.float64, device=device)
+    host = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    host.copy_(text[:nbytes])
+    torch.cuda.synchronize()
+    host_np = host.numpy()
+    e2e_steps = max(1, min(args.steps, 3))
+    build_host = idx.build_fastq
+    clear = local.clear
+    clear(); build_host(host_np)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        clear()
+        n = build_host(host_np)
+        sz = idx.size()
+    barrier()
+    dt = torch.tensor([(time.perf_counter() - t0) / e2e_steps], dtype=torch.float64, device=device)
+    if world > 1:
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        dt = float(dt.item())
-        assert n == n_kmers_rank and sz == distinct, (n, sz, distinct)
-        e2e = {"value": total_kmers / dt, "unit": "kmers/s", "h2d_bytes_per_step": int(nbytes) * world,
-               "d2h_bytes_per_step": 72 * world, "ms_per_step": dt * 1e3,
-               "how": "per rank: pinned host text -> 4 chunks, H2D of chunk i+1 under parse/exchange/insert of chunk i"}
+    dt = float(dt.item())
+    assert n == n_kmers_rank and sz == distinct, (n, sz, distinct)
+    # what the host side of this box can deliver: every rank copies its pinned text to its GPU at the same time
+    barrier()
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c0.record()
+    for _ in range(2):
+        text[:nbytes].copy_(host, non_blocking=True)
+    c1.record()
+    barrier()
+    h2d = torch.tensor([c0.elapsed_time(c1) / 2], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(h2d, op=dist.ReduceOp.MAX)
+    h2d_ms = float(h2d.item())
+    e2e = {"value": total_kmers / dt, "unit": "kmers/s", "h2d_bytes_per_step": int(nbytes) * world, "d2h_bytes_per_step": 72 * world,
+           "ms_per_step": dt * 1e3, "h2d_copy_alone_ms": h2d_ms, "h2d_gbs_per_gpu": nbytes / h2d_ms / 1e6,
+           "how": "per rank: pinned host text -> kmi_%sbuild_fastq (H2D in rounds on a copy stream under the parse%s); the copy alone "
+                  "(all ranks at once) is this box's ceiling for the number" % ("dist_" if world > 1 else "", " / push" if world > 1 else "")}
+    # the caller's memory as the reference's caller has it: pageable
+    if world == 1 and not os.environ.get("KMI_BENCH_NO_PAGEABLE"):
+        pg = np.empty(nbytes, dtype=np.uint8)
+        pg[:] = host_np
+        clear(); build_host(pg)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        clear()
+        n = build_host(pg)
+        sz = idx.size()
+        torch.cuda.synchronize()
+        e2e["pageable"] = {"value": n_kmers_rank / (time.perf_counter() - t0), "unit": "kmers/s", "ms_per_step": (time.perf_counter() - t0) * 1e3}
+        del pg
 
     peak, peak_kind = measured_peaks()
+    traffic = _traffic()
+    km = np.mean(np.array(kern_ms), axis=0)   # [whole build, parse+scatter, fine scatter, insert, overflow]
     if world == 1:
-        km = np.mean(np.array(kern_ms), axis=0)   # [whole build, parse+scatter, fine scatter, insert, overflow]
         kernels = []
         for (name, alg), ms in zip(ALG_BYTES.items(), km[1:4]):
             ach = alg * n_kmers_rank / (max(float(ms), 1e-6) * 1e-3) / 1e9
-            kernels.append({"kernel": name, "ms_per_step": float(ms), "alg_bytes_per_kmer": alg, "achieved": ach, "frac": ach / peak})
+            tr = traffic.get(name.split("<")[0])
+            kernels.append({"kernel": name, "ms_per_step": float(ms), "alg_bytes_per_kmer": alg, "achieved": ach, "frac": ach / peak,
+                            "traffic": tr, "frac_measured": (tr / (max(float(ms), 1e-6) * 1e-3) / 1e9 / peak) if tr else None})
         dom = max(kernels, key=lambda k_: k_["ms_per_step"])
-        # traffic: dram bytes read+written per launch of the dominant kernel, from profiles/ (ncu --set full), if recorded
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp):
-            try:
-                traffic = json.load(open(tp)).get(dom["kernel"].split("<")[0])
-            except Exception:
-                traffic = None
+        whole = ALG_BYTES_BUILD * n_kmers_rank / (float(km[0]) * 1e-3) / 1e9
         roofline = {"bound": "hbm", "kernel": dom["kernel"], "achieved": dom["achieved"], "peak": peak, "peak_source": peak_kind,
-                    "unit": "GB/s", "frac": dom["frac"], "traffic": traffic, "alg_bytes_per_kmer": dom["alg_bytes_per_kmer"],
-                    "kernel_ms_per_step": dom["ms_per_step"], "build_ms_per_step": float(km[0]), "kernels": kernels,
-                    "whole_build": {"alg_bytes_per_kmer": ALG_BYTES_FUSED,
-                                    "achieved": ALG_BYTES_FUSED * n_kmers_rank / (float(km[0]) * 1e-3) / 1e9,
-                                    "frac": ALG_BYTES_FUSED * n_kmers_rank / (float(km[0]) * 1e-3) / 1e9 / peak}}
+                    "unit": "GB/s", "frac": dom["frac"], "traffic": dom["traffic"], "frac_measured": dom["frac_measured"],
+                    "alg_bytes_per_kmer": dom["alg_bytes_per_kmer"], "kernel_ms_per_step": dom["ms_per_step"],
+                    "build_ms_per_step": float(km[0]), "kernels": kernels,
+                    "whole_build": {"alg_bytes_per_kmer": ALG_BYTES_BUILD, "achieved": whole, "frac": whole / peak,
+                                    "note": "SURVEY 8d single-GPU budget: S1 3.06 + S2/S3 8.42 + S5 32 B per k-mer"}}
     else:
         smean = {k_: float(np.mean(v_)) for k_, v_ in stage.items()}
-        k_ms = smean.get("insert", 0.0)
-        # insert of received keys = coarse scatter (16) + fine scatter (16) + segment insert (32) algorithmic B/k-mer
-        achieved = 64.0 * idx.n_received / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
-        x_ms = smean.get("parse+scatter+exchange", smean.get("a2a", 1e9))
-        roofline = {"bound": "hbm", "kernel": "insert of received keys (k_scatter_keys + k_scatter_fine + k_insert_segments)",
-                    "achieved": achieved, "peak": peak, "peak_source": peak_kind, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": None, "alg_bytes_per_kmer": 64.0, "kernel_ms_per_step": k_ms, "stage_ms": smean,
-                    "nvlink_gbs_per_dir": (8.0 * n_kmers_rank * (world - 1) / world) / (x_ms * 1e-3) / 1e9,
-                    "exchange": "peer stores from the parse kernel (CUDA IPC)" if peer else "NCCL all_to_all"}
+        x_ms = smean.get("parse+push", smean.get("parse+exchange", 1e9))
+        ins_ms = smean.get("insert", 0.0)
+        n_recv = idx.n_received
+        kernels = [{"kernel": "k_scatter_fine (received regions -> table-segment buckets)", "ms_per_step": float(km[2]), "alg_bytes_per_kmer": 16.0,
+                    "achieved": 16.0 * n_recv / (max(float(km[2]), 1e-6) * 1e-3) / 1e9},
+                   {"kernel": "k_insert_segments (segment buckets -> table)", "ms_per_step": float(km[3]), "alg_bytes_per_kmer": 32.0,
+                    "achieved": 32.0 * n_recv / (max(float(km[3]), 1e-6) * 1e-3) / 1e9}]
+        for k_ in kernels:
+            k_["frac"] = k_["achieved"] / peak
+        dom = max(kernels, key=lambda k_: k_["ms_per_step"])
+        nv = (8.0 * n_kmers_rank * (world - 1) / world) / (x_ms * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "kernel": dom["kernel"], "achieved": dom["achieved"], "peak": peak, "peak_source": peak_kind,
+                    "unit": "GB/s", "frac": dom["frac"], "traffic": None, "alg_bytes_per_kmer": dom["alg_bytes_per_kmer"],
+                    "kernel_ms_per_step": dom["ms_per_step"], "kernels": kernels, "stage_ms": smean,
+                    "nvlink": {"gbs_per_dir_per_gpu": nv, "peak": 770.0, "peak_source": "B200_PROFILING.md measured peer copy",
+                               "frac": nv / 770.0, "note": "8 B x k-mers leaving the GPU / (parse + push stage): the pushes of round i run "
+                                                           "under the parse of round i+1, so the stage is not NVLink time alone"},
+                    "exchange": "k_owner_push: stores into the owners' HBM (CUDA IPC, NVLink)" if idx.path == 1 else "NCCL all-to-all"}
 
     if rank == 0:
         line = {"metric": "canonical k-mers inserted/sec into count index", "value": value, "unit": "kmers/s", "n_gpus": world,
@@ -390,17 +475,16 @@ def run_gpu_arm(args):
                 "config": workload_config(world, n_reads),
                 "index": {"distinct_keys": int(distinct), "table_slots_per_gpu": info["slots"], "table_bytes_per_gpu": info["slots"] * info["slot_bytes"],
                           "path": "1xB200 text->buckets->segment insert" if world == 1 else
-                                  "%dxB200 %s" % (world, "parse+owner scatter into peer HBM over NVLink (one kernel)->bucketed insert" if peer
-                                                 else "parse+owner scatter->NCCL all-to-all->bucketed insert")},
-                "clocks": clocks, "gpu_launches": int(launches), "roofline": roofline}
-        if e2e is not None:
-            line["e2e"] = e2e
+                                  "%dxB200 %s" % (world, "parse->buckets | k_owner_push into the owners' HBM over NVLink (overlapped)->fine scatter->segment insert"
+                                                  if idx.path == 1 else "parse->partition->NCCL all-to-all->bucketed insert")},
+                "clocks": clocks, "gpu_launches": int(launches), "roofline": roofline, "e2e": e2e}
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
         if parity is not None:
             line["parity"] = parity
         print(json.dumps(line))
     if world > 1:
+        idx.close()
         dist.destroy_process_group()
 
 

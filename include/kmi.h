@@ -68,6 +68,8 @@ typedef struct kmi_index kmi_index;
 int kmi_create(const kmi_config* cfg, kmi_index** out);
 void kmi_destroy(kmi_index* idx);
 const char* kmi_last_error(void);
+/* CUDA devices visible to this process (0 and KMI_ERR_CUDA without a driver) */
+int kmi_device_count(int* n);
 /* run subsequent work of this index on `cuda_stream` (a cudaStream_t); NULL = default stream */
 int kmi_set_stream(kmi_index* idx, void* cuda_stream);
 /* Tuning knobs without a reference counterpart. KMI_PARAM_BUILD_PATH: how k-mers reach the table —
@@ -88,8 +90,7 @@ int kmi_clear(kmi_index* idx);
  * start position) and hold whole records; `file_offset` is the offset of bytes[0] in the file
  * (only used for position ids: a POSITION-mode index built from FASTQ stores ShortSequenceKmerId values, from FASTA
  * LongSequenceKmerId values). Every k-mer of the block is inserted into THIS index regardless
- * of owner (nranks == 1 semantics); the sharded build is parse_*_dev + partition_dev + exchange +
- * insert_dev. n_kmers (optional) receives the number of k-mer occurrences generated. */
+ * of owner (nranks == 1 semantics); the sharded build is kmi_dist_build_*. n_kmers (optional) receives the number of k-mer occurrences generated. */
 int kmi_build_fastq(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers);
 int kmi_build_fasta(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t* n_kmers);
 int kmi_build_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers);
@@ -164,33 +165,6 @@ int kmi_parse_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n,
                         uint64_t* d_keys, uint64_t* d_ids, size_t cap, uint64_t* n_kmers);
 int kmi_parse_fasta_block_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, const kmi_fasta_block* block,
                               uint64_t* d_keys, uint64_t* d_ids, size_t cap, uint64_t* n_kmers);
-/* a2-a14 fused for the sharded build: parse + owner = dist_hash % nranks + scatter, straight into one
- * region of `region_cap` keys per owning rank (d_regions + r * region_cap * nw): the send buffers of the
- * all-to-all, with h_counts[nranks] the send counts (imxx::distribute up to mxx::all2allv,
- * incremental_mxx.hpp:1039-1098). Order inside a region is unspecified. KMI_ERR_CAPACITY when a region
- * overflows (skewed owners): fall back to kmi_parse_fastq_dev + kmi_partition_dev. */
-int kmi_parse_fastq_by_owner_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* d_regions,
-                                 size_t region_cap, uint64_t* h_counts, uint64_t* n_kmers);
-/* ---- fused exchange over NVLink peer memory (replaces mxx::all2allv, incremental_mxx.hpp:1098, in the
- * build): each rank owns a receive buffer of nranks regions of `region_cap` keys (region s = keys from
- * rank s). kmi_exchange_setup allocates it and returns its CUDA IPC handle; the caller all-gathers the
- * nranks handles (any transport) and passes them to kmi_exchange_connect. kmi_exchange_parse_fastq_dev
- * then runs parse + owner + scatter as ONE kernel whose stores land directly in the owners' buffers;
- * the caller exchanges the send counts (this is also the completion handshake) and calls
- * kmi_exchange_insert with the counts it received. All ranks must be on one node (CUDA IPC).
- *
- * Sub-bins (opt-in, environment KMI_EXCHANGE_PREFIX=1): for one-word keys on 2/4/8 ranks every (source, owner) region is cut into B = 256 / nranks sub-bins by the top
- * bits of the table-placement hash, inside the same shared-memory sort of the sender, so that the receiver's table build
- * starts at its fine scatter (no coarse pass over the received keys). kmi_exchange_bins returns B (1 otherwise); the
- * count arrays then hold nranks * B entries, entry r * B + c = keys for / from rank r in sub-bin c, and are exchanged
- * block-wise (all-to-all of B counts per peer). */
-#define KMI_IPC_HANDLE_BYTES 64
-int kmi_exchange_setup(kmi_index* idx, size_t region_cap, uint8_t* handle_out /* KMI_IPC_HANDLE_BYTES */);
-int kmi_exchange_connect(kmi_index* idx, const uint8_t* handles /* nranks * KMI_IPC_HANDLE_BYTES */);
-int kmi_exchange_bins(kmi_index* idx, uint32_t* bins_per_rank);
-int kmi_exchange_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* h_send_counts /* nranks * B */,
-                                 uint64_t* n_kmers);
-int kmi_exchange_insert(kmi_index* idx, const uint64_t* h_recv_counts /* nranks * B */);
 /* a10: out = canonical(in) (lex_less, kmer_transform.hpp:109-126); in == out allowed */
 int kmi_canonicalize_dev(kmi_index* idx, const uint64_t* d_keys, uint64_t* d_out, size_t n);
 /* a11/a12: which = 0 store hash, 1 dist hash, of the keys AS GIVEN (no transform) */
@@ -248,6 +222,62 @@ int kmi_last_stage_ms(kmi_index* idx, float* ms3);
  * [0] whole build, [1] parse (+ bucket scatter), [2] fine scatter, [3] table insert (shared-memory
  * segments or L2 atomics), [4] overflow / spill insert. [2]-[4] are 0 on the direct path. */
 int kmi_last_kernel_ms(kmi_index* idx, float* ms5);
+
+/* ---- the sharded index: one process per GPU, owner(key) = dist_hash(key) % nranks -------------------------------------
+ * Replaces the collective half of the reference's distributed maps (every rank calls every operation, also with empty
+ * input: distributed_densehash_map.hpp:2567-2573): imxx::distribute (src/io/incremental_mxx.hpp:1039-1109: bucket by
+ * KeyToRank, mxx::all2all of the counts, mxx::all2allv of the elements) + the local operation + the way back for queries.
+ *
+ * kmi_comm wraps one NCCL communicator (libnccl.so.2 is loaded with dlopen on first use). Bootstrap as NCCL wants it: rank 0
+ * calls kmi_comm_unique_id and hands the KMI_COMM_ID_BYTES bytes to every rank by any means (MPI_Bcast in the reference's
+ * world, a pipe, torch.distributed), then every rank calls kmi_comm_create. kmi_dist_attach binds an index created with the
+ * same rank / nranks / device to the communicator (collective; it also maps every rank's receive buffer with CUDA IPC when
+ * the ranks share an NVLink domain). After that:
+ *   kmi_dist_build_fastq[_dev]  rank r passes ITS record-aligned block of the reads (kmi_fastq_find_first_record cuts them).
+ *       COUNT index, <= 8 ranks, peer mapping available: the parser's 256 hash-prefix buckets are pushed by k_owner_push
+ *       straight into the owners' HBM over NVLink while the next round is parsed, and every owner starts its table build at
+ *       the fine scatter (no pass over received keys, no NCCL for the keys). Otherwise, and for POSITION indices: parse ->
+ *       stable partition (kmi_partition_dev) -> NCCL all-to-all -> insert. Skewed keys that overflow a receive region make
+ *       every rank redo the build on the second path (decided by one all-reduce: no rank is left alone in a collective).
+ *   kmi_dist_build_fasta[_dev]  rank r passes block r of ONE file (kmi_fasta_part; blocks in rank order, cut at any byte,
+ *       followed by the K-1 halo of kmi_fasta_halo_end) or, with part == NULL, a whole file of its own. The cross-rank part
+ *       of FASTAParser::init_parser (fasta_loader.hpp:202-483) is one all-gather of the block summaries.
+ *   kmi_dist_insert / count / find / find_positions / erase   the batch operations of kmer_index.hpp:132-225 on keys held
+ *       by any rank; answers arrive in the caller's input order. kmi_dist_size = map_base::size (distributed_map_base.hpp:243).
+ * kmi_local_size / kmi_dump / kmi_checksum / kmi_save / ... keep working on this rank's shard. */
+typedef struct kmi_comm kmi_comm;
+#define KMI_COMM_ID_BYTES 128
+int kmi_comm_unique_id(uint8_t* id_out /* KMI_COMM_ID_BYTES */);
+int kmi_comm_create(const uint8_t* id, int nranks, int rank, int device, kmi_comm** out);
+void kmi_comm_destroy(kmi_comm* comm);
+int kmi_comm_rank(const kmi_comm* comm);
+int kmi_comm_size(const kmi_comm* comm);
+int kmi_comm_barrier(kmi_comm* comm);
+/* small host-value collectives for callers that have no other transport: op 0 sum, 1 max, 2 min */
+int kmi_comm_allreduce_u64(kmi_comm* comm, uint64_t* vals, int n, int op);
+int kmi_comm_allgather_u64(kmi_comm* comm, const uint64_t* mine, int n, uint64_t* all /* nranks * n */);
+
+typedef struct {
+  uint64_t file_offset;   /* file byte of the block's first byte */
+  uint64_t n_valid;       /* bytes the rank owns; the rest of the buffer is halo */
+  int32_t bol;            /* the block's first byte starts a line */
+  int32_t reserved;
+} kmi_fasta_part;
+int kmi_dist_attach(kmi_index* idx, kmi_comm* comm);
+int kmi_dist_build_fastq(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers);
+int kmi_dist_build_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers);
+int kmi_dist_build_fasta(kmi_index* idx, const uint8_t* bytes, size_t n, const kmi_fasta_part* part, uint64_t* n_kmers);
+int kmi_dist_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, const kmi_fasta_part* part, uint64_t* n_kmers);
+int kmi_dist_insert(kmi_index* idx, const uint64_t* keys, const uint64_t* vals, size_t n);
+int kmi_dist_insert_dev(kmi_index* idx, const uint64_t* d_keys, const uint64_t* d_vals, size_t n);
+int kmi_dist_count(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* counts);
+int kmi_dist_find(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* vals, uint8_t* found);
+int kmi_dist_find_positions(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* offsets, uint64_t* vals, size_t cap);
+int kmi_dist_erase(kmi_index* idx, const uint64_t* keys, size_t n);
+int kmi_dist_size(kmi_index* idx, uint64_t* n);
+/* last sharded build: device ms [0] whole, [1] parse + push / exchange, [2] insert of the received keys, [3] unused; keys this
+ * rank received; path 1 = NVLink push, 2 = NCCL all-to-all */
+int kmi_dist_last_stats(kmi_index* idx, float* ms4, uint64_t* n_received, int32_t* path);
 
 /* ---- synthetic workload (same bytes as oracle/kmi_oracle.c kmio_synth_fastq) - */
 size_t kmi_synth_record_bytes(uint32_t read_len);

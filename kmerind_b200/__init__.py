@@ -64,7 +64,7 @@ def load_library(build_if_missing=False):
     lib.kmi_destroy.argtypes = [_P]
     lib.kmi_destroy.restype = None
     sig = {
-        "kmi_set_stream": [_P, _P], "kmi_set_param": [_P, ctypes.c_int, ctypes.c_int64], "kmi_reserve": [_P, _U64], "kmi_clear": [_P],
+        "kmi_device_count": [_P], "kmi_set_stream": [_P, _P], "kmi_set_param": [_P, ctypes.c_int, ctypes.c_int64], "kmi_reserve": [_P, _U64], "kmi_clear": [_P],
         "kmi_build_fastq": [_P, _P, _SZ, _U64, _P], "kmi_build_fasta": [_P, _P, _SZ, _P],
         "kmi_build_fastq_dev": [_P, _P, _SZ, _U64, _P], "kmi_build_fasta_dev": [_P, _P, _SZ, _P],
         "kmi_parse_fastq_dev": [_P, _P, _SZ, _U64, _P, _P, _SZ, _P],
@@ -75,10 +75,16 @@ def load_library(build_if_missing=False):
         "kmi_fasta_halo_end": [_P, _U64, _SZ, _U64, ctypes.c_int, _P],
         "kmi_build_file": [_P, ctypes.c_char_p, ctypes.c_int, _P],
         "kmi_save": [_P, ctypes.c_char_p], "kmi_load": [_P, ctypes.c_char_p, _P],
-        "kmi_parse_fastq_by_owner_dev": [_P, _P, _SZ, _P, _SZ, _P, _P],
-        "kmi_exchange_setup": [_P, _SZ, _P], "kmi_exchange_connect": [_P, _P],
-        "kmi_exchange_parse_fastq_dev": [_P, _P, _SZ, _P, _P], "kmi_exchange_insert": [_P, _P],
-        "kmi_exchange_bins": [_P, _P],
+        "kmi_comm_unique_id": [_P], "kmi_comm_create": [_P, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(_P)],
+        "kmi_comm_rank": [_P], "kmi_comm_size": [_P], "kmi_comm_barrier": [_P],
+        "kmi_comm_allreduce_u64": [_P, _P, ctypes.c_int, ctypes.c_int], "kmi_comm_allgather_u64": [_P, _P, ctypes.c_int, _P],
+        "kmi_dist_attach": [_P, _P],
+        "kmi_dist_build_fastq": [_P, _P, _SZ, _U64, _P], "kmi_dist_build_fastq_dev": [_P, _P, _SZ, _U64, _P],
+        "kmi_dist_build_fasta": [_P, _P, _SZ, _P, _P], "kmi_dist_build_fasta_dev": [_P, _P, _SZ, _P, _P],
+        "kmi_dist_insert": [_P, _P, _P, _SZ], "kmi_dist_insert_dev": [_P, _P, _P, _SZ],
+        "kmi_dist_count": [_P, _P, _SZ, _P], "kmi_dist_find": [_P, _P, _SZ, _P, _P],
+        "kmi_dist_find_positions": [_P, _P, _SZ, _P, _P, _SZ], "kmi_dist_erase": [_P, _P, _SZ],
+        "kmi_dist_size": [_P, _P], "kmi_dist_last_stats": [_P, _P, _P, _P],
         "kmi_fastq_find_first_record": [_P, _U64, _SZ, _U64, _U64, _U64, _U64, _P],
         "kmi_canonicalize_dev": [_P, _P, _P, _SZ], "kmi_hash_dev": [_P, ctypes.c_int, _P, _P, _SZ],
         "kmi_partition_dev": [_P, _P, _P, _SZ, _P, _P, _P],
@@ -96,16 +102,21 @@ def load_library(build_if_missing=False):
         fn = getattr(lib, name)
         fn.argtypes = args
         fn.restype = ctypes.c_int
+    lib.kmi_comm_destroy.argtypes = [_P]
+    lib.kmi_comm_destroy.restype = None
     _lib = lib
     return lib
 
 
 EXPORTED_SYMBOLS = (
-    "kmi_create", "kmi_destroy", "kmi_last_error", "kmi_set_stream", "kmi_set_param", "kmi_reserve", "kmi_clear",
+    "kmi_create", "kmi_destroy", "kmi_last_error", "kmi_device_count", "kmi_set_stream", "kmi_set_param", "kmi_reserve", "kmi_clear",
     "kmi_build_fastq", "kmi_build_fasta", "kmi_build_fastq_dev", "kmi_build_fasta_dev",
     "kmi_parse_fastq_dev", "kmi_parse_fasta_dev", "kmi_parse_fasta_block_dev", "kmi_build_fasta_block", "kmi_build_fasta_block_dev",
-    "kmi_fasta_block_summary_dev", "kmi_fasta_halo_end", "kmi_build_file", "kmi_save", "kmi_load", "kmi_parse_fastq_by_owner_dev", "kmi_exchange_setup", "kmi_exchange_connect",
-    "kmi_exchange_parse_fastq_dev", "kmi_exchange_insert", "kmi_exchange_bins", "kmi_fastq_find_first_record", "kmi_canonicalize_dev", "kmi_hash_dev",
+    "kmi_fasta_block_summary_dev", "kmi_fasta_halo_end", "kmi_build_file", "kmi_save", "kmi_load", "kmi_fastq_find_first_record",
+    "kmi_comm_unique_id", "kmi_comm_create", "kmi_comm_destroy", "kmi_comm_rank", "kmi_comm_size", "kmi_comm_barrier",
+    "kmi_comm_allreduce_u64", "kmi_comm_allgather_u64", "kmi_dist_attach", "kmi_dist_build_fastq", "kmi_dist_build_fastq_dev",
+    "kmi_dist_build_fasta", "kmi_dist_build_fasta_dev", "kmi_dist_insert", "kmi_dist_insert_dev", "kmi_dist_count", "kmi_dist_find",
+    "kmi_dist_find_positions", "kmi_dist_erase", "kmi_dist_size", "kmi_dist_last_stats", "kmi_canonicalize_dev", "kmi_hash_dev",
     "kmi_partition_dev", "kmi_insert", "kmi_insert_dev", "kmi_count", "kmi_find", "kmi_find_positions",
     "kmi_erase", "kmi_count_dev", "kmi_find_dev", "kmi_local_size", "kmi_num_keys", "kmi_dump",
     "kmi_checksum", "kmi_table_info", "kmi_launch_count", "kmi_last_stage_ms", "kmi_last_kernel_ms",
@@ -271,40 +282,6 @@ class Index:
         n = _U64(0)
         _check(self._lib.kmi_parse_fastq_dev(self._h, dptr, nbytes, file_offset, d_keys, d_ids, cap, ctypes.byref(n)))
         return n.value
-
-    def parse_fastq_by_owner_dev(self, dptr, nbytes, d_regions, region_cap, nranks):
-        """(send counts per owner, k-mers generated); owner r's keys at d_regions + r * region_cap * nw."""
-        counts = np.zeros(nranks, dtype=np.uint64)
-        n = _U64(0)
-        _check(self._lib.kmi_parse_fastq_by_owner_dev(self._h, dptr, nbytes, d_regions, region_cap, _hptr(counts),
-                                                      ctypes.byref(n)))
-        return counts, n.value
-
-    # -- fused exchange over NVLink peer memory (kmi_exchange_*) -------------------------------------
-    def exchange_setup(self, region_cap):
-        h = np.zeros(64, dtype=np.uint8)
-        _check(self._lib.kmi_exchange_setup(self._h, region_cap, _hptr(h)))
-        return h.tobytes()
-
-    def exchange_connect(self, handles):
-        buf = np.frombuffer(b"".join(handles), dtype=np.uint8).copy()
-        _check(self._lib.kmi_exchange_connect(self._h, _hptr(buf)))
-
-    def exchange_bins(self):
-        """sub-bins per peer of the count arrays (kmi_exchange_bins): 1, or 256 / nranks with the prefix layout"""
-        b = ctypes.c_uint32(0)
-        _check(self._lib.kmi_exchange_bins(self._h, ctypes.byref(b)))
-        return b.value
-
-    def exchange_parse_fastq_dev(self, dptr, nbytes, nranks):
-        counts = np.zeros(nranks * self.exchange_bins(), dtype=np.uint64)
-        n = _U64(0)
-        _check(self._lib.kmi_exchange_parse_fastq_dev(self._h, dptr, nbytes, _hptr(counts), ctypes.byref(n)))
-        return counts, n.value
-
-    def exchange_insert(self, recv_counts):
-        c = np.ascontiguousarray(recv_counts, dtype=np.uint64)
-        _check(self._lib.kmi_exchange_insert(self._h, _hptr(c)))
 
     def parse_fasta_dev(self, dptr, nbytes, d_keys, cap, d_ids=None, block=None):
         """block = None (whole file) or (file_offset, n_valid, header_runs_before, flags): kmi_fasta_block"""

@@ -45,16 +45,17 @@ def build(force=False, verbose=False):
         objs.append(o)
         if force or _newer(o, hdrs + [inst]):
             jobs.append([NVCC] + FLAGS + ["-DKMI_K=%d" % k, "-c", inst, "-o", o])
-    api = os.path.join(CSRC, "kmi_api.cu")
-    o = os.path.join(objdir, "kmi_api.o")
-    objs.append(o)
-    if force or _newer(o, hdrs + [api]):
-        jobs.append([NVCC] + FLAGS + ["-c", api, "-o", o])
+    for name in ("kmi_api", "kmi_dist"):
+        src = os.path.join(CSRC, name + ".cu")
+        o = os.path.join(objdir, name + ".o")
+        objs.append(o)
+        if force or _newer(o, hdrs + [src]):
+            jobs.append([NVCC] + FLAGS + ["-c", src, "-o", o])
     if jobs:
         with ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
             list(ex.map(_run, jobs))
     if jobs or not os.path.exists(OUT):
-        _run([NVCC, "-shared", "-o", OUT] + objs + ["-cudart", "static"])
+        _run([NVCC, "-shared", "-o", OUT] + objs + ["-cudart", "static", "-ldl"])
     if verbose:
         print("built", OUT)
     return OUT

@@ -2,8 +2,7 @@
 // No CPU fallback: every compute entry point needs a CUDA device and fails with KMI_ERR_CUDA
 // otherwise. Reference interfaces replaced are cited in include/kmi.h next to each function.
 #define KMI_SHARED_KERNELS
-#include "../../include/kmi.h"
-#include "kmi_ops.cuh"
+#include "kmi_internal.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -26,116 +25,15 @@ const Ops* kmi_ops_k63(int);
 using namespace kmi;
 
 static thread_local char g_err[512] = "";
-static int fail(int code, const char* fmt, ...) {
+namespace kmi {
+int fail(int code, const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
   return code;
 }
-#define CU(call)                                                                              \
-  do {                                                                                        \
-    cudaError_t e_ = (call);                                                                  \
-    if (e_ != cudaSuccess) return fail(KMI_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
-  } while (0)
-#define OK(call)            \
-  do {                      \
-    int r_ = (call);        \
-    if (r_ != KMI_OK) return r_; \
-  } while (0)
-
-namespace {
-
-struct DevBuf {
-  void* p = nullptr;
-  size_t cap = 0;
-  int ensure(size_t bytes) {
-    if (bytes <= cap) return KMI_OK;
-    if (p) { cudaFree(p); p = nullptr; cap = 0; }
-    size_t want = bytes + bytes / 8 + 256;
-    cudaError_t e = cudaMalloc(&p, want);
-    if (e != cudaSuccess) { p = nullptr; return fail(KMI_ERR_NOMEM, "cudaMalloc(%zu): %s", want, cudaGetErrorString(e)); }
-    cap = want;
-    return KMI_OK;
-  }
-  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
-  template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
-};
-
-// device counters block
-enum { CTR_SIZE = 0, CTR_NKMERS = 1, CTR_CURSOR = 2, CTR_CK0 = 3, CTR_CK1 = 4, CTR_REMOVED = 5, CTR_ERR = 6, CTR_PERR = 7, CTR_CARRY = 8, CTR_FIRST_LS = 9, CTR_N = 10 };
-
-// bkt_meta layout (u32 words): cursors [0, N_BUCKETS], HLL registers from META_HLL
-enum { META_HLL = 512, META_WORDS = META_HLL + HLL_M };
-
-}  // namespace
-
-struct kmi_index {
-  kmi_config cfg;
-  const Ops* ops = nullptr;
-  cudaStream_t stream = 0;
-  int nw = 1;
-  size_t slot_bytes = 16;
-  // table
-  void* slots = nullptr;
-  u64 cap = 0;             // number of slots (power of two)
-  u64* ctr = nullptr;      // device counters (CTR_N x u64)
-  u64 size_exact = 0;      // last size read back
-  u64 size_upper = 0;      // upper bound on the current size (exact + keys issued since)
-  u64 tombstones = 0;      // DELETED slots in the table: they occupy probe sequences like live keys (dense_hash_map counts
-                           // them in its resize decision too); dropped by the next rehash
-  // scratch
-  DevBuf mid_keys, mid_cur;        // first of two fine passes (very large tables)
-  DevBuf parse_keys, parse_ids;   // staging of the parse -> insert builds (FASTA, FASTQ positions): kept between calls
-  DevBuf tile_rec;   // FASTQ position ids: record start open at every tile (k_fastq_rec_carry)
-  DevBuf tile_lines, block_sums, stage_in, stage_keys, stage_vals, stage_out, stage_found, hist, hist_sums;
-  // POSITION mode: tuple log + CSR
-  DevBuf log_keys, log_ids, log_keys2, log_ids2, offsets, csr_sums, values;
-  u64 log_n = 0;
-  bool csr_dirty = false;
-  // hash-prefix buckets (kmi_bucket.cuh): key regions, cursors + HyperLogLog registers
-  DevBuf bkt_keys, bkt_meta, fine_keys, fine_cur;
-  u32 h_cursor[N_BUCKETS + 1];   // last read-back of the coarse cursors
-  int seg_path = 1;        // KMI_PARAM_SEGMENT_INSERT: 1 = shared-memory segment insert where possible, 0 = L2 atomics
-  bool hll_ready = false;
-  u64 non_hll_upper = 0;   // keys inserted by paths that do not feed the HLL (upper bound on their distinct keys)
-  int build_path = 0;      // kmi_param KMI_PARAM_BUILD_PATH: 0 auto, 1 direct atomics, 2 bucketed
-  // accounting
-  u64 launches = 0;
-  float stage_ms[3] = {0, 0, 0};
-  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-  float scatter_ms = 0;
-  cudaEvent_t kev[4] = {nullptr, nullptr, nullptr, nullptr};  // around the kernels of bucket_commit
-  bool kev_pending = false;
-  float kernel_ms[5] = {0, 0, 0, 0, 0};  // last build: total, parse+scatter, fine scatter, segment/L2 insert, overflow insert
-  // fused exchange (kmi_exchange_*): receive regions of this rank, peers' regions mapped over CUDA IPC
-  void* xchg_recv = nullptr;
-  u64 xchg_region_cap = 0;
-  u32 xchg_log_cb = 0;              // > 0: every (source, owner) region is cut into 2^log_cb sub-bins by slot-hash prefix
-  u64 xchg_cap_bin = 0;             // keys per sub-bin
-  u64 xchg_ovf_cap = 0;             // overflow region behind the sub-bins (fine-scatter excess, segment spills)
-  std::vector<void*> xchg_peer;     // base of rank r's receive buffer in this process (own buffer for r == rank)
-  DevBuf xchg_bases;                // device array: where THIS rank writes keys owned by rank r
-  uint8_t* file_buf[2] = {nullptr, nullptr};   // pinned buffers of kmi_build_file (kept between calls: pinning is slow)
-  size_t file_buf_cap[2] = {0, 0};
-  cudaStream_t copy_stream = nullptr;        // H2D copies of the pipelined host-pointer build
-  std::vector<cudaEvent_t> copy_events;    // parse+scatter share of the last bucketed build
-
-  // Lazy clear: `virgin` = the table is logically empty but its memory has not been written. The segment insert of a
-  // bucketed build initialises every segment in shared memory and writes all of them, so a build into an empty table
-  // never pays the 16 B/slot clear nor the read of empty segments; everything else goes through view(), which clears first.
-  bool virgin = false;
-  void touch() {
-    if (virgin && slots) { ops->table_clear(stream, slots, cap); launches++; }
-    virgin = false;
-  }
-  TableView view() { touch(); return raw_view(); }
-  TableView raw_view() const {
-    TableView t;
-    t.slots = slots; t.mask = cap - 1; t.shift = 64u - (u32)__builtin_ctzll(cap ? cap : 1); t.size = ctr + CTR_SIZE; t.error = reinterpret_cast<u32*>(ctr + CTR_ERR);
-    return t;
-  }
-};
+}  // namespace kmi
 
 static const Ops* find_ops(int k, int hash) {
   switch (k) {
@@ -156,22 +54,22 @@ static u64 pow2_at_least(u64 x) {
 }
 static const double MAX_LOAD = 0.7;  // dense_hash_map max load, reference densehash_map.hpp:969
 
-static int read_ctr(kmi_index* idx, int which, u64* out) {
+int kmi::read_ctr(kmi_index* idx, int which, u64* out) {
   CU(cudaMemcpyAsync(out, idx->ctr + which, sizeof(u64), cudaMemcpyDeviceToHost, idx->stream));
   CU(cudaStreamSynchronize(idx->stream));
   return KMI_OK;
 }
-static int zero_ctr(kmi_index* idx, int which, int count = 1) {
+int kmi::zero_ctr(kmi_index* idx, int which, int count) {
   CU(cudaMemsetAsync(idx->ctr + which, 0, sizeof(u64) * count, idx->stream));
   return KMI_OK;
 }
 // CTR_ERR holds the sticky TERR_* bits (cleared by kmi_clear only)
-static int table_error(u64 e) {
+int kmi::table_error(u64 e) {
   if (e & TERR_SPILL) return fail(KMI_ERR_CAPACITY, "segment spill list exhausted (keys homed past their table segment's end): index contents are incomplete");
   if (e) return fail(KMI_ERR_CAPACITY, "hash table overflow (probe limit reached)");
   return KMI_OK;
 }
-static int check_table_error(kmi_index* idx) {
+int kmi::check_table_error(kmi_index* idx) {
   u64 e = 0;
   OK(read_ctr(idx, CTR_ERR, &e));
   return table_error(e);
@@ -238,11 +136,15 @@ static int table_room(kmi_index* idx, u64 incoming, u64* grant) {
   return KMI_OK;
 }
 
-static void exchange_close(kmi_index* idx);
-static const size_t AUTO_BUCKET_KEYS = 1u << 21;   // below this the direct path wins (bucket set-up dominates)
-static const size_t AUTO_BUCKET_BYTES = 8u << 20;
 
 extern "C" const char* kmi_last_error(void) { return g_err; }
+extern "C" int kmi_device_count(int* n) {
+  if (!n) return fail(KMI_ERR_ARG, "null argument");
+  *n = 0;
+  cudaError_t e = cudaGetDeviceCount(n);
+  if (e != cudaSuccess) { *n = 0; return fail(KMI_ERR_CUDA, "no CUDA device (%s)", cudaGetErrorString(e)); }
+  return KMI_OK;
+}
 
 extern "C" int kmi_create(const kmi_config* cfg, kmi_index** out) {
   if (!cfg || !out) return fail(KMI_ERR_ARG, "null argument");
@@ -287,14 +189,14 @@ extern "C" void kmi_destroy(kmi_index* idx) {
   if (idx->ctr) cudaFree(idx->ctr);
   DevBuf* bufs[] = {&idx->tile_lines, &idx->block_sums, &idx->stage_in, &idx->stage_keys, &idx->stage_vals,
                     &idx->stage_out, &idx->stage_found, &idx->hist, &idx->hist_sums, &idx->log_keys, &idx->log_ids,
-                    &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->xchg_bases, &idx->mid_keys, &idx->mid_cur};
+                    &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->mid_keys, &idx->mid_cur};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 6; ++i) if (idx->ev[i]) cudaEventDestroy(idx->ev[i]);
   for (int i = 0; i < 4; ++i) if (idx->kev[i]) cudaEventDestroy(idx->kev[i]);
   for (cudaEvent_t e : idx->copy_events) cudaEventDestroy(e);
   if (idx->copy_stream) cudaStreamDestroy(idx->copy_stream);
   for (int i = 0; i < 2; ++i) if (idx->file_buf[i]) cudaFreeHost(idx->file_buf[i]);
-  exchange_close(idx);
+  if (idx->dist) kmi_dist_release(idx);
   delete idx;
 }
 
@@ -342,15 +244,8 @@ extern "C" int kmi_clear(kmi_index* idx) {
 
 
 // ---- hash-prefix buckets (kmi_bucket.cuh) -------------------------------------------------------------
-static const u64 BUCKET_MAX_KEYS = 1ULL << 31;   // per round trip; keeps every cursor and their sum below 2^32
 
-// (re)size the bucket regions for up to `max_keys` keys and zero the cursors
-static int bucket_prepare(kmi_index* idx, u64 max_keys, BucketSink* bs) {
-  if (max_keys > BUCKET_MAX_KEYS) return fail(KMI_ERR_ARG, "bucket round of %llu keys", (unsigned long long)max_keys);
-  // uniform hash: a bucket receives max_keys/256 +- a few sigma; 6 % + 1024 slack, the rest goes to the overflow region
-  u64 capb = max_keys / N_BUCKETS + max_keys / (N_BUCKETS * 16) + 1024;
-  u64 ovf = max_keys / 8 + 4096;
-  OK(idx->bkt_keys.ensure((capb * N_BUCKETS + ovf) * sizeof(u64) * idx->nw));
+int kmi::bucket_meta_prepare(kmi_index* idx) {
   if (!idx->hll_ready) {
     OK(idx->bkt_meta.ensure(sizeof(u32) * META_WORDS));
     CU(cudaMemsetAsync(idx->bkt_meta.p, 0, sizeof(u32) * META_WORDS, idx->stream));
@@ -358,6 +253,17 @@ static int bucket_prepare(kmi_index* idx, u64 max_keys, BucketSink* bs) {
   } else {
     CU(cudaMemsetAsync(idx->bkt_meta.p, 0, sizeof(u32) * META_HLL, idx->stream));
   }
+  return KMI_OK;
+}
+
+// (re)size the bucket regions for up to `max_keys` keys and zero the cursors
+int kmi::bucket_prepare(kmi_index* idx, u64 max_keys, BucketSink* bs) {
+  if (max_keys > BUCKET_MAX_KEYS) return fail(KMI_ERR_ARG, "bucket round of %llu keys", (unsigned long long)max_keys);
+  // uniform hash: a bucket receives max_keys/256 +- a few sigma; 6 % + 1024 slack, the rest goes to the overflow region
+  u64 capb = max_keys / N_BUCKETS + max_keys / (N_BUCKETS * 16) + 1024;
+  u64 ovf = max_keys / 8 + 4096;
+  OK(idx->bkt_keys.ensure((capb * N_BUCKETS + ovf) * sizeof(u64) * idx->nw));
+  OK(bucket_meta_prepare(idx));
   bs->keys = idx->bkt_keys.as<u64>();
   bs->cursor = idx->bkt_meta.as<u32>();
   bs->hll = idx->bkt_meta.as<u32>() + META_HLL;
@@ -379,7 +285,7 @@ static double hll_estimate(const u32* reg) {
 }
 
 // add the kernel times of the last bucket_commit (its events have completed: call after a sync)
-static void harvest_commit_times(kmi_index* idx) {
+void kmi::harvest_commit_times(kmi_index* idx) {
   if (!idx->kev_pending) return;
   float a = 0, b = 0, c = 0;
   cudaEventElapsedTime(&a, idx->kev[0], idx->kev[1]);
@@ -390,13 +296,13 @@ static void harvest_commit_times(kmi_index* idx) {
 }
 
 // one synchronisation per round: counters + HLL registers
-static int bucket_readback(kmi_index* idx, const BucketSink& bs, u64* host_ctr, std::vector<u32>& reg) {
+int kmi::bucket_readback(kmi_index* idx, const BucketSink& bs, u64* host_ctr, std::vector<u32>& reg) {
   reg.resize(HLL_M);
   idx->ops->hll_buckets(idx->stream, bs);
   idx->launches++;
   CU(cudaMemcpyAsync(reg.data(), bs.hll, sizeof(u32) * HLL_M, cudaMemcpyDeviceToHost, idx->stream));
   CU(cudaMemcpyAsync(host_ctr, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
-  CU(cudaMemcpyAsync(idx->h_cursor, bs.cursor, sizeof(u32) * (N_BUCKETS + 1), cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaMemcpyAsync(&idx->h_ovf_cursor, ovf_cur(bs), sizeof(u32), cudaMemcpyDeviceToHost, idx->stream));
   CU(cudaStreamSynchronize(idx->stream));
   harvest_commit_times(idx);
   return KMI_OK;
@@ -404,7 +310,8 @@ static int bucket_readback(kmi_index* idx, const BucketSink& bs, u64* host_ctr, 
 
 // Size the table for what the buckets hold, then insert them segment by segment. n_keys = keys
 // scattered this round; size_now = live keys in the table before the insert.
-static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 size_now, const std::vector<u32>& reg) {
+int kmi::bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 size_now, const std::vector<u32>& reg, bool* not_inserted) {
+  if (not_inserted) *not_inserted = false;
   if (n_keys == 0) return KMI_OK;
   // distinct keys after this insert: at most size + n_keys, and (6 sigma) at most 1.05 * HLL + keys the HLL never saw
   // (the registers see a 1/HLL_SAMPLE hash-sampled subset: scale back, add 6 sigma of the sampling error)
@@ -422,7 +329,8 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
   // (regions of the exchange buffer share only log_pre < 8 prefix bits: their fine scatter is wider, never skipped)
   const int log_pre = (int)bs.log_pre;
   const int log_seg_slots = idx->nw == 1 ? KMI_LOG_SEG_SLOTS : LOG_SEG_SLOTS2;
-  int log_segs = std::max(std::max(LOG_BUCKETS, log_pre + (log_pre < LOG_BUCKETS ? 1 : 0)), log_cap - log_seg_slots);
+  // (a receive buffer has `sub` regions per prefix: they always need the fine pass to become one region per segment)
+  int log_segs = std::max(std::max(LOG_BUCKETS, log_pre + ((log_pre < LOG_BUCKETS || bs.sub > 1) ? 1 : 0)), log_cap - log_seg_slots);
   // beyond 2^9 fine buckets per coarse bucket the scatter runs shrink to one or two keys: very large tables take TWO
   // fine passes instead (2^(log_f - 8) mid buckets, then 256 fine buckets inside every group of 256 mid regions)
   const bool two_pass = log_pre == LOG_BUCKETS && log_segs - log_pre >= 10 && log_segs - log_pre <= 16;
@@ -466,7 +374,7 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
           bg.cursor = mid.cursor + g * N_BUCKETS;
           bg.capb = (u32)capm; bg.ovf_cap = bs.ovf_cap; bg.hll = nullptr; bg.bases = nullptr;
           bg.log_pre = (u32)LOG_BUCKETS + mid.log_f; bg.pre_mask = N_BUCKETS - 1; bg.pre_base = (u32)(g * N_BUCKETS);
-          bg.ovf_keys = bs.keys + (u64)N_BUCKETS * bs.capb * idx->nw; bg.ovf_cursor = bs.cursor + N_BUCKETS;
+          bg.ovf_keys = idx->nw == 1 ? ovf_base<1>(bs) : ovf_base<2>(bs); bg.ovf_cursor = ovf_cur(bs);
           idx->ops->scatter_fine(idx->stream, bg, fs, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), n_keys / (n_mid / N_BUCKETS) + 1);
           idx->launches++;
         }
@@ -477,7 +385,7 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
       if (perr & PERR_OVERFLOW) {
         // skewed fine buckets exhausted the overflow region: undo its tail and take the L2 path below
         OK(zero_ctr(idx, CTR_PERR));
-        CU(cudaMemcpyAsync(bs.cursor + N_BUCKETS, idx->h_cursor + N_BUCKETS, sizeof(u32), cudaMemcpyHostToDevice, idx->stream));
+        CU(cudaMemcpyAsync(ovf_cur(bs), &idx->h_ovf_cursor, sizeof(u32), cudaMemcpyHostToDevice, idx->stream));
         fine_ok = false;
       }
     }
@@ -496,6 +404,11 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
       return KMI_OK;
     }
   }
+  if (bs.sub > 1) {   // the L2-atomic kernel walks one region per prefix: the caller inserts the regions as key streams
+    if (!not_inserted) return fail(KMI_ERR_ARG, "receive buffer needs the segment path");
+    *not_inserted = true;
+    return KMI_OK;
+  }
   CU(cudaEventRecord(idx->kev[0], idx->stream));
   CU(cudaEventRecord(idx->kev[1], idx->stream));
   idx->ops->insert_buckets(idx->stream, idx->view(), bs, n_keys);
@@ -509,7 +422,7 @@ static int bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 s
 static int insert_keys_chunked(kmi_index* idx, const u64* d_keys, size_t n, bool canon, const u64* d_counts = nullptr);
 
 // several key streams -> the same buckets -> table (one table sweep for all of them); total <= BUCKET_MAX_KEYS
-static int insert_streams_bucketed(kmi_index* idx, const u64* const* d_keys, const u64* counts, int n_streams, bool canon) {
+int kmi::insert_streams_bucketed(kmi_index* idx, const u64* const* d_keys, const u64* counts, int n_streams, bool canon) {
   u64 total = 0;
   for (int i = 0; i < n_streams; ++i) total += counts[i];
   if (total == 0) return KMI_OK;
@@ -598,7 +511,7 @@ extern "C" int kmi_fastq_find_first_record(const uint8_t* bytes, uint64_t mem_of
 }
 
 // ---- record boundaries (pass A + scan), shared by parse and fused build ------------------------
-static int fastq_scan_alloc(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64* n_tiles_out) {
+int kmi::fastq_scan_alloc(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64* n_tiles_out) {
   if ((reinterpret_cast<uintptr_t>(d_bytes) & 15) != 0) return fail(KMI_ERR_ARG, "device text buffer must be 16-byte aligned");
   u64 n_tiles = (n + TILE_BYTES - 1) / TILE_BYTES;
   *n_tiles_out = n_tiles;
@@ -611,7 +524,7 @@ static int fastq_scan_alloc(kmi_index* idx, const uint8_t* d_bytes, size_t n, u6
 }
 // line starts of tiles [t0, t1) (t0 a multiple of 1024) -> per-tile prefixes; the running total of
 // earlier ranges is carried in CTR_CARRY so that ranges can be scanned as their bytes arrive
-static int fastq_scan_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64 t0, u64 t1) {
+int kmi::fastq_scan_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64 t0, u64 t1) {
   if (t1 <= t0) return KMI_OK;
   const u64 nt = t1 - t0, nb = (nt + 1023) / 1024;
   k_fastq_count_lines<<<(unsigned)std::min<u64>((nt + 7) / 8, 148 * 16), COUNT_THREADS, 0, idx->stream>>>(d_bytes, n, idx->tile_lines.as<u32>(), (u32)t0, (u32)nt);
@@ -620,7 +533,7 @@ static int fastq_scan_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, u6
   idx->launches += 3;
   return KMI_OK;
 }
-static int fastq_scan(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64* n_tiles_out) {
+int kmi::fastq_scan(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64* n_tiles_out) {
   OK(fastq_scan_alloc(idx, d_bytes, n, n_tiles_out));
   return fastq_scan_range(idx, d_bytes, n, 0, *n_tiles_out);
 }
@@ -633,7 +546,7 @@ static int fastq_rec_carry(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64
   idx->launches++;
   return KMI_OK;
 }
-static int parse_error(u64 perr) {
+int kmi::parse_error(u64 perr) {
   if (perr & PERR_NO_AT) return fail(KMI_ERR_FORMAT, "malformed FASTQ: missing @ on first line of a record");
   if (perr & PERR_NO_PLUS) return fail(KMI_ERR_FORMAT, "malformed FASTQ: missing + on third line of a record");
   if (perr & PERR_ID_RANGE) return fail(KMI_ERR_ARG, "FASTQ record longer than 64 KiB: ShortSequenceKmerId cannot hold the k-mer's offset in its record");
@@ -664,229 +577,6 @@ extern "C" int kmi_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_
   CU(cudaStreamSynchronize(idx->stream));
   if (n_kmers) *n_kmers = host[CTR_NKMERS];
   return parse_error(host[CTR_PERR]);
-}
-
-// S1-S4 fused for the sharded build: text -> one key region per owning rank (the all-to-all send buffers)
-extern "C" int kmi_parse_fastq_by_owner_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* d_regions,
-                                            size_t region_cap, uint64_t* h_counts, uint64_t* n_kmers) {
-  if (!idx || (!d_bytes && n) || !d_regions || !h_counts) return fail(KMI_ERR_ARG, "null argument");
-  if (region_cap == 0 || region_cap > 0xffffffffULL) return fail(KMI_ERR_ARG, "region capacity out of range");
-  CU(cudaSetDevice(idx->cfg.device));
-  const u32 p = (u32)idx->cfg.nranks;
-  for (u32 r = 0; r < p; ++r) h_counts[r] = 0;
-  if (n_kmers) *n_kmers = 0;
-  u64 n_tiles = 0;
-  OK(fastq_scan(idx, d_bytes, n, &n_tiles));
-  if (n_tiles == 0) return KMI_OK;
-  if (!idx->hll_ready) {
-    OK(idx->bkt_meta.ensure(sizeof(u32) * META_WORDS));
-    CU(cudaMemsetAsync(idx->bkt_meta.p, 0, sizeof(u32) * META_WORDS, idx->stream));
-    idx->hll_ready = true;
-  } else {
-    CU(cudaMemsetAsync(idx->bkt_meta.p, 0, sizeof(u32) * META_HLL, idx->stream));
-  }
-  OK(zero_ctr(idx, CTR_NKMERS));
-  OK(zero_ctr(idx, CTR_PERR));
-  BucketSink bs;
-  bs.keys = reinterpret_cast<u64*>(d_regions); bs.cursor = idx->bkt_meta.as<u32>(); bs.capb = (u32)region_cap; bs.ovf_cap = 0;
-  bs.hll = nullptr; bs.bases = nullptr;
-  KeySink nosink; nosink.keys = nullptr; nosink.ids = nullptr; nosink.cap = 0; nosink.cursor = nullptr;
-  TableView none; none.slots = nullptr; none.mask = 0; none.shift = 63; none.size = nullptr; none.error = nullptr;
-  idx->ops->fastq_kmers(idx->stream, 3, d_bytes, n, n_tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), nosink, none, bs,
-                        idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0,
-                        idx->cfg.nsplit != 0, 0, p | (idx->xchg_log_cb << 16));
-  idx->launches++;
-  u64 host[CTR_N];
-  CU(cudaMemcpyAsync(host, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
-  CU(cudaMemcpyAsync(idx->h_cursor, bs.cursor, sizeof(u32) * (N_BUCKETS + 1), cudaMemcpyDeviceToHost, idx->stream));
-  CU(cudaStreamSynchronize(idx->stream));
-  if (n_kmers) *n_kmers = host[CTR_NKMERS];
-  if (host[CTR_PERR] & PERR_OVERFLOW) return fail(KMI_ERR_CAPACITY, "an owner region overflowed (skewed owners): use parse + partition");
-  for (u32 r = 0; r < p; ++r) h_counts[r] = idx->h_cursor[r];
-  return parse_error(host[CTR_PERR]);
-}
-
-// ---- fused exchange over NVLink peer memory ---------------------------------------------------------------
-// Replaces mxx::all2allv in imxx::distribute (incremental_mxx.hpp:1098) for the build: every rank owns a
-// receive buffer of nranks regions (one per SOURCE rank); the parse kernel of rank s writes the keys owned
-// by rank r straight into region s of rank r's buffer with plain stores over NVLink (CUDA IPC mapping), so
-// the transfer overlaps the parsing and no separate collective moves keys. Only the nranks x nranks count
-// matrix still travels through the process group (it doubles as the "writes are complete" handshake).
-static void exchange_close(kmi_index* idx) {
-  for (size_t r = 0; r < idx->xchg_peer.size(); ++r)
-    if (idx->xchg_peer[r] && (int)r != idx->cfg.rank) cudaIpcCloseMemHandle(idx->xchg_peer[r]);
-  idx->xchg_peer.clear();
-  if (idx->xchg_recv) cudaFree(idx->xchg_recv);
-  idx->xchg_recv = nullptr;
-  idx->xchg_region_cap = 0;
-}
-
-extern "C" int kmi_exchange_setup(kmi_index* idx, size_t region_cap, uint8_t* handle_out) {
-  if (!idx || !handle_out || region_cap == 0 || region_cap > 0xffffffffULL) return fail(KMI_ERR_ARG, "bad argument");
-  CU(cudaSetDevice(idx->cfg.device));
-  static_assert(sizeof(cudaIpcMemHandle_t) == KMI_IPC_HANDLE_BYTES, "IPC handle size");
-  CU(cudaStreamSynchronize(idx->stream));
-  exchange_close(idx);
-  // Sub-bin layout (one-word keys, 2/4/8 ranks; opt-in with KMI_EXCHANGE_PREFIX=1): the sender's 256-way shared-memory
-  // sort bins by (owner, top bits of the slot hash), so what arrives is already cut by hash prefix and the receiver needs
-  // no coarse scatter pass. Measured at 2 GPUs it LOSES: the receiver saves 2.1 ms (11.9 -> 9.8) but the peer stores
-  // shrink from 8 KB to 64-byte runs and the parse+exchange kernel goes from 7.4 to 12.8 ms (250 GB/s over NVLink), so
-  // the default keeps one large run per owner.
-  const int p0 = idx->cfg.nranks;
-  const char* env = getenv("KMI_EXCHANGE_PREFIX");
-  idx->xchg_log_cb = 0;
-  if (idx->nw == 1 && p0 >= 2 && p0 <= 8 && (p0 & (p0 - 1)) == 0 && env && env[0] == '1') {
-    int lp = 0;
-    while ((1 << lp) < p0) ++lp;
-    idx->xchg_log_cb = (u32)(LOG_BUCKETS - lp);
-  }
-  size_t bytes = (size_t)p0 * region_cap * idx->nw * sizeof(u64);
-  if (idx->xchg_log_cb) {
-    const u64 cb = 1ULL << idx->xchg_log_cb;
-    idx->xchg_cap_bin = region_cap / cb + region_cap / (cb * 16) + 1024;
-    idx->xchg_ovf_cap = (u64)p0 * region_cap / 8 + 4096;
-    bytes = ((size_t)N_BUCKETS * idx->xchg_cap_bin + idx->xchg_ovf_cap) * sizeof(u64);
-  }
-  cudaError_t e = cudaMalloc(&idx->xchg_recv, bytes);
-  if (e != cudaSuccess) { idx->xchg_recv = nullptr; return fail(KMI_ERR_NOMEM, "cudaMalloc exchange buffer %zu: %s", bytes, cudaGetErrorString(e)); }
-  idx->xchg_region_cap = region_cap;
-  cudaIpcMemHandle_t h;
-  CU(cudaIpcGetMemHandle(&h, idx->xchg_recv));
-  memcpy(handle_out, &h, sizeof(h));
-  return KMI_OK;
-}
-
-extern "C" int kmi_exchange_connect(kmi_index* idx, const uint8_t* handles) {
-  if (!idx || !handles) return fail(KMI_ERR_ARG, "null argument");
-  if (!idx->xchg_recv) return fail(KMI_ERR_ARG, "kmi_exchange_setup first");
-  CU(cudaSetDevice(idx->cfg.device));
-  const int p = idx->cfg.nranks, me = idx->cfg.rank;
-  idx->xchg_peer.assign(p, nullptr);
-  const u32 cb = 1u << idx->xchg_log_cb;                 // 1 without sub-bins
-  std::vector<u64*> bases((size_t)p * cb);
-  for (int r = 0; r < p; ++r) {
-    void* base = idx->xchg_recv;
-    if (r != me) {
-      cudaIpcMemHandle_t h;
-      memcpy(&h, handles + (size_t)r * KMI_IPC_HANDLE_BYTES, sizeof(h));
-      cudaError_t e = cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess);
-      if (e != cudaSuccess) { exchange_close(idx); return fail(KMI_ERR_CUDA, "cudaIpcOpenMemHandle(rank %d): %s", r, cudaGetErrorString(e)); }
-    }
-    idx->xchg_peer[r] = base;
-    if (!idx->xchg_log_cb) {
-      bases[r] = reinterpret_cast<u64*>(base) + (size_t)me * idx->xchg_region_cap * idx->nw;   // my region in r's buffer
-    } else {
-      for (u32 c = 0; c < cb; ++c)                       // my sub-bin c in r's buffer: region me * CB + c
-        bases[(size_t)r * cb + c] = reinterpret_cast<u64*>(base) + ((size_t)me * cb + c) * idx->xchg_cap_bin;
-    }
-  }
-  OK(idx->xchg_bases.ensure(sizeof(u64*) * bases.size()));
-  CU(cudaMemcpy(idx->xchg_bases.p, bases.data(), sizeof(u64*) * bases.size(), cudaMemcpyHostToDevice));
-  return KMI_OK;
-}
-
-extern "C" int kmi_exchange_bins(kmi_index* idx, uint32_t* bins_per_rank) {
-  if (!idx || !bins_per_rank) return fail(KMI_ERR_ARG, "null argument");
-  *bins_per_rank = 1u << idx->xchg_log_cb;
-  return KMI_OK;
-}
-
-// parse + owner + scatter into the owners' receive buffers. h_send_counts[r] = keys written to rank r.
-// The caller must make sure (barrier) that no peer is still reading its receive buffer from the last round.
-extern "C" int kmi_exchange_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t* h_send_counts,
-                                            uint64_t* n_kmers) {
-  if (!idx || (!d_bytes && n) || !h_send_counts) return fail(KMI_ERR_ARG, "null argument");
-  if (idx->xchg_peer.empty()) return fail(KMI_ERR_ARG, "kmi_exchange_connect first");
-  CU(cudaSetDevice(idx->cfg.device));
-  const u32 p = (u32)idx->cfg.nranks;
-  const u32 n_bins = p << idx->xchg_log_cb;
-  for (u32 r = 0; r < n_bins; ++r) h_send_counts[r] = 0;
-  if (n_kmers) *n_kmers = 0;
-  u64 n_tiles = 0;
-  OK(fastq_scan(idx, d_bytes, n, &n_tiles));
-  if (n_tiles == 0) return KMI_OK;
-  if (!idx->hll_ready) {
-    OK(idx->bkt_meta.ensure(sizeof(u32) * META_WORDS));
-    CU(cudaMemsetAsync(idx->bkt_meta.p, 0, sizeof(u32) * META_WORDS, idx->stream));
-    idx->hll_ready = true;
-  } else {
-    CU(cudaMemsetAsync(idx->bkt_meta.p, 0, sizeof(u32) * META_HLL, idx->stream));
-  }
-  OK(zero_ctr(idx, CTR_NKMERS));
-  OK(zero_ctr(idx, CTR_PERR));
-  BucketSink bs;
-  bs.keys = nullptr; bs.cursor = idx->bkt_meta.as<u32>(); bs.ovf_cap = 0; bs.hll = nullptr;
-  bs.capb = (u32)(idx->xchg_log_cb ? idx->xchg_cap_bin : idx->xchg_region_cap);
-  bs.bases = idx->xchg_bases.as<u64*>();
-  KeySink nosink; nosink.keys = nullptr; nosink.ids = nullptr; nosink.cap = 0; nosink.cursor = nullptr;
-  TableView none; none.slots = nullptr; none.mask = 0; none.shift = 63; none.size = nullptr; none.error = nullptr;
-  idx->ops->fastq_kmers(idx->stream, 3, d_bytes, n, n_tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), nosink, none, bs,
-                        idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0,
-                        idx->cfg.nsplit != 0, 0, p | (idx->xchg_log_cb << 16));
-  idx->launches++;
-  u64 host[CTR_N];
-  CU(cudaMemcpyAsync(host, idx->ctr, sizeof(u64) * CTR_N, cudaMemcpyDeviceToHost, idx->stream));
-  CU(cudaMemcpyAsync(idx->h_cursor, bs.cursor, sizeof(u32) * (N_BUCKETS + 1), cudaMemcpyDeviceToHost, idx->stream));
-  CU(cudaStreamSynchronize(idx->stream));   // kernel complete => its peer stores are visible system-wide
-  if (n_kmers) *n_kmers = host[CTR_NKMERS];
-  if (host[CTR_PERR] & PERR_OVERFLOW) return fail(KMI_ERR_CAPACITY, "an owner region overflowed (skewed owners)");
-  for (u32 r = 0; r < n_bins; ++r) h_send_counts[r] = idx->h_cursor[r];
-  return parse_error(host[CTR_PERR]);
-}
-
-// insert what the peers wrote: h_recv_counts[s] = keys rank s put into region s of this rank's buffer
-extern "C" int kmi_exchange_insert(kmi_index* idx, const uint64_t* h_recv_counts) {
-  if (!idx || !h_recv_counts) return fail(KMI_ERR_ARG, "null argument");
-  if (!idx->xchg_recv) return fail(KMI_ERR_ARG, "kmi_exchange_setup first");
-  if (idx->cfg.mode != KMI_MODE_COUNT) return fail(KMI_ERR_UNSUPPORTED, "exchange insert is built for the count index");
-  CU(cudaSetDevice(idx->cfg.device));
-  const int p = idx->cfg.nranks;
-  if (idx->xchg_log_cb) {
-    // region s * CB + c holds the keys of source s whose slot hash starts with c: the 256 regions go to the fine scatter
-    // as they are (k_scatter_fine with log_pre = log2 CB), no coarse pass
-    u32 cur[N_BUCKETS + 1];
-    u64 total = 0;
-    for (int r = 0; r < N_BUCKETS; ++r) {
-      if (h_recv_counts[r] > idx->xchg_cap_bin) return fail(KMI_ERR_ARG, "receive count exceeds the sub-bin capacity");
-      cur[r] = (u32)h_recv_counts[r];
-      total += h_recv_counts[r];
-    }
-    cur[N_BUCKETS] = 0;
-    if (total == 0) return KMI_OK;
-    if (total > BUCKET_MAX_KEYS) return fail(KMI_ERR_ARG, "exchange round of %llu keys", (unsigned long long)total);
-    BucketSink bs;
-    bs.keys = reinterpret_cast<u64*>(idx->xchg_recv);
-    bs.cursor = idx->bkt_meta.as<u32>();
-    bs.hll = idx->bkt_meta.as<u32>() + META_HLL;
-    bs.capb = (u32)idx->xchg_cap_bin;
-    bs.ovf_cap = (u32)std::min<u64>(idx->xchg_ovf_cap, 0xffffffffULL);
-    bs.bases = nullptr;
-    bs.log_pre = idx->xchg_log_cb;
-    bs.pre_mask = (1u << idx->xchg_log_cb) - 1u;
-    CU(cudaMemcpyAsync(bs.cursor, cur, sizeof(cur), cudaMemcpyHostToDevice, idx->stream));
-    OK(zero_ctr(idx, CTR_PERR));
-    std::vector<u32> reg;
-    u64 host[CTR_N];
-    OK(bucket_readback(idx, bs, host, reg));
-    return bucket_commit(idx, bs, total, host[CTR_SIZE], reg);
-  }
-  std::vector<const u64*> ptrs(p);
-  std::vector<u64> cnt(p);
-  u64 total = 0;
-  for (int s = 0; s < p; ++s) {
-    if (h_recv_counts[s] > idx->xchg_region_cap) return fail(KMI_ERR_ARG, "receive count exceeds the region capacity");
-    ptrs[s] = reinterpret_cast<const u64*>(idx->xchg_recv) + (size_t)s * idx->xchg_region_cap * idx->nw;
-    cnt[s] = h_recv_counts[s];
-    total += cnt[s];
-  }
-  // keys arrive canonical already (the sender's parser applied the transform)
-  if (total <= BUCKET_MAX_KEYS && (idx->build_path == 2 || (idx->build_path == 0 && total >= AUTO_BUCKET_KEYS)))
-    return insert_streams_bucketed(idx, ptrs.data(), cnt.data(), p, false);
-  for (int s = 0; s < p; ++s) {
-    if (idx->build_path != 1 && cnt[s] >= AUTO_BUCKET_KEYS) OK(insert_keys_bucketed(idx, ptrs[s], cnt[s], false));
-    else OK(insert_keys_chunked(idx, ptrs[s], cnt[s], false));
-  }
-  return KMI_OK;
 }
 
 // S1-S5 with direct atomics: text -> table, no key stream in HBM (tiles [tile, tile_end))
@@ -1414,7 +1104,7 @@ extern "C" int kmi_table_info(kmi_index* idx, uint64_t* slots, uint64_t* slot_by
     u64 b = idx->cap * idx->slot_bytes;
     const DevBuf* bufs[] = {&idx->tile_lines, &idx->block_sums, &idx->stage_in, &idx->stage_keys, &idx->stage_vals,
                             &idx->stage_out, &idx->stage_found, &idx->hist, &idx->hist_sums, &idx->log_keys, &idx->log_ids,
-                            &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->xchg_bases, &idx->mid_keys, &idx->mid_cur};
+                            &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->mid_keys, &idx->mid_cur};
     for (const DevBuf* d : bufs) b += d->cap;
     *device_bytes = b;
   }

@@ -42,13 +42,18 @@ struct BucketSink {
   // regions of a first fine pass, taken 256 at a time): prefix of region r = pre_base + (r & pre_mask); the overflow
   // region then is not "behind region 255" but wherever the owner of the whole set keeps it.
   u32 pre_base = 0;
-  u64* ovf_keys = nullptr;        // null: keys + N_BUCKETS * capb (* words per key)
-  u32* ovf_cursor = nullptr;      // null: cursor + N_BUCKETS
+  // Receive buffer of the sharded build (kmi_dist.cu): every hash prefix has `sub` regions, one per SOURCE rank, filled by
+  // that rank's k_owner_push over NVLink: region index = prefix * sub + source, N_BUCKETS * sub regions and cursors in all.
+  // The scatter kernels of the local build always write sub == 1 sinks; the fine scatter and the HLL kernel read any sub.
+  u32 sub = 1;
+  u64* ovf_keys = nullptr;        // null: keys + N_BUCKETS * sub * capb (* words per key)
+  u32* ovf_cursor = nullptr;      // null: cursor + N_BUCKETS * sub
 };
-template <int NW> __device__ __forceinline__ u64* ovf_base(const BucketSink& bs) {
-  return bs.ovf_keys ? bs.ovf_keys : bs.keys + (u64)N_BUCKETS * bs.capb * NW;
+static constexpr int MAX_SUB = 8;                         // ranks of one NVLink domain that push into one receive buffer
+template <int NW> __host__ __device__ __forceinline__ u64* ovf_base(const BucketSink& bs) {
+  return bs.ovf_keys ? bs.ovf_keys : bs.keys + (u64)N_BUCKETS * bs.sub * bs.capb * NW;
 }
-__device__ __forceinline__ u32* ovf_cur(const BucketSink& bs) { return bs.ovf_cursor ? bs.ovf_cursor : bs.cursor + N_BUCKETS; }
+__host__ __device__ __forceinline__ u32* ovf_cur(const BucketSink& bs) { return bs.ovf_cursor ? bs.ovf_cursor : bs.cursor + N_BUCKETS * bs.sub; }
 
 template <int NW> struct BucketSmem;
 template <> struct BucketSmem<0> { u32 unused; };   // kernels instantiated without the bucket sink
@@ -170,8 +175,8 @@ __device__ __forceinline__ void bucket_round(const BucketSink& bs, BucketSmem<NW
     u32 at = sm.delta[b] + r;
     u64* base = bs.bases ? bs.bases[b] : bs.keys + (u64)b * bs.capb * NW;
     if (at >= bs.capb) {
-      at = atomicAdd(bs.cursor + N_BUCKETS, 1u);
-      base = bs.keys + (u64)N_BUCKETS * bs.capb * NW;
+      at = atomicAdd(ovf_cur(bs), 1u);
+      base = ovf_base<NW>(bs);
       if (at >= bs.ovf_cap) { atomicOr(perr, PERR_OVERFLOW); continue; }
     }
     if (NW == 1) base[at] = sm.sorted[r];
@@ -230,16 +235,18 @@ k_scatter_keys(const u64* __restrict__ keys, u64 n, BucketSink bs, u32* __restri
 template <int K>
 __global__ void __launch_bounds__(256) k_hll_buckets(BucketSink bs) {
   constexpr int NW = (K <= 32 ? 1 : 2);
-  // y-slice = (group, j): the region of group `y / 4` whose prefix covers sampled bucket j * HLL_SAMPLE; a local build
-  // has one group (region = bucket), the exchange buffer one per source rank; the last slice is the overflow region
-  const u32 n_groups = N_BUCKETS >> bs.log_pre;          // regions per prefix value
-  const bool ovf = blockIdx.y == HLL_SAMPLE_BUCKETS * n_groups;
-  const u32 grp = blockIdx.y / HLL_SAMPLE_BUCKETS, j = blockIdx.y % HLL_SAMPLE_BUCKETS;
-  const u32 b = ovf ? (u32)N_BUCKETS : (grp << bs.log_pre) + ((j * HLL_SAMPLE) >> (LOG_BUCKETS - bs.log_pre));
-  const u32 n = ovf ? min(bs.cursor[N_BUCKETS], bs.ovf_cap) : min(bs.cursor[b], bs.capb);
-  const u64 base = (u64)b * bs.capb;
+  // y-slice = (group, j, s): the region of group `grp` whose prefix covers sampled bucket j * HLL_SAMPLE, sub-region s; a
+  // local build has one group and one sub-region (region = bucket); the last slice is the overflow region
+  const u32 n_groups = N_BUCKETS >> bs.log_pre;          // regions per prefix value (two-pass layouts)
+  const u32 n_slices = HLL_SAMPLE_BUCKETS * n_groups * bs.sub;
+  const bool ovf = blockIdx.y == n_slices;
+  const u32 sidx = blockIdx.y % bs.sub, y = blockIdx.y / bs.sub;
+  const u32 grp = y / HLL_SAMPLE_BUCKETS, j = y % HLL_SAMPLE_BUCKETS;
+  const u32 b = ((grp << bs.log_pre) + ((j * HLL_SAMPLE) >> (LOG_BUCKETS - bs.log_pre))) * bs.sub + sidx;
+  const u32 n = ovf ? min(*ovf_cur(bs), bs.ovf_cap) : min(bs.cursor[b], bs.capb);
+  const u64* src = ovf ? ovf_base<NW>(bs) : bs.keys + (u64)b * bs.capb * NW;
   for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const u64 h = slot_hash<K>(load_key<NW>(bs.keys, base + i));
+    const u64 h = slot_hash<K>(load_key<NW>(src, i));
     if (hll_sampled(bucket_of(h))) hll_update(bs.hll, h);
   }
 }
@@ -258,7 +265,7 @@ __global__ void __launch_bounds__(256) k_insert_buckets(TableView t, BucketSink 
     pre[threadIdx.x] = ex;
     if (threadIdx.x == 0) {
       pre[N_BUCKETS] = total;
-      pre[N_BUCKETS + 1] = (u64)total + min(bs.cursor[N_BUCKETS], bs.ovf_cap);
+      pre[N_BUCKETS + 1] = (u64)total + min(*ovf_cur(bs), bs.ovf_cap);
     }
   }
   __syncthreads();
@@ -271,8 +278,7 @@ __global__ void __launch_bounds__(256) k_insert_buckets(TableView t, BucketSink 
       const int mid = (lo + hi + 1) >> 1;
       if (pre[mid] <= g) lo = mid; else hi = mid - 1;
     }
-    const u64 at = (u64)lo * bs.capb + (g - pre[lo]);
-    Key<NW> key = load_key<NW>(bs.keys, at);
+    const Key<NW> key = lo < N_BUCKETS ? load_key<NW>(bs.keys, (u64)lo * bs.capb + (g - pre[lo])) : load_key<NW>(ovf_base<NW>(bs), g - pre[lo]);
     bool was_new;
     const u64 s = table_upsert<NW>(t, key, slot_hash<K>(key), was_new);
     if (s != ~0ULL) {
@@ -324,7 +330,7 @@ __global__ void __launch_bounds__(TILE_THREADS, KMI_FINE_MINB)
 k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
   static_assert(K <= 32, "segment path is built for one-word keys");
   extern __shared__ __align__(16) unsigned char fine_raw[];
-  __shared__ u32 cpre[N_BUCKETS + 1];
+  __shared__ u32 cpre[N_BUCKETS * MAX_SUB + 1];
   __shared__ u32 tmp[TILE_THREADS / 32 + 1];
   constexpr int R = FINE_ROUND / TILE_THREADS;
   const int t = threadIdx.x;
@@ -335,29 +341,31 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
   u32* delta = hist + F;                                                // F
   unsigned short* sbid = reinterpret_cast<unsigned short*>(delta + F);  // FINE_ROUND
   const u32 EPT = F >= TILE_THREADS ? F / TILE_THREADS : 1u;   // histogram entries per thread
-  const u32 my_cnt = min(bs.cursor[t], bs.capb);
+  const u32 sub = bs.sub, NR = N_BUCKETS * sub;                // input regions: prefix * sub + source
   u32 n_chunks;
   {
-    const u32 ex = block_excl_scan((my_cnt + FINE_ROUND - 1) / FINE_ROUND, tmp, n_chunks);
-    cpre[t] = ex;
-    if (t == 0) cpre[N_BUCKETS] = n_chunks;
+    u32 mine = 0;
+    for (u32 q = 0; q < sub; ++q) mine += (min(bs.cursor[t * sub + q], bs.capb) + FINE_ROUND - 1) / FINE_ROUND;
+    u32 ex = block_excl_scan(mine, tmp, n_chunks);
+    for (u32 q = 0; q < sub; ++q) { cpre[t * sub + q] = ex; ex += (min(bs.cursor[t * sub + q], bs.capb) + FINE_ROUND - 1) / FINE_ROUND; }
+    if (t == 0) cpre[NR] = n_chunks;
   }
   for (u32 f = t; f < F; f += TILE_THREADS) hist[f] = 0;
   __syncthreads();
   // software pipeline: the keys of the NEXT chunk are requested before this chunk is ranked, so the
   // global-load latency hides behind a whole round
   auto locate = [&](u32 c, u32& b, u32& m, const u64*& src) {
-    int lo = 0, hi = N_BUCKETS - 1;                       // largest b with cpre[b] <= c and a non-empty bucket
+    int lo = 0, hi = (int)NR - 1;                         // largest region with cpre[region] <= c: the non-empty one that holds chunk c
 #pragma unroll
-    for (int s = 0; s < LOG_BUCKETS; ++s) {
+    for (int s = 0; s < LOG_BUCKETS + 3; ++s) {
       const int mid = (lo + hi + 1) >> 1;
       if (cpre[mid] <= c) lo = mid; else hi = mid - 1;
     }
-    b = (u32)lo;
-    const u32 first = (c - cpre[b]) * FINE_ROUND;
-    const u32 cnt_b = min(bs.cursor[b], bs.capb);
+    const u32 first = (c - cpre[lo]) * FINE_ROUND;
+    const u32 cnt_b = min(bs.cursor[lo], bs.capb);
     m = min((u32)FINE_ROUND, cnt_b - first);
-    src = bs.keys + (u64)b * bs.capb + first;
+    src = bs.keys + (u64)lo * bs.capb + first;
+    b = sub == 1 ? (u32)lo : (u32)lo / sub;               // hash-prefix index of the region
   };
   u64 nkey[R];
   u32 nb = 0, nm = 0;
@@ -593,8 +601,8 @@ k_insert_segments(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, co
           atomicAdd(vp, 1u);
           key = KEY_EMPTY_TOP;
         } else if (++li == SEG) {
-          const u32 o = atomicAdd(bs.cursor + N_BUCKETS, 1u);
-          if (o < bs.ovf_cap) bs.keys[(u64)N_BUCKETS * bs.capb + o] = key;
+          const u32 o = atomicAdd(ovf_cur(bs), 1u);
+          if (o < bs.ovf_cap) ovf_base<1>(bs)[o] = key;
           else atomicOr(t.error, TERR_SPILL);   // dropped: sticky table error, every caller's check_table_error sees it
           key = KEY_EMPTY_TOP;
         }
@@ -633,7 +641,7 @@ __global__ void __launch_bounds__(TILE_THREADS, 4)
 k_scatter_fine2(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
   static_assert(K > 32, "two-word keys");
   extern __shared__ __align__(16) unsigned char fine_raw[];
-  __shared__ u32 cpre[N_BUCKETS + 1];
+  __shared__ u32 cpre[N_BUCKETS * MAX_SUB + 1];
   __shared__ u32 tmp[TILE_THREADS / 32 + 1];
   constexpr int R = FINE_ROUND2 / TILE_THREADS;
   const int t = threadIdx.x;
@@ -643,25 +651,28 @@ k_scatter_fine2(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
   u32* hist = reinterpret_cast<u32*>(dst + F);
   u32* delta = hist + F;
   unsigned short* sbid = reinterpret_cast<unsigned short*>(delta + F);
-  const u32 my_cnt = min(bs.cursor[t], bs.capb);
+  const u32 sub = bs.sub, NR = N_BUCKETS * sub;
   u32 n_chunks;
   {
-    const u32 ex = block_excl_scan((my_cnt + FINE_ROUND2 - 1) / FINE_ROUND2, tmp, n_chunks);
-    cpre[t] = ex;
-    if (t == 0) cpre[N_BUCKETS] = n_chunks;
+    u32 mine = 0;
+    for (u32 q = 0; q < sub; ++q) mine += (min(bs.cursor[t * sub + q], bs.capb) + FINE_ROUND2 - 1) / FINE_ROUND2;
+    u32 ex = block_excl_scan(mine, tmp, n_chunks);
+    for (u32 q = 0; q < sub; ++q) { cpre[t * sub + q] = ex; ex += (min(bs.cursor[t * sub + q], bs.capb) + FINE_ROUND2 - 1) / FINE_ROUND2; }
+    if (t == 0) cpre[NR] = n_chunks;
   }
   for (u32 f = t; f < F; f += TILE_THREADS) hist[f] = 0;
   __syncthreads();
   for (u32 c = blockIdx.x; c < n_chunks; c += gridDim.x) {
-    int lo = 0, hi = N_BUCKETS - 1;                       // largest b with cpre[b] <= c
+    int lo = 0, hi = (int)NR - 1;                         // largest region with cpre[region] <= c
 #pragma unroll
-    for (int s = 0; s < LOG_BUCKETS; ++s) {
+    for (int s = 0; s < LOG_BUCKETS + 3; ++s) {
       const int mid = (lo + hi + 1) >> 1;
       if (cpre[mid] <= c) lo = mid; else hi = mid - 1;
     }
-    const u32 b = (u32)lo, first = (c - cpre[b]) * FINE_ROUND2;
-    const u32 m = min((u32)FINE_ROUND2, min(bs.cursor[b], bs.capb) - first);
-    const ulonglong2* src = reinterpret_cast<const ulonglong2*>(bs.keys) + (u64)b * bs.capb + first;
+    const u32 first = (c - cpre[lo]) * FINE_ROUND2;
+    const u32 m = min((u32)FINE_ROUND2, min(bs.cursor[lo], bs.capb) - first);
+    const ulonglong2* src = reinterpret_cast<const ulonglong2*>(bs.keys) + (u64)lo * bs.capb + first;
+    const u32 b = sub == 1 ? (u32)lo : (u32)lo / sub;
     const u64 region0 = (u64)(bs.pre_base + (b & bs.pre_mask)) << fs.log_f;
     ulonglong2 key[R];
     u32 fid[R], rank[R];
@@ -780,8 +791,8 @@ k_insert_segments2(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, c
         if (h == KEY_LOCK_TOP) continue;                   // being claimed: look again
         if (h == key.y && lds_volatile(slo + li) == key.x) { atomicAdd(sval + li, 1u); break; }
         if (++li == SEG) {                                 // ran off the segment: global linear probe continues there
-          const u32 o = atomicAdd(bs.cursor + N_BUCKETS, 1u);
-          if (o < bs.ovf_cap) reinterpret_cast<ulonglong2*>(bs.keys)[(u64)N_BUCKETS * bs.capb + o] = key;
+          const u32 o = atomicAdd(ovf_cur(bs), 1u);
+          if (o < bs.ovf_cap) reinterpret_cast<ulonglong2*>(ovf_base<2>(bs))[o] = key;
           else atomicOr(t.error, TERR_SPILL);   // dropped: sticky table error, every caller's check_table_error sees it
           break;
         }
@@ -800,15 +811,176 @@ k_insert_segments2(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, c
   if ((tid & 31) == 0 && n_new) atomicAdd(t.size, (u64)n_new);
 }
 
+// ======================================================================================================
+// Sharded build: coarse buckets -> the owners' receive buffers over NVLink (replaces mxx::all2allv of
+// imxx::distribute, reference src/io/incremental_mxx.hpp:1039-1109, for the count-index build).
+//
+// The parser has already cut this rank's k-mers into the 256 hash-prefix buckets of its LOCAL staging buffer (the same
+// kernel as the single-GPU build). This kernel reads a bucket chunk by chunk, computes each key's owner with the
+// reference's dist hash (KeyToRank = farm/murmur % p, distributed_densehash_map.hpp:148-170, bit-exact), ranks the chunk
+// by owner in shared memory, and stores each owner's run — ~FINE_ROUND / p consecutive keys — straight into region
+// (prefix, this rank) of that owner's receive buffer (peer memory mapped with CUDA IPC; plain stores that travel over
+// NVLink / NVSwitch). Because every (prefix, source) region has exactly one writer, its fill cursor is a LOCAL counter:
+// no remote atomics, and the receiver's table build starts at its fine scatter (the regions of one prefix are the
+// `sub` inputs of k_scatter_fine) — no coarse pass over received keys. Runs while the parser produces the next round.
+struct PushSink {
+  u64* const* peer_keys;  // [p]: base of owner r's receive regions as seen from THIS process (own buffer for r == me)
+  u32* cursor;            // [N_BUCKETS * p], local: keys sent so far to owner r for prefix b at b * p + r (accumulates over rounds)
+  u32 cap_sub;            // keys per (prefix, source) region of a receive buffer
+  u32 p, me;              // ranks; this rank is sub-region `me` of every prefix in every receive buffer
+  u32* status;            // |= 1: a receive region would overflow (skew) -> the round is redone through the generic exchange
+};
+static constexpr int PUSH_ROUND = 2048;
+template <int NW> struct PushSmem {
+  u64 sorted[PUSH_ROUND * NW];
+  u64 dst[MAX_SUB];       // byte address sorted[0] would land at in owner r's region (0: the run does not fit)
+  u32 hist[MAX_SUB];      // keys per owner while ranking, exclusive prefix afterwards
+  uint8_t sbid[PUSH_ROUND];
+};
+template <int K, int HASH>
+__global__ void __launch_bounds__(TILE_THREADS, 4)
+k_owner_push(BucketSink bs, PushSink ps) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  constexpr int R = PUSH_ROUND / TILE_THREADS;
+  __shared__ PushSmem<NW> sm;
+  __shared__ u32 cpre[N_BUCKETS + 2];
+  __shared__ u32 tmp[TILE_THREADS / 32 + 1];
+  const int t = threadIdx.x, lane = t & 31;
+  const u32 lt = (1u << lane) - 1u;
+  const u32 p = ps.p;
+  // chunks of the 256 buckets, then of the overflow region (keys of any prefix: placed one by one)
+  u32 n_chunks;
+  {
+    const u32 mine = (min(bs.cursor[t], bs.capb) + PUSH_ROUND - 1) / PUSH_ROUND;
+    const u32 ex = block_excl_scan(mine, tmp, n_chunks);
+    cpre[t] = ex;
+    if (t == 0) {
+      cpre[N_BUCKETS] = n_chunks;
+      cpre[N_BUCKETS + 1] = n_chunks + (min(*ovf_cur(bs), bs.ovf_cap) + PUSH_ROUND - 1) / PUSH_ROUND;
+    }
+  }
+  if (t < MAX_SUB) sm.hist[t] = 0;
+  __syncthreads();
+  const u32 n_all = cpre[N_BUCKETS + 1];
+  for (u32 c = blockIdx.x; c < n_all; c += gridDim.x) {
+    int lo = 0, hi = N_BUCKETS;                           // largest region with cpre[region] <= c (256 = overflow region)
+#pragma unroll
+    for (int s = 0; s < LOG_BUCKETS + 1; ++s) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (cpre[mid] <= c) lo = mid; else hi = mid - 1;
+    }
+    const u32 b = (u32)lo, first = (c - cpre[b]) * PUSH_ROUND;
+    const bool is_ovf = b == N_BUCKETS;
+    const u32 cnt_b = is_ovf ? min(*ovf_cur(bs), bs.ovf_cap) : min(bs.cursor[b], bs.capb);
+    const u32 m = min((u32)PUSH_ROUND, cnt_b - first);
+    const u64* src = (is_ovf ? ovf_base<NW>(bs) : bs.keys + (u64)b * bs.capb * NW) + (u64)first * NW;
+    Key<NW> key[R];
+    u32 own[R], rank[R];
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+      const u32 i = q * TILE_THREADS + t;
+      own[q] = BKT_NONE;
+      if (i < m) {
+        key[q] = load_key<NW>(src, i);
+        u64 hs, hd;
+        kmer_hashes<K, HASH>(key[q], hs, hd);
+        own[q] = mod_ranks(hd, p);
+      }
+    }
+    if (is_ovf) {                                          // rare: every key finds its own prefix and slot
+#pragma unroll
+      for (int q = 0; q < R; ++q) {
+        if (own[q] == BKT_NONE) continue;
+        const u32 pb = bucket_of(slot_hash<K>(key[q]));
+        const u32 at = atomicAdd(ps.cursor + pb * p + own[q], 1u);
+        if (at < ps.cap_sub) store_key<NW>(ps.peer_keys[own[q]] + ((u64)(pb * p + ps.me) * ps.cap_sub) * NW, at, key[q]);
+        else atomicOr(ps.status, 1u);
+      }
+      continue;                                            // block-uniform
+    }
+    // rank by owner: one shared-memory atomic per distinct owner and warp instruction (p <= 8 owners)
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+      const u32 peers = __match_any_sync(0xffffffffu, own[q]);
+      u32 base = 0;
+      if (own[q] != BKT_NONE && (peers & lt) == 0) base = atomicAdd(&sm.hist[own[q]], (u32)__popc(peers));
+      base = __shfl_sync(0xffffffffu, base, __ffs((int)peers) - 1);
+      rank[q] = base + (u32)__popc(peers & lt);
+    }
+    __syncthreads();
+    if (t < 32) {                                          // owners' counts -> exclusive prefix, global run reservation
+      const u32 cnt = (u32)t < p ? sm.hist[t] : 0u;
+      u32 inc = cnt;
+#pragma unroll
+      for (int d = 1; d < MAX_SUB; d <<= 1) {
+        const u32 o = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += o;
+      }
+      const u32 ex = inc - cnt;
+      if ((u32)t < p) {
+        u64 d = 0;
+        if (cnt) {
+          const u32 gb = atomicAdd(ps.cursor + b * p + t, cnt);
+          if ((u64)gb + cnt <= (u64)ps.cap_sub)
+            d = reinterpret_cast<u64>(ps.peer_keys[t] + ((u64)(b * p + ps.me) * ps.cap_sub + gb) * NW) - (u64)ex * (8u * NW);
+          else atomicOr(ps.status, 1u);
+        }
+        sm.dst[t] = d;
+        sm.hist[t] = ex;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+      if (own[q] != BKT_NONE) {
+        const u32 pos = sm.hist[own[q]] + rank[q];
+        if (NW == 1) sm.sorted[pos] = key[q].w[0];
+        else reinterpret_cast<ulonglong2*>(sm.sorted)[pos] = make_ulonglong2(key[q].w[0], key[q].w[NW - 1]);
+        sm.sbid[pos] = (uint8_t)own[q];
+      }
+    }
+    __syncthreads();
+    if (t < MAX_SUB) sm.hist[t] = 0;
+    for (u32 r = t; r < m; r += TILE_THREADS) {
+      const u64 d = sm.dst[sm.sbid[r]];
+      if (!d) continue;
+      if (NW == 1) *reinterpret_cast<u64*>(d + (u64)r * 8u) = sm.sorted[r];
+      else *reinterpret_cast<ulonglong2*>(d + (u64)r * 16u) = reinterpret_cast<const ulonglong2*>(sm.sorted)[r];
+    }
+    __syncthreads();
+  }
+}
+#ifdef KMI_DIST_KERNELS  // non-template: compiled once, in kmi_dist.cu
+// after k_owner_push of a round: publish this rank's running totals in the owners' receive buffers (count word of region
+// (prefix, me) in owner r's count array) and clear the staging cursors for the next round
+__global__ void __launch_bounds__(256) k_push_publish(PushSink ps, u32* const* __restrict__ peer_counts, u32* __restrict__ stage_cursor,
+                                                      const u32* __restrict__ perr) {
+  // what the parser reported for this round joins the status words the ranks all-reduce: [0] something overflowed (the
+  // round must be redone through the generic exchange), [1] malformed input
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    const u32 e = *perr;
+    if (e & PERR_OVERFLOW) atomicOr(ps.status, 1u);
+    if (e & (PERR_NO_AT | PERR_NO_PLUS)) ps.status[1] = 1u;
+  }
+  const u32 n = N_BUCKETS * ps.p;
+  for (u32 j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+    const u32 b = j / ps.p, r = j % ps.p;
+    peer_counts[r][b * ps.p + ps.me] = min(ps.cursor[j], ps.cap_sub);
+  }
+  if (blockIdx.x == 0) for (u32 j = threadIdx.x; j <= N_BUCKETS; j += blockDim.x) stage_cursor[j] = 0;
+  __threadfence_system();
+}
+#endif  // KMI_DIST_KERNELS
+
 // the overflow region (bucket overflow + segment spills) -> table with global atomics
 template <int K, int HASH>
 __global__ void __launch_bounds__(256) k_insert_overflow(TableView t, BucketSink bs) {
   constexpr int NW = (K <= 32 ? 1 : 2);
-  const u64 n = min(bs.cursor[N_BUCKETS], bs.ovf_cap);
-  const u64 base = (u64)N_BUCKETS * bs.capb;
+  const u64 n = min(*ovf_cur(bs), bs.ovf_cap);
+  const u64* ovf = ovf_base<NW>(bs);
   u32 n_new = 0;
   for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
-    Key<NW> key = load_key<NW>(bs.keys, base + i);
+    Key<NW> key = load_key<NW>(ovf, i);
     bool was_new;
     const u64 s = table_upsert<NW>(t, key, slot_hash<K>(key), was_new);
     if (s != ~0ULL) {

@@ -21,6 +21,8 @@ struct Ops {
   void (*scatter_fine)(cudaStream_t, BucketSink bsink, FineSink fsink, u32* perr, u64 n_hint);
   int (*insert_segments)(cudaStream_t, TableView, FineSink fsink, BucketSink bsink, u32 log_seg, u32 n_segs, u32* perr, bool fresh);
   void (*insert_overflow)(cudaStream_t, TableView, BucketSink bsink);
+  // sharded build: coarse buckets -> owners' receive buffers (peer memory), owner = dist hash % p
+  void (*owner_push)(cudaStream_t, BucketSink bsink, PushSink psink, u64 n_hint);
   // parse (FASTA) to a key(+id) stream; wide_halo selects the 1 KiB halo variant
   void (*fasta_kmers)(cudaStream_t, bool wide_halo, const uint8_t* bytes, u64 n, u64 n_tiles, const u32* tile_enc_scanned,
                       const u32* enc_block_max, const u32* tile_runs, const u32* runs_block_sums, KeySink sink, u64* n_kmers,
@@ -65,18 +67,15 @@ struct OpsImpl {
     else if (sink_kind == 1)
       k_fastq_kmers<K, HASH, 1><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table, bsink,
                                                                           n_kmers, perr, canon, nsplit, tile_begin, nranks);
-    else if (sink_kind == 2)
-      k_fastq_kmers<K, HASH, 2><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table, bsink,
-                                                                          n_kmers, perr, canon, nsplit, tile_begin, nranks);
     else
-      k_fastq_kmers<K, HASH, 3><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table, bsink,
+      k_fastq_kmers<K, HASH, 2><<<(unsigned)n_tiles, TILE_THREADS, 0, st>>>(bytes, n, tile_lines, block_sums, sink, table, bsink,
                                                                           n_kmers, perr, canon, nsplit, tile_begin, nranks);
   }
   static void scatter_keys(cudaStream_t st, const u64* keys, u64 n, BucketSink bsink, u32* perr, bool canon) {
     if (n) k_scatter_keys<K, HASH><<<grid_for(n, TILE_THREADS * BktRound<NW>::R, 148u * 8u * 16u), TILE_THREADS, 0, st>>>(keys, n, bsink, perr, canon);
   }
   static void hll_buckets(cudaStream_t st, BucketSink bsink) {
-    k_hll_buckets<K><<<dim3(148u * 2u, HLL_SAMPLE_BUCKETS * (N_BUCKETS >> bsink.log_pre) + 1), 256, 0, st>>>(bsink);
+    k_hll_buckets<K><<<dim3(148u * 2u, HLL_SAMPLE_BUCKETS * (N_BUCKETS >> bsink.log_pre) * bsink.sub + 1), 256, 0, st>>>(bsink);
   }
   static void insert_buckets(cudaStream_t st, TableView t, BucketSink bsink, u64 n_hint) {
     k_insert_buckets<K, HASH><<<grid_for(n_hint ? n_hint : 1, 256, 148u * 8u), 256, 0, st>>>(t, bsink);
@@ -135,6 +134,9 @@ struct OpsImpl {
     }
     return 0;
   }
+  static void owner_push(cudaStream_t st, BucketSink bsink, PushSink psink, u64 n_hint) {
+    k_owner_push<K, HASH><<<grid_for(n_hint ? n_hint : 1, PUSH_ROUND, 148u * 4u * 16u), TILE_THREADS, 0, st>>>(bsink, psink);
+  }
   static void insert_overflow(cudaStream_t st, TableView t, BucketSink bsink) {
     k_insert_overflow<K, HASH><<<148u * 4u, 256, 0, st>>>(t, bsink);
   }
@@ -184,7 +186,7 @@ struct OpsImpl {
     Ops o;
     o.K = K; o.NW = NW; o.hash = HASH;
     o.fastq_kmers = fastq_kmers; o.scatter_keys = scatter_keys; o.insert_buckets = insert_buckets; o.hll_buckets = hll_buckets;
-    o.scatter_fine = scatter_fine; o.insert_segments = insert_segments; o.insert_overflow = insert_overflow; o.fasta_kmers = fasta_kmers; o.table_clear = table_clear; o.insert_keys = insert_keys; o.rehash = rehash;
+    o.scatter_fine = scatter_fine; o.insert_segments = insert_segments; o.insert_overflow = insert_overflow; o.owner_push = owner_push; o.fasta_kmers = fasta_kmers; o.table_clear = table_clear; o.insert_keys = insert_keys; o.rehash = rehash;
     o.lookup = lookup; o.erase = erase; o.dump = dump; o.checksum = checksum; o.canonicalize = canonicalize;
     o.hash_keys = hash_keys; o.part_hist = part_hist; o.part_scatter = part_scatter; o.csr_scan_l1 = csr_scan_l1;
     o.csr_fill = csr_fill; o.log_filter = log_filter; o.zero_aux = zero_aux;

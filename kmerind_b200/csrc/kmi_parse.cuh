@@ -372,8 +372,6 @@ template <> struct RecSmem<true> { u32 hdr[TILE_THREADS]; u32 before[TILE_THREAD
 // SINK 0: write canonical (or forward) keys to sink.keys (block-contiguous, order of blocks free)
 // SINK 1: insert straight into the count table (val += 1), no key stream at all
 // SINK 2: scatter into the 256 hash-prefix buckets of kmi_bucket.cuh (the default build path)
-// SINK 3: scatter into one region per owning rank, owner = dist_hash % nranks (KeyToRank,
-//         distributed_densehash_map.hpp:148-170): the send buffers of the all-to-all, no key stream pass
 #ifndef KMI_PARSE_MINB
 #define KMI_PARSE_MINB 5      // CTAs per SM the parser is compiled for (48 registers; measured 5.59 ms at 5, 5.61 at 6, 5.71 at 7 and 8)
 #endif
@@ -547,17 +545,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
 #pragma unroll
         for (int q = 0; q < R; ++q) {
           key[q] = roll.get(q, CANON);
-          u32 b;
-          if (SINK == 2) {
-            b = bucket_of(slot_hash<K>(key[q]));
-          } else {
-            u64 hs, hd;
-            kmer_hashes<K, HASH>(key[q], hs, hd);
-            b = mod_ranks(hd, nranks & 0xFFFFu);
-            const u32 lcb = nranks >> 16;                  // sub-bins per owner by slot-hash prefix (fused exchange)
-            if (lcb) b = (b << lcb) | (u32)(slot_hash<K>(key[q]) >> (64 - lcb));
-          }
-          bkt[q] = ((v >> q) & 1u) ? b : BKT_NONE;
+          bkt[q] = ((v >> q) & 1u) ? bucket_of(slot_hash<K>(key[q])) : BKT_NONE;
         }
       }
       bucket_round<NW>(bsink, sm, key, bkt, perr);
