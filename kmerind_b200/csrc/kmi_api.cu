@@ -260,7 +260,7 @@ int kmi::bucket_meta_prepare(kmi_index* idx) {
 int kmi::bucket_prepare(kmi_index* idx, u64 max_keys, BucketSink* bs) {
   if (max_keys > BUCKET_MAX_KEYS) return fail(KMI_ERR_ARG, "bucket round of %llu keys", (unsigned long long)max_keys);
   // uniform hash: a bucket receives max_keys/256 +- a few sigma; 6 % + 1024 slack, the rest goes to the overflow region
-  u64 capb = max_keys / N_BUCKETS + max_keys / (N_BUCKETS * 16) + 1024;
+  u64 capb = (max_keys / N_BUCKETS + max_keys / (N_BUCKETS * 16) + 1024 + 7) & ~7ULL;   // multiple of 8: flush chunks stay 64-byte aligned
   u64 ovf = max_keys / 8 + 4096;
   OK(idx->bkt_keys.ensure((capb * N_BUCKETS + ovf) * sizeof(u64) * idx->nw));
   OK(bucket_meta_prepare(idx));
@@ -516,20 +516,20 @@ int kmi::fastq_scan_alloc(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64*
   u64 n_tiles = (n + TILE_BYTES - 1) / TILE_BYTES;
   *n_tiles_out = n_tiles;
   if (n_tiles == 0) return KMI_OK;
-  if (n_tiles > 0x7fffffffULL) return fail(KMI_ERR_ARG, "block of %zu bytes too large for one call (max 8 TiB)", n);
-  OK(idx->tile_lines.ensure(sizeof(u32) * n_tiles));
-  OK(idx->block_sums.ensure(sizeof(u32) * ((n_tiles + 1023) / 1024)));
+  if (n_tiles > 0x7fffffffULL / TILE_CHUNKS) return fail(KMI_ERR_ARG, "block of %zu bytes too large for one call (max 1 TiB)", n);
+  OK(idx->tile_lines.ensure(sizeof(u32) * n_tiles * TILE_CHUNKS));                       // line starts before every 512-byte chunk
+  OK(idx->block_sums.ensure(sizeof(u32) * ((n_tiles * TILE_CHUNKS + 1023) / 1024)));
   OK(zero_ctr(idx, CTR_CARRY));
   return KMI_OK;
 }
-// line starts of tiles [t0, t1) (t0 a multiple of 1024) -> per-tile prefixes; the running total of
+// line starts of tiles [t0, t1) (t0 a multiple of 1024) -> per-chunk prefixes; the running total of
 // earlier ranges is carried in CTR_CARRY so that ranges can be scanned as their bytes arrive
 int kmi::fastq_scan_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64 t0, u64 t1) {
   if (t1 <= t0) return KMI_OK;
-  const u64 nt = t1 - t0, nb = (nt + 1023) / 1024;
+  const u64 nt = t1 - t0, nc = nt * TILE_CHUNKS, c0 = t0 * TILE_CHUNKS, nb = (nc + 1023) / 1024;
   k_fastq_count_lines<<<(unsigned)std::min<u64>((nt + 7) / 8, 148 * 16), COUNT_THREADS, 0, idx->stream>>>(d_bytes, n, idx->tile_lines.as<u32>(), (u32)t0, (u32)nt);
-  k_scan_l1<<<(unsigned)nb, 1024, 0, idx->stream>>>(idx->tile_lines.as<u32>() + t0, nt, idx->block_sums.as<u32>() + t0 / 1024);
-  k_scan_tiles<<<1, 1024, 0, idx->stream>>>(idx->block_sums.as<u32>() + t0 / 1024, nb, reinterpret_cast<u32*>(idx->ctr + CTR_CARRY));
+  k_scan_l1<<<(unsigned)nb, 1024, 0, idx->stream>>>(idx->tile_lines.as<u32>() + c0, nc, idx->block_sums.as<u32>() + c0 / 1024);
+  k_scan_tiles<<<1, 1024, 0, idx->stream>>>(idx->block_sums.as<u32>() + c0 / 1024, nb, reinterpret_cast<u32*>(idx->ctr + CTR_CARRY));
   idx->launches += 3;
   return KMI_OK;
 }
@@ -623,7 +623,6 @@ static int build_fastq_bucketed(kmi_index* idx, uint8_t* d_bytes, size_t n, u64 
   per_round = (per_round + 1023) / 1024 * 1024;  // the two-level line scan works in blocks of 1024 tiles
   const u64 n_rounds = (n_tiles + per_round - 1) / per_round;
   CopyGuard guard{nullptr};
-  std::vector<cudaEvent_t> copied;
   if (host_src) {
     if (!idx->copy_stream) CU(cudaStreamCreateWithFlags(&idx->copy_stream, cudaStreamNonBlocking));
     guard.s = idx->copy_stream;

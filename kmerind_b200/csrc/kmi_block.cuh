@@ -9,6 +9,8 @@ static constexpr int GROUP_BYTES = 16;
 static constexpr int TILE_BYTES = TILE_THREADS * GROUP_BYTES;  // 4096
 static constexpr int HALO_GROUPS = 4;                          // 64 bytes >= K-1 for K <= 63
 static constexpr int TILE_GROUPS = TILE_THREADS + HALO_GROUPS;
+static constexpr int CHUNK_BYTES = 32 * GROUP_BYTES;            // 512: what one warp of the parser owns; line starts are counted per chunk
+static constexpr int TILE_CHUNKS = TILE_BYTES / CHUNK_BYTES;    // 8
 
 // error bits reported by the parse kernels
 static constexpr u32 PERR_NO_AT = 1u;    // fastq_loader.hpp:393,419

@@ -357,9 +357,16 @@ k_scatter_fine(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
   auto locate = [&](u32 c, u32& b, u32& m, const u64*& src) {
     int lo = 0, hi = (int)NR - 1;                         // largest region with cpre[region] <= c: the non-empty one that holds chunk c
 #pragma unroll
-    for (int s = 0; s < LOG_BUCKETS + 3; ++s) {
+    for (int s = 0; s < LOG_BUCKETS; ++s) {
       const int mid = (lo + hi + 1) >> 1;
       if (cpre[mid] <= c) lo = mid; else hi = mid - 1;
+    }
+    if (sub > 1) {                                        // up to MAX_SUB * 256 regions: three more halvings
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (cpre[mid] <= c) lo = mid; else hi = mid - 1;
+      }
     }
     const u32 first = (c - cpre[lo]) * FINE_ROUND;
     const u32 cnt_b = min(bs.cursor[lo], bs.capb);
@@ -665,9 +672,16 @@ k_scatter_fine2(BucketSink bs, FineSink fs, u32* __restrict__ perr) {
   for (u32 c = blockIdx.x; c < n_chunks; c += gridDim.x) {
     int lo = 0, hi = (int)NR - 1;                         // largest region with cpre[region] <= c
 #pragma unroll
-    for (int s = 0; s < LOG_BUCKETS + 3; ++s) {
+    for (int s = 0; s < LOG_BUCKETS; ++s) {
       const int mid = (lo + hi + 1) >> 1;
       if (cpre[mid] <= c) lo = mid; else hi = mid - 1;
+    }
+    if (sub > 1) {                                        // up to MAX_SUB * 256 regions: three more halvings
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (cpre[mid] <= c) lo = mid; else hi = mid - 1;
+      }
     }
     const u32 first = (c - cpre[lo]) * FINE_ROUND2;
     const u32 m = min((u32)FINE_ROUND2, min(bs.cursor[lo], bs.capb) - first);

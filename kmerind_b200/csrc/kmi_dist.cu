@@ -232,7 +232,7 @@ int peers_ensure(kmi_index* idx, u64 cap_sub, u64 ovf_cap) {
 // staging sink of one parse round (local coarse buckets, same layout as the single-GPU build's)
 int stage_sink(kmi_index* idx, int which, u64 max_keys, BucketSink* bs) {
   kmi_dist_state* d = idx->dist;
-  const u64 capb = max_keys / N_BUCKETS + max_keys / (N_BUCKETS * 16) + 1024;
+  const u64 capb = (max_keys / N_BUCKETS + max_keys / (N_BUCKETS * 16) + 1024 + 7) & ~7ULL;
   const u64 ovf = max_keys / 8 + 4096;
   OK(d->stage_keys[which].ensure((capb * N_BUCKETS + ovf) * sizeof(u64) * idx->nw));
   OK(d->stage_meta[which].ensure(sizeof(u32) * (N_BUCKETS + 1)));
@@ -684,9 +684,11 @@ int build_fastq_push(kmi_index* idx, uint8_t* d_text, size_t n, const uint8_t* h
   cudaStream_t st = idx->stream;
   *redo = false;
   // ---- geometry every rank derives from the agreed maximum text size
-  const u64 tiles_max = (n_max + TILE_BYTES - 1) / TILE_BYTES;
-  u64 per_round = std::max<u64>((tiles_max + 7) / 8, (64u << 20) / TILE_BYTES);            // <= 8 rounds of >= 64 MiB
-  if (const char* e = getenv("KMI_DIST_ROUND_BYTES")) per_round = std::max<u64>(strtoull(e, nullptr, 10) / TILE_BYTES, 1);
+  const u64 TB = TILE_BYTES;
+  const u64 tiles_max = (n_max + TB - 1) / TB;
+  u64 per_round = std::max<u64>((tiles_max + 7) / 8, (64u << 20) / TB);                    // <= 8 rounds of >= 64 MiB
+  if (const char* e = getenv("KMI_DIST_ROUND_BYTES")) per_round = std::max<u64>(strtoull(e, nullptr, 10) / TB, 1);
+  per_round = std::min<u64>(per_round, std::max<u64>(tiles_max, 1));
   per_round = (per_round + 1023) / 1024 * 1024;                                             // the line scan works in blocks of 1024 tiles
   const u64 n_rounds = std::max<u64>((tiles_max + per_round - 1) / per_round, 1);
   const u64 upper = n_max / 2 + 1;                                                          // k-mers one rank can generate
@@ -711,7 +713,7 @@ int build_fastq_push(kmi_index* idx, uint8_t* d_text, size_t n, const uint8_t* h
   NC(g_nccl.AllReduce(st_in, st_out, 2, ncclUint32, ncclMax, c->comm, st));
   CU(cudaEventRecord(d->ev_t[0], st));
   // ---- rounds
-  const u64 n_tiles = (n + TILE_BYTES - 1) / TILE_BYTES;
+  const u64 n_tiles = (n + TB - 1) / TB;
   u64 scan_tiles = 0;
   OK(fastq_scan_alloc(idx, d_text, n, &scan_tiles));
   if (host_src) {
@@ -724,7 +726,7 @@ int build_fastq_push(kmi_index* idx, uint8_t* d_text, size_t n, const uint8_t* h
       idx->copy_events.push_back(e);
     }
     for (u64 r = 0; r < n_rounds; ++r) {
-      const u64 b0 = std::min<u64>(n, r * per_round * TILE_BYTES), b1 = std::min<u64>(n, (r + 1) * per_round * TILE_BYTES);
+      const u64 b0 = std::min<u64>(n, r * per_round * TB), b1 = std::min<u64>(n, (r + 1) * per_round * TB);
       if (b1 > b0) CU(cudaMemcpyAsync(d_text + b0, host_src + b0, b1 - b0, cudaMemcpyHostToDevice, idx->copy_stream));
       CU(cudaEventRecord(idx->copy_events[r], idx->copy_stream));
     }
@@ -747,7 +749,7 @@ int build_fastq_push(kmi_index* idx, uint8_t* d_text, size_t n, const uint8_t* h
     const u64 tiles = p1 - p0;
     next_tile = p1;
     BucketSink bs;
-    OK(stage_sink(idx, w, std::max<u64>(per_round + 1, 1) * TILE_BYTES / 2 + 1, &bs));
+    OK(stage_sink(idx, w, std::max<u64>(per_round + 1, 1) * TB / 2 + 1, &bs));
     if (r >= 2) CU(cudaStreamWaitEvent(st, d->ev_pushed[w], 0));     // staging buffer w was read by the push of round r - 2
     else CU(cudaMemsetAsync(bs.cursor, 0, sizeof(u32) * (N_BUCKETS + 1), st));
     if (tiles) {
@@ -757,7 +759,7 @@ int build_fastq_push(kmi_index* idx, uint8_t* d_text, size_t n, const uint8_t* h
     }
     CU(cudaEventRecord(d->ev_parsed[w], st));
     CU(cudaStreamWaitEvent(d->push_stream, d->ev_parsed[w], 0));
-    idx->ops->owner_push(d->push_stream, bs, ps, tiles * TILE_BYTES / 2 + 1);
+    idx->ops->owner_push(d->push_stream, bs, ps, tiles * TB / 2 + 1);
     k_push_publish<<<8, 256, 0, d->push_stream>>>(ps, d->peer_cnt.as<u32*>(), bs.cursor, reinterpret_cast<const u32*>(idx->ctr + CTR_PERR));
     idx->launches += 2;
     CU(cudaEventRecord(d->ev_pushed[w], d->push_stream));
@@ -812,6 +814,8 @@ int dist_build_fastq(kmi_index* idx, uint8_t* d_text, size_t n, const uint8_t* h
   if (n_kmers) *n_kmers = 0;
   d->n_received = 0;
   for (int i = 0; i < 4; ++i) d->ms[i] = 0;
+  for (int i = 0; i < 5; ++i) idx->kernel_ms[i] = 0;
+  idx->kev_pending = false;
   // what every rank must agree on before any collective with data-dependent shape: the largest block, and the path
   u64 v[1] = {n};
   OK(comm_allreduce(d->comm, v, 1, ncclMax, st));

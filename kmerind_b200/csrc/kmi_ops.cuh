@@ -2,6 +2,8 @@
 // kmi_ops_inst.cu is compiled once per supported K (-DKMI_K=...), so that the API translation
 // unit carries no templates and the per-K objects build in parallel.
 #pragma once
+#include <algorithm>
+#include <cstdlib>
 #include "kmi_parse.cuh"
 #include "kmi_kernels.cuh"
 #include "kmi_fasta.cuh"

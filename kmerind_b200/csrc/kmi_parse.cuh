@@ -94,15 +94,16 @@ __device__ __forceinline__ u32 line_starts(u32 eol, bool prev_eol) {
 }
 
 #ifdef KMI_SHARED_KERNELS  // non-template kernels: compiled once, in the API translation unit
-// ---- pass A: line starts per tile ------------------------------------------------------------
-// One WARP per 4 KiB tile, no block barrier: the eight 512-byte rows of the tile are requested together
-// (eight 128-bit loads in flight per lane), the "previous byte is an EOL" bit of a group comes from its
-// left neighbour's mask by shuffle, and the warp total goes out with one store. Warps stride over tiles.
+// ---- pass A: line starts per 512-byte CHUNK (= one warp's 32 groups in the parser) -----------------------------------
+// One WARP per 4 KiB tile, no block barrier: the eight 512-byte rows (= chunks) of the tile are requested together
+// (eight 128-bit loads in flight per lane), the "previous byte is an EOL" bit of a group comes from its left
+// neighbour's mask by shuffle, and the eight chunk totals go out as two 16-byte stores. Warps stride over tiles.
+// Per-chunk (not per-tile) counts let the parser number its lines with a warp scan instead of a block scan.
 static constexpr int COUNT_THREADS = 256;
 __global__ void __launch_bounds__(COUNT_THREADS) k_fastq_count_lines(const uint8_t* __restrict__ bytes, u64 n,
-                                                                      u32* __restrict__ tile_lines, const u32 tile_begin,
+                                                                      u32* __restrict__ chunk_lines, const u32 tile_begin,
                                                                       const u32 n_tiles) {
-  constexpr int ROWS = TILE_BYTES / (32 * GROUP_BYTES);   // 8
+  constexpr int ROWS = TILE_CHUNKS;   // 8
   const int lane = threadIdx.x & 31;
   const u32 warps = gridDim.x * (COUNT_THREADS / 32);
   for (u32 w = blockIdx.x * (COUNT_THREADS / 32) + (threadIdx.x >> 5); w < n_tiles; w += warps) {
@@ -110,19 +111,26 @@ __global__ void __launch_bounds__(COUNT_THREADS) k_fastq_count_lines(const uint8
     const u64 base = tile * TILE_BYTES + (u64)lane * GROUP_BYTES;
     u32 e[ROWS];
 #pragma unroll
-    for (int j = 0; j < ROWS; ++j) e[j] = eol16(load_group(bytes, base + (u64)j * 32 * GROUP_BYTES, n));   // past the end: all EOL
+    for (int j = 0; j < ROWS; ++j) e[j] = eol16(load_group(bytes, base + (u64)j * CHUNK_BYTES, n));   // past the end: all EOL
     u32 prev_last = prev_is_eol(bytes, tile * TILE_BYTES, n) ? 0x8000u : 0u;   // mask whose bit 15 = byte before the row
-    u32 cnt = 0;
+    u32 pk[ROWS / 2];                                      // two rows per word: a row holds <= 512 line starts
 #pragma unroll
     for (int j = 0; j < ROWS; ++j) {
       u32 left = __shfl_up_sync(0xffffffffu, e[j], 1);
       if (lane == 0) left = prev_last;
-      cnt += __popc(line_starts(e[j], (left >> 15) & 1u));
+      const u32 c = __popc(line_starts(e[j], (left >> 15) & 1u));
+      if (j & 1) pk[j >> 1] |= c << 16; else pk[j >> 1] = c;
       prev_last = __shfl_sync(0xffffffffu, e[j], 31);
     }
 #pragma unroll
-    for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
-    if (lane == 0) tile_lines[tile] = cnt;
+    for (int q = 0; q < ROWS / 2; ++q) {
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) pk[q] += __shfl_xor_sync(0xffffffffu, pk[q], d);
+    }
+    if (lane < 2) {
+      const u32 a = lane ? pk[2] : pk[0], b = lane ? pk[3] : pk[1];
+      reinterpret_cast<uint4*>(chunk_lines + tile * TILE_CHUNKS)[lane] = make_uint4(a & 0xFFFFu, a >> 16, b & 0xFFFFu, b >> 16);
+    }
   }
 }
 
@@ -138,7 +146,7 @@ __global__ void __launch_bounds__(COUNT_THREADS) k_fastq_rec_carry(const uint8_t
   const int lane = threadIdx.x & 31;
   const u32 warps = gridDim.x * (COUNT_THREADS / 32);
   for (u32 tile = blockIdx.x * (COUNT_THREADS / 32) + (threadIdx.x >> 5); tile < n_tiles; tile += warps) {
-    const u32 first = tile_lines[tile] + block_sums[tile >> 10];
+    const u32 first = tile_lines[(u64)tile * TILE_CHUNKS] + block_sums[((u64)tile * TILE_CHUNKS) >> 10];   // per-chunk prefixes: the tile's first chunk
     u32 j = first & 3u;
     if (j == 0) j = 4;
     u64 end = (u64)tile * TILE_BYTES, found = 0;
@@ -386,9 +394,9 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   __shared__ u32 s_codes[TILE_GROUPS + 1];
   __shared__ u32 s_flags[TILE_GROUPS + 1];
   __shared__ u32 s_aux[HALO_GROUPS * 2];       // halo: line-start masks / popcounts
-  __shared__ u32 s_tmp[TILE_THREADS / 32 + 1], s_tmp2[TILE_THREADS / 32 + 1];
   __shared__ u32 s_ent[TILE_THREADS * (GROUP_BYTES / BktRound<(K <= 32 ? 1 : 2)>::R)];   // entry list (P4)
   __shared__ u64 s_base;
+  __shared__ u32 s_cnt;                           // entries << 16 | k-mers of the tile (P4)
   __shared__ RecSmem<(SINK == 0)> s_rec;
 
   const int t = threadIdx.x;
@@ -397,7 +405,14 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   const u64 off = tile_off + (u64)t * GROUP_BYTES;
 
   // -- P1: load + classify own group (and, for the first HALO_GROUPS threads, a halo group)
-  const u32 tile_first_a = __ldg(tile_lines + tile), tile_first_b = __ldg(block_sums + (tile >> 10));   // needed in P3: in flight with the text
+  // line starts before this warp's chunk (and, for the halo lanes, before the next tile); needed in P3: in flight with the text
+  const u64 chunk = tile * TILE_CHUNKS + (u64)(t >> 5);
+  const u32 chunk_first_a = __ldg(tile_lines + chunk), chunk_first_b = __ldg(block_sums + (chunk >> 10));
+  u32 halo_first_a = 0, halo_first_b = 0;
+  if (t < HALO_GROUPS && tile_off + TILE_BYTES < n) {
+    halo_first_a = __ldg(tile_lines + (tile + 1) * TILE_CHUNKS);
+    halo_first_b = __ldg(block_sums + (((tile + 1) * TILE_CHUNKS) >> 10));
+  }
   uint4 v = load_group(bytes, off, n);
   Group g;                                            // FASTQ needs no separate '\n' mask, and the N mask only when splitting
   g.codes = codes16(v); g.eol = eol16(v); g.nl = 0; g.nmask = NSPLIT ? nmask16(v) : 0u;
@@ -421,18 +436,29 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
     s_codes[TILE_THREADS + t] = hg.codes;
     s_aux[t] = __popc(hls);
   }
-  if (t == 0) s_codes[TILE_GROUPS] = 0;
+  if (t == 0) { s_codes[TILE_GROUPS] = 0; s_cnt = 0; }
   if (SINK >= 2) reinterpret_cast<BucketSmem<NW>&>(s_bkt).hist[t] = 0;   // bucket_init, under the barriers of P2-P4
 
-  // -- P2: line number at the start of every group
-  u32 total_ls;
-  u32 before = block_excl_scan_nb(__popc(ls), s_tmp, total_ls);
-  const u32 tile_first = tile_first_a + tile_first_b;
-  // (the scan contains a barrier after the writes above: s_aux is visible)
+  // -- P2: line number at the start of every group. A warp is one 512-byte chunk and pass A counted the line starts before
+  // every chunk, so this is a warp scan on top of the chunk's prefix; the halo continues at the next tile's first chunk
+  // (a tile whose halo lies beyond the text needs no line numbers there: those bytes read as EOLs).
+  u32 before;
+  {
+    const u32 own = __popc(ls);
+    u32 inc = own;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const u32 o = __shfl_up_sync(0xffffffffu, inc, d);
+      if ((t & 31) >= d) inc += o;
+    }
+    before = inc - own;
+  }
+  const u32 chunk_first = chunk_first_a + chunk_first_b;   // line starts before this warp's chunk
+  __syncwarp();                                           // s_aux of the halo lanes (all in warp 0) is visible to them
 
   // -- P3: per-byte "base of a sequence line" flags; header checks at line starts
   {
-    u32 idx = tile_first + before;  // number of line starts before this group
+    u32 idx = chunk_first + before;  // number of line starts before this group
     u32 flags;
     u32 hdr = 0;                    // 1 + byte of the last header-line ('@', line 0 mod 4) start in this group
     if (ls == 0) {
@@ -458,7 +484,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
     if (NSPLIT) flags &= ~g.nmask;
     s_flags[t] = flags & 0xFFFFu;
     if (t < HALO_GROUPS) {
-      u32 hidx = tile_first + total_ls;
+      u32 hidx = halo_first_a + halo_first_b;               // line starts before the next tile
       for (int q = 0; q < t; ++q) hidx += s_aux[q];
       u32 hflags = 0;
       {
@@ -508,9 +534,20 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
   u32 ne = 0;
 #pragma unroll
   for (int e = 0; e < EPG; ++e) ne += ((valid >> (e * R)) & ((1u << R) - 1u)) ? 1u : 0u;
-  u32 tot;
-  const u32 pre = block_excl_scan_nb((ne << 16) | (u32)__popc(valid), s_tmp2, tot);   // entries : k-mers (<= 4096)
-  const u32 total_e = tot >> 16, total = tot & 0xFFFFu;
+  // dense positions: warp scan of (entries : k-mers), one shared-memory atomic per warp for the warp's base
+  u32 pre;
+  {
+    const u32 own = (ne << 16) | (u32)__popc(valid);
+    u32 inc = own;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const u32 o = __shfl_up_sync(0xffffffffu, inc, d);
+      if ((t & 31) >= d) inc += o;
+    }
+    u32 wbase = 0;
+    if ((t & 31) == 31 && inc) wbase = atomicAdd(&s_cnt, inc);
+    pre = __shfl_sync(0xffffffffu, wbase, 31) + inc - own;
+  }
   {
     u32 er = pre >> 16, kp = pre & 0xFFFFu;
 #pragma unroll
@@ -519,15 +556,13 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
       if (v) { s_ent[er++] = (u32)(t * EPG + e) | (v << 10) | (kp << 18); kp += __popc(v); }   // id : mask : k-mers before it
     }
   }
-  if (t == 0) {
-    u64 base = 0;
-    if (total) {
-      if (SINK == 0) base = atomicAdd(sink.cursor, (u64)total);
-      atomicAdd(n_kmers, (u64)total);
-    }
-    s_base = base;
-  }
   __syncthreads();
+  const u32 total_e = s_cnt >> 16, total = s_cnt & 0xFFFFu;   // entries : k-mers of the tile (<= 4096)
+  if (t == 0 && total) {
+    if (SINK == 0) s_base = atomicAdd(sink.cursor, (u64)total);
+    atomicAdd(n_kmers, (u64)total);
+  }
+  if (SINK == 0) __syncthreads();                         // s_base
 
   // -- P5: one entry per thread: load its code words once, roll the window over the R positions
   if (SINK >= 2) {

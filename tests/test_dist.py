@@ -127,12 +127,13 @@ def _build_dist_check(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("k,reads,push", [(31, 60000, None), (31, 60000, "0"), (31, 3000, "1"), (63, 30000, None), (21, 40000, None)])
+@pytest.mark.parametrize("k,reads,push", [(31, 240000, None), (31, 60000, "0"), (31, 3000, "1"), (63, 30000, "1"), (21, 40000, "1")])
 def test_sharded_index_from_cpp_main(tmp_path, k, reads, push):
     """C++ main(), one process per visible GPU (1 on a single-GPU box): sharded build from host blocks, size, per-shard dump,
     find / count / erase from every rank, sharded PositionIndex from FASTA blocks + find_positions — all against the oracle.
-    push None = the library's choice (NVLink push for a COUNT index of this size), "0" = the NCCL all-to-all path,
-    "1" = push forced on a small input (receive regions that send the table build down its key-stream fallback)."""
+    push None = the library's choice (NVLink push when every rank's block is >= 8 MiB: 240000 reads = 76 MB over <= 8 ranks),
+    "0" = the NCCL all-to-all path, "1" = push forced on a small input (small tables also send the received regions down
+    the key-stream fallback of the table build)."""
     exe = _build_dist_check(tmp_path)
     env = dict(os.environ)
     if push is not None:
