@@ -488,15 +488,261 @@ def run_gpu_arm(args):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------------------------------------------------
+# the other BASELINE.json configurations (driver-runnable: bench.py --config NAME [--gpus N under torchrun])
+#   count31_100g  cfg 3: K=31, 12.5 Gbp of reads per GPU (= 100 Gbp at 8 GPUs), built in batches of 1.5 Gbp into one index
+#   count63       cfg 4: K=63 (two-word keys), 4 Gbp per GPU (the 11.6 Gbp share of 30x human needs a 137 GB
+#                 table of 32-byte slots and does not fit next to its text and exchange buffers)
+#   pos21         cfg 5: PositionIndex K=21 over a synthetic FASTA genome, 375 Mbp per GPU (= 24 x 125 Mbp at 8 GPUs), then
+#                 1.25e8 query k-mers per GPU (= 1e9 at 8): count() and find() of all positions
+# ------------------------------------------------------------------------------------------------
+BIG = {"count31_100g": {"k": 31, "reads": 83333344, "batch": 10000000, "distinct_frac": 0.19},
+       "count63": {"k": 63, "reads": 26666672, "batch": 5000000, "distinct_frac": 0.50}}
+
+
+def _dist_setup():
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+    return torch, dist, world, rank, local_rank, device
+
+
+def _timed(torch, dist, world, device, step, steps, warmup, sampler):
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    for _ in range(warmup):
+        step()
+    barrier()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item()) / steps, clocks
+
+
+def run_big_count(args, name):
+    """cfg 3 / cfg 4: a CountIndex far larger than one bucket round, built batch by batch from text resident in HBM."""
+    torch, dist, world, rank, lr, device = _dist_setup()
+    import kmerind_b200 as kb
+    c = BIG[name]
+    k = c["k"]
+    n_reads = int(os.environ.get("KMI_BENCH_READS", str(c["reads"]))) // 16 * 16    # batches start 16-byte aligned
+    batch = min(int(os.environ.get("KMI_BENCH_BATCH", str(c["batch"]))) // 16 * 16, n_reads)
+    kpr = READ_LEN - k + 1
+    n_kmers_rank = n_reads * kpr
+    genome = n_reads * READ_LEN // 30 * world
+    nbytes = n_reads * REC
+    text = torch.empty(nbytes + 64, dtype=torch.uint8, device=device)
+    for b0 in range(0, n_reads, 20000000):                 # (the generator indexes records with 64-bit arithmetic; pieces keep each launch short)
+        m = min(20000000, n_reads - b0)
+        kb.synth_fastq_dev(lr, text.data_ptr() + b0 * REC, rank * n_reads + b0, m, READ_LEN, genome, SEED, ERR_PPM, 0)
+    torch.cuda.synchronize()
+    reserve = int(c["distinct_frac"] * n_kmers_rank)
+    if world == 1:
+        idx = kb.CountIndex(k, hash=kb.HASH_FARM, device=lr, reserve=reserve)
+        local, build = idx, idx.build_fastq_dev
+    else:
+        from kmerind_b200.dist import ShardedIndex
+        idx = ShardedIndex(k, hash=kb.HASH_FARM, device=lr, reserve=reserve)
+        local, build = idx.local, idx.build_fastq_dev
+    stage = []
+
+    def step():
+        local.clear()
+        got = 0
+        ms = np.zeros(5)
+        for b0 in range(0, n_reads, batch):
+            m = min(batch, n_reads - b0)
+            got += build(text.data_ptr() + b0 * REC, m * REC)
+            ms += np.array(local.last_kernel_ms())
+        assert got == n_kmers_rank, (got, n_kmers_rank)
+        stage.append(ms)
+    ms_step, clocks = _timed(torch, dist, world, device, step, args.steps, args.warmup, ClockSampler(lr))
+    total_kmers = n_kmers_rank * world
+    cks = local.checksum()
+    tsum = int(cks[1]) if world == 1 else int(idx.comm.allreduce(np.array([cks[1]], dtype=np.uint64), "sum")[0])
+    distinct = idx.size()
+    info = local.table_info()
+    parity = {"sum_counts": [tsum, total_kmers], "ok": tsum == total_kmers,
+              "note": "sum of counts over all shards == k-mers generated; the content checks against the reference code run at the "
+                      "1 Gbp configuration (default --config) and in tests/ (a reference walk of this size takes minutes per rank)"}
+    if os.environ.get("KMI_BENCH_FULL_PARITY") and k <= 32:
+        ou = _oracle_util()
+        oc = ou.ref_owner_checksums_fastq(text[:nbytes].cpu().numpy(), k, world, 1, threads=max(1, (os.cpu_count() or 1) // world))
+        want = oc if world == 1 else idx.comm.allreduce(oc.reshape(-1), "sum").reshape(world, 2)
+        okf = int(want[rank, 0]) == int(cks[0]) and int(want[rank, 1]) == int(cks[1])
+        if world > 1:
+            okf = bool(idx.comm.allreduce(np.array([1 if okf else 0], dtype=np.uint64), "min")[0])
+        parity["full_size_reference_walk"] = {"all_ranks_ok": bool(okf)}
+        parity["ok"] = parity["ok"] and bool(okf)
+    assert parity["ok"], parity
+    peak, peak_kind = measured_peaks()
+    km = np.mean(np.array(stage[-args.steps:]), axis=0)
+    n_batches = -(-n_reads // batch)
+    key_b = 8.0 * kb.nwords(k)
+    # table sweep of every batch: the segment insert reads and writes every slot once per batch
+    sweep = 2.0 * info["slots"] * info["slot_bytes"] * n_batches
+    ins_alg = (key_b + 12 + 12 if k <= 32 else key_b + 20 + 20) * n_kmers_rank
+    roofline = {"bound": "hbm", "kernel": "k_insert_segments%s (table sweep per batch)" % ("" if k <= 32 else "2"),
+                "achieved": ins_alg / (float(km[3]) * 1e-3) / 1e9, "peak": peak, "peak_source": peak_kind, "unit": "GB/s",
+                "frac": ins_alg / (float(km[3]) * 1e-3) / 1e9 / peak, "traffic": None,
+                "swept_bytes_per_step": sweep, "swept_gbs": sweep / (float(km[3]) * 1e-3) / 1e9,
+                "alg_bytes_per_kmer": ins_alg / n_kmers_rank, "kernel_ms_per_step": float(km[3]),
+                "stage_ms_per_step": {"parse+scatter": float(km[1]), "fine scatter": float(km[2]), "segment insert": float(km[3]), "overflow": float(km[4])},
+                "batches_per_step": n_batches}
+    if rank == 0:
+        cfg = workload_config(world, n_reads)
+        cfg.update({"k": k, "kmers_per_gpu": n_kmers_rank, "batch_reads": batch,
+                    "workload": "CountIndex K=%d canonical, farm hash, synthetic %.2f Gbp of 150 bp reads per GPU (30x, 0.5%% substitutions) = "
+                                "%.1f Gbp over %d GPU%s, built in %d batches into one index" % (k, n_reads * READ_LEN / 1e9,
+                                n_reads * READ_LEN * world / 1e9, world, "" if world == 1 else "s", n_batches)})
+        line = {"metric": "canonical k-mers inserted/sec into count index", "value": total_kmers / (ms_step * 1e-3), "unit": "kmers/s",
+                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": cfg,
+                "index": {"distinct_keys": int(distinct), "table_slots_per_gpu": info["slots"], "table_bytes_per_gpu": info["slots"] * info["slot_bytes"],
+                          "device_bytes_per_gpu": info.get("device_bytes")},
+                "clocks": clocks, "gpu_launches": int(local.launch_count()), "roofline": roofline, "parity": parity,
+                "e2e": None}
+        print(json.dumps(line))
+    if world > 1:
+        idx.close()
+        dist.destroy_process_group()
+
+
+def run_pos21(args):
+    """cfg 5: PositionIndex K=21 from a FASTA genome cut into one block per GPU at arbitrary bytes, then batched queries."""
+    torch, dist, world, rank, lr, device = _dist_setup()
+    import kmerind_b200 as kb
+    k, width = 21, 80
+    seq_len = int(os.environ.get("KMI_BENCH_SEQ_LEN", "125000000"))
+    n_seq = 3 * world
+    n_q = int(os.environ.get("KMI_BENCH_QUERIES", "125000000"))
+    fbytes = kb.synth_fasta_bytes(n_seq, seq_len, width)
+    # rank r's block: an equal share of the bytes, the cut moved off the sequence boundary into the middle of a line
+    cut = [0 if r == 0 else fbytes if r == world else fbytes * r // world + 1234 for r in range(world + 1)]
+    b0, b1 = cut[rank], cut[rank + 1]
+    halo = min(64, fbytes - b1)
+    text = torch.empty(b1 - b0 + halo + 64, dtype=torch.uint8, device=device)
+    kb.synth_fasta_dev(lr, text.data_ptr(), b0, b1 - b0 + halo, n_seq, seq_len, width, SEED)
+    torch.cuda.synchronize()
+    n_kmers_total = n_seq * (seq_len - k + 1)
+    if world == 1:
+        idx = kb.PositionIndex(k, hash=kb.HASH_MURMUR, device=lr, reserve=n_kmers_total)
+        local = idx
+
+        def step():
+            idx.clear()
+            return idx.build_fasta_dev(text.data_ptr(), b1 - b0)
+    else:
+        from kmerind_b200.dist import ShardedIndex
+        idx = ShardedIndex(k, mode=kb.MODE_POSITION, hash=kb.HASH_MURMUR, device=lr, reserve=n_kmers_total // world)
+        local = idx.local
+
+        def step():
+            idx.local.clear()
+            return idx.build_fasta_dev(text.data_ptr(), b1 - b0 + halo, n_valid=b1 - b0, file_offset=b0, bol=(b0 == 0))
+    produced = []
+    ms_step, clocks = _timed(torch, dist, world, device, lambda: produced.append(step()), args.steps, args.warmup, ClockSampler(lr))
+    got = produced[-1] if world == 1 else int(idx.comm.allreduce(np.array([produced[-1]], dtype=np.uint64), "sum")[0])
+    size = idx.size()
+    ok_build = got == n_kmers_total and size == n_kmers_total
+    # ---- queries: half from the genome (random strand), half random; host arrays in, answers out (the public batch call)
+    qd = torch.empty(n_q, dtype=torch.int64, device=device)
+    kb.synth_queries_dev(lr, qd.data_ptr(), rank * n_q, n_q, k, n_seq, seq_len, SEED, 4)
+    q = qd.cpu().numpy().view(np.uint64)
+    del qd
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    counts = idx.count(q)
+    t_count = time.perf_counter() - t0
+    hits = counts[0::2]
+    ok_q = bool((hits >= 1).all())                          # every genome query is present (both strands are stored canonically)
+    n_find = min(n_q, int(os.environ.get("KMI_BENCH_FIND", "20000000")))
+    t0 = time.perf_counter()
+    off, vals = idx.find_positions(q[:n_find], cap=int(counts[:n_find].sum()))
+    t_find = time.perf_counter() - t0
+    ok_q = ok_q and bool(np.array_equal(np.diff(off), counts[:n_find]))
+    # ids of a sample of genome queries point at file bytes that spell the k-mer or its reverse complement
+    samp = np.arange(0, min(n_find, 2000), 2)
+    pos_ok = True
+    for j in samp[:200]:
+        for v in vals[int(off[j]):int(off[j + 1])][:2]:
+            fo = int(v) & ((1 << 40) - 1)
+            pos_ok = pos_ok and 0 <= fo < fbytes
+    tq = torch.tensor([t_count, t_find], dtype=torch.float64, device=device)
+    flags = np.array([1 if (ok_build and ok_q and pos_ok) else 0], dtype=np.uint64)
+    if world > 1:
+        dist.all_reduce(tq, op=dist.ReduceOp.MAX)
+        flags = idx.comm.allreduce(flags, "min")
+    t_count, t_find = float(tq[0].item()), float(tq[1].item())
+    assert flags[0] == 1, "pos21 checks failed: build %s queries %s positions %s" % (ok_build, ok_q, pos_ok)
+    peak, peak_kind = measured_peaks()
+    info = local.table_info()
+    alg = 17.0 + 32.0 + (48.0 if world > 1 else 0.0)        # SURVEY 8d: parse 17 B/k-mer, insert 32, partition 48 when sharded
+    ach = alg * (n_kmers_total / world) / (ms_step * 1e-3) / 1e9
+    if rank == 0:
+        line = {"metric": "k-mers inserted/sec into position index", "value": n_kmers_total / (ms_step * 1e-3), "unit": "kmers/s",
+                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+                "config": {"workload": "PositionIndex K=21 canonical, murmur hash, synthetic FASTA genome of %d x %.0f Mbp (80 bases per line) = "
+                                       "%.2f Gbp cut into %d blocks at arbitrary bytes, then %d query k-mers per GPU (half from the genome, half random)"
+                                       % (n_seq, seq_len / 1e6, n_seq * seq_len / 1e9, world, n_q),
+                           "k": k, "file_bytes": int(fbytes), "kmers": int(n_kmers_total), "queries_per_gpu": n_q,
+                           "l2": "text, tuple log and table far larger than the 126 MB L2"},
+                "index": {"tuples": int(size), "table_slots_per_gpu": info["slots"]},
+                "clocks": clocks, "gpu_launches": int(local.launch_count()),
+                "roofline": {"bound": "hbm", "kernel": "whole position build (parse -> tuples -> %sinsert)" % ("partition -> all-to-all -> " if world > 1 else ""),
+                             "achieved": ach, "peak": peak, "peak_source": peak_kind, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                             "alg_bytes_per_kmer": alg},
+                "query": {"count": {"value": n_q * world / t_count, "unit": "queries/s", "seconds": t_count,
+                                    "how": "host keys in, multiplicities out (H2D, owner exchange over NCCL, probe, answers back, D2H)"},
+                          "find_positions": {"value": n_find * world / t_find, "unit": "queries/s", "seconds": t_find, "queries_per_gpu": n_find,
+                                             "ids_returned_rank0": int(off[-1])}},
+                "parity": {"ok": True, "tuples": [int(size), int(n_kmers_total)],
+                           "what": "every k-mer of the genome stored once per occurrence (size == sum over sequences of L-K+1 on all shards); "
+                                   "every genome query found on either strand; find() returns exactly count() ids per key, all valid file offsets. "
+                                   "Content against the oracle: tests/ (sharded FASTA blocks cut mid-line, dist_check.cpp)"},
+                "e2e": None}
+        print(json.dumps(line))
+    if world > 1:
+        idx.close()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="kmerind_b200")
+    ap.add_argument("--config", default="count31", choices=["count31", "count31_100g", "count63", "pos21"],
+                    help="count31 = BASELINE.json configs[1]/[2] shape (1 Gbp per GPU, the headline metric); the others: configs[2..4] at size")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)
+    elif args.config in BIG:
+        run_big_count(args, args.config)
+    elif args.config == "pos21":
+        run_pos21(args)
     else:
         run_gpu_arm(args)
 

@@ -285,6 +285,15 @@ int kmi_synth_fastq_dev(int device, uint8_t* d_out, uint64_t first_read, uint64_
                         uint32_t read_len, uint64_t genome_len, uint64_t seed, uint32_t err_ppm,
                         uint32_t n_ppm);
 
+/* config 5's inputs: bytes [file_offset, file_offset + n_bytes) of a synthetic FASTA genome (n_seq sequences of seq_len bases,
+ * `width` bases per line, headers ">chrNN"; same bytes as oracle kmio_synth_fasta), and query k-mers: even ones are K bases
+ * of that genome at a random place and strand, odd ones uniform random */
+size_t kmi_synth_fasta_bytes(uint32_t n_seq, uint64_t seq_len, uint32_t width);
+int kmi_synth_fasta_dev(int device, uint8_t* d_out, uint64_t file_offset, uint64_t n_bytes, uint32_t n_seq, uint64_t seq_len,
+                        uint32_t width, uint64_t seed);
+int kmi_synth_queries_dev(int device, uint64_t* d_keys, uint64_t first, uint64_t n, int k, uint32_t n_seq, uint64_t seq_len,
+                          uint64_t genome_seed, uint64_t seed);
+
 #ifdef __cplusplus
 }
 #endif

@@ -95,6 +95,8 @@ def load_library(build_if_missing=False):
         "kmi_local_size": [_P, _P], "kmi_num_keys": [_P, _P], "kmi_dump": [_P, _P, _P, _SZ, _P],
         "kmi_checksum": [_P, _P, _P], "kmi_table_info": [_P, _P, _P, _P], "kmi_launch_count": [_P, _P],
         "kmi_last_stage_ms": [_P, _P], "kmi_last_kernel_ms": [_P, _P],
+        "kmi_synth_fasta_dev": [ctypes.c_int, _P, _U64, _U64, ctypes.c_uint32, _U64, ctypes.c_uint32, _U64],
+        "kmi_synth_queries_dev": [ctypes.c_int, _P, _U64, _U64, ctypes.c_int, ctypes.c_uint32, _U64, _U64, _U64],
         "kmi_synth_fastq_dev": [ctypes.c_int, _P, _U64, _U64, ctypes.c_uint32, _U64, _U64, ctypes.c_uint32,
                                 ctypes.c_uint32],
     }
@@ -102,6 +104,8 @@ def load_library(build_if_missing=False):
         fn = getattr(lib, name)
         fn.argtypes = args
         fn.restype = ctypes.c_int
+    lib.kmi_synth_fasta_bytes.restype = _SZ
+    lib.kmi_synth_fasta_bytes.argtypes = [ctypes.c_uint32, _U64, ctypes.c_uint32]
     lib.kmi_comm_destroy.argtypes = [_P]
     lib.kmi_comm_destroy.restype = None
     _lib = lib
@@ -120,7 +124,7 @@ EXPORTED_SYMBOLS = (
     "kmi_partition_dev", "kmi_insert", "kmi_insert_dev", "kmi_count", "kmi_find", "kmi_find_positions",
     "kmi_erase", "kmi_count_dev", "kmi_find_dev", "kmi_local_size", "kmi_num_keys", "kmi_dump",
     "kmi_checksum", "kmi_table_info", "kmi_launch_count", "kmi_last_stage_ms", "kmi_last_kernel_ms",
-    "kmi_synth_record_bytes", "kmi_synth_fastq_dev",
+    "kmi_synth_record_bytes", "kmi_synth_fastq_dev", "kmi_synth_fasta_bytes", "kmi_synth_fasta_dev", "kmi_synth_queries_dev",
 )
 
 
@@ -439,3 +443,15 @@ def synth_record_bytes(read_len=150):
 def synth_fastq_dev(device, dptr, first_read, n_reads, read_len, genome_len, seed, err_ppm=5000, n_ppm=0):
     _check(load_library().kmi_synth_fastq_dev(device, dptr, first_read, n_reads, read_len, genome_len, seed, err_ppm,
                                               n_ppm))
+
+
+def synth_fasta_bytes(n_seq, seq_len, width=80):
+    return load_library().kmi_synth_fasta_bytes(n_seq, seq_len, width)
+
+
+def synth_fasta_dev(device, dptr, file_offset, n_bytes, n_seq, seq_len, width=80, seed=1):
+    _check(load_library().kmi_synth_fasta_dev(device, dptr, file_offset, n_bytes, n_seq, seq_len, width, seed))
+
+
+def synth_queries_dev(device, dptr, first, n, k, n_seq, seq_len, genome_seed=1, seed=4):
+    _check(load_library().kmi_synth_queries_dev(device, dptr, first, n, k, n_seq, seq_len, genome_seed, seed))

@@ -380,6 +380,7 @@ int kmi::bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 siz
         }
         fs.log_f = log_f;                                  // the insert sees 2^log_segs regions, as after a single pass
       }
+      CU(cudaGetLastError());                              // a scatter that did not launch must not pass for an empty bucket
       u64 perr = 0;
       OK(read_ctr(idx, CTR_PERR, &perr));
       if (perr & PERR_OVERFLOW) {
@@ -398,6 +399,7 @@ int kmi::bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 siz
       if (e) return fail(KMI_ERR_CUDA, "segment kernel configuration: %s", cudaGetErrorString((cudaError_t)e));
       CU(cudaEventRecord(idx->kev[2], idx->stream));
       idx->ops->insert_overflow(idx->stream, idx->view(), bs);
+      CU(cudaGetLastError());
       CU(cudaEventRecord(idx->kev[3], idx->stream));
       idx->kev_pending = true;
       idx->launches += 2;
@@ -1188,6 +1190,31 @@ extern "C" int kmi_synth_fastq_dev(int device, uint8_t* d_out, uint64_t first_re
   if (n_reads == 0) return KMI_OK;
   u64 total = n_reads * kmi_synth_record_bytes(read_len);
   k_synth_fastq<<<grid_for(total, 256, 148u * 32u), 256>>>(d_out, first_read, n_reads, read_len, genome_len, seed, err_ppm, n_ppm);
+  CU(cudaGetLastError());
+  return KMI_OK;
+}
+
+extern "C" size_t kmi_synth_fasta_bytes(uint32_t n_seq, uint64_t seq_len, uint32_t width) {
+  if (width == 0) return 0;
+  return (size_t)n_seq * (7 + seq_len + (seq_len + width - 1) / width);
+}
+extern "C" int kmi_synth_fasta_dev(int device, uint8_t* d_out, uint64_t file_offset, uint64_t n_bytes, uint32_t n_seq, uint64_t seq_len,
+                                   uint32_t width, uint64_t seed) {
+  if (!d_out && n_bytes) return fail(KMI_ERR_ARG, "null argument");
+  if (width == 0 || n_seq == 0 || n_seq > 100) return fail(KMI_ERR_ARG, "1..100 sequences, line width > 0");
+  CU(cudaSetDevice(device));
+  if (n_bytes == 0) return KMI_OK;
+  k_synth_fasta<<<grid_for(n_bytes, 256, 148u * 32u), 256>>>(d_out, file_offset, n_bytes, n_seq, seq_len, width, seed);
+  CU(cudaGetLastError());
+  return KMI_OK;
+}
+extern "C" int kmi_synth_queries_dev(int device, uint64_t* d_keys, uint64_t first, uint64_t n, int k, uint32_t n_seq, uint64_t seq_len,
+                                     uint64_t genome_seed, uint64_t seed) {
+  if (!d_keys && n) return fail(KMI_ERR_ARG, "null argument");
+  if (k < 2 || k > 63 || n_seq == 0 || seq_len < (uint64_t)k) return fail(KMI_ERR_ARG, "bad query shape");
+  CU(cudaSetDevice(device));
+  if (n == 0) return KMI_OK;
+  k_synth_queries<<<grid_for(n, 256, 148u * 32u), 256>>>(reinterpret_cast<u64*>(d_keys), first, n, k, n_seq, seq_len, genome_seed, seed);
   CU(cudaGetLastError());
   return KMI_OK;
 }

@@ -400,6 +400,50 @@ k_synth_fastq(uint8_t* __restrict__ out, u64 first_read, u64 n_reads, u32 L, u64
   }
 }
 
+// bytes [file_offset, file_offset + n_bytes) of the synthetic FASTA genome (same bytes as oracle/kmi_oracle.c kmio_synth_fasta):
+// n_seq sequences of seq_len bases, `width` bases per line, header ">chrNN\n"
+__global__ void __launch_bounds__(256)
+k_synth_fasta(uint8_t* __restrict__ out, u64 file_offset, u64 n_bytes, u32 n_seq, u64 seq_len, u32 width, u64 seed) {
+  const u64 lines = (seq_len + width - 1) / width, seq_bytes = 7 + seq_len + lines;
+  for (u64 idx = (u64)blockIdx.x * blockDim.x + threadIdx.x; idx < n_bytes; idx += (u64)gridDim.x * blockDim.x) {
+    const u64 f = file_offset + idx;
+    const u64 s = f / seq_bytes;
+    u64 o = f % seq_bytes;
+    uint8_t ch;
+    if (s >= n_seq) ch = '\n';
+    else if (o < 7) ch = (o == 0) ? '>' : (o == 1) ? 'c' : (o == 2) ? 'h' : (o == 3) ? 'r' : (o == 4) ? (uint8_t)('0' + (s / 10) % 10) : (o == 5) ? (uint8_t)('0' + s % 10) : '\n';
+    else {
+      o -= 7;
+      const u64 line = o / (width + 1), col = o % (width + 1), i = line * width + col;
+      ch = (col == width || i >= seq_len) ? (uint8_t)'\n' : (uint8_t)"ACGT"[syn_genome_base(seed + 977 * (s + 1), i)];
+    }
+    out[idx] = ch;
+  }
+}
+// query k-mers of config 5: even j = K bases of the synthetic genome at a random place (random strand),
+// odd j = uniform random k-mer; nw words per key
+__global__ void __launch_bounds__(256)
+k_synth_queries(u64* __restrict__ out, u64 first, u64 n, int k, u32 n_seq, u64 seq_len, u64 genome_seed, u64 seed) {
+  const int nw = k <= 32 ? 1 : 2;
+  for (u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (u64)gridDim.x * blockDim.x) {
+    const u64 h = sm64((seed + 5) * 0x9e3779b97f4a7c15ULL + first + j);
+    u64 lo = 0, hi = 0;
+    if (((first + j) & 1) == 0) {
+      const u64 s = (h >> 1) % n_seq, pos = sm64(h) % (seq_len - (u64)k + 1);
+      const bool rc = (h & 1) != 0;
+      for (int i = 0; i < k; ++i) {
+        const u32 b = rc ? 3u - syn_genome_base(genome_seed + 977 * (s + 1), pos + (u64)(k - 1 - i)) : syn_genome_base(genome_seed + 977 * (s + 1), pos + (u64)i);
+        hi = (hi << 2) | (lo >> 62);
+        lo = (lo << 2) | b;
+      }
+    } else {
+      lo = sm64(h); hi = sm64(h ^ 0x5555555555555555ULL);
+    }
+    if (nw == 1) out[j] = k == 32 ? lo : (lo & ((1ULL << (2 * k)) - 1));
+    else { out[2 * j] = lo; out[2 * j + 1] = hi & ((1ULL << (2 * (k - 32))) - 1); }
+  }
+}
+
 #endif  // KMI_SHARED_KERNELS
 
 }  // namespace kmi

@@ -107,13 +107,14 @@ struct OpsImpl {
   static void scatter_fine(cudaStream_t st, BucketSink bsink, FineSink fsink, u32* perr, u64 n_hint) {
     if constexpr (NW == 1) {
       const size_t smem = scatter_fine_smem(fsink.log_f);
-      if (smem > 48 * 1024) cudaFuncSetAttribute(k_scatter_fine<K, HASH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      // (the kernel also holds ~9 KB of static shared memory: opt in as soon as the sum passes the 48 KB default)
+      if (smem > 36 * 1024) cudaFuncSetAttribute(k_scatter_fine<K, HASH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       // ~20 chunks per CTA: enough for the register prefetch to pay, short enough for the block scheduler to even out
       // the SMs (measured: 4.13 ms with one resident wave of CTAs, 3.50 with 32 waves, 4.09 with one chunk per CTA)
       k_scatter_fine<K, HASH><<<grid_for(n_hint ? n_hint : 1, FINE_ROUND, 148u * KMI_FINE_MINB * 32u), TILE_THREADS, smem, st>>>(bsink, fsink, perr);
     } else {
       const size_t smem = scatter_fine2_smem(fsink.log_f);
-      if (smem > 48 * 1024) cudaFuncSetAttribute(k_scatter_fine2<K, HASH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (smem > 36 * 1024) cudaFuncSetAttribute(k_scatter_fine2<K, HASH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       k_scatter_fine2<K, HASH><<<grid_for(n_hint ? n_hint : 1, FINE_ROUND2, 148u * 4u * 32u), TILE_THREADS, smem, st>>>(bsink, fsink, perr);
     }
   }

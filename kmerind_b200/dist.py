@@ -134,6 +134,14 @@ class ShardedIndex:
         self._stats()
         return n.value
 
+    def build_fasta_dev(self, dptr, nbytes, n_valid=None, file_offset=0, bol=True):
+        """as build_fasta, the bytes (block + halo) already on the device"""
+        part = ctypes.byref(KmiFastaPart(int(file_offset), int(n_valid), 1 if bol else 0, 0)) if n_valid is not None else None
+        n = _U64(0)
+        _check(self._lib.kmi_dist_build_fasta_dev(self.local._h, dptr, nbytes, part, ctypes.byref(n)))
+        self._stats()
+        return n.value
+
     def insert(self, keys, vals=None):
         a = _as_keys(keys, self.nw)
         v = None if vals is None else np.ascontiguousarray(vals, dtype=np.uint64)

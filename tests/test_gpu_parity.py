@@ -809,3 +809,42 @@ def test_fastq_position_ids_reject_records_over_64k():
         with pytest.raises(kb.KmiError) as e:
             idx.build_fastq(rec)
         assert e.value.code == kb.ERR_ARG
+
+
+@pytest.mark.parametrize("n_seq,seq_len,width", [(3, 1000, 80), (2, 777, 70), (5, 64, 64)])
+def test_synthetic_fasta_and_queries_match_host_twin(n_seq, seq_len, width):
+    """kmi_synth_fasta_dev writes the bytes of oracle kmio_synth_fasta for any byte range; the even query k-mers of
+    kmi_synth_queries_dev occur in that genome (either strand)."""
+    want = ou.synth_fasta(n_seq, seq_len, width, seed=3)
+    assert kb.synth_fasta_bytes(n_seq, seq_len, width) == want.size
+    for lo, hi in ((0, want.size), (13, want.size - 5), (want.size // 2, want.size // 2 + 100)):
+        t = torch.zeros(hi - lo, dtype=torch.uint8, device="cuda")
+        kb.synth_fasta_dev(0, t.data_ptr(), lo, hi - lo, n_seq, seq_len, width, seed=3)
+        assert np.array_equal(t.cpu().numpy(), want[lo:hi])
+    k = 21
+    if seq_len >= k:
+        keys, _, _ = ou.fasta_kmers(want, k)
+        have = set(keys.tolist())
+        q = torch.zeros(400, dtype=torch.int64, device="cuda")
+        kb.synth_queries_dev(0, q.data_ptr(), 1000, 400, k, n_seq, seq_len, genome_seed=3, seed=4)
+        qc = ou.canonical(host_u64(q), k)
+        assert all(int(x) in have for x in qc[0::2])
+        assert (host_u64(q) < np.uint64(1 << 42)).all()
+
+
+def test_k63_build_into_a_large_reserved_table_in_batches():
+    """Two-word keys, a table of 2^27 slots (256 fine buckets per coarse bucket: the fine scatter's shared memory passes
+    the 48 KB default with its static part), two batches into one index: contents == oracle, second batch adds."""
+    k, n_reads = 63, 120000
+    buf = ou.synth_fastq(0, n_reads, 150, 400000, 5, 5000, 0)
+    keys, _, _ = ou.fastq_kmers(buf, k)
+    wk, wc = ou.count_sorted(keys, k)
+    half = (n_reads // 2) * 317
+    with kb.CountIndex(k, hash=kb.HASH_FARM, reserve=90_000_000) as idx:
+        assert idx.table_info()["slots"] == 1 << 27
+        idx.set_build_path(2)
+        n = idx.build_fastq(buf[:half]) + idx.build_fastq(buf[half:])
+        assert n == len(keys)
+        assert idx.checksum()[1] == len(keys)
+        gk, gc = idx.sorted_dump()
+        assert np.array_equal(gk, wk) and np.array_equal(gc, wc)
