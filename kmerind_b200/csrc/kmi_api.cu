@@ -648,8 +648,9 @@ static int build_fastq_bucketed(kmi_index* idx, uint8_t* d_bytes, size_t n, u64 
   for (u64 r = 0; r < n_rounds; ++r) {
     const u64 t0 = r * per_round, t1 = std::min(n_tiles, t0 + per_round);
     const bool last = r + 1 == n_rounds;
-    if (host_src) CU(cudaStreamWaitEvent(idx->stream, idx->copy_events[r], 0));
-    OK(fastq_scan_range(idx, d_bytes, n, t0, t1));
+    // (a tile's halo continues at the next tile's line count: resident text is counted whole before the first round)
+    if (host_src) { CU(cudaStreamWaitEvent(idx->stream, idx->copy_events[r], 0)); OK(fastq_scan_range(idx, d_bytes, n, t0, t1)); }
+    else if (r == 0) OK(fastq_scan_range(idx, d_bytes, n, 0, n_tiles));
     const u64 p0 = (host_src && r > 0) ? t0 - 1 : t0;
     const u64 p1 = (host_src && !last) ? t1 - 1 : t1;
     const u64 tiles = p1 - p0;

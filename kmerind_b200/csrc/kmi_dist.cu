@@ -740,8 +740,10 @@ int build_fastq_push(kmi_index* idx, uint8_t* d_text, size_t n, const uint8_t* h
   for (u64 r = 0; r < n_rounds; ++r) {
     const int w = (int)(r & 1);
     const u64 t0 = std::min(n_tiles, r * per_round), t1 = std::min(n_tiles, t0 + per_round);
-    if (host_src) CU(cudaStreamWaitEvent(st, idx->copy_events[r], 0));
-    OK(fastq_scan_range(idx, d_text, n, t0, t1));
+    // line counts: a tile's halo continues at the NEXT tile's count, so resident text is counted whole before the first
+    // round; arriving text is counted round by round and the last tile that has arrived waits for the next round
+    if (host_src) { CU(cudaStreamWaitEvent(st, idx->copy_events[r], 0)); OK(fastq_scan_range(idx, d_text, n, t0, t1)); }
+    else if (r == 0) OK(fastq_scan_range(idx, d_text, n, 0, n_tiles));
     // with a host source the last tile that has arrived needs the first bytes of the next round (k-mer halo), unless the
     // text ends there: it is parsed with the next round
     const u64 p0 = next_tile;
