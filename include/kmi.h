@@ -208,6 +208,14 @@ int kmi_num_keys(kmi_index* idx, uint64_t* n);
 /* to_vector(): every (key, value) entry, unordered. COUNT: value = frequency. POSITION: one
  * entry per stored (key, id) tuple. n_out receives the number written (<= cap). */
 int kmi_dump(kmi_index* idx, uint64_t* keys, uint64_t* vals, size_t cap, size_t* n_out);
+/* ---- f2: find(pred) / count(pred) / erase(pred) over the local map (kmer_index.hpp:156-194;
+ * distributed_densehash_map.hpp:1666-1686,1835-1903) for predicates on the stored VALUE, evaluated on the device: one
+ * compare fused into the table sweep instead of a dump of the whole table to the host. COUNT indices (value = frequency):
+ * "k-mers seen at least c times", "singletons" (the error k-mers), ... kmi_count_if sizes the buffers of kmi_dump_if. */
+typedef enum { KMI_PRED_GE = 0, KMI_PRED_LE = 1, KMI_PRED_EQ = 2 } kmi_pred_op;
+int kmi_count_if(kmi_index* idx, int op, uint64_t value, uint64_t* n);
+int kmi_dump_if(kmi_index* idx, int op, uint64_t value, uint64_t* keys, uint64_t* vals, size_t cap, size_t* n_out);
+int kmi_erase_if(kmi_index* idx, int op, uint64_t value, uint64_t* n_removed);
 /* order-independent 64-bit checksums of the contents: sum over entries of mix(key)*value and of
  * value (mod 2^64) — used to compare builds at sizes where a dump diff is impractical */
 int kmi_checksum(kmi_index* idx, uint64_t* key_value_sum, uint64_t* value_sum);

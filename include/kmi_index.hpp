@@ -151,6 +151,21 @@ inline void check(int status) {
   throw std::runtime_error(msg);
 }
 
+/// Predicates on the stored value that the library evaluates on the device (kmi_count_if / kmi_dump_if / kmi_erase_if): pass
+/// one to find / erase / count_if of a COUNT map and only the matching entries cross PCIe. They are ordinary functors too,
+/// so the generic (host-side) predicate overloads accept them as well.
+struct value_pred {
+  int op;
+  uint64_t x;
+  template <typename V> bool operator()(const V& v) const {
+    const uint64_t c = (uint64_t)v.second;
+    return op == KMI_PRED_GE ? c >= x : op == KMI_PRED_LE ? c <= x : c == x;
+  }
+};
+inline value_pred count_at_least(uint64_t c) { value_pred p = {KMI_PRED_GE, c}; return p; }
+inline value_pred count_at_most(uint64_t c) { value_pred p = {KMI_PRED_LE, c}; return p; }
+inline value_pred count_equal(uint64_t c) { value_pred p = {KMI_PRED_EQ, c}; return p; }
+
 struct map_options {
   int hash = KMI_HASH_MURMUR;   // reference default MurmurHash (kmer_index.hpp:437-438); benchmarks use FARM
   bool canonical = true;        // CanonicalHashMapParams (kmer_index.hpp:453-466)
@@ -221,6 +236,36 @@ class b200_map {
     std::vector<value_type> out = to_vector();
     out.erase(std::remove_if(out.begin(), out.end(), [&](const value_type& v) { return !pred(v); }), out.end());
     return out;
+  }
+  /// find(pred) with a device-side value predicate: only the matching entries are read back
+  std::vector<value_type> find(const value_pred& pred) const {
+    if (Mode != KMI_MODE_COUNT) return find<value_pred>(pred);
+    uint64_t n = 0;
+    check(kmi_count_if(h_, pred.op, pred.x, &n));
+    std::vector<uint64_t> k(n * nw() + 1), v(n + 1);
+    size_t got = 0;
+    check(kmi_dump_if(h_, pred.op, pred.x, k.data(), v.data(), n, &got));
+    std::vector<value_type> out;
+    out.reserve(got);
+    for (size_t i = 0; i < got; ++i) {
+      Key key;
+      std::memcpy(key.getDataRef(), &k[i * nw()], sizeof(Key));
+      out.emplace_back(key, from_u64(v[i]));
+    }
+    return out;
+  }
+  /// number of local entries that satisfy a device-side value predicate (no entry leaves the GPU)
+  size_t count_if(const value_pred& pred) const {
+    uint64_t n = 0;
+    check(kmi_count_if(h_, pred.op, pred.x, &n));
+    return (size_t)n;
+  }
+  /// erase(pred) with a device-side value predicate: one sweep of the table
+  size_t erase(const value_pred& pred) {
+    if (Mode != KMI_MODE_COUNT) return erase<value_pred>(pred);
+    uint64_t n = 0;
+    check(kmi_erase_if(h_, pred.op, pred.x, &n));
+    return (size_t)n;
   }
   /// count: one (key, size_t) per query, zeros included — LocalCount, :234-266
   std::vector<std::pair<Key, size_t>> count(std::vector<Key>& keys) const {

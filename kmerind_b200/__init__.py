@@ -93,7 +93,8 @@ def load_library(build_if_missing=False):
         "kmi_find_positions": [_P, _P, _SZ, _P, _P, _SZ], "kmi_erase": [_P, _P, _SZ],
         "kmi_count_dev": [_P, _P, _SZ, _P], "kmi_find_dev": [_P, _P, _SZ, _P, _P],
         "kmi_local_size": [_P, _P], "kmi_num_keys": [_P, _P], "kmi_dump": [_P, _P, _P, _SZ, _P],
-        "kmi_checksum": [_P, _P, _P], "kmi_table_info": [_P, _P, _P, _P], "kmi_launch_count": [_P, _P],
+        "kmi_checksum": [_P, _P, _P], "kmi_count_if": [_P, ctypes.c_int, _U64, _P], "kmi_dump_if": [_P, ctypes.c_int, _U64, _P, _P, _SZ, _P],
+        "kmi_erase_if": [_P, ctypes.c_int, _U64, _P], "kmi_table_info": [_P, _P, _P, _P], "kmi_launch_count": [_P, _P],
         "kmi_last_stage_ms": [_P, _P], "kmi_last_kernel_ms": [_P, _P],
         "kmi_synth_fasta_dev": [ctypes.c_int, _P, _U64, _U64, ctypes.c_uint32, _U64, ctypes.c_uint32, _U64],
         "kmi_synth_queries_dev": [ctypes.c_int, _P, _U64, _U64, ctypes.c_int, ctypes.c_uint32, _U64, _U64, _U64],
@@ -123,7 +124,7 @@ EXPORTED_SYMBOLS = (
     "kmi_dist_find_positions", "kmi_dist_erase", "kmi_dist_size", "kmi_dist_last_stats", "kmi_canonicalize_dev", "kmi_hash_dev",
     "kmi_partition_dev", "kmi_insert", "kmi_insert_dev", "kmi_count", "kmi_find", "kmi_find_positions",
     "kmi_erase", "kmi_count_dev", "kmi_find_dev", "kmi_local_size", "kmi_num_keys", "kmi_dump",
-    "kmi_checksum", "kmi_table_info", "kmi_launch_count", "kmi_last_stage_ms", "kmi_last_kernel_ms",
+    "kmi_checksum", "kmi_count_if", "kmi_dump_if", "kmi_erase_if", "kmi_table_info", "kmi_launch_count", "kmi_last_stage_ms", "kmi_last_kernel_ms",
     "kmi_synth_record_bytes", "kmi_synth_fastq_dev", "kmi_synth_fasta_bytes", "kmi_synth_fasta_dev", "kmi_synth_queries_dev",
 )
 
@@ -388,6 +389,26 @@ class Index:
         else:
             order = np.lexsort((vals, keys))
         return keys[order], vals[order]
+
+    def count_if(self, op, value):
+        """entries whose value is >= / <= / == value (op "ge" / "le" / "eq"), counted on the device"""
+        n = _U64(0)
+        _check(self._lib.kmi_count_if(self._h, {"ge": 0, "le": 1, "eq": 2}[op], value, ctypes.byref(n)))
+        return n.value
+
+    def find_if(self, op, value):
+        n = self.count_if(op, value)
+        keys = np.zeros(max(n, 1) * self.nw, dtype=np.uint64)
+        vals = np.zeros(max(n, 1), dtype=np.uint64)
+        got = _SZ(0)
+        _check(self._lib.kmi_dump_if(self._h, {"ge": 0, "le": 1, "eq": 2}[op], value, _hptr(keys), _hptr(vals), n, ctypes.byref(got)))
+        k = keys[:got.value * self.nw]
+        return (k.reshape(-1, 2) if self.nw == 2 else k), vals[:got.value]
+
+    def erase_if(self, op, value):
+        n = _U64(0)
+        _check(self._lib.kmi_erase_if(self._h, {"ge": 0, "le": 1, "eq": 2}[op], value, ctypes.byref(n)))
+        return n.value
 
     def checksum(self):
         a, b = _U64(0), _U64(0)

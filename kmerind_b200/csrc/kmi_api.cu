@@ -1071,7 +1071,7 @@ extern "C" int kmi_dump(kmi_index* idx, uint64_t* keys, uint64_t* vals, size_t c
   if (r == KMI_OK) {
     zero_ctr(idx, CTR_CURSOR);
     idx->touch();
-    idx->ops->dump(idx->stream, idx->slots, idx->cap, dk.as<u64>(), dv.as<u64>(), size, idx->ctr + CTR_CURSOR);
+    idx->ops->dump(idx->stream, idx->slots, idx->cap, dk.as<u64>(), dv.as<u64>(), size, idx->ctr + CTR_CURSOR, -1, 0);
     idx->launches++;
     cudaError_t e = cudaSuccess;
     if (keys) e = cudaMemcpyAsync(keys, dk.p, size * kb, cudaMemcpyDeviceToHost, idx->stream);
@@ -1082,6 +1082,75 @@ extern "C" int kmi_dump(kmi_index* idx, uint64_t* keys, uint64_t* vals, size_t c
   }
   dk.release(); dv.release();
   return r;
+}
+
+// ---- f2: predicates on the stored value, evaluated on the device (COUNT index: the frequency) -----------------------------
+static int pred_args(kmi_index* idx, int op) {
+  if (!idx) return fail(KMI_ERR_ARG, "null index");
+  if (op < KMI_PRED_GE || op > KMI_PRED_EQ) return fail(KMI_ERR_ARG, "predicate must be KMI_PRED_GE, _LE or _EQ");
+  if (idx->cfg.mode != KMI_MODE_COUNT) return fail(KMI_ERR_UNSUPPORTED, "value predicates are evaluated on the device for COUNT indices");
+  return KMI_OK;
+}
+extern "C" int kmi_count_if(kmi_index* idx, int op, uint64_t value, uint64_t* n) {
+  OK(pred_args(idx, op));
+  if (!n) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  *n = 0;
+  if (!idx->slots) return KMI_OK;
+  OK(zero_ctr(idx, CTR_CURSOR));
+  idx->touch();
+  idx->ops->dump(idx->stream, idx->slots, idx->cap, nullptr, nullptr, 0, idx->ctr + CTR_CURSOR, op, value);
+  idx->launches++;
+  u64 v = 0;
+  OK(read_ctr(idx, CTR_CURSOR, &v));
+  *n = v;
+  return check_table_error(idx);
+}
+extern "C" int kmi_dump_if(kmi_index* idx, int op, uint64_t value, uint64_t* keys, uint64_t* vals, size_t cap, size_t* n_out) {
+  OK(pred_args(idx, op));
+  if (!n_out || (!keys && cap)) return fail(KMI_ERR_ARG, "null argument");
+  CU(cudaSetDevice(idx->cfg.device));
+  *n_out = 0;
+  if (!idx->slots || cap == 0) return KMI_OK;
+  const size_t kb = sizeof(u64) * idx->nw;
+  DevBuf dk, dv;
+  int r = dk.ensure(cap * kb);
+  if (r == KMI_OK) r = dv.ensure(cap * sizeof(u64));
+  if (r == KMI_OK) {
+    zero_ctr(idx, CTR_CURSOR);
+    idx->touch();
+    idx->ops->dump(idx->stream, idx->slots, idx->cap, dk.as<u64>(), dv.as<u64>(), cap, idx->ctr + CTR_CURSOR, op, value);
+    idx->launches++;
+    u64 m = 0;
+    r = read_ctr(idx, CTR_CURSOR, &m);
+    if (r == KMI_OK && m > cap) r = fail(KMI_ERR_CAPACITY, "dump_if: %llu entries satisfy the predicate, capacity %zu (kmi_count_if sizes it)", (unsigned long long)m, cap);
+    if (r == KMI_OK && m) {
+      cudaError_t e = cudaMemcpyAsync(keys, dk.p, m * kb, cudaMemcpyDeviceToHost, idx->stream);
+      if (e == cudaSuccess && vals) e = cudaMemcpyAsync(vals, dv.p, m * sizeof(u64), cudaMemcpyDeviceToHost, idx->stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(idx->stream);
+      if (e != cudaSuccess) r = fail(KMI_ERR_CUDA, "dump_if: %s", cudaGetErrorString(e));
+    }
+    if (r == KMI_OK) *n_out = m;
+  }
+  dk.release(); dv.release();
+  return r;
+}
+extern "C" int kmi_erase_if(kmi_index* idx, int op, uint64_t value, uint64_t* n_removed) {
+  OK(pred_args(idx, op));
+  CU(cudaSetDevice(idx->cfg.device));
+  if (n_removed) *n_removed = 0;
+  if (!idx->slots) return KMI_OK;
+  OK(zero_ctr(idx, CTR_REMOVED));
+  idx->touch();
+  idx->ops->erase_if(idx->stream, idx->slots, idx->cap, idx->ctr + CTR_SIZE, idx->ctr + CTR_REMOVED, op, value);
+  idx->launches++;
+  u64 removed = 0;
+  OK(read_ctr(idx, CTR_REMOVED, &removed));
+  OK(read_ctr(idx, CTR_SIZE, &idx->size_exact));
+  idx->size_upper = idx->size_exact;
+  idx->tombstones += removed;
+  if (n_removed) *n_removed = removed;
+  return KMI_OK;
 }
 
 extern "C" int kmi_checksum(kmi_index* idx, uint64_t* key_value_sum, uint64_t* value_sum) {

@@ -98,21 +98,28 @@ __global__ void __launch_bounds__(256) k_erase(TableView t, const u64* __restric
   }
 }
 
-// to_vector(): compact live entries (unordered)
+// value predicate evaluated on the device (find(pred) / count(pred) / erase(pred) of the reference with the predicates its
+// drivers use: frequency thresholds; kmer_index.hpp:156-194, distributed_densehash_map.hpp:1666-1686,1835-1903).
+// op: -1 always, 0 val >= x, 1 val <= x, 2 val == x
+__device__ __forceinline__ bool value_pred(int op, u64 x, u32 val) {
+  return op < 0 || (op == 0 ? (u64)val >= x : op == 1 ? (u64)val <= x : (u64)val == x);
+}
+// to_vector() / find(pred): compact the live entries that satisfy the predicate (unordered). keys == nullptr: count only.
 template <int NW>
 __global__ void __launch_bounds__(256)
 k_dump(const Slot<NW>* __restrict__ slots, u64 n_slots, u64* __restrict__ keys, u64* __restrict__ vals, u64 cap,
-       u64* __restrict__ cursor) {
+       u64* __restrict__ cursor, const int op, const u64 x) {
   for (u64 base = (u64)blockIdx.x * blockDim.x; base < n_slots; base += (u64)gridDim.x * blockDim.x) {
     u64 i = base + threadIdx.x;
     Key<NW> key; key.w[NW - 1] = KEY_EMPTY_TOP;
     if (i < n_slots) key = slot_key<NW>(slots + i);
     bool live = is_live<NW>(key);
+    if (live && op >= 0) live = value_pred(op, x, slots[i].val);
     u32 m = __ballot_sync(0xffffffffu, live);
     u64 wbase = 0;
     if ((threadIdx.x & 31) == 0 && m) wbase = atomicAdd(cursor, (u64)__popc(m));
     wbase = __shfl_sync(0xffffffffu, wbase, 0);
-    if (live) {
+    if (live && keys) {
       u64 at = wbase + __popc(m & ((1u << (threadIdx.x & 31)) - 1));
       if (at < cap) {
         store_key<NW>(keys, at, key);
@@ -120,6 +127,22 @@ k_dump(const Slot<NW>* __restrict__ slots, u64 n_slots, u64* __restrict__ keys, 
       }
     }
   }
+}
+
+// erase(pred): tombstone every live entry whose value satisfies the predicate; *removed += entries erased
+template <int NW>
+__global__ void __launch_bounds__(256)
+k_erase_if(Slot<NW>* __restrict__ slots, u64 n_slots, u64* __restrict__ size, u64* __restrict__ removed, const int op, const u64 x) {
+  u32 n = 0;
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (u64)gridDim.x * blockDim.x) {
+    const Key<NW> key = slot_key<NW>(slots + i);
+    if (!is_live<NW>(key) || !value_pred(op, x, slots[i].val)) continue;
+    if (NW == 1) reinterpret_cast<Slot<1>*>(slots + i)->key = KEY_DELETED_TOP;   // one thread per slot: no race inside this kernel
+    else { Slot<2>* s2 = reinterpret_cast<Slot<2>*>(slots + i); s2->lo = 0; s2->hi = KEY_DELETED_TOP; }
+    ++n;
+  }
+  n = warp_sum(n);
+  if ((threadIdx.x & 31) == 0 && n) { atomicAdd(size, ~(u64)n + 1); atomicAdd(removed, (u64)n); }
 }
 
 // order-independent checksums: sum mix(key)*val, sum val

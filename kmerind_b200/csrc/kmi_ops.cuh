@@ -34,7 +34,8 @@ struct Ops {
   void (*rehash)(cudaStream_t, const void* old_slots, u64 n_old, TableView);
   void (*lookup)(cudaStream_t, TableView, const u64* keys, u64 n, u64* vals, uint8_t* found, u64* slot_idx, bool canon);
   void (*erase)(cudaStream_t, TableView, const u64* keys, u64 n, u64* vals_removed, bool canon);
-  void (*dump)(cudaStream_t, const void* slots, u64 n_slots, u64* keys, u64* vals, u64 cap, u64* cursor);
+  void (*dump)(cudaStream_t, const void* slots, u64 n_slots, u64* keys, u64* vals, u64 cap, u64* cursor, int op, u64 x);
+  void (*erase_if)(cudaStream_t, void* slots, u64 n_slots, u64* size, u64* removed, int op, u64 x);
   void (*checksum)(cudaStream_t, const void* slots, u64 n_slots, u64* out2);
   void (*canonicalize)(cudaStream_t, const u64* in, u64* out, u64 n);
   void (*hash_keys)(cudaStream_t, int which, const u64* in, u64* out, u64 n);
@@ -150,8 +151,11 @@ struct OpsImpl {
   static void erase(cudaStream_t st, TableView t, const u64* keys, u64 n, u64* vals_removed, bool canon) {
     if (n) k_erase<K, HASH><<<grid_for(n, 256), 256, 0, st>>>(t, keys, n, vals_removed, canon);
   }
-  static void dump(cudaStream_t st, const void* slots, u64 n_slots, u64* keys, u64* vals, u64 cap, u64* cursor) {
-    k_dump<NW><<<grid_for(n_slots, 256), 256, 0, st>>>(reinterpret_cast<const S*>(slots), n_slots, keys, vals, cap, cursor);
+  static void dump(cudaStream_t st, const void* slots, u64 n_slots, u64* keys, u64* vals, u64 cap, u64* cursor, int op, u64 x) {
+    k_dump<NW><<<grid_for(n_slots, 256), 256, 0, st>>>(reinterpret_cast<const S*>(slots), n_slots, keys, vals, cap, cursor, op, x);
+  }
+  static void erase_if(cudaStream_t st, void* slots, u64 n_slots, u64* size, u64* removed, int op, u64 x) {
+    k_erase_if<NW><<<grid_for(n_slots, 256), 256, 0, st>>>(reinterpret_cast<S*>(slots), n_slots, size, removed, op, x);
   }
   static void checksum(cudaStream_t st, const void* slots, u64 n_slots, u64* out2) {
     k_checksum<NW><<<grid_for(n_slots, 256), 256, 0, st>>>(reinterpret_cast<const S*>(slots), n_slots, out2);
@@ -190,7 +194,7 @@ struct OpsImpl {
     o.K = K; o.NW = NW; o.hash = HASH;
     o.fastq_kmers = fastq_kmers; o.scatter_keys = scatter_keys; o.insert_buckets = insert_buckets; o.hll_buckets = hll_buckets;
     o.scatter_fine = scatter_fine; o.insert_segments = insert_segments; o.insert_overflow = insert_overflow; o.owner_push = owner_push; o.fasta_kmers = fasta_kmers; o.table_clear = table_clear; o.insert_keys = insert_keys; o.rehash = rehash;
-    o.lookup = lookup; o.erase = erase; o.dump = dump; o.checksum = checksum; o.canonicalize = canonicalize;
+    o.lookup = lookup; o.erase = erase; o.dump = dump; o.erase_if = erase_if; o.checksum = checksum; o.canonicalize = canonicalize;
     o.hash_keys = hash_keys; o.part_hist = part_hist; o.part_scatter = part_scatter; o.csr_scan_l1 = csr_scan_l1;
     o.csr_fill = csr_fill; o.log_filter = log_filter; o.zero_aux = zero_aux;
     return o;

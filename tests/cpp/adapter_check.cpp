@@ -133,6 +133,18 @@ static int count_checks() {
     for (const auto& kc : per_key) s += kc.second;
     CHECK(s == n3);
   }
+  // the same predicates evaluated on the device (kmi::count_at_least & co.): only matching entries are read back
+  {
+    std::vector<V> dev = idx.find(kmi::count_at_least(3));
+    std::vector<V> host = idx.find(often);
+    sort_pairs(dev); sort_pairs(host);
+    CHECK(dev.size() == host.size());
+    for (size_t i = 0; i < dev.size(); ++i) CHECK(dev[i].first == host[i].first && dev[i].second == host[i].second);
+    CHECK(idx.count_if(kmi::count_at_least(3)) == dev.size());
+    size_t ones = 0, le2 = 0;
+    for (const auto& kv : want) { ones += kv.second == 1 ? 1 : 0; le2 += kv.second <= 2 ? 1 : 0; }
+    CHECK(idx.count_if(kmi::count_equal(1)) == ones && idx.count_if(kmi::count_at_most(2)) == le2);
+  }
   // erase with a predicate on half of the queries, then by predicate over the whole map, then plain
   {
     std::vector<Key> half(q.begin(), q.begin() + q.size() / 2);
@@ -148,7 +160,8 @@ static int count_checks() {
     for (auto it = want.begin(); it != want.end();) {
       if (it->second == 1) { it = want.erase(it); ++expect; } else ++it;
     }
-    CHECK(idx.erase(single) == expect);
+    CHECK(idx.erase(kmi::count_equal(1)) == expect);      // device-side sweep
+    CHECK(idx.erase(single) == 0);                        // nothing left for the host-side form
     CHECK(idx.local_size() == want.size());
     std::vector<Key> some(q.begin() + q.size() / 2, q.begin() + q.size() / 2 + 300);
     expect = 0;

@@ -848,3 +848,29 @@ def test_k63_build_into_a_large_reserved_table_in_batches():
         assert idx.checksum()[1] == len(keys)
         gk, gc = idx.sorted_dump()
         assert np.array_equal(gk, wk) and np.array_equal(gc, wc)
+
+
+def test_value_predicates_on_the_device():
+    """find(pred) / count(pred) / erase(pred) for frequency thresholds (kmer_index.hpp:156-194) evaluated by the table sweep:
+    equal to filtering the oracle's dump; erased entries are gone for queries and size, and the table keeps working."""
+    k = 31
+    buf = ou.read_fixture("test.medium.fastq")
+    keys, _, _ = ou.fastq_kmers(buf, k)
+    extra = ou.canonical(ou.random_keys(k, 5000, seed=2), k)
+    allk = np.concatenate([keys, extra, extra[:1000]])
+    wk, wc = ou.count_sorted(allk, k)
+    with kb.CountIndex(k) as idx:
+        idx.insert(allk)
+        for op, x, sel in (("ge", 3, wc >= 3), ("le", 1, wc <= 1), ("eq", 2, wc == 2), ("ge", 10**9, wc >= 10**9)):
+            assert idx.count_if(op, x) == int(sel.sum())
+            gk, gv = idx.find_if(op, x)
+            o = np.argsort(gk)
+            assert np.array_equal(gk[o], wk[sel]) and np.array_equal(gv[o], wc[sel])
+        assert idx.erase_if("eq", 1) == int((wc == 1).sum())
+        assert idx.local_size() == int((wc != 1).sum())
+        assert np.array_equal(idx.count(wk), (wc != 1).astype(np.uint64))
+        idx.insert(wk[wc == 1][:10])
+        assert idx.local_size() == int((wc != 1).sum()) + min(10, int((wc == 1).sum()))
+    with kb.PositionIndex(21) as pidx:
+        with pytest.raises(kb.KmiError):
+            pidx.count_if("ge", 1)
