@@ -76,8 +76,10 @@ int kmi_set_stream(kmi_index* idx, void* cuda_stream);
  * 0 auto (by input size), 1 direct atomics from the parser, 2 through the 256 hash-prefix buckets
  * (table segments stay L2-resident). KMI_PARAM_SEGMENT_INSERT (bucketed path): 1 (default) =
  * second-level scatter + table segments updated in shared memory, 0 = L2-resident global atomics.
- * Results are identical on every path. */
-typedef enum { KMI_PARAM_BUILD_PATH = 1, KMI_PARAM_SEGMENT_INSERT = 2 } kmi_param;
+ * Results are identical on every path.
+ * KMI_PARAM_SATURATE (COUNT index): 1 = counts stick at 2^32 - 1 instead of wrapping — saturating_counting_densehash_map,
+ * distributed_densehash_map.hpp:2904-3075 (default 0: std::plus<uint32_t>, :2475); such an index inserts on path 1. */
+typedef enum { KMI_PARAM_BUILD_PATH = 1, KMI_PARAM_SEGMENT_INSERT = 2, KMI_PARAM_SATURATE = 3 } kmi_param;
 int kmi_set_param(kmi_index* idx, int param, int64_t value);
 /* map_base::reserve — src/containers/distributed_map_base.hpp:149-302 */
 int kmi_reserve(kmi_index* idx, uint64_t n_distinct);

@@ -439,6 +439,10 @@ class Index:
         """0 auto, 1 direct atomics, 2 hash-prefix buckets (KMI_PARAM_BUILD_PATH)."""
         _check(self._lib.kmi_set_param(self._h, 1, path))
 
+    def set_saturate(self, on):
+        """counts stick at 2^32 - 1 instead of wrapping (saturating_counting_densehash_map)"""
+        _check(self._lib.kmi_set_param(self._h, 3, 1 if on else 0))
+
     def set_segment_insert(self, on):
         """bucketed path: shared-memory segment insert (default) or L2 atomics (KMI_PARAM_SEGMENT_INSERT)."""
         _check(self._lib.kmi_set_param(self._h, 2, 1 if on else 0))

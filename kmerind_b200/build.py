@@ -61,5 +61,39 @@ def build(force=False, verbose=False):
     return OUT
 
 
+# k-mer lengths whose kernels are built as loadable modules by default (kmods/libkmi_k<K>.so); any K in 2..31, 33..63 can be
+# added with --k / --all-k. libkmi.so loads them on demand (kmi_create).
+KMODS_DEFAULT = (17, 25, 27, 33, 55)
+
+
+def build_kmods(ks=KMODS_DEFAULT, force=False, verbose=False):
+    hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh")]
+    inst = os.path.join(CSRC, "kmi_ops_inst.cu")
+    outdir = os.path.join(HERE, "kmods")
+    os.makedirs(outdir, exist_ok=True)
+    jobs, outs = [], []
+    for k in ks:
+        if k in KS:
+            continue
+        if not (2 <= k <= 63) or k == 32:
+            raise ValueError("k=%d needs >= 2 pad bits (2..31, 33..63)" % k)
+        o = os.path.join(outdir, "libkmi_k%d.so" % k)
+        outs.append(o)
+        if force or _newer(o, hdrs + [inst]):
+            jobs.append([NVCC] + FLAGS + ["-DKMI_K=%d" % k, "-DKMI_MODULE", "-shared", inst, "-o", o, "-cudart", "static"])
+    if jobs:
+        with ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
+            list(ex.map(_run, jobs))
+    if verbose:
+        print("k-mer length modules:", ", ".join(os.path.basename(o) for o in outs))
+    return outs
+
+
 if __name__ == "__main__":
     build(force="--force" in sys.argv, verbose=True)
+    ks = list(KMODS_DEFAULT)
+    if "--all-k" in sys.argv:
+        ks = [k for k in range(2, 64) if k != 32]
+    if "--k" in sys.argv:
+        ks = [int(x) for x in sys.argv[sys.argv.index("--k") + 1:] if x.isdigit()]
+    build_kmods(ks, force="--force" in sys.argv, verbose=True)

@@ -35,6 +35,46 @@ int fail(int code, const char* fmt, ...) {
 }
 }  // namespace kmi
 
+// any other K: its kernels live in kmods/libkmi_k<K>.so next to this library (python -m kmerind_b200.build --k K ...)
+#include <dlfcn.h>
+#include <map>
+#include <mutex>
+#include <string>
+static const Ops* find_ops_module(int k, int hash) {
+  static std::mutex mu;
+  static std::map<int, void*> loaded;
+  std::lock_guard<std::mutex> lock(mu);
+  void* h = nullptr;
+  auto it = loaded.find(k);
+  if (it != loaded.end()) h = it->second;
+  else {
+    std::string dir;
+    if (const char* e = getenv("KMI_KMOD_DIR")) dir = e;
+    else {
+      Dl_info info;
+      if (dladdr(reinterpret_cast<const void*>(&find_ops_module), &info) && info.dli_fname) {
+        dir = info.dli_fname;
+        const size_t slash = dir.rfind('/');
+        dir = (slash == std::string::npos ? std::string(".") : dir.substr(0, slash)) + "/kmods";
+      }
+    }
+    const std::string path = dir + "/libkmi_k" + std::to_string(k) + ".so";
+    h = dlopen(path.c_str(), RTLD_NOW | RTLD_LOCAL);
+    if (h) {
+      typedef unsigned long (*abi_fn)(void);
+      typedef int (*k_fn)(void);
+      abi_fn abi = reinterpret_cast<abi_fn>(dlsym(h, "kmi_ops_module_abi"));
+      k_fn kk = reinterpret_cast<k_fn>(dlsym(h, "kmi_ops_module_k"));
+      if (!abi || !kk || abi() != sizeof(Ops) || kk() != k) { dlclose(h); h = nullptr; }   // built from other headers
+    }
+    loaded[k] = h;
+  }
+  if (!h) return nullptr;
+  typedef const Ops* (*ops_fn)(int);
+  ops_fn f = reinterpret_cast<ops_fn>(dlsym(h, "kmi_ops_module"));
+  return f ? f(hash) : nullptr;
+}
+
 static const Ops* find_ops(int k, int hash) {
   switch (k) {
     case 15: return kmi_ops_k15(hash);
@@ -43,7 +83,7 @@ static const Ops* find_ops(int k, int hash) {
     case 35: return kmi_ops_k35(hash);
     case 47: return kmi_ops_k47(hash);
     case 63: return kmi_ops_k63(hash);
-    default: return nullptr;
+    default: return find_ops_module(k, hash);
   }
 }
 
@@ -155,7 +195,8 @@ extern "C" int kmi_create(const kmi_config* cfg, kmi_index** out) {
   if (cfg->nranks < 1 || cfg->nranks > MAX_RANKS || cfg->rank < 0 || cfg->rank >= cfg->nranks)
     return fail(KMI_ERR_ARG, "bad rank %d / nranks %d (max %d)", cfg->rank, cfg->nranks, MAX_RANKS);
   const Ops* ops = find_ops(cfg->k, cfg->hash);
-  if (!ops) return fail(KMI_ERR_UNSUPPORTED, "k=%d is not instantiated (built: 15, 21, 31, 35, 47, 63)", cfg->k);
+  if (!ops) return fail(KMI_ERR_UNSUPPORTED, "k=%d: libkmi.so carries 15, 21, 31, 35, 47, 63 and found no kmods/libkmi_k%d.so next to it "
+                                 "(python -m kmerind_b200.build --k %d builds it)", cfg->k, cfg->k, cfg->k);
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0)
@@ -210,11 +251,18 @@ extern "C" int kmi_set_param(kmi_index* idx, int param, int64_t value) {
   if (!idx) return fail(KMI_ERR_ARG, "null index");
   if (param == KMI_PARAM_BUILD_PATH) {
     if (value < 0 || value > 2) return fail(KMI_ERR_ARG, "build path must be 0 (auto), 1 (direct) or 2 (bucketed)");
+    if (idx->saturate && value != 1) return fail(KMI_ERR_ARG, "a saturating index inserts with direct atomics (build path 1)");
     idx->build_path = (int)value;
     return KMI_OK;
   }
   if (param == KMI_PARAM_SEGMENT_INSERT) {
     idx->seg_path = value != 0;
+    return KMI_OK;
+  }
+  if (param == KMI_PARAM_SATURATE) {
+    if (idx->cfg.mode != KMI_MODE_COUNT) return fail(KMI_ERR_ARG, "saturating counts belong to a COUNT index");
+    idx->saturate = value != 0;
+    if (idx->saturate) idx->build_path = 1;              // the shared-memory segment insert adds with plain wrap-around
     return KMI_OK;
   }
   return fail(KMI_ERR_ARG, "unknown parameter %d", param);
@@ -569,7 +617,7 @@ extern "C" int kmi_parse_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_
   KeySink sink;
   sink.keys = reinterpret_cast<u64*>(d_keys); sink.ids = reinterpret_cast<u64*>(d_ids); sink.cap = cap; sink.cursor = idx->ctr + CTR_CURSOR;
   sink.file_offset = file_offset; sink.tile_rec = d_ids ? idx->tile_rec.as<u64>() : nullptr;
-  TableView none; none.slots = nullptr; none.mask = 0; none.shift = 63; none.size = nullptr; none.error = nullptr;
+  TableView none; none.slots = nullptr; none.mask = 0; none.shift = 63; none.size = nullptr; none.error = nullptr; none.saturate = 0;
   idx->ops->fastq_kmers(idx->stream, 0, d_bytes, n, n_tiles, idx->tile_lines.as<u32>(), idx->block_sums.as<u32>(), sink, none, BucketSink(),
                         idx->ctr + CTR_NKMERS, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), idx->cfg.canonical != 0,
                         idx->cfg.nsplit != 0, 0, 1);
@@ -697,7 +745,7 @@ static int build_fastq_positions(kmi_index* idx, const uint8_t* d_bytes, size_t 
   DevBuf& keys = idx->parse_keys; DevBuf& ids = idx->parse_ids;
   int r = keys.ensure(cap * sizeof(u64) * idx->nw);
   if (r == KMI_OK) r = ids.ensure(cap * sizeof(u64));
-  TableView none; none.slots = nullptr; none.mask = 0; none.shift = 63; none.size = nullptr; none.error = nullptr;
+  TableView none; none.slots = nullptr; none.mask = 0; none.shift = 63; none.size = nullptr; none.error = nullptr; none.saturate = 0;
   u64 total = 0, perr = 0;
   for (u64 tile = 0; r == KMI_OK && tile < n_tiles; tile += CHUNK_TILES) {
     const u64 tiles = std::min<u64>(CHUNK_TILES, n_tiles - tile);

@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(256) k_insert_buckets(TableView t, BucketSink 
     bool was_new;
     const u64 s = table_upsert<NW>(t, key, slot_hash<K>(key), was_new);
     if (s != ~0ULL) {
-      atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].val, 1u);
+      table_add<NW>(t, s, 1u);
       n_new += was_new ? 1u : 0u;
     }
   }
@@ -998,7 +998,7 @@ __global__ void __launch_bounds__(256) k_insert_overflow(TableView t, BucketSink
     bool was_new;
     const u64 s = table_upsert<NW>(t, key, slot_hash<K>(key), was_new);
     if (s != ~0ULL) {
-      atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].val, 1u);
+      table_add<NW>(t, s, 1u);
       n_new += was_new ? 1u : 0u;
     }
   }

@@ -81,6 +81,7 @@ struct kmi_index {
   int seg_path = 1;        // KMI_PARAM_SEGMENT_INSERT: 1 = shared-memory segment insert where possible, 0 = L2 atomics
   bool hll_ready = false;
   kmi::u64 non_hll_upper = 0;   // keys inserted by paths that do not feed the HLL (upper bound on their distinct keys)
+  bool saturate = false;   // KMI_PARAM_SATURATE: counts stick at 2^32 - 1; such an index builds with direct atomics (table_add)
   int build_path = 0;      // kmi_param KMI_PARAM_BUILD_PATH: 0 auto, 1 direct atomics, 2 bucketed
   // accounting
   kmi::u64 launches = 0;
@@ -106,7 +107,7 @@ struct kmi_index {
   kmi::TableView view() { touch(); return raw_view(); }
   kmi::TableView raw_view() const {
     kmi::TableView t;
-    t.slots = slots; t.mask = cap - 1; t.shift = 64u - (kmi::u32)__builtin_ctzll(cap ? cap : 1); t.size = ctr + kmi::CTR_SIZE; t.error = reinterpret_cast<kmi::u32*>(ctr + kmi::CTR_ERR);
+    t.slots = slots; t.mask = cap - 1; t.shift = 64u - (kmi::u32)__builtin_ctzll(cap ? cap : 1); t.size = ctr + kmi::CTR_SIZE; t.saturate = saturate ? 1u : 0u; t.error = reinterpret_cast<kmi::u32*>(ctr + kmi::CTR_ERR);
     return t;
   }
 };

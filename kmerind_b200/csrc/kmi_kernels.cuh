@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(256) k_insert_keys(TableView t, const u64* __r
     bool was_new;
     u64 s = table_upsert<NW>(t, key, slot_hash<K>(key), was_new);
     if (s != ~0ULL) {
-      atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].val, vals ? (u32)vals[i] : 1u);
+      table_add<NW>(t, s, vals ? (u32)vals[i] : 1u);
       n_new += was_new ? 1u : 0u;
     }
   }
@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(256) k_rehash(const Slot<(K <= 32 ? 1 : 2)>* _
     bool was_new;
     u64 s = table_upsert<NW>(t, key, slot_hash<K>(key), was_new);
     if (s != ~0ULL) {
-      atomicAdd(&reinterpret_cast<Slot<NW>*>(t.slots)[s].val, old[i].val);
+      table_add<NW>(t, s, old[i].val);
       n_new += was_new ? 1u : 0u;
     }
   }

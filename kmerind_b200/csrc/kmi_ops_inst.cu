@@ -16,3 +16,12 @@ const Ops* KMI_CAT(kmi_ops_k, KMI_K)(int hash) {
   return hash == 0 ? &murmur : hash == 1 ? &farm : hash == 2 ? &farm_dbg : nullptr;
 }
 }  // namespace kmi
+
+#ifdef KMI_MODULE
+// Built as its own shared object (kmods/libkmi_k<K>.so): libkmi.so carries the common k-mer lengths and loads any other K
+// on demand (kmi_create -> find_ops -> dlopen), so bliss::common::Kmer<KMER_SIZE, ...> being a template over ANY K
+// (reference src/common/kmer.hpp:128-139) does not mean shipping sixty instantiations in one library.
+extern "C" const kmi::Ops* kmi_ops_module(int hash) { return kmi::KMI_CAT(kmi_ops_k, KMI_K)(hash); }
+extern "C" int kmi_ops_module_k(void) { return KMI_K; }
+extern "C" unsigned long kmi_ops_module_abi(void) { return (unsigned long)sizeof(kmi::Ops); }
+#endif

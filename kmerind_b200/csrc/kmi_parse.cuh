@@ -627,7 +627,7 @@ k_fastq_kmers(const uint8_t* __restrict__ bytes, u64 n, const u32* __restrict__ 
         bool was_new;
         u64 slot = table_upsert<NW>(table, key, slot_hash<K>(key), was_new);
         if (slot != ~0ULL) {
-          atomicAdd(&reinterpret_cast<Slot<NW>*>(table.slots)[slot].val, 1u);
+          table_add<NW>(table, slot, 1u);
           n_new += was_new ? 1u : 0u;
         }
       }

@@ -21,6 +21,8 @@ struct TableView {
   u32 shift;       // 64 - log2(slots): home slot = store_hash >> shift (TOP bits, so that a hash
                    // prefix names a contiguous table segment for any capacity: kmi_bucket.cuh)
   u64* size;       // device counter: occupied (live) keys
+  u32 saturate;    // 1: counts stick at 2^32 - 1 instead of wrapping (saturating_counting_densehash_map,
+                   // distributed_densehash_map.hpp:2904-3075); 0: std::plus<uint32_t> wraps (:2475)
   u32* error;      // device flags, sticky until kmi_clear: TERR_FULL probe limit hit (table full), TERR_SPILL a segment insert
                    // dropped a key because the spill list was exhausted (kmi_bucket.cuh)
 };
@@ -81,6 +83,15 @@ __device__ __forceinline__ u64 table_upsert(const TableView& t, const Key<NW>& k
   }
   atomicOr(t.error, TERR_FULL);
   return ~0ULL;
+}
+
+// val += add. Saturating mode: an add that wraps is followed by a store of the maximum; any later add either lands before
+// that store (and is overwritten by it) or after it (and wraps itself, storing the maximum again), so the final value is
+// the maximum whatever the interleaving.
+template <int NW> __device__ __forceinline__ void table_add(const TableView& t, u64 slot, u32 add) {
+  u32* const v = &reinterpret_cast<Slot<NW>*>(t.slots)[slot].val;
+  const u32 old = atomicAdd(v, add);
+  if (t.saturate && old + add < old) atomicExch(v, 0xFFFFFFFFu);
 }
 
 // read-only probe: slot index or ~0

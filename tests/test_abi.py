@@ -84,8 +84,10 @@ def test_argument_validation_and_no_cpu_fallback(lib):
     for bad_k in (0, 1, 32, 64, 100):
         cfg = kb.KmiConfig(bad_k, 0, 1, 0, 0, 0, 0, 1, 0)
         assert lib.kmi_create(ctypes.byref(cfg), ctypes.byref(h)) == kb.ERR_ARG
-    cfg = kb.KmiConfig(33, 0, 1, 0, 0, 0, 0, 1, 0)
+    # K outside the built-in set needs its kernel module (kmerind_b200/kmods/libkmi_k<K>.so): 34 is never built by default
+    cfg = kb.KmiConfig(34, 0, 1, 0, 0, 0, 0, 1, 0)
     assert lib.kmi_create(ctypes.byref(cfg), ctypes.byref(h)) == kb.ERR_UNSUPPORTED
+    assert b"kmods/libkmi_k34.so" in lib.kmi_last_error()
     cfg = kb.KmiConfig(31, 0, 1, 7, 0, 0, 0, 1, 0)
     assert lib.kmi_create(ctypes.byref(cfg), ctypes.byref(h)) == kb.ERR_ARG
     cfg = kb.KmiConfig(31, 0, 1, 0, 0, 0, 2, 2, 0)

@@ -874,3 +874,52 @@ def test_value_predicates_on_the_device():
     with kb.PositionIndex(21) as pidx:
         with pytest.raises(kb.KmiError):
             pidx.count_if("ge", 1)
+
+
+def test_saturating_counts():
+    """std::plus<uint32_t> wraps at 2^32 (distributed_densehash_map.hpp:2475); the saturating map sticks at 2^32 - 1 (:2904-2947)."""
+    k = 31
+    keys = ou.canonical(ou.random_keys(k, 3, seed=8), k)
+    big = np.array([0xFFFFFFF0, 5, 0xFFFFFFFF], dtype=np.uint64)
+    more = np.array([0x20, 7, 1], dtype=np.uint64)
+    for sat, want in ((False, [0x10, 12, 0]), (True, [0xFFFFFFFF, 12, 0xFFFFFFFF])):
+        with kb.CountIndex(k) as idx:
+            idx.set_saturate(sat)
+            idx.insert(keys, big)
+            idx.insert(keys, more)
+            vals, found = idx.find(keys)
+            assert found.all() and vals.tolist() == want
+            if sat:   # plain key inserts on top of a saturated entry stay saturated, also when many threads add at once
+                idx.insert(np.repeat(keys[:1], 5000))
+                assert idx.find(keys[:1])[0][0] == 0xFFFFFFFF
+
+
+@pytest.mark.parametrize("k", (17, 27, 33, 55))
+def test_kmer_lengths_from_modules(k):
+    """bliss::common::Kmer is a template over any K (kmer.hpp:128-139): lengths outside libkmi.so's built-in set come from
+    kmods/libkmi_k<K>.so, loaded by kmi_create. Hashes, canonical form, FASTQ parse and a count index against the C oracle."""
+    if not os.path.exists(os.path.join(os.path.dirname(kb.LIB_PATH), "kmods", "libkmi_k%d.so" % k)):
+        pytest.skip("module for k=%d not built (python -m kmerind_b200.build --k %d)" % (k, k))
+    keys = ou.random_keys(k, 4000, seed=k)
+    buf = ou.read_fixture("natural.fastq")
+    wk, _, _ = ou.fastq_kmers(buf, k)
+    dk, dc = ou.count_sorted(wk, k)
+    with kb.CountIndex(k, hash=kb.HASH_FARM) as idx:
+        d = dev(keys)
+        out = torch.empty_like(d)
+        idx.canonicalize_dev(d.data_ptr(), out.data_ptr(), 4000)
+        assert np.array_equal(host_u64(out).reshape(keys.shape), ou.canonical(keys, k))
+        h = torch.empty(4000, dtype=torch.int64, device="cuda")
+        for which in (0, 1):
+            idx.hash_dev(which, d.data_ptr(), h.data_ptr(), 4000)
+            assert np.array_equal(host_u64(h), ou.hashes(keys, k, ou.hash_which(kb.HASH_FARM, which == 1)))
+        assert idx.build_fastq(buf) == len(wk)
+        gk, gc = idx.sorted_dump()
+        assert np.array_equal(gk, dk) and np.array_equal(gc, dc)
+    syn = ou.synth_fastq(0, 40000, 150, 200000, 3, 5000, 200)
+    sk, _, _ = ou.fastq_kmers(syn, k)
+    wk2, wc2 = ou.count_sorted(sk, k)
+    with kb.CountIndex(k, hash=kb.HASH_MURMUR) as idx:    # 12.7 MB: the bucketed build
+        assert idx.build_fastq(syn) == len(sk)
+        gk, gc = idx.sorted_dump()
+        assert np.array_equal(gk, wk2) and np.array_equal(gc, wc2)
