@@ -923,3 +923,26 @@ def test_kmer_lengths_from_modules(k):
         assert idx.build_fastq(syn) == len(sk)
         gk, gc = idx.sorted_dump()
         assert np.array_equal(gk, wk2) and np.array_equal(gc, wc2)
+
+
+@pytest.mark.parametrize("k,fx", [(31, "natural.withN.fastq"), (31, "test.medium.fastq"), (35, "natural.fastq")])
+def test_reference_index_template_over_b200_map(k, fx, tmp_path):
+    """The drop-in itself: the REFERENCE's bliss::index::kmer::CountIndex<MapType> template (Index::build_posix with its own file
+    reader and FASTQ / k-mer parsers, insert, find, count, size: kmer_index.hpp:98-394), compiled from /root/reference with
+    MapType = kmi::b200_map<bliss::common::Kmer<K, DNA, uint64_t>, uint32_t, COUNT> over a single-rank mpi.h
+    (oracle/Makefile -> oracle/_ref/ref_index_b200), runs on the GPU and dumps the same sorted (k-mer, count) rows as the
+    reference's own counting_densehash_map did (tests/golden/ref_t1.json)."""
+    import hashlib
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "oracle", "_ref", "ref_index_b200")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/ref_index_b200 not built (needs /root/reference at build time)")
+    out = str(tmp_path / "dump.bin")
+    r = subprocess.run([exe, "adapter", str(k), os.path.join(ou.DATA, fx), out], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    a = np.fromfile(out, dtype=np.uint64)
+    golden = json.load(open(os.path.join(root, "tests", "golden", "ref_t1.json")))["entries"]
+    want = [e for e in golden if e["mode"] == "count" and e["k"] == k and e["fixture"] == fx][0]
+    assert int(a[0]) == want["rows"]
+    assert hashlib.sha256(a[2:].tobytes()).hexdigest() == want["sha256"]

@@ -207,3 +207,37 @@ def test_oracle_vs_live_reference(k):
         assert np.array_equal(h, ou.hashes(keys, k, which + 2))
     for c in range(256):
         assert ref.kmiref_from_ascii(c) == ou.oracle().kmio_from_ascii(c)
+
+
+# ---- oracle tier T1: the reference's REAL parsers and index, executed at p = 1 (tests/golden/make_golden_t1.py) -------------
+import hashlib
+
+T1 = json.load(open(os.path.join(ou.ROOT, "tests", "golden", "ref_t1.json")))["entries"] if os.path.exists(
+    os.path.join(ou.ROOT, "tests", "golden", "ref_t1.json")) else []
+
+
+def _rows(keys, last, k):
+    keys = np.ascontiguousarray(keys, dtype=np.uint64).reshape(len(last), -1)
+    return np.concatenate([keys, np.asarray(last, dtype=np.uint64).reshape(-1, 1)], axis=1)
+
+
+@pytest.mark.parametrize("e", T1, ids=["%s-k%d-%s" % (e["mode"], e["k"], e["fixture"]) for e in T1])
+def test_oracle_equals_reference_executed_vectors(e):
+    """Every (k-mer, position id) tuple the oracle's walkers emit — in file order — and every (canonical k-mer, count) entry of
+    its count index equal what the reference's own FASTQParser / FASTAParser / KmerPositionTupleParser / CountIndex code
+    produced when it was run over the same fixture (SHA-256 of the row dump)."""
+    assert "error" not in e, e
+    buf = ou.read_fixture(e["fixture"])
+    k = e["k"]
+    if e["mode"] == "fastq_pos":
+        keys, ids, _ = ou.fastq_kmers(buf, k, canonical=False, want_ids=True)
+        rows = _rows(keys, ids, k)
+    elif e["mode"] == "fasta_pos":
+        keys, ids, _ = ou.fasta_kmers(buf, k, canonical=False)
+        rows = _rows(keys, ids, k)
+    else:
+        keys, _, _ = ou.fastq_kmers(buf, k, canonical=True)
+        dk, dc = ou.count_sorted(keys, k)
+        rows = _rows(dk, dc, k)
+    assert rows.shape[0] == e["rows"]
+    assert hashlib.sha256(np.ascontiguousarray(rows).tobytes()).hexdigest() == e["sha256"]
