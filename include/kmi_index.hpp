@@ -138,9 +138,31 @@ inline void canonical_words(uint64_t* w, unsigned k) {
 /// what the adapter needs from mxx::comm (rank / size); one process drives one GPU shard
 struct comm {
   int rank_, size_;
-  explicit comm(int rank = 0, int size = 1) : rank_(rank), size_(size) {}
+  void (*bcast_)(void* buf, int n, void* arg);   ///< rank 0's bytes to every rank (size() > 1 only)
+  void* bcast_arg_;
+  explicit comm(int rank = 0, int size = 1, void (*bcast)(void*, int, void*) = nullptr, void* arg = nullptr)
+      : rank_(rank), size_(size), bcast_(bcast), bcast_arg_(arg) {}
   int rank() const { return rank_; }
   int size() const { return size_; }
+};
+
+/// How a communicator of the caller's world carries NCCL's unique id from rank 0 to every rank when a map is created over
+/// more than one rank (kmi_comm_unique_id / kmi_comm_create). Specialise it for your communicator type; for the reference's
+/// mxx::comm that is one line:
+///   template <> struct kmi::comm_bootstrap<mxx::comm> {
+///     static void bcast(const mxx::comm& c, void* buf, int n) { MPI_Bcast(buf, n, MPI_BYTE, 0, c); } };
+/// kmi::comm carries a std::function for it (tests/cpp/dist_check.cpp hands the bytes through shared memory).
+template <typename Comm> struct comm_bootstrap {
+  static void bcast(const Comm&, void*, int) {
+    throw std::logic_error("kmi::b200_map over more than one rank: specialise kmi::comm_bootstrap<Comm>::bcast (see INTEGRATION.md)");
+  }
+};
+
+template <> struct comm_bootstrap<comm> {
+  static void bcast(const comm& c, void* buf, int n) {
+    if (!c.bcast_) throw std::logic_error("kmi::comm of more than one rank needs a bcast function");
+    c.bcast_(buf, n, c.bcast_arg_);
+  }
 };
 
 inline void check(int status) {
@@ -187,15 +209,28 @@ class b200_map {
 
   /// Comm: anything with rank() and size() — mxx::comm (Index::Index(const mxx::comm&), kmer_index.hpp:115) or kmi::comm
   template <typename Comm>
-  explicit b200_map(const Comm& c, const map_options& o = map_options()) : comm_(c.rank(), c.size()), canonical_(o.canonical) { create(o); }
+  explicit b200_map(const Comm& c, const map_options& o = map_options()) : comm_(c.rank(), c.size()), canonical_(o.canonical) {
+    uint8_t id[KMI_COMM_ID_BYTES];
+    if (c.size() > 1) {                                   // collective: every rank constructs its map
+      std::memset(id, 0, sizeof(id));
+      if (c.rank() == 0) kmi_comm_unique_id(id);           // (a failure leaves zeros: kmi_comm_create then fails on every rank alike)
+      comm_bootstrap<Comm>::bcast(c, id, (int)sizeof(id));
+    }
+    create(o);
+    if (c.size() > 1) {
+      int r = kmi_comm_create(id, c.size(), c.rank(), o.device, &kc_);
+      if (r == KMI_OK) r = kmi_dist_attach(h_, kc_);
+      if (r != KMI_OK) { kmi_destroy(h_); h_ = nullptr; if (kc_) kmi_comm_destroy(kc_); kc_ = nullptr; check(r); }
+    }
+  }
   explicit b200_map(const map_options& o = map_options()) : comm_(), canonical_(o.canonical) { create(o); }
-  ~b200_map() { kmi_destroy(h_); }
+  ~b200_map() { kmi_destroy(h_); if (kc_) kmi_comm_destroy(kc_); }
   b200_map(const b200_map&) = delete;
   b200_map& operator=(const b200_map&) = delete;
 
   /// counting_densehash_map::insert(std::vector<Key>&) — distributed_densehash_map.hpp:2714-2899
   size_t insert(std::vector<Key>& keys) {
-    check(kmi_insert(h_, reinterpret_cast<const uint64_t*>(keys.data()), nullptr, keys.size()));
+    check((kc_ ? kmi_dist_insert : kmi_insert)(h_, reinterpret_cast<const uint64_t*>(keys.data()), nullptr, keys.size()));
     return keys.size();
   }
   /// insert(std::vector<std::pair<Key,T>>&): COUNT adds the tuple's count to the key's entry (reduction insert with
@@ -209,7 +244,7 @@ class b200_map {
       std::memcpy(&id, &tuples[i].second, sizeof(T) < 8 ? sizeof(T) : 8);
       v[i] = id;
     }
-    check(kmi_insert(h_, k.data(), v.data(), tuples.size()));
+    check((kc_ ? kmi_dist_insert : kmi_insert)(h_, k.data(), v.data(), tuples.size()));
     return tuples.size();
   }
   /// find: COUNT -> (key, frequency) for hits; POSITION -> every (key, id) of every hit — :327-448. As in the reference the
@@ -271,7 +306,7 @@ class b200_map {
   std::vector<std::pair<Key, size_t>> count(std::vector<Key>& keys) const {
     transform_input(keys);
     std::vector<uint64_t> cnt(keys.size());
-    check(kmi_count(h_, reinterpret_cast<const uint64_t*>(keys.data()), keys.size(), cnt.data()));
+    check((kc_ ? kmi_dist_count : kmi_count)(h_, reinterpret_cast<const uint64_t*>(keys.data()), keys.size(), cnt.data()));
     std::vector<std::pair<Key, size_t>> out;
     out.reserve(keys.size());
     for (size_t i = 0; i < keys.size(); ++i) out.emplace_back(keys[i], (size_t)cnt[i]);
@@ -307,7 +342,7 @@ class b200_map {
   size_t erase(std::vector<Key>& keys) {
     transform_input(keys);
     uint64_t before = local_size();
-    check(kmi_erase(h_, reinterpret_cast<const uint64_t*>(keys.data()), keys.size()));
+    check((kc_ ? kmi_dist_erase : kmi_erase)(h_, reinterpret_cast<const uint64_t*>(keys.data()), keys.size()));
     return (size_t)(before - local_size());
   }
   /// erase(keys, sorted_input, pred) — kmer_index.hpp:188: the entries of the keys that satisfy the predicate (for the
@@ -350,8 +385,13 @@ class b200_map {
   void reserve(size_t n) { check(kmi_reserve(h_, n)); }
   void clear() { check(kmi_clear(h_)); }
   size_t local_size() const { uint64_t n = 0; check(kmi_local_size(h_, &n)); return (size_t)n; }
-  /// collective in the reference (allreduce, distributed_map_base.hpp:243); one shard here
-  size_t size() const { return local_size(); }
+  /// collective (allreduce of the local sizes, distributed_map_base.hpp:243) when the map spans several ranks
+  size_t size() const {
+    if (!kc_) return local_size();
+    uint64_t n = 0;
+    check(kmi_dist_size(h_, &n));
+    return (size_t)n;
+  }
   bool local_empty() const { return local_size() == 0; }
   float get_multiplicity() const {
     if (Mode == KMI_MODE_COUNT) return 1.0f;
@@ -383,9 +423,10 @@ class b200_map {
     check(kmi_build_file(h_, filename.c_str(), 0, &kmers));   // wrong extension -> std::invalid_argument, as the reference
     return kmers;
   }
+  /// this rank's record-aligned block of the reads (kmi::fastq_cuts); sharded maps exchange the k-mers by owner
   uint64_t build_fastq(const uint8_t* bytes, size_t n, uint64_t file_offset = 0) {
     uint64_t kmers = 0;
-    check(kmi_build_fastq(h_, bytes, n, file_offset, &kmers));
+    check((kc_ ? kmi_dist_build_fastq : kmi_build_fastq)(h_, bytes, n, file_offset, &kmers));
     return kmers;
   }
   uint64_t build_fasta(const uint8_t* bytes, size_t n) {
@@ -419,7 +460,7 @@ class b200_map {
     if (Mode == KMI_MODE_COUNT) {
       std::vector<uint64_t> v(keys.size());
       std::vector<uint8_t> found(keys.size());
-      check(kmi_find(h_, kp, keys.size(), v.data(), found.data()));
+      check((kc_ ? kmi_dist_find : kmi_find)(h_, kp, keys.size(), v.data(), found.data()));
       vals.clear();
       for (size_t i = 0; i < keys.size(); ++i) {
         if (found[i]) vals.push_back(v[i]);
@@ -427,16 +468,17 @@ class b200_map {
       }
     } else {
       std::vector<uint64_t> cnt(keys.size());
-      check(kmi_count(h_, kp, keys.size(), cnt.data()));
+      check((kc_ ? kmi_dist_count : kmi_count)(h_, kp, keys.size(), cnt.data()));
       uint64_t total = 0;
       for (uint64_t c : cnt) total += c;
       vals.assign(total ? total : 1, 0);
-      check(kmi_find_positions(h_, kp, keys.size(), off.data(), vals.data(), total));
+      check((kc_ ? kmi_dist_find_positions : kmi_find_positions)(h_, kp, keys.size(), off.data(), vals.data(), total));
       vals.resize(total);
     }
   }
   static T from_u64(uint64_t v) { T t; std::memset(&t, 0, sizeof(T)); std::memcpy(&t, &v, sizeof(T) < 8 ? sizeof(T) : 8); return t; }
   comm comm_;
+  kmi_comm* kc_ = nullptr;      // the map spans comm_.size() > 1 ranks: batch operations are the collective kmi_dist_* calls
   bool canonical_ = true;
   kmi_index* h_ = nullptr;
   mutable std::vector<value_type> snapshot_;

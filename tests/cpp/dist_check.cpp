@@ -35,7 +35,15 @@ void kmio_hash(int K, int which, const uint64_t* in, uint64_t* out, size_t n);
 struct Shared {
   std::atomic<int> id_ready;
   uint8_t id[KMI_COMM_ID_BYTES];
+  std::atomic<int> box_ready;            // second hand-over: the adapter's own communicator (kmi::comm_bootstrap)
+  uint8_t box[KMI_COMM_ID_BYTES];
 };
+struct BoxArg { Shared* sh; int rank; };
+static void box_bcast(void* buf, int n, void* arg) {
+  BoxArg* a = static_cast<BoxArg*>(arg);
+  if (a->rank == 0) { std::memcpy(a->sh->box, buf, (size_t)n); a->sh->box_ready.store(1); }
+  else { while (!a->sh->box_ready.load()) usleep(1000); std::memcpy(buf, a->sh->box, (size_t)n); }
+}
 
 #define CHECK(c)                                                                         \
   do {                                                                                   \
@@ -228,6 +236,35 @@ static int run_rank(int rank, int p, size_t n_reads, int K, Shared* sh) {
     }
     kmi_destroy(pidx);
   }
+  // ---- the C++ adapter over all ranks: kmi::b200_map constructed from a p-rank communicator routes to the collective calls
+  if (K <= 31) {
+    BoxArg arg = {sh, rank};
+    kmi::map_options o;
+    o.hash = KMI_HASH_FARM; o.device = device;
+    try {
+      kmi::b200_map<kmi::Kmer<31>, uint32_t, KMI_MODE_COUNT> map(kmi::comm(rank, p, box_bcast, &arg), o);
+      if (K == 31) {
+        const uint64_t produced = map.build_fastq(file.data() + cuts[rank], cuts[rank + 1] - cuts[rank], cuts[rank]);
+        uint64_t s1[1] = {produced};
+        KOK(kmi_comm_allreduce_u64(comm, s1, 1, 0));
+        CHECK(s1[0] == (uint64_t)total);
+        CHECK(map.local_size() == mine.size());
+        uint64_t s2[1] = {(uint64_t)mine.size()};
+        KOK(kmi_comm_allreduce_u64(comm, s2, 1, 0));
+        CHECK(map.size() == s2[0]);
+        std::vector<kmi::Kmer<31>> q(200);
+        for (size_t i = 0; i < q.size(); ++i) q[i].getDataRef()[0] = keys[(i * 11 + (size_t)rank) % (size_t)total];
+        auto hits = map.find(q);                           // every query is a k-mer of the file: all found, with its global count
+        CHECK(hits.size() == q.size());
+        std::map<uint64_t, uint32_t> all1;
+        for (long i = 0; i < total; ++i) all1[keys[i]]++;
+        for (const auto& h : hits) CHECK(all1[h.first.getData()[0]] == h.second);
+      }
+    } catch (const std::exception& ex) {
+      std::printf("rank %d FAIL adapter: %s\n", rank, ex.what());
+      return 1;
+    }
+  }
   KOK(kmi_comm_barrier(comm));
   kmi_comm_destroy(comm);
   if (rank == 0) std::printf("dist ok: %d ranks, K=%d, %zu reads\n", p, K, n_reads);
@@ -254,6 +291,7 @@ int main(int argc, char** argv) {
   if (sh == MAP_FAILED) return 2;
   new (sh) Shared();
   sh->id_ready.store(0);
+  sh->box_ready.store(0);
   std::vector<pid_t> kids;
   for (int r = 0; r < p; ++r) {
     pid_t c = fork();
