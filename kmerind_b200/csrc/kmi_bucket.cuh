@@ -852,7 +852,7 @@ template <int NW> struct PushSmem {
   uint8_t sbid[PUSH_ROUND];
 };
 template <int K, int HASH>
-__global__ void __launch_bounds__(TILE_THREADS, 4)
+__global__ void __launch_bounds__(TILE_THREADS, 3)
 k_owner_push(BucketSink bs, PushSink ps) {
   constexpr int NW = (K <= 32 ? 1 : 2);
   constexpr int R = PUSH_ROUND / TILE_THREADS;
@@ -876,26 +876,47 @@ k_owner_push(BucketSink bs, PushSink ps) {
   if (t < MAX_SUB) sm.hist[t] = 0;
   __syncthreads();
   const u32 n_all = cpre[N_BUCKETS + 1];
-  for (u32 c = blockIdx.x; c < n_all; c += gridDim.x) {
+  // chunk c -> (region, its keys); the keys of the NEXT chunk are requested before this one is hashed and ranked, so the
+  // global-load latency hides behind a whole round (the kernel was waiting on its key loads half of the time)
+  auto locate = [&](u32 c, u32& b, u32& m, const u64*& src) {
     int lo = 0, hi = N_BUCKETS;                           // largest region with cpre[region] <= c (256 = overflow region)
 #pragma unroll
     for (int s = 0; s < LOG_BUCKETS + 1; ++s) {
       const int mid = (lo + hi + 1) >> 1;
       if (cpre[mid] <= c) lo = mid; else hi = mid - 1;
     }
-    const u32 b = (u32)lo, first = (c - cpre[b]) * PUSH_ROUND;
+    b = (u32)lo;
+    const u32 first = (c - cpre[b]) * PUSH_ROUND;
+    const u32 cnt_b = b == N_BUCKETS ? min(*ovf_cur(bs), bs.ovf_cap) : min(bs.cursor[b], bs.capb);
+    m = min((u32)PUSH_ROUND, cnt_b - first);
+    src = (b == N_BUCKETS ? ovf_base<NW>(bs) : bs.keys + (u64)b * bs.capb * NW) + (u64)first * NW;
+  };
+  Key<NW> nkey[R];
+  u32 nb = 0, nm = 0;
+  if (blockIdx.x < n_all) {
+    const u64* src;
+    locate(blockIdx.x, nb, nm, src);
+#pragma unroll
+    for (int q = 0; q < R; ++q) { const u32 i = q * TILE_THREADS + t; if (i < nm) nkey[q] = load_key<NW>(src, i); }
+  }
+  for (u32 c = blockIdx.x; c < n_all; c += gridDim.x) {
+    const u32 b = nb, m = nm;
     const bool is_ovf = b == N_BUCKETS;
-    const u32 cnt_b = is_ovf ? min(*ovf_cur(bs), bs.ovf_cap) : min(bs.cursor[b], bs.capb);
-    const u32 m = min((u32)PUSH_ROUND, cnt_b - first);
-    const u64* src = (is_ovf ? ovf_base<NW>(bs) : bs.keys + (u64)b * bs.capb * NW) + (u64)first * NW;
     Key<NW> key[R];
+#pragma unroll
+    for (int q = 0; q < R; ++q) key[q] = nkey[q];
+    if (c + gridDim.x < n_all) {
+      const u64* src;
+      locate(c + gridDim.x, nb, nm, src);
+#pragma unroll
+      for (int q = 0; q < R; ++q) { const u32 i = q * TILE_THREADS + t; if (i < nm) nkey[q] = load_key<NW>(src, i); }
+    }
     u32 own[R], rank[R];
 #pragma unroll
     for (int q = 0; q < R; ++q) {
       const u32 i = q * TILE_THREADS + t;
       own[q] = BKT_NONE;
       if (i < m) {
-        key[q] = load_key<NW>(src, i);
         u64 hs, hd;
         kmer_hashes<K, HASH>(key[q], hs, hd);
         own[q] = mod_ranks(hd, p);

@@ -139,7 +139,8 @@ struct OpsImpl {
     return 0;
   }
   static void owner_push(cudaStream_t st, BucketSink bsink, PushSink psink, u64 n_hint) {
-    k_owner_push<K, HASH><<<grid_for(n_hint ? n_hint : 1, PUSH_ROUND, 148u * 4u * 16u), TILE_THREADS, 0, st>>>(bsink, psink);
+    // ~16 chunks per CTA: enough for the key prefetch to pay, short enough for the block scheduler to even out the SMs
+    k_owner_push<K, HASH><<<grid_for(n_hint ? n_hint / 16 + 1 : 1, PUSH_ROUND, 148u * 3u * 8u), TILE_THREADS, 0, st>>>(bsink, psink);
   }
   static void insert_overflow(cudaStream_t st, TableView t, BucketSink bsink) {
     k_insert_overflow<K, HASH><<<148u * 4u, 256, 0, st>>>(t, bsink);
