@@ -837,18 +837,31 @@ k_insert_segments2(TableView t, FineSink fs, BucketSink bs, const u32 log_seg, c
 // NVLink / NVSwitch). Because every (prefix, source) region has exactly one writer, its fill cursor is a LOCAL counter:
 // no remote atomics, and the receiver's table build starts at its fine scatter (the regions of one prefix are the
 // `sub` inputs of k_scatter_fine) — no coarse pass over received keys. Runs while the parser produces the next round.
+// TMA bulk copy shared -> global (cp.async.bulk, SASS UBLKCP): one thread hands a whole run to the copy engine of the SM,
+// which writes it as full-width bursts while the CTA goes on hashing the next chunk. src / dst 16-byte aligned, bytes % 16 == 0.
+__device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, u32 bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               :: "l"(__cvta_generic_to_global(gdst)), "r"((u32)__cvta_generic_to_shared(ssrc)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
 struct PushSink {
   u64* const* peer_keys;  // [p]: base of owner r's receive regions as seen from THIS process (own buffer for r == me)
   u32* cursor;            // [N_BUCKETS * p], local: keys sent so far to owner r for prefix b at b * p + r (accumulates over rounds)
   u32 cap_sub;            // keys per (prefix, source) region of a receive buffer
   u32 p, me;              // ranks; this rank is sub-region `me` of every prefix in every receive buffer
   u32* status;            // |= 1: a receive region would overflow (skew) -> the round is redone through the generic exchange
+  u32 bulk;               // 1: runs leave as TMA bulk copies (one thread per owner), 0: 8-byte stores by all threads
 };
 static constexpr int PUSH_ROUND = 2048;
 template <int NW> struct PushSmem {
-  u64 sorted[PUSH_ROUND * NW];
+  u64 sorted[(PUSH_ROUND + 2 * MAX_SUB + 2) * NW];   // every owner's run may start one key late (16-byte alignment of the bulk copies)
   u64 dst[MAX_SUB];       // byte address sorted[0] would land at in owner r's region (0: the run does not fit)
-  u32 hist[MAX_SUB];      // keys per owner while ranking, exclusive prefix afterwards
+  u32 hist[MAX_SUB];      // keys per owner while ranking, start of the owner's run in sorted[] afterwards
+  u32 cnt[MAX_SUB];       // keys per owner of this round
   uint8_t sbid[PUSH_ROUND];
 };
 template <int K, int HASH>
@@ -951,17 +964,23 @@ k_owner_push(BucketSink bs, PushSink ps) {
         const u32 o = __shfl_up_sync(0xffffffffu, inc, d);
         if (lane >= d) inc += o;
       }
-      const u32 ex = inc - cnt;
+      u32 ex = inc - cnt;
       if ((u32)t < p) {
         u64 d = 0;
+        u32 gb = 0;
         if (cnt) {
-          const u32 gb = atomicAdd(ps.cursor + b * p + t, cnt);
-          if ((u64)gb + cnt <= (u64)ps.cap_sub)
-            d = reinterpret_cast<u64>(ps.peer_keys[t] + ((u64)(b * p + ps.me) * ps.cap_sub + gb) * NW) - (u64)ex * (8u * NW);
-          else atomicOr(ps.status, 1u);
+          gb = atomicAdd(ps.cursor + b * p + t, cnt);
+          if ((u64)gb + cnt > (u64)ps.cap_sub) { atomicOr(ps.status, 1u); gb = ~0u; }
         }
+        if (ps.bulk) {
+          // the run starts where its first key is 16-byte aligned in shared memory exactly when it is in the region
+          if (NW == 1) ex += 2u * (u32)t + ((ex ^ gb) & 1u);
+          bulk_wait_read();                                // the copies of the last round have read their runs
+        }
+        if (cnt && gb != ~0u) d = reinterpret_cast<u64>(ps.peer_keys[t] + ((u64)(b * p + ps.me) * ps.cap_sub + gb) * NW) - (u64)ex * (8u * NW);
         sm.dst[t] = d;
         sm.hist[t] = ex;
+        sm.cnt[t] = cnt;
       }
     }
     __syncthreads();
@@ -971,19 +990,40 @@ k_owner_push(BucketSink bs, PushSink ps) {
         const u32 pos = sm.hist[own[q]] + rank[q];
         if (NW == 1) sm.sorted[pos] = key[q].w[0];
         else reinterpret_cast<ulonglong2*>(sm.sorted)[pos] = make_ulonglong2(key[q].w[0], key[q].w[NW - 1]);
-        sm.sbid[pos] = (uint8_t)own[q];
+        if (!ps.bulk) sm.sbid[pos] = (uint8_t)own[q];
+      }
+    }
+    if (ps.bulk) fence_async_smem();                       // the copy engine reads what the threads just wrote
+    __syncthreads();
+    if (ps.bulk) {
+      if ((u32)t < p) {                                    // one thread per owner: head key, bulk body, tail key
+        const u64 d = sm.dst[t];
+        u32 cnt = sm.cnt[t], at = sm.hist[t];
+        if (d && cnt) {
+          if (NW == 1) {
+            if ((d + (u64)at * 8u) & 8u) { *reinterpret_cast<u64*>(d + (u64)at * 8u) = sm.sorted[at]; ++at; --cnt; }
+            const u32 body = cnt & ~1u;
+            if (body) bulk_store(reinterpret_cast<void*>(d + (u64)at * 8u), sm.sorted + at, body * 8u);
+            if (cnt & 1u) *reinterpret_cast<u64*>(d + (u64)(at + body) * 8u) = sm.sorted[at + body];
+          } else {
+            bulk_store(reinterpret_cast<void*>(d + (u64)at * 16u), sm.sorted + 2 * at, cnt * 16u);
+          }
+        }
+        bulk_commit();
+      }
+      if (t < MAX_SUB) sm.hist[t] = 0;
+    } else {
+      if (t < MAX_SUB) sm.hist[t] = 0;
+      for (u32 r = t; r < m; r += TILE_THREADS) {
+        const u64 d = sm.dst[sm.sbid[r]];
+        if (!d) continue;
+        if (NW == 1) *reinterpret_cast<u64*>(d + (u64)r * 8u) = sm.sorted[r];
+        else *reinterpret_cast<ulonglong2*>(d + (u64)r * 16u) = reinterpret_cast<const ulonglong2*>(sm.sorted)[r];
       }
     }
     __syncthreads();
-    if (t < MAX_SUB) sm.hist[t] = 0;
-    for (u32 r = t; r < m; r += TILE_THREADS) {
-      const u64 d = sm.dst[sm.sbid[r]];
-      if (!d) continue;
-      if (NW == 1) *reinterpret_cast<u64*>(d + (u64)r * 8u) = sm.sorted[r];
-      else *reinterpret_cast<ulonglong2*>(d + (u64)r * 16u) = reinterpret_cast<const ulonglong2*>(sm.sorted)[r];
-    }
-    __syncthreads();
   }
+  if (ps.bulk && (u32)t < p) bulk_wait_all();
 }
 #ifdef KMI_DIST_KERNELS  // non-template: compiled once, in kmi_dist.cu
 // after k_owner_push of a round: publish this rank's running totals in the owners' receive buffers (count word of region

@@ -736,6 +736,7 @@ int build_fastq_push(kmi_index* idx, uint8_t* d_text, size_t n, const uint8_t* h
   PushSink ps;
   ps.peer_keys = d->peer_keys.as<u64*>(); ps.cursor = d->push_cursor.as<u32>(); ps.cap_sub = (u32)d->cap_sub; ps.p = (u32)p; ps.me = (u32)me;
   ps.status = st_in;
+  { const char* e = getenv("KMI_PUSH_BULK"); ps.bulk = (e && e[0] == '0') ? 0u : 1u; }   // TMA bulk copies of the runs (0: plain stores, A/B)
   u64 next_tile = 0;                                        // first tile not parsed yet
   for (u64 r = 0; r < n_rounds; ++r) {
     const int w = (int)(r & 1);
