@@ -177,6 +177,21 @@ int kmi_hash_dev(kmi_index* idx, int which, const uint64_t* d_keys, uint64_t* d_
 int kmi_partition_dev(kmi_index* idx, const uint64_t* d_keys, const uint64_t* d_vals, size_t n,
                       uint64_t* d_keys_out, uint64_t* d_vals_out, uint64_t* h_counts);
 
+/* kmi_partition_dev for callers that cannot allocate. NO COUNTERPART IN THE REFERENCE: added
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). Same stable
+ * counting-sort by owner, same outputs, but the scratch (per-chunk owner histogram + scan sums) is one file-scope
+ * __device__ array of KMI_PARTITION_NOALLOC_MAX_HIST + ~1100 32-bit words (4.2 MB) that every GPU loading the library holds
+ * until exit, and the per-owner counts are written to DEVICE memory (d_counts[nranks]) with no stream synchronisation.
+ * The call performs no cudaMalloc / cudaFree and grows no buffer of the index; work is queued on the index's stream.
+ * Limit: ceil(n / 2048) * nranks <= KMI_PARTITION_NOALLOC_MAX_HIST, i.e. n <= kmi_partition_noalloc_max_keys(nranks)
+ * (268 M keys at 8 ranks); beyond it the call returns KMI_ERR_ARG and touches nothing. All calls on one GPU share the
+ * scratch: calls that overlap on the device (different streams / indexes / threads) race — serialise them. The first call per
+ * device looks the array's address up (cudaGetSymbolAddress); make that call once before starting a graph capture. */
+#define KMI_PARTITION_NOALLOC_MAX_HIST (1u << 20)
+size_t kmi_partition_noalloc_max_keys(int nranks);
+int kmi_partition_noalloc_dev(kmi_index* idx, const uint64_t* d_keys, const uint64_t* d_vals, size_t n,
+                              uint64_t* d_keys_out, uint64_t* d_vals_out, uint64_t* d_counts);
+
 /* ---- insert (Index::insert, kmer_index.hpp:201-225) ---------------------------------------- */
 /* COUNT mode: vals == NULL: each key counts 1 (counting_densehash_map::insert(vector<Key>&),
  * distributed_densehash_map.hpp:2714-2899); vals != NULL: (key, count) tuples, vals[i] is ADDED to the entry of keys[i]

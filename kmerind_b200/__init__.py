@@ -87,7 +87,7 @@ def load_library(build_if_missing=False):
         "kmi_dist_size": [_P, _P], "kmi_dist_last_stats": [_P, _P, _P, _P],
         "kmi_fastq_find_first_record": [_P, _U64, _SZ, _U64, _U64, _U64, _U64, _P],
         "kmi_canonicalize_dev": [_P, _P, _P, _SZ], "kmi_hash_dev": [_P, ctypes.c_int, _P, _P, _SZ],
-        "kmi_partition_dev": [_P, _P, _P, _SZ, _P, _P, _P],
+        "kmi_partition_dev": [_P, _P, _P, _SZ, _P, _P, _P], "kmi_partition_noalloc_dev": [_P, _P, _P, _SZ, _P, _P, _P],
         "kmi_insert": [_P, _P, _P, _SZ], "kmi_insert_dev": [_P, _P, _P, _SZ],
         "kmi_count": [_P, _P, _SZ, _P], "kmi_find": [_P, _P, _SZ, _P, _P],
         "kmi_find_positions": [_P, _P, _SZ, _P, _P, _SZ], "kmi_erase": [_P, _P, _SZ],
@@ -105,6 +105,8 @@ def load_library(build_if_missing=False):
         fn = getattr(lib, name)
         fn.argtypes = args
         fn.restype = ctypes.c_int
+    lib.kmi_partition_noalloc_max_keys.restype = _SZ
+    lib.kmi_partition_noalloc_max_keys.argtypes = [ctypes.c_int]
     lib.kmi_synth_fasta_bytes.restype = _SZ
     lib.kmi_synth_fasta_bytes.argtypes = [ctypes.c_uint32, _U64, ctypes.c_uint32]
     lib.kmi_comm_destroy.argtypes = [_P]
@@ -122,7 +124,7 @@ EXPORTED_SYMBOLS = (
     "kmi_comm_allreduce_u64", "kmi_comm_allgather_u64", "kmi_dist_attach", "kmi_dist_build_fastq", "kmi_dist_build_fastq_dev",
     "kmi_dist_build_fasta", "kmi_dist_build_fasta_dev", "kmi_dist_insert", "kmi_dist_insert_dev", "kmi_dist_count", "kmi_dist_find",
     "kmi_dist_find_positions", "kmi_dist_erase", "kmi_dist_size", "kmi_dist_last_stats", "kmi_canonicalize_dev", "kmi_hash_dev",
-    "kmi_partition_dev", "kmi_insert", "kmi_insert_dev", "kmi_count", "kmi_find", "kmi_find_positions",
+    "kmi_partition_dev", "kmi_partition_noalloc_dev", "kmi_partition_noalloc_max_keys", "kmi_insert", "kmi_insert_dev", "kmi_count", "kmi_find", "kmi_find_positions",
     "kmi_erase", "kmi_count_dev", "kmi_find_dev", "kmi_local_size", "kmi_num_keys", "kmi_dump",
     "kmi_checksum", "kmi_count_if", "kmi_dump_if", "kmi_erase_if", "kmi_table_info", "kmi_launch_count", "kmi_last_stage_ms", "kmi_last_kernel_ms",
     "kmi_synth_record_bytes", "kmi_synth_fastq_dev", "kmi_synth_fasta_bytes", "kmi_synth_fasta_dev", "kmi_synth_queries_dev",
@@ -310,6 +312,10 @@ class Index:
         counts = np.zeros(nranks, dtype=np.uint64)
         _check(self._lib.kmi_partition_dev(self._h, d_keys, d_vals, n, d_keys_out, d_vals_out, _hptr(counts)))
         return counts
+
+    def partition_noalloc_dev(self, d_keys, d_vals, n, d_keys_out, d_vals_out, d_counts):
+        """kmi_partition_noalloc_dev: scratch in the library's static device array, counts to device memory, no sync"""
+        _check(self._lib.kmi_partition_noalloc_dev(self._h, d_keys, d_vals, n, d_keys_out, d_vals_out, d_counts))
 
     def insert_dev(self, d_keys, n, d_vals=None):
         _check(self._lib.kmi_insert_dev(self._h, d_keys, d_vals, n))

@@ -1298,6 +1298,79 @@ extern "C" int kmi_partition_dev(kmi_index* idx, const uint64_t* d_keys, const u
   return KMI_OK;
 }
 
+// ---- partition without allocation ----------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid it). Same three kernels as kmi_partition_dev; their
+// scratch — the [owner][chunk] histogram and its block sums — lives in ONE file-scope device array, held by every GPU that
+// loads the library until exit. g_part_scratch is a host-side stand-in here: host code must not hand it to a kernel, only the
+// address cudaGetSymbolAddress returns for the current device. Every call shares the array (calls that overlap on one
+// GPU race); every word a call reads was written earlier by the same call (k_part_hist fills all n_chunks * p histogram
+// words, k_scan_l1 all block sums), so nothing has to start at zero.
+static constexpr u32 NOALLOC_HIST_WORDS = KMI_PARTITION_NOALLOC_MAX_HIST;            // histogram words (n_chunks * nranks)
+static constexpr u32 NOALLOC_SUMS_AT = NOALLOC_HIST_WORDS + 64;                      // block sums start here (256-byte aligned)
+static constexpr u32 NOALLOC_WORDS = NOALLOC_SUMS_AT + NOALLOC_HIST_WORDS / 1024 + 64;
+static __device__ __align__(256) u32 g_part_scratch[NOALLOC_WORDS];                  // 4.2 MB
+
+static constexpr int NOALLOC_MAX_DEVICES = 64;
+static std::mutex g_noalloc_mu;
+static u32* g_noalloc_ptr[NOALLOC_MAX_DEVICES];   // device address of g_part_scratch, per device
+
+// counts[r] = start of owner r+1 - start of owner r, from the scanned histogram (no host read-back)
+__global__ void k_part_counts(const u32* __restrict__ hist_scanned, const u32* __restrict__ sums, u64 n_chunks, u32 p, u64 n,
+                              u64* __restrict__ counts) {
+  u32 r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= p) return;
+  u64 hi = (u64)r * n_chunks, hj = hi + n_chunks;
+  u64 b = (u64)hist_scanned[hi] + sums[hi >> 10];
+  u64 e = (r + 1 < p) ? (u64)hist_scanned[hj] + sums[hj >> 10] : n;
+  counts[r] = e - b;
+}
+
+extern "C" size_t kmi_partition_noalloc_max_keys(int nranks) {
+  if (nranks < 1 || nranks > MAX_RANKS) return 0;
+  return (size_t)(NOALLOC_HIST_WORDS / (u32)nranks) * PART_ITEMS;
+}
+
+extern "C" int kmi_partition_noalloc_dev(kmi_index* idx, const uint64_t* d_keys, const uint64_t* d_vals, size_t n,
+                                         uint64_t* d_keys_out, uint64_t* d_vals_out, uint64_t* d_counts) {
+  if (!idx || !d_counts || ((!d_keys || !d_keys_out) && n) || (d_vals && !d_vals_out)) return fail(KMI_ERR_ARG, "null argument");
+  const int dev = idx->cfg.device;
+  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return fail(KMI_ERR_ARG, "partition_noalloc: device ordinal out of range");
+  CU(cudaSetDevice(dev));
+  const u32 p = (u32)idx->cfg.nranks;
+  const u64 n_chunks = (n + PART_ITEMS - 1) / PART_ITEMS;
+  const u64 n_hist = n_chunks * p;
+  if (n_hist > NOALLOC_HIST_WORDS)
+    return fail(KMI_ERR_ARG, "partition_noalloc: %llu keys over %u ranks exceed the static scratch (at most %llu keys; use kmi_partition_dev)",
+                (unsigned long long)n, p, (unsigned long long)kmi_partition_noalloc_max_keys((int)p));
+  u32* scratch;
+  {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);     // set-up: once per device, with that device current
+    if (!g_noalloc_ptr[dev]) {
+      void* sym = nullptr;
+      CU(cudaGetSymbolAddress(&sym, g_part_scratch));
+      g_noalloc_ptr[dev] = static_cast<u32*>(sym);
+    }
+    scratch = g_noalloc_ptr[dev];
+  }
+  u32* hist = scratch;
+  u32* sums = scratch + NOALLOC_SUMS_AT;
+  if (n == 0) {
+    CU(cudaMemsetAsync(d_counts, 0, sizeof(u64) * p, idx->stream));
+    return KMI_OK;
+  }
+  const u64 n_blocks = (n_hist + 1023) / 1024;
+  idx->ops->part_hist(idx->stream, reinterpret_cast<const u64*>(d_keys), n, p, hist, n_chunks);
+  k_scan_l1<<<(unsigned)n_blocks, 1024, 0, idx->stream>>>(hist, n_hist, sums);
+  k_scan_tiles<<<1, 1024, 0, idx->stream>>>(sums, n_blocks);
+  idx->ops->part_scatter(idx->stream, reinterpret_cast<const u64*>(d_keys), reinterpret_cast<const u64*>(d_vals), n, p, hist, sums, n_chunks,
+                         reinterpret_cast<u64*>(d_keys_out), reinterpret_cast<u64*>(d_vals_out));
+  k_part_counts<<<(p + 255) / 256, 256, 0, idx->stream>>>(hist, sums, n_chunks, p, n, reinterpret_cast<u64*>(d_counts));
+  CU(cudaGetLastError());
+  idx->launches += 5;
+  return KMI_OK;
+}
+
 // ---- synthetic workload ------------------------------------------------------------------------------------
 extern "C" size_t kmi_synth_record_bytes(uint32_t read_len) { return 13 + 2 * (size_t)read_len + 4; }
 extern "C" int kmi_synth_fastq_dev(int device, uint8_t* d_out, uint64_t first_read, uint64_t n_reads, uint32_t read_len,
