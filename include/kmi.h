@@ -46,8 +46,13 @@ typedef enum { KMI_MODE_COUNT = 0, KMI_MODE_POSITION = 1 } kmi_mode;
  * murmur h[0] / farm seed 42) places a key in the local table, the dist hash (Prefix=true:
  * murmur h[1] / farm seed 83) picks the owning rank: owner = dist % nranks
  * (src/containers/distributed_densehash_map.hpp:148-170). FARM_DEBUG is farmhash as the
- * reference's default RelWithDebInfo build computes it (DebugTweak, no NDEBUG). */
-typedef enum { KMI_HASH_MURMUR = 0, KMI_HASH_FARM = 1, KMI_HASH_FARM_DEBUG = 2 } kmi_hash_kind;
+ * reference's default RelWithDebInfo build computes it (DebugTweak, no NDEBUG).
+ * IDENTITY and STD are the remaining two flavours of the reference's benchmark matrix (kmer_hash.hpp:157-232,
+ * BenchmarkKmerIndex.cpp:164-193): identity = the key's low 64 bits (store) / its top ceilLog2(nranks) bits (dist,
+ * Kmer::getPrefix); cpp_std = XOR of (std::hash<size_t>(word) << 1) over the words, shifted down to ceilLog2(nranks) + ...
+ * bits for the dist flavour exactly as cpp_std<KMER, true> does. Both make the owner a PREFIX of the key, so shards are as
+ * skewed as the keys are (the reference's too); their sharded builds always take the partition + all-to-all path. */
+typedef enum { KMI_HASH_MURMUR = 0, KMI_HASH_FARM = 1, KMI_HASH_FARM_DEBUG = 2, KMI_HASH_IDENTITY = 3, KMI_HASH_STD = 4 } kmi_hash_kind;
 
 typedef struct {
   int32_t k;            /* k-mer length */
@@ -78,8 +83,12 @@ int kmi_set_stream(kmi_index* idx, void* cuda_stream);
  * second-level scatter + table segments updated in shared memory, 0 = L2-resident global atomics.
  * Results are identical on every path.
  * KMI_PARAM_SATURATE (COUNT index): 1 = counts stick at 2^32 - 1 instead of wrapping — saturating_counting_densehash_map,
- * distributed_densehash_map.hpp:2904-3075 (default 0: std::plus<uint32_t>, :2475); such an index inserts on path 1. */
-typedef enum { KMI_PARAM_BUILD_PATH = 1, KMI_PARAM_SEGMENT_INSERT = 2, KMI_PARAM_SATURATE = 3 } kmi_param;
+ * distributed_densehash_map.hpp:2904-3075 (default 0: std::plus<uint32_t>, :2475); such an index inserts on path 1.
+ * KMI_PARAM_DIST_TRANS (non-canonical index): the DistTrans of SingleStrandHashMapParams<Key, DistHash, StoreHash, DistTrans>
+ * (BenchmarkKmerIndex.cpp:152-161,246-249) — owner = dist_hash(T(key)) % nranks with T = 0 identity (default), 1 lex_less,
+ * 2 xor_rev_comp (kmer_transform.hpp:91-107), so both strands of a k-mer meet on one rank while the stored key stays as
+ * given. Enters kmi_partition_dev and every sharded operation built on it. */
+typedef enum { KMI_PARAM_BUILD_PATH = 1, KMI_PARAM_SEGMENT_INSERT = 2, KMI_PARAM_SATURATE = 3, KMI_PARAM_DIST_TRANS = 4 } kmi_param;
 int kmi_set_param(kmi_index* idx, int param, int64_t value);
 /* map_base::reserve — src/containers/distributed_map_base.hpp:149-302 */
 int kmi_reserve(kmi_index* idx, uint64_t n_distinct);
@@ -225,6 +234,9 @@ int kmi_num_keys(kmi_index* idx, uint64_t* n);
 /* to_vector(): every (key, value) entry, unordered. COUNT: value = frequency. POSITION: one
  * entry per stored (key, id) tuple. n_out receives the number written (<= cap). */
 int kmi_dump(kmi_index* idx, uint64_t* keys, uint64_t* vals, size_t cap, size_t* n_out);
+/* the same entries ordered by (key, value) — Kmer::operator< on the key, most significant word first — sorted on the
+ * device (the radix sort of the sorted back end below). This is the order kmi_save writes. */
+int kmi_dump_sorted(kmi_index* idx, uint64_t* keys, uint64_t* vals, size_t cap, size_t* n_out);
 /* ---- f2: find(pred) / count(pred) / erase(pred) over the local map (kmer_index.hpp:156-194;
  * distributed_densehash_map.hpp:1666-1686,1835-1903) for predicates on the stored VALUE, evaluated on the device: one
  * compare fused into the table sweep instead of a dump of the whole table to the host. COUNT indices (value = frequency):
@@ -303,6 +315,41 @@ int kmi_dist_size(kmi_index* idx, uint64_t* n);
 /* last sharded build: device ms [0] whole, [1] parse + push / exchange, [2] insert of the received keys, [3] unused; keys this
  * rank received; path 1 = NVLink push, 2 = NCCL all-to-all */
 int kmi_dist_last_stats(kmi_index* idx, float* ms4, uint64_t* n_received, int32_t* path);
+
+/* ---- f4: the sort-based back end — dsc::counting_sorted_map (COUNT) / dsc::sorted_multimap (POSITION) of reference
+ * src/containers/distributed_sorted_map.hpp, the alternative MapType of the same Index<> facade (BenchmarkKmerIndex.cpp:
+ * 206-219, pMAP == SORTED). The reference keeps a std::vector per rank: insert() appends, rehash() sorts and reduces
+ * (local_reduction, :1521-1540,2560-2600), count()/find() are binary searches (:228-480). Here the entries live in HBM:
+ * build / insert append canonical keys (+ ids), kmi_sorted_rehash is one device LSD radix sort (8-bit digits, stable) over
+ * old + new entries followed by a run-length reduction (COUNT: counts summed as uint32_t, wrapping like the mapped type),
+ * queries are one binary search per key and call rehash first when entries are pending. kmi_sorted_dump returns the
+ * entries IN KEY ORDER (POSITION: ordered by (key, id)). ONE SHARD ONLY: the reference's cross-rank half — sample sort
+ * with splitters, :1544-1700 — is not built, so cfg.nranks must be 1 (KMI_ERR_UNSUPPORTED otherwise).
+ * Same conventions as the hash index: keys are canonicalised first when cfg.canonical, host pointers unless `_dev`. */
+typedef struct kmi_sorted kmi_sorted;
+int kmi_sorted_create(const kmi_config* cfg, kmi_sorted** out);
+void kmi_sorted_destroy(kmi_sorted* s);
+int kmi_sorted_build_fastq(kmi_sorted* s, const uint8_t* bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers);
+int kmi_sorted_build_fasta(kmi_sorted* s, const uint8_t* bytes, size_t n, uint64_t* n_kmers);
+int kmi_sorted_build_fastq_dev(kmi_sorted* s, const uint8_t* d_bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers);
+int kmi_sorted_build_fasta_dev(kmi_sorted* s, const uint8_t* d_bytes, size_t n, uint64_t* n_kmers);
+/* COUNT: vals == NULL counts 1 per key, else vals[i] is added; POSITION: vals[i] is the id of keys[i] */
+int kmi_sorted_insert(kmi_sorted* s, const uint64_t* keys, const uint64_t* vals, size_t n);
+int kmi_sorted_insert_dev(kmi_sorted* s, const uint64_t* d_keys, const uint64_t* d_vals, size_t n);
+int kmi_sorted_rehash(kmi_sorted* s);
+int kmi_sorted_local_size(kmi_sorted* s, uint64_t* n);
+/* counts[i]: 0/1 (COUNT) or the multiplicity (POSITION) */
+int kmi_sorted_count(kmi_sorted* s, const uint64_t* keys, size_t n, uint64_t* counts);
+int kmi_sorted_find(kmi_sorted* s, const uint64_t* keys, size_t n, uint64_t* vals, uint8_t* found);
+int kmi_sorted_find_positions(kmi_sorted* s, const uint64_t* keys, size_t n, uint64_t* offsets, uint64_t* vals, size_t cap);
+int kmi_sorted_dump(kmi_sorted* s, uint64_t* keys, uint64_t* vals, size_t cap, size_t* n_out);
+/* device ms of the last build's parse [0] and of the last rehash: sort [1], reduce [2]; kernels launched so far */
+int kmi_sorted_stats(kmi_sorted* s, float* ms3, uint64_t* launches);
+/* the radix sort by itself: n entries of idx's key width in d_keys (+ optional 8-byte values in d_vals) are sorted by
+ * (key, low val_bits bits of the value); the *_tmp arrays are scratch of the same sizes and *sorted_in_tmp tells which pair
+ * holds the result (the passes ping-pong). Stream-ordered on the index's stream. */
+int kmi_sort_pairs_dev(kmi_index* idx, uint64_t* d_keys, uint64_t* d_vals, uint64_t* d_keys_tmp, uint64_t* d_vals_tmp, size_t n,
+                       int val_bits, int* sorted_in_tmp);
 
 /* ---- synthetic workload (same bytes as oracle/kmi_oracle.c kmio_synth_fastq) - */
 size_t kmi_synth_record_bytes(uint32_t read_len);

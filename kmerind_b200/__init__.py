@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libkmi.so")
 
 MODE_COUNT, MODE_POSITION = 0, 1
-HASH_MURMUR, HASH_FARM, HASH_FARM_DEBUG = 0, 1, 2
+HASH_MURMUR, HASH_FARM, HASH_FARM_DEBUG, HASH_IDENTITY, HASH_STD = 0, 1, 2, 3, 4
 SUPPORTED_K = (15, 21, 31, 35, 47, 63)
 
 KMI_OK = 0
@@ -96,6 +96,14 @@ def load_library(build_if_missing=False):
         "kmi_checksum": [_P, _P, _P], "kmi_count_if": [_P, ctypes.c_int, _U64, _P], "kmi_dump_if": [_P, ctypes.c_int, _U64, _P, _P, _SZ, _P],
         "kmi_erase_if": [_P, ctypes.c_int, _U64, _P], "kmi_table_info": [_P, _P, _P, _P], "kmi_launch_count": [_P, _P],
         "kmi_last_stage_ms": [_P, _P], "kmi_last_kernel_ms": [_P, _P],
+        "kmi_dump_sorted": [_P, _P, _P, _SZ, _P],
+        "kmi_sorted_create": [ctypes.POINTER(KmiConfig), ctypes.POINTER(_P)],
+        "kmi_sorted_build_fastq": [_P, _P, _SZ, _U64, _P], "kmi_sorted_build_fasta": [_P, _P, _SZ, _P],
+        "kmi_sorted_build_fastq_dev": [_P, _P, _SZ, _U64, _P], "kmi_sorted_build_fasta_dev": [_P, _P, _SZ, _P],
+        "kmi_sorted_insert": [_P, _P, _P, _SZ], "kmi_sorted_insert_dev": [_P, _P, _P, _SZ], "kmi_sorted_rehash": [_P],
+        "kmi_sorted_local_size": [_P, _P], "kmi_sorted_count": [_P, _P, _SZ, _P], "kmi_sorted_find": [_P, _P, _SZ, _P, _P],
+        "kmi_sorted_find_positions": [_P, _P, _SZ, _P, _P, _SZ], "kmi_sorted_dump": [_P, _P, _P, _SZ, _P],
+        "kmi_sorted_stats": [_P, _P, _P], "kmi_sort_pairs_dev": [_P, _P, _P, _P, _P, _SZ, ctypes.c_int, _P],
         "kmi_synth_fasta_dev": [ctypes.c_int, _P, _U64, _U64, ctypes.c_uint32, _U64, ctypes.c_uint32, _U64],
         "kmi_synth_queries_dev": [ctypes.c_int, _P, _U64, _U64, ctypes.c_int, ctypes.c_uint32, _U64, _U64, _U64],
         "kmi_synth_fastq_dev": [ctypes.c_int, _P, _U64, _U64, ctypes.c_uint32, _U64, _U64, ctypes.c_uint32,
@@ -111,6 +119,8 @@ def load_library(build_if_missing=False):
     lib.kmi_synth_fasta_bytes.argtypes = [ctypes.c_uint32, _U64, ctypes.c_uint32]
     lib.kmi_comm_destroy.argtypes = [_P]
     lib.kmi_comm_destroy.restype = None
+    lib.kmi_sorted_destroy.argtypes = [_P]
+    lib.kmi_sorted_destroy.restype = None
     _lib = lib
     return lib
 
@@ -128,6 +138,10 @@ EXPORTED_SYMBOLS = (
     "kmi_erase", "kmi_count_dev", "kmi_find_dev", "kmi_local_size", "kmi_num_keys", "kmi_dump",
     "kmi_checksum", "kmi_count_if", "kmi_dump_if", "kmi_erase_if", "kmi_table_info", "kmi_launch_count", "kmi_last_stage_ms", "kmi_last_kernel_ms",
     "kmi_synth_record_bytes", "kmi_synth_fastq_dev", "kmi_synth_fasta_bytes", "kmi_synth_fasta_dev", "kmi_synth_queries_dev",
+    "kmi_dump_sorted", "kmi_sorted_create", "kmi_sorted_destroy", "kmi_sorted_build_fastq", "kmi_sorted_build_fasta",
+    "kmi_sorted_build_fastq_dev", "kmi_sorted_build_fasta_dev", "kmi_sorted_insert", "kmi_sorted_insert_dev", "kmi_sorted_rehash",
+    "kmi_sorted_local_size", "kmi_sorted_count", "kmi_sorted_find", "kmi_sorted_find_positions", "kmi_sorted_dump", "kmi_sorted_stats",
+    "kmi_sort_pairs_dev",
 )
 
 
@@ -387,6 +401,21 @@ class Index:
         _check(self._lib.kmi_dump(self._h, _hptr(keys), _hptr(vals), n, ctypes.byref(got)))
         return keys[:got.value], vals[:got.value]
 
+    def dump_sorted(self):
+        """to_vector() ordered by (key, value) ON THE DEVICE (kmi_dump_sorted: the radix sort of the sorted back end)."""
+        n = self.local_size()
+        keys = np.zeros((n, 2) if self.nw == 2 else (n,), dtype=np.uint64)
+        vals = np.zeros(n, dtype=np.uint64)
+        got = _SZ(0)
+        _check(self._lib.kmi_dump_sorted(self._h, _hptr(keys), _hptr(vals), n, ctypes.byref(got)))
+        return keys[:got.value], vals[:got.value]
+
+    def sort_pairs_dev(self, d_keys, d_vals, d_keys_tmp, d_vals_tmp, n, val_bits=0):
+        """kmi_sort_pairs_dev; returns True when the result sits in the *_tmp pair"""
+        w = ctypes.c_int(0)
+        _check(self._lib.kmi_sort_pairs_dev(self._h, d_keys, d_vals, d_keys_tmp, d_vals_tmp, n, val_bits, ctypes.byref(w)))
+        return bool(w.value)
+
     def sorted_dump(self):
         """Sorted by (key as multi-word unsigned integer, value): the parity dump."""
         keys, vals = self.to_vector()
@@ -445,6 +474,10 @@ class Index:
         """0 auto, 1 direct atomics, 2 hash-prefix buckets (KMI_PARAM_BUILD_PATH)."""
         _check(self._lib.kmi_set_param(self._h, 1, path))
 
+    def set_dist_trans(self, t):
+        """KMI_PARAM_DIST_TRANS: 0 identity, 1 lex_less, 2 xor_rev_comp under the dist hash (non-canonical index)."""
+        _check(self._lib.kmi_set_param(self._h, 4, int(t)))
+
     def set_saturate(self, on):
         """counts stick at 2^32 - 1 instead of wrapping (saturating_counting_densehash_map)"""
         _check(self._lib.kmi_set_param(self._h, 3, 1 if on else 0))
@@ -455,6 +488,98 @@ class Index:
 
     def set_stream(self, cuda_stream_ptr):
         _check(self._lib.kmi_set_stream(self._h, cuda_stream_ptr))
+
+
+class SortedMap:
+    """The sort-based back end (kmi_sorted_*): dsc::counting_sorted_map (MODE_COUNT) / dsc::sorted_multimap (MODE_POSITION)
+    of reference src/containers/distributed_sorted_map.hpp, one shard. Entries live in HBM as sorted arrays; insert / build
+    append, rehash() = device radix sort + run-length reduction, queries = binary searches."""
+
+    def __init__(self, k=31, mode=MODE_COUNT, canonical=True, hash=HASH_MURMUR, nsplit=False, device=0):
+        self._lib = load_library()
+        self.k, self.mode, self.nw = k, mode, nwords(k)
+        cfg = KmiConfig(k, mode, 1 if canonical else 0, hash, 1 if nsplit else 0, device, 0, 1, 0)
+        self._h = _P()
+        _check(self._lib.kmi_sorted_create(ctypes.byref(cfg), ctypes.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            self._lib.kmi_sorted_destroy(self._h)
+            self._h = _P()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def build_fastq(self, buf, file_offset=0):
+        a = np.ascontiguousarray(np.frombuffer(buf, dtype=np.uint8))
+        n = _U64(0)
+        _check(self._lib.kmi_sorted_build_fastq(self._h, _hptr(a), a.size, file_offset, ctypes.byref(n)))
+        return n.value
+
+    def build_fasta(self, buf):
+        a = np.ascontiguousarray(np.frombuffer(buf, dtype=np.uint8))
+        n = _U64(0)
+        _check(self._lib.kmi_sorted_build_fasta(self._h, _hptr(a), a.size, ctypes.byref(n)))
+        return n.value
+
+    def build_fastq_dev(self, dptr, nbytes, file_offset=0):
+        n = _U64(0)
+        _check(self._lib.kmi_sorted_build_fastq_dev(self._h, dptr, nbytes, file_offset, ctypes.byref(n)))
+        return n.value
+
+    def insert(self, keys, vals=None):
+        a = _as_keys(keys, self.nw)
+        v = np.ascontiguousarray(vals, dtype=np.uint64) if vals is not None else None
+        _check(self._lib.kmi_sorted_insert(self._h, _hptr(a), _hptr(v), a.shape[0]))
+
+    def rehash(self):
+        _check(self._lib.kmi_sorted_rehash(self._h))
+
+    def local_size(self):
+        n = _U64(0)
+        _check(self._lib.kmi_sorted_local_size(self._h, ctypes.byref(n)))
+        return n.value
+
+    def count(self, keys):
+        a = _as_keys(keys, self.nw)
+        out = np.zeros(a.shape[0], dtype=np.uint64)
+        _check(self._lib.kmi_sorted_count(self._h, _hptr(a), a.shape[0], _hptr(out)))
+        return out
+
+    def find(self, keys):
+        a = _as_keys(keys, self.nw)
+        vals = np.zeros(a.shape[0], dtype=np.uint64)
+        found = np.zeros(a.shape[0], dtype=np.uint8)
+        _check(self._lib.kmi_sorted_find(self._h, _hptr(a), a.shape[0], _hptr(vals), _hptr(found)))
+        return vals, found.astype(bool)
+
+    def find_positions(self, keys):
+        a = _as_keys(keys, self.nw)
+        n = a.shape[0]
+        cnt = self.count(keys)
+        total = int(cnt.sum())
+        off = np.zeros(n + 1, dtype=np.uint64)
+        vals = np.zeros(max(total, 1), dtype=np.uint64)
+        _check(self._lib.kmi_sorted_find_positions(self._h, _hptr(a), n, _hptr(off), _hptr(vals), max(total, 1)))
+        return off, vals[:total]
+
+    def dump(self):
+        """entries in key order (POSITION: (key, id) order)"""
+        n = self.local_size()
+        keys = np.zeros((n, 2) if self.nw == 2 else (n,), dtype=np.uint64)
+        vals = np.zeros(n, dtype=np.uint64)
+        got = _SZ(0)
+        _check(self._lib.kmi_sorted_dump(self._h, _hptr(keys), _hptr(vals), n, ctypes.byref(got)))
+        return keys[:got.value], vals[:got.value]
+
+    def stats(self):
+        ms = (ctypes.c_float * 3)()
+        n = _U64(0)
+        _check(self._lib.kmi_sorted_stats(self._h, ms, ctypes.byref(n)))
+        return [float(x) for x in ms], n.value
 
 
 def CountIndex(k=31, **kw):

@@ -191,7 +191,7 @@ extern "C" int kmi_create(const kmi_config* cfg, kmi_index** out) {
   *out = nullptr;
   if (cfg->k < 2 || cfg->k > 63 || cfg->k == 32) return fail(KMI_ERR_ARG, "k=%d needs >= 2 pad bits (k <= 31 or 33..63)", cfg->k);
   if (cfg->mode != KMI_MODE_COUNT && cfg->mode != KMI_MODE_POSITION) return fail(KMI_ERR_ARG, "bad mode %d", cfg->mode);
-  if (cfg->hash < 0 || cfg->hash > 2) return fail(KMI_ERR_ARG, "bad hash kind %d", cfg->hash);
+  if (cfg->hash < 0 || cfg->hash > 4) return fail(KMI_ERR_ARG, "bad hash kind %d", cfg->hash);
   if (cfg->nranks < 1 || cfg->nranks > MAX_RANKS || cfg->rank < 0 || cfg->rank >= cfg->nranks)
     return fail(KMI_ERR_ARG, "bad rank %d / nranks %d (max %d)", cfg->rank, cfg->nranks, MAX_RANKS);
   const Ops* ops = find_ops(cfg->k, cfg->hash);
@@ -263,6 +263,13 @@ extern "C" int kmi_set_param(kmi_index* idx, int param, int64_t value) {
     if (idx->cfg.mode != KMI_MODE_COUNT) return fail(KMI_ERR_ARG, "saturating counts belong to a COUNT index");
     idx->saturate = value != 0;
     if (idx->saturate) idx->build_path = 1;              // the shared-memory segment insert adds with plain wrap-around
+    return KMI_OK;
+  }
+  if (param == KMI_PARAM_DIST_TRANS) {
+    if (value < 0 || value > 2) return fail(KMI_ERR_ARG, "dist transform must be 0 (identity), 1 (lex_less) or 2 (xor_rev_comp)");
+    if (idx->cfg.canonical && value == 2)
+      return fail(KMI_ERR_ARG, "a canonical index distributes its lex_less keys as they are (CanonicalHashMapParams fixes DistTrans)");
+    idx->dist_trans = (u32)value;
     return KMI_OK;
   }
   return fail(KMI_ERR_ARG, "unknown parameter %d", param);
@@ -1257,7 +1264,7 @@ extern "C" int kmi_hash_dev(kmi_index* idx, int which, const uint64_t* d_keys, u
   if (!idx || ((!d_keys || !d_hash) && n)) return fail(KMI_ERR_ARG, "null argument");
   if (which != 0 && which != 1) return fail(KMI_ERR_ARG, "which must be 0 (store) or 1 (dist)");
   CU(cudaSetDevice(idx->cfg.device));
-  idx->ops->hash_keys(idx->stream, which, reinterpret_cast<const u64*>(d_keys), reinterpret_cast<u64*>(d_hash), n);
+  idx->ops->hash_keys(idx->stream, which, reinterpret_cast<const u64*>(d_keys), reinterpret_cast<u64*>(d_hash), n, (u32)idx->cfg.nranks);
   idx->launches++;
   return KMI_OK;
 }
@@ -1275,12 +1282,12 @@ extern "C" int kmi_partition_dev(kmi_index* idx, const uint64_t* d_keys, const u
   u64 n_blocks = (n_hist + 1023) / 1024;
   OK(idx->hist.ensure(sizeof(u32) * (n_hist + 1)));
   OK(idx->hist_sums.ensure(sizeof(u32) * (n_blocks + 1)));
-  idx->ops->part_hist(idx->stream, reinterpret_cast<const u64*>(d_keys), n, p, idx->hist.as<u32>(), n_chunks);
+  idx->ops->part_hist(idx->stream, reinterpret_cast<const u64*>(d_keys), n, p, idx->hist.as<u32>(), n_chunks, idx->dist_trans);
   k_scan_l1<<<(unsigned)n_blocks, 1024, 0, idx->stream>>>(idx->hist.as<u32>(), n_hist, idx->hist_sums.as<u32>());
   k_scan_tiles<<<1, 1024, 0, idx->stream>>>(idx->hist_sums.as<u32>(), n_blocks);
   idx->ops->part_scatter(idx->stream, reinterpret_cast<const u64*>(d_keys), reinterpret_cast<const u64*>(d_vals), n, p,
                          idx->hist.as<u32>(), idx->hist_sums.as<u32>(), n_chunks, reinterpret_cast<u64*>(d_keys_out),
-                         reinterpret_cast<u64*>(d_vals_out));
+                         reinterpret_cast<u64*>(d_vals_out), idx->dist_trans);
   idx->launches += 4;
   // owner r starts at scanned[r * n_chunks]: read the p starts back
   std::vector<u32> starts(p), sums(p);
@@ -1360,11 +1367,11 @@ extern "C" int kmi_partition_noalloc_dev(kmi_index* idx, const uint64_t* d_keys,
     return KMI_OK;
   }
   const u64 n_blocks = (n_hist + 1023) / 1024;
-  idx->ops->part_hist(idx->stream, reinterpret_cast<const u64*>(d_keys), n, p, hist, n_chunks);
+  idx->ops->part_hist(idx->stream, reinterpret_cast<const u64*>(d_keys), n, p, hist, n_chunks, idx->dist_trans);
   k_scan_l1<<<(unsigned)n_blocks, 1024, 0, idx->stream>>>(hist, n_hist, sums);
   k_scan_tiles<<<1, 1024, 0, idx->stream>>>(sums, n_blocks);
   idx->ops->part_scatter(idx->stream, reinterpret_cast<const u64*>(d_keys), reinterpret_cast<const u64*>(d_vals), n, p, hist, sums, n_chunks,
-                         reinterpret_cast<u64*>(d_keys_out), reinterpret_cast<u64*>(d_vals_out));
+                         reinterpret_cast<u64*>(d_keys_out), reinterpret_cast<u64*>(d_vals_out), idx->dist_trans);
   k_part_counts<<<(p + 255) / 256, 256, 0, idx->stream>>>(hist, sums, n_chunks, p, n, reinterpret_cast<u64*>(d_counts));
   CU(cudaGetLastError());
   idx->launches += 5;
@@ -1893,13 +1900,7 @@ extern "C" int kmi_save(kmi_index* idx, const char* path) {
   OK(kmi_local_size(idx, &n));
   const size_t nw = (size_t)idx->nw;
   std::vector<uint64_t> keys(n * nw + 1), vals(n + 1);
-  OK(kmi_dump(idx, keys.data(), vals.data(), n, &got));
-  std::vector<uint64_t> order(got);
-  for (uint64_t i = 0; i < got; ++i) order[i] = i;
-  std::sort(order.begin(), order.end(), [&](uint64_t a, uint64_t b) {
-    for (size_t w = nw; w-- > 0;) if (keys[a * nw + w] != keys[b * nw + w]) return keys[a * nw + w] < keys[b * nw + w];
-    return vals[a] < vals[b];
-  });
+  OK(kmi_dump_sorted(idx, keys.data(), vals.data(), n, &got));   // (key, value) order from the device radix sort (kmi_sorted.cu)
   FileGuard g{fopen(path, "wb")};
   if (!g.f) return fail(KMI_ERR_ARG, "cannot create %s", path);
   KmiFileHeader h;
@@ -1909,17 +1910,8 @@ extern "C" int kmi_save(kmi_index* idx, const char* path) {
   h.n_entries = got;
   h.hash = (uint32_t)idx->cfg.hash; h.rank = (uint32_t)idx->cfg.rank; h.nranks = (uint32_t)idx->cfg.nranks; h.flags = 1u;
   bool ok = fwrite(&h, sizeof(h), 1, g.f) == 1;
-  std::vector<uint64_t> out(1u << 16);
-  for (uint64_t i = 0; ok && i < got;) {            // keys, then values, in sorted order
-    size_t m = 0;
-    for (; i < got && m + nw <= out.size(); ++i) for (size_t w = 0; w < nw; ++w) out[m++] = keys[order[i] * nw + w];
-    ok = fwrite(out.data(), 8, m, g.f) == m;
-  }
-  for (uint64_t i = 0; ok && i < got;) {
-    size_t m = 0;
-    for (; i < got && m < out.size(); ++i) out[m++] = vals[order[i]];
-    ok = fwrite(out.data(), 8, m, g.f) == m;
-  }
+  if (ok && got) ok = fwrite(keys.data(), 8, got * nw, g.f) == got * nw;   // keys, then values, in sorted order
+  if (ok && got) ok = fwrite(vals.data(), 8, got, g.f) == got;
   if (!ok) return fail(KMI_ERR_ARG, "write error on %s", path);
   return KMI_OK;
 }

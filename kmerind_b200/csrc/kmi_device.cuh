@@ -136,14 +136,42 @@ __device__ __forceinline__ u64 farm_finish(u64 h0to16, u64 seed, bool tweak) {
   return h;
 }
 
-// HASH: 0 murmur, 1 farm (NDEBUG), 2 farm with DebugTweak. Returns store and dist hash together
+// HASH: 0 murmur, 1 farm (NDEBUG), 2 farm with DebugTweak, 3 identity, 4 cpp_std. Returns store and dist hash together
 // (murmur: one evaluation gives both halves; farm: the seed only enters the last mixing step).
-template <int K, int HASH> __device__ __forceinline__ void kmer_hashes(const Key<(K <= 32 ? 1 : 2)>& x, u64& store, u64& dist) {
+// identity / cpp_std (reference src/index/kmer_hash.hpp:157-232) take the number of prefix bits the reference's KeyToRank
+// constructs its DistHash with, ceilLog2(comm_size) (distributed_densehash_map.hpp:153-156): `pbits`.
+//   identity: store = Kmer::getSuffix(min(nBits, 64)) (kmer.hpp:1245-1249), dist = Kmer::getPrefix(min(nBits, pbits)):
+//             the top bits of the most significant word, below the pad (kmer.hpp:1203-1210).
+//   cpp_std:  h = XOR over the words of (std::hash<size_t>(word) << 1) — libstdc++'s std::hash<size_t> is the identity —
+//             store = h, dist = h >> (min(nBits, 64) - min(pbits, nBits)).
+__host__ __device__ __forceinline__ u32 ceil_log2_u32(u32 p) {
+  u32 b = 0;
+  while ((1ull << b) < (u64)p) ++b;
+  return b;
+}
+template <int K, int HASH> __device__ __forceinline__ void kmer_hashes(const Key<(K <= 32 ? 1 : 2)>& x, u64& store, u64& dist,
+                                                                       const u32 pbits = 0) {
   constexpr int NW = (K <= 32 ? 1 : 2);
   constexpr int NB = (2 * K + 7) / 8;
+  constexpr u32 NBITS = 2u * K, PAD = 64u * NW - NBITS;
   u64 lo = x.w[0], hi = (NW == 2) ? x.w[NW - 1] : 0;
   if (HASH == 0) {
     murmur3_128<NB>(lo, hi, store, dist);
+  } else if (HASH == 3) {
+    const u32 bits = pbits < NBITS ? pbits : NBITS;
+    store = (NW == 1 && NBITS < 64) ? (lo & ((1ull << (NBITS & 63)) - 1ull)) : lo;
+    if (!bits) dist = 0ull;
+    else if (PAD + bits <= 64u) dist = x.w[NW - 1] >> (64u - bits - PAD);
+    else {                                                    // prefix longer than the top word's used bits (two-word keys)
+      const u32 sh = NBITS - bits;                            // 0 < sh < 64
+      dist = ((lo >> sh) | (hi << (64u - sh))) & (bits >= 64u ? ~0ull : ((1ull << bits) - 1ull));
+    }
+  } else if (HASH == 4) {
+    u64 h = lo << 1;
+    if (NW == 2) h ^= hi << 1;
+    const u32 nb64 = NBITS < 64u ? NBITS : 64u, bits = pbits < NBITS ? pbits : NBITS;
+    store = h;
+    dist = (nb64 - bits) >= 64u ? 0ull : (h >> (nb64 - bits));
   } else {
     u64 h = farm_len0to16<NB>(lo, hi);
     store = farm_finish(h, 42, HASH == 2);
@@ -151,11 +179,9 @@ template <int K, int HASH> __device__ __forceinline__ void kmer_hashes(const Key
   }
 }
 template <int K, int HASH> __device__ __forceinline__ u64 store_hash(const Key<(K <= 32 ? 1 : 2)>& x) {
-  constexpr int NW = (K <= 32 ? 1 : 2);
-  constexpr int NB = (2 * K + 7) / 8;
-  u64 lo = x.w[0], hi = (NW == 2) ? x.w[NW - 1] : 0;
-  if (HASH == 0) { u64 a, b; murmur3_128<NB>(lo, hi, a, b); return a; }
-  return farm_finish(farm_len0to16<NB>(lo, hi), 42, HASH == 2);
+  u64 s, d;
+  kmer_hashes<K, HASH>(x, s, d);
+  return s;
 }
 
 // 16-byte asynchronous global -> shared copy (LDGSTS), bypassing L1

@@ -827,7 +827,7 @@ int dist_build_fastq(kmi_index* idx, uint8_t* d_text, size_t n, const uint8_t* h
   const bool count_mode = idx->cfg.mode == KMI_MODE_COUNT;
   const char* force = getenv("KMI_DIST_PUSH");
   const bool big = n_max >= AUTO_BUCKET_BYTES || (force && force[0] == '1');
-  bool use_push = count_mode && d->peer_ok && big && !idx->saturate;   // (saturating counts add with direct atomics)
+  bool use_push = count_mode && d->peer_ok && big && !idx->saturate && idx->ops->owner_push != nullptr && idx->dist_trans == 0;   // (saturating counts add with direct atomics)
   if (use_push) {
     bool redo = false;
     int r = build_fastq_push(idx, d_text, n, host_src, n_max, &total, &redo);

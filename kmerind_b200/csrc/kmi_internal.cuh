@@ -81,6 +81,7 @@ struct kmi_index {
   int seg_path = 1;        // KMI_PARAM_SEGMENT_INSERT: 1 = shared-memory segment insert where possible, 0 = L2 atomics
   bool hll_ready = false;
   kmi::u64 non_hll_upper = 0;   // keys inserted by paths that do not feed the HLL (upper bound on their distinct keys)
+  kmi::u32 dist_trans = 0; // KMI_PARAM_DIST_TRANS: transform under the dist hash of a non-canonical index (0 iden, 1 lex_less, 2 xor)
   bool saturate = false;   // KMI_PARAM_SATURATE: counts stick at 2^32 - 1; such an index builds with direct atomics (table_add)
   int build_path = 0;      // kmi_param KMI_PARAM_BUILD_PATH: 0 auto, 1 direct atomics, 2 bucketed
   // accounting
@@ -134,5 +135,8 @@ int fastq_scan_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64 t0, u
 int bucket_prepare(kmi_index* idx, u64 max_keys, BucketSink* bs);
 int fastq_scan(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64* n_tiles_out);
 void harvest_commit_times(kmi_index* idx);
+// kmi_sorted.cu: stable LSD radix sort of (key, value) pairs; keys/vals ping-pong with their *_tmp twins (see there)
+int device_sort_pairs(cudaStream_t st, DevBuf& hist, DevBuf& sums, u64*& keys, u64*& vals, u64*& keys_tmp, u64*& vals_tmp, u64 n,
+                      int nw, int key_bits, int val_bits, u64* launches);
 }  // namespace kmi
 void kmi_dist_release(kmi_index* idx);   // kmi_dist.cu: frees idx->dist

@@ -171,11 +171,11 @@ template <int K> __global__ void __launch_bounds__(256) k_canonicalize(const u64
   for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x)
     store_key<NW>(out, i, canonical<K>(load_key<NW>(in, i)));
 }
-template <int K, int HASH> __global__ void __launch_bounds__(256) k_hash(int which, const u64* __restrict__ in, u64* __restrict__ out, u64 n) {
+template <int K, int HASH> __global__ void __launch_bounds__(256) k_hash(int which, const u64* __restrict__ in, u64* __restrict__ out, u64 n, const u32 pbits) {
   constexpr int NW = (K <= 32 ? 1 : 2);
   for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
     u64 s, d;
-    kmer_hashes<K, HASH>(load_key<NW>(in, i), s, d);
+    kmer_hashes<K, HASH>(load_key<NW>(in, i), s, d, pbits);
     out[i] = which ? d : s;
   }
 }
@@ -189,16 +189,30 @@ static constexpr int PART_ROUNDS = 8;
 static constexpr int PART_ITEMS = PART_THREADS * PART_ROUNDS;
 static constexpr int MAX_RANKS = 256;
 
+// `trans` = the DistTrans of the reference's map parameters (SingleStrandHashMapParams<Key, DistHash, StoreHash, DistTrans>,
+// kmer_index.hpp; BenchmarkKmerIndex.cpp:152-161): 0 identity, 1 lex_less, 2 xor_rev_comp (x ^ rc(x),
+// kmer_transform.hpp:91-107) — applied to the key for the OWNER computation only; the key itself travels unchanged.
+// (A canonical index has lex_less keys already, and lex_less of a canonical key is itself.)
 template <int K, int HASH>
-__device__ __forceinline__ u32 owner_of(const Key<(K <= 32 ? 1 : 2)>& key, u32 p) {
+__device__ __forceinline__ u32 owner_of(const Key<(K <= 32 ? 1 : 2)>& key, u32 p, u32 trans = 0) {
+  constexpr int NW = (K <= 32 ? 1 : 2);
+  Key<NW> x = key;
+  if (trans) {
+    const Key<NW> rc = revcomp<K>(key);
+    if (trans == 1) { if (!key_less<NW>(key, rc)) x = rc; }
+    else {
+#pragma unroll
+      for (int w = 0; w < NW; ++w) x.w[w] = key.w[w] ^ rc.w[w];
+    }
+  }
   u64 s, d;
-  kmer_hashes<K, HASH>(key, s, d);
+  kmer_hashes<K, HASH>(x, s, d, HASH >= 3 ? ceil_log2_u32(p) : 0u);
   return mod_ranks(d, p);
 }
 
 template <int K, int HASH>
 __global__ void __launch_bounds__(PART_THREADS)
-k_part_hist(const u64* __restrict__ keys, u64 n, u32 p, u32* __restrict__ hist, u64 n_chunks) {
+k_part_hist(const u64* __restrict__ keys, u64 n, u32 p, u32* __restrict__ hist, u64 n_chunks, const u32 trans) {
   constexpr int NW = (K <= 32 ? 1 : 2);
   __shared__ u32 h[MAX_RANKS];
   for (u32 r = threadIdx.x; r < p; r += PART_THREADS) h[r] = 0;
@@ -206,7 +220,7 @@ k_part_hist(const u64* __restrict__ keys, u64 n, u32 p, u32* __restrict__ hist, 
   const u64 base = (u64)blockIdx.x * PART_ITEMS;
   for (int rd = 0; rd < PART_ROUNDS; ++rd) {
     u64 i = base + (u64)rd * PART_THREADS + threadIdx.x;
-    if (i < n) atomicAdd(&h[owner_of<K, HASH>(load_key<NW>(keys, i), p)], 1u);
+    if (i < n) atomicAdd(&h[owner_of<K, HASH>(load_key<NW>(keys, i), p, trans)], 1u);
   }
   __syncthreads();
   for (u32 r = threadIdx.x; r < p; r += PART_THREADS) hist[(u64)r * n_chunks + blockIdx.x] = h[r];
@@ -216,7 +230,7 @@ template <int K, int HASH>
 __global__ void __launch_bounds__(PART_THREADS)
 k_part_scatter(const u64* __restrict__ keys, const u64* __restrict__ vals, u64 n, u32 p,
                const u32* __restrict__ hist_scanned, const u32* __restrict__ hist_block_sums, u64 n_chunks,
-               u64* __restrict__ keys_out, u64* __restrict__ vals_out) {
+               u64* __restrict__ keys_out, u64* __restrict__ vals_out, const u32 trans) {
   constexpr int NW = (K <= 32 ? 1 : 2);
   constexpr int NWARPS = PART_THREADS / 32;
   __shared__ u32 run[MAX_RANKS];              // next free offset per owner for this chunk
@@ -234,7 +248,7 @@ k_part_scatter(const u64* __restrict__ keys, const u64* __restrict__ vals, u64 n
     bool ok = i < n;
     Key<NW> key;
     u32 own = 0xFFFFFFFFu;
-    if (ok) { key = load_key<NW>(keys, i); own = owner_of<K, HASH>(key, p); }
+    if (ok) { key = load_key<NW>(keys, i); own = owner_of<K, HASH>(key, p, trans); }
     u32 peers = __match_any_sync(0xffffffffu, own);
     u32 rank_in_warp = __popc(peers & ((1u << lane) - 1));
     if (ok && rank_in_warp == 0) wcnt[warp][own] = __popc(peers);

@@ -38,10 +38,10 @@ struct Ops {
   void (*erase_if)(cudaStream_t, void* slots, u64 n_slots, u64* size, u64* removed, int op, u64 x);
   void (*checksum)(cudaStream_t, const void* slots, u64 n_slots, u64* out2);
   void (*canonicalize)(cudaStream_t, const u64* in, u64* out, u64 n);
-  void (*hash_keys)(cudaStream_t, int which, const u64* in, u64* out, u64 n);
-  void (*part_hist)(cudaStream_t, const u64* keys, u64 n, u32 p, u32* hist, u64 n_chunks);
+  void (*hash_keys)(cudaStream_t, int which, const u64* in, u64* out, u64 n, u32 nranks);
+  void (*part_hist)(cudaStream_t, const u64* keys, u64 n, u32 p, u32* hist, u64 n_chunks, u32 dist_trans);
   void (*part_scatter)(cudaStream_t, const u64* keys, const u64* vals, u64 n, u32 p, const u32* hist_scanned,
-                       const u32* hist_block_sums, u64 n_chunks, u64* keys_out, u64* vals_out);
+                       const u32* hist_block_sums, u64 n_chunks, u64* keys_out, u64* vals_out, u32 dist_trans);
   void (*csr_scan_l1)(cudaStream_t, const void* slots, u64 n_slots, u64* offsets, u64* block_sums);
   void (*csr_fill)(cudaStream_t, TableView, const u64* keys, const u64* ids, u64 n, const u64* offsets, u64* values);
   void (*log_filter)(cudaStream_t, TableView, const u64* keys, const u64* ids, u64 n, u64* keys_out, u64* ids_out,
@@ -164,17 +164,17 @@ struct OpsImpl {
   static void canonicalize(cudaStream_t st, const u64* in, u64* out, u64 n) {
     if (n) k_canonicalize<K><<<grid_for(n, 256), 256, 0, st>>>(in, out, n);
   }
-  static void hash_keys(cudaStream_t st, int which, const u64* in, u64* out, u64 n) {
-    if (n) k_hash<K, HASH><<<grid_for(n, 256), 256, 0, st>>>(which, in, out, n);
+  static void hash_keys(cudaStream_t st, int which, const u64* in, u64* out, u64 n, u32 nranks) {
+    if (n) k_hash<K, HASH><<<grid_for(n, 256), 256, 0, st>>>(which, in, out, n, ceil_log2_u32(nranks ? nranks : 1u));
   }
-  static void part_hist(cudaStream_t st, const u64* keys, u64 n, u32 p, u32* hist, u64 n_chunks) {
-    if (n_chunks) k_part_hist<K, HASH><<<(unsigned)n_chunks, PART_THREADS, 0, st>>>(keys, n, p, hist, n_chunks);
+  static void part_hist(cudaStream_t st, const u64* keys, u64 n, u32 p, u32* hist, u64 n_chunks, u32 dist_trans) {
+    if (n_chunks) k_part_hist<K, HASH><<<(unsigned)n_chunks, PART_THREADS, 0, st>>>(keys, n, p, hist, n_chunks, dist_trans);
   }
   static void part_scatter(cudaStream_t st, const u64* keys, const u64* vals, u64 n, u32 p, const u32* hist_scanned,
-                           const u32* hist_block_sums, u64 n_chunks, u64* keys_out, u64* vals_out) {
+                           const u32* hist_block_sums, u64 n_chunks, u64* keys_out, u64* vals_out, u32 dist_trans) {
     if (n_chunks)
       k_part_scatter<K, HASH><<<(unsigned)n_chunks, PART_THREADS, 0, st>>>(keys, vals, n, p, hist_scanned, hist_block_sums,
-                                                                          n_chunks, keys_out, vals_out);
+                                                                          n_chunks, keys_out, vals_out, dist_trans);
   }
   static void csr_scan_l1(cudaStream_t st, const void* slots, u64 n_slots, u64* offsets, u64* block_sums) {
     k_csr_scan_l1<NW><<<(unsigned)((n_slots + 1023) / 1024), 1024, 0, st>>>(reinterpret_cast<const S*>(slots), n_slots,
@@ -198,6 +198,17 @@ struct OpsImpl {
     o.lookup = lookup; o.erase = erase; o.dump = dump; o.erase_if = erase_if; o.checksum = checksum; o.canonicalize = canonicalize;
     o.hash_keys = hash_keys; o.part_hist = part_hist; o.part_scatter = part_scatter; o.csr_scan_l1 = csr_scan_l1;
     o.csr_fill = csr_fill; o.log_filter = log_filter; o.zero_aux = zero_aux;
+    return o;
+  }
+  // The hash kind only enters the kernels that evaluate the DIST hash (kmi_hash_dev, the partition by owner, the NVLink
+  // push): the identity / cpp_std flavours reuse every other launcher of this instantiation and swap those in. They get no
+  // owner_push — a prefix of the key as the owner is far too skewed for fixed-capacity receive regions, so their sharded
+  // builds take the partition + all-to-all path.
+  template <int H2> static Ops make_with_dist_hash() {
+    Ops o = make();
+    o.hash = H2;
+    o.hash_keys = OpsImpl<K, H2>::hash_keys; o.part_hist = OpsImpl<K, H2>::part_hist; o.part_scatter = OpsImpl<K, H2>::part_scatter;
+    o.owner_push = nullptr;
     return o;
   }
 };

@@ -13,7 +13,9 @@ const Ops* KMI_CAT(kmi_ops_k, KMI_K)(int hash) {
   static const Ops murmur = OpsImpl<KMI_K, 0>::make();
   static const Ops farm = OpsImpl<KMI_K, 1>::make();
   static const Ops farm_dbg = OpsImpl<KMI_K, 2>::make();
-  return hash == 0 ? &murmur : hash == 1 ? &farm : hash == 2 ? &farm_dbg : nullptr;
+  static const Ops iden = OpsImpl<KMI_K, 0>::make_with_dist_hash<3>();
+  static const Ops cppstd = OpsImpl<KMI_K, 0>::make_with_dist_hash<4>();
+  return hash == 0 ? &murmur : hash == 1 ? &farm : hash == 2 ? &farm_dbg : hash == 3 ? &iden : hash == 4 ? &cppstd : nullptr;
 }
 }  // namespace kmi
 

@@ -183,6 +183,39 @@ void kmio_hash(int K, int which, const uint64_t* in, uint64_t* out, size_t n) {
     }
   }
 }
+/* f3: the identity and cpp_std flavours (src/index/kmer_hash.hpp:157-232), built the way KeyToRank builds its DistHash:
+ * prefix bits = ceilLog2(comm_size) (distributed_densehash_map.hpp:153-156).
+ * kind 0 identity store = Kmer::getSuffix(min(nBits,64)) (kmer.hpp:1245-1249: data[0] masked to the low bits);
+ *      1 identity dist  = Kmer::getPrefix(min(nBits,pbits)) (kmer.hpp:1203-1221: top word >> (64 - bits - padBits), or,
+ *        when the prefix is longer than the top word's used bits, the whole k-mer >> (nBits - bits), low `bits` bits);
+ *      2 cpp_std store  = XOR over the 64-bit words of (std::hash<size_t>(w) << 1), std::hash<size_t> = identity (libstdc++);
+ *      3 cpp_std dist   = that >> (min(nBits,64) - min(pbits,nBits)) (kmer_hash.hpp:170,196-199). */
+void kmio_hash_prefix(int K, int kind, unsigned pbits, const uint64_t* in, uint64_t* out, size_t n) {
+  int nw = kmio_nwords(K);
+  unsigned nbits = 2u * (unsigned)K, pad = 64u * (unsigned)nw - nbits;
+  unsigned bits = pbits < nbits ? pbits : nbits;
+  for (size_t i = 0; i < n; ++i) {
+    const uint64_t* w = in + i * nw;
+    if (kind == 0) {
+      out[i] = (nw == 1 && nbits < 64) ? (w[0] & ((1ULL << nbits) - 1ULL)) : w[0];
+    } else if (kind == 1) {
+      if (!bits) out[i] = 0ULL;
+      else if (pad + bits <= 64u) out[i] = w[nw - 1] >> (64u - bits - pad);
+      else {                                      /* the prefix runs into the low word: shift right by nBits - bits, keep `bits` bits */
+        unsigned sh = nbits - bits;               /* 0 < sh < 64 */
+        out[i] = ((w[0] >> sh) | (w[1] << (64u - sh))) & (bits >= 64u ? ~0ULL : ((1ULL << bits) - 1ULL));
+      }
+    } else {
+      uint64_t h = 0;
+      for (int j = 0; j < nw; ++j) h ^= (w[j] << 1);
+      if (kind == 3) {
+        unsigned sh = (nbits < 64u ? nbits : 64u) - bits;
+        h = sh >= 64u ? 0ULL : (h >> sh);   /* the reference's shift by 64 is undefined; only reachable at p = 1, owner 0 */
+      }
+      out[i] = h;
+    }
+  }
+}
 /* a13: KeyToRank, src/containers/distributed_densehash_map.hpp:148-170: dist_hash % p */
 void kmio_owner(const uint64_t* dist_hash, size_t n, uint32_t p, uint32_t* out) {
   for (size_t i = 0; i < n; ++i) out[i] = (uint32_t)(dist_hash[i] % p);

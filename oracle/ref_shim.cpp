@@ -127,6 +127,16 @@ struct Ops {
       out[i] = which == 0 ? ms(km) : which == 1 ? md(km) : which == 2 ? fs(km) : fd(km);
     }
   }
+  // the two remaining hash flavours of the benchmark matrix (kmer_hash.hpp:157-232), constructed the way KeyToRank does
+  // (prefix bits = ceilLog2(comm_size)): kind 0 identity store, 1 identity dist, 2 cpp_std store, 3 cpp_std dist
+  static void hash_prefix(int kind, unsigned pbits, const uint64_t* in, uint64_t* out, size_t n) {
+    bliss::kmer::hash::identity<Kmer, false> is;  bliss::kmer::hash::identity<Kmer, true> id(pbits);
+    bliss::kmer::hash::cpp_std<Kmer, false> ss;   bliss::kmer::hash::cpp_std<Kmer, true> sd(pbits);
+    for (size_t i = 0; i < n; ++i) {
+      Kmer km; std::memcpy(km.getDataRef(), in + i * NW, NW * 8);
+      out[i] = kind == 0 ? is(km) : kind == 1 ? id(km) : kind == 2 ? ss(km) : sd(km);
+    }
+  }
   static void sentinels(uint64_t* out) {
     bliss::kmer::hash::sparsehash::special_keys<Kmer, true> sk;
     Kmer e = sk.generate(0), d = sk.generate(1);
@@ -315,6 +325,7 @@ size_t kmiref_windows(int K, const uint8_t* s, size_t n, uint64_t* out) { DISPAT
 void kmiref_revcomp(int K, const uint64_t* in, uint64_t* out, size_t n) { DISPATCH(K, revcomp(in, out, n), (void)0) }
 void kmiref_canonical(int K, const uint64_t* in, uint64_t* out, size_t n) { DISPATCH(K, canonical(in, out, n), (void)0) }
 void kmiref_hash(int K, int which, const uint64_t* in, uint64_t* out, size_t n) { DISPATCH(K, hash(which, in, out, n), (void)0) }
+void kmiref_hash_prefix(int K, int kind, unsigned pbits, const uint64_t* in, uint64_t* out, size_t n) { DISPATCH(K, hash_prefix(kind, pbits, in, out, n), (void)0) }
 void kmiref_sentinels(int K, uint64_t* out) { DISPATCH(K, sentinels(out), (void)0) }
 size_t kmiref_count_build(int K, const uint8_t* seqs, const uint64_t* off, size_t nseq, int p, int hash_kind,
                           uint64_t* out_keys, uint32_t* out_counts, size_t cap, uint64_t* per_rank_sizes) {

@@ -34,6 +34,7 @@ def oracle():
         lib.kmio_canonical.argtypes = [ctypes.c_int, _P, _P, _SZ]
         lib.kmio_hash.argtypes = [ctypes.c_int, ctypes.c_int, _P, _P, _SZ]
         lib.kmio_owner.argtypes = [_P, _SZ, ctypes.c_uint32, _P]
+        lib.kmio_hash_prefix.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_uint, _P, _P, _SZ]
         lib.kmio_fastq_find_first_record.argtypes = [_P, _U64, _SZ, _U64, _U64, _U64, _U64, _P]
         lib.kmio_count_sorted.restype = _SZ
         lib.kmio_count_sorted.argtypes = [ctypes.c_int, _P, _SZ, _P]
@@ -61,6 +62,8 @@ def ref_lib(flavour="ndebug"):
     lib.kmiref_canonical.argtypes = [ctypes.c_int, _P, _P, _SZ]
     lib.kmiref_hash.argtypes = [ctypes.c_int, ctypes.c_int, _P, _P, _SZ]
     lib.kmiref_sentinels.argtypes = [ctypes.c_int, _P]
+    if hasattr(lib, "kmiref_hash_prefix"):
+        lib.kmiref_hash_prefix.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_uint, _P, _P, _SZ]
     lib.kmiref_count_build.restype = _SZ
     lib.kmiref_count_build.argtypes = [ctypes.c_int, _P, _P, _SZ, ctypes.c_int, ctypes.c_int, _P, _P, _SZ, _P]
     lib.kmiref_count_build_fastq.restype = _SZ
@@ -204,6 +207,22 @@ def hashes(keys, k, which):
     n = a.size // nwords(k)
     out = np.zeros(n, dtype=np.uint64)
     oracle().kmio_hash(k, which, _ptr(a), _ptr(out), n)
+    return out
+
+
+def ceil_log2(p):
+    b = 0
+    while (1 << b) < p:
+        b += 1
+    return b
+
+
+def hashes_prefix(keys, k, hash_kind, dist, nranks=1):
+    """identity (hash_kind 3) / cpp_std (4) flavours; the dist hash is built with ceilLog2(nranks) prefix bits, as KeyToRank does."""
+    a = np.ascontiguousarray(keys, dtype=np.uint64)
+    n = a.size // nwords(k)
+    out = np.zeros(n, dtype=np.uint64)
+    oracle().kmio_hash_prefix(k, (hash_kind - 3) * 2 + (1 if dist else 0), ceil_log2(nranks), _ptr(a), _ptr(out), n)
     return out
 
 

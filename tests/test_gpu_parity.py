@@ -88,6 +88,44 @@ def test_hash_and_canonical_bit_exact(k, hash_kind):
             assert np.array_equal(h[:ng], want)  # values computed by the reference's own code
 
 
+@pytest.mark.parametrize("k", KS)
+@pytest.mark.parametrize("hash_kind", (kb.HASH_IDENTITY, kb.HASH_STD))
+def test_identity_and_std_hash_bit_exact(k, hash_kind):
+    """f3: the identity / cpp_std flavours (kmer_hash.hpp:157-232). The dist hash carries ceilLog2(nranks) prefix bits, as
+    KeyToRank builds it; values of the reference's own classes from tests/golden/ref_kat_hash2.json."""
+    kat2 = json.load(open(os.path.join(ou.ROOT, "tests", "golden", "ref_kat_hash2.json")))
+    nw = ou.nwords(k)
+    can_g = np.array([int(x, 16) for x in KAT["k"][str(k)]["canonical"]], dtype=np.uint64)
+    ng = can_g.size // nw
+    keys = np.concatenate([can_g, np.ascontiguousarray(ou.canonical(ou.random_keys(k, 100000, seed=3 * k), k)).reshape(-1)])
+    n = keys.size // nw
+    name = {kb.HASH_IDENTITY: "identity", kb.HASH_STD: "std"}[hash_kind]
+    for p in (1, 2, 3, 8, 64, 200):
+        with kb.Index(k=k, hash=hash_kind, nranks=p) as idx:
+            d_in = dev(keys)
+            for which in (0, 1):
+                if which == 1 and p == 1 and hash_kind == kb.HASH_STD and k > 32:
+                    continue   # the reference shifts a 64-bit word by 64 there (undefined); every key is rank 0's anyway
+                d_h = torch.zeros(n, dtype=torch.int64, device="cuda")
+                idx.hash_dev(which, d_in.data_ptr(), d_h.data_ptr(), n)
+                h = host_u64(d_h)
+                assert np.array_equal(h, ou.hashes_prefix(keys, k, hash_kind, which == 1, p)), (k, name, p, which)
+                if which == 0 or p in kat2["ranks"]:
+                    want = kat2["k"][str(k)][name + ("_store" if which == 0 else "_dist_p%d" % p)]
+                    assert np.array_equal(h[:ng], np.array([int(x, 16) for x in want], dtype=np.uint64))
+            if p > 1:   # KeyToRank with these flavours: stable partition by (prefix hash % p)
+                vals = np.arange(n, dtype=np.uint64)
+                dk, dv = dev(keys), dev(vals)
+                ok, ov = torch.zeros_like(dk), torch.zeros_like(dv)
+                counts = idx.partition_dev(dk.data_ptr(), dv.data_ptr(), n, ok.data_ptr(), ov.data_ptr(), p)
+                torch.cuda.synchronize()
+                owner = (ou.hashes_prefix(keys, k, hash_kind, True, p) % np.uint64(p)).astype(np.int64)
+                assert counts.tolist() == np.bincount(owner, minlength=p).tolist()
+                order = np.argsort(owner, kind="stable")
+                assert np.array_equal(host_u64(ov), vals[order])
+                assert np.array_equal(host_u64(ok).reshape(n, nw), keys.reshape(n, nw)[order])
+
+
 @pytest.mark.parametrize("name", FASTQ)
 @pytest.mark.parametrize("k", (15, 31, 35, 63))
 def test_fastq_parse_matches_oracle(name, k):
@@ -453,6 +491,38 @@ def test_partition_is_stable_and_by_owner(k, p):
             order = np.argsort(owner, kind="stable")  # imxx::distribute keeps the sender's order per bucket
             assert np.array_equal(host_u64(ov), vals[order])
             assert np.array_equal(host_u64(ok).reshape(n, nw), keys.reshape(n, nw)[order])
+
+
+@pytest.mark.parametrize("k", (21, 31, 63))
+def test_partition_dist_transform(k):
+    """f3: DistTrans of SingleStrandHashMapParams (BenchmarkKmerIndex.cpp:152-161): owner = dist_hash(T(key)) % p with
+    T = lex_less / xor_rev_comp (kmer_transform.hpp:91-126); the keys themselves travel as given, both strands to one rank."""
+    nw = ou.nwords(k)
+    p = 5
+    fw = np.ascontiguousarray(ou.random_keys(k, 50001, seed=77 + k)).reshape(-1)
+    keys = np.concatenate([fw, np.ascontiguousarray(ou.revcomp(fw, k)).reshape(-1)])   # every k-mer with its other strand
+    n = keys.size // nw
+    vals = np.arange(n, dtype=np.uint64)
+    rc = np.ascontiguousarray(ou.revcomp(keys, k)).reshape(-1)
+    hashed = {0: keys, 1: np.ascontiguousarray(ou.canonical(keys, k)).reshape(-1), 2: keys ^ rc}
+    with kb.Index(k=k, hash=kb.HASH_FARM, nranks=p, canonical=False) as idx:
+        for trans in (0, 1, 2, 0):
+            idx.set_dist_trans(trans)
+            dk, dv = dev(keys), dev(vals)
+            ok, ov = torch.zeros_like(dk), torch.zeros_like(dv)
+            counts = idx.partition_dev(dk.data_ptr(), dv.data_ptr(), n, ok.data_ptr(), ov.data_ptr(), p)
+            torch.cuda.synchronize()
+            owner = (ou.hashes(hashed[trans], k, ou.hash_which(kb.HASH_FARM, True)) % np.uint64(p)).astype(np.int64)
+            if trans:
+                assert np.array_equal(owner[:n // 2], owner[n // 2:])   # the two strands meet
+            assert counts.tolist() == np.bincount(owner, minlength=p).tolist()
+            order = np.argsort(owner, kind="stable")
+            assert np.array_equal(host_u64(ov), vals[order])
+            assert np.array_equal(host_u64(ok).reshape(n, nw), keys.reshape(n, nw)[order])
+    with kb.Index(k=k, hash=kb.HASH_FARM, nranks=p) as idx:   # canonical index: xor is refused, lex_less is a no-op
+        with pytest.raises(kb.KmiError):
+            idx.set_dist_trans(2)
+        idx.set_dist_trans(1)
 
 
 def test_synthetic_generator_matches_host_twin():

@@ -17,6 +17,7 @@ import oracle_util as ou
 
 KAT = json.load(open(os.path.join(ou.ROOT, "tests", "golden", "ref_kat.json")))
 KS = (15, 21, 31, 35, 47, 63)
+kb_hash_identity, kb_hash_std = 3, 4   # kmi_hash_kind (include/kmi.h)
 
 
 def unhex(lst, k):
@@ -241,3 +242,38 @@ def test_oracle_equals_reference_executed_vectors(e):
         rows = _rows(dk, dc, k)
     assert rows.shape[0] == e["rows"]
     assert hashlib.sha256(np.ascontiguousarray(rows).tobytes()).hexdigest() == e["sha256"]
+
+
+# ---- f3: identity / cpp_std hash flavours (reference src/index/kmer_hash.hpp:157-232) -----------------------------------------
+KAT2 = json.load(open(os.path.join(ou.ROOT, "tests", "golden", "ref_kat_hash2.json")))
+
+
+@pytest.mark.parametrize("k", KS)
+def test_identity_and_std_hash_match_reference_executed_vectors(k):
+    """The C oracle's restatement against values computed by the reference's own identity<> / cpp_std<> classes, built
+    with ceilLog2(p) prefix bits as KeyToRank builds them (tests/golden/make_golden_hash2.py)."""
+    can = np.array([int(x, 16) for x in KAT["k"][str(k)]["canonical"]], dtype=np.uint64)
+    e = KAT2["k"][str(k)]
+    for kind, name in ((kb_hash_identity, "identity"), (kb_hash_std, "std")):
+        want = np.array([int(x, 16) for x in e[name + "_store"]], dtype=np.uint64)
+        assert np.array_equal(ou.hashes_prefix(can, k, kind, False), want), (k, name)
+        for p in KAT2["ranks"]:
+            want = np.array([int(x, 16) for x in e["%s_dist_p%d" % (name, p)]], dtype=np.uint64)
+            assert np.array_equal(ou.hashes_prefix(can, k, kind, True, p), want), (k, name, p)
+            if name == "identity":
+                assert int(want.max()) < (1 << ou.ceil_log2(p))   # a prefix of ceilLog2(p) bits
+
+
+def test_identity_std_vs_live_reference():
+    ref = ou.ref_lib("ndebug")
+    if ref is None or not hasattr(ref, "kmiref_hash_prefix"):
+        pytest.skip("oracle/_ref not built")
+    for k in KS:
+        keys = np.ascontiguousarray(ou.canonical(ou.random_keys(k, 20000, seed=100 + k), k)).reshape(-1)
+        n = keys.size // ou.nwords(k)
+        for kind in (3, 4):
+            for dist, pbits_p in ((False, 1), (True, 2), (True, 5), (True, 8), (True, 256)):
+                got = ou.hashes_prefix(keys, k, kind, dist, pbits_p)
+                want = np.zeros(n, dtype=np.uint64)
+                ref.kmiref_hash_prefix(k, (kind - 3) * 2 + (1 if dist else 0), ou.ceil_log2(pbits_p), ou._ptr(keys), ou._ptr(want), n)
+                assert np.array_equal(got, want), (k, kind, dist, pbits_p)
