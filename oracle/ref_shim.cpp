@@ -17,6 +17,7 @@
 #include "common/kmer_transform.hpp"
 #include "common/alphabets.hpp"
 #include "index/kmer_hash.hpp"
+#include "index/quality_score_iterator.hpp"
 #include <sparsehash/dense_hash_map>
 
 using bliss::common::DNA;
@@ -136,6 +137,16 @@ struct Ops {
       Kmer km; std::memcpy(km.getDataRef(), in + i * NW, NW * 8);
       out[i] = kind == 0 ? is(km) : kind == 1 ? id(km) : kind == 2 ? ss(km) : sd(km);
     }
+  }
+  // f4: the reference's k-mer quality score (QualityScoreGenerationIterator over Illumina18QualityScoreCodec<float>,
+  // src/index/quality_score_iterator.hpp, quality_scores.hpp:529) of every K-window of one quality line
+  static size_t quality(const uint8_t* q, size_t n, float* out) {
+    if (n < K) return 0;
+    typedef const unsigned char* It;
+    bliss::index::QualityScoreGenerationIterator<It, K, bliss::index::Illumina18QualityScoreCodec<float> > it(q);
+    const size_t m = n - K + 1;
+    for (size_t i = 0; i < m; ++i, ++it) out[i] = *it;
+    return m;
   }
   static void sentinels(uint64_t* out) {
     bliss::kmer::hash::sparsehash::special_keys<Kmer, true> sk;
@@ -326,6 +337,10 @@ void kmiref_revcomp(int K, const uint64_t* in, uint64_t* out, size_t n) { DISPAT
 void kmiref_canonical(int K, const uint64_t* in, uint64_t* out, size_t n) { DISPATCH(K, canonical(in, out, n), (void)0) }
 void kmiref_hash(int K, int which, const uint64_t* in, uint64_t* out, size_t n) { DISPATCH(K, hash(which, in, out, n), (void)0) }
 void kmiref_hash_prefix(int K, int kind, unsigned pbits, const uint64_t* in, uint64_t* out, size_t n) { DISPATCH(K, hash_prefix(kind, pbits, in, out, n), (void)0) }
+size_t kmiref_quality(int K, const uint8_t* q, size_t n, float* out) { DISPATCH(K, quality(q, n, out), 0) }
+void kmiref_quality_lut(float* out96) {
+  for (int i = 0; i < 96; ++i) out96[i] = bliss::index::Illumina18QualityScoreCodec<float>::decode((unsigned char)(33 + i));
+}
 void kmiref_sentinels(int K, uint64_t* out) { DISPATCH(K, sentinels(out), (void)0) }
 size_t kmiref_count_build(int K, const uint8_t* seqs, const uint64_t* off, size_t nseq, int p, int hash_kind,
                           uint64_t* out_keys, uint32_t* out_counts, size_t cap, uint64_t* per_rank_sizes) {

@@ -97,7 +97,7 @@ def test_counting_sorted_map_wraps_like_uint32():
 
 
 @pytest.mark.parametrize("k,fasta,name", ((21, True, "test2.fasta"), (21, True, "test.medium.fasta"), (35, True, "test.fasta"),
-                                          (31, False, "natural.fastq"), (63, False, "natural.fastq")))
+                                          (31, False, "natural.fastq"), (63, False, "test.unitiq1.fastq")))
 def test_sorted_multimap_equals_oracle(k, fasta, name):
     buf = ou.read_fixture(name)
     if fasta:
@@ -111,6 +111,7 @@ def test_sorted_multimap_equals_oracle(k, fasta, name):
         gk, gi = sm.dump()
         assert np.array_equal(gk, sk) and np.array_equal(gi, si)
         nw = ou.nwords(k)
+        assert len(sk) > 0
         rows = sk.reshape(len(sk), -1)
         uk, first, cnt = np.unique(rows, axis=0, return_index=True, return_counts=True)
         if nw == 2:                                                  # np.unique sorts by column 0 (low word) first: re-derive from sk order
