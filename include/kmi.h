@@ -351,6 +351,33 @@ int kmi_sorted_stats(kmi_sorted* s, float* ms3, uint64_t* launches);
 int kmi_sort_pairs_dev(kmi_index* idx, uint64_t* d_keys, uint64_t* d_vals, uint64_t* d_keys_tmp, uint64_t* d_vals_tmp, size_t n,
                        int val_bits, int* sorted_in_tmp);
 
+/* ---- f4: PositionQualityIndex — k-mer -> (position id, quality score): Index<MapType, KmerPositionQualityTupleParser<...>>
+ * (kmer_index.hpp:406; src/io/kmer_parser.hpp:578-760) with the score of QualityScoreSlidingWindow over
+ * Illumina18QualityScoreCodec<float> (src/index/quality_score_iterator.hpp:60-140, quality_scores.hpp:60-170,529): Phred+33,
+ * per base log2(1 - 10^(-q/10)), per k-mer exp2 of the window's running float sum, 0 when a base of the window has a score
+ * outside 1..93. THE ONLY FLOATING-POINT PATH: the running sum is replayed in the reference's operation order (bit-identical
+ * float adds / subtracts), the final exp2f is the device's — tolerance 1e-6 relative (tests/test_quality.py).
+ * kmi_fastq_quality_dev is the stage: d_ids are the ShortSequenceKmerId values kmi_parse_fastq_dev produced over the same
+ * d_bytes / file_offset (any order); d_quals[i] receives the score of the k-mer d_ids[i] names. With cfg.nsplit the window
+ * restarts after every N, as the sub-sequences of NSplitSequencesIterator do. kmi_quality_lut returns the 96-entry table.
+ * kmi_posqual is the index (one shard): a POSITION-mode index over the same parser that also keeps every tuple's score. */
+int kmi_quality_lut(float* out96);
+int kmi_fastq_quality_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset, const uint64_t* d_ids, size_t n_ids,
+                          float* d_quals);
+typedef struct kmi_posqual kmi_posqual;
+int kmi_posqual_create(const kmi_config* cfg, kmi_posqual** out);
+void kmi_posqual_destroy(kmi_posqual* pq);
+int kmi_posqual_build_fastq(kmi_posqual* pq, const uint8_t* bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers);
+int kmi_posqual_build_fastq_dev(kmi_posqual* pq, const uint8_t* d_bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers);
+int kmi_posqual_local_size(kmi_posqual* pq, uint64_t* n);
+int kmi_posqual_count(kmi_posqual* pq, const uint64_t* keys, size_t n, uint64_t* counts);
+/* CSR answer like kmi_find_positions, with the score of every (k-mer, id) hit in quals */
+int kmi_posqual_find(kmi_posqual* pq, const uint64_t* keys, size_t n, uint64_t* offsets, uint64_t* ids, float* quals, size_t cap);
+int kmi_posqual_erase(kmi_posqual* pq, const uint64_t* keys, size_t n);
+/* to_vector(): one entry per stored tuple, unordered */
+int kmi_posqual_dump(kmi_posqual* pq, uint64_t* keys, uint64_t* ids, float* quals, size_t cap, size_t* n_out);
+int kmi_posqual_launch_count(kmi_posqual* pq, uint64_t* n);
+
 /* ---- synthetic workload (same bytes as oracle/kmi_oracle.c kmio_synth_fastq) - */
 size_t kmi_synth_record_bytes(uint32_t read_len);
 int kmi_synth_fastq_dev(int device, uint8_t* d_out, uint64_t first_read, uint64_t n_reads,

@@ -97,6 +97,12 @@ def load_library(build_if_missing=False):
         "kmi_erase_if": [_P, ctypes.c_int, _U64, _P], "kmi_table_info": [_P, _P, _P, _P], "kmi_launch_count": [_P, _P],
         "kmi_last_stage_ms": [_P, _P], "kmi_last_kernel_ms": [_P, _P],
         "kmi_dump_sorted": [_P, _P, _P, _SZ, _P],
+        "kmi_quality_lut": [_P], "kmi_fastq_quality_dev": [_P, _P, _SZ, _U64, _P, _SZ, _P],
+        "kmi_posqual_create": [ctypes.POINTER(KmiConfig), ctypes.POINTER(_P)],
+        "kmi_posqual_build_fastq": [_P, _P, _SZ, _U64, _P], "kmi_posqual_build_fastq_dev": [_P, _P, _SZ, _U64, _P],
+        "kmi_posqual_local_size": [_P, _P], "kmi_posqual_count": [_P, _P, _SZ, _P],
+        "kmi_posqual_find": [_P, _P, _SZ, _P, _P, _P, _SZ], "kmi_posqual_erase": [_P, _P, _SZ],
+        "kmi_posqual_dump": [_P, _P, _P, _P, _SZ, _P], "kmi_posqual_launch_count": [_P, _P],
         "kmi_sorted_create": [ctypes.POINTER(KmiConfig), ctypes.POINTER(_P)],
         "kmi_sorted_build_fastq": [_P, _P, _SZ, _U64, _P], "kmi_sorted_build_fasta": [_P, _P, _SZ, _P],
         "kmi_sorted_build_fastq_dev": [_P, _P, _SZ, _U64, _P], "kmi_sorted_build_fasta_dev": [_P, _P, _SZ, _P],
@@ -121,6 +127,8 @@ def load_library(build_if_missing=False):
     lib.kmi_comm_destroy.restype = None
     lib.kmi_sorted_destroy.argtypes = [_P]
     lib.kmi_sorted_destroy.restype = None
+    lib.kmi_posqual_destroy.argtypes = [_P]
+    lib.kmi_posqual_destroy.restype = None
     _lib = lib
     return lib
 
@@ -141,7 +149,9 @@ EXPORTED_SYMBOLS = (
     "kmi_dump_sorted", "kmi_sorted_create", "kmi_sorted_destroy", "kmi_sorted_build_fastq", "kmi_sorted_build_fasta",
     "kmi_sorted_build_fastq_dev", "kmi_sorted_build_fasta_dev", "kmi_sorted_insert", "kmi_sorted_insert_dev", "kmi_sorted_rehash",
     "kmi_sorted_local_size", "kmi_sorted_count", "kmi_sorted_find", "kmi_sorted_find_positions", "kmi_sorted_dump", "kmi_sorted_stats",
-    "kmi_sort_pairs_dev",
+    "kmi_sort_pairs_dev", "kmi_quality_lut", "kmi_fastq_quality_dev", "kmi_posqual_create", "kmi_posqual_destroy",
+    "kmi_posqual_build_fastq", "kmi_posqual_build_fastq_dev", "kmi_posqual_local_size", "kmi_posqual_count", "kmi_posqual_find",
+    "kmi_posqual_erase", "kmi_posqual_dump", "kmi_posqual_launch_count",
 )
 
 
@@ -318,6 +328,9 @@ class Index:
 
     def canonicalize_dev(self, d_in, d_out, n):
         _check(self._lib.kmi_canonicalize_dev(self._h, d_in, d_out, n))
+
+    def fastq_quality_dev(self, d_bytes, nbytes, file_offset, d_ids, n_ids, d_quals):
+        _check(self._lib.kmi_fastq_quality_dev(self._h, d_bytes, nbytes, file_offset, d_ids, n_ids, d_quals))
 
     def hash_dev(self, which, d_keys, d_out, n):
         _check(self._lib.kmi_hash_dev(self._h, which, d_keys, d_out, n))
@@ -580,6 +593,80 @@ class SortedMap:
         n = _U64(0)
         _check(self._lib.kmi_sorted_stats(self._h, ms, ctypes.byref(n)))
         return [float(x) for x in ms], n.value
+
+
+def quality_lut():
+    out = np.zeros(96, dtype=np.float32)
+    _check(load_library().kmi_quality_lut(_hptr(out)))
+    return out
+
+
+class PositionQualityIndex:
+    """kmi_posqual_*: k-mer -> (ShortSequenceKmerId, float quality score) from FASTQ (PositionQualityIndex, kmer_index.hpp:406)."""
+
+    def __init__(self, k=21, canonical=True, hash=HASH_MURMUR, nsplit=False, device=0):
+        self._lib = load_library()
+        self.k, self.nw = k, nwords(k)
+        cfg = KmiConfig(k, MODE_POSITION, 1 if canonical else 0, hash, 1 if nsplit else 0, device, 0, 1, 0)
+        self._h = _P()
+        _check(self._lib.kmi_posqual_create(ctypes.byref(cfg), ctypes.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            self._lib.kmi_posqual_destroy(self._h)
+            self._h = _P()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def build_fastq(self, buf, file_offset=0):
+        a = np.ascontiguousarray(np.frombuffer(buf, dtype=np.uint8))
+        n = _U64(0)
+        _check(self._lib.kmi_posqual_build_fastq(self._h, _hptr(a), a.size, file_offset, ctypes.byref(n)))
+        return n.value
+
+    def local_size(self):
+        n = _U64(0)
+        _check(self._lib.kmi_posqual_local_size(self._h, ctypes.byref(n)))
+        return n.value
+
+    def count(self, keys):
+        a = _as_keys(keys, self.nw)
+        out = np.zeros(a.shape[0], dtype=np.uint64)
+        _check(self._lib.kmi_posqual_count(self._h, _hptr(a), a.shape[0], _hptr(out)))
+        return out
+
+    def erase(self, keys):
+        a = _as_keys(keys, self.nw)
+        _check(self._lib.kmi_posqual_erase(self._h, _hptr(a), a.shape[0]))
+
+    def find(self, keys):
+        """(offsets[n+1], ids, quals): CSR answer"""
+        a = _as_keys(keys, self.nw)
+        n = a.shape[0]
+        total = int(self.count(keys).sum())
+        off = np.zeros(n + 1, dtype=np.uint64)
+        ids = np.zeros(max(total, 1), dtype=np.uint64)
+        quals = np.zeros(max(total, 1), dtype=np.float32)
+        _check(self._lib.kmi_posqual_find(self._h, _hptr(a), n, _hptr(off), _hptr(ids), _hptr(quals), max(total, 1)))
+        return off, ids[:total], quals[:total]
+
+    def to_vector(self):
+        n = self.local_size()
+        keys = np.zeros((n, 2) if self.nw == 2 else (n,), dtype=np.uint64)
+        ids = np.zeros(max(n, 1), dtype=np.uint64)
+        quals = np.zeros(max(n, 1), dtype=np.float32)
+        got = _SZ(0)
+        _check(self._lib.kmi_posqual_dump(self._h, _hptr(keys), _hptr(ids), _hptr(quals), n, ctypes.byref(got)))
+        return keys[:got.value], ids[:got.value], quals[:got.value]
+
+    def launch_count(self):
+        n = _U64(0)
+        _check(self._lib.kmi_posqual_launch_count(self._h, ctypes.byref(n)))
+        return n.value
 
 
 def CountIndex(k=31, **kw):

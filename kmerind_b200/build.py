@@ -45,7 +45,7 @@ def build(force=False, verbose=False):
         objs.append(o)
         if force or _newer(o, hdrs + [inst]):
             jobs.append([NVCC] + FLAGS + ["-DKMI_K=%d" % k, "-c", inst, "-o", o])
-    for name in ("kmi_api", "kmi_dist", "kmi_sorted"):
+    for name in ("kmi_api", "kmi_dist", "kmi_sorted", "kmi_quality"):
         src = os.path.join(CSRC, name + ".cu")
         o = os.path.join(objdir, name + ".o")
         objs.append(o)

@@ -295,6 +295,94 @@ long kmio_fastq_kmers(const uint8_t* buf, size_t n, uint64_t file_offset, int K,
   return (long)total;
 }
 
+/* ---- f4: k-mer quality scores of the PositionQualityIndex (KmerPositionQualityTupleParser, src/io/kmer_parser.hpp:578-760;
+ * QualityScoreSlidingWindow, src/index/quality_score_iterator.hpp:60-140; Illumina18QualityScoreCodec<float> =
+ * QualityScoreCodec<float, 33, 126, 0>, src/index/quality_scores.hpp:60-170,529). One float per k-mer, in the order
+ * kmio_fastq_kmers emits its tuples: DecodeLUT[c - 33] = log2(1 - 10^(-q/10)) (the table's literals, reproduced with log1p and
+ * rounded to float: checked against the reference's own table in tests/test_oracle.py); a base is "correct" when its value
+ * lies strictly between LUT[0] (lowest) and LUT[95] (0.0), i.e. Phred 1..93; the window keeps a running float sum, adding
+ * the entering and subtracting the leaving value IN THAT ORDER OF OPERATIONS (init sums the first K left to right; next()
+ * subtracts the old value, then adds the new one), and a count of incorrect bases; value = 0 if any base of the window is
+ * incorrect, else exp2f(sum). With nsplit every N-free run restarts the window (the sub-sequence's qual_begin is advanced
+ * by the same distance as its seq_begin, kmer_parser.hpp:650-654). A record without a quality line yields 0. */
+#include <math.h>
+static float kmio_qlut[96];
+static int kmio_qlut_ready = 0;
+void kmio_quality_lut(float* out96) {
+  if (!kmio_qlut_ready) {
+    kmio_qlut[0] = -3.402823466e+38F;                                   /* std::numeric_limits<float>::lowest() */
+    for (int q = 1; q <= 93; ++q) kmio_qlut[q] = (float)(log1p(-pow(10.0, -(double)q / 10.0)) / log(2.0));
+    kmio_qlut[94] = kmio_qlut[95] = 0.0f;
+    kmio_qlut_ready = 1;
+  }
+  if (out96) memcpy(out96, kmio_qlut, sizeof(kmio_qlut));
+}
+static float kmio_qdecode(uint8_t c, int* ok) {
+  if (c < 33 || c > 128) { *ok = 0; return 0.0f; }                     /* outside the table: the reference reads out of bounds */
+  float v = kmio_qlut[c - 33];
+  *ok = (v > kmio_qlut[0]) && (v < kmio_qlut[95]);
+  return v;
+}
+/* windows of one run: bases [b, e) of the sequence line, their quality bytes at q[0 .. e-b) */
+static long kmio_quality_run(const uint8_t* q, size_t len, size_t q_avail, int K, float* out, size_t have, size_t cap) {
+  if (len < (size_t)K) return 0;
+  long m = 0;
+  float sum = 0.0f;
+  int bad = 0;
+  for (size_t t = 0; t + (size_t)K <= len; ++t) {
+    if (t == 0) {
+      for (int j = 0; j < K; ++j) { int ok; float v = ((size_t)j < q_avail) ? kmio_qdecode(q[j], &ok) : (ok = 0, 0.0f); if (ok) sum += v; else ++bad; }
+    } else {
+      int ok_o, ok_n;
+      float o = (t - 1 < q_avail) ? kmio_qdecode(q[t - 1], &ok_o) : (ok_o = 0, 0.0f);
+      float v = (t - 1 + (size_t)K < q_avail) ? kmio_qdecode(q[t - 1 + (size_t)K], &ok_n) : (ok_n = 0, 0.0f);
+      if (ok_o) sum -= o; else --bad;
+      if (ok_n) sum += v; else ++bad;
+    }
+    if (have + (size_t)m >= cap) return KMIO_ERR_CAP;
+    out[have + (size_t)m] = bad > 0 ? 0.0f : exp2f(sum);
+    ++m;
+  }
+  return m;
+}
+long kmio_fastq_quality(const uint8_t* buf, size_t n, int K, int nsplit, float* quals, size_t cap) {
+  kmio_quality_lut(NULL);
+  size_t i = 0, total = 0;
+  while (i < n && is_eol(buf[i])) ++i;
+  while (i < n) {
+    if (buf[i] != '@') return KMIO_ERR_NO_AT;
+    while (i < n && !is_eol(buf[i])) ++i;
+    while (i < n && is_eol(buf[i])) ++i;
+    size_t sb = i;
+    while (i < n && !is_eol(buf[i])) ++i;
+    size_t se = i;
+    while (i < n && is_eol(buf[i])) ++i;
+    if (i < n && buf[i] != '+') return KMIO_ERR_NO_PLUS;
+    while (i < n && !is_eol(buf[i])) ++i;
+    while (i < n && is_eol(buf[i])) ++i;
+    size_t qb = i;
+    while (i < n && !is_eol(buf[i])) ++i;
+    size_t qe = i;
+    while (i < n && is_eol(buf[i])) ++i;
+    if (sb != se && qb != qe && (se - sb) != (qe - qb)) return KMIO_ERR_LEN;
+    size_t b = sb;
+    while (b < se) {
+      size_t e = se;
+      if (nsplit) {
+        while (b < se && is_n(buf[b])) ++b;
+        e = b;
+        while (e < se && !is_n(buf[e])) ++e;
+      }
+      size_t qoff = b - sb, qav = (qe - qb) > qoff ? (qe - qb) - qoff : 0;
+      long m = kmio_quality_run(buf + qb + qoff, e - b, qav, K, quals, total, cap);
+      if (m < 0) return m;
+      total += (size_t)m;
+      b = e;
+    }
+  }
+  return (long)total;
+}
+
 /* ---- a2: FASTQParser::find_first_record (serial), src/io/fastq_loader.hpp:269-357: first record start inside the
  * search range [s, e) of a file whose bytes [mem, mem + n) are in buf; parent = [ps, pe) is the enclosing
  * record-aligned range. Walks to the first line start, takes the first characters of four consecutive non-empty

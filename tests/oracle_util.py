@@ -35,6 +35,9 @@ def oracle():
         lib.kmio_hash.argtypes = [ctypes.c_int, ctypes.c_int, _P, _P, _SZ]
         lib.kmio_owner.argtypes = [_P, _SZ, ctypes.c_uint32, _P]
         lib.kmio_hash_prefix.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_uint, _P, _P, _SZ]
+        lib.kmio_quality_lut.argtypes = [_P]
+        lib.kmio_fastq_quality.restype = ctypes.c_long
+        lib.kmio_fastq_quality.argtypes = [_P, _SZ, ctypes.c_int, ctypes.c_int, _P, _SZ]
         lib.kmio_fastq_find_first_record.argtypes = [_P, _U64, _SZ, _U64, _U64, _U64, _U64, _P]
         lib.kmio_count_sorted.restype = _SZ
         lib.kmio_count_sorted.argtypes = [ctypes.c_int, _P, _SZ, _P]
@@ -62,6 +65,10 @@ def ref_lib(flavour="ndebug"):
     lib.kmiref_canonical.argtypes = [ctypes.c_int, _P, _P, _SZ]
     lib.kmiref_hash.argtypes = [ctypes.c_int, ctypes.c_int, _P, _P, _SZ]
     lib.kmiref_sentinels.argtypes = [ctypes.c_int, _P]
+    if hasattr(lib, "kmiref_quality"):
+        lib.kmiref_quality.restype = _SZ
+        lib.kmiref_quality.argtypes = [ctypes.c_int, _P, _SZ, _P]
+        lib.kmiref_quality_lut.argtypes = [_P]
     if hasattr(lib, "kmiref_hash_prefix"):
         lib.kmiref_hash_prefix.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_uint, _P, _P, _SZ]
     lib.kmiref_count_build.restype = _SZ
@@ -132,6 +139,22 @@ def fastq_kmers(buf, k, canonical=True, nsplit=False, want_ids=False, file_offse
     if m < 0:
         raise ValueError("oracle: malformed FASTQ (%d)" % m)
     return shape_keys(keys[:m * nw].copy(), k), (ids[:m].copy() if want_ids else None), reads.value
+
+
+def fastq_quality(buf, k, nsplit=False):
+    """one float per k-mer, in the order fastq_kmers emits its tuples (PositionQualityIndex scores)"""
+    n = int(buf.size)
+    out = np.zeros(max(n, 1), dtype=np.float32)
+    m = oracle().kmio_fastq_quality(_ptr(buf), n, k, int(nsplit), _ptr(out), max(n, 1))
+    if m < 0:
+        raise ValueError("oracle: malformed FASTQ (%d)" % m)
+    return out[:m].copy()
+
+
+def quality_lut():
+    out = np.zeros(96, dtype=np.float32)
+    oracle().kmio_quality_lut(_ptr(out))
+    return out
 
 
 def fastq_find_first_record(buf, s, e=None, mem=0, parent=None):

@@ -277,3 +277,34 @@ def test_identity_std_vs_live_reference():
                 want = np.zeros(n, dtype=np.uint64)
                 ref.kmiref_hash_prefix(k, (kind - 3) * 2 + (1 if dist else 0), ou.ceil_log2(pbits_p), ou._ptr(keys), ou._ptr(want), n)
                 assert np.array_equal(got, want), (k, kind, dist, pbits_p)
+
+
+# ---- f4: k-mer quality scores (reference src/index/quality_score_iterator.hpp, quality_scores.hpp) ---------------------------
+QKAT = json.load(open(os.path.join(ou.ROOT, "tests", "golden", "ref_quality.json")))
+
+
+def test_quality_lut_matches_reference_table():
+    want = np.array(QKAT["lut_bits"], dtype=np.uint32).view(np.float32)
+    assert np.array_equal(ou.quality_lut().view(np.uint32), want.view(np.uint32))     # bit for bit
+
+
+@pytest.mark.parametrize("k", KS)
+def test_quality_scores_match_reference_executed_vectors(k):
+    """The C oracle's rolling window against the reference's own QualityScoreGenerationIterator<.., Illumina18<float>>,
+    float bit patterns (same glibc exp2f on both sides, so even the last step is exact here)."""
+    for name, lines in QKAT["lines"].items():
+        for ln, want_bits in zip(lines, QKAT["scores"][str(k)][name]):
+            q = ln.encode("latin1")
+            rec = np.frombuffer(b"@r\n" + b"A" * len(q) + b"\n+\n" + q + b"\n", dtype=np.uint8).copy()
+            got = ou.fastq_quality(rec, k)
+            assert np.array_equal(got.view(np.uint32), np.array(want_bits, dtype=np.uint32)), (k, name)
+
+
+def test_quality_order_and_nsplit_follow_the_tuple_stream():
+    """scores come in the order fastq_kmers emits tuples; with nsplit every N-free run restarts the window"""
+    buf = ou.read_fixture("natural.withN.fastq")
+    for nsplit in (False, True):
+        keys, ids, _ = ou.fastq_kmers(buf, 21, nsplit=nsplit, want_ids=True)
+        q = ou.fastq_quality(buf, 21, nsplit=nsplit)
+        assert len(q) == len(keys)
+        assert np.all((q >= 0) & (q <= 1))
