@@ -496,8 +496,10 @@ def run_gpu_arm(args):
 #   pos21         cfg 5: PositionIndex K=21 over a synthetic FASTA genome, 375 Mbp per GPU (= 24 x 125 Mbp at 8 GPUs), then
 #                 1.25e8 query k-mers per GPU (= 1e9 at 8): count() and find() of all positions
 # ------------------------------------------------------------------------------------------------
-BIG = {"count31_100g": {"k": 31, "reads": 83333344, "batch": 10000000, "distinct_frac": 0.19},
-       "count63": {"k": 63, "reads": 26666672, "batch": 5000000, "distinct_frac": 0.50}}
+# "defer": staging budget (keys) of bulk-load mode (KMI_PARAM_DEFER_INSERT): the batches' fine buckets are staged and the table
+# is swept once per flush instead of once per batch (the library clamps the budget to 60 % of the free device memory)
+BIG = {"count31_100g": {"k": 31, "reads": 83333344, "batch": 10000000, "distinct_frac": 0.19, "defer": 10000001280},
+       "count63": {"k": 63, "reads": 26666672, "batch": 5000000, "distinct_frac": 0.50, "defer": 2400000000}}
 
 
 def _dist_setup():
@@ -564,18 +566,26 @@ def run_big_count(args, name):
         from kmerind_b200.dist import ShardedIndex
         idx = ShardedIndex(k, hash=kb.HASH_FARM, device=lr, reserve=reserve)
         local, build = idx.local, idx.build_fastq_dev
+    defer = int(os.environ.get("KMI_BENCH_DEFER", str(c["defer"])))
+    local.set_defer_insert(defer)
     stage = []
+    sweeps = []
 
     def step():
         local.clear()
         got = 0
         ms = np.zeros(5)
+        f0 = local.bulk_stats()[1]
         for b0 in range(0, n_reads, batch):
             m = min(batch, n_reads - b0)
             got += build(text.data_ptr() + b0 * REC, m * REC)
             ms += np.array(local.last_kernel_ms())
+        before = np.array(local.last_kernel_ms())
+        local.flush()                                      # bulk load: what is still staged goes in now, inside the timed region
+        ms += np.array(local.last_kernel_ms()) - before
         assert got == n_kmers_rank, (got, n_kmers_rank)
         stage.append(ms)
+        sweeps.append((local.bulk_stats()[1] - f0) if defer else -(-n_reads // batch))
     ms_step, clocks = _timed(torch, dist, world, device, step, args.steps, args.warmup, ClockSampler(lr))
     total_kmers = n_kmers_rank * world
     cks = local.checksum()
@@ -598,23 +608,25 @@ def run_big_count(args, name):
     peak, peak_kind = measured_peaks()
     km = np.mean(np.array(stage[-args.steps:]), axis=0)
     n_batches = -(-n_reads // batch)
+    n_sweeps = int(sweeps[-1])
     key_b = 8.0 * kb.nwords(k)
-    # table sweep of every batch: the segment insert reads and writes every slot once per batch
-    sweep = 2.0 * info["slots"] * info["slot_bytes"] * n_batches
+    # table sweeps: a segment insert reads and writes every slot (the first one after kmi_clear only writes)
+    sweep = (2.0 * n_sweeps - 1.0) * info["slots"] * info["slot_bytes"]
     ins_alg = (key_b + 12 + 12 if k <= 32 else key_b + 20 + 20) * n_kmers_rank
-    roofline = {"bound": "hbm", "kernel": "k_insert_segments%s (table sweep per batch)" % ("" if k <= 32 else "2"),
+    roofline = {"bound": "hbm", "kernel": "k_insert_segments%s (%d table sweep%s per step)" % ("" if k <= 32 else "2", n_sweeps, "" if n_sweeps == 1 else "s"),
                 "achieved": ins_alg / (float(km[3]) * 1e-3) / 1e9, "peak": peak, "peak_source": peak_kind, "unit": "GB/s",
                 "frac": ins_alg / (float(km[3]) * 1e-3) / 1e9 / peak, "traffic": None,
                 "swept_bytes_per_step": sweep, "swept_gbs": sweep / (float(km[3]) * 1e-3) / 1e9,
                 "alg_bytes_per_kmer": ins_alg / n_kmers_rank, "kernel_ms_per_step": float(km[3]),
                 "stage_ms_per_step": {"parse+scatter": float(km[1]), "fine scatter": float(km[2]), "segment insert": float(km[3]), "overflow": float(km[4])},
-                "batches_per_step": n_batches}
+                "batches_per_step": n_batches, "table_sweeps_per_step": n_sweeps, "defer_budget_keys": defer}
     if rank == 0:
         cfg = workload_config(world, n_reads)
         cfg.update({"k": k, "kmers_per_gpu": n_kmers_rank, "batch_reads": batch,
                     "workload": "CountIndex K=%d canonical, farm hash, synthetic %.2f Gbp of 150 bp reads per GPU (30x, 0.5%% substitutions) = "
-                                "%.1f Gbp over %d GPU%s, built in %d batches into one index" % (k, n_reads * READ_LEN / 1e9,
-                                n_reads * READ_LEN * world / 1e9, world, "" if world == 1 else "s", n_batches)})
+                                "%.1f Gbp over %d GPU%s, built in %d batches into one index (%s)" % (k, n_reads * READ_LEN / 1e9,
+                                n_reads * READ_LEN * world / 1e9, world, "" if world == 1 else "s", n_batches,
+                                "bulk load: %d table sweep%s" % (n_sweeps, "" if n_sweeps == 1 else "s") if defer else "one table sweep per batch")})
         line = {"metric": "canonical k-mers inserted/sec into count index", "value": total_kmers / (ms_step * 1e-3), "unit": "kmers/s",
                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": cfg,

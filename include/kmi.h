@@ -87,9 +87,21 @@ int kmi_set_stream(kmi_index* idx, void* cuda_stream);
  * KMI_PARAM_DIST_TRANS (non-canonical index): the DistTrans of SingleStrandHashMapParams<Key, DistHash, StoreHash, DistTrans>
  * (BenchmarkKmerIndex.cpp:152-161,246-249) — owner = dist_hash(T(key)) % nranks with T = 0 identity (default), 1 lex_less,
  * 2 xor_rev_comp (kmer_transform.hpp:91-107), so both strands of a k-mer meet on one rank while the stored key stays as
- * given. Enters kmi_partition_dev and every sharded operation built on it. */
-typedef enum { KMI_PARAM_BUILD_PATH = 1, KMI_PARAM_SEGMENT_INSERT = 2, KMI_PARAM_SATURATE = 3, KMI_PARAM_DIST_TRANS = 4 } kmi_param;
+ * given. Enters kmi_partition_dev and every sharded operation built on it.
+ * KMI_PARAM_DEFER_INSERT (COUNT index; bulk load): value = staging budget in keys, 0 = off (default). The reference inserts
+ * a whole file's k-mers in ONE Index::insert (kmer_index.hpp:201-225, 332-372); a GPU build far larger than one bucket round
+ * (2^31 k-mers) otherwise runs the shared-memory segment insert — a read + write of the WHOLE table — once per round or per
+ * call. In bulk-load mode the bucketed builds (kmi_build_fastq_dev of >= 8 MiB, kmi_dist_build_fastq*) stop after the fine
+ * scatter, which appends to a staging area laid out for `value` keys (clamped to 60 % of the free device memory); the single
+ * segment insert runs when the area is full, when the table must grow, when anything reads or changes the table (find, count,
+ * erase, dump, size, checksum, save ...) or on kmi_flush. Results are identical; only the number of table sweeps changes. */
+typedef enum { KMI_PARAM_BUILD_PATH = 1, KMI_PARAM_SEGMENT_INSERT = 2, KMI_PARAM_SATURATE = 3, KMI_PARAM_DIST_TRANS = 4,
+               KMI_PARAM_DEFER_INSERT = 5 } kmi_param;
 int kmi_set_param(kmi_index* idx, int param, int64_t value);
+/* insert whatever bulk-load mode has staged and wait for it; reports a sticky table error like the size readers do */
+int kmi_flush(kmi_index* idx);
+/* bulk-load accounting: keys staged right now, deferred segment inserts (table sweeps) run since creation */
+int kmi_bulk_stats(kmi_index* idx, uint64_t* staged_keys, uint64_t* flushes);
 /* map_base::reserve — src/containers/distributed_map_base.hpp:149-302 */
 int kmi_reserve(kmi_index* idx, uint64_t n_distinct);
 /* remove every entry, keep the allocation */

@@ -64,7 +64,7 @@ def load_library(build_if_missing=False):
     lib.kmi_destroy.argtypes = [_P]
     lib.kmi_destroy.restype = None
     sig = {
-        "kmi_device_count": [_P], "kmi_set_stream": [_P, _P], "kmi_set_param": [_P, ctypes.c_int, ctypes.c_int64], "kmi_reserve": [_P, _U64], "kmi_clear": [_P],
+        "kmi_device_count": [_P], "kmi_set_stream": [_P, _P], "kmi_set_param": [_P, ctypes.c_int, ctypes.c_int64], "kmi_flush": [_P], "kmi_bulk_stats": [_P, _P, _P], "kmi_reserve": [_P, _U64], "kmi_clear": [_P],
         "kmi_build_fastq": [_P, _P, _SZ, _U64, _P], "kmi_build_fasta": [_P, _P, _SZ, _P],
         "kmi_build_fastq_dev": [_P, _P, _SZ, _U64, _P], "kmi_build_fasta_dev": [_P, _P, _SZ, _P],
         "kmi_parse_fastq_dev": [_P, _P, _SZ, _U64, _P, _P, _SZ, _P],
@@ -134,7 +134,7 @@ def load_library(build_if_missing=False):
 
 
 EXPORTED_SYMBOLS = (
-    "kmi_create", "kmi_destroy", "kmi_last_error", "kmi_device_count", "kmi_set_stream", "kmi_set_param", "kmi_reserve", "kmi_clear",
+    "kmi_create", "kmi_destroy", "kmi_last_error", "kmi_device_count", "kmi_set_stream", "kmi_set_param", "kmi_flush", "kmi_bulk_stats", "kmi_reserve", "kmi_clear",
     "kmi_build_fastq", "kmi_build_fasta", "kmi_build_fastq_dev", "kmi_build_fasta_dev",
     "kmi_parse_fastq_dev", "kmi_parse_fasta_dev", "kmi_parse_fasta_block_dev", "kmi_build_fasta_block", "kmi_build_fasta_block_dev",
     "kmi_fasta_block_summary_dev", "kmi_fasta_halo_end", "kmi_build_file", "kmi_save", "kmi_load", "kmi_fastq_find_first_record",
@@ -486,6 +486,19 @@ class Index:
     def set_build_path(self, path):
         """0 auto, 1 direct atomics, 2 hash-prefix buckets (KMI_PARAM_BUILD_PATH)."""
         _check(self._lib.kmi_set_param(self._h, 1, path))
+
+    def set_defer_insert(self, budget_keys):
+        """KMI_PARAM_DEFER_INSERT (bulk load): stage up to budget_keys k-mers in fine buckets, one table sweep per flush; 0 = off"""
+        _check(self._lib.kmi_set_param(self._h, 5, int(budget_keys)))
+
+    def flush(self):
+        _check(self._lib.kmi_flush(self._h))
+
+    def bulk_stats(self):
+        """(keys staged right now, deferred segment inserts run so far)"""
+        a, b = _U64(0), _U64(0)
+        _check(self._lib.kmi_bulk_stats(self._h, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
 
     def set_dist_trans(self, t):
         """KMI_PARAM_DIST_TRANS: 0 identity, 1 lex_less, 2 xor_rev_comp under the dist hash (non-canonical index)."""

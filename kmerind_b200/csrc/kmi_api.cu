@@ -126,6 +126,7 @@ static int table_alloc(kmi_index* idx, u64 cap, void** out) {
 
 // grow (rehash) to `new_cap` slots
 static int table_grow(kmi_index* idx, u64 new_cap) {
+  if (idx->pend_keys) OK(flush_pending(idx));            // staged fine buckets are cut for the current capacity
   void* fresh = nullptr;
   OK(table_alloc(idx, new_cap, &fresh));
   void* old = idx->slots;
@@ -230,7 +231,8 @@ extern "C" void kmi_destroy(kmi_index* idx) {
   if (idx->ctr) cudaFree(idx->ctr);
   DevBuf* bufs[] = {&idx->tile_lines, &idx->block_sums, &idx->stage_in, &idx->stage_keys, &idx->stage_vals,
                     &idx->stage_out, &idx->stage_found, &idx->hist, &idx->hist_sums, &idx->log_keys, &idx->log_ids,
-                    &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->mid_keys, &idx->mid_cur};
+                    &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->mid_keys, &idx->mid_cur,
+                    &idx->pend_ovf, &idx->pend_ovf_cur, &idx->pend_cur_save};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 6; ++i) if (idx->ev[i]) cudaEventDestroy(idx->ev[i]);
   for (int i = 0; i < 4; ++i) if (idx->kev[i]) cudaEventDestroy(idx->kev[i]);
@@ -265,6 +267,13 @@ extern "C" int kmi_set_param(kmi_index* idx, int param, int64_t value) {
     if (idx->saturate) idx->build_path = 1;              // the shared-memory segment insert adds with plain wrap-around
     return KMI_OK;
   }
+  if (param == KMI_PARAM_DEFER_INSERT) {
+    if (value < 0) return fail(KMI_ERR_ARG, "staging budget must be >= 0 keys");
+    if (idx->cfg.mode != KMI_MODE_COUNT) return fail(KMI_ERR_ARG, "bulk-load staging belongs to a COUNT index");
+    if (!value) OK(flush_pending(idx));
+    idx->defer_budget = (u64)value;
+    return KMI_OK;
+  }
   if (param == KMI_PARAM_DIST_TRANS) {
     if (value < 0 || value > 2) return fail(KMI_ERR_ARG, "dist transform must be 0 (identity), 1 (lex_less) or 2 (xor_rev_comp)");
     if (idx->cfg.canonical && value == 2)
@@ -273,6 +282,22 @@ extern "C" int kmi_set_param(kmi_index* idx, int param, int64_t value) {
     return KMI_OK;
   }
   return fail(KMI_ERR_ARG, "unknown parameter %d", param);
+}
+
+extern "C" int kmi_flush(kmi_index* idx) {
+  if (!idx) return fail(KMI_ERR_ARG, "null index");
+  CU(cudaSetDevice(idx->cfg.device));
+  OK(flush_pending(idx));
+  CU(cudaStreamSynchronize(idx->stream));
+  harvest_commit_times(idx);
+  return check_table_error(idx);
+}
+
+extern "C" int kmi_bulk_stats(kmi_index* idx, uint64_t* staged_keys, uint64_t* flushes) {
+  if (!idx) return fail(KMI_ERR_ARG, "null index");
+  if (staged_keys) *staged_keys = idx->pend_keys;
+  if (flushes) *flushes = idx->flushes;
+  return KMI_OK;
 }
 
 extern "C" int kmi_reserve(kmi_index* idx, uint64_t n_distinct) {
@@ -287,6 +312,10 @@ extern "C" int kmi_clear(kmi_index* idx) {
   if (!idx) return fail(KMI_ERR_ARG, "null index");
   CU(cudaSetDevice(idx->cfg.device));
   idx->virgin = idx->slots != nullptr;                  // cleared lazily (kmi_index::touch) or never (segment insert)
+  if (idx->pend_keys) {                                 // staged keys are dropped with everything else
+    idx->pend_keys = 0;
+    CU(cudaMemsetAsync(idx->fine_cur.p, 0, ((u64)1 << idx->pend_log_segs) * sizeof(u32), idx->stream));
+  }
   CU(cudaMemsetAsync(idx->ctr, 0, sizeof(u64) * CTR_N, idx->stream));
   idx->size_exact = idx->size_upper = 0;
   idx->tombstones = 0;
@@ -363,37 +392,230 @@ int kmi::bucket_readback(kmi_index* idx, const BucketSink& bs, u64* host_ctr, st
   return KMI_OK;
 }
 
+// ---- geometry of the segment path for the current table capacity and a sink's prefix layout --------------------------------
+namespace {
+struct SegPlan {
+  bool ok = false;        // table segments fit shared memory: fine scatter + k_insert_segments can run
+  bool two_pass = false;  // very large tables: mid buckets first, then 256 fine buckets per group of 256 mid regions
+  int log_pre = 0, log_segs = 0, log_seg = 0;
+  u32 log_f = 0;
+  u64 n_regions = 0;
+};
+SegPlan seg_plan(const kmi_index* idx, const BucketSink& bs) {
+  SegPlan pl;
+  // second level: table segments of <= 4096 slots (8192 beyond 2^31 slots) updated in shared memory
+  const int log_cap = __builtin_ctzll(idx->cap);
+  // (regions of the exchange buffer share only log_pre < 8 prefix bits: their fine scatter is wider, never skipped)
+  pl.log_pre = (int)bs.log_pre;
+  const int log_seg_slots = idx->nw == 1 ? KMI_LOG_SEG_SLOTS : LOG_SEG_SLOTS2;
+  // (a receive buffer has `sub` regions per prefix: they always need the fine pass to become one region per segment)
+  pl.log_segs = std::max(std::max(LOG_BUCKETS, pl.log_pre + ((pl.log_pre < LOG_BUCKETS || bs.sub > 1) ? 1 : 0)), log_cap - log_seg_slots);
+  // beyond 2^9 fine buckets per coarse bucket the scatter runs shrink to one or two keys: very large tables take TWO
+  // fine passes instead (2^(log_f - 8) mid buckets, then 256 fine buckets inside every group of 256 mid regions)
+  pl.two_pass = pl.log_pre == LOG_BUCKETS && pl.log_segs - pl.log_pre >= 10 && pl.log_segs - pl.log_pre <= 16;
+  if (!pl.two_pass) pl.log_segs = std::min(pl.log_segs, pl.log_pre + MAX_LOG_F);
+  pl.log_seg = log_cap - pl.log_segs;
+  pl.ok = idx->seg_path && idx->ops->insert_segments && pl.log_seg <= (idx->nw == 1 ? 13 : 12) && pl.log_seg >= 8;
+  pl.log_f = (u32)(pl.log_segs - pl.log_pre);
+  pl.n_regions = (u64)1 << pl.log_segs;
+  return pl;
+}
+
+// coarse regions of `bs` -> the fine regions `fs` (one per table segment), in one or two passes. The fine cursors are NOT
+// reset here: a regular commit zeroes them first, a deferred one appends to what earlier rounds staged.
+int fine_scatter_launch(kmi_index* idx, const BucketSink& bs, const SegPlan& pl, FineSink fs, u64 n_keys) {
+  if (!pl.two_pass) {
+    idx->ops->scatter_fine(idx->stream, bs, fs, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), n_keys);
+    idx->launches++;
+  } else {
+    FineSink mid;
+    mid.log_f = pl.log_f - LOG_BUCKETS;
+    const u64 n_mid = (u64)N_BUCKETS << mid.log_f;
+    const double mean1 = (double)n_keys / (double)n_mid;
+    const u64 capm = (u64)(mean1 + 8.0 * std::sqrt(mean1) + 32.0);
+    OK(idx->mid_keys.ensure(n_mid * capm * sizeof(u64) * idx->nw));
+    OK(idx->mid_cur.ensure(n_mid * sizeof(u32)));
+    CU(cudaMemsetAsync(idx->mid_cur.p, 0, n_mid * sizeof(u32), idx->stream));
+    mid.keys = idx->mid_keys.as<u64>(); mid.cursor = idx->mid_cur.as<u32>(); mid.capf = (u32)capm;
+    idx->ops->scatter_fine(idx->stream, bs, mid, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), n_keys);
+    idx->launches++;
+    fs.log_f = LOG_BUCKETS;                            // per group of 256 mid regions
+    for (u64 g = 0; g < n_mid / N_BUCKETS; ++g) {
+      BucketSink bg;
+      bg.keys = mid.keys + g * N_BUCKETS * capm * idx->nw;
+      bg.cursor = mid.cursor + g * N_BUCKETS;
+      bg.capb = (u32)capm; bg.ovf_cap = bs.ovf_cap; bg.hll = nullptr; bg.bases = nullptr;
+      bg.log_pre = (u32)LOG_BUCKETS + mid.log_f; bg.pre_mask = N_BUCKETS - 1; bg.pre_base = (u32)(g * N_BUCKETS);
+      bg.ovf_keys = idx->nw == 1 ? ovf_base<1>(bs) : ovf_base<2>(bs); bg.ovf_cursor = ovf_cur(bs);
+      idx->ops->scatter_fine(idx->stream, bg, fs, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), n_keys / (n_mid / N_BUCKETS) + 1);
+      idx->launches++;
+    }
+  }
+  CU(cudaGetLastError());                              // a scatter that did not launch must not pass for an empty bucket
+  return KMI_OK;
+}
+
+// distinct keys after an insert of n_keys more: at most size + n_keys, and (6 sigma) at most 1.05 * HLL + keys the HLL never saw
+// (the registers see a 1/HLL_SAMPLE hash-sampled subset: scale back, add 6 sigma of the sampling error)
+u64 need_after(const kmi_index* idx, u64 n_keys, u64 size_now, const std::vector<u32>& reg) {
+  const double est = hll_estimate(reg.data()) * (double)HLL_SAMPLE;
+  const u64 by_hll = (u64)(est * 1.05 + 6.0 * std::sqrt(est * (double)HLL_SAMPLE)) + 4096 + idx->non_hll_upper;
+  return std::min(size_now + n_keys, std::max(by_hll, size_now));
+}
+}  // namespace
+
+// ---- KMI_PARAM_DEFER_INSERT (bulk load): the fine buckets of several rounds / calls are STAGED and inserted together ---------
+// A build far larger than one bucket round used to sweep the whole table once per round (the segment insert reads and writes
+// every segment): at the 100 Gbp configuration's per-GPU share that was 5-9 sweeps of a 68.7 GB table, all of the insert
+// time. In bulk-load mode a round stops after the fine scatter, which APPENDS to fine regions sized for `defer_budget` keys;
+// the one segment insert runs when the staging area is full, when the table has to grow, or when anything looks at the table
+// (kmi_index::touch, the size readers, kmi_flush). Invariant: staged keys always fit the current table (checked with the HLL
+// bound when they are staged), so a flush never grows the table and the regions never outlive the geometry they were cut for.
+int kmi::flush_pending(kmi_index* idx) {
+  if (!idx->pend_keys) return KMI_OK;
+  idx->pend_keys = 0;                                     // (first: insert_overflow below goes through view())
+  CU(cudaSetDevice(idx->cfg.device));
+  CU(cudaStreamSynchronize(idx->stream));
+  harvest_commit_times(idx);
+  const int log_cap = __builtin_ctzll(idx->cap);
+  const int log_seg = log_cap - idx->pend_log_segs;
+  FineSink fs;
+  fs.keys = idx->fine_keys.as<u64>(); fs.cursor = idx->fine_cur.as<u32>(); fs.capf = idx->pend_capf; fs.log_f = 0;
+  BucketSink sp;                                          // only its spill list is used
+  sp.keys = nullptr; sp.cursor = nullptr; sp.capb = 0; sp.hll = nullptr; sp.bases = nullptr;
+  sp.ovf_keys = idx->pend_ovf.as<u64>(); sp.ovf_cursor = idx->pend_ovf_cur.as<u32>(); sp.ovf_cap = idx->pend_ovf_cap;
+  CU(cudaMemsetAsync(sp.ovf_cursor, 0, sizeof(u32), idx->stream));
+  CU(cudaEventRecord(idx->kev[0], idx->stream));
+  CU(cudaEventRecord(idx->kev[1], idx->stream));
+  const bool fresh_table = idx->virgin;
+  const u64 n_regions = (u64)1 << idx->pend_log_segs;
+  int e = idx->ops->insert_segments(idx->stream, idx->raw_view(), fs, sp, (u32)log_seg, (u32)n_regions,
+                                    reinterpret_cast<u32*>(idx->ctr + CTR_PERR), fresh_table);
+  idx->virgin = false;
+  if (e) return fail(KMI_ERR_CUDA, "segment kernel configuration: %s", cudaGetErrorString((cudaError_t)e));
+  CU(cudaEventRecord(idx->kev[2], idx->stream));
+  idx->ops->insert_overflow(idx->stream, idx->raw_view(), sp);
+  CU(cudaGetLastError());
+  CU(cudaEventRecord(idx->kev[3], idx->stream));
+  idx->kev_pending = true;
+  idx->launches += 2;
+  CU(cudaMemsetAsync(idx->fine_cur.p, 0, n_regions * sizeof(u32), idx->stream));
+  idx->size_exact = ~0ULL;
+  idx->flushes++;
+  return KMI_OK;
+}
+
+namespace {
+// One round of a bulk-load build: size the table for everything seen so far, fine-scatter the round's coarse buckets BEHIND
+// what is staged, insert nothing. *staged = false: the segment path cannot run for this table / sink and the caller commits
+// the round the regular way (nothing of it has been touched).
+int bucket_stage(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 size_now, const std::vector<u32>& reg, bool* staged) {
+  *staged = false;
+  u64 need = need_after(idx, idx->pend_keys + n_keys, size_now, reg);
+  if (!idx->slots || (double)(need + idx->tombstones) > idx->cap * MAX_LOAD) {
+    if (idx->pend_keys) {                                 // what is staged fits the table as it is: insert it, then grow
+      OK(flush_pending(idx));
+      OK(read_ctr(idx, CTR_SIZE, &size_now));
+      need = need_after(idx, n_keys, size_now, reg);
+    }
+    if (!idx->slots || (double)(need + idx->tombstones) > idx->cap * MAX_LOAD) {
+      u64 want = pow2_at_least((u64)(need / MAX_LOAD) + 1);
+      if (want > idx->cap || idx->tombstones) OK(table_grow(idx, std::max(want, idx->cap)));
+    }
+  }
+  const SegPlan pl = seg_plan(idx, bs);
+  if (!pl.ok || pl.log_f == 0) return KMI_OK;             // regular commit (it flushes what is staged first)
+  // staging area: laid out for this geometry; its size is the budget, clamped by what the device has left
+  if (idx->pend_log_segs != pl.log_segs || idx->pend_cap != idx->cap || !idx->fine_keys.p || idx->pend_req != idx->defer_budget) {
+    OK(flush_pending(idx));
+    size_t free_b = 0, total_b = 0;
+    CU(cudaMemGetInfo(&free_b, &total_b));
+    free_b += idx->fine_keys.cap;                         // (the old staging area is released by ensure)
+    const u64 by_mem = (u64)((double)free_b * 0.6) / (sizeof(u64) * idx->nw);
+    u64 budget = std::min<u64>(idx->defer_budget, by_mem);
+    if (budget < 2 * n_keys) return KMI_OK;               // no room to hold more than this round: nothing to gain
+    const double mean = (double)budget / (double)pl.n_regions;
+    const u64 capf = (u64)(mean + 8.0 * std::sqrt(mean) + 32.0);
+    if (capf >= 0xffffffffULL) return KMI_OK;
+    OK(idx->fine_keys.ensure(pl.n_regions * capf * sizeof(u64) * idx->nw));
+    OK(idx->fine_cur.ensure(pl.n_regions * sizeof(u32)));
+    OK(idx->pend_cur_save.ensure(pl.n_regions * sizeof(u32)));
+    const u64 spill = budget / 16 + 4096;
+    OK(idx->pend_ovf.ensure(spill * sizeof(u64) * idx->nw));
+    OK(idx->pend_ovf_cur.ensure(sizeof(u32) * 2));
+    idx->pend_ovf_cap = (u32)std::min<u64>(spill, 0xffffffffULL);
+    CU(cudaMemsetAsync(idx->fine_cur.p, 0, pl.n_regions * sizeof(u32), idx->stream));
+    idx->pend_log_segs = pl.log_segs; idx->pend_cap = idx->cap; idx->pend_capf = (u32)capf; idx->pend_budget = budget;
+    idx->pend_req = idx->defer_budget;
+  }
+  if (idx->pend_keys + n_keys > idx->pend_budget) OK(flush_pending(idx));   // staging area full: one sweep, then go on
+  FineSink fs;
+  fs.keys = idx->fine_keys.as<u64>(); fs.cursor = idx->fine_cur.as<u32>(); fs.capf = idx->pend_capf; fs.log_f = pl.log_f;
+  if (idx->kev_pending) { CU(cudaStreamSynchronize(idx->stream)); harvest_commit_times(idx); }   // (a flush above left its events)
+  // the cursors as they are now: a scatter that exhausts the overflow region is rolled back to them
+  CU(cudaMemcpyAsync(idx->pend_cur_save.p, idx->fine_cur.p, pl.n_regions * sizeof(u32), cudaMemcpyDeviceToDevice, idx->stream));
+  CU(cudaEventRecord(idx->kev[0], idx->stream));
+  OK(fine_scatter_launch(idx, bs, pl, fs, n_keys));
+  CU(cudaEventRecord(idx->kev[1], idx->stream));
+  CU(cudaEventRecord(idx->kev[2], idx->stream));
+  CU(cudaEventRecord(idx->kev[3], idx->stream));
+  u64 perr = 0;
+  u32 n_ovf = 0;
+  CU(cudaMemcpyAsync(&n_ovf, ovf_cur(bs), sizeof(u32), cudaMemcpyDeviceToHost, idx->stream));
+  OK(read_ctr(idx, CTR_PERR, &perr));                     // (synchronises)
+  idx->kev_pending = true;
+  harvest_commit_times(idx);
+  if (perr & PERR_OVERFLOW) {
+    // skewed fine buckets exhausted the round's overflow region: take this round's appends back, settle what was staged
+    // before it, and let the caller commit the round on the regular path (which ends at the L2-atomic insert)
+    OK(zero_ctr(idx, CTR_PERR));
+    CU(cudaMemcpyAsync(ovf_cur(bs), &idx->h_ovf_cursor, sizeof(u32), cudaMemcpyHostToDevice, idx->stream));
+    CU(cudaMemcpyAsync(idx->fine_cur.p, idx->pend_cur_save.p, pl.n_regions * sizeof(u32), cudaMemcpyDeviceToDevice, idx->stream));
+    CU(cudaStreamSynchronize(idx->stream));
+    return KMI_OK;
+  }
+  if (n_ovf) {
+    // keys that did not fit their coarse / fine region sit in the round's own overflow region, which the next round reuses:
+    // they go into the table now, with global atomics (the table then is no longer untouched: the flush will read it)
+    if (idx->virgin && idx->slots) { idx->ops->table_clear(idx->stream, idx->slots, idx->cap); idx->launches++; idx->virgin = false; }
+    idx->ops->insert_overflow(idx->stream, idx->raw_view(), bs);
+    CU(cudaMemsetAsync(ovf_cur(bs), 0, sizeof(u32), idx->stream));
+    idx->launches++;
+  }
+  idx->pend_keys += n_keys;
+  idx->size_upper = need;
+  idx->size_exact = ~0ULL;
+  *staged = true;
+  return KMI_OK;
+}
+}  // namespace
+
 // Size the table for what the buckets hold, then insert them segment by segment. n_keys = keys
 // scattered this round; size_now = live keys in the table before the insert.
 int kmi::bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 size_now, const std::vector<u32>& reg, bool* not_inserted) {
   if (not_inserted) *not_inserted = false;
   if (n_keys == 0) return KMI_OK;
-  // distinct keys after this insert: at most size + n_keys, and (6 sigma) at most 1.05 * HLL + keys the HLL never saw
-  // (the registers see a 1/HLL_SAMPLE hash-sampled subset: scale back, add 6 sigma of the sampling error)
-  const double est = hll_estimate(reg.data()) * (double)HLL_SAMPLE;
-  const u64 by_hll = (u64)(est * 1.05 + 6.0 * std::sqrt(est * (double)HLL_SAMPLE)) + 4096 + idx->non_hll_upper;
-  const u64 need = std::min(size_now + n_keys, std::max(by_hll, size_now));
+  if (idx->defer_budget) {
+    bool staged = false;
+    OK(bucket_stage(idx, bs, n_keys, size_now, reg, &staged));
+    if (staged) return KMI_OK;
+  }
+  if (idx->pend_keys) {                                   // the regular path uses the staging buffers and may grow the table
+    OK(flush_pending(idx));
+    OK(read_ctr(idx, CTR_SIZE, &size_now));
+  }
+  const u64 need = need_after(idx, n_keys, size_now, reg);
   if (!idx->slots || (double)(need + idx->tombstones) > idx->cap * MAX_LOAD) {
     u64 want = pow2_at_least((u64)(need / MAX_LOAD) + 1);
     if (want > idx->cap || idx->tombstones) OK(table_grow(idx, std::max(want, idx->cap)));   // same capacity: purge tombstones
   }
   idx->size_upper = need;
   idx->size_exact = ~0ULL;  // stale until read back
-  // second level: table segments of <= 4096 slots (8192 beyond 2^31 slots) updated in shared memory
-  const int log_cap = __builtin_ctzll(idx->cap);
-  // (regions of the exchange buffer share only log_pre < 8 prefix bits: their fine scatter is wider, never skipped)
-  const int log_pre = (int)bs.log_pre;
-  const int log_seg_slots = idx->nw == 1 ? KMI_LOG_SEG_SLOTS : LOG_SEG_SLOTS2;
-  // (a receive buffer has `sub` regions per prefix: they always need the fine pass to become one region per segment)
-  int log_segs = std::max(std::max(LOG_BUCKETS, log_pre + ((log_pre < LOG_BUCKETS || bs.sub > 1) ? 1 : 0)), log_cap - log_seg_slots);
-  // beyond 2^9 fine buckets per coarse bucket the scatter runs shrink to one or two keys: very large tables take TWO
-  // fine passes instead (2^(log_f - 8) mid buckets, then 256 fine buckets inside every group of 256 mid regions)
-  const bool two_pass = log_pre == LOG_BUCKETS && log_segs - log_pre >= 10 && log_segs - log_pre <= 16;
-  if (!two_pass) log_segs = std::min(log_segs, log_pre + MAX_LOG_F);
-  const int log_seg = log_cap - log_segs;
-  if (idx->seg_path && idx->ops->insert_segments && log_seg <= (idx->nw == 1 ? 13 : 12) && log_seg >= 8) {
-    const u32 log_f = (u32)(log_segs - log_pre);
-    const u64 n_regions = (u64)1 << log_segs;
+  const SegPlan pl = seg_plan(idx, bs);
+  if (pl.ok) {
+    const u32 log_f = pl.log_f;
+    const u64 n_regions = pl.n_regions;
+    const int log_seg = pl.log_seg;
     FineSink fs;
     fs.log_f = log_f;
     bool fine_ok = true;
@@ -405,37 +627,10 @@ int kmi::bucket_commit(kmi_index* idx, const BucketSink& bs, u64 n_keys, u64 siz
       const u64 capf = (u64)(mean + 8.0 * std::sqrt(mean) + 32.0);
       OK(idx->fine_keys.ensure(n_regions * capf * sizeof(u64) * idx->nw));
       OK(idx->fine_cur.ensure(n_regions * sizeof(u32)));
+      idx->pend_log_segs = -1;                             // (the staging layout, if there was one, is gone)
       CU(cudaMemsetAsync(idx->fine_cur.p, 0, n_regions * sizeof(u32), idx->stream));
       fs.keys = idx->fine_keys.as<u64>(); fs.cursor = idx->fine_cur.as<u32>(); fs.capf = (u32)capf;
-      if (!two_pass) {
-        idx->ops->scatter_fine(idx->stream, bs, fs, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), n_keys);
-        idx->launches++;
-      } else {
-        FineSink mid;
-        mid.log_f = log_f - LOG_BUCKETS;
-        const u64 n_mid = (u64)N_BUCKETS << mid.log_f;
-        const double mean1 = (double)n_keys / (double)n_mid;
-        const u64 capm = (u64)(mean1 + 8.0 * std::sqrt(mean1) + 32.0);
-        OK(idx->mid_keys.ensure(n_mid * capm * sizeof(u64) * idx->nw));
-        OK(idx->mid_cur.ensure(n_mid * sizeof(u32)));
-        CU(cudaMemsetAsync(idx->mid_cur.p, 0, n_mid * sizeof(u32), idx->stream));
-        mid.keys = idx->mid_keys.as<u64>(); mid.cursor = idx->mid_cur.as<u32>(); mid.capf = (u32)capm;
-        idx->ops->scatter_fine(idx->stream, bs, mid, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), n_keys);
-        idx->launches++;
-        fs.log_f = LOG_BUCKETS;                            // per group of 256 mid regions
-        for (u64 g = 0; g < n_mid / N_BUCKETS; ++g) {
-          BucketSink bg;
-          bg.keys = mid.keys + g * N_BUCKETS * capm * idx->nw;
-          bg.cursor = mid.cursor + g * N_BUCKETS;
-          bg.capb = (u32)capm; bg.ovf_cap = bs.ovf_cap; bg.hll = nullptr; bg.bases = nullptr;
-          bg.log_pre = (u32)LOG_BUCKETS + mid.log_f; bg.pre_mask = N_BUCKETS - 1; bg.pre_base = (u32)(g * N_BUCKETS);
-          bg.ovf_keys = idx->nw == 1 ? ovf_base<1>(bs) : ovf_base<2>(bs); bg.ovf_cursor = ovf_cur(bs);
-          idx->ops->scatter_fine(idx->stream, bg, fs, reinterpret_cast<u32*>(idx->ctr + CTR_PERR), n_keys / (n_mid / N_BUCKETS) + 1);
-          idx->launches++;
-        }
-        fs.log_f = log_f;                                  // the insert sees 2^log_segs regions, as after a single pass
-      }
-      CU(cudaGetLastError());                              // a scatter that did not launch must not pass for an empty bucket
+      OK(fine_scatter_launch(idx, bs, pl, fs, n_keys));
       u64 perr = 0;
       OK(read_ctr(idx, CTR_PERR, &perr));
       if (perr & PERR_OVERFLOW) {
@@ -819,7 +1014,7 @@ static int build_fastq_impl(kmi_index* idx, uint8_t* d_bytes, size_t n, const ui
     idx->stage_ms[2] = idx->stage_ms[1] - idx->scatter_ms;
     idx->stage_ms[1] = idx->scatter_ms;
   }
-  idx->size_exact = idx->size_upper = host[CTR_SIZE];
+  if (!idx->pend_keys) idx->size_exact = idx->size_upper = host[CTR_SIZE];   // (staged keys are not in the counter yet)
   if (n_kmers) *n_kmers = host[CTR_NKMERS];
   OK(table_error(host[CTR_ERR]));
   return parse_error(host[CTR_PERR]);
@@ -1051,6 +1246,7 @@ extern "C" int kmi_erase(kmi_index* idx, const uint64_t* keys, size_t n) {
   if (!idx || (!keys && n)) return fail(KMI_ERR_ARG, "null argument");
   CU(cudaSetDevice(idx->cfg.device));
   if (n == 0 || !idx->slots) return KMI_OK;
+  OK(flush_pending(idx));
   OK(stage_query(idx, keys, n));
   OK(zero_ctr(idx, CTR_REMOVED));
   u64 live_before = 0;
@@ -1084,6 +1280,7 @@ extern "C" int kmi_erase(kmi_index* idx, const uint64_t* keys, size_t n) {
 extern "C" int kmi_num_keys(kmi_index* idx, uint64_t* n) {
   if (!idx || !n) return fail(KMI_ERR_ARG, "null argument");
   CU(cudaSetDevice(idx->cfg.device));
+  OK(flush_pending(idx));
   u64 v = 0;
   OK(read_ctr(idx, CTR_SIZE, &v));
   idx->size_exact = idx->size_upper = v;
@@ -1104,6 +1301,7 @@ extern "C" int kmi_local_size(kmi_index* idx, uint64_t* n) {
 extern "C" int kmi_dump(kmi_index* idx, uint64_t* keys, uint64_t* vals, size_t cap, size_t* n_out) {
   if (!idx || !n_out) return fail(KMI_ERR_ARG, "null argument");
   CU(cudaSetDevice(idx->cfg.device));
+  OK(flush_pending(idx));
   *n_out = 0;
   size_t kb = sizeof(u64) * idx->nw;
   if (idx->cfg.mode == KMI_MODE_POSITION) {
@@ -1230,7 +1428,8 @@ extern "C" int kmi_table_info(kmi_index* idx, uint64_t* slots, uint64_t* slot_by
     u64 b = idx->cap * idx->slot_bytes;
     const DevBuf* bufs[] = {&idx->tile_lines, &idx->block_sums, &idx->stage_in, &idx->stage_keys, &idx->stage_vals,
                             &idx->stage_out, &idx->stage_found, &idx->hist, &idx->hist_sums, &idx->log_keys, &idx->log_ids,
-                            &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->mid_keys, &idx->mid_cur};
+                            &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->mid_keys, &idx->mid_cur,
+                            &idx->pend_ovf, &idx->pend_ovf_cur, &idx->pend_cur_save};
     for (const DevBuf* d : bufs) b += d->cap;
     *device_bytes = b;
   }

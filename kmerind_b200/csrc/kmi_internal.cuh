@@ -50,6 +50,8 @@ enum { META_HLL = 512, META_WORDS = META_HLL + HLL_M };
 }  // namespace kmi
 
 struct kmi_dist_state;   // kmi_dist.cu
+struct kmi_index;
+namespace kmi { int flush_pending(kmi_index* idx); }   // kmi_api.cu: the deferred segment insert of bulk-load mode
 
 struct kmi_index {
   kmi_config cfg;
@@ -81,6 +83,16 @@ struct kmi_index {
   int seg_path = 1;        // KMI_PARAM_SEGMENT_INSERT: 1 = shared-memory segment insert where possible, 0 = L2 atomics
   bool hll_ready = false;
   kmi::u64 non_hll_upper = 0;   // keys inserted by paths that do not feed the HLL (upper bound on their distinct keys)
+  // KMI_PARAM_DEFER_INSERT (bulk load): fine buckets of several rounds / calls staged in fine_keys, inserted with ONE table sweep
+  kmi::u64 defer_budget = 0;    // 0 = off; else the number of keys the staging area is laid out for (clamped by free memory)
+  kmi::u64 pend_keys = 0;       // keys staged, not yet in the table
+  kmi::u64 pend_budget = 0;     // keys the current staging layout holds (the budget, clamped by free memory)
+  kmi::u64 pend_req = 0;        // the budget that layout was made for
+  int pend_log_segs = -1;       // the layout: 2^pend_log_segs regions, cut for a table of pend_cap slots
+  kmi::u64 pend_cap = 0;
+  kmi::u32 pend_capf = 0, pend_ovf_cap = 0;
+  kmi::DevBuf pend_ovf, pend_ovf_cur, pend_cur_save;   // spill list of the deferred insert; cursor snapshot for roll-back
+  kmi::u64 flushes = 0;         // deferred segment inserts run so far
   kmi::u32 dist_trans = 0; // KMI_PARAM_DIST_TRANS: transform under the dist hash of a non-canonical index (0 iden, 1 lex_less, 2 xor)
   bool saturate = false;   // KMI_PARAM_SATURATE: counts stick at 2^32 - 1; such an index builds with direct atomics (table_add)
   int build_path = 0;      // kmi_param KMI_PARAM_BUILD_PATH: 0 auto, 1 direct atomics, 2 bucketed
@@ -102,6 +114,7 @@ struct kmi_index {
   // never pays the 16 B/slot clear nor the read of empty segments; everything else goes through view(), which clears first.
   bool virgin = false;
   void touch() {
+    if (pend_keys) kmi::flush_pending(this);   // bulk-load mode: whatever looks at the table sees every staged key
     if (virgin && slots) { ops->table_clear(stream, slots, cap); launches++; }
     virgin = false;
   }

@@ -144,7 +144,7 @@ def test_sharded_index_from_cpp_main(tmp_path, k, reads, push):
     assert ("path 2" if push == "0" else "path 1") in r.stdout, r.stdout
 
 
-def _world_worker(rank, world, port, out_dir, k, n_reads, rounds_env):
+def _world_worker(rank, world, port, out_dir, k, n_reads, rounds_env, defer=0):
     _init(rank, world, port)
     if rounds_env:
         os.environ["KMI_DIST_ROUND_BYTES"] = rounds_env
@@ -154,6 +154,8 @@ def _world_worker(rank, world, port, out_dir, k, n_reads, rounds_env):
         torch.cuda.set_device(rank)
         buf = ou.synth_fastq(rank * n_reads, n_reads, 150, 5 * n_reads * world, 11, 5000, 0)
         with ShardedIndex(k, hash=kb.HASH_FARM, device=rank) as idx:
+            if defer:
+                idx.local.set_defer_insert(defer)       # bulk load: received keys are staged, one table sweep per flush
             text = torch.from_numpy(np.concatenate([buf, np.zeros(64, np.uint8)])).cuda()
             n = idx.build_fastq_dev(text.data_ptr(), buf.size)
             assert n == n_reads * (150 - k + 1)
@@ -176,15 +178,15 @@ def _world_worker(rank, world, port, out_dir, k, n_reads, rounds_env):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("k,rounds", [(31, None), (31, str(8 << 20)), (63, None)])
-def test_sharded_build_equals_reference_per_rank(tmp_path, k, rounds):
+@pytest.mark.parametrize("k,rounds,defer", [(31, None, 0), (31, str(8 << 20), 0), (63, None, 0), (31, None, 40000000), (63, str(8 << 20), 40000000)])
+def test_sharded_build_equals_reference_per_rank(tmp_path, k, rounds, defer):
     """Every rank's shard must be what the REFERENCE's rank holds at p = world: local_size and the content checksum against
     oracle/_ref (reference Kmer / lex_less / farm KeyToRank / dense_hash_map, p ranks over the same blocks), where that was
     built; else against the C oracle's owner split. rounds: several parse/push rounds per build."""
     import kmerind_b200 as kb
     world = max(torch.cuda.device_count(), 1)
     n_reads = 90000
-    mp.spawn(_world_worker, args=(world, _free_port(), str(tmp_path), k, n_reads, rounds), nprocs=world, join=True)
+    mp.spawn(_world_worker, args=(world, _free_port(), str(tmp_path), k, n_reads, rounds, defer), nprocs=world, join=True)
     texts = [ou.synth_fastq(r * n_reads, n_reads, 150, 5 * n_reads * world, 11, 5000, 0) for r in range(world)]
     whole = np.concatenate(texts)
     cuts = [r * texts[0].size for r in range(world + 1)]
