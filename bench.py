@@ -681,13 +681,29 @@ def run_pos21(args):
     qd = torch.empty(n_q, dtype=torch.int64, device=device)
     kb.synth_queries_dev(lr, qd.data_ptr(), rank * n_q, n_q, k, n_seq, seq_len, SEED, 4)
     q = qd.cpu().numpy().view(np.uint64)
-    del qd
+    # the same batch with the queries resident in HBM and the answers left there: the probe + owner exchange without the host
+    cd = torch.zeros(n_q, dtype=torch.int64, device=device)
+    count_dev = (lambda: idx.count_dev(qd.data_ptr(), n_q, cd.data_ptr())) if world > 1 else (lambda: idx.count_dev(qd.data_ptr(), n_q, cd.data_ptr()))
+    count_dev()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(3):
+        count_dev()
+    ev1.record()
+    torch.cuda.synchronize()
+    t_count_dev = ev0.elapsed_time(ev1) / 3.0 * 1e-3
+    counts_dev = cd.cpu().numpy().view(np.uint64).copy()
+    del qd, cd
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     counts = idx.count(q)
     t_count = time.perf_counter() - t0
     hits = counts[0::2]
     ok_q = bool((hits >= 1).all())                          # every genome query is present (both strands are stored canonically)
+    ok_q = ok_q and bool(np.array_equal(counts, counts_dev))
     n_find = min(n_q, int(os.environ.get("KMI_BENCH_FIND", "20000000")))
     t0 = time.perf_counter()
     off, vals = idx.find_positions(q[:n_find], cap=int(counts[:n_find].sum()))
@@ -700,12 +716,12 @@ def run_pos21(args):
         for v in vals[int(off[j]):int(off[j + 1])][:2]:
             fo = int(v) & ((1 << 40) - 1)
             pos_ok = pos_ok and 0 <= fo < fbytes
-    tq = torch.tensor([t_count, t_find], dtype=torch.float64, device=device)
+    tq = torch.tensor([t_count, t_find, t_count_dev], dtype=torch.float64, device=device)
     flags = np.array([1 if (ok_build and ok_q and pos_ok) else 0], dtype=np.uint64)
     if world > 1:
         dist.all_reduce(tq, op=dist.ReduceOp.MAX)
         flags = idx.comm.allreduce(flags, "min")
-    t_count, t_find = float(tq[0].item()), float(tq[1].item())
+    t_count, t_find, t_count_dev = float(tq[0].item()), float(tq[1].item()), float(tq[2].item())
     assert flags[0] == 1, "pos21 checks failed: build %s queries %s positions %s" % (ok_build, ok_q, pos_ok)
     peak, peak_kind = measured_peaks()
     info = local.table_info()
@@ -727,6 +743,12 @@ def run_pos21(args):
                              "alg_bytes_per_kmer": alg},
                 "query": {"count": {"value": n_q * world / t_count, "unit": "queries/s", "seconds": t_count,
                                     "how": "host keys in, multiplicities out (H2D, owner exchange over NCCL, probe, answers back, D2H)"},
+                          "count_dev": {"value": n_q * world / t_count_dev, "unit": "queries/s", "seconds": t_count_dev,
+                                        "how": "queries resident in HBM, answers left there (kmi_%scount_dev), CUDA events, mean of 3" % ("dist_" if world > 1 else ""),
+                                        "roofline": {"bound": "hbm", "alg_bytes_per_query": 36.0 + (32.0 if world > 1 else 0.0),
+                                                     "achieved": (36.0 + (32.0 if world > 1 else 0.0)) * n_q / t_count_dev / 1e9, "peak": peak, "unit": "GB/s",
+                                                     "frac": (36.0 + (32.0 if world > 1 else 0.0)) * n_q / t_count_dev / 1e9 / peak,
+                                                     "note": "36 B/query = key 8 + slot 12 + answer 16 (SURVEY 8d); sharded: + 24 B partition of (key, tag) + 8 B un-permute; NVLink 8 B out + 8 B back per query"}},
                           "find_positions": {"value": n_find * world / t_find, "unit": "queries/s", "seconds": t_find, "queries_per_gpu": n_find,
                                              "ids_returned_rank0": int(off[-1])}},
                 "parity": {"ok": True, "tuples": [int(size), int(n_kmers_total)],

@@ -323,6 +323,9 @@ int kmi_dist_count(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* cou
 int kmi_dist_find(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* vals, uint8_t* found);
 int kmi_dist_find_positions(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* offsets, uint64_t* vals, size_t cap);
 int kmi_dist_erase(kmi_index* idx, const uint64_t* keys, size_t n);
+/* the same batch queries with the keys already in HBM and the answers left there (input order) */
+int kmi_dist_count_dev(kmi_index* idx, const uint64_t* d_keys, size_t n, uint64_t* d_counts);
+int kmi_dist_find_dev(kmi_index* idx, const uint64_t* d_keys, size_t n, uint64_t* d_vals, uint8_t* d_found);
 int kmi_dist_size(kmi_index* idx, uint64_t* n);
 /* last sharded build: device ms [0] whole, [1] parse + push / exchange, [2] insert of the received keys, [3] unused; keys this
  * rank received; path 1 = NVLink push, 2 = NCCL all-to-all */

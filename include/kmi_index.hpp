@@ -194,6 +194,9 @@ struct map_options {
   bool nsplit = false;          // NSplitSequencesIterator instead of SequencesIterator
   int device = 0;
   uint64_t reserve = 0;
+  int dist_trans = 0;           // non-canonical maps: DistTrans under the dist hash, 0 identity / 1 lex_less / 2 xor_rev_comp
+                                // (SingleStrandHashMapParams<Key, DistHash, StoreHash, DistTrans>, BenchmarkKmerIndex.cpp:152-161)
+  uint64_t bulk_load_keys = 0;  // COUNT maps: KMI_PARAM_DEFER_INSERT staging budget (0 = every build inserts at once)
 };
 
 template <typename Key, typename T, int Mode>
@@ -451,6 +454,8 @@ class b200_map {
     cfg.k = (int32_t)K; cfg.mode = Mode; cfg.canonical = o.canonical ? 1 : 0; cfg.hash = o.hash; cfg.nsplit = o.nsplit ? 1 : 0;
     cfg.device = o.device; cfg.rank = comm_.rank(); cfg.nranks = comm_.size(); cfg.reserve = o.reserve;
     check(kmi_create(&cfg, &h_));
+    if (o.dist_trans) check(kmi_set_param(h_, KMI_PARAM_DIST_TRANS, o.dist_trans));
+    if (o.bulk_load_keys && Mode == KMI_MODE_COUNT) check(kmi_set_param(h_, KMI_PARAM_DEFER_INSERT, (int64_t)o.bulk_load_keys));
   }
   /// per query key i its values vals[off[i] .. off[i+1]): COUNT 0 or 1 value (the frequency), POSITION every id
   void lookup(std::vector<Key>& keys, std::vector<uint64_t>& off, std::vector<uint64_t>& vals) const {
@@ -482,6 +487,198 @@ class b200_map {
   bool canonical_ = true;
   kmi_index* h_ = nullptr;
   mutable std::vector<value_type> snapshot_;
+};
+
+/// The sort-based MapType: dsc::counting_sorted_map (Mode COUNT) / dsc::sorted_multimap (Mode POSITION) of
+/// reference src/containers/distributed_sorted_map.hpp — what BenchmarkKmerIndex.cpp:206-219 picks for pMAP == SORTED — over
+/// kmi_sorted_* (device radix sort + run-length reduction, binary-search queries). Same member shapes as b200_map for what
+/// Index<> forwards (insert / find / count / size / local_size / to_vector / reserve); ONE rank only, as the C layer.
+template <typename Key, typename T, int Mode>
+class b200_sorted_map {
+  static_assert(sizeof(Key) == 8 || sizeof(Key) == 16, "Key must be 1 or 2 uint64_t words");
+
+ public:
+  using key_type = Key;
+  using mapped_type = T;
+  using value_type = std::pair<Key, T>;
+  using const_iterator = typename std::vector<value_type>::const_iterator;
+  static constexpr unsigned K = Key::size;
+
+  template <typename Comm>
+  explicit b200_sorted_map(const Comm& c, const map_options& o = map_options()) : canonical_(o.canonical) {
+    if (c.size() != 1) throw std::invalid_argument("b200_sorted_map spans one rank");
+    create(o);
+  }
+  explicit b200_sorted_map(const map_options& o = map_options()) : canonical_(o.canonical) { create(o); }
+  ~b200_sorted_map() { kmi_sorted_destroy(h_); }
+  b200_sorted_map(const b200_sorted_map&) = delete;
+  b200_sorted_map& operator=(const b200_sorted_map&) = delete;
+
+  /// sorted_map_base::insert (distributed_sorted_map.hpp:1186-1300): appended; sorted and reduced by the next rehash / query
+  size_t insert(std::vector<Key>& keys) {
+    if (Mode != KMI_MODE_COUNT) throw std::invalid_argument("a sorted multimap inserts (key, id) tuples");
+    check(kmi_sorted_insert(h_, reinterpret_cast<const uint64_t*>(keys.data()), nullptr, keys.size()));
+    return keys.size();
+  }
+  size_t insert(std::vector<value_type>& tuples) {
+    std::vector<uint64_t> k(tuples.size() * nw()), v(tuples.size());
+    for (size_t i = 0; i < tuples.size(); ++i) {
+      std::memcpy(&k[i * nw()], tuples[i].first.getData(), sizeof(Key));
+      uint64_t id = 0;
+      std::memcpy(&id, &tuples[i].second, sizeof(T) < 8 ? sizeof(T) : 8);
+      v[i] = id;
+    }
+    check(kmi_sorted_insert(h_, k.data(), v.data(), tuples.size()));
+    return tuples.size();
+  }
+  size_t build_fastq(const uint8_t* bytes, size_t n, uint64_t file_offset = 0) {
+    uint64_t m = 0;
+    check(kmi_sorted_build_fastq(h_, bytes, n, file_offset, &m));
+    return (size_t)m;
+  }
+  size_t build_fasta(const uint8_t* bytes, size_t n) {
+    uint64_t m = 0;
+    check(kmi_sorted_build_fasta(h_, bytes, n, &m));
+    return (size_t)m;
+  }
+  /// local_reduction + sort (distributed_sorted_map.hpp:1521-1540,1601-1700 at one rank)
+  void rehash() { check(kmi_sorted_rehash(h_)); }
+  void reserve(size_t) {}
+  std::vector<value_type> find(std::vector<Key>& keys) const {
+    transform_input(keys);
+    const uint64_t* kp = reinterpret_cast<const uint64_t*>(keys.data());
+    std::vector<value_type> out;
+    if (Mode == KMI_MODE_COUNT) {
+      std::vector<uint64_t> v(keys.size());
+      std::vector<uint8_t> found(keys.size());
+      check(kmi_sorted_find(h_, kp, keys.size(), v.data(), found.data()));
+      for (size_t i = 0; i < keys.size(); ++i) if (found[i]) out.emplace_back(keys[i], from_u64(v[i]));
+    } else {
+      std::vector<uint64_t> cnt(keys.size()), off(keys.size() + 1, 0);
+      check(kmi_sorted_count(h_, kp, keys.size(), cnt.data()));
+      uint64_t total = 0;
+      for (uint64_t c : cnt) total += c;
+      std::vector<uint64_t> vals(total ? total : 1);
+      check(kmi_sorted_find_positions(h_, kp, keys.size(), off.data(), vals.data(), total));
+      for (size_t i = 0; i < keys.size(); ++i)
+        for (uint64_t j = off[i]; j < off[i + 1]; ++j) out.emplace_back(keys[i], from_u64(vals[j]));
+    }
+    return out;
+  }
+  std::vector<std::pair<Key, size_t>> count(std::vector<Key>& keys) const {
+    transform_input(keys);
+    std::vector<uint64_t> cnt(keys.size());
+    check(kmi_sorted_count(h_, reinterpret_cast<const uint64_t*>(keys.data()), keys.size(), cnt.data()));
+    std::vector<std::pair<Key, size_t>> out;
+    out.reserve(keys.size());
+    for (size_t i = 0; i < keys.size(); ++i) out.emplace_back(keys[i], (size_t)cnt[i]);
+    return out;
+  }
+  size_t local_size() const {
+    uint64_t n = 0;
+    check(kmi_sorted_local_size(h_, &n));
+    return (size_t)n;
+  }
+  size_t size() const { return local_size(); }
+  /// the container itself: entries in key order (a sorted_map's vector after rehash)
+  std::vector<value_type> to_vector() const {
+    const size_t n = local_size();
+    std::vector<uint64_t> k(n * nw() + 1), v(n + 1);
+    size_t got = 0;
+    check(kmi_sorted_dump(h_, k.data(), v.data(), n, &got));
+    std::vector<value_type> out(got);
+    for (size_t i = 0; i < got; ++i) {
+      std::memcpy(out[i].first.getDataRef(), &k[i * nw()], sizeof(Key));
+      out[i].second = from_u64(v[i]);
+    }
+    return out;
+  }
+  void to_vector(std::vector<value_type>& out) const { out = to_vector(); }
+  kmi_sorted* handle() const { return h_; }
+
+ private:
+  static constexpr size_t nw() { return sizeof(Key) / 8; }
+  void transform_input(std::vector<Key>& keys) const {
+    if (canonical_) for (Key& k : keys) canonical_words(k.getDataRef(), K);
+  }
+  void create(const map_options& o) {
+    kmi_config cfg;
+    cfg.k = (int32_t)K; cfg.mode = Mode; cfg.canonical = o.canonical ? 1 : 0; cfg.hash = o.hash; cfg.nsplit = o.nsplit ? 1 : 0;
+    cfg.device = o.device; cfg.rank = 0; cfg.nranks = 1; cfg.reserve = 0;
+    check(kmi_sorted_create(&cfg, &h_));
+  }
+  static T from_u64(uint64_t v) { T t; std::memset(&t, 0, sizeof(T)); std::memcpy(&t, &v, sizeof(T) < 8 ? sizeof(T) : 8); return t; }
+  bool canonical_ = true;
+  kmi_sorted* h_ = nullptr;
+};
+
+/// PositionQualityIndex's map (kmer_index.hpp:406, BenchmarkKmerIndex.cpp:131-137): k-mer -> (position id,
+/// quality score), built from FASTQ bytes by kmi_posqual_* (the scores are KmerPositionQualityTupleParser's,
+/// src/io/kmer_parser.hpp:578-760). mapped_type = std::pair<uint64_t, float>, the reference's KmerInfoType with the id as its
+/// raw 64-bit word. One rank.
+template <typename Key>
+class b200_posqual_map {
+ public:
+  using key_type = Key;
+  using mapped_type = std::pair<uint64_t, float>;
+  using value_type = std::pair<Key, mapped_type>;
+  static constexpr unsigned K = Key::size;
+
+  explicit b200_posqual_map(const map_options& o = map_options()) : canonical_(o.canonical) {
+    kmi_config cfg;
+    cfg.k = (int32_t)K; cfg.mode = KMI_MODE_POSITION; cfg.canonical = o.canonical ? 1 : 0; cfg.hash = o.hash; cfg.nsplit = o.nsplit ? 1 : 0;
+    cfg.device = o.device; cfg.rank = 0; cfg.nranks = 1; cfg.reserve = o.reserve;
+    check(kmi_posqual_create(&cfg, &h_));
+  }
+  ~b200_posqual_map() { kmi_posqual_destroy(h_); }
+  b200_posqual_map(const b200_posqual_map&) = delete;
+  b200_posqual_map& operator=(const b200_posqual_map&) = delete;
+
+  size_t build_fastq(const uint8_t* bytes, size_t n, uint64_t file_offset = 0) {
+    uint64_t m = 0;
+    check(kmi_posqual_build_fastq(h_, bytes, n, file_offset, &m));
+    return (size_t)m;
+  }
+  std::vector<value_type> find(std::vector<Key>& keys) const {
+    if (canonical_) for (Key& k : keys) canonical_words(k.getDataRef(), K);
+    const uint64_t* kp = reinterpret_cast<const uint64_t*>(keys.data());
+    std::vector<uint64_t> cnt(keys.size()), off(keys.size() + 1, 0);
+    check(kmi_posqual_count(h_, kp, keys.size(), cnt.data()));
+    uint64_t total = 0;
+    for (uint64_t c : cnt) total += c;
+    std::vector<uint64_t> ids(total ? total : 1);
+    std::vector<float> q(total ? total : 1);
+    check(kmi_posqual_find(h_, kp, keys.size(), off.data(), ids.data(), q.data(), total));
+    std::vector<value_type> out;
+    out.reserve(total);
+    for (size_t i = 0; i < keys.size(); ++i)
+      for (uint64_t j = off[i]; j < off[i + 1]; ++j) out.emplace_back(keys[i], mapped_type(ids[j], q[j]));
+    return out;
+  }
+  size_t local_size() const {
+    uint64_t n = 0;
+    check(kmi_posqual_local_size(h_, &n));
+    return (size_t)n;
+  }
+  size_t size() const { return local_size(); }
+  std::vector<value_type> to_vector() const {
+    const size_t n = local_size();
+    std::vector<uint64_t> k(n * (sizeof(Key) / 8) + 1), ids(n + 1);
+    std::vector<float> q(n + 1);
+    size_t got = 0;
+    check(kmi_posqual_dump(h_, k.data(), ids.data(), q.data(), n, &got));
+    std::vector<value_type> out(got);
+    for (size_t i = 0; i < got; ++i) {
+      std::memcpy(out[i].first.getDataRef(), &k[i * (sizeof(Key) / 8)], sizeof(Key));
+      out[i].second = mapped_type(ids[i], q[i]);
+    }
+    return out;
+  }
+  kmi_posqual* handle() const { return h_; }
+
+ private:
+  bool canonical_ = true;
+  kmi_posqual* h_ = nullptr;
 };
 
 /// standalone aliases mirroring bliss::index::kmer::CountIndex / PositionIndex (kmer_index.hpp:402-409)

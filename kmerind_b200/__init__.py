@@ -83,6 +83,7 @@ def load_library(build_if_missing=False):
         "kmi_dist_build_fasta": [_P, _P, _SZ, _P, _P], "kmi_dist_build_fasta_dev": [_P, _P, _SZ, _P, _P],
         "kmi_dist_insert": [_P, _P, _P, _SZ], "kmi_dist_insert_dev": [_P, _P, _P, _SZ],
         "kmi_dist_count": [_P, _P, _SZ, _P], "kmi_dist_find": [_P, _P, _SZ, _P, _P],
+        "kmi_dist_count_dev": [_P, _P, _SZ, _P], "kmi_dist_find_dev": [_P, _P, _SZ, _P, _P],
         "kmi_dist_find_positions": [_P, _P, _SZ, _P, _P, _SZ], "kmi_dist_erase": [_P, _P, _SZ],
         "kmi_dist_size": [_P, _P], "kmi_dist_last_stats": [_P, _P, _P, _P],
         "kmi_fastq_find_first_record": [_P, _U64, _SZ, _U64, _U64, _U64, _U64, _P],
@@ -141,7 +142,7 @@ EXPORTED_SYMBOLS = (
     "kmi_comm_unique_id", "kmi_comm_create", "kmi_comm_destroy", "kmi_comm_rank", "kmi_comm_size", "kmi_comm_barrier",
     "kmi_comm_allreduce_u64", "kmi_comm_allgather_u64", "kmi_dist_attach", "kmi_dist_build_fastq", "kmi_dist_build_fastq_dev",
     "kmi_dist_build_fasta", "kmi_dist_build_fasta_dev", "kmi_dist_insert", "kmi_dist_insert_dev", "kmi_dist_count", "kmi_dist_find",
-    "kmi_dist_find_positions", "kmi_dist_erase", "kmi_dist_size", "kmi_dist_last_stats", "kmi_canonicalize_dev", "kmi_hash_dev",
+    "kmi_dist_find_positions", "kmi_dist_erase", "kmi_dist_count_dev", "kmi_dist_find_dev", "kmi_dist_size", "kmi_dist_last_stats", "kmi_canonicalize_dev", "kmi_hash_dev",
     "kmi_partition_dev", "kmi_partition_noalloc_dev", "kmi_partition_noalloc_max_keys", "kmi_insert", "kmi_insert_dev", "kmi_count", "kmi_find", "kmi_find_positions",
     "kmi_erase", "kmi_count_dev", "kmi_find_dev", "kmi_local_size", "kmi_num_keys", "kmi_dump",
     "kmi_checksum", "kmi_count_if", "kmi_dump_if", "kmi_erase_if", "kmi_table_info", "kmi_launch_count", "kmi_last_stage_ms", "kmi_last_kernel_ms",

@@ -478,7 +478,9 @@ extern "C" int kmi_dist_insert(kmi_index* idx, const uint64_t* keys, const uint6
 
 // ---- batched query: canonicalise -> distribute -> local probe -> answers back along the transposed counts
 // (distributed_densehash_map.hpp:1122-1216); answers are delivered in INPUT order
-static int dist_query(kmi_index* idx, const uint64_t* keys, size_t n, int what /*0 count, 1 find, 2 erase*/, uint64_t* vals, uint8_t* found) {
+// `dev`: keys / vals / found are DEVICE pointers (queries already resident in HBM, answers left there)
+static int dist_query(kmi_index* idx, const uint64_t* keys, size_t n, int what /*0 count, 1 find, 2 erase*/, uint64_t* vals, uint8_t* found,
+                      bool dev = false) {
   kmi_dist_state* d = dist_of(idx);
   if (!d || (!keys && n)) return fail(KMI_ERR_ARG, "kmi_dist_attach first");
   CU(cudaSetDevice(idx->cfg.device));
@@ -487,7 +489,7 @@ static int dist_query(kmi_index* idx, const uint64_t* keys, size_t n, int what /
   OK(d->q_keys.ensure(std::max<size_t>(n, 1) * kb));
   OK(d->q_tags.ensure(std::max<size_t>(n, 1) * sizeof(u64)));
   if (n) {
-    CU(cudaMemcpyAsync(d->q_keys.p, keys, n * kb, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d->q_keys.p, keys, n * kb, dev ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
     k_iota<<<grid_for(n, 256), 256, 0, st>>>(d->q_tags.as<u64>(), n);
   }
   std::vector<u64> sc, rc;
@@ -545,8 +547,8 @@ static int dist_query(kmi_index* idx, const uint64_t* keys, size_t n, int what /
     OK(d->ids.ensure(n));
     k_unpermute<<<grid_for(n, 256), 256, 0, st>>>(d->part_vals.as<u64>(), d->q_back.as<u64>(), (what == 1 && found) ? d->q_backf.as<uint8_t>() : nullptr,
                                                  d->recv_vals.as<u64>(), (what == 1 && found) ? d->ids.as<uint8_t>() : nullptr, n);
-    if (vals) CU(cudaMemcpyAsync(vals, d->recv_vals.p, n * sizeof(u64), cudaMemcpyDeviceToHost, st));
-    if (what == 1 && found) CU(cudaMemcpyAsync(found, d->ids.p, n, cudaMemcpyDeviceToHost, st));
+    if (vals) CU(cudaMemcpyAsync(vals, d->recv_vals.p, n * sizeof(u64), dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
+    if (what == 1 && found) CU(cudaMemcpyAsync(found, d->ids.p, n, dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
   }
   CU(cudaStreamSynchronize(st));
   return KMI_OK;
@@ -559,6 +561,13 @@ extern "C" int kmi_dist_find(kmi_index* idx, const uint64_t* keys, size_t n, uin
   return dist_query(idx, keys, n, 1, vals, found);
 }
 extern "C" int kmi_dist_erase(kmi_index* idx, const uint64_t* keys, size_t n) { return dist_query(idx, keys, n, 2, nullptr, nullptr); }
+extern "C" int kmi_dist_count_dev(kmi_index* idx, const uint64_t* d_keys, size_t n, uint64_t* d_counts) {
+  if (!d_counts && n) return fail(KMI_ERR_ARG, "null argument");
+  return dist_query(idx, d_keys, n, 0, d_counts, nullptr, true);
+}
+extern "C" int kmi_dist_find_dev(kmi_index* idx, const uint64_t* d_keys, size_t n, uint64_t* d_vals, uint8_t* d_found) {
+  return dist_query(idx, d_keys, n, 1, d_vals, d_found, true);
+}
 
 // find on a sharded PositionIndex: every id of every query key (LocalFind of the multimap, :2094-2133), CSR in input order.
 // Two round trips: the multiplicities come back first (they size the second answer), then the ids.

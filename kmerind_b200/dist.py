@@ -154,6 +154,13 @@ class ShardedIndex:
         _check(self._lib.kmi_dist_count(self.local._h, _hptr(a), a.shape[0], _hptr(out)))
         return out
 
+    def count_dev(self, d_keys, n, d_counts):
+        """queries resident in HBM, answers left there (kmi_dist_count_dev); collective"""
+        _check(self._lib.kmi_dist_count_dev(self.local._h, d_keys, n, d_counts))
+
+    def find_dev(self, d_keys, n, d_vals, d_found):
+        _check(self._lib.kmi_dist_find_dev(self.local._h, d_keys, n, d_vals, d_found))
+
     def find(self, keys):
         a = _as_keys(keys, self.nw)
         vals = np.zeros(a.shape[0], dtype=np.uint64)

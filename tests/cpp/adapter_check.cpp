@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <map>
 #include <random>
+#include <string>
 #include <vector>
 
 #include "kmi_index.hpp"
@@ -263,7 +264,90 @@ static int position_checks() {
   return 0;
 }
 
+// the sort-based MapType (dsc::counting_sorted_map / sorted_multimap's member shapes) against std::map, and the
+// PositionQualityIndex map: ids equal the position map's, scores in (0, 1] for 'I' qualities
+template <unsigned K>
+static int sorted_checks() {
+  using Key = KeyT<K>;
+  using Map = kmi::b200_sorted_map<Key, uint32_t, KMI_MODE_COUNT>;
+  using V = typename Map::value_type;
+  std::mt19937_64 rng(100 + K);
+  std::vector<Key> pool;
+  for (int i = 0; i < 2000; ++i) pool.push_back(random_kmer<K>(rng));
+  std::vector<Key> input;
+  std::map<Key, uint32_t> want;
+  for (int i = 0; i < 15000; ++i) {
+    Key k = pool[(rng() % 2000) * (rng() % 2000) / 2000];
+    if (rng() & 1) k = k.reverse_complement();
+    input.push_back(k);
+    ++want[canon(k)];
+  }
+  Map m{ref_like_comm()};
+  std::vector<Key> in2 = input;
+  CHECK(m.insert(in2) == input.size());
+  CHECK(m.size() == want.size());
+  std::vector<V> all = m.to_vector();                      // in key order, as the reference's sorted vector
+  CHECK(all.size() == want.size());
+  size_t i = 0;
+  for (const auto& kv : want) { CHECK(all[i].first == kv.first && all[i].second == kv.second); ++i; }
+  std::vector<Key> q(pool.begin(), pool.begin() + 300);
+  for (int j = 0; j < 50; ++j) q.push_back(random_kmer<K>(rng));
+  std::vector<Key> qq = q;
+  auto cnt = m.count(qq);
+  qq = q;
+  auto found = m.find(qq);
+  size_t hits = 0;
+  for (size_t j = 0; j < q.size(); ++j) {
+    auto it = want.find(canon(q[j]));
+    CHECK(cnt[j].second == (it != want.end() ? 1u : 0u));
+    hits += it != want.end();
+  }
+  CHECK(found.size() == hits);
+  for (const V& f : found) CHECK(want.at(f.first) == f.second);
+  std::vector<V> more;
+  more.emplace_back(all[0].first, 7u);
+  m.insert(more);
+  all = m.to_vector();
+  CHECK(all[0].second == want.begin()->second + 7u);
+  return 0;
+}
+
+static int posqual_checks() {
+  using Key = KeyT<21>;
+  std::mt19937_64 rng(5);
+  std::string fq;
+  const char* acgt = "ACGT";
+  for (int r = 0; r < 200; ++r) {
+    std::string seq;
+    for (int b = 0; b < 100; ++b) seq += acgt[rng() & 3];
+    fq += "@r" + std::to_string(r) + "\n" + seq + "\n+\n" + std::string(100, 'I') + "\n";
+  }
+  kmi::b200_posqual_map<Key> pq;
+  kmi::b200_map<Key, uint64_t, KMI_MODE_POSITION> pos{ref_like_comm()};
+  const size_t n = pq.build_fastq(reinterpret_cast<const uint8_t*>(fq.data()), fq.size());
+  CHECK(n == 200u * 80u && pq.size() == n);
+  CHECK(pos.build_fastq(reinterpret_cast<const uint8_t*>(fq.data()), fq.size()) == n);
+  auto a = pq.to_vector();
+  auto b = pos.to_vector();
+  std::vector<std::pair<Key, uint64_t>> ai;
+  for (const auto& t : a) {
+    ai.emplace_back(t.first, t.second.first);
+    CHECK(t.second.second > 0.99f && t.second.second <= 1.0f);   // 21 bases of Phred 40: (1 - 1e-4)^21
+  }
+  sort_pairs(ai);
+  sort_pairs(b);
+  CHECK(ai == b);
+  std::vector<Key> q;
+  for (size_t j = 0; j < a.size(); j += 97) q.push_back(a[j].first.reverse_complement());
+  auto f = pq.find(q);
+  CHECK(f.size() >= q.size());
+  return 0;
+}
+
 int main() {
+  if (sorted_checks<31>()) return 1;
+  if (sorted_checks<47>()) return 1;
+  if (posqual_checks()) return 1;
   if (count_checks<21>()) return 1;
   if (count_checks<31>()) return 1;
   if (count_checks<63>()) return 1;

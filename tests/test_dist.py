@@ -173,6 +173,17 @@ def _world_worker(rank, world, port, out_dir, k, n_reads, rounds_env, defer=0):
             np.save(os.path.join(out_dir, "q%d.npy" % rank), keys)
             np.save(os.path.join(out_dir, "v%d.npy" % rank), vals)
             assert found.all()
+            # the same batch with the queries resident in HBM and the answers left there
+            dk = torch.from_numpy(np.ascontiguousarray(keys).view(np.int64).reshape(-1)).cuda()
+            nq = len(keys)
+            dv = torch.zeros(nq, dtype=torch.int64, device="cuda")
+            df = torch.zeros(nq, dtype=torch.uint8, device="cuda")
+            dc = torch.zeros(nq, dtype=torch.int64, device="cuda")
+            idx.find_dev(dk.data_ptr(), nq, dv.data_ptr(), df.data_ptr())
+            idx.count_dev(dk.data_ptr(), nq, dc.data_ptr())
+            torch.cuda.synchronize()
+            assert np.array_equal(dv.cpu().numpy().view(np.uint64), vals) and bool(df.cpu().numpy().all())
+            assert np.array_equal(dc.cpu().numpy().view(np.uint64), idx.count(keys))
     finally:
         dist.destroy_process_group()
 
