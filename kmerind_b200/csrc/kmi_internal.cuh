@@ -72,6 +72,7 @@ struct kmi_index {
   kmi::DevBuf mid_keys, mid_cur;        // first of two fine passes (very large tables)
   kmi::DevBuf parse_keys, parse_ids;   // staging of the parse -> insert builds (FASTA, FASTQ positions): kept between calls
   kmi::DevBuf tile_rec;   // FASTQ position ids: record start open at every tile (k_fastq_rec_carry)
+  kmi::DevBuf q_perm_keys, q_perm_pos, q_perm_vals, q_perm_found;   // large query batches probed in table order (kmi_find_dev)
   kmi::DevBuf tile_lines, block_sums, stage_in, stage_keys, stage_vals, stage_out, stage_found, hist, hist_sums;
   // POSITION mode: tuple log + CSR
   kmi::DevBuf log_keys, log_ids, log_keys2, log_ids2, offsets, csr_sums, values;

@@ -525,6 +525,58 @@ def test_partition_dist_transform(k):
         idx.set_dist_trans(1)
 
 
+@pytest.mark.parametrize("k,mode", ((31, kb.MODE_COUNT), (63, kb.MODE_COUNT), (21, kb.MODE_POSITION)))
+def test_large_query_batches_in_table_order_equal_small_batches(k, mode):
+    """kmi_find_dev / kmi_count_dev sort batches of >= 2^20 queries by hash prefix, probe in table order and gather the answers
+    back (k_q_hist / k_q_scatter / k_q_gather) when the table is larger than the L2: same answers, in input order, as the
+    plain probe that smaller batches take — and as the oracle's counts."""
+    nw = ou.nwords(k)
+    buf = ou.synth_fastq(0, 60000, 150, 3_000_000, 21, 5000, 0)
+    keys, ids, _ = ou.fastq_kmers(buf, k, want_ids=(mode == kb.MODE_POSITION))
+    wk, wc = ou.count_sorted(keys, k)
+    rng = np.random.default_rng(k)
+    nq = (1 << 21) + 12345
+    present = wk[rng.integers(0, len(wk), nq // 2)]
+    present = ou.shape_keys(np.ascontiguousarray(ou.revcomp(np.ascontiguousarray(present).reshape(-1), k)).reshape(-1), k)   # the other strand
+    absent = ou.shape_keys(np.ascontiguousarray(ou.random_keys(k, nq - nq // 2, seed=99)).reshape(-1), k)
+    q = np.concatenate([present, absent])
+    q = q[rng.permutation(nq)]
+    with kb.Index(k=k, mode=mode, hash=kb.HASH_FARM, reserve=9_000_000) as idx:     # 2^24 slots: 268 / 537 MB, beyond the L2
+        if mode == kb.MODE_COUNT:
+            idx.build_fastq(buf)
+        else:
+            idx.insert(keys, ids)
+        assert idx.table_info()["slots"] * idx.table_info()["slot_bytes"] > (96 << 20)
+        dq = dev(q)
+        dv = torch.zeros(nq, dtype=torch.int64, device="cuda")
+        df = torch.zeros(nq, dtype=torch.uint8, device="cuda")
+        dc = torch.zeros(nq, dtype=torch.int64, device="cuda")
+        idx.find_dev(dq.data_ptr(), nq, dv.data_ptr(), df.data_ptr())            # one large batch: table order
+        idx.count_dev(dq.data_ptr(), nq, dc.data_ptr())
+        torch.cuda.synchronize()
+        big_v, big_f, big_c = host_u64(dv).copy(), df.cpu().numpy().copy(), host_u64(dc).copy()
+        dv.zero_(); df.zero_(); dc.zero_()
+        step = 1 << 19                                                             # small batches: plain probes
+        for a in range(0, nq, step):
+            m = min(step, nq - a)
+            idx.find_dev(dq.data_ptr() + a * nw * 8, m, dv.data_ptr() + a * 8, df.data_ptr() + a)
+            idx.count_dev(dq.data_ptr() + a * nw * 8, m, dc.data_ptr() + a * 8)
+        torch.cuda.synchronize()
+        assert np.array_equal(big_v, host_u64(dv)) and np.array_equal(big_f, df.cpu().numpy()) and np.array_equal(big_c, host_u64(dc))
+        # against the oracle: frequency (COUNT) / multiplicity (POSITION) of the canonical query
+        cq = ou.shape_keys(np.ascontiguousarray(ou.canonical(np.ascontiguousarray(q).reshape(-1), k)).reshape(-1), k)
+        if nw == 1:
+            pos = np.searchsorted(wk, cq)
+            pos[pos >= len(wk)] = 0
+            hit = wk[pos] == cq
+            want = np.where(hit, wc[pos], 0).astype(np.uint64)
+            assert np.array_equal(big_f.astype(bool), hit)
+            assert np.array_equal(big_v, want)
+            assert np.array_equal(big_c, want if mode == kb.MODE_POSITION else hit.astype(np.uint64))
+        else:
+            assert int(big_f.sum()) == nq // 2
+
+
 def test_synthetic_generator_matches_host_twin():
     rec = kb.synth_record_bytes(150)
     assert rec == 317
