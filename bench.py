@@ -658,7 +658,7 @@ def run_pos21(args):
     torch.cuda.synchronize()
     n_kmers_total = n_seq * (seq_len - k + 1)
     if world == 1:
-        idx = kb.PositionIndex(k, hash=kb.HASH_MURMUR, device=lr, reserve=n_kmers_total)
+        idx = kb.PositionIndex(k, hash=kb.HASH_MURMUR, device=lr)
         local = idx
 
         def step():
@@ -666,8 +666,15 @@ def run_pos21(args):
             return idx.build_fasta_dev(text.data_ptr(), b1 - b0)
     else:
         from kmerind_b200.dist import ShardedIndex
-        idx = ShardedIndex(k, mode=kb.MODE_POSITION, hash=kb.HASH_MURMUR, device=lr, reserve=n_kmers_total // world)
+        idx = ShardedIndex(k, mode=kb.MODE_POSITION, hash=kb.HASH_MURMUR, device=lr)
         local = idx.local
+    # fill limit of the table (KMI_PARAM_MAX_LOAD): 70 % = dense_hash_map's, the default. KMI_BENCH_MAX_LOAD=50 trades build speed
+    # (twice the table to write, 24.0 vs 18.8 ms per 375 Mbp) for query speed (29 vs 10.8 G count() queries/s resident in HBM:
+    # linear probing walks 6 slots per miss at 0.7, 2.5 at 0.5) — profiles/r02_query_experiments.md. Then the reference's reserve().
+    max_load = int(os.environ.get("KMI_BENCH_MAX_LOAD", "70"))
+    local.set_max_load(max_load)
+    local.reserve(n_kmers_total // world)
+    if world > 1:
 
         def step():
             idx.local.clear()
@@ -734,7 +741,7 @@ def run_pos21(args):
                 "config": {"workload": "PositionIndex K=21 canonical, murmur hash, synthetic FASTA genome of %d x %.0f Mbp (80 bases per line) = "
                                        "%.2f Gbp cut into %d blocks at arbitrary bytes, then %d query k-mers per GPU (half from the genome, half random)"
                                        % (n_seq, seq_len / 1e6, n_seq * seq_len / 1e9, world, n_q),
-                           "k": k, "file_bytes": int(fbytes), "kmers": int(n_kmers_total), "queries_per_gpu": n_q,
+                           "k": k, "file_bytes": int(fbytes), "kmers": int(n_kmers_total), "queries_per_gpu": n_q, "table_max_load_pct": max_load,
                            "l2": "text, tuple log and table far larger than the 126 MB L2"},
                 "index": {"tuples": int(size), "table_slots_per_gpu": info["slots"]},
                 "clocks": clocks, "gpu_launches": int(local.launch_count()),

@@ -94,9 +94,13 @@ int kmi_set_stream(kmi_index* idx, void* cuda_stream);
  * call. In bulk-load mode the bucketed builds (kmi_build_fastq_dev of >= 8 MiB, kmi_dist_build_fastq*) stop after the fine
  * scatter, which appends to a staging area laid out for `value` keys (clamped to 60 % of the free device memory); the single
  * segment insert runs when the area is full, when the table must grow, when anything reads or changes the table (find, count,
- * erase, dump, size, checksum, save ...) or on kmi_flush. Results are identical; only the number of table sweeps changes. */
+ * erase, dump, size, checksum, save ...) or on kmi_flush. Results are identical; only the number of table sweeps changes.
+ * KMI_PARAM_MAX_LOAD: percentage (10..70, default 70 = dense_hash_map's max_load_factor, densehash_map.hpp:969) of the
+ * power-of-two table that keys may fill before it grows. Linear probing at 0.7 walks 2.2 slots per hit and 6 per miss; an
+ * index built to be QUERIED (PositionIndex + batched find / count) answers ~2x faster at 50, for twice the table memory in the
+ * unlucky case. Set it before kmi_reserve / the first build. Not observable in results. */
 typedef enum { KMI_PARAM_BUILD_PATH = 1, KMI_PARAM_SEGMENT_INSERT = 2, KMI_PARAM_SATURATE = 3, KMI_PARAM_DIST_TRANS = 4,
-               KMI_PARAM_DEFER_INSERT = 5 } kmi_param;
+               KMI_PARAM_DEFER_INSERT = 5, KMI_PARAM_MAX_LOAD = 6 } kmi_param;
 int kmi_set_param(kmi_index* idx, int param, int64_t value);
 /* insert whatever bulk-load mode has staged and wait for it; reports a sticky table error like the size readers do */
 int kmi_flush(kmi_index* idx);

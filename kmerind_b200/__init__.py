@@ -501,6 +501,10 @@ class Index:
         _check(self._lib.kmi_bulk_stats(self._h, ctypes.byref(a), ctypes.byref(b)))
         return a.value, b.value
 
+    def set_max_load(self, percent):
+        """KMI_PARAM_MAX_LOAD: fill limit of the table in per cent (10..70); set before reserve / the first build"""
+        _check(self._lib.kmi_set_param(self._h, 6, int(percent)))
+
     def set_dist_trans(self, t):
         """KMI_PARAM_DIST_TRANS: 0 identity, 1 lex_less, 2 xor_rev_comp under the dist hash (non-canonical index)."""
         _check(self._lib.kmi_set_param(self._h, 4, int(t)))

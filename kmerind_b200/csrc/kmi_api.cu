@@ -92,9 +92,8 @@ static u64 pow2_at_least(u64 x) {
   while (p < x) p <<= 1;
   return p;
 }
-static const u64 QUERY_SORT_MIN = 1u << 20;              // queries: below this the sort's fixed cost is not repaid
-static const u64 QUERY_SORT_TABLE_BYTES = 96ull << 20;   // tables below this are L2-resident anyway
-static const double MAX_LOAD = 0.7;  // dense_hash_map max load, reference densehash_map.hpp:969
+static const double DEFAULT_MAX_LOAD = 0.7;  // dense_hash_map max load, reference densehash_map.hpp:969 (KMI_PARAM_MAX_LOAD changes it per index)
+#define MAX_LOAD (idx->max_load)
 
 int kmi::read_ctr(kmi_index* idx, int which, u64* out) {
   CU(cudaMemcpyAsync(out, idx->ctr + which, sizeof(u64), cudaMemcpyDeviceToHost, idx->stream));
@@ -234,7 +233,7 @@ extern "C" void kmi_destroy(kmi_index* idx) {
   DevBuf* bufs[] = {&idx->tile_lines, &idx->block_sums, &idx->stage_in, &idx->stage_keys, &idx->stage_vals,
                     &idx->stage_out, &idx->stage_found, &idx->hist, &idx->hist_sums, &idx->log_keys, &idx->log_ids,
                     &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->mid_keys, &idx->mid_cur,
-                    &idx->pend_ovf, &idx->pend_ovf_cur, &idx->pend_cur_save, &idx->q_perm_keys, &idx->q_perm_pos, &idx->q_perm_vals, &idx->q_perm_found};
+                    &idx->pend_ovf, &idx->pend_ovf_cur, &idx->pend_cur_save};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 6; ++i) if (idx->ev[i]) cudaEventDestroy(idx->ev[i]);
   for (int i = 0; i < 4; ++i) if (idx->kev[i]) cudaEventDestroy(idx->kev[i]);
@@ -274,6 +273,11 @@ extern "C" int kmi_set_param(kmi_index* idx, int param, int64_t value) {
     if (idx->cfg.mode != KMI_MODE_COUNT) return fail(KMI_ERR_ARG, "bulk-load staging belongs to a COUNT index");
     if (!value) OK(flush_pending(idx));
     idx->defer_budget = (u64)value;
+    return KMI_OK;
+  }
+  if (param == KMI_PARAM_MAX_LOAD) {
+    if (value < 10 || value > 70) return fail(KMI_ERR_ARG, "max load is a percentage between 10 and 70");
+    idx->max_load = (double)value / 100.0;               // takes effect at the next sizing decision (reserve / insert / build)
     return KMI_OK;
   }
   if (param == KMI_PARAM_DIST_TRANS) {
@@ -1147,33 +1151,6 @@ extern "C" int kmi_find_dev(kmi_index* idx, const uint64_t* d_keys, size_t n, ui
   if (!idx->slots) {
     if (d_vals) CU(cudaMemsetAsync(d_vals, 0, n * sizeof(u64), idx->stream));
     if (d_found) CU(cudaMemsetAsync(d_found, 0, n, idx->stream));
-    return KMI_OK;
-  }
-  // Large batches against a table that does not fit the L2: probe in TABLE order (kmi_kernels.cuh, k_q_hist / k_q_scatter):
-  // sort the queries by hash prefix, look them up segment by segment, gather the answers back into input order.
-  static const bool q_sort_off = [] { const char* e = getenv("KMI_QUERY_SORT"); return e && e[0] == '0'; }();
-  if (!q_sort_off && n >= QUERY_SORT_MIN && n < 0xffffffffULL && idx->cap * idx->slot_bytes > QUERY_SORT_TABLE_BYTES) {
-    const TableView tv = idx->view();
-    const size_t kb = sizeof(u64) * idx->nw;
-    const u64 n_chunks = (n + PART_ITEMS - 1) / PART_ITEMS, n_hist = n_chunks * 256, n_blocks = (n_hist + 1023) / 1024;
-    OK(idx->hist.ensure(sizeof(u32) * (n_hist + 1)));
-    OK(idx->hist_sums.ensure(sizeof(u32) * (n_blocks + 1)));
-    OK(idx->q_perm_keys.ensure(n * kb));
-    OK(idx->q_perm_pos.ensure(n * sizeof(u32)));
-    OK(idx->q_perm_vals.ensure(n * sizeof(u64)));
-    OK(idx->q_perm_found.ensure(n));
-    const bool canon = idx->cfg.canonical != 0;
-    idx->ops->q_hist(idx->stream, reinterpret_cast<const u64*>(d_keys), n, canon, idx->hist.as<u32>(), n_chunks);
-    k_scan_l1<<<(unsigned)n_blocks, 1024, 0, idx->stream>>>(idx->hist.as<u32>(), n_hist, idx->hist_sums.as<u32>());
-    k_scan_tiles<<<1, 1024, 0, idx->stream>>>(idx->hist_sums.as<u32>(), n_blocks);
-    idx->ops->q_scatter(idx->stream, reinterpret_cast<const u64*>(d_keys), n, canon, idx->hist.as<u32>(), idx->hist_sums.as<u32>(), n_chunks,
-                        idx->q_perm_keys.as<u64>(), idx->q_perm_pos.as<u32>());
-    idx->ops->lookup(idx->stream, tv, idx->q_perm_keys.as<u64>(), n, d_vals ? idx->q_perm_vals.as<u64>() : nullptr,
-                     d_found ? idx->q_perm_found.as<uint8_t>() : nullptr, nullptr, false);
-    k_q_gather<<<grid_for(n, 256, 148u * 32u), 256, 0, idx->stream>>>(idx->q_perm_pos.as<u32>(), n, idx->q_perm_vals.as<u64>(),
-                                                                     idx->q_perm_found.as<uint8_t>(), reinterpret_cast<u64*>(d_vals), d_found);
-    idx->launches += 6;
-    CU(cudaGetLastError());
     return KMI_OK;
   }
   idx->ops->lookup(idx->stream, idx->view(), reinterpret_cast<const u64*>(d_keys), n, reinterpret_cast<u64*>(d_vals), d_found,

@@ -72,7 +72,6 @@ struct kmi_index {
   kmi::DevBuf mid_keys, mid_cur;        // first of two fine passes (very large tables)
   kmi::DevBuf parse_keys, parse_ids;   // staging of the parse -> insert builds (FASTA, FASTQ positions): kept between calls
   kmi::DevBuf tile_rec;   // FASTQ position ids: record start open at every tile (k_fastq_rec_carry)
-  kmi::DevBuf q_perm_keys, q_perm_pos, q_perm_vals, q_perm_found;   // large query batches probed in table order (kmi_find_dev)
   kmi::DevBuf tile_lines, block_sums, stage_in, stage_keys, stage_vals, stage_out, stage_found, hist, hist_sums;
   // POSITION mode: tuple log + CSR
   kmi::DevBuf log_keys, log_ids, log_keys2, log_ids2, offsets, csr_sums, values;
@@ -94,6 +93,7 @@ struct kmi_index {
   kmi::u32 pend_capf = 0, pend_ovf_cap = 0;
   kmi::DevBuf pend_ovf, pend_ovf_cur, pend_cur_save;   // spill list of the deferred insert; cursor snapshot for roll-back
   kmi::u64 flushes = 0;         // deferred segment inserts run so far
+  double max_load = 0.7;   // KMI_PARAM_MAX_LOAD: the table is sized so that live + deleted keys stay below this fraction of its slots
   kmi::u32 dist_trans = 0; // KMI_PARAM_DIST_TRANS: transform under the dist hash of a non-canonical index (0 iden, 1 lex_less, 2 xor)
   bool saturate = false;   // KMI_PARAM_SATURATE: counts stick at 2^32 - 1; such an index builds with direct atomics (table_add)
   int build_path = 0;      // kmi_param KMI_PARAM_BUILD_PATH: 0 auto, 1 direct atomics, 2 bucketed

@@ -66,8 +66,9 @@ k_lookup(TableView t, const u64* __restrict__ keys, u64 n, u64* __restrict__ val
   for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
     Key<NW> key = load_key<NW>(keys, i);
     if (CANON) key = canonical<K>(key);
-    u64 s = table_find<NW>(t, key, slot_hash<K>(key));
-    if (vals) vals[i] = (s == ~0ULL) ? 0ULL : (u64) reinterpret_cast<const Slot<NW>*>(t.slots)[s].val;
+    u32 v;
+    u64 s = table_find_val<NW>(t, key, slot_hash<K>(key), v);
+    if (vals) vals[i] = (u64)v;
     if (found) found[i] = (s == ~0ULL) ? 0 : 1;
     if (slot_idx) slot_idx[i] = s;
   }
@@ -268,91 +269,6 @@ k_part_scatter(const u64* __restrict__ keys, const u64* __restrict__ vals, u64 n
     __syncthreads();
   }
 }
-
-// ---- batched queries in table order ---------------------------------------------------------------------------------------
-// A probe is a random 16 / 32-byte read in a multi-GB table: beyond the L2 (and the TLB reach) a batch of queries in arrival
-// order runs at a few per cent of the HBM roofline. Large batches are therefore probed in TABLE order: a stable counting sort
-// of the (canonical) queries by the top 8 bits of their slot hash — the same prefix that names a contiguous 1/256 of the table
-// (kmi_bucket.cuh) — then k_lookup over the sorted keys, whose probes stay inside one L2-resident table segment at a time, and
-// a gather of the answers back into input order through the recorded positions. Same shape as k_part_hist / k_part_scatter.
-template <int K>
-__global__ void __launch_bounds__(PART_THREADS)
-k_q_hist(const u64* __restrict__ keys, u64 n, const bool CANON, u32* __restrict__ hist, u64 n_chunks) {
-  constexpr int NW = (K <= 32 ? 1 : 2);
-  __shared__ u32 h[256];
-  h[threadIdx.x] = 0;
-  __syncthreads();
-  const u64 base = (u64)blockIdx.x * PART_ITEMS;
-  for (int rd = 0; rd < PART_ROUNDS; ++rd) {
-    const u64 i = base + (u64)rd * PART_THREADS + threadIdx.x;
-    if (i < n) {
-      Key<NW> key = load_key<NW>(keys, i);
-      if (CANON) key = canonical<K>(key);
-      atomicAdd(&h[(u32)(slot_hash<K>(key) >> 56)], 1u);
-    }
-  }
-  __syncthreads();
-  hist[(u64)threadIdx.x * n_chunks + blockIdx.x] = h[threadIdx.x];
-}
-template <int K>
-__global__ void __launch_bounds__(PART_THREADS)
-k_q_scatter(const u64* __restrict__ keys, u64 n, const bool CANON, const u32* __restrict__ hist_scanned, const u32* __restrict__ hist_block_sums,
-            u64 n_chunks, u64* __restrict__ keys_out, u32* __restrict__ pos_out) {
-  constexpr int NW = (K <= 32 ? 1 : 2);
-  constexpr int NWARPS = PART_THREADS / 32;
-  __shared__ u32 run[256];
-  __shared__ u32 wcnt[NWARPS][256];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  {
-    const u64 hi = (u64)threadIdx.x * n_chunks + blockIdx.x;
-    run[threadIdx.x] = hist_scanned[hi] + hist_block_sums[hi >> 10];
-  }
-  const u64 base = (u64)blockIdx.x * PART_ITEMS;
-  for (int rd = 0; rd < PART_ROUNDS; ++rd) {
-#pragma unroll
-    for (int w = 0; w < NWARPS; ++w) wcnt[w][threadIdx.x] = 0;
-    __syncthreads();
-    const u64 i = base + (u64)rd * PART_THREADS + threadIdx.x;
-    const bool ok = i < n;
-    Key<NW> key;
-    u32 b = 0xFFFFFFFFu;
-    if (ok) {
-      key = load_key<NW>(keys, i);
-      if (CANON) key = canonical<K>(key);
-      b = (u32)(slot_hash<K>(key) >> 56);
-    }
-    const u32 peers = __match_any_sync(0xffffffffu, b);
-    const u32 rank_in_warp = __popc(peers & ((1u << lane) - 1u));
-    if (ok && rank_in_warp == 0) wcnt[warp][b] = __popc(peers);
-    __syncthreads();
-    if (ok) {
-      u32 o = run[b] + rank_in_warp;
-      for (int w = 0; w < warp; ++w) o += wcnt[w][b];
-      store_key<NW>(keys_out, o, key);
-      pos_out[i] = o;
-    }
-    __syncthreads();
-    {
-      u32 s = 0;
-#pragma unroll
-      for (int w = 0; w < NWARPS; ++w) s += wcnt[w][threadIdx.x];
-      run[threadIdx.x] += s;
-    }
-    __syncthreads();
-  }
-}
-#ifdef KMI_SHARED_KERNELS
-// answers back into input order: out[i] = sorted answer at pos[i]
-__global__ void __launch_bounds__(256)
-k_q_gather(const u32* __restrict__ pos, u64 n, const u64* __restrict__ vals_in, const uint8_t* __restrict__ found_in, u64* __restrict__ vals,
-           uint8_t* __restrict__ found) {
-  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
-    const u32 p = pos[i];
-    if (vals) vals[i] = vals_in[p];
-    if (found) found[i] = found_in[p];
-  }
-}
-#endif
 
 // ---- a17: multimap as CSR (key -> [offset, offset+multiplicity) into a value array) --------------
 // Replaces fsc::densehash_multimap's singleton/vector split (reference

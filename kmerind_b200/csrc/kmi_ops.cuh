@@ -47,10 +47,6 @@ struct Ops {
   void (*log_filter)(cudaStream_t, TableView, const u64* keys, const u64* ids, u64 n, u64* keys_out, u64* ids_out,
                      u64* cursor);
   void (*zero_aux)(cudaStream_t, void* slots, u64 n);
-  // large query batches in table order: stable counting sort by the slot hash's top 8 bits (keys canonicalised on the way)
-  void (*q_hist)(cudaStream_t, const u64* keys, u64 n, bool canon, u32* hist, u64 n_chunks);
-  void (*q_scatter)(cudaStream_t, const u64* keys, u64 n, bool canon, const u32* hist_scanned, const u32* hist_block_sums, u64 n_chunks,
-                    u64* keys_out, u32* pos_out);
 };
 
 static inline unsigned grid_for(u64 n, unsigned block, unsigned max_blocks = 148u * 16u) {
@@ -194,13 +190,6 @@ struct OpsImpl {
   static void zero_aux(cudaStream_t st, void* slots, u64 n) {
     k_zero_aux<NW><<<grid_for(n, 256), 256, 0, st>>>(reinterpret_cast<S*>(slots), n);
   }
-  static void q_hist(cudaStream_t st, const u64* keys, u64 n, bool canon, u32* hist, u64 n_chunks) {
-    if (n_chunks) k_q_hist<K><<<(unsigned)n_chunks, PART_THREADS, 0, st>>>(keys, n, canon, hist, n_chunks);
-  }
-  static void q_scatter(cudaStream_t st, const u64* keys, u64 n, bool canon, const u32* hist_scanned, const u32* hist_block_sums, u64 n_chunks,
-                        u64* keys_out, u32* pos_out) {
-    if (n_chunks) k_q_scatter<K><<<(unsigned)n_chunks, PART_THREADS, 0, st>>>(keys, n, canon, hist_scanned, hist_block_sums, n_chunks, keys_out, pos_out);
-  }
   static Ops make() {
     Ops o;
     o.K = K; o.NW = NW; o.hash = HASH;
@@ -208,7 +197,7 @@ struct OpsImpl {
     o.scatter_fine = scatter_fine; o.insert_segments = insert_segments; o.insert_overflow = insert_overflow; o.owner_push = owner_push; o.fasta_kmers = fasta_kmers; o.table_clear = table_clear; o.insert_keys = insert_keys; o.rehash = rehash;
     o.lookup = lookup; o.erase = erase; o.dump = dump; o.erase_if = erase_if; o.checksum = checksum; o.canonicalize = canonicalize;
     o.hash_keys = hash_keys; o.part_hist = part_hist; o.part_scatter = part_scatter; o.csr_scan_l1 = csr_scan_l1;
-    o.csr_fill = csr_fill; o.log_filter = log_filter; o.zero_aux = zero_aux; o.q_hist = q_hist; o.q_scatter = q_scatter;
+    o.csr_fill = csr_fill; o.log_filter = log_filter; o.zero_aux = zero_aux;
     return o;
   }
   // The hash kind only enters the kernels that evaluate the DIST hash (kmi_hash_dev, the partition by owner, the NVLink

@@ -108,4 +108,45 @@ __device__ __forceinline__ u64 table_find(const TableView& t, const Key<NW>& key
   return ~0ULL;
 }
 
+// read-only probe that also returns the value, for the batched queries. One-word keys: a slot is 16 bytes, so an aligned
+// PAIR of slots is one 32-byte sector — both are requested together (two 128-bit loads in flight, one sector, one latency)
+// and tested in probe order, which halves the dependent round trips of a long probe sequence (tables sit at load 0.35-0.7;
+// at 0.7 a miss walks 6 slots on average). Two-word keys: a slot is its own sector; key and value come with one 32-byte read.
+template <int NW>
+__device__ __forceinline__ u64 table_find_val(const TableView& t, const Key<NW>& key, u64 hash, u32& val) {
+  val = 0;
+  u64 i = hash >> t.shift;
+  if (NW == 1) {
+    const char* base = reinterpret_cast<const char*>(t.slots);
+    u64 k0, v0, k1, v1;
+    u64 probes = 0;
+    if (i & 1) {                                          // odd home slot: alone in its sector's second half
+      ld_cg_u64x2(base + i * 16, k0, v0);
+      if (k0 == key.w[0]) { val = (u32)v0; return i; }
+      if (k0 == KEY_EMPTY_TOP) return ~0ULL;
+      i = (i + 1) & t.mask; probes = 1;
+    }
+    for (; probes <= t.mask; probes += 2) {               // i is even: slots i, i + 1 share a sector (mask is odd)
+      ld_cg_u64x2(base + i * 16, k0, v0);
+      ld_cg_u64x2(base + i * 16 + 16, k1, v1);
+      if (k0 == key.w[0]) { val = (u32)v0; return i; }
+      if (k0 == KEY_EMPTY_TOP) return ~0ULL;
+      if (k1 == key.w[0]) { val = (u32)v1; return i + 1; }
+      if (k1 == KEY_EMPTY_TOP) return ~0ULL;
+      i = (i + 2) & t.mask;
+    }
+    return ~0ULL;
+  } else {
+    const Slot<NW>* slots = reinterpret_cast<const Slot<NW>*>(t.slots);
+    for (u64 probes = 0; probes <= t.mask; ++probes) {
+      u64 lo, hi, vw, pad;
+      asm volatile("ld.global.cg.v4.u64 {%0, %1, %2, %3}, [%4];" : "=l"(lo), "=l"(hi), "=l"(vw), "=l"(pad) : "l"(slots + i));
+      if (lo == key.w[0] && hi == key.w[NW - 1]) { val = (u32)vw; return i; }
+      if (hi == KEY_EMPTY_TOP) return ~0ULL;
+      i = (i + 1) & t.mask;
+    }
+    return ~0ULL;
+  }
+}
+
 }  // namespace kmi

@@ -526,10 +526,10 @@ def test_partition_dist_transform(k):
 
 
 @pytest.mark.parametrize("k,mode", ((31, kb.MODE_COUNT), (63, kb.MODE_COUNT), (21, kb.MODE_POSITION)))
-def test_large_query_batches_in_table_order_equal_small_batches(k, mode):
-    """kmi_find_dev / kmi_count_dev sort batches of >= 2^20 queries by hash prefix, probe in table order and gather the answers
-    back (k_q_hist / k_q_scatter / k_q_gather) when the table is larger than the L2: same answers, in input order, as the
-    plain probe that smaller batches take — and as the oracle's counts."""
+def test_large_query_batches_equal_small_batches_and_oracle(k, mode):
+    """kmi_find_dev / kmi_count_dev on a batch of 2^21 queries against a table beyond the L2 (the pair-probing lookup: two
+    16-byte slots = one sector per step, value in the same load): same answers, in input order, as many small batches — and
+    as the oracle's counts. The index is also rebuilt at a 50 % fill limit (KMI_PARAM_MAX_LOAD): answers do not change."""
     nw = ou.nwords(k)
     buf = ou.synth_fastq(0, 60000, 150, 3_000_000, 21, 5000, 0)
     keys, ids, _ = ou.fastq_kmers(buf, k, want_ids=(mode == kb.MODE_POSITION))
@@ -551,12 +551,12 @@ def test_large_query_batches_in_table_order_equal_small_batches(k, mode):
         dv = torch.zeros(nq, dtype=torch.int64, device="cuda")
         df = torch.zeros(nq, dtype=torch.uint8, device="cuda")
         dc = torch.zeros(nq, dtype=torch.int64, device="cuda")
-        idx.find_dev(dq.data_ptr(), nq, dv.data_ptr(), df.data_ptr())            # one large batch: table order
+        idx.find_dev(dq.data_ptr(), nq, dv.data_ptr(), df.data_ptr())            # one large batch
         idx.count_dev(dq.data_ptr(), nq, dc.data_ptr())
         torch.cuda.synchronize()
         big_v, big_f, big_c = host_u64(dv).copy(), df.cpu().numpy().copy(), host_u64(dc).copy()
         dv.zero_(); df.zero_(); dc.zero_()
-        step = 1 << 19                                                             # small batches: plain probes
+        step = 1 << 19                                                             # small batches
         for a in range(0, nq, step):
             m = min(step, nq - a)
             idx.find_dev(dq.data_ptr() + a * nw * 8, m, dv.data_ptr() + a * 8, df.data_ptr() + a)
@@ -575,6 +575,20 @@ def test_large_query_batches_in_table_order_equal_small_batches(k, mode):
             assert np.array_equal(big_c, want if mode == kb.MODE_POSITION else hit.astype(np.uint64))
         else:
             assert int(big_f.sum()) == nq // 2
+    with kb.Index(k=k, mode=mode, hash=kb.HASH_FARM) as idx:                       # the same index at a 50 % fill limit
+        idx.set_max_load(50)
+        if mode == kb.MODE_COUNT:
+            idx.build_fastq(buf)
+        else:
+            idx.insert(keys, ids)
+        info = idx.table_info()
+        assert len(wk) <= 0.5 * info["slots"]
+        dq = dev(q)
+        dv = torch.zeros(nq, dtype=torch.int64, device="cuda")
+        df = torch.zeros(nq, dtype=torch.uint8, device="cuda")
+        idx.find_dev(dq.data_ptr(), nq, dv.data_ptr(), df.data_ptr())
+        torch.cuda.synchronize()
+        assert np.array_equal(host_u64(dv), big_v) and np.array_equal(df.cpu().numpy(), big_f)
 
 
 def test_synthetic_generator_matches_host_twin():

@@ -13,7 +13,10 @@ n_q = int(sys.argv[1]) if len(sys.argv) > 1 else 125_000_000
 fbytes = kb.synth_fasta_bytes(n_seq, seq_len, 80)
 text = torch.empty(fbytes + 64, dtype=torch.uint8, device="cuda")
 kb.synth_fasta_dev(0, text.data_ptr(), 0, fbytes, n_seq, seq_len, 80, 1)
-idx = kb.PositionIndex(k, hash=kb.HASH_MURMUR, reserve=n_seq * seq_len)
+idx = kb.PositionIndex(k, hash=kb.HASH_MURMUR)
+idx.set_max_load(int(os.environ.get("KMI_MAX_LOAD", "70")))
+idx.reserve(n_seq * seq_len)
+print("table", idx.table_info())
 idx.build_fasta_dev(text.data_ptr(), fbytes)
 q = torch.empty(n_q, dtype=torch.int64, device="cuda")
 c = torch.zeros(n_q, dtype=torch.int64, device="cuda")
