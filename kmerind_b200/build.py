@@ -33,7 +33,7 @@ def _run(cmd):
 
 
 def build(force=False, verbose=False):
-    hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh")]
+    hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".hpp"))]
     hdrs.append(os.path.join(HERE, "..", "include", "kmi.h"))
     objdir = os.path.join(CSRC, "build", VARIANT) if VARIANT else os.path.join(CSRC, "build")
     os.makedirs(objdir, exist_ok=True)
@@ -67,7 +67,7 @@ KMODS_DEFAULT = (17, 25, 27, 33, 55)
 
 
 def build_kmods(ks=KMODS_DEFAULT, force=False, verbose=False):
-    hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh")]
+    hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".hpp"))]
     inst = os.path.join(CSRC, "kmi_ops_inst.cu")
     outdir = os.path.join(HERE, "kmods")
     os.makedirs(outdir, exist_ok=True)

@@ -116,6 +116,168 @@ int kmi::check_table_error(kmi_index* idx) {
   return table_error(e);
 }
 
+// ---- pageable host memory <-> device (kmi_hoststage.hpp) ----------------------------------------------------------------
+// The reference's callers hold file bytes, query vectors and answers in ordinary heap memory; cudaMemcpy from there runs on
+// one driver thread (~9 GB/s on the bench box). Large copies are cut into slices that KMI_STAGE_THREADS host threads (default
+// min(8, cores); 0 = off: plain cudaMemcpyAsync) move through a ring of pinned slots of KMI_STAGE_SLICE_BYTES (4 MiB),
+// 3 slots per thread, kept with the index; copies below KMI_STAGE_MIN_BYTES (16 MiB) and pinned / registered / managed memory
+// go straight to cudaMemcpyAsync.
+#include "kmi_hoststage.hpp"
+#include <thread>
+namespace kmi {
+struct HostRing {
+  uint8_t* ring = nullptr;
+  size_t slice = 0, min_bytes = 0;
+  int slots = 0, threads = 0;
+  std::vector<cudaEvent_t> ev;   // per slot: the last device copy that touched it
+  cudaEvent_t one = nullptr;     // the single mark of copy_to_device / the hand-over from idx->stream
+  bool busy = false;             // a HostFeed is running on it
+};
+struct CudaStageBackend {
+  int device; cudaStream_t stream; cudaEvent_t* slot_ev; cudaEvent_t* mark_ev; size_t n_marks;
+  void thread_init() { cudaSetDevice(device); }
+  bool copy_in(void* dev, const void* pinned, size_t n) { return cudaMemcpyAsync(dev, pinned, n, cudaMemcpyHostToDevice, stream) == cudaSuccess; }
+  bool copy_out(void* pinned, const void* dev, size_t n) { return cudaMemcpyAsync(pinned, dev, n, cudaMemcpyDeviceToHost, stream) == cudaSuccess; }
+  bool record_slot(int s) { return cudaEventRecord(slot_ev[s], stream) == cudaSuccess; }
+  bool wait_slot(int s) { return cudaEventSynchronize(slot_ev[s]) == cudaSuccess; }
+  bool record_mark(size_t i) { return i < n_marks && cudaEventRecord(mark_ev[i], stream) == cudaSuccess; }
+};
+static size_t env_size(const char* name, size_t dflt) {
+  const char* e = getenv(name);
+  return (e && *e) ? (size_t)strtoull(e, nullptr, 10) : dflt;
+}
+// the index's ring, or nullptr when staging is off or the pinned memory cannot be had (callers then copy directly)
+static HostRing* host_ring(kmi_index* idx) {
+  if (idx->hring || idx->hring_tried) return idx->hring;
+  idx->hring_tried = true;
+  const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+  const int threads = (int)std::min<size_t>(env_size("KMI_STAGE_THREADS", std::min(8u, hw)), 64);
+  if (threads <= 0) return nullptr;
+  HostRing* r = new (std::nothrow) HostRing();
+  if (!r) return nullptr;
+  r->threads = threads;
+  r->slots = std::max(4, 3 * threads);
+  r->slice = std::max<size_t>(env_size("KMI_STAGE_SLICE_BYTES", 4u << 20), 256);
+  r->min_bytes = env_size("KMI_STAGE_MIN_BYTES", 16u << 20);
+  bool ok = cudaHostAlloc(reinterpret_cast<void**>(&r->ring), r->slice * (size_t)r->slots, cudaHostAllocDefault) == cudaSuccess;
+  if (!ok) r->ring = nullptr;
+  for (int i = 0; ok && i < r->slots; ++i) {
+    cudaEvent_t e = nullptr;
+    ok = cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess;
+    if (ok) r->ev.push_back(e);
+  }
+  ok = ok && cudaEventCreateWithFlags(&r->one, cudaEventDisableTiming) == cudaSuccess;
+  ok = ok && (idx->copy_stream || cudaStreamCreateWithFlags(&idx->copy_stream, cudaStreamNonBlocking) == cudaSuccess);
+  idx->hring = r;
+  if (!ok) { cudaGetLastError(); host_ring_release(idx); }
+  return idx->hring;
+}
+void host_ring_release(kmi_index* idx) {
+  HostRing* r = idx->hring;
+  if (!r) return;
+  for (cudaEvent_t e : r->ev) cudaEventDestroy(e);
+  if (r->one) cudaEventDestroy(r->one);
+  if (r->ring) cudaFreeHost(r->ring);
+  delete r;
+  idx->hring = nullptr;
+}
+// ordinary heap / stack / mmap memory: neither pinned nor registered nor managed nor device
+static bool host_is_pageable(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
+  return a.type == cudaMemoryTypeUnregistered;
+}
+static HostRing* ring_for(kmi_index* idx, const void* host, size_t bytes) {
+  if (bytes == 0) return nullptr;
+  HostRing* r = host_ring(idx);
+  if (!r || r->busy || bytes < r->min_bytes || !host_is_pageable(host)) return nullptr;
+  return r;
+}
+
+int copy_to_device(kmi_index* idx, void* d_dst, const void* src, size_t bytes) {
+  if (bytes == 0) return KMI_OK;
+  HostRing* r = ring_for(idx, src, bytes);
+  if (!r) { CU(cudaMemcpyAsync(d_dst, src, bytes, cudaMemcpyHostToDevice, idx->stream)); return KMI_OK; }
+  CU(cudaEventRecord(r->one, idx->stream));                 // d_dst may still be in use by work queued earlier
+  CU(cudaStreamWaitEvent(idx->copy_stream, r->one, 0));
+  CudaStageBackend b{idx->cfg.device, idx->copy_stream, r->ev.data(), &r->one, 1};
+  bool ok;
+  {
+    HostStageJob<CudaStageBackend> job(b, r->ring, r->slice, r->slots, r->threads);
+    job.start_in(static_cast<uint8_t*>(d_dst), static_cast<const uint8_t*>(src), std::vector<uint64_t>{(uint64_t)bytes});
+    ok = job.wait_mark(0);          // every slice has left the caller's memory and is enqueued
+    ok = job.finish(false) && ok;
+  }
+  if (!ok) { cudaError_t e = cudaGetLastError(); return fail(KMI_ERR_CUDA, "staged host -> device copy of %zu bytes: %s", bytes, cudaGetErrorString(e)); }
+  CU(cudaStreamWaitEvent(idx->stream, r->one, 0));
+  return KMI_OK;
+}
+int copy_to_host(kmi_index* idx, void* dst, const void* d_src, size_t bytes) {
+  if (bytes == 0) return KMI_OK;
+  HostRing* r = ring_for(idx, dst, bytes);
+  if (!r) { CU(cudaMemcpyAsync(dst, d_src, bytes, cudaMemcpyDeviceToHost, idx->stream)); return KMI_OK; }
+  CU(cudaEventRecord(r->one, idx->stream));                 // whatever produces d_src
+  CU(cudaStreamWaitEvent(idx->copy_stream, r->one, 0));
+  CudaStageBackend b{idx->cfg.device, idx->copy_stream, r->ev.data(), nullptr, 0};
+  HostStageJob<CudaStageBackend> job(b, r->ring, r->slice, r->slots, r->threads);
+  if (!job.run_out(static_cast<uint8_t*>(dst), static_cast<const uint8_t*>(d_src), bytes)) {
+    cudaError_t e = cudaGetLastError();
+    return fail(KMI_ERR_CUDA, "staged device -> host copy of %zu bytes: %s", bytes, cudaGetErrorString(e));
+  }
+  return KMI_OK;
+}
+
+struct HostFeed::Impl {
+  CudaStageBackend b;
+  HostStageJob<CudaStageBackend> job;
+  Impl(const CudaStageBackend& b_, HostRing* r) : b(b_), job(b, r->ring, r->slice, r->slots, r->threads) {}
+};
+int HostFeed::start(kmi_index* idx, uint8_t* d_dst, const uint8_t* src, const std::vector<u64>& ends, cudaStream_t after) {
+  idx_ = idx;
+  if (!idx->copy_stream) CU(cudaStreamCreateWithFlags(&idx->copy_stream, cudaStreamNonBlocking));
+  CU(cudaEventRecord(idx->ev[3], after));                   // the destination may still be in use by earlier work
+  CU(cudaStreamWaitEvent(idx->copy_stream, idx->ev[3], 0));
+  while (idx->copy_events.size() < ends.size()) {
+    cudaEvent_t e;
+    CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    idx->copy_events.push_back(e);
+  }
+  const u64 total = ends.empty() ? 0 : ends.back();
+  HostRing* r = ring_for(idx, src, (size_t)total);
+  if (!r) {   // pinned (or small): cudaMemcpyAsync does not block, everything is enqueued now
+    u64 at = 0;
+    for (size_t i = 0; i < ends.size(); ++i) {
+      if (ends[i] > at) CU(cudaMemcpyAsync(d_dst + at, src + at, ends[i] - at, cudaMemcpyHostToDevice, idx->copy_stream));
+      at = std::max(at, ends[i]);
+      CU(cudaEventRecord(idx->copy_events[i], idx->copy_stream));
+    }
+    return KMI_OK;
+  }
+  CudaStageBackend b{idx->cfg.device, idx->copy_stream, r->ev.data(), idx->copy_events.data(), ends.size()};
+  impl_ = new (std::nothrow) Impl(b, r);
+  if (!impl_) return fail(KMI_ERR_NOMEM, "out of host memory");
+  r->busy = true;
+  std::vector<uint64_t> e64(ends.begin(), ends.end());
+  impl_->job.start_in(d_dst, src, e64);
+  return KMI_OK;
+}
+int HostFeed::wait(size_t i, cudaStream_t consumer) {
+  if (impl_ && !impl_->job.wait_mark(i)) {
+    cudaError_t e = cudaGetLastError();
+    return fail(KMI_ERR_CUDA, "staged host -> device copy (range %zu): %s", i, cudaGetErrorString(e));
+  }
+  CU(cudaStreamWaitEvent(consumer, idx_->copy_events[i], 0));
+  return KMI_OK;
+}
+HostFeed::~HostFeed() {
+  if (impl_) {
+    delete impl_;   // stops and joins the workers
+    if (idx_->hring) idx_->hring->busy = false;
+  }
+  if (idx_ && idx_->copy_stream) cudaStreamSynchronize(idx_->copy_stream);
+}
+}  // namespace kmi
+
 // allocate a table of `cap` slots (contents undefined: the caller clears it or marks the index virgin)
 static int table_alloc(kmi_index* idx, u64 cap, void** out) {
   void* p = nullptr;
@@ -237,9 +399,11 @@ extern "C" void kmi_destroy(kmi_index* idx) {
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 6; ++i) if (idx->ev[i]) cudaEventDestroy(idx->ev[i]);
   for (int i = 0; i < 4; ++i) if (idx->kev[i]) cudaEventDestroy(idx->kev[i]);
+  if (idx->copy_stream) cudaStreamSynchronize(idx->copy_stream);
   for (cudaEvent_t e : idx->copy_events) cudaEventDestroy(e);
   if (idx->copy_stream) cudaStreamDestroy(idx->copy_stream);
   for (int i = 0; i < 2; ++i) if (idx->file_buf[i]) cudaFreeHost(idx->file_buf[i]);
+  host_ring_release(idx);
   if (idx->dist) kmi_dist_release(idx);
   delete idx;
 }
@@ -862,10 +1026,6 @@ static int build_fastq_direct(kmi_index* idx, const uint8_t* d_bytes, size_t n, 
 // are copied into d_bytes on the copy stream while the previous round computes, so the PCIe transfer
 // hides the whole build except the last round. A round's last tile needs 64 bytes of the next round
 // (k-mer halo), so it is parsed with the next round.
-struct CopyGuard {  // never return while a copy from the caller's memory is in flight
-  cudaStream_t s;
-  ~CopyGuard() { if (s) cudaStreamSynchronize(s); }
-};
 static int build_fastq_bucketed(kmi_index* idx, uint8_t* d_bytes, size_t n, u64 n_tiles, const uint8_t* host_src) {
   if (n_tiles == 0) return KMI_OK;
   const u64 MAX_TILES = (2 * BUCKET_MAX_KEYS) / TILE_BYTES;
@@ -880,23 +1040,11 @@ static int build_fastq_bucketed(kmi_index* idx, uint8_t* d_bytes, size_t n, u64 
   }
   per_round = (per_round + 1023) / 1024 * 1024;  // the two-level line scan works in blocks of 1024 tiles
   const u64 n_rounds = (n_tiles + per_round - 1) / per_round;
-  CopyGuard guard{nullptr};
+  HostFeed feed;   // (its destructor never returns while a copy from the caller's memory is in flight)
   if (host_src) {
-    if (!idx->copy_stream) CU(cudaStreamCreateWithFlags(&idx->copy_stream, cudaStreamNonBlocking));
-    guard.s = idx->copy_stream;
-    // the staging buffer may still be in use by earlier work on the compute stream
-    CU(cudaEventRecord(idx->ev[3], idx->stream));
-    CU(cudaStreamWaitEvent(idx->copy_stream, idx->ev[3], 0));
-    while (idx->copy_events.size() < n_rounds) {
-      cudaEvent_t e;
-      CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-      idx->copy_events.push_back(e);
-    }
-    for (u64 r = 0; r < n_rounds; ++r) {
-      const u64 b0 = r * per_round * TILE_BYTES, b1 = std::min<u64>(n, (r + 1) * per_round * TILE_BYTES);
-      CU(cudaMemcpyAsync(d_bytes + b0, host_src + b0, b1 - b0, cudaMemcpyHostToDevice, idx->copy_stream));
-      CU(cudaEventRecord(idx->copy_events[r], idx->copy_stream));
-    }
+    std::vector<u64> ends(n_rounds);
+    for (u64 r = 0; r < n_rounds; ++r) ends[r] = std::min<u64>(n, (r + 1) * per_round * TILE_BYTES);
+    OK(feed.start(idx, d_bytes, host_src, ends, idx->stream));
   }
   KeySink nosink; nosink.keys = nullptr; nosink.ids = nullptr; nosink.cap = 0; nosink.cursor = nullptr;
   std::vector<u32> reg;
@@ -905,7 +1053,7 @@ static int build_fastq_bucketed(kmi_index* idx, uint8_t* d_bytes, size_t n, u64 
     const u64 t0 = r * per_round, t1 = std::min(n_tiles, t0 + per_round);
     const bool last = r + 1 == n_rounds;
     // (a tile's halo continues at the next tile's line count: resident text is counted whole before the first round)
-    if (host_src) { CU(cudaStreamWaitEvent(idx->stream, idx->copy_events[r], 0)); OK(fastq_scan_range(idx, d_bytes, n, t0, t1)); }
+    if (host_src) { OK(feed.wait(r, idx->stream)); OK(fastq_scan_range(idx, d_bytes, n, t0, t1)); }
     else if (r == 0) OK(fastq_scan_range(idx, d_bytes, n, 0, n_tiles));
     const u64 p0 = (host_src && r > 0) ? t0 - 1 : t0;
     const u64 p1 = (host_src && !last) ? t1 - 1 : t1;
@@ -986,14 +1134,14 @@ static int build_fastq_positions(kmi_index* idx, const uint8_t* d_bytes, size_t 
 static int build_fastq_impl(kmi_index* idx, uint8_t* d_bytes, size_t n, const uint8_t* host_src, uint64_t* n_kmers,
                             u64 file_offset = 0) {
   if (idx->cfg.mode != KMI_MODE_COUNT) {
-    if (host_src) CU(cudaMemcpyAsync(d_bytes, host_src, n, cudaMemcpyHostToDevice, idx->stream));
+    if (host_src) OK(copy_to_device(idx, d_bytes, host_src, n));
     return build_fastq_positions(idx, d_bytes, n, file_offset, n_kmers);
   }
   u64 n_tiles = 0;
   const bool bucketed = idx->build_path == 2 || (idx->build_path == 0 && n >= AUTO_BUCKET_BYTES);
   CU(cudaEventRecord(idx->ev[0], idx->stream));
   if (host_src && !bucketed) {
-    CU(cudaMemcpyAsync(d_bytes, host_src, n, cudaMemcpyHostToDevice, idx->stream));
+    OK(copy_to_device(idx, d_bytes, host_src, n));
     host_src = nullptr;
   }
   OK(fastq_scan_alloc(idx, d_bytes, n, &n_tiles));
@@ -1110,12 +1258,12 @@ extern "C" int kmi_insert(kmi_index* idx, const uint64_t* keys, const uint64_t* 
   if (n == 0) return KMI_OK;
   size_t kb = sizeof(u64) * idx->nw;
   OK(idx->stage_keys.ensure(n * kb));
-  CU(cudaMemcpyAsync(idx->stage_keys.p, keys, n * kb, cudaMemcpyHostToDevice, idx->stream));
+  OK(copy_to_device(idx, idx->stage_keys.p, keys, n * kb));
   const uint64_t* dv = nullptr;
   if (idx->cfg.mode == KMI_MODE_POSITION || vals) {
     if (!vals) return fail(KMI_ERR_ARG, "POSITION insert needs ids");
     OK(idx->stage_vals.ensure(n * sizeof(u64)));
-    CU(cudaMemcpyAsync(idx->stage_vals.p, vals, n * sizeof(u64), cudaMemcpyHostToDevice, idx->stream));
+    OK(copy_to_device(idx, idx->stage_vals.p, vals, n * sizeof(u64)));
     dv = idx->stage_vals.as<uint64_t>();
   }
   OK(kmi_insert_dev(idx, idx->stage_keys.as<uint64_t>(), dv, n));
@@ -1176,8 +1324,7 @@ static int stage_query(kmi_index* idx, const uint64_t* keys, size_t n) {
   OK(idx->stage_keys.ensure(std::max<size_t>(n * kb, 16)));
   OK(idx->stage_out.ensure(std::max<size_t>((n + 1) * sizeof(u64), 16)));
   OK(idx->stage_found.ensure(std::max<size_t>(n, 16)));
-  CU(cudaMemcpyAsync(idx->stage_keys.p, keys, n * kb, cudaMemcpyHostToDevice, idx->stream));
-  return KMI_OK;
+  return copy_to_device(idx, idx->stage_keys.p, keys, n * kb);
 }
 
 extern "C" int kmi_count(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* counts) {
@@ -1185,16 +1332,11 @@ extern "C" int kmi_count(kmi_index* idx, const uint64_t* keys, size_t n, uint64_
   CU(cudaSetDevice(idx->cfg.device));
   if (n == 0) return KMI_OK;
   OK(stage_query(idx, keys, n));
-  DevBuf tmp;  // counts need their own buffer: count_dev uses stage_found internally
-  OK(tmp.ensure(n * sizeof(u64)));
-  int r = kmi_count_dev(idx, idx->stage_keys.as<uint64_t>(), n, tmp.as<uint64_t>());
-  if (r == KMI_OK) {
-    cudaError_t e = cudaMemcpyAsync(counts, tmp.p, n * sizeof(u64), cudaMemcpyDeviceToHost, idx->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(idx->stream);
-    if (e != cudaSuccess) r = fail(KMI_ERR_CUDA, "count copy back: %s", cudaGetErrorString(e));
-  }
-  tmp.release();
-  return r;
+  // counts land in stage_out (stage_query sized it): kmi_count_dev itself only uses stage_found
+  OK(kmi_count_dev(idx, idx->stage_keys.as<uint64_t>(), n, idx->stage_out.as<uint64_t>()));
+  OK(copy_to_host(idx, counts, idx->stage_out.p, n * sizeof(u64)));
+  CU(cudaStreamSynchronize(idx->stream));
+  return KMI_OK;
 }
 
 extern "C" int kmi_find(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* vals, uint8_t* found) {
@@ -1203,8 +1345,8 @@ extern "C" int kmi_find(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t
   if (n == 0) return KMI_OK;
   OK(stage_query(idx, keys, n));
   OK(kmi_find_dev(idx, idx->stage_keys.as<uint64_t>(), n, idx->stage_out.as<uint64_t>(), idx->stage_found.as<uint8_t>()));
-  if (vals) CU(cudaMemcpyAsync(vals, idx->stage_out.p, n * sizeof(u64), cudaMemcpyDeviceToHost, idx->stream));
-  if (found) CU(cudaMemcpyAsync(found, idx->stage_found.p, n, cudaMemcpyDeviceToHost, idx->stream));
+  if (vals) OK(copy_to_host(idx, vals, idx->stage_out.p, n * sizeof(u64)));
+  if (found) OK(copy_to_host(idx, found, idx->stage_found.p, n));
   CU(cudaStreamSynchronize(idx->stream));
   return KMI_OK;
 }
@@ -1228,8 +1370,9 @@ extern "C" int kmi_find_positions(kmi_index* idx, const uint64_t* keys, size_t n
                    idx->cfg.canonical != 0);
   k_scan64<<<1, 1024, 0, idx->stream>>>(out_off.as<u64>(), n + 1);
   idx->launches += 2;
-  cudaMemcpyAsync(offsets, out_off.p, (n + 1) * sizeof(u64), cudaMemcpyDeviceToHost, idx->stream);
+  r = copy_to_host(idx, offsets, out_off.p, (n + 1) * sizeof(u64));
   cudaStreamSynchronize(idx->stream);
+  if (r != KMI_OK) { slot_idx.release(); out_off.release(); return r; }
   u64 total = offsets[n];
   if (total > cap) { slot_idx.release(); out_off.release(); return fail(KMI_ERR_CAPACITY, "find_positions: %llu values, capacity %zu", (unsigned long long)total, cap); }
   if (total) {
@@ -1238,7 +1381,7 @@ extern "C" int kmi_find_positions(kmi_index* idx, const uint64_t* keys, size_t n
       k_csr_gather<<<grid_for(n, 256), 256, 0, idx->stream>>>(slot_idx.as<u64>(), out_off.as<u64>(), n, idx->offsets.as<u64>(),
                                                             idx->values.as<u64>(), out_vals.as<u64>(), total);
       idx->launches++;
-      cudaMemcpyAsync(vals, out_vals.p, total * sizeof(u64), cudaMemcpyDeviceToHost, idx->stream);
+      r = copy_to_host(idx, vals, out_vals.p, total * sizeof(u64));
       cudaStreamSynchronize(idx->stream);
     }
   }
@@ -1313,8 +1456,8 @@ extern "C" int kmi_dump(kmi_index* idx, uint64_t* keys, uint64_t* vals, size_t c
   if (idx->cfg.mode == KMI_MODE_POSITION) {
     if (idx->log_n > cap) return fail(KMI_ERR_CAPACITY, "dump: %llu tuples, capacity %zu", (unsigned long long)idx->log_n, cap);
     if (idx->log_n) {
-      if (keys) CU(cudaMemcpyAsync(keys, idx->log_keys.p, idx->log_n * kb, cudaMemcpyDeviceToHost, idx->stream));
-      if (vals) CU(cudaMemcpyAsync(vals, idx->log_ids.p, idx->log_n * sizeof(u64), cudaMemcpyDeviceToHost, idx->stream));
+      if (keys) OK(copy_to_host(idx, keys, idx->log_keys.p, idx->log_n * kb));
+      if (vals) OK(copy_to_host(idx, vals, idx->log_ids.p, idx->log_n * sizeof(u64)));
     }
     CU(cudaStreamSynchronize(idx->stream));
     *n_out = idx->log_n;
@@ -1332,12 +1475,11 @@ extern "C" int kmi_dump(kmi_index* idx, uint64_t* keys, uint64_t* vals, size_t c
     idx->touch();
     idx->ops->dump(idx->stream, idx->slots, idx->cap, dk.as<u64>(), dv.as<u64>(), size, idx->ctr + CTR_CURSOR, -1, 0);
     idx->launches++;
-    cudaError_t e = cudaSuccess;
-    if (keys) e = cudaMemcpyAsync(keys, dk.p, size * kb, cudaMemcpyDeviceToHost, idx->stream);
-    if (e == cudaSuccess && vals) e = cudaMemcpyAsync(vals, dv.p, size * sizeof(u64), cudaMemcpyDeviceToHost, idx->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(idx->stream);
-    if (e != cudaSuccess) r = fail(KMI_ERR_CUDA, "dump: %s", cudaGetErrorString(e));
-    else *n_out = size;
+    if (keys) r = copy_to_host(idx, keys, dk.p, size * kb);
+    if (r == KMI_OK && vals) r = copy_to_host(idx, vals, dv.p, size * sizeof(u64));
+    const cudaError_t e = cudaStreamSynchronize(idx->stream);   // also when a copy failed: dk / dv are freed below
+    if (r == KMI_OK && e != cudaSuccess) r = fail(KMI_ERR_CUDA, "dump: %s", cudaGetErrorString(e));
+    if (r == KMI_OK) *n_out = size;
   }
   dk.release(); dv.release();
   return r;
@@ -1384,10 +1526,10 @@ extern "C" int kmi_dump_if(kmi_index* idx, int op, uint64_t value, uint64_t* key
     r = read_ctr(idx, CTR_CURSOR, &m);
     if (r == KMI_OK && m > cap) r = fail(KMI_ERR_CAPACITY, "dump_if: %llu entries satisfy the predicate, capacity %zu (kmi_count_if sizes it)", (unsigned long long)m, cap);
     if (r == KMI_OK && m) {
-      cudaError_t e = cudaMemcpyAsync(keys, dk.p, m * kb, cudaMemcpyDeviceToHost, idx->stream);
-      if (e == cudaSuccess && vals) e = cudaMemcpyAsync(vals, dv.p, m * sizeof(u64), cudaMemcpyDeviceToHost, idx->stream);
-      if (e == cudaSuccess) e = cudaStreamSynchronize(idx->stream);
-      if (e != cudaSuccess) r = fail(KMI_ERR_CUDA, "dump_if: %s", cudaGetErrorString(e));
+      r = copy_to_host(idx, keys, dk.p, m * kb);
+      if (r == KMI_OK && vals) r = copy_to_host(idx, vals, dv.p, m * sizeof(u64));
+      const cudaError_t e = cudaStreamSynchronize(idx->stream);
+      if (r == KMI_OK && e != cudaSuccess) r = fail(KMI_ERR_CUDA, "dump_if: %s", cudaGetErrorString(e));
     }
     if (r == KMI_OK) *n_out = m;
   }
@@ -1844,19 +1986,11 @@ static int build_fasta_host(kmi_index* idx, const uint8_t* bytes, size_t n, FaBl
   CHUNK = (CHUNK + TILE_BYTES - 1) / TILE_BYTES * TILE_BYTES;
   const u64 ROUND = std::min<u64>(ROUND_MAX, 4 * CHUNK);
   const u64 n_chunks = std::max<u64>((base.n_valid + CHUNK - 1) / CHUNK, 1);
-  if (!idx->copy_stream) CU(cudaStreamCreateWithFlags(&idx->copy_stream, cudaStreamNonBlocking));
-  CopyGuard guard{idx->copy_stream};
-  CU(cudaEventRecord(idx->ev[3], idx->stream));           // the staging buffer may still be in use by earlier work
-  CU(cudaStreamWaitEvent(idx->copy_stream, idx->ev[3], 0));
-  while (idx->copy_events.size() < n_chunks) {
-    cudaEvent_t e;
-    CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    idx->copy_events.push_back(e);
-  }
-  for (u64 c = 0; c < n_chunks; ++c) {   // the last copy takes the caller's halo along
-    const u64 b0 = c * CHUNK, b1 = (c + 1 == n_chunks) ? n : std::min<u64>(n, (c + 1) * CHUNK);
-    if (b1 > b0) CU(cudaMemcpyAsync(d + b0, bytes + b0, b1 - b0, cudaMemcpyHostToDevice, idx->copy_stream));
-    CU(cudaEventRecord(idx->copy_events[c], idx->copy_stream));
+  HostFeed feed;
+  {   // the last copy takes the caller's halo along
+    std::vector<u64> ends(n_chunks);
+    for (u64 c = 0; c < n_chunks; ++c) ends[c] = (c + 1 == n_chunks) ? n : std::min<u64>(n, (c + 1) * CHUNK);
+    OK(feed.start(idx, d, bytes, ends, idx->stream));
   }
   const bool pos = idx->cfg.mode == KMI_MODE_POSITION;
   const u64 cap = std::min<u64>(ROUND, (base.n_valid + TILE_BYTES - 1) / TILE_BYTES * TILE_BYTES) + 1;
@@ -1887,7 +2021,7 @@ static int build_fasta_host(kmi_index* idx, const uint8_t* bytes, size_t n, FaBl
     blk.bol = (c == 0) ? base.bol : (bytes[b0 - 1] == '\n' ? 1u : 0u);
     const u64 avail = (last ? n : std::min<u64>(n, (c + 2) * CHUNK)) - b0;
     if (staged + blk.n_valid > cap) { OK(flush(staged)); staged = 0; }
-    CU(cudaStreamWaitEvent(idx->stream, idx->copy_events[last ? c : c + 1], 0));   // own bytes + halo = the next chunk
+    OK(feed.wait(last ? c : c + 1, idx->stream));   // own bytes + halo = the next chunk
     u64 n_tiles = 0;
     OK(fasta_scan(idx, d + b0, avail, &blk, &n_tiles));
     if (n_tiles == 0) continue;

@@ -466,11 +466,11 @@ extern "C" int kmi_dist_insert(kmi_index* idx, const uint64_t* keys, const uint6
   CU(cudaSetDevice(idx->cfg.device));
   const size_t kb = sizeof(u64) * idx->nw;
   OK(d->q_keys.ensure(std::max<size_t>(n, 1) * kb));
-  if (n) CU(cudaMemcpyAsync(d->q_keys.p, keys, n * kb, cudaMemcpyHostToDevice, idx->stream));
+  OK(copy_to_device(idx, d->q_keys.p, keys, n * kb));
   const uint64_t* dv = nullptr;
   if (vals) {
     OK(d->q_back.ensure(std::max<size_t>(n, 1) * sizeof(u64)));
-    if (n) CU(cudaMemcpyAsync(d->q_back.p, vals, n * sizeof(u64), cudaMemcpyHostToDevice, idx->stream));
+    OK(copy_to_device(idx, d->q_back.p, vals, n * sizeof(u64)));
     dv = d->q_back.as<uint64_t>();
   }
   return kmi_dist_insert_dev(idx, d->q_keys.as<uint64_t>(), dv, n);
@@ -489,7 +489,8 @@ static int dist_query(kmi_index* idx, const uint64_t* keys, size_t n, int what /
   OK(d->q_keys.ensure(std::max<size_t>(n, 1) * kb));
   OK(d->q_tags.ensure(std::max<size_t>(n, 1) * sizeof(u64)));
   if (n) {
-    CU(cudaMemcpyAsync(d->q_keys.p, keys, n * kb, dev ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    if (dev) CU(cudaMemcpyAsync(d->q_keys.p, keys, n * kb, cudaMemcpyDeviceToDevice, st));
+    else OK(copy_to_device(idx, d->q_keys.p, keys, n * kb));
     k_iota<<<grid_for(n, 256), 256, 0, st>>>(d->q_tags.as<u64>(), n);
   }
   std::vector<u64> sc, rc;
@@ -547,8 +548,14 @@ static int dist_query(kmi_index* idx, const uint64_t* keys, size_t n, int what /
     OK(d->ids.ensure(n));
     k_unpermute<<<grid_for(n, 256), 256, 0, st>>>(d->part_vals.as<u64>(), d->q_back.as<u64>(), (what == 1 && found) ? d->q_backf.as<uint8_t>() : nullptr,
                                                  d->recv_vals.as<u64>(), (what == 1 && found) ? d->ids.as<uint8_t>() : nullptr, n);
-    if (vals) CU(cudaMemcpyAsync(vals, d->recv_vals.p, n * sizeof(u64), dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
-    if (what == 1 && found) CU(cudaMemcpyAsync(found, d->ids.p, n, dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
+    if (vals) {
+      if (dev) CU(cudaMemcpyAsync(vals, d->recv_vals.p, n * sizeof(u64), cudaMemcpyDeviceToDevice, st));
+      else OK(copy_to_host(idx, vals, d->recv_vals.p, n * sizeof(u64)));
+    }
+    if (what == 1 && found) {
+      if (dev) CU(cudaMemcpyAsync(found, d->ids.p, n, cudaMemcpyDeviceToDevice, st));
+      else OK(copy_to_host(idx, found, d->ids.p, n));
+    }
   }
   CU(cudaStreamSynchronize(st));
   return KMI_OK;
@@ -585,7 +592,7 @@ extern "C" int kmi_dist_find_positions(kmi_index* idx, const uint64_t* keys, siz
   OK(d->part_keys.ensure(std::max<size_t>(n, 1) * kb));
   OK(d->part_vals.ensure(std::max<size_t>(n, 1) * sizeof(u64)));
   if (n) {
-    CU(cudaMemcpyAsync(d->q_keys.p, keys, n * kb, cudaMemcpyHostToDevice, st));
+    OK(copy_to_device(idx, d->q_keys.p, keys, n * kb));
     k_iota<<<grid_for(n, 256), 256, 0, st>>>(d->q_tags.as<u64>(), n);
     if (idx->cfg.canonical) OK(kmi_canonicalize_dev(idx, d->q_keys.as<uint64_t>(), d->q_keys.as<uint64_t>(), n));
   }
@@ -725,20 +732,11 @@ int build_fastq_push(kmi_index* idx, uint8_t* d_text, size_t n, const uint8_t* h
   const u64 n_tiles = (n + TB - 1) / TB;
   u64 scan_tiles = 0;
   OK(fastq_scan_alloc(idx, d_text, n, &scan_tiles));
+  HostFeed feed;   // declared before the guard below: the streams are drained first, then the feed's workers stop
   if (host_src) {
-    if (!idx->copy_stream) CU(cudaStreamCreateWithFlags(&idx->copy_stream, cudaStreamNonBlocking));
-    CU(cudaEventRecord(idx->ev[3], st));
-    CU(cudaStreamWaitEvent(idx->copy_stream, idx->ev[3], 0));
-    while (idx->copy_events.size() < n_rounds) {
-      cudaEvent_t e;
-      CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-      idx->copy_events.push_back(e);
-    }
-    for (u64 r = 0; r < n_rounds; ++r) {
-      const u64 b0 = std::min<u64>(n, r * per_round * TB), b1 = std::min<u64>(n, (r + 1) * per_round * TB);
-      if (b1 > b0) CU(cudaMemcpyAsync(d_text + b0, host_src + b0, b1 - b0, cudaMemcpyHostToDevice, idx->copy_stream));
-      CU(cudaEventRecord(idx->copy_events[r], idx->copy_stream));
-    }
+    std::vector<u64> ends(n_rounds);
+    for (u64 r = 0; r < n_rounds; ++r) ends[r] = std::min<u64>(n, (r + 1) * per_round * TB);
+    OK(feed.start(idx, d_text, host_src, ends, st));
   }
   struct Guard { cudaStream_t a, b; ~Guard() { if (a) cudaStreamSynchronize(a); if (b) cudaStreamSynchronize(b); } } guard{host_src ? idx->copy_stream : nullptr, d->push_stream};
   KeySink nosink; nosink.keys = nullptr; nosink.ids = nullptr; nosink.cap = 0; nosink.cursor = nullptr;
@@ -752,7 +750,7 @@ int build_fastq_push(kmi_index* idx, uint8_t* d_text, size_t n, const uint8_t* h
     const u64 t0 = std::min(n_tiles, r * per_round), t1 = std::min(n_tiles, t0 + per_round);
     // line counts: a tile's halo continues at the NEXT tile's count, so resident text is counted whole before the first
     // round; arriving text is counted round by round and the last tile that has arrived waits for the next round
-    if (host_src) { CU(cudaStreamWaitEvent(st, idx->copy_events[r], 0)); OK(fastq_scan_range(idx, d_text, n, t0, t1)); }
+    if (host_src) { OK(feed.wait(r, st)); OK(fastq_scan_range(idx, d_text, n, t0, t1)); }
     else if (r == 0) OK(fastq_scan_range(idx, d_text, n, 0, n_tiles));
     // with a host source the last tile that has arrived needs the first bytes of the next round (k-mer halo), unless the
     // text ends there: it is parsed with the next round
@@ -854,7 +852,7 @@ int dist_build_fastq(kmi_index* idx, uint8_t* d_text, size_t n, const uint8_t* h
     total = 0; d->n_received = 0;                           // (a host text is simply copied again below: rare path)
   }
   d->last_path = 2;
-  if (host_src && n) CU(cudaMemcpyAsync(d_text, host_src, n, cudaMemcpyHostToDevice, st));
+  if (host_src && n) OK(copy_to_device(idx, d_text, host_src, n));
   // generic path in slices (bounded key staging); every rank runs the same number of slices
   const u64 SLICE = 1ULL << 30;
   const u64 n_slices = std::max<u64>((n_max + SLICE - 1) / SLICE, 1);
@@ -966,6 +964,6 @@ extern "C" int kmi_dist_build_fasta(kmi_index* idx, const uint8_t* bytes, size_t
   if (!d || (!bytes && n)) return fail(KMI_ERR_ARG, "kmi_dist_attach first");
   CU(cudaSetDevice(idx->cfg.device));
   OK(d->text.ensure(n + 64));
-  if (n) CU(cudaMemcpyAsync(d->text.p, bytes, n, cudaMemcpyHostToDevice, idx->stream));
+  OK(copy_to_device(idx, d->text.p, bytes, n));
   return kmi_dist_build_fasta_dev(idx, d->text.as<uint8_t>(), n, part, n_kmers);
 }

@@ -52,6 +52,7 @@ enum { META_HLL = 512, META_WORDS = META_HLL + HLL_M };
 struct kmi_dist_state;   // kmi_dist.cu
 struct kmi_index;
 namespace kmi { int flush_pending(kmi_index* idx); }   // kmi_api.cu: the deferred segment insert of bulk-load mode
+namespace kmi { struct HostRing; }                     // kmi_api.cu: pinned slice ring for pageable host memory (kmi_hoststage.hpp)
 
 struct kmi_index {
   kmi_config cfg;
@@ -108,6 +109,8 @@ struct kmi_index {
   uint8_t* file_buf[2] = {nullptr, nullptr};   // pinned buffers of kmi_build_file (kept between calls: pinning is slow)
   size_t file_buf_cap[2] = {0, 0};
   cudaStream_t copy_stream = nullptr;        // H2D copies of the pipelined host-pointer build
+  kmi::HostRing* hring = nullptr;            // pageable host memory goes through this ring of pinned slices (created on first use)
+  bool hring_tried = false;
   std::vector<cudaEvent_t> copy_events;    // parse+scatter share of the last bucketed build
 
   // Lazy clear: `virgin` = the table is logically empty but its memory has not been written. The segment insert of a
@@ -149,6 +152,32 @@ int fastq_scan_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64 t0, u
 int bucket_prepare(kmi_index* idx, u64 max_keys, BucketSink* bs);
 int fastq_scan(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64* n_tiles_out);
 void harvest_commit_times(kmi_index* idx);
+// ---- host <-> device copies (kmi_api.cu). Large copies whose host side is PAGEABLE go through the index's ring of pinned
+// slices, filled / drained by host threads (kmi_hoststage.hpp); pinned or small ones are plain cudaMemcpyAsync.
+// copy_to_device: on return the caller's memory has been read (or is pinned and the copy enqueued) and idx->stream is ordered
+// behind the copy. copy_to_host: like cudaMemcpyAsync(.., idx->stream) for the caller — the data is valid after the next
+// cudaStreamSynchronize(idx->stream) (a staged copy has in fact completed on return).
+int copy_to_device(kmi_index* idx, void* d_dst, const void* src, size_t bytes);
+int copy_to_host(kmi_index* idx, void* dst, const void* d_src, size_t bytes);
+void host_ring_release(kmi_index* idx);
+// HostFeed: the host -> device transfer of a pipelined build. Range i = bytes [ends[i-1], ends[i]) of `src` goes to the same
+// offsets of d_dst on idx->copy_stream (created on demand, ordered behind the work already queued on `after`), and
+// idx->copy_events[i] is recorded behind it. wait(i, s) makes stream s wait for range i (blocking the host until the range
+// has been enqueued when the source is pageable and therefore staged by threads). The destructor never returns while a copy
+// from the caller's memory is in flight.
+class HostFeed {
+ public:
+  HostFeed() = default;
+  HostFeed(const HostFeed&) = delete;
+  HostFeed& operator=(const HostFeed&) = delete;
+  ~HostFeed();
+  int start(kmi_index* idx, uint8_t* d_dst, const uint8_t* src, const std::vector<u64>& ends, cudaStream_t after);
+  int wait(size_t i, cudaStream_t consumer);
+ private:
+  struct Impl;
+  Impl* impl_ = nullptr;
+  kmi_index* idx_ = nullptr;
+};
 // kmi_sorted.cu: stable LSD radix sort of (key, value) pairs; keys/vals ping-pong with their *_tmp twins (see there)
 int device_sort_pairs(cudaStream_t st, DevBuf& hist, DevBuf& sums, u64*& keys, u64*& vals, u64*& keys_tmp, u64*& vals_tmp, u64 n,
                       int nw, int key_bits, int val_bits, u64* launches);

@@ -223,7 +223,7 @@ extern "C" int kmi_posqual_build_fastq(kmi_posqual* pq, const uint8_t* bytes, si
   if (!pq || (!bytes && n)) return fail(KMI_ERR_ARG, "null argument");
   CU(cudaSetDevice(pq->base->cfg.device));
   OK(pq->text.ensure(n + 64));
-  CU(cudaMemcpyAsync(pq->text.p, bytes, n, cudaMemcpyHostToDevice, pq->base->stream));
+  OK(copy_to_device(pq->base, pq->text.p, bytes, n));
   return kmi_posqual_build_fastq_dev(pq, pq->text.as<uint8_t>(), n, file_offset, n_kmers);
 }
 

@@ -480,8 +480,8 @@ static int sorted_build_host(kmi_sorted* s, const uint8_t* bytes, size_t n, uint
   CU(cudaSetDevice(s->base->cfg.device));
   DevBuf text;
   OK(text.ensure(n + 64));
-  CU(cudaMemcpyAsync(text.p, bytes, n, cudaMemcpyHostToDevice, sstream(s)));
-  const int r = sorted_build_dev(s, text.as<uint8_t>(), n, file_offset, fasta, n_kmers);
+  int r = copy_to_device(s->base, text.p, bytes, n);
+  if (r == KMI_OK) r = sorted_build_dev(s, text.as<uint8_t>(), n, file_offset, fasta, n_kmers);
   cudaStreamSynchronize(sstream(s));
   text.release();
   return r;
@@ -647,8 +647,8 @@ extern "C" int kmi_dump_sorted(kmi_index* idx, uint64_t* keys, uint64_t* vals, s
   }
   u64 *k = dk[0].as<u64>(), *v = dv[0].as<u64>(), *kt = dk[1].as<u64>(), *vt = dv[1].as<u64>();
   OK(device_sort_pairs(st, idx->hist, idx->hist_sums, k, v, kt, vt, n, idx->nw, 2 * idx->cfg.k, val_bits, &idx->launches));
-  if (keys) CU(cudaMemcpyAsync(keys, k, n * kb, cudaMemcpyDeviceToHost, st));
-  if (vals) CU(cudaMemcpyAsync(vals, v, n * sizeof(u64), cudaMemcpyDeviceToHost, st));
+  if (keys) OK(copy_to_host(idx, keys, k, n * kb));
+  if (vals) OK(copy_to_host(idx, vals, v, n * sizeof(u64)));
   CU(cudaStreamSynchronize(st));
   CU(cudaGetLastError());
   *n_out = n;
