@@ -124,6 +124,7 @@ int kmi::check_table_error(kmi_index* idx) {
 // go straight to cudaMemcpyAsync.
 #include "kmi_hoststage.hpp"
 #include <thread>
+#include <unistd.h>
 namespace kmi {
 struct HostRing {
   uint8_t* ring = nullptr;
@@ -187,6 +188,21 @@ static bool host_is_pageable(const void* p) {
   if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
   return a.type == cudaMemoryTypeUnregistered;
 }
+bool host_ring_ready(kmi_index* idx) {
+  HostRing* r = host_ring(idx);
+  return r && !r->busy;
+}
+// `want` bytes of the file at offset `at` (short only at the end of the file), or -1
+static long long pread_full(int fd, uint8_t* dst, size_t want, unsigned long long at) {
+  size_t got = 0;
+  while (got < want) {
+    const ssize_t r = pread(fd, dst + got, want - got, (off_t)(at + got));
+    if (r < 0) return -1;
+    if (r == 0) break;
+    got += (size_t)r;
+  }
+  return (long long)got;
+}
 static HostRing* ring_for(kmi_index* idx, const void* host, size_t bytes) {
   if (bytes == 0) return nullptr;
   HostRing* r = host_ring(idx);
@@ -232,8 +248,17 @@ struct HostFeed::Impl {
   HostStageJob<CudaStageBackend> job;
   Impl(const CudaStageBackend& b_, HostRing* r) : b(b_), job(b, r->ring, r->slice, r->slots, r->threads) {}
 };
-int HostFeed::start(kmi_index* idx, uint8_t* d_dst, const uint8_t* src, const std::vector<u64>& ends, cudaStream_t after) {
+int copy_to_device(kmi_index* idx, void* d_dst, const HostSrc& src, size_t bytes) {
+  if (src.fd < 0) return copy_to_device(idx, d_dst, static_cast<const void*>(src.mem), bytes);
+  if (bytes == 0) return KMI_OK;
+  HostFeed feed;
+  OK(feed.start(idx, static_cast<uint8_t*>(d_dst), src, std::vector<u64>{(u64)bytes}, idx->stream));
+  return feed.wait(0, idx->stream);   // (the feed's destructor then waits for the copies themselves)
+}
+
+int HostFeed::start(kmi_index* idx, uint8_t* d_dst, const HostSrc& hs, const std::vector<u64>& ends, cudaStream_t after) {
   idx_ = idx;
+  const uint8_t* src = hs.mem;
   if (!idx->copy_stream) CU(cudaStreamCreateWithFlags(&idx->copy_stream, cudaStreamNonBlocking));
   CU(cudaEventRecord(idx->ev[3], after));                   // the destination may still be in use by earlier work
   CU(cudaStreamWaitEvent(idx->copy_stream, idx->ev[3], 0));
@@ -243,7 +268,13 @@ int HostFeed::start(kmi_index* idx, uint8_t* d_dst, const uint8_t* src, const st
     idx->copy_events.push_back(e);
   }
   const u64 total = ends.empty() ? 0 : ends.back();
-  HostRing* r = ring_for(idx, src, (size_t)total);
+  HostRing* r = nullptr;
+  if (hs.fd >= 0) {
+    if (!host_ring_ready(idx)) return fail(KMI_ERR_UNSUPPORTED, "reading a file into the device needs the pinned slice ring (KMI_STAGE_THREADS > 0)");
+    r = idx->hring;
+  } else {
+    r = ring_for(idx, src, (size_t)total);
+  }
   if (!r) {   // pinned (or small): cudaMemcpyAsync does not block, everything is enqueued now
     u64 at = 0;
     for (size_t i = 0; i < ends.size(); ++i) {
@@ -258,6 +289,11 @@ int HostFeed::start(kmi_index* idx, uint8_t* d_dst, const uint8_t* src, const st
   if (!impl_) return fail(KMI_ERR_NOMEM, "out of host memory");
   r->busy = true;
   std::vector<uint64_t> e64(ends.begin(), ends.end());
+  if (hs.fd >= 0) {
+    const int fd = hs.fd;
+    const u64 base = hs.fd_off;
+    impl_->job.set_fill([fd, base](uint8_t* dst, uint64_t off, size_t len) { return pread_full(fd, dst, len, base + off) == (long long)len; });
+  }
   impl_->job.start_in(d_dst, src, e64);
   return KMI_OK;
 }
@@ -1026,7 +1062,7 @@ static int build_fastq_direct(kmi_index* idx, const uint8_t* d_bytes, size_t n, 
 // are copied into d_bytes on the copy stream while the previous round computes, so the PCIe transfer
 // hides the whole build except the last round. A round's last tile needs 64 bytes of the next round
 // (k-mer halo), so it is parsed with the next round.
-static int build_fastq_bucketed(kmi_index* idx, uint8_t* d_bytes, size_t n, u64 n_tiles, const uint8_t* host_src) {
+static int build_fastq_bucketed(kmi_index* idx, uint8_t* d_bytes, size_t n, u64 n_tiles, const HostSrc& host_src) {
   if (n_tiles == 0) return KMI_OK;
   const u64 MAX_TILES = (2 * BUCKET_MAX_KEYS) / TILE_BYTES;
   u64 per_round;
@@ -1131,7 +1167,7 @@ static int build_fastq_positions(kmi_index* idx, const uint8_t* d_bytes, size_t 
   return check_table_error(idx);
 }
 
-static int build_fastq_impl(kmi_index* idx, uint8_t* d_bytes, size_t n, const uint8_t* host_src, uint64_t* n_kmers,
+static int build_fastq_impl(kmi_index* idx, uint8_t* d_bytes, size_t n, HostSrc host_src, uint64_t* n_kmers,
                             u64 file_offset = 0) {
   if (idx->cfg.mode != KMI_MODE_COUNT) {
     if (host_src) OK(copy_to_device(idx, d_bytes, host_src, n));
@@ -1142,7 +1178,7 @@ static int build_fastq_impl(kmi_index* idx, uint8_t* d_bytes, size_t n, const ui
   CU(cudaEventRecord(idx->ev[0], idx->stream));
   if (host_src && !bucketed) {
     OK(copy_to_device(idx, d_bytes, host_src, n));
-    host_src = nullptr;
+    host_src = HostSrc();
   }
   OK(fastq_scan_alloc(idx, d_bytes, n, &n_tiles));
   if (!bucketed) OK(fastq_scan_range(idx, d_bytes, n, 0, n_tiles));
@@ -2123,6 +2159,39 @@ bool has_suffix(const char* s, const char* e) {
 }
 }  // namespace
 
+// FASTQ files when the pinned slice ring is available: no copy of the file in host memory at all. The file is cut into
+// chunks at record boundaries found by reading only a chunk's last bytes (FASTQParser::find_first_record on a tail window),
+// and every chunk is ONE pipelined build whose bytes the ring's threads pread straight into pinned slices (HostSrc::file):
+// the reads, the H2D copies and the rounds of the build overlap from the first slice on, where the chunked reader below
+// reads a whole chunk before its build starts.
+static int build_file_fastq_stream(kmi_index* idx, int fd, u64 size, u64 CH, const char* path, uint64_t* n_kmers) {
+  std::vector<uint8_t> tail;
+  u64 pos = 0, total = 0;
+  while (pos < size) {
+    const u64 end = std::min<u64>(size, pos + CH), len = end - pos;
+    u64 cut = end;
+    if (end < size) {
+      cut = 0;
+      for (u64 w = std::min<u64>(len, std::max<u64>(std::min<u64>(len / 8, 1u << 20), 2048));; w = std::min<u64>(len, w * 4)) {
+        tail.resize(w);
+        if (pread_full(fd, tail.data(), (size_t)w, end - w) != (long long)w) return fail(KMI_ERR_ARG, "read error on %s", path);
+        uint64_t off = 0;
+        const int r = kmi_fastq_find_first_record(tail.data(), end - w, (size_t)w, end - w, end, 0, size, &off);
+        if (r == KMI_OK && off < end && off > pos) { cut = off; break; }
+        if (w == len) break;
+      }
+      if (cut == 0) return fail(KMI_ERR_FORMAT, "no FASTQ record boundary inside a chunk of %llu bytes at offset %llu", (unsigned long long)len, (unsigned long long)pos);
+    }
+    OK(idx->stage_in.ensure(cut - pos + 64));
+    uint64_t produced = 0;
+    OK(build_fastq_impl(idx, idx->stage_in.as<uint8_t>(), (size_t)(cut - pos), HostSrc::file(fd, pos), &produced, pos));
+    total += produced;
+    pos = cut;
+  }
+  if (n_kmers) *n_kmers = total;
+  return KMI_OK;
+}
+
 extern "C" int kmi_build_file(kmi_index* idx, const char* path, int format, uint64_t* n_kmers) {
   if (!idx || !path) return fail(KMI_ERR_ARG, "null argument");
   if (n_kmers) *n_kmers = 0;
@@ -2139,7 +2208,10 @@ extern "C" int kmi_build_file(kmi_index* idx, const char* path, int format, uint
   if (fstat(f.fd, &st) != 0) return fail(KMI_ERR_ARG, "cannot stat %s", path);
   const u64 size = (u64)st.st_size;
   u64 CH = 1ull << 30;   // measured on the 2.1 GB bench file (page cache): 134 ms with 256 MiB chunks, 120 with 1 GiB
+  const bool stream = format == 1 && size > 0 && host_ring_ready(idx);
+  if (stream) CH = 4ull << 30;   // (no pinned buffer of the chunk's size: only the device staging buffer grows with it)
   if (const char* e = getenv("KMI_FILE_CHUNK_BYTES")) CH = std::max<u64>(strtoull(e, nullptr, 10), 256);
+  if (stream) return build_file_fastq_stream(idx, f.fd, size, CH, path, n_kmers);
   CH = std::min<u64>(CH, std::max<u64>(size, 1));
   const u64 CARRY_MAX = std::min<u64>(CH, 16ull << 20);   // a record / the K-1 tail never comes near this
   OK(pinned_ensure(idx, 0, CH + CARRY_MAX + 64));

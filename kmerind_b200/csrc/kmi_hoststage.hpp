@@ -24,6 +24,7 @@
 #include <condition_variable>
 #include <cstdint>
 #include <cstring>
+#include <functional>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -37,6 +38,10 @@ template <class Backend> class HostStageJob {
   HostStageJob(const HostStageJob&) = delete;
   HostStageJob& operator=(const HostStageJob&) = delete;
   ~HostStageJob() { finish(true); }
+
+  // where the bytes of a host -> device job come from when it is not memory: fill(dst, offset, len) puts bytes [offset,
+  // offset + len) of the source into dst (a pread of a file: kmi_build_file) and returns false on failure. Set before start_in.
+  void set_fill(std::function<bool(uint8_t*, uint64_t, size_t)> f) { fill_ = std::move(f); }
 
   // host -> device, asynchronous: range i is [ends[i-1], ends[i]) (ends ascending, empty ranges allowed). Returns at once;
   // wait_mark(i) blocks the caller until range i has been enqueued and record_mark(i) has run.
@@ -124,7 +129,9 @@ template <class Backend> class HostStageJob {
         // the slot is free once the device copy of the slice that used it last has finished
         if (s >= R_ && !wait_state(s - R_, 2)) return;
         if (!b_.wait_slot(slot)) { fail(); return; }
-        std::memcpy(ring_ + (size_t)slot * slice_, hsrc_ + sl.off, (size_t)sl.len);
+        uint8_t* dst = ring_ + (size_t)slot * slice_;
+        if (!fill_) std::memcpy(dst, hsrc_ + sl.off, (size_t)sl.len);
+        else if (!fill_(dst, sl.off, (size_t)sl.len)) { fail(); return; }
       }
       set_state(s, 1);
     }
@@ -165,6 +172,7 @@ template <class Backend> class HostStageJob {
   const int T_;
   uint8_t* dev_ = nullptr; const uint8_t* hsrc_ = nullptr;
   uint8_t* hdst_ = nullptr; const uint8_t* dsrc_ = nullptr;
+  std::function<bool(uint8_t*, uint64_t, size_t)> fill_;
   std::vector<Slice> slices_;
   std::vector<char> state_;
   std::vector<std::thread> threads_;

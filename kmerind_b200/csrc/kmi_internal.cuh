@@ -160,6 +160,19 @@ void harvest_commit_times(kmi_index* idx);
 int copy_to_device(kmi_index* idx, void* d_dst, const void* src, size_t bytes);
 int copy_to_host(kmi_index* idx, void* dst, const void* d_src, size_t bytes);
 void host_ring_release(kmi_index* idx);
+// where the bytes of a host-side build come from: the caller's memory, or a file read with pread straight into the pinned
+// slices (kmi_build_file: no intermediate copy of the file in host memory; needs the ring — host_ring_ready)
+struct HostSrc {
+  const uint8_t* mem = nullptr;
+  int fd = -1;
+  u64 fd_off = 0;                                   // file offset of byte 0 of the source
+  HostSrc() {}
+  HostSrc(const uint8_t* m) : mem(m) {}             // (implicit: every host-pointer entry point passes its pointer)
+  static HostSrc file(int fd_, u64 off) { HostSrc s; s.fd = fd_; s.fd_off = off; return s; }
+  explicit operator bool() const { return mem != nullptr || fd >= 0; }
+};
+bool host_ring_ready(kmi_index* idx);               // the ring exists (or can be created) and no feed is running on it
+int copy_to_device(kmi_index* idx, void* d_dst, const HostSrc& src, size_t bytes);
 // HostFeed: the host -> device transfer of a pipelined build. Range i = bytes [ends[i-1], ends[i]) of `src` goes to the same
 // offsets of d_dst on idx->copy_stream (created on demand, ordered behind the work already queued on `after`), and
 // idx->copy_events[i] is recorded behind it. wait(i, s) makes stream s wait for range i (blocking the host until the range
@@ -171,7 +184,7 @@ class HostFeed {
   HostFeed(const HostFeed&) = delete;
   HostFeed& operator=(const HostFeed&) = delete;
   ~HostFeed();
-  int start(kmi_index* idx, uint8_t* d_dst, const uint8_t* src, const std::vector<u64>& ends, cudaStream_t after);
+  int start(kmi_index* idx, uint8_t* d_dst, const HostSrc& src, const std::vector<u64>& ends, cudaStream_t after);
   int wait(size_t i, cudaStream_t consumer);
  private:
   struct Impl;

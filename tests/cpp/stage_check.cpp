@@ -132,6 +132,29 @@ int main() {
       check(!job.run_out(host.data(), dev.data(), n), "run_out must report the failed copy");
     }
   }
+  // a source that is not memory (the pread of kmi_build_file): bytes come from the fill function; a failing read is reported
+  for (int bad = 0; bad < 2; ++bad) {
+    const size_t n = 300000, slice = 4096;
+    std::vector<uint8_t> file(n), dev(n, 0), ring(slice * 5);
+    for (size_t i = 0; i < n; ++i) file[i] = (uint8_t)(i * 2654435761u >> 13);
+    FakeStream st;
+    FakeBackend b(st, 5, 3);
+    kmi::HostStageJob<FakeBackend> job(b, ring.data(), slice, 5, 4);
+    job.set_fill([&](uint8_t* dst, uint64_t off, size_t len) {
+      if (bad && off >= 200000) return false;
+      std::memcpy(dst, file.data() + off, len);
+      return true;
+    });
+    job.start_in(dev.data(), nullptr, std::vector<uint64_t>{100000, 100000, n});
+    if (!bad) {   // (once a read has failed every wait reports it, also for marks that were reached before)
+      check(job.wait_mark(0) && job.wait_mark(1), "marks of a healthy job");
+      st.wait(b.mark(1));
+      check(std::memcmp(dev.data(), file.data(), 100000) == 0, "bytes from the fill function");
+    }
+    check(job.wait_mark(2) == !bad, "a failed read must fail the mark");
+    check(job.finish(false) == !bad, "a failed read must fail the job");
+    if (!bad) { st.wait(b.mark(2)); check(std::memcmp(dev.data(), file.data(), n) == 0, "all bytes from the fill function"); }
+  }
   // a job abandoned half way (early return of the caller): the destructor stops the workers
   {
     const size_t n = 4000000, slice = 1000;

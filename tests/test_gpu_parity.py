@@ -747,14 +747,19 @@ def test_cpp_adapter_with_the_reference_key_type():
     assert r.returncode == 0 and "adapter ok (bliss::common::Kmer)" in r.stdout, r.stdout + r.stderr
 
 
+@pytest.mark.parametrize("stage_threads", ("3", "0"))
 @pytest.mark.parametrize("name,k,chunk", [("natural.fastq", 21, 3000), ("test.medium.fastq", 31, 5000), ("natural.withN.fastq", 15, 1 << 28)])
-def test_build_file_fastq_streams_record_aligned_chunks(name, k, chunk, tmp_path, monkeypatch):
-    """kmi_build_file: the file is read in chunks that end at record boundaries (the rest is carried into the next buffer);
-    count index == oracle; position index ids are file offsets of the whole file."""
+def test_build_file_fastq_streams_record_aligned_chunks(name, k, chunk, stage_threads, tmp_path, monkeypatch):
+    """kmi_build_file: the file is cut into chunks that end at record boundaries — read by the slice ring's threads straight
+    into pinned slices (stage_threads > 0: boundaries found in a chunk's tail window), or chunk by chunk into two pinned
+    buffers with the rest carried over (stage_threads 0); count index == oracle; position index ids are file offsets of the
+    whole file."""
     buf = ou.read_fixture(name)
     path = tmp_path / name
     path.write_bytes(buf.tobytes())
     monkeypatch.setenv("KMI_FILE_CHUNK_BYTES", str(chunk))
+    monkeypatch.setenv("KMI_STAGE_THREADS", stage_threads)
+    monkeypatch.setenv("KMI_STAGE_SLICE_BYTES", "1024")
     wk, wi, _ = ou.fastq_kmers(buf, k, want_ids=True)
     dk, dc = ou.count_sorted(wk, k)
     with kb.CountIndex(k) as idx:

@@ -141,3 +141,28 @@ def test_pageable_fasta_positions(tiny_ring):
         p = np.searchsorted(uk, ou.canonical(q, k))
         assert np.array_equal(np.diff(off), cnt[p].astype(np.uint64))
         assert np.array_equal(np.sort(vals[off[0]:off[1]]), si[first[p[0]]:first[p[0]] + cnt[p[0]]])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("chunk", (12 << 20, 1 << 32))
+def test_file_streamed_through_the_ring_equals_resident(monkeypatch, tmp_path, chunk):
+    """kmi_build_file on a 48 MB FASTQ file: the ring's threads pread the file's slices (no host copy of the file); with
+    12 MiB chunks the file is cut at record boundaries found in each chunk's tail and every chunk is a bucketed build"""
+    torch = pytest.importorskip("torch")
+    import kmerind_b200 as kb
+    monkeypatch.setenv("KMI_FILE_CHUNK_BYTES", str(chunk))
+    monkeypatch.setenv("KMI_STAGE_SLICE_BYTES", str(1 << 20))
+    reads, k = 150000, 31
+    rec = kb.synth_record_bytes(150)
+    dev = torch.empty(reads * rec, dtype=torch.uint8, device="cuda")
+    kb.synth_fastq_dev(0, dev.data_ptr(), 0, reads, 150, 2_000_000, 13, 5000, 0)
+    torch.cuda.synchronize()
+    text = dev.cpu().numpy()
+    path = tmp_path / "reads.fastq"
+    path.write_bytes(text.tobytes())
+    want = _dev_build(kb, torch, text, k)
+    for threads in ("4", "0"):
+        monkeypatch.setenv("KMI_STAGE_THREADS", threads)
+        with kb.CountIndex(k, hash=kb.HASH_FARM) as idx:
+            n = idx.build_file(str(path))
+            assert (n, idx.local_size(), idx.checksum()) == want

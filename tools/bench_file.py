@@ -27,9 +27,12 @@ def main():
     del text
     n_kmers = n_reads * (150 - k + 1)
     try:
-        with kb.CountIndex(k, hash=kb.HASH_FARM, reserve=int(0.25 * n_kmers)) as idx:
-            for chunk in (256 << 20, 1 << 30, 4 << 30):
-                os.environ["KMI_FILE_CHUNK_BYTES"] = str(chunk)
+        # stage threads 0 = the chunked reader (whole chunk into a pinned buffer, then its build); > 0 = slices pread straight
+        # into the pinned ring by that many threads while the build runs
+        for threads, chunk in ((0, 1 << 30), (4, 4 << 30), (8, 4 << 30), (8, 1 << 30), (12, 4 << 30), (16, 4 << 30)):
+            os.environ["KMI_STAGE_THREADS"] = str(threads)
+            os.environ["KMI_FILE_CHUNK_BYTES"] = str(chunk)
+            with kb.CountIndex(k, hash=kb.HASH_FARM, reserve=int(0.25 * n_kmers)) as idx:
                 best = None
                 for rep in range(4):
                     idx.clear()
@@ -40,8 +43,8 @@ def main():
                     assert n == n_kmers and idx.checksum()[1] == n
                     if rep:
                         best = dt if best is None else min(best, dt)
-                print("build_file, %.2f GB FASTQ, chunk %d MiB: %.1f ms = %.2f G k-mers/s (%.1f GB/s of text)"
-                      % (nbytes / 1e9, chunk >> 20, best, n_kmers / best / 1e6, nbytes / best / 1e6))
+                print("build_file, %.2f GB FASTQ, stage threads %d, chunk %d MiB: %.1f ms = %.2f G k-mers/s (%.1f GB/s of text)"
+                      % (nbytes / 1e9, threads, chunk >> 20, best, n_kmers / best / 1e6, nbytes / best / 1e6), flush=True)
     finally:
         os.remove(path)
 
