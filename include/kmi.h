@@ -159,6 +159,13 @@ int kmi_fasta_halo_end(const uint8_t* bytes, uint64_t mem_offset, size_t n, uint
  * chunks end at a record boundary (kmi_fastq_find_first_record), FASTA chunks are blocks with a K-1 halo (kmi_fasta_block);
  * position ids carry file offsets. Chunk size 1 GiB (environment KMI_FILE_CHUNK_BYTES overrides it). */
 int kmi_build_file(kmi_index* idx, const char* path, int format, uint64_t* n_kmers);
+/* a1: rank `rank`'s block of ONE file shared by `nranks` ranks — partitioned_file<posix_file, Parser>::read_file with the
+ * BlockPartitioner (src/io/file.hpp:1239-1251,1342-1431): the equal byte ranges [size * r / p, size * (r + 1) / p); for FASTQ
+ * every boundary is moved forward to the first whole record at or after it (FASTQParser::find_first_record on a window of
+ * the file, fastq_loader.hpp:269-357,696-873), so blocks hold whole records and tile the file; a FASTA block is the byte
+ * range as it is (kmi_fasta_block / kmi_fasta_part take any cut). Host only: reads a few KiB around the two boundaries.
+ * format as in kmi_build_file. file_size is optional. */
+int kmi_file_block(const char* path, int format, int rank, int nranks, uint64_t* begin, uint64_t* end, uint64_t* file_size);
 
 /* ---- f2: persistence. The reference keeps no index on disk; this is the wire format of one shard: a 64-byte header
  * ("KMIDX001", k, mode, words per key, canonical, entry count) followed by the entries of to_vector()
@@ -321,6 +328,13 @@ int kmi_dist_build_fastq(kmi_index* idx, const uint8_t* bytes, size_t n, uint64_
 int kmi_dist_build_fastq_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, uint64_t file_offset, uint64_t* n_kmers);
 int kmi_dist_build_fasta(kmi_index* idx, const uint8_t* bytes, size_t n, const kmi_fasta_part* part, uint64_t* n_kmers);
 int kmi_dist_build_fasta_dev(kmi_index* idx, const uint8_t* d_bytes, size_t n, const kmi_fasta_part* part, uint64_t* n_kmers);
+/* Index::build_posix<FASTQParser|FASTAParser>(filename, comm) at p ranks (kmer_index.hpp:231-260,332-372 over
+ * partitioned_file::read_file, file.hpp:1342-1431): collective; every rank passes the SAME path, takes its block of the
+ * file (kmi_file_block with the communicator's rank / size), reads it — FASTQ: the pinned slice ring's threads pread it
+ * straight into pinned slices while the sharded build runs; FASTA: block + K-1 halo, then kmi_dist_build_fasta with the block
+ * as kmi_fasta_part — and the k-mers go to their owners. n_kmers: k-mers generated from THIS rank's block. A rank that cannot
+ * read the file makes every rank return the error (one all-reduce before the build). */
+int kmi_dist_build_file(kmi_index* idx, const char* path, int format, uint64_t* n_kmers);
 int kmi_dist_insert(kmi_index* idx, const uint64_t* keys, const uint64_t* vals, size_t n);
 int kmi_dist_insert_dev(kmi_index* idx, const uint64_t* d_keys, const uint64_t* d_vals, size_t n);
 int kmi_dist_count(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* counts);

@@ -420,10 +420,12 @@ class b200_map {
   const_iterator cbegin() const { to_vector(snapshot_); return snapshot_.cbegin(); }
   const_iterator cend() const { return snapshot_.cend(); }
 
-  /// Index::build_posix<FASTQParser|FASTAParser>(filename) — kmer_index.hpp:332-372
+  /// Index::build_posix<FASTQParser|FASTAParser>(filename, comm) — kmer_index.hpp:231-260,332-372. A map that spans several
+  /// ranks is built collectively: every rank passes the same file and takes its block of it (partitioned_file::read_file,
+  /// file.hpp:1342-1431 -> kmi_dist_build_file); returns the k-mers generated from this rank's share
   uint64_t build_file(const std::string& filename) {
     uint64_t kmers = 0;
-    check(kmi_build_file(h_, filename.c_str(), 0, &kmers));   // wrong extension -> std::invalid_argument, as the reference
+    check((kc_ ? kmi_dist_build_file : kmi_build_file)(h_, filename.c_str(), 0, &kmers));   // wrong extension -> std::invalid_argument, as the reference
     return kmers;
   }
   /// this rank's record-aligned block of the reads (kmi::fastq_cuts); sharded maps exchange the k-mers by owner

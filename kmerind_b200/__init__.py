@@ -74,6 +74,8 @@ def load_library(build_if_missing=False):
         "kmi_fasta_block_summary_dev": [_P, _P, _SZ, ctypes.c_int, _P],
         "kmi_fasta_halo_end": [_P, _U64, _SZ, _U64, ctypes.c_int, _P],
         "kmi_build_file": [_P, ctypes.c_char_p, ctypes.c_int, _P],
+        "kmi_file_block": [ctypes.c_char_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, _P, _P, _P],
+        "kmi_dist_build_file": [_P, ctypes.c_char_p, ctypes.c_int, _P],
         "kmi_save": [_P, ctypes.c_char_p], "kmi_load": [_P, ctypes.c_char_p, _P],
         "kmi_comm_unique_id": [_P], "kmi_comm_create": [_P, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(_P)],
         "kmi_comm_rank": [_P], "kmi_comm_size": [_P], "kmi_comm_barrier": [_P],
@@ -138,7 +140,7 @@ EXPORTED_SYMBOLS = (
     "kmi_create", "kmi_destroy", "kmi_last_error", "kmi_device_count", "kmi_set_stream", "kmi_set_param", "kmi_flush", "kmi_bulk_stats", "kmi_reserve", "kmi_clear",
     "kmi_build_fastq", "kmi_build_fasta", "kmi_build_fastq_dev", "kmi_build_fasta_dev",
     "kmi_parse_fastq_dev", "kmi_parse_fasta_dev", "kmi_parse_fasta_block_dev", "kmi_build_fasta_block", "kmi_build_fasta_block_dev",
-    "kmi_fasta_block_summary_dev", "kmi_fasta_halo_end", "kmi_build_file", "kmi_save", "kmi_load", "kmi_fastq_find_first_record",
+    "kmi_fasta_block_summary_dev", "kmi_fasta_halo_end", "kmi_build_file", "kmi_file_block", "kmi_dist_build_file", "kmi_save", "kmi_load", "kmi_fastq_find_first_record",
     "kmi_comm_unique_id", "kmi_comm_create", "kmi_comm_destroy", "kmi_comm_rank", "kmi_comm_size", "kmi_comm_barrier",
     "kmi_comm_allreduce_u64", "kmi_comm_allgather_u64", "kmi_dist_attach", "kmi_dist_build_fastq", "kmi_dist_build_fastq_dev",
     "kmi_dist_build_fasta", "kmi_dist_build_fasta_dev", "kmi_dist_insert", "kmi_dist_insert_dev", "kmi_dist_count", "kmi_dist_find",
@@ -224,6 +226,14 @@ def fasta_chain(summaries, bol, file_starts_with_header):
             runs += int(r) - (1 if (first_h and kind) else 0)
             kind = int(last_h)
     return out
+
+
+def file_block(path, rank, nranks, format=0):
+    """(begin, end, file size) of rank's block of ONE file shared by nranks ranks (kmi_file_block): equal byte ranges, FASTQ
+    boundaries moved forward to whole records — partitioned_file::read_file + BlockPartitioner (file.hpp:1239-1251,1342-1431)"""
+    b, e, sz = _U64(0), _U64(0), _U64(0)
+    _check(load_library().kmi_file_block(os.fsencode(path), format, rank, nranks, ctypes.byref(b), ctypes.byref(e), ctypes.byref(sz)))
+    return b.value, e.value, sz.value
 
 
 def fastq_cuts(buf, parts):

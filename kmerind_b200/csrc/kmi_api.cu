@@ -151,8 +151,11 @@ static size_t env_size(const char* name, size_t dflt) {
 static HostRing* host_ring(kmi_index* idx) {
   if (idx->hring || idx->hring_tried) return idx->hring;
   idx->hring_tried = true;
+  // default: up to 8 threads (the bench box's memcpy rate peaks there: 39 GB/s), and the cores are shared with the other
+  // ranks of a sharded index (one process per GPU on one host)
   const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-  const int threads = (int)std::min<size_t>(env_size("KMI_STAGE_THREADS", std::min(8u, hw)), 64);
+  const unsigned share = (unsigned)std::max(1, idx->cfg.nranks);
+  const int threads = (int)std::min<size_t>(env_size("KMI_STAGE_THREADS", std::min(8u, std::max(1u, hw / share))), 64);
   if (threads <= 0) return nullptr;
   HostRing* r = new (std::nothrow) HostRing();
   if (!r) return nullptr;
@@ -2159,6 +2162,72 @@ bool has_suffix(const char* s, const char* e) {
 }
 }  // namespace
 
+int kmi::file_format(const char* path, int* format) {
+  if (*format == 0) {
+    if (has_suffix(path, ".fastq") || has_suffix(path, ".fq")) *format = 1;
+    else if (has_suffix(path, ".fasta") || has_suffix(path, ".fa")) *format = 2;
+    else return fail(KMI_ERR_ARG, "input filename extension is not supported.");   // kmer_index.hpp:245-254
+  }
+  if (*format != 1 && *format != 2) return fail(KMI_ERR_ARG, "format must be 0 (by extension), 1 (FASTQ) or 2 (FASTA)");
+  return KMI_OK;
+}
+long long kmi::file_read(int fd, uint8_t* dst, size_t want, u64 at) { return read_at(fd, dst, want, at); }
+
+// first whole FASTQ record at or after `start` (FASTQParser::find_first_record on a growing window of the file): what
+// partitioned_file::read_file does at every block boundary (file.hpp:1342-1431). `size` when no record starts after it.
+static int fastq_cut_at(int fd, u64 size, u64 start, u64* cut) {
+  if (start == 0 || start >= size) { *cut = std::min(start, size); return KMI_OK; }
+  std::vector<uint8_t> win;
+  for (u64 w = std::min<u64>(size - start, 64u << 10);; w = std::min<u64>(size - start, w * 4)) {
+    win.resize(w);
+    if (pread_full(fd, win.data(), (size_t)w, start) != (long long)w) return fail(KMI_ERR_ARG, "read error at offset %llu", (unsigned long long)start);
+    uint64_t off = 0;
+    const int r = kmi_fastq_find_first_record(win.data(), start, (size_t)w, start, start + w, 0, size, &off);
+    if (r == KMI_OK && off < start + w) { *cut = off; return KMI_OK; }
+    if (start + w >= size) {                               // the window reached the end of the file: no record starts after `start`
+      if (r != KMI_OK) return r;
+      *cut = size;
+      return KMI_OK;
+    }
+  }
+}
+int kmi::file_block_fd(int fd, u64 size, int format, int rank, int nranks, u64* begin, u64* end) {
+  if (nranks < 1 || rank < 0 || rank >= nranks) return fail(KMI_ERR_ARG, "rank %d of %d", rank, nranks);
+  // BlockPartitioner: equal byte ranges (128-bit product: size * rank does not overflow for any file)
+  const u64 b0 = (u64)((unsigned __int128)size * (unsigned)rank / (unsigned)nranks);
+  const u64 e0 = (u64)((unsigned __int128)size * (unsigned)(rank + 1) / (unsigned)nranks);
+  if (format == 2) { *begin = b0; *end = e0; return KMI_OK; }
+  OK(fastq_cut_at(fd, size, b0, begin));
+  if (rank + 1 == nranks) *end = size;
+  else OK(fastq_cut_at(fd, size, e0, end));
+  if (*end < *begin) *end = *begin;
+  return KMI_OK;
+}
+int kmi::file_fasta_halo_end(int fd, u64 size, u64 valid_end, int k, u64* halo_end) {
+  if (valid_end >= size) { *halo_end = size; return KMI_OK; }
+  std::vector<uint8_t> win;
+  for (u64 w = std::min<u64>(size - valid_end, 4096 + 2 * (u64)k);; w = std::min<u64>(size - valid_end, w * 4)) {
+    win.resize(w);
+    if (pread_full(fd, win.data(), (size_t)w, valid_end) != (long long)w) return fail(KMI_ERR_ARG, "read error at offset %llu", (unsigned long long)valid_end);
+    uint64_t he = 0;
+    OK(kmi_fasta_halo_end(win.data(), valid_end, (size_t)w, valid_end, k, &he));
+    if (he < valid_end + w || valid_end + w >= size) { *halo_end = he; return KMI_OK; }   // K-1 bases found, or the file ends
+  }
+}
+extern "C" int kmi_file_block(const char* path, int format, int rank, int nranks, uint64_t* begin, uint64_t* end, uint64_t* file_size) {
+  if (!path || !begin || !end) return fail(KMI_ERR_ARG, "null argument");
+  OK(file_format(path, &format));
+  FdGuard f{open(path, O_RDONLY)};
+  if (f.fd < 0) return fail(KMI_ERR_ARG, "cannot open %s", path);
+  struct stat st;
+  if (fstat(f.fd, &st) != 0) return fail(KMI_ERR_ARG, "cannot stat %s", path);
+  if (file_size) *file_size = (uint64_t)st.st_size;
+  u64 b = 0, e = 0;
+  OK(file_block_fd(f.fd, (u64)st.st_size, format, rank, nranks, &b, &e));
+  *begin = b; *end = e;
+  return KMI_OK;
+}
+
 // FASTQ files when the pinned slice ring is available: no copy of the file in host memory at all. The file is cut into
 // chunks at record boundaries found by reading only a chunk's last bytes (FASTQParser::find_first_record on a tail window),
 // and every chunk is ONE pipelined build whose bytes the ring's threads pread straight into pinned slices (HostSrc::file):
@@ -2195,12 +2264,7 @@ static int build_file_fastq_stream(kmi_index* idx, int fd, u64 size, u64 CH, con
 extern "C" int kmi_build_file(kmi_index* idx, const char* path, int format, uint64_t* n_kmers) {
   if (!idx || !path) return fail(KMI_ERR_ARG, "null argument");
   if (n_kmers) *n_kmers = 0;
-  if (format == 0) {
-    if (has_suffix(path, ".fastq") || has_suffix(path, ".fq")) format = 1;
-    else if (has_suffix(path, ".fasta") || has_suffix(path, ".fa")) format = 2;
-    else return fail(KMI_ERR_ARG, "input filename extension is not supported.");   // kmer_index.hpp:245-254
-  }
-  if (format != 1 && format != 2) return fail(KMI_ERR_ARG, "format must be 0 (by extension), 1 (FASTQ) or 2 (FASTA)");
+  OK(file_format(path, &format));
   CU(cudaSetDevice(idx->cfg.device));
   FdGuard f{open(path, O_RDONLY)};
   if (f.fd < 0) return fail(KMI_ERR_ARG, "cannot open %s", path);

@@ -693,7 +693,7 @@ int build_fastq_generic(kmi_index* idx, const uint8_t* d_text, size_t n, u64 fil
 
 // The count-index build over NVLink. Text: `n` bytes at d_text (device). With host_src the bytes are copied round by
 // round on the copy stream while earlier rounds are parsed and pushed.
-int build_fastq_push(kmi_index* idx, uint8_t* d_text, size_t n, const uint8_t* host_src, u64 n_max, u64* n_kmers, bool* redo) {
+int build_fastq_push(kmi_index* idx, uint8_t* d_text, size_t n, const HostSrc& host_src, u64 n_max, u64* n_kmers, bool* redo) {
   kmi_dist_state* d = idx->dist;
   kmi_comm* c = d->comm;
   const int p = c->nranks, me = c->rank;
@@ -818,7 +818,7 @@ int build_fastq_push(kmi_index* idx, uint8_t* d_text, size_t n, const uint8_t* h
   return KMI_OK;
 }
 
-int dist_build_fastq(kmi_index* idx, uint8_t* d_text, size_t n, const uint8_t* host_src, u64 file_offset, uint64_t* n_kmers) {
+int dist_build_fastq(kmi_index* idx, uint8_t* d_text, size_t n, const HostSrc& host_src, u64 file_offset, uint64_t* n_kmers) {
   kmi_dist_state* d = idx->dist;
   cudaStream_t st = idx->stream;
   if (n_kmers) *n_kmers = 0;
@@ -904,6 +904,54 @@ extern "C" int kmi_dist_build_fastq(kmi_index* idx, const uint8_t* bytes, size_t
   CU(cudaSetDevice(idx->cfg.device));
   OK(idx->stage_in.ensure(n + 64));
   return dist_build_fastq(idx, idx->stage_in.as<uint8_t>(), n, bytes, file_offset, n_kmers);
+}
+
+// Index::build_posix(filename, comm) at p ranks: every rank takes its block of the ONE file (kmi_file_block) and builds from it
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+extern "C" int kmi_dist_build_file(kmi_index* idx, const char* path, int format, uint64_t* n_kmers) {
+  kmi_dist_state* d = dist_of(idx);
+  if (!d || !path) return fail(KMI_ERR_ARG, "kmi_dist_attach first");
+  CU(cudaSetDevice(idx->cfg.device));
+  if (n_kmers) *n_kmers = 0;
+  const int p = d->comm->nranks, me = d->comm->rank;
+  struct Fd { int fd; ~Fd() { if (fd >= 0) close(fd); } } f{-1};
+  u64 size = 0, b = 0, e = 0, he = 0;
+  std::vector<uint8_t> buf;                                // FASTA block + halo; FASTQ block when the slice ring is off
+  int r = file_format(path, &format);
+  if (r == KMI_OK) {
+    f.fd = open(path, O_RDONLY);
+    struct stat st;
+    if (f.fd < 0 || fstat(f.fd, &st) != 0) r = fail(KMI_ERR_ARG, "cannot open %s", path);
+    else size = (u64)st.st_size;
+  }
+  if (r == KMI_OK) r = file_block_fd(f.fd, size, format, me, p, &b, &e);
+  const bool stream = r == KMI_OK && format == 1 && e > b && host_ring_ready(idx);
+  if (r == KMI_OK && format == 2) r = file_fasta_halo_end(f.fd, size, e, idx->cfg.k, &he);
+  if (r == KMI_OK && !stream) {
+    const u64 hi = format == 2 ? he : e;
+    buf.resize((size_t)(hi - b));
+    if (file_read(f.fd, buf.data(), buf.size(), b) != (long long)buf.size()) r = fail(KMI_ERR_ARG, "read error on %s", path);
+  }
+  // nobody enters the build's collectives unless every rank has its block
+  char msg[400];
+  snprintf(msg, sizeof(msg), "%s", kmi_last_error());
+  u64 bad = r == KMI_OK ? 0 : 1;
+  OK(comm_allreduce(d->comm, &bad, 1, ncclMax, idx->stream));
+  if (r != KMI_OK) return fail(r, "%s", msg);
+  if (bad) return fail(KMI_ERR_ARG, "another rank could not read its block of %s", path);
+  if (format == 1) {
+    const size_t n = (size_t)(e - b);
+    OK(idx->stage_in.ensure(n + 64));
+    const HostSrc src = stream ? HostSrc::file(f.fd, b) : HostSrc(buf.data());
+    return dist_build_fastq(idx, idx->stage_in.as<uint8_t>(), n, src, b, n_kmers);
+  }
+  uint8_t before = '\n';
+  if (b > 0 && pread(f.fd, &before, 1, (off_t)(b - 1)) != 1) before = 0;   // (cannot fail after the reads above; 0 = not a line start)
+  kmi_fasta_part part;
+  part.file_offset = b; part.n_valid = e - b; part.bol = (b == 0 || before == '\n') ? 1 : 0; part.reserved = 0;
+  return kmi_dist_build_fasta(idx, buf.data(), buf.size(), &part, n_kmers);
 }
 
 // FASTA: rank r holds block r of ONE file (blocks in rank order, cut at any byte) or — part == NULL — a whole file of its own.

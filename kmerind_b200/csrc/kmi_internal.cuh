@@ -171,6 +171,11 @@ struct HostSrc {
   static HostSrc file(int fd_, u64 off) { HostSrc s; s.fd = fd_; s.fd_off = off; return s; }
   explicit operator bool() const { return mem != nullptr || fd >= 0; }
 };
+// file helpers of kmi_build_file, shared with the sharded file build (kmi_dist.cu)
+int file_format(const char* path, int* format);                          // 0 = by extension -> 1 FASTQ / 2 FASTA (KMI_ERR_ARG)
+long long file_read(int fd, uint8_t* dst, size_t want, u64 at);          // parallel pread; bytes read (short at EOF) or -1
+int file_block_fd(int fd, u64 size, int format, int rank, int nranks, u64* begin, u64* end);
+int file_fasta_halo_end(int fd, u64 size, u64 valid_end, int k, u64* halo_end);
 bool host_ring_ready(kmi_index* idx);               // the ring exists (or can be created) and no feed is running on it
 int copy_to_device(kmi_index* idx, void* d_dst, const HostSrc& src, size_t bytes);
 // HostFeed: the host -> device transfer of a pipelined build. Range i = bytes [ends[i-1], ends[i]) of `src` goes to the same

@@ -7,6 +7,7 @@ torch.distributed group (any backend: nccl on the GPU box, gloo in the CPU tests
 MPI_Bcast, and (2) forwards calls. Test / bench harness; C++ callers use include/kmi.h directly (tests/cpp/dist_check.cpp).
 """
 import ctypes
+import os
 
 import numpy as np
 
@@ -121,6 +122,14 @@ class ShardedIndex:
         a = np.ascontiguousarray(data, dtype=np.uint8)
         n = _U64(0)
         _check(self._lib.kmi_dist_build_fastq(self.local._h, _hptr(a), a.size, file_offset, ctypes.byref(n)))
+        self._stats()
+        return n.value
+
+    def build_file(self, path, format=0):
+        """Index::build_posix(filename, comm): every rank passes the same path and builds from ITS block of the file
+        (kmi_dist_build_file); returns the k-mers generated from this rank's block"""
+        n = _U64(0)
+        _check(self._lib.kmi_dist_build_file(self.local._h, os.fsencode(path), format, ctypes.byref(n)))
         self._stats()
         return n.value
 

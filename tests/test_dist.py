@@ -224,3 +224,82 @@ def test_sharded_build_equals_reference_per_rank(tmp_path, k, rounds, defer):
                 sk = ref["keys"][order]
                 pos = np.searchsorted(sk, q)
                 assert np.array_equal(sk[pos], q) and np.array_equal(v, 2 * ref["counts"][order][pos].astype(np.uint64))
+
+
+# ---- Index::build_posix(filename, comm): ONE file, every rank builds from its block (kmi_dist_build_file) -------------------
+def _file_worker(rank, world, port, out_dir, path, k, fasta, stage_threads):
+    _init(rank, world, port)
+    os.environ["KMI_STAGE_THREADS"] = stage_threads
+    try:
+        import kmerind_b200 as kb
+        from kmerind_b200.dist import ShardedIndex
+        torch.cuda.set_device(rank)
+        mode = kb.MODE_POSITION if fasta else kb.MODE_COUNT
+        with ShardedIndex(k, mode=mode, hash=kb.HASH_FARM, device=rank) as idx:
+            n = idx.build_file(path)
+            if fasta:
+                gk, gi = idx.local.sorted_dump()
+                np.save(os.path.join(out_dir, "fk%d.npy" % rank), gk)
+                np.save(os.path.join(out_dir, "fi%d.npy" % rank), gi)
+                np.save(os.path.join(out_dir, "r%d.npy" % rank), np.array([n, idx.size()], dtype=np.uint64))
+            else:
+                ck = idx.local.checksum()
+                np.save(os.path.join(out_dir, "r%d.npy" % rank), np.array([idx.local_size(), ck[0], ck[1], idx.size(), n, idx.path], dtype=np.uint64))
+            with pytest.raises(kb.KmiError):                      # every rank gets the error, nobody waits in a collective
+                idx.build_file(path + ".missing.fastq")
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("k,stage_threads", [(31, "4"), (63, "4"), (31, "0")])
+def test_sharded_build_from_one_fastq_file(tmp_path, k, stage_threads):
+    """every rank reads ITS record-aligned block of the one file (streamed through the pinned slice ring, or read whole when
+    the ring is off) and the shards must be the REFERENCE's ranks at p = world over the same blocks"""
+    import kmerind_b200 as kb
+    world = max(torch.cuda.device_count(), 1)
+    n_reads = 90000 * world
+    whole = ou.synth_fastq(0, n_reads, 150, 5 * n_reads, 17, 5000, 0)
+    path = tmp_path / "reads.fastq"
+    path.write_bytes(whole.tobytes())
+    mp.spawn(_file_worker, args=(world, _free_port(), str(tmp_path), str(path), k, False, stage_threads), nprocs=world, join=True)
+    cuts = [kb.file_block(str(path), r, world)[0] for r in range(world)] + [whole.size]
+    assert cuts == kb.fastq_cuts(whole, world)
+    got = [np.load(tmp_path / ("r%d.npy" % r)) for r in range(world)]
+    for r in range(world):
+        assert int(got[r][4]) == (cuts[r + 1] - cuts[r]) // 317 * (150 - k + 1) and int(got[r][5]) == 1      # its block's k-mers, NVLink push path
+    ref = ou.ref_count_build_fastq(whole, k, world, 1, cuts=cuts)
+    if ref is None:
+        keys, _, _ = ou.fastq_kmers(whole, k)
+        owner = (ou.hashes(keys, k, 3) % np.uint64(world)).astype(np.int64)
+        sizes, cks = [len(ou.count_sorted(shape_keys(keys, k)[owner == r], k)[0]) for r in range(world)], None
+    else:
+        sizes, cks = ref["sizes"].tolist(), ref["ck"]
+    for r in range(world):
+        assert int(got[r][0]) == int(sizes[r]) and int(got[r][3]) == int(sum(sizes))
+        if cks is not None:
+            assert int(got[r][1]) == int(cks[r, 0]) and int(got[r][2]) == int(cks[r, 1]), "rank %d differs from the reference's rank" % r
+
+
+def shape_keys(keys, k):
+    return ou.shape_keys(np.ascontiguousarray(keys).reshape(-1), k)
+
+
+@pytest.mark.gpu
+def test_sharded_position_index_from_one_fasta_file(tmp_path):
+    """FASTA: rank r takes the byte range [size r / p, size (r + 1) / p) + K-1 halo of the one file; the union of the shards is
+    the oracle's (k-mer, LongSequenceKmerId) list of the whole file"""
+    world = max(torch.cuda.device_count(), 1)
+    k = 21
+    fa = ou.synth_fasta(5, 150000, 70, 3)
+    path = tmp_path / "genome.fasta"
+    path.write_bytes(fa.tobytes())
+    mp.spawn(_file_worker, args=(world, _free_port(), str(tmp_path), str(path), k, True, "4"), nprocs=world, join=True)
+    keys, ids, _ = ou.fasta_kmers(fa, k)
+    sk, si = ou.sort_tuples(keys, ids, k)
+    gk = np.concatenate([np.load(tmp_path / ("fk%d.npy" % r)) for r in range(world)])
+    gi = np.concatenate([np.load(tmp_path / ("fi%d.npy" % r)) for r in range(world)])
+    uk, ui = ou.sort_tuples(gk, gi, k)
+    assert np.array_equal(uk, sk) and np.array_equal(ui, si)
+    tot = sum(int(np.load(tmp_path / ("r%d.npy" % r))[0]) for r in range(world))
+    assert tot == len(keys) and int(np.load(tmp_path / "r0.npy")[1]) == len(keys)

@@ -133,3 +133,46 @@ def test_fasta_blocks_oracle_partition():
     parts = [ou.fasta_block_kmers(buf, 21, a, b) for a, b in zip(cuts, cuts[1:])]
     assert sum(len(p[0]) for p in parts) == len(wk)
     assert np.array_equal(np.sort(np.concatenate([p[1] for p in parts])), np.sort(wi))
+
+
+# ---- row a1: one file, p ranks (partitioned_file::read_file + BlockPartitioner, file.hpp:1239-1251,1342-1431) ----------
+@pytest.mark.parametrize("name", FASTQ)
+@pytest.mark.parametrize("parts", (1, 2, 3, 8, 64))
+def test_file_block_fastq_equals_in_memory_cuts(name, parts, tmp_path):
+    """kmi_file_block reads only windows of the file around the boundaries; its blocks must be the ones kmi::fastq_cuts /
+    kb.fastq_cuts finds with the whole file in memory: whole records, tiling the file, in rank order"""
+    buf = ou.read_fixture(name)
+    path = tmp_path / name
+    path.write_bytes(buf.tobytes())
+    cuts = kb.fastq_cuts(buf, parts)
+    starts = set(record_starts(buf).tolist()) | {buf.size}
+    prev_end = 0
+    for r in range(parts):
+        b, e, size = kb.file_block(str(path), r, parts)
+        assert size == buf.size and (b, e) == (cuts[r], cuts[r + 1]), (name, parts, r)
+        assert b == prev_end and b in starts and e in starts
+        prev_end = e
+    assert prev_end == buf.size
+
+
+def test_file_block_large_windows_fasta_and_errors(tmp_path):
+    # records longer than the first 64 KiB window: the window grows until it holds four lines
+    seq = b"ACGT" * 50000
+    rec = b"@r\n" + seq + b"\n+\n" + b"I" * len(seq) + b"\n"
+    path = tmp_path / "long.fq"
+    path.write_bytes(rec * 3)
+    assert kb.file_block(str(path), 0, 2)[:2] == (0, 2 * len(rec))
+    assert kb.file_block(str(path), 1, 2)[:2] == (2 * len(rec), 3 * len(rec))
+    assert kb.file_block(str(path), 3, 4)[:2] == (3 * len(rec), 3 * len(rec))       # nothing starts after 3/4 of the file
+    # FASTA: the byte ranges as they are; format by extension or explicit
+    fa = tmp_path / "g.fasta"
+    fa.write_bytes(b">a\n" + b"ACGT" * 100 + b"\n")
+    n = fa.stat().st_size
+    assert [kb.file_block(str(fa), r, 3)[:2] for r in range(3)] == [(0, n // 3), (n // 3, 2 * n // 3), (2 * n // 3, n)]
+    assert kb.file_block(str(path), 0, 1, format=2)[:2] == (0, 3 * len(rec))
+    empty = tmp_path / "e.fastq"
+    empty.write_bytes(b"")
+    assert kb.file_block(str(empty), 1, 2) == (0, 0, 0)
+    for bad in ((str(tmp_path / "missing.fastq"), 0, 1), (str(tmp_path / "x.txt"), 0, 1), (str(path), 2, 2), (str(path), -1, 2), (str(path), 0, 0)):
+        with pytest.raises(kb.KmiError):
+            kb.file_block(*bad)
