@@ -434,7 +434,7 @@ extern "C" void kmi_destroy(kmi_index* idx) {
   DevBuf* bufs[] = {&idx->tile_lines, &idx->block_sums, &idx->stage_in, &idx->stage_keys, &idx->stage_vals,
                     &idx->stage_out, &idx->stage_found, &idx->hist, &idx->hist_sums, &idx->log_keys, &idx->log_ids,
                     &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->mid_keys, &idx->mid_cur,
-                    &idx->pend_ovf, &idx->pend_ovf_cur, &idx->pend_cur_save};
+                    &idx->pend_ovf, &idx->pend_ovf_cur, &idx->pend_cur_save, &idx->scan_tmp};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 6; ++i) if (idx->ev[i]) cudaEventDestroy(idx->ev[i]);
   for (int i = 0; i < 4; ++i) if (idx->kev[i]) cudaEventDestroy(idx->kev[i]);
@@ -1330,6 +1330,22 @@ static int csr_finalize(kmi_index* idx) {
   return KMI_OK;
 }
 
+int kmi::scan64_dev(kmi_index* idx, u64* d_v, u64 n) {
+  if (n == 0) return KMI_OK;
+  if (n <= 8192) {
+    k_scan64<<<1, 1024, 0, idx->stream>>>(d_v, n);
+    idx->launches++;
+    return KMI_OK;
+  }
+  const u64 nb = (n + 1023) / 1024;
+  OK(idx->scan_tmp.ensure(nb * sizeof(u64)));
+  k_scan64_l1<<<(unsigned)nb, 1024, 0, idx->stream>>>(d_v, n, idx->scan_tmp.as<u64>());
+  k_scan64<<<1, 1024, 0, idx->stream>>>(idx->scan_tmp.as<u64>(), nb);
+  k_csr_add_block<<<(unsigned)nb, 1024, 0, idx->stream>>>(d_v, n, idx->scan_tmp.as<u64>());
+  idx->launches += 3;
+  return KMI_OK;
+}
+
 // ---- batched query -----------------------------------------------------------------------------------
 extern "C" int kmi_find_dev(kmi_index* idx, const uint64_t* d_keys, size_t n, uint64_t* d_vals, uint8_t* d_found) {
   if (!idx || (!d_keys && n)) return fail(KMI_ERR_ARG, "null argument");
@@ -1390,6 +1406,28 @@ extern "C" int kmi_find(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t
   return KMI_OK;
 }
 
+int kmi::find_positions_dev(kmi_index* idx, const u64* d_keys, u64 m, u64* d_off, DevBuf& slot_idx, DevBuf& vals, u64* total) {
+  *total = 0;
+  CU(cudaMemsetAsync(d_off, 0, (m + 1) * sizeof(u64), idx->stream));
+  if (m == 0 || !idx->slots) return KMI_OK;
+  OK(csr_finalize(idx));
+  OK(slot_idx.ensure(m * sizeof(u64)));
+  // multiplicities -> exclusive scan (m + 1 entries) -> gather
+  idx->ops->lookup(idx->stream, idx->view(), d_keys, m, d_off, nullptr, slot_idx.as<u64>(), false);
+  idx->launches++;
+  OK(scan64_dev(idx, d_off, m + 1));
+  CU(cudaMemcpyAsync(total, d_off + m, sizeof(u64), cudaMemcpyDeviceToHost, idx->stream));
+  CU(cudaStreamSynchronize(idx->stream));
+  if (*total) {
+    OK(vals.ensure(*total * sizeof(u64)));
+    k_csr_gather<<<grid_for(m, 256), 256, 0, idx->stream>>>(slot_idx.as<u64>(), d_off, m, idx->offsets.as<u64>(), idx->values.as<u64>(),
+                                                          vals.as<u64>(), *total);
+    idx->launches++;
+  }
+  CU(cudaGetLastError());
+  return KMI_OK;
+}
+
 extern "C" int kmi_find_positions(kmi_index* idx, const uint64_t* keys, size_t n, uint64_t* offsets, uint64_t* vals, size_t cap) {
   if (!idx || (!keys && n) || !offsets) return fail(KMI_ERR_ARG, "null argument");
   if (idx->cfg.mode != KMI_MODE_POSITION) return fail(KMI_ERR_ARG, "find_positions needs a POSITION index");
@@ -1407,9 +1445,9 @@ extern "C" int kmi_find_positions(kmi_index* idx, const uint64_t* keys, size_t n
   cudaMemsetAsync(out_off.p, 0, (n + 1) * sizeof(u64), idx->stream);
   idx->ops->lookup(idx->stream, idx->view(), idx->stage_keys.as<u64>(), n, out_off.as<u64>(), nullptr, slot_idx.as<u64>(),
                    idx->cfg.canonical != 0);
-  k_scan64<<<1, 1024, 0, idx->stream>>>(out_off.as<u64>(), n + 1);
-  idx->launches += 2;
-  r = copy_to_host(idx, offsets, out_off.p, (n + 1) * sizeof(u64));
+  idx->launches++;
+  r = scan64_dev(idx, out_off.as<u64>(), n + 1);
+  if (r == KMI_OK) r = copy_to_host(idx, offsets, out_off.p, (n + 1) * sizeof(u64));
   cudaStreamSynchronize(idx->stream);
   if (r != KMI_OK) { slot_idx.release(); out_off.release(); return r; }
   u64 total = offsets[n];
@@ -1616,7 +1654,7 @@ extern "C" int kmi_table_info(kmi_index* idx, uint64_t* slots, uint64_t* slot_by
     const DevBuf* bufs[] = {&idx->tile_lines, &idx->block_sums, &idx->stage_in, &idx->stage_keys, &idx->stage_vals,
                             &idx->stage_out, &idx->stage_found, &idx->hist, &idx->hist_sums, &idx->log_keys, &idx->log_ids,
                             &idx->log_keys2, &idx->log_ids2, &idx->offsets, &idx->csr_sums, &idx->values, &idx->bkt_keys, &idx->bkt_meta, &idx->fine_keys, &idx->fine_cur, &idx->parse_keys, &idx->parse_ids, &idx->tile_rec, &idx->mid_keys, &idx->mid_cur,
-                            &idx->pend_ovf, &idx->pend_ovf_cur, &idx->pend_cur_save};
+                            &idx->pend_ovf, &idx->pend_ovf_cur, &idx->pend_cur_save, &idx->scan_tmp};
     for (const DevBuf* d : bufs) b += d->cap;
     *device_bytes = b;
   }

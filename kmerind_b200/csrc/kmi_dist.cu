@@ -104,6 +104,7 @@ struct kmi_dist_state {
   cudaEvent_t ev_parsed[2] = {nullptr, nullptr}, ev_pushed[2] = {nullptr, nullptr}, ev_t[4] = {nullptr, nullptr, nullptr, nullptr};
   // generic exchange scratch
   DevBuf part_keys, part_vals, recv_keys, recv_vals, q_keys, q_tags, q_vals, q_found, q_back, q_backf, text, keys, ids;
+  DevBuf fp_cnt, fp_slot, fp_part_off, fp_out_off, fp_out_vals;   // sharded find_positions: multiplicities, slots, the two offset arrays, the CSR values
   u64 n_received = 0;
   float ms[4] = {0, 0, 0, 0};           // last build: [0] whole, [1] parse + push + exchange, [2] insert of received keys, [3] unused
   int last_path = 0;                    // 1 = NVLink push, 2 = generic NCCL exchange
@@ -282,6 +283,19 @@ int insert_owned(kmi_index* idx, const u64* d_keys, const u64* d_vals, u64 n) {
   return r;
 }
 
+// cnt[i] = off[i + 1] - off[i]
+__global__ void k_adj_diff(const u64* __restrict__ off, u64* __restrict__ cnt, u64 n) {
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) cnt[i] = off[i + 1] - off[i];
+}
+// sharded find_positions: query i (partition order, input position tags[i]) got cnt[i] ids at src_off[i] of the stream that
+// came back; they belong at dst_off[tags[i]] of the caller's CSR
+__global__ void k_place_ids(const u64* __restrict__ tags, const u64* __restrict__ cnt, const u64* __restrict__ src_off,
+                            const u64* __restrict__ dst_off, const u64* __restrict__ got, u64* __restrict__ out, u64 n) {
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+    const u64 c = cnt[i], s0 = src_off[i], d0 = dst_off[tags[i]];
+    for (u64 j = 0; j < c; ++j) out[d0 + j] = got[s0 + j];
+  }
+}
 __global__ void k_iota(u64* out, u64 n) {
   for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) out[i] = i;
 }
@@ -306,7 +320,8 @@ void kmi_dist_release(kmi_index* idx) {
   peers_close(idx);
   DevBuf* bufs[] = {&d->peer_keys, &d->peer_cnt, &d->push_cursor, &d->status, &d->stage_keys[0], &d->stage_keys[1], &d->stage_meta[0],
                     &d->stage_meta[1], &d->part_keys, &d->part_vals, &d->recv_keys, &d->recv_vals, &d->q_keys, &d->q_tags, &d->q_vals,
-                    &d->q_found, &d->q_back, &d->q_backf, &d->text, &d->keys, &d->ids};
+                    &d->q_found, &d->q_back, &d->q_backf, &d->text, &d->keys, &d->ids, &d->fp_cnt, &d->fp_slot, &d->fp_part_off,
+                    &d->fp_out_off, &d->fp_out_vals};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 2; ++i) { if (d->ev_parsed[i]) cudaEventDestroy(d->ev_parsed[i]); if (d->ev_pushed[i]) cudaEventDestroy(d->ev_pushed[i]); }
   for (int i = 0; i < 4; ++i) if (d->ev_t[i]) cudaEventDestroy(d->ev_t[i]);
@@ -603,64 +618,54 @@ extern "C" int kmi_dist_find_positions(kmi_index* idx, const uint64_t* keys, siz
   for (int s = 0; s < p; ++s) m += rc[s];
   OK(d->recv_keys.ensure(std::max<u64>(m, 1) * kb));
   OK(exchange_rows(d, st, d->part_keys.p, sc.data(), rc.data(), kb, d->recv_keys.p));
-  // 2. local answer for the m received queries (host CSR through the single-shard call), multiplicities back
-  std::vector<u64> hk(std::max<u64>(m, 1) * idx->nw), hoff(m + 1, 0), hcnt(std::max<u64>(m, 1), 0);
-  if (m) CU(cudaMemcpyAsync(hk.data(), d->recv_keys.p, m * kb, cudaMemcpyDeviceToHost, st));
-  CU(cudaStreamSynchronize(st));
-  std::vector<u64> hvals;
-  int lr = KMI_OK;
-  {
-    const int32_t canon = idx->cfg.canonical;
-    idx->cfg.canonical = 0;
-    if (m) {
-      lr = kmi_count(idx, A(hk.data()), m, A(hcnt.data()));
-      u64 total = 0;
-      for (u64 i = 0; i < m; ++i) total += hcnt[i];
-      hvals.assign(std::max<u64>(total, 1), 0);
-      if (lr == KMI_OK) lr = kmi_find_positions(idx, A(hk.data()), m, A(hoff.data()), A(hvals.data()), total);
-    }
-    idx->cfg.canonical = canon;
-  }
+  // 2. local answers for the m received queries, all on the device: offsets (exclusive scan of the multiplicities) and the ids
+  // of every hit in query order; the multiplicities go back to the asking ranks
+  OK(d->q_vals.ensure((m + 1) * sizeof(u64)));
+  OK(d->fp_cnt.ensure(std::max<u64>(m, 1) * sizeof(u64)));
+  u64 total_send = 0;
+  const int lr = find_positions_dev(idx, d->recv_keys.as<u64>(), m, d->q_vals.as<u64>(), d->fp_slot, d->recv_vals, &total_send);
   u64 bad = lr != KMI_OK;
   OK(comm_allreduce(d->comm, &bad, 1, ncclMax, st));
   if (bad) return lr != KMI_OK ? lr : fail(KMI_ERR_CUDA, "another rank failed in find_positions");
-  OK(d->q_vals.ensure(std::max<u64>(m, 1) * sizeof(u64)));
-  if (m) CU(cudaMemcpyAsync(d->q_vals.p, hcnt.data(), m * sizeof(u64), cudaMemcpyHostToDevice, st));
+  if (m) k_adj_diff<<<grid_for(m, 256), 256, 0, st>>>(d->q_vals.as<u64>(), d->fp_cnt.as<u64>(), m);
   OK(d->q_back.ensure(std::max<size_t>(n, 1) * sizeof(u64)));
-  OK(exchange_rows(d, st, d->q_vals.p, rc.data(), sc.data(), sizeof(u64), d->q_back.p));
-  std::vector<u64> back_cnt(std::max<size_t>(n, 1), 0), tags(std::max<size_t>(n, 1), 0);
-  if (n) {
-    CU(cudaMemcpyAsync(back_cnt.data(), d->q_back.p, n * sizeof(u64), cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(tags.data(), d->part_vals.p, n * sizeof(u64), cudaMemcpyDeviceToHost, st));
-  }
-  CU(cudaStreamSynchronize(st));
-  // 3. ids back: rank s answers my queries for it with sum(back_cnt over that group) ids, in query order
-  std::vector<u64> ids_send(p, 0), ids_recv(p, 0);
+  OK(exchange_rows(d, st, d->fp_cnt.p, rc.data(), sc.data(), sizeof(u64), d->q_back.p));      // back_cnt, in partition order
+  // where every query's ids will sit in the stream of ids that comes back (groups arrive in rank order, each in the order the
+  // queries were sent: the partition order), and where they belong in the caller's order
+  OK(d->fp_part_off.ensure((n + 1) * sizeof(u64)));
+  OK(d->fp_out_off.ensure((n + 1) * sizeof(u64)));
+  if (n) CU(cudaMemcpyAsync(d->fp_part_off.p, d->q_back.p, n * sizeof(u64), cudaMemcpyDeviceToDevice, st));
+  CU(cudaMemsetAsync(d->fp_part_off.as<u64>() + n, 0, sizeof(u64), st));
+  OK(scan64_dev(idx, d->fp_part_off.as<u64>(), n + 1));
+  CU(cudaMemsetAsync(d->fp_out_off.p, 0, (n + 1) * sizeof(u64), st));
+  if (n) k_unpermute<<<grid_for(n, 256), 256, 0, st>>>(d->part_vals.as<u64>(), d->q_back.as<u64>(), nullptr, d->fp_out_off.as<u64>(), nullptr, n);
+  OK(scan64_dev(idx, d->fp_out_off.as<u64>(), n + 1));
+  // 3. ids back: rank s answers my queries for it with sum(back_cnt over that group) ids. The per-rank sums are differences
+  // of the two offset arrays at the group boundaries: p + 1 words each way
+  std::vector<u64> ids_send(p, 0), ids_recv(p, 0), bs(p + 1, 0), br(p + 1, 0);
   {
-    u64 q = 0;
-    for (int s = 0; s < p; ++s) { for (u64 i = 0; i < rc[s]; ++i) ids_send[s] += hcnt[q + i]; q += rc[s]; }
-    q = 0;
-    for (int s = 0; s < p; ++s) { for (u64 i = 0; i < sc[s]; ++i) ids_recv[s] += back_cnt[q + i]; q += sc[s]; }
+    u64 qs = 0, qr = 0;
+    for (int r = 0; r <= p; ++r) {
+      CU(cudaMemcpyAsync(&bs[r], d->q_vals.as<u64>() + qs, sizeof(u64), cudaMemcpyDeviceToHost, st));
+      CU(cudaMemcpyAsync(&br[r], d->fp_part_off.as<u64>() + qr, sizeof(u64), cudaMemcpyDeviceToHost, st));
+      if (r < p) { qs += rc[r]; qr += sc[r]; }
+    }
+    CU(cudaStreamSynchronize(st));
+    for (int r = 0; r < p; ++r) { ids_send[r] = bs[r + 1] - bs[r]; ids_recv[r] = br[r + 1] - br[r]; }
   }
-  u64 total_send = 0, total_recv = 0;
-  for (int s = 0; s < p; ++s) { total_send += ids_send[s]; total_recv += ids_recv[s]; }
-  OK(d->recv_vals.ensure(std::max<u64>(total_send, 1) * sizeof(u64)));
+  const u64 total_recv = br[p];
   OK(d->keys.ensure(std::max<u64>(total_recv, 1) * sizeof(u64)));
-  if (total_send) CU(cudaMemcpyAsync(d->recv_vals.p, hvals.data(), total_send * sizeof(u64), cudaMemcpyHostToDevice, st));
+  OK(d->recv_vals.ensure(std::max<u64>(total_send, 1) * sizeof(u64)));                        // (untouched when there were no hits)
   OK(exchange_rows(d, st, d->recv_vals.p, ids_send.data(), ids_recv.data(), sizeof(u64), d->keys.p));
-  std::vector<u64> got(std::max<u64>(total_recv, 1), 0);
-  if (total_recv) CU(cudaMemcpyAsync(got.data(), d->keys.p, total_recv * sizeof(u64), cudaMemcpyDeviceToHost, st));
-  CU(cudaStreamSynchronize(st));
   // 4. CSR in input order
-  for (size_t i = 0; i <= n; ++i) offsets[i] = 0;
-  for (size_t i = 0; i < n; ++i) offsets[tags[i] + 1] = back_cnt[i];
-  for (size_t i = 0; i < n; ++i) offsets[i + 1] += offsets[i];
-  if (offsets[n] > cap) return fail(KMI_ERR_CAPACITY, "find_positions: %llu values, capacity %zu", (unsigned long long)offsets[n], cap);
-  u64 at = 0;
-  for (size_t i = 0; i < n; ++i) {
-    if (back_cnt[i]) memcpy(vals + offsets[tags[i]], got.data() + at, back_cnt[i] * sizeof(u64));
-    at += back_cnt[i];
-  }
+  if (total_recv > cap) { CU(cudaStreamSynchronize(st)); return fail(KMI_ERR_CAPACITY, "find_positions: %llu values, capacity %zu", (unsigned long long)total_recv, cap); }
+  OK(d->fp_out_vals.ensure(std::max<u64>(total_recv, 1) * sizeof(u64)));
+  if (n && total_recv) k_place_ids<<<grid_for(n, 256), 256, 0, st>>>(d->part_vals.as<u64>(), d->q_back.as<u64>(), d->fp_part_off.as<u64>(), d->fp_out_off.as<u64>(),
+                                                                     d->keys.as<u64>(), d->fp_out_vals.as<u64>(), n);
+  OK(copy_to_host(idx, offsets, d->fp_out_off.p, (n + 1) * sizeof(u64)));
+  if (total_recv) OK(copy_to_host(idx, vals, d->fp_out_vals.p, total_recv * sizeof(u64)));
+  CU(cudaStreamSynchronize(st));
+  CU(cudaGetLastError());
   return KMI_OK;
 }
 

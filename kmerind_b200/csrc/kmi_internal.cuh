@@ -73,7 +73,7 @@ struct kmi_index {
   kmi::DevBuf mid_keys, mid_cur;        // first of two fine passes (very large tables)
   kmi::DevBuf parse_keys, parse_ids;   // staging of the parse -> insert builds (FASTA, FASTQ positions): kept between calls
   kmi::DevBuf tile_rec;   // FASTQ position ids: record start open at every tile (k_fastq_rec_carry)
-  kmi::DevBuf tile_lines, block_sums, stage_in, stage_keys, stage_vals, stage_out, stage_found, hist, hist_sums;
+  kmi::DevBuf tile_lines, block_sums, stage_in, stage_keys, stage_vals, stage_out, stage_found, hist, hist_sums, scan_tmp;
   // POSITION mode: tuple log + CSR
   kmi::DevBuf log_keys, log_ids, log_keys2, log_ids2, offsets, csr_sums, values;
   kmi::u64 log_n = 0;
@@ -152,6 +152,11 @@ int fastq_scan_range(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64 t0, u
 int bucket_prepare(kmi_index* idx, u64 max_keys, BucketSink* bs);
 int fastq_scan(kmi_index* idx, const uint8_t* d_bytes, size_t n, u64* n_tiles_out);
 void harvest_commit_times(kmi_index* idx);
+// in-place exclusive scan of n u64 values on the index's stream (two levels above 8192 values)
+int scan64_dev(kmi_index* idx, u64* d_v, u64 n);
+// POSITION index, everything left on the device: for m keys AS GIVEN (no transform) d_off[0..m] = exclusive scan of their
+// multiplicities, vals = the ids of every hit in query order (grown as needed), *total = d_off[m] (read back: one sync)
+int find_positions_dev(kmi_index* idx, const u64* d_keys, u64 m, u64* d_off, DevBuf& slot_idx, DevBuf& vals, u64* total);
 // ---- host <-> device copies (kmi_api.cu). Large copies whose host side is PAGEABLE go through the index's ring of pinned
 // slices, filled / drained by host threads (kmi_hoststage.hpp); pinned or small ones are plain cudaMemcpyAsync.
 // copy_to_device: on return the caller's memory has been read (or is pinned and the copy enqueued) and idx->stream is ordered

@@ -342,6 +342,36 @@ __global__ void __launch_bounds__(1024) k_scan64(u64* __restrict__ v, u64 n) {
     __syncthreads();
   }
 }
+// level 1 of a multi-block exclusive scan of u64 values: every block scans its 1024 values in place and writes its total
+// (k_scan64 over the totals and k_csr_add_block finish it: kmi::scan64_dev)
+__global__ void __launch_bounds__(1024) k_scan64_l1(u64* __restrict__ v, u64 n, u64* __restrict__ block_sums) {
+  __shared__ u64 tmp[33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const u64 i = (u64)blockIdx.x * 1024 + threadIdx.x;
+  const u64 x = (i < n) ? v[i] : 0;
+  u64 inc = x;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const u64 o = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += o;
+  }
+  if (lane == 31) tmp[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    const u64 w = tmp[lane];
+    u64 winc = w;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const u64 o = __shfl_up_sync(0xffffffffu, winc, d);
+      if (lane >= d) winc += o;
+    }
+    tmp[lane] = winc - w;
+    if (lane == 31) tmp[32] = winc;
+  }
+  __syncthreads();
+  if (i < n) v[i] = tmp[warp] + inc - x;
+  if (threadIdx.x == 0) block_sums[blockIdx.x] = tmp[32];
+}
 __global__ void __launch_bounds__(1024) k_csr_add_block(u64* __restrict__ offsets, u64 n, const u64* __restrict__ block_sums) {
   u64 i = (u64)blockIdx.x * 1024 + threadIdx.x;
   if (i < n) offsets[i] += block_sums[blockIdx.x];

@@ -242,6 +242,19 @@ def _file_worker(rank, world, port, out_dir, path, k, fasta, stage_threads):
                 np.save(os.path.join(out_dir, "fk%d.npy" % rank), gk)
                 np.save(os.path.join(out_dir, "fi%d.npy" % rank), gi)
                 np.save(os.path.join(out_dir, "r%d.npy" % rank), np.array([n, idx.size()], dtype=np.uint64))
+                # sharded find_positions (answered on the device, ids exchanged back, CSR in input order) from every rank:
+                # 20000 k-mers of the file on the other strand + absent keys, against the oracle's tuples
+                fa = np.fromfile(path, dtype=np.uint8)
+                keys, ids, _ = ou.fasta_kmers(fa, k)
+                sk, si = ou.sort_tuples(keys, ids, k)
+                q = np.concatenate([ou.revcomp(keys[rank::37][:20000], k), ou.random_keys(k, 3000, 5 + rank)])
+                off, vals = idx.find_positions(q)
+                cq = ou.canonical(q, k)
+                lo, hi = np.searchsorted(sk, cq, "left"), np.searchsorted(sk, cq, "right")
+                assert np.array_equal(np.diff(off.astype(np.int64)), hi - lo) and int(off[-1]) == len(vals)
+                want = np.concatenate([si[a:b] for a, b in zip(lo, hi)])
+                grp = np.repeat(np.arange(len(q)), hi - lo)
+                assert np.array_equal(vals[np.lexsort((vals, grp))], want)       # (ids of one key come in any order)
             else:
                 ck = idx.local.checksum()
                 np.save(os.path.join(out_dir, "r%d.npy" % rank), np.array([idx.local_size(), ck[0], ck[1], idx.size(), n, idx.path], dtype=np.uint64))
