@@ -5,6 +5,7 @@
 //   ref_t1 fasta_pos  K file  ->  (k-mer words, LongSequenceKmerId) over FASTAParser
 //   ref_t1 count      K file  ->  sorted (canonical k-mer, count) of CountIndex<counting_densehash_map, lex_less, farm> built by
 //                                  Index::build_posix / insert — the reference's whole path, end to end
+//   ref_t1 first_record 0 file ->  FASTQParser::find_first_record over a grid of search ranges + the p-rank block boundaries
 //   ref_t1 adapter    K file  ->  the reference's Index<> template instantiated with kmi::b200_map as MapType (compile-time
 //                                  proof of the drop-in; needs a GPU to run)
 // Nothing here is copied: it only includes and drives reference headers.
@@ -101,12 +102,55 @@ template <unsigned K> struct B200Count {
 };
 #endif
 
+// the reference's FASTQParser::find_first_record (fastq_loader.hpp:269-357) on its own, over the byte ranges a partitioned read
+// hands it: for every cut c of a grid over the file, the search range [c, c + window) clipped to the file, the file being the
+// parent and in memory whole. One row per call: c, end of the search range, result (or ~0 when the reference throws: no FASTQ
+// markers in a range that does not reach the parent's end). Also the block boundaries of p ranks as partitioned_file<..,
+// FASTQParser>::read_file computes them (file.hpp:1342-1431): find_first_record over [size * r / p, size).
+static int dump_first_record(const std::string& file, const char* out) {
+  std::vector<unsigned char> data;
+  {
+    FILE* f = fopen(file.c_str(), "rb");
+    if (!f) return 2;
+    unsigned char buf[65536];
+    size_t got;
+    while ((got = fread(buf, 1, sizeof(buf), f)) > 0) data.insert(data.end(), buf, buf + got);
+    fclose(f);
+  }
+  typedef bliss::partition::range<size_t> Range;
+  const size_t n = data.size();
+  bliss::io::FASTQParser<unsigned char*> parser;
+  std::vector<uint64_t> rows;
+  auto call = [&](size_t b, size_t e) {
+    uint64_t r;
+    try { r = parser.find_first_record(data.data(), Range(0, n), Range(0, n), Range(b, e)); }
+    catch (const std::exception&) { r = ~0ULL; }
+    rows.push_back(b); rows.push_back(e); rows.push_back(r);
+  };
+  const size_t step = std::max<size_t>(1, n / 400);
+  const size_t windows[] = {n, 64, 300, 1000, 5000};
+  for (size_t w : windows)
+    for (size_t c = 0; c <= n; c += step) call(c, std::min(n, c + w));
+  const int parts[] = {2, 3, 8, 64};
+  for (int p : parts)
+    for (int r = 0; r <= p; ++r) call((size_t)((unsigned __int128)n * r / p), n);
+  FILE* f = fopen(out, "wb");
+  if (!f) return 2;
+  const uint64_t nr = rows.size() / 3, nw = 2;   // same container as the other dumps: nr rows of (nw + 1) words
+  put(f, &nr, 8); put(f, &nw, 8);
+  put(f, rows.data(), rows.size() * 8);
+  fclose(f);
+  std::printf("%s: %llu calls of find_first_record\n", out, (unsigned long long)nr);
+  return 0;
+}
+
 int main(int argc, char** argv) {
   mxx::env e(argc, argv);
   mxx::comm comm;
   if (argc < 5) { std::fprintf(stderr, "usage: ref_t1 fastq_pos|fasta_pos|count K file out\n"); return 1; }
   const std::string what = argv[1], file = argv[3];
   const int K = std::atoi(argv[2]);
+  if (what == "first_record") return dump_first_record(file, argv[4]);
   if (what == "fastq_pos") {
     using Id = bliss::common::ShortSequenceKmerId;
     if (K == 21) return dump_positions<21, Id, bliss::io::FASTQParser>(file, argv[4], comm);

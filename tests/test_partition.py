@@ -176,3 +176,51 @@ def test_file_block_large_windows_fasta_and_errors(tmp_path):
     for bad in ((str(tmp_path / "missing.fastq"), 0, 1), (str(tmp_path / "x.txt"), 0, 1), (str(path), 2, 2), (str(path), -1, 2), (str(path), 0, 0)):
         with pytest.raises(kb.KmiError):
             kb.file_block(*bad)
+
+
+# ---- pinned to the REFERENCE's own find_first_record, executed (tests/golden/make_golden_first_record.py) -------------------
+def _golden_first_record():
+    import os
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_first_record.npz"))
+
+
+def _golden_text(name):
+    if name.startswith("synthetic."):
+        import importlib.util
+        import os
+        spec = importlib.util.spec_from_file_location("mgfr", os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "make_golden_first_record.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        return np.frombuffer(mod.synthetic()[name], dtype=np.uint8)
+    return ou.read_fixture(name)
+
+
+@pytest.mark.parametrize("name", sorted(_golden_first_record().files))
+def test_find_first_record_equals_the_reference_function(name, tmp_path):
+    """every row is one call of the reference's FASTQParser::find_first_record (fastq_loader.hpp:269-357; compiled from the
+    reference, oracle tier T1): search range [b, e) of the file, result or 'throws'. The C ABI function, the C oracle's
+    restatement and — for the rows that are p-rank block boundaries — kmi_file_block on the file on disk must all agree."""
+    rows = _golden_first_record()[name]
+    buf = _golden_text(name)
+    n = buf.size
+    throws = np.uint64(2**64 - 1)
+    for b, e, want in rows.tolist():
+        if want == int(throws):
+            with pytest.raises(kb.KmiFormatError):
+                kb.fastq_find_first_record(buf, b, e, parent=(0, n))
+            with pytest.raises(ValueError):
+                ou.fastq_find_first_record(buf, b, e, 0, (0, n))
+        else:
+            assert kb.fastq_find_first_record(buf, b, e, parent=(0, n)) == want, (name, b, e)
+            assert ou.fastq_find_first_record(buf, b, e, 0, (0, n)) == want, (name, b, e)
+    # partitioned_file::read_file: rank r's block begins at find_first_record over [n r / p, n)
+    path = tmp_path / name
+    path.write_bytes(buf.tobytes())
+    whole = {int(b): int(w) for b, e, w in rows.tolist() if e == n and w != int(throws)}
+    for p in (2, 3, 8, 64):
+        # (rank 0 begins at byte 0 by definition — where the reference's search from 0 lands in any file that starts with a
+        #  record; a text without records, like the junk one, is left to the parser to reject instead of being skipped)
+        cuts = [0] + [whole[n * r // p] for r in range(1, p)] + [n]
+        for r in range(p):
+            b, e, size = kb.file_block(str(path), r, p, format=1)
+            assert (b, e) == (cuts[r], max(cuts[r], cuts[r + 1])), (name, p, r)
