@@ -316,3 +316,32 @@ def test_sharded_position_index_from_one_fasta_file(tmp_path):
     assert np.array_equal(uk, sk) and np.array_equal(ui, si)
     tot = sum(int(np.load(tmp_path / ("r%d.npy" % r))[0]) for r in range(world))
     assert tot == len(keys) and int(np.load(tmp_path / "r0.npy")[1]) == len(keys)
+
+
+# ---- CPU, world_size 2: the blocks two ranks take from ONE file (kmi_file_block: host code, no GPU) tile it at record starts ---
+def _gloo_file_block_worker(rank, world, port, out_dir, path):
+    _init(rank, world, port)
+    try:
+        import kmerind_b200 as kb
+        b, e, size = kb.file_block(path, rank, world)
+        every = [None] * world
+        dist.all_gather_object(every, (b, e, size))
+        np.save(os.path.join(out_dir, "blocks%d.npy" % rank), np.array(every, dtype=np.int64))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("name", ("natural.fastq", "test.medium.fastq"))
+def test_file_blocks_gloo_world2(tmp_path, name):
+    """what kmi_dist_build_file does first on every rank: rank r's block of the shared file. Both ranks must see the same
+    partition, it must tile the file, and the inner boundary must be the record start the in-memory cut finds"""
+    import kmerind_b200 as kb
+    world = 2
+    buf = ou.read_fixture(name)
+    path = tmp_path / name
+    path.write_bytes(buf.tobytes())
+    mp.spawn(_gloo_file_block_worker, args=(world, _free_port(), str(tmp_path), str(path)), nprocs=world, join=True)
+    a, b = (np.load(tmp_path / ("blocks%d.npy" % r)) for r in range(world))
+    assert np.array_equal(a, b)
+    cuts = kb.fastq_cuts(buf, world)
+    assert a[:, :2].tolist() == [[cuts[0], cuts[1]], [cuts[1], cuts[2]]] and (a[:, 2] == buf.size).all()
