@@ -24,6 +24,8 @@ def test_stage_threads_on_fake_device(tmp_path, flags):
     assert r.returncode == 0, r.stderr
     for _ in range(3):
         out = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+        if flags and "FATAL: ThreadSanitizer" in out.stderr and "memory mapping" in out.stderr:
+            pytest.skip("ThreadSanitizer cannot run under this kernel's address-space layout")
         assert out.returncode == 0 and "stage_check ok" in out.stdout, out.stdout + out.stderr
 
 
